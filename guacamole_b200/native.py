@@ -1,0 +1,285 @@
+"""ctypes binding of libguac_b200.so (include/guac_b200.h).
+
+This is the tested consumer of the C ABI in this repository (the Scala/JNI shim of
+INTEGRATION.md binds the same symbols).  There is no CPU fallback: if the shared library
+is missing, or no CUDA device is present, constructing a Context raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .io import Reference
+from .reads import ReadBatch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libguac_b200.so")
+
+
+class GuacError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"guac status {status}: {message}")
+        self.status = status
+        self.message = message
+
+
+GUAC_OK, GUAC_E_INVALID_INPUT, GUAC_E_CUDA, GUAC_E_NO_DEVICE, GUAC_E_OOM, GUAC_E_UNSUPPORTED, GUAC_E_STATE = 0, -1, -2, -3, -4, -5, -6
+
+u8p, u32p, u64p, i32p, i64p = (C.POINTER(t) for t in (C.c_uint8, C.c_uint32, C.c_uint64, C.c_int32, C.c_int64))
+
+
+class ReadBatchC(C.Structure):
+    _fields_ = [("n_reads", C.c_int64), ("n_samples", C.c_int32), ("contig_id", i32p), ("start", i64p),
+                ("cigar_off", u32p), ("cigar", u32p), ("seq_off", u64p), ("bases2", u8p), ("nmask", u8p),
+                ("n_exc", C.c_int64), ("exc_pos", u64p), ("exc_base", u8p), ("qual", u8p), ("mapq", u8p),
+                ("flags", u8p), ("sample_id", u8p)]
+
+
+class RangeC(C.Structure):
+    _fields_ = [("contig_id", C.c_int32), ("_pad", C.c_int32), ("start", C.c_int64), ("end", C.c_int64)]
+
+
+class LocusCountsC(C.Structure):
+    _fields_ = [(n, C.c_uint32) for n in ("depth", "reference_depth", "positive_depth", "mismatches", "insertions",
+                                          "deletions", "mid_deletions", "clipped")]
+
+
+class ElementC(C.Structure):
+    _fields_ = [("read_index", C.c_int64), ("read_position", C.c_int32), ("cigar_element_index", C.c_int32),
+                ("cigar_element_locus", C.c_int64), ("index_within_cigar_element", C.c_int32), ("kind", C.c_uint8),
+                ("base", C.c_uint8), ("quality", C.c_uint8), ("sample_id", C.c_uint8), ("indel_length", C.c_int32),
+                ("_pad", C.c_int32)]
+
+
+class AlleleEvidenceC(C.Structure):
+    _fields_ = [("probability", C.c_double), ("read_depth", C.c_int32), ("allele_read_depth", C.c_int32),
+                ("forward_depth", C.c_int32), ("allele_forward_depth", C.c_int32), ("mean_mapping_quality", C.c_double),
+                ("median_mapping_quality", C.c_double), ("mean_base_quality", C.c_double),
+                ("median_base_quality", C.c_double), ("median_mismatches_per_read", C.c_double)]
+
+
+class SSParamsC(C.Structure):
+    _fields_ = [("normal_sample_id", C.c_int32), ("tumor_sample_id", C.c_int32), ("normal_odds_threshold", C.c_int32),
+                ("tumor_odds_threshold", C.c_int32), ("max_read_depth", C.c_int32),
+                ("max_normal_alternate_read_depth", C.c_int32), ("min_tumor_variant_allele_frequency", C.c_float),
+                ("_pad", C.c_int32)]
+
+
+class SSCallC(C.Structure):
+    _fields_ = [("contig_id", C.c_int32), ("_pad", C.c_int32), ("start", C.c_int64), ("ref_off", C.c_uint32),
+                ("ref_len", C.c_uint32), ("alt_off", C.c_uint32), ("alt_len", C.c_uint32), ("somatic_log_odds", C.c_double),
+                ("tumor_ref_log_prob", C.c_double), ("tumor_alt_log_prob", C.c_double), ("normal_ref_log_prob", C.c_double),
+                ("normal_alt_log_prob", C.c_double), ("tumor_variant_evidence", AlleleEvidenceC),
+                ("normal_reference_evidence", AlleleEvidenceC)]
+
+
+class LocusSummaryC(C.Structure):
+    _fields_ = [("depth", C.c_uint16), ("reference_depth", C.c_uint16), ("top_alt_count", C.c_uint16), ("flags", C.c_uint16)]
+
+
+LOCUS_COUNTS_DTYPE = np.dtype([(n, np.uint32) for n, _ in LocusCountsC._fields_])
+ELEMENT_DTYPE = np.dtype([("read_index", np.int64), ("read_position", np.int32), ("cigar_element_index", np.int32),
+                          ("cigar_element_locus", np.int64), ("index_within_cigar_element", np.int32), ("kind", np.uint8),
+                          ("base", np.uint8), ("quality", np.uint8), ("sample_id", np.uint8), ("indel_length", np.int32),
+                          ("_pad", np.int32)])
+_EV = [("probability", np.float64), ("read_depth", np.int32), ("allele_read_depth", np.int32), ("forward_depth", np.int32),
+       ("allele_forward_depth", np.int32), ("mean_mapping_quality", np.float64), ("median_mapping_quality", np.float64),
+       ("mean_base_quality", np.float64), ("median_base_quality", np.float64), ("median_mismatches_per_read", np.float64)]
+SS_CALL_DTYPE = np.dtype([("contig_id", np.int32), ("_pad", np.int32), ("start", np.int64), ("ref_off", np.uint32),
+                          ("ref_len", np.uint32), ("alt_off", np.uint32), ("alt_len", np.uint32),
+                          ("somatic_log_odds", np.float64), ("tumor_ref_log_prob", np.float64),
+                          ("tumor_alt_log_prob", np.float64), ("normal_ref_log_prob", np.float64),
+                          ("normal_alt_log_prob", np.float64), ("tumor_variant_evidence", np.dtype(_EV)),
+                          ("normal_reference_evidence", np.dtype(_EV))])
+LOCUS_SUMMARY_DTYPE = np.dtype([("depth", np.uint16), ("reference_depth", np.uint16), ("top_alt_count", np.uint16),
+                                ("flags", np.uint16)])
+assert LOCUS_COUNTS_DTYPE.itemsize == C.sizeof(LocusCountsC)
+assert ELEMENT_DTYPE.itemsize == C.sizeof(ElementC)
+assert SS_CALL_DTYPE.itemsize == C.sizeof(SSCallC)
+
+
+def ptr(a: np.ndarray, t):
+    return a.ctypes.data_as(t)
+
+
+def make_ranges(ranges: Sequence[Tuple[int, int, int]]):
+    arr = (RangeC * max(1, len(ranges)))()
+    for i, (c, s, e) in enumerate(ranges):
+        arr[i].contig_id, arr[i].start, arr[i].end = c, s, e
+    return arr
+
+
+def ss_params(normal_sample_id=0, tumor_sample_id=1, normal_odds_threshold=5, tumor_odds_threshold=10,
+              max_read_depth=2**31 - 1, max_normal_alternate_read_depth=4, min_tumor_variant_allele_frequency_percent=3):
+    """Defaults of SomaticStandard.Arguments (commands/SomaticStandardCaller.scala:44-70);
+    the VAF floor is percent / 100.0f as a float (:97)."""
+    p = SSParamsC()
+    p.normal_sample_id, p.tumor_sample_id = normal_sample_id, tumor_sample_id
+    p.normal_odds_threshold, p.tumor_odds_threshold = normal_odds_threshold, tumor_odds_threshold
+    p.max_read_depth = max_read_depth
+    p.max_normal_alternate_read_depth = max_normal_alternate_read_depth
+    p.min_tumor_variant_allele_frequency = float(np.float32(min_tumor_variant_allele_frequency_percent) / np.float32(100.0))
+    return p
+
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Loads the CUDA library.  Raises (loudly) if it has not been built: there is no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.guac_last_error.restype = C.c_char_p
+        _lib.guac_last_error.argtypes = [C.c_void_p]
+        _lib.guac_kernel_launches.restype = C.c_int64
+        _lib.guac_kernel_launches.argtypes = [C.c_void_p]
+        _lib.guac_free.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.guac_free.restype = None
+        _lib.guac_ctx_destroy.argtypes = [C.c_void_p]
+        _lib.guac_ctx_destroy.restype = None
+    return _lib
+
+
+def pack_bases(ascii_bases: np.ndarray):
+    """guac_pack_bases over a whole batch -> dict(bases2, nmask, exc_pos, exc_base)."""
+    lib = load_library()
+    n = int(ascii_bases.shape[0])
+    bases2 = np.zeros((n + 3) // 4 + 8, np.uint8)
+    nmask = np.zeros((n + 7) // 8 + 8, np.uint8)
+    cap = max(16, int(np.count_nonzero(~np.isin(ascii_bases, (65, 67, 71, 84)))))
+    exc_pos = np.zeros(cap, np.uint64)
+    exc_base = np.zeros(cap, np.uint8)
+    n_exc = C.c_int64(0)
+    a = np.ascontiguousarray(ascii_bases)
+    st = lib.guac_pack_bases(ptr(a, u8p), C.c_int64(n), C.c_uint64(0), ptr(bases2, u8p), ptr(nmask, u8p), ptr(exc_pos, u64p),
+                             ptr(exc_base, u8p), C.c_int64(cap), C.byref(n_exc))
+    if st != 0:
+        raise GuacError(st, "guac_pack_bases failed")
+    return dict(bases2=bases2, nmask=nmask, exc_pos=exc_pos[:max(1, n_exc.value)], exc_base=exc_base[:max(1, n_exc.value)],
+                n_exc=n_exc.value)
+
+
+def batch_struct(batch: ReadBatch) -> ReadBatchC:
+    if batch.packed is None:
+        batch.packed = pack_bases(batch.bases_ascii)
+    p = batch.packed
+    b = ReadBatchC()
+    b.n_reads, b.n_samples = batch.n_reads, batch.n_samples
+    b.contig_id, b.start = ptr(batch.contig_id, i32p), ptr(batch.start, i64p)
+    b.cigar_off, b.cigar = ptr(batch.cigar_off, u32p), ptr(batch.cigar, u32p)
+    b.seq_off = ptr(batch.seq_off, u64p)
+    b.bases2, b.nmask = ptr(p["bases2"], u8p), ptr(p["nmask"], u8p)
+    b.n_exc, b.exc_pos, b.exc_base = p["n_exc"], ptr(p["exc_pos"], u64p), ptr(p["exc_base"], u8p)
+    b.qual, b.mapq, b.flags, b.sample_id = ptr(batch.qual, u8p), ptr(batch.mapq, u8p), ptr(batch.flags, u8p), ptr(batch.sample_id, u8p)
+    return b
+
+
+def _take(lib, ctx, p, dtype, n) -> np.ndarray:
+    """Copies a library-owned output buffer into numpy and releases it."""
+    if n == 0 or not p:
+        out = np.zeros(0, dtype)
+    else:
+        nbytes = int(n) * np.dtype(dtype).itemsize
+        out = np.frombuffer(C.string_at(C.cast(p, C.c_void_p), nbytes), dtype=dtype).copy()
+    if p:
+        lib.guac_free(ctx, C.cast(p, C.c_void_p))
+    return out
+
+
+class Context:
+    """guac_ctx: one CUDA device, one stream, not thread-safe."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self.ctx = C.c_void_p()
+        st = self.lib.guac_ctx_create(C.c_int(device), C.byref(self.ctx))
+        if st != 0:
+            raise GuacError(st, "guac_ctx_create failed (no CUDA device? there is no CPU fallback)")
+        self.contig_names: List[str] = []
+
+    def close(self):
+        if self.ctx:
+            self.lib.guac_ctx_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st: int):
+        if st != 0:
+            raise GuacError(st, (self.lib.guac_last_error(self.ctx) or b"").decode())
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self.lib.guac_kernel_launches(self.ctx))
+
+    # -- reference ---------------------------------------------------------------
+    def upload_reference(self, reference: Reference, contig_names: Sequence[str]):
+        self.contig_names = list(contig_names)
+        for cid, name in enumerate(contig_names):
+            if name not in reference.contigs:
+                continue
+            w = reference.contigs[name]
+            self._check(self.lib.guac_ref_reserve(self.ctx, C.c_int32(cid), C.c_int64(w.offset), C.c_int64(w.bases.shape[0])))
+            # upload only the present runs so that absent loci stay "missing"
+            present = w.bases != 0
+            edges = np.flatnonzero(np.diff(np.concatenate([[0], present.view(np.int8), [0]])))
+            for s, e in zip(edges[0::2], edges[1::2]):
+                seg = np.ascontiguousarray(w.bases[s:e])
+                self._check(self.lib.guac_ref_upload(self.ctx, C.c_int32(cid), ptr(seg, u8p), C.c_int64(e - s),
+                                                     C.c_int64(w.offset + int(s))))
+
+    # -- reads -------------------------------------------------------------------
+    def upload_reads(self, batch: ReadBatch):
+        b = batch_struct(batch)
+        self._check(self.lib.guac_reads_upload(self.ctx, C.byref(b)))
+        self._batch = batch  # keep host arrays alive
+
+    # -- pileup ------------------------------------------------------------------
+    def pileup_counts(self, ranges: Sequence[Tuple[int, int, int]], skip_empty: bool = True):
+        r = make_ranges(ranges)
+        oc, ol, cnt, n = i32p(), i64p(), C.POINTER(LocusCountsC)(), C.c_int64()
+        self._check(self.lib.guac_pileup_counts(self.ctx, r, C.c_int32(len(ranges)), C.c_int32(int(skip_empty)), C.byref(oc),
+                                                C.byref(ol), C.byref(cnt), C.byref(n)))
+        ns = self._batch.n_samples
+        return (_take(self.lib, self.ctx, oc, np.int32, n.value), _take(self.lib, self.ctx, ol, np.int64, n.value),
+                _take(self.lib, self.ctx, cnt, LOCUS_COUNTS_DTYPE, n.value * ns).reshape(n.value, ns))
+
+    def pileup_elements(self, ranges: Sequence[Tuple[int, int, int]], skip_empty: bool = True):
+        r = make_ranges(ranges)
+        oc, ol, off, els, n = i32p(), i64p(), i64p(), C.POINTER(ElementC)(), C.c_int64()
+        self._check(self.lib.guac_pileup_elements(self.ctx, r, C.c_int32(len(ranges)), C.c_int32(int(skip_empty)), C.byref(oc),
+                                                  C.byref(ol), C.byref(off), C.byref(els), C.byref(n)))
+        offsets = _take(self.lib, self.ctx, off, np.int64, n.value + 1)
+        total = int(offsets[-1]) if offsets.shape[0] else 0
+        return (_take(self.lib, self.ctx, oc, np.int32, n.value), _take(self.lib, self.ctx, ol, np.int64, n.value), offsets,
+                _take(self.lib, self.ctx, els, ELEMENT_DTYPE, total))
+
+    # -- callers -----------------------------------------------------------------
+    def somatic_standard(self, ranges: Sequence[Tuple[int, int, int]], params: Optional[SSParamsC] = None,
+                         want_summary: bool = False):
+        params = params or ss_params()
+        r = make_ranges(ranges)
+        calls, n, arena, alen = C.POINTER(SSCallC)(), C.c_int64(), C.c_char_p(), C.c_int64()
+        summ, nv = C.POINTER(LocusSummaryC)(), C.c_int64()
+        arena_p = C.c_void_p()
+        self._check(self.lib.guac_somatic_standard(self.ctx, C.byref(params), r, C.c_int32(len(ranges)), C.byref(calls),
+                                                   C.byref(n), C.byref(arena_p), C.byref(alen),
+                                                   C.byref(summ) if want_summary else None, C.byref(nv)))
+        arena_b = C.string_at(arena_p, alen.value) if arena_p else b""
+        if arena_p:
+            self.lib.guac_free(self.ctx, arena_p)
+        out = dict(calls=_take(self.lib, self.ctx, calls, SS_CALL_DTYPE, n.value), arena=arena_b, n_visited=nv.value)
+        if want_summary:
+            out["summary"] = _take(self.lib, self.ctx, summ, LOCUS_SUMMARY_DTYPE, nv.value * 2).reshape(nv.value, 2)
+        return out

@@ -1,0 +1,248 @@
+/*
+ * guac_b200.h — C ABI of libguac_b200.so
+ *
+ * B200-native (sm_100a) implementation of Guacamole's per-locus hot path:
+ * pileup construction -> genotype / somatic likelihoods.  Every entry point
+ * names the reference (hammerlab/guacamole, Scala) interface it replaces as
+ * `file:line` relative to src/main/scala/org/hammerlab/guacamole/ ("M/").
+ *
+ * Conventions
+ *   - every function returns GUAC_OK (0) or a negative guac_status; the
+ *     message is available from guac_last_error(ctx).  No C++ exception
+ *     crosses this boundary.
+ *   - inputs are caller-owned host memory and must stay valid until the call
+ *     returns; calls are synchronous at return.
+ *   - outputs are library-owned host memory, released with guac_free().
+ *   - a guac_ctx is bound to one CUDA device and is not thread-safe.
+ *   - loci are 0-based, ranges are half-open [start, end), exactly like
+ *     the reference's Locus / LociSet.
+ *   - there is no CPU fallback: without a CUDA device guac_ctx_create fails.
+ */
+#ifndef GUAC_B200_H
+#define GUAC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct guac_ctx guac_ctx;
+
+typedef enum {
+  GUAC_OK = 0,
+  GUAC_E_INVALID_INPUT = -1, /* reference-side assume()/assert()/InvalidCigarElementException */
+  GUAC_E_CUDA = -2,
+  GUAC_E_NO_DEVICE = -3,
+  GUAC_E_OOM = -4,
+  GUAC_E_UNSUPPORTED = -5, /* a documented capacity limit of this library was exceeded */
+  GUAC_E_STATE = -6        /* e.g. no reads / reference uploaded yet */
+} guac_status;
+
+/* CIGAR operator codes: BAM encoding, word = (length << 4) | op.
+ * (htsjdk CigarOperator, used by M/pileup/PileupElement.scala:59-117) */
+enum { GUAC_CIGAR_M = 0, GUAC_CIGAR_I = 1, GUAC_CIGAR_D = 2, GUAC_CIGAR_N = 3, GUAC_CIGAR_S = 4,
+       GUAC_CIGAR_H = 5, GUAC_CIGAR_P = 6, GUAC_CIGAR_EQ = 7, GUAC_CIGAR_X = 8 };
+
+/* per-read flag bits (M/reads/MappedRead.scala:21-33) */
+enum { GUAC_READ_POSITIVE_STRAND = 1, GUAC_READ_PAIRED = 2, GUAC_READ_DUPLICATE = 4, GUAC_READ_FAILED_QC = 8 };
+
+/*
+ * Columnar (struct-of-arrays) batch of mapped reads: the data contract of
+ * M/reads/MappedRead.scala:21-33 for one partition of
+ * M/readsets/rdd/PartitionedRegions.scala:56 (reads of all samples, sorted by
+ * (contig_id, start); every read that overlaps the partition's loci is present,
+ * halo reads included).
+ *
+ * Bases are 2 bit/base (A=0 C=1 G=2 T=3), base i of the batch in bits
+ * [2*(i%4), 2*(i%4)+1] of bases2[i/4].  Bases other than upper-case ACGT are
+ * stored as 0 in bases2, have their bit set in nmask (bit i%8 of nmask[i/8]) and
+ * are listed in (exc_pos, exc_base), sorted by exc_pos (batch-global base index).
+ * guac_pack_bases() produces this encoding from ASCII.
+ */
+typedef struct {
+  int64_t n_reads;
+  int32_t n_samples;
+  const int32_t* contig_id;  /* [n_reads] */
+  const int64_t* start;      /* [n_reads] 0-based alignment start */
+  const uint32_t* cigar_off; /* [n_reads+1] offsets into cigar */
+  const uint32_t* cigar;     /* BAM-encoded operators */
+  const uint64_t* seq_off;   /* [n_reads+1] offsets into the base/qual streams, in bases */
+  const uint8_t* bases2;     /* [(seq_off[n]+3)/4] */
+  const uint8_t* nmask;      /* [(seq_off[n]+7)/8] */
+  int64_t n_exc;
+  const uint64_t* exc_pos;   /* [n_exc] */
+  const uint8_t* exc_base;   /* [n_exc] ASCII */
+  const uint8_t* qual;       /* [seq_off[n]] Phred, not +33 */
+  const uint8_t* mapq;       /* [n_reads] */
+  const uint8_t* flags;      /* [n_reads] GUAC_READ_* */
+  const uint8_t* sample_id;  /* [n_reads] < n_samples */
+} guac_read_batch;
+
+/* One contiguous run of loci, the unit of M/loci/partitioning/LociPartitioning.scala:25-40 */
+typedef struct {
+  int32_t contig_id;
+  int32_t _pad;
+  int64_t start;
+  int64_t end;
+} guac_range;
+
+/* ---- context ------------------------------------------------------------ */
+
+/* Binds a context to CUDA device `device`.  Fails with GUAC_E_NO_DEVICE when no
+ * GPU is present (no CPU fallback).  Replaces the per-task setup of
+ * M/readsets/rdd/PartitionedRegions.scala:56-72. */
+int guac_ctx_create(int device, guac_ctx** out);
+void guac_ctx_destroy(guac_ctx* ctx);
+const char* guac_last_error(guac_ctx* ctx);
+/* Releases any buffer handed out through an out-pointer of this API. */
+void guac_free(guac_ctx* ctx, void* p);
+/* Number of kernels this context launched so far (bench.py's gpu_launches). */
+int64_t guac_kernel_launches(guac_ctx* ctx);
+
+/* ---- host-side packing helper (no device work) ---------------------------
+ * ASCII bases -> (bases2, nmask, exceptions).  `base_index0` is the batch-global
+ * index of ascii[0] and must be a multiple of 8.  exc_pos/exc_base must have room
+ * for exc_cap entries; *n_exc receives the number found (GUAC_E_OOM if > cap).
+ * Mirrors what M/reads/Read.scala:63-116 does when it materialises `sequence`. */
+int guac_pack_bases(const uint8_t* ascii, int64_t n, uint64_t base_index0, uint8_t* bases2, uint8_t* nmask,
+                    uint64_t* exc_pos, uint8_t* exc_base, int64_t exc_cap, int64_t* n_exc);
+
+/* ---- reference ------------------------------------------------------------
+ * M/reference/ReferenceBroadcast.scala:42-83 (ContigSequence.apply / slice).
+ * guac_ref_reserve declares the window [offset, offset+len) of a contig that will
+ * be addressable; guac_ref_upload copies upper-case ASCII bases into it.  Loci of
+ * the window that were never uploaded read as "missing" and make any pileup that
+ * touches them fail with GUAC_E_INVALID_INPUT, like MapBackedReferenceSequence. */
+int guac_ref_reserve(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t len);
+int guac_ref_upload(guac_ctx* ctx, int32_t contig_id, const uint8_t* bases_ascii_upper, int64_t len,
+                    int64_t offset);
+
+/* ---- reads ---------------------------------------------------------------- */
+/* Copies one partition's reads to the device (async H2D on the context's stream)
+ * and derives per-read end loci.  Replaces the Iterator[MappedRead] handed to the
+ * closure of M/readsets/rdd/PartitionedRegions.scala:56-72. */
+int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* batch);
+
+/* ---- pileup --------------------------------------------------------------- */
+
+/* Per visited locus, per sample summary of the pileup
+ * (M/pileup/Pileup.scala:32-52,100-106 — depth, positiveDepth, referenceDepth — and the
+ * alignment classes of M/pileup/Alignment.scala:14-75). */
+typedef struct {
+  uint32_t depth;          /* Pileup.depth */
+  uint32_t reference_depth;/* Pileup.referenceDepth: Match elements only */
+  uint32_t positive_depth; /* Pileup.positiveDepth */
+  uint32_t mismatches;     /* Mismatch */
+  uint32_t insertions;     /* Insertion */
+  uint32_t deletions;      /* Deletion (anchor base before the deleted run) */
+  uint32_t mid_deletions;  /* MidDeletion */
+  uint32_t clipped;        /* Clipped (N skips) */
+} guac_locus_counts;
+
+/*
+ * pileupFlatMap{OneSample,TwoSamples,MultipleSamples} with a counting closure
+ * (M/distributed/PileupFlatMapUtils.scala:52,79,105; locus visitation of
+ * M/windowing/SlidingWindow.scala:124-162 with halfWindowSize = 0).
+ * Visits, in order, every locus of `loci` (sorted, disjoint) — with skip_empty != 0
+ * only those where at least one sample has a read overlapping the locus.
+ * Outputs: *n_out loci; out_contig[i], out_locus[i]; out_counts[i*n_samples + s].
+ */
+int guac_pileup_counts(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, int32_t skip_empty,
+                       int32_t** out_contig, int64_t** out_locus, guac_locus_counts** out_counts, int64_t* n_out);
+
+/* One PileupElement (M/pileup/PileupElement.scala:24-31) plus its classification. */
+typedef struct {
+  int64_t read_index;                 /* index into the uploaded batch */
+  int32_t read_position;              /* readPosition */
+  int32_t cigar_element_index;        /* cigarElementIndex */
+  int64_t cigar_element_locus;        /* cigarElementLocus */
+  int32_t index_within_cigar_element; /* indexWithinCigarElement */
+  uint8_t kind;                       /* guac_alignment_kind */
+  uint8_t base;                       /* Match/Mismatch: sequenced base (ASCII); else 0 */
+  uint8_t quality;                    /* PileupElement.qualityScore :149-154 */
+  uint8_t sample_id;
+  int32_t indel_length;               /* Insertion: inserted bases; Deletion: deleted bases; else 0 */
+  int32_t _pad;
+} guac_element;
+
+typedef enum {
+  GUAC_ALN_MATCH = 0, GUAC_ALN_MISMATCH = 1, GUAC_ALN_INSERTION = 2, GUAC_ALN_DELETION = 3,
+  GUAC_ALN_MID_DELETION = 4, GUAC_ALN_CLIPPED = 5
+} guac_alignment_kind;
+
+/*
+ * Same operator, materialising every PileupElement so that a host closure can be
+ * run on real Pileup objects (generic-closure path of PileupFlatMapUtils).
+ * Elements of locus i, all samples, ordered by read_index, are
+ * out_elements[out_offsets[i] .. out_offsets[i+1]).
+ */
+int guac_pileup_elements(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, int32_t skip_empty,
+                         int32_t** out_contig, int64_t** out_locus, int64_t** out_offsets,
+                         guac_element** out_elements, int64_t* n_out);
+
+/* ---- callers -------------------------------------------------------------- */
+
+/* M/variants/AlleleEvidence.scala:25-35 */
+typedef struct {
+  double probability;
+  int32_t read_depth;
+  int32_t allele_read_depth;
+  int32_t forward_depth;
+  int32_t allele_forward_depth;
+  double mean_mapping_quality;
+  double median_mapping_quality;
+  double mean_base_quality;
+  double median_base_quality;
+  double median_mismatches_per_read;
+} guac_allele_evidence;
+
+/* SomaticStandard.Arguments (M/commands/SomaticStandardCaller.scala:35-73) */
+typedef struct {
+  int32_t normal_sample_id;                  /* sample_id of the normal reads (pileupFlatMapTwoSamples sample1) */
+  int32_t tumor_sample_id;
+  int32_t normal_odds_threshold;             /* --normal-odds, default 5 */
+  int32_t tumor_odds_threshold;              /* --tumor-odds, default 10 */
+  int32_t max_read_depth;                    /* maxTumorReadDepth, default INT32_MAX */
+  int32_t max_normal_alternate_read_depth;   /* default 4 */
+  float min_tumor_variant_allele_frequency;  /* percent / 100.0f, default 0.03f */
+  int32_t _pad;
+} guac_ss_params;
+
+/* M/variants/CalledSomaticAllele.scala:25-34.  ref/alt are (offset,len) into the
+ * returned string arena. */
+typedef struct {
+  int32_t contig_id;
+  int32_t _pad;
+  int64_t start;
+  uint32_t ref_off, ref_len, alt_off, alt_len;
+  double somatic_log_odds;
+  double tumor_ref_log_prob, tumor_alt_log_prob, normal_ref_log_prob, normal_alt_log_prob;
+  guac_allele_evidence tumor_variant_evidence;
+  guac_allele_evidence normal_reference_evidence;
+} guac_ss_call;
+
+/* Dense per-(visited locus, sample) summary written by the fused callers. */
+typedef struct {
+  uint16_t depth;           /* saturating at 65535 */
+  uint16_t reference_depth;
+  uint16_t top_alt_count;   /* count of the most frequent variant allele */
+  uint16_t flags;           /* bit0: likelihoods were evaluated here; bit1: a call was emitted */
+} guac_locus_summary;
+
+/*
+ * somatic-standard: pileupFlatMapTwoSamples(normal, tumor, skipEmpty = true,
+ * findPotentialVariantAtLocus) — M/commands/SomaticStandardCaller.scala:100-117,155-253,
+ * with M/likelihood/Likelihood.scala:99-210 and M/variants/AlleleEvidence.scala:42-85
+ * fused on the device.  Calls come back sorted by (range order, locus).
+ * out_summary (optional, may be NULL) receives [*n_visited * 2] records, sample order
+ * (normal, tumor); out_n_visited (optional) the number of loci visited.
+ */
+int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const guac_range* loci, int32_t n_ranges,
+                          guac_ss_call** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
+                          guac_locus_summary** out_summary, int64_t* out_n_visited);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GUAC_B200_H */

@@ -1,0 +1,447 @@
+// oracle/guac_oracle.cpp — TEST INFRASTRUCTURE ONLY (see guac_oracle.hpp).
+// C entry points so that tests / bench.py's cpu_baseline can drive the CPU restatement
+// through ctypes.  Inputs use the same SoA shapes as include/guac_b200.h except that
+// bases are plain ASCII (the oracle does not trust the product's 2-bit packer).
+#include "guac_oracle.hpp"
+
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+
+#include "../include/guac_b200.h"  // POD result structs only
+
+using namespace guac_oracle;
+
+extern "C" {
+
+typedef struct {
+  int64_t n_reads;
+  int32_t n_samples;
+  const int32_t* contig_id;
+  const int64_t* start;
+  const uint32_t* cigar_off;
+  const uint32_t* cigar;
+  const uint64_t* seq_off;
+  const uint8_t* bases_ascii;
+  const uint8_t* qual;
+  const uint8_t* mapq;
+  const uint8_t* flags;
+  const uint8_t* sample_id;
+} oracle_reads;
+
+typedef struct {
+  int32_t contig_id;
+  int32_t _pad;
+  int64_t offset;
+  int64_t len;
+  const uint8_t* bases;
+} oracle_contig;
+}
+
+namespace {
+
+thread_local std::string g_error;
+
+std::vector<MappedRead> buildReads(const oracle_reads* b) {
+  std::vector<MappedRead> reads((size_t)b->n_reads);
+  for (int64_t i = 0; i < b->n_reads; ++i) {
+    MappedRead& r = reads[i];
+    r.index = i;
+    r.contig = b->contig_id[i];
+    r.start = b->start[i];
+    for (uint32_t c = b->cigar_off[i]; c < b->cigar_off[i + 1]; ++c)
+      r.cigarElements.push_back(CigarElement{(int)(b->cigar[c] >> 4), (uint8_t)(b->cigar[c] & 15)});
+    uint64_t s0 = b->seq_off[i], s1 = b->seq_off[i + 1];
+    r.sequence.assign((const char*)b->bases_ascii + s0, (size_t)(s1 - s0));
+    r.baseQualities.assign(b->qual + s0, b->qual + s1);
+    r.alignmentQuality = b->mapq[i];
+    r.isPositiveStrand = b->flags[i] & GUAC_READ_POSITIVE_STRAND;
+    r.isPaired = b->flags[i] & GUAC_READ_PAIRED;
+    r.isDuplicate = b->flags[i] & GUAC_READ_DUPLICATE;
+    r.failedVendorQualityChecks = b->flags[i] & GUAC_READ_FAILED_QC;
+    r.sampleId = b->sample_id[i];
+    r.finish();
+  }
+  return reads;
+}
+
+std::vector<ContigSequence> buildContigs(const oracle_contig* c, int n) {
+  std::vector<ContigSequence> v;
+  for (int i = 0; i < n; ++i) {
+    ContigSequence s;
+    s.contig_id = c[i].contig_id;
+    s.offset = c[i].offset;
+    s.len = c[i].len;
+    s.bases = c[i].bases;
+    v.push_back(s);
+  }
+  return v;
+}
+
+std::vector<Range> buildRanges(const guac_range* r, int n) {
+  std::vector<Range> v;
+  for (int i = 0; i < n; ++i) v.push_back(Range{r[i].contig_id, r[i].start, r[i].end});
+  return v;
+}
+
+template <class T>
+T* toC(const std::vector<T>& v) {
+  T* p = (T*)std::malloc(std::max<size_t>(1, v.size()) * sizeof(T));
+  if (!v.empty()) std::memcpy(p, v.data(), v.size() * sizeof(T));
+  return p;
+}
+
+guac_allele_evidence toC(const AlleleEvidence& e) {
+  guac_allele_evidence c;
+  c.probability = e.probability;
+  c.read_depth = e.readDepth;
+  c.allele_read_depth = e.alleleReadDepth;
+  c.forward_depth = e.forwardDepth;
+  c.allele_forward_depth = e.alleleForwardDepth;
+  c.mean_mapping_quality = e.meanMappingQuality;
+  c.median_mapping_quality = e.medianMappingQuality;
+  c.mean_base_quality = e.meanBaseQuality;
+  c.median_base_quality = e.medianBaseQuality;
+  c.median_mismatches_per_read = e.medianMismatchesPerRead;
+  return c;
+}
+
+guac_element toC(const Element& e) {
+  guac_element g;
+  std::memset(&g, 0, sizeof g);
+  g.read_index = e.pe.read->index;
+  g.read_position = e.pe.readPosition;
+  g.cigar_element_index = e.pe.cigarElementIndex;
+  g.cigar_element_locus = e.pe.cigarElementLocus;
+  g.index_within_cigar_element = e.pe.indexWithinCigarElement;
+  g.kind = e.aln.kind;
+  g.base = (e.aln.kind == MATCH || e.aln.kind == MISMATCH) ? (uint8_t)e.aln.sequencedBases[0] : 0;
+  g.quality = (uint8_t)e.qualityScore;
+  g.sample_id = (uint8_t)e.pe.read->sampleId;
+  g.indel_length = e.aln.kind == INSERTION  ? (int)e.aln.sequencedBases.size() - 1
+                   : e.aln.kind == DELETION ? (int)e.aln.referenceBases.size() - 1
+                                            : 0;
+  return g;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* oracle_last_error() { return g_error.c_str(); }
+void oracle_free(void* p) { std::free(p); }
+
+// pileupFlatMapMultipleSamples with a counting closure.
+int oracle_pileup_counts(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, const guac_range* ranges,
+                         int n_ranges, int skip_empty, int32_t** out_contig, int64_t** out_locus,
+                         guac_locus_counts** out_counts, int64_t* n_out) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    std::vector<int32_t> oc;
+    std::vector<int64_t> ol;
+    std::vector<guac_locus_counts> cnt;
+    pileupFlatMapMultipleSamples(reads, b->n_samples, buildRanges(ranges, n_ranges), cs, skip_empty != 0,
+                                 [&](const std::vector<Pileup>& pileups) {
+                                   oc.push_back(pileups[0].contig);
+                                   ol.push_back(pileups[0].locus);
+                                   for (auto& p : pileups) {
+                                     guac_locus_counts c;
+                                     std::memset(&c, 0, sizeof c);
+                                     c.depth = p.depth();
+                                     c.reference_depth = p.referenceDepth();
+                                     c.positive_depth = p.positiveDepth();
+                                     for (auto& e : p.elements) switch (e.aln.kind) {
+                                         case MISMATCH: ++c.mismatches; break;
+                                         case INSERTION: ++c.insertions; break;
+                                         case DELETION: ++c.deletions; break;
+                                         case MID_DELETION: ++c.mid_deletions; break;
+                                         case CLIPPED: ++c.clipped; break;
+                                         default: break;
+                                       }
+                                     cnt.push_back(c);
+                                   }
+                                 });
+    *out_contig = toC(oc);
+    *out_locus = toC(ol);
+    *out_counts = toC(cnt);
+    *n_out = (int64_t)ol.size();
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// Same operator, materialising the elements.  Elements of a locus are reported sorted by
+// read index (the CUDA path's canonical order); the reference's own order (priority-queue
+// array order, then stable filter + append) is returned in out_ref_order as the read
+// indices in reference order, same offsets.
+int oracle_pileup_elements(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, const guac_range* ranges,
+                           int n_ranges, int skip_empty, int32_t** out_contig, int64_t** out_locus,
+                           int64_t** out_offsets, guac_element** out_elements, int64_t** out_ref_order, int64_t* n_out) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    std::vector<int32_t> oc;
+    std::vector<int64_t> ol, off{0}, order;
+    std::vector<guac_element> els;
+    pileupFlatMapMultipleSamples(reads, b->n_samples, buildRanges(ranges, n_ranges), cs, skip_empty != 0,
+                                 [&](const std::vector<Pileup>& pileups) {
+                                   oc.push_back(pileups[0].contig);
+                                   ol.push_back(pileups[0].locus);
+                                   std::vector<guac_element> here;
+                                   for (auto& p : pileups)
+                                     for (auto& e : p.elements) {
+                                       here.push_back(toC(e));
+                                       order.push_back(e.pe.read->index);
+                                     }
+                                   std::stable_sort(here.begin(), here.end(), [](const guac_element& x, const guac_element& y) {
+                                     return x.read_index < y.read_index;
+                                   });
+                                   els.insert(els.end(), here.begin(), here.end());
+                                   off.push_back((int64_t)els.size());
+                                 });
+    *out_contig = toC(oc);
+    *out_locus = toC(ol);
+    *out_offsets = toC(off);
+    *out_elements = toC(els);
+    *out_ref_order = toC(order);
+    *n_out = (int64_t)ol.size();
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// Allele strings (ref, alt) of every element at one locus of one sample, '\t' separated
+// pairs joined by '\n', in reference element order.  For PileupSuite-style vectors.
+int oracle_pileup_alleles(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, int32_t contig, int64_t locus,
+                          int sample, char** out_text) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    const ContigSequence* c = nullptr;
+    for (auto& x : cs)
+      if (x.contig_id == contig) c = &x;
+    if (!c) throw InvalidInput("contig not found");
+    std::string text;
+    for (auto& r : reads)
+      if (r.contig == contig && r.sampleId == sample && r.overlapsLocus(locus)) {
+        Element e = makeElement(PileupElement::make(r, locus, *c));
+        text += e.allele.refBases + "\t" + e.allele.altBases + "\t" + std::to_string((int)e.aln.kind) + "\t" +
+                std::to_string(e.qualityScore) + "\n";
+      }
+    *out_text = (char*)std::malloc(text.size() + 1);
+    std::memcpy(*out_text, text.c_str(), text.size() + 1);
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// Likelihood.likelihoodsOfGenotypes for the pileup of one sample at one locus.  Genotype g
+// has n_alleles[g] alleles; allele strings are given as NUL-separated "ref\0alt\0" pairs in
+// `allele_text`, fractions in `fractions`, both flattened in genotype order.
+int oracle_likelihoods_of_genotypes(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, int32_t contig,
+                                    int64_t locus, int sample, int n_genotypes, const int32_t* n_alleles,
+                                    const char* allele_text, const double* fractions, int include_alignment, int log_space,
+                                    int normalize, double* out) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    const ContigSequence* c = nullptr;
+    for (auto& x : cs)
+      if (x.contig_id == contig) c = &x;
+    if (!c) throw InvalidInput("contig not found");
+    std::vector<const MappedRead*> rs;
+    for (auto& r : reads)
+      if (r.contig == contig && r.sampleId == sample && r.overlapsLocus(locus)) rs.push_back(&r);
+    Pileup p = Pileup::make(rs, sample, contig, locus, *c);
+    std::vector<Genotype> gs;
+    const char* t = allele_text;
+    int k = 0;
+    for (int g = 0; g < n_genotypes; ++g) {
+      Genotype G;
+      for (int a = 0; a < n_alleles[g]; ++a) {
+        std::string ref(t);
+        t += ref.size() + 1;
+        std::string alt(t);
+        t += alt.size() + 1;
+        G.alleleMixture.push_back({Allele{ref, alt}, fractions[k++]});
+      }
+      gs.push_back(G);
+    }
+    auto l = likelihoodsOfGenotypes(p.elements, gs, include_alignment != 0, log_space != 0, normalize != 0);
+    for (size_t i = 0; i < l.size(); ++i) out[i] = l[i];
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// Likelihood.probabilitiesOfAllPossibleGenotypesFromPileup; result text lines
+// "ref1\talt1\tref2\talt2\tvalue" (homozygous genotypes repeat the allele).
+int oracle_all_genotypes(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, int32_t contig, int64_t locus,
+                         int sample, int include_alignment, int log_space, char** out_text) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    const ContigSequence* c = nullptr;
+    for (auto& x : cs)
+      if (x.contig_id == contig) c = &x;
+    if (!c) throw InvalidInput("contig not found");
+    std::vector<const MappedRead*> rs;
+    for (auto& r : reads)
+      if (r.contig == contig && r.sampleId == sample && r.overlapsLocus(locus)) rs.push_back(&r);
+    Pileup p = Pileup::make(rs, sample, contig, locus, *c);
+    auto res = probabilitiesOfAllPossibleGenotypesFromPileup(p, include_alignment != 0, log_space != 0);
+    std::string text;
+    char buf[64];
+    for (auto& gv : res) {
+      auto& m = gv.first.alleleMixture;
+      const Allele& a0 = m[0].first;
+      const Allele& a1 = m.size() > 1 ? m[1].first : m[0].first;
+      snprintf(buf, sizeof buf, "%.17g", gv.second);
+      text += a0.refBases + "\t" + a0.altBases + "\t" + a1.refBases + "\t" + a1.altBases + "\t" + buf + "\n";
+    }
+    *out_text = (char*)std::malloc(text.size() + 1);
+    std::memcpy(*out_text, text.c_str(), text.size() + 1);
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+namespace {
+struct SSOut {
+  std::vector<guac_ss_call> calls;
+  std::string arena;
+  std::vector<guac_locus_summary> summary;
+  int64_t visited = 0;
+};
+
+void runSomaticStandard(const std::vector<MappedRead>& reads, const std::vector<ContigSequence>& cs,
+                        const std::vector<Range>& ranges, const guac_ss_params* params, bool wantSummary, SSOut& out) {
+  SomaticStandardParams p;
+  p.normalOddsThreshold = params->normal_odds_threshold;
+  p.tumorOddsThreshold = params->tumor_odds_threshold;
+  p.maxReadDepth = params->max_read_depth;
+  p.maxNormalAlternateReadDepth = params->max_normal_alternate_read_depth;
+  p.minTumorVariantAlleleFrequency = params->min_tumor_variant_allele_frequency;
+  int ns = std::max(params->normal_sample_id, params->tumor_sample_id) + 1;
+  pileupFlatMapMultipleSamples(reads, ns, ranges, cs, true, [&](const std::vector<Pileup>& pileups) {
+    const Pileup& normal = pileups[params->normal_sample_id];
+    const Pileup& tumor = pileups[params->tumor_sample_id];
+    CalledSomaticAllele c;
+    LocusSummary ts, nsum;
+    ++out.visited;
+    bool called = findPotentialVariantAtLocus(tumor, normal, p, &c, &ts, &nsum);
+    if (wantSummary) {
+      auto sat = [](int v) { return (uint16_t)std::min(v, 65535); };
+      out.summary.push_back(guac_locus_summary{sat(nsum.depth), sat(nsum.referenceDepth), sat(nsum.topAltCount), (uint16_t)nsum.flags});
+      out.summary.push_back(guac_locus_summary{sat(ts.depth), sat(ts.referenceDepth), sat(ts.topAltCount), (uint16_t)ts.flags});
+    }
+    if (called) {
+      guac_ss_call g;
+      std::memset(&g, 0, sizeof g);
+      g.contig_id = c.contig;
+      g.start = c.start;
+      g.ref_off = (uint32_t)out.arena.size();
+      g.ref_len = (uint32_t)c.allele.refBases.size();
+      out.arena += c.allele.refBases;
+      g.alt_off = (uint32_t)out.arena.size();
+      g.alt_len = (uint32_t)c.allele.altBases.size();
+      out.arena += c.allele.altBases;
+      g.somatic_log_odds = c.somaticLogOdds;
+      g.tumor_ref_log_prob = c.tumorRefLogProb;
+      g.tumor_alt_log_prob = c.tumorAltLogProb;
+      g.normal_ref_log_prob = c.normalRefLogProb;
+      g.normal_alt_log_prob = c.normalAltLogProb;
+      g.tumor_variant_evidence = toC(c.tumorVariantEvidence);
+      g.normal_reference_evidence = toC(c.normalReferenceEvidence);
+      out.calls.push_back(g);
+    }
+  });
+}
+}  // namespace
+
+// somatic-standard over one partition; n_threads > 1 splits the ranges into contiguous
+// chunks run in parallel (mirrors Spark local[N] over LociPartitioning ranges) — results
+// are concatenated in range order.
+int oracle_somatic_standard(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, const guac_ss_params* params,
+                            const guac_range* ranges, int n_ranges, int n_threads, guac_ss_call** out_calls, int64_t* n_calls,
+                            char** out_arena, int64_t* arena_len, guac_locus_summary** out_summary, int64_t* out_n_visited) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    auto all = buildRanges(ranges, n_ranges);
+    // split every range into n_threads pieces (UniformPartitioner-style contiguous loci)
+    std::vector<std::vector<Range>> parts(std::max(1, n_threads));
+    if (n_threads <= 1) {
+      parts[0] = all;
+    } else {
+      int64_t total = 0;
+      for (auto& r : all) total += r.end - r.start;
+      int64_t per = (total + n_threads - 1) / n_threads, acc = 0;
+      for (auto& r : all) {
+        int64_t s = r.start;
+        while (s < r.end) {
+          int t = (int)std::min<int64_t>(n_threads - 1, acc / per);
+          int64_t room = (t + 1) * per - acc;
+          int64_t e = std::min(r.end, s + room);
+          parts[t].push_back(Range{r.contig, s, e});
+          acc += e - s;
+          s = e;
+        }
+      }
+    }
+    std::vector<SSOut> outs(parts.size());
+    std::vector<std::string> errs(parts.size());
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < parts.size(); ++t)
+      th.emplace_back([&, t] {
+        try {
+          // each thread works on its own copy-free view: MappedRead::cachedCountOfMismatches is
+          // the only mutable field; races there are benign (same value written).
+          runSomaticStandard(reads, cs, parts[t], params, out_summary != nullptr, outs[t]);
+        } catch (const std::exception& e) {
+          errs[t] = e.what();
+        }
+      });
+    for (auto& x : th) x.join();
+    for (auto& e : errs)
+      if (!e.empty()) throw InvalidInput(e);
+    SSOut merged;
+    for (auto& o : outs) {
+      for (auto c : o.calls) {
+        c.ref_off += (uint32_t)merged.arena.size();
+        c.alt_off += (uint32_t)merged.arena.size();
+        merged.calls.push_back(c);
+      }
+      merged.arena += o.arena;
+      merged.summary.insert(merged.summary.end(), o.summary.begin(), o.summary.end());
+      merged.visited += o.visited;
+    }
+    *out_calls = toC(merged.calls);
+    *n_calls = (int64_t)merged.calls.size();
+    *out_arena = (char*)std::malloc(merged.arena.size() + 1);
+    std::memcpy(*out_arena, merged.arena.c_str(), merged.arena.size() + 1);
+    *arena_len = (int64_t)merged.arena.size();
+    if (out_summary) *out_summary = toC(merged.summary);
+    if (out_n_visited) *out_n_visited = merged.visited;
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+int oracle_success_probability_to_phred(double p) { return successProbabilityToPhred(p); }
+double oracle_phred_to_success_probability(int q) { return phredToSuccessProbability(q); }
+
+}  // extern "C"

@@ -1,0 +1,194 @@
+"""ctypes wrapper of oracle/libguac_oracle.so — TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+may import this module.  It is the parity checker (a CPU restatement of the reference,
+see guac_oracle.hpp), never the thing measured as the product or shipped.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from guacamole_b200.io import Reference
+from guacamole_b200.native import (ELEMENT_DTYPE, LOCUS_COUNTS_DTYPE, LOCUS_SUMMARY_DTYPE, SS_CALL_DTYPE, ElementC,
+                                   LocusCountsC, LocusSummaryC, SSCallC, SSParamsC, i32p, i64p, make_ranges, ptr,
+                                   ss_params, u8p, u32p, u64p)
+from guacamole_b200.reads import ReadBatch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libguac_oracle.so")
+
+
+class OracleReads(C.Structure):
+    _fields_ = [("n_reads", C.c_int64), ("n_samples", C.c_int32), ("contig_id", i32p), ("start", i64p), ("cigar_off", u32p),
+                ("cigar", u32p), ("seq_off", u64p), ("bases_ascii", u8p), ("qual", u8p), ("mapq", u8p), ("flags", u8p),
+                ("sample_id", u8p)]
+
+
+class OracleContig(C.Structure):
+    _fields_ = [("contig_id", C.c_int32), ("_pad", C.c_int32), ("offset", C.c_int64), ("len", C.c_int64), ("bases", u8p)]
+
+
+def build(force: bool = False) -> str:
+    if force or not os.path.exists(LIB_PATH) or any(
+            os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(LIB_PATH) for f in ("guac_oracle.cpp", "guac_oracle.hpp")):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(LIB_PATH)
+        _lib.oracle_last_error.restype = C.c_char_p
+        _lib.oracle_free.argtypes = [C.c_void_p]
+        _lib.oracle_phred_to_success_probability.restype = C.c_double
+        _lib.oracle_phred_to_success_probability.argtypes = [C.c_int]
+        _lib.oracle_success_probability_to_phred.argtypes = [C.c_double]
+    return _lib
+
+
+class OracleError(RuntimeError):
+    pass
+
+
+def _check(st):
+    if st != 0:
+        raise OracleError(lib().oracle_last_error().decode())
+
+
+def _take(p, dtype, n):
+    if n == 0 or not p:
+        out = np.zeros(0, dtype)
+    else:
+        out = np.frombuffer(C.string_at(C.cast(p, C.c_void_p), int(n) * np.dtype(dtype).itemsize), dtype=dtype).copy()
+    if p:
+        lib().oracle_free(C.cast(p, C.c_void_p))
+    return out
+
+
+def _reads(batch: ReadBatch) -> OracleReads:
+    b = OracleReads()
+    b.n_reads, b.n_samples = batch.n_reads, batch.n_samples
+    b.contig_id, b.start = ptr(batch.contig_id, i32p), ptr(batch.start, i64p)
+    b.cigar_off, b.cigar, b.seq_off = ptr(batch.cigar_off, u32p), ptr(batch.cigar, u32p), ptr(batch.seq_off, u64p)
+    b.bases_ascii, b.qual = ptr(batch.bases_ascii, u8p), ptr(batch.qual, u8p)
+    b.mapq, b.flags, b.sample_id = ptr(batch.mapq, u8p), ptr(batch.flags, u8p), ptr(batch.sample_id, u8p)
+    return b
+
+
+def _contigs(reference: Reference, contig_names: Sequence[str]):
+    present = [(i, reference.contigs[n]) for i, n in enumerate(contig_names) if n in reference.contigs]
+    arr = (OracleContig * max(1, len(present)))()
+    for k, (cid, w) in enumerate(present):
+        arr[k].contig_id, arr[k].offset, arr[k].len, arr[k].bases = cid, w.offset, w.bases.shape[0], ptr(w.bases, u8p)
+    return arr, len(present)
+
+
+def pileup_counts(batch: ReadBatch, reference: Reference, ranges, skip_empty=True):
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    r = make_ranges(ranges)
+    oc, ol, cnt, n = i32p(), i64p(), C.POINTER(LocusCountsC)(), C.c_int64()
+    _check(lib().oracle_pileup_counts(C.byref(b), cs, nc, r, len(ranges), int(skip_empty), C.byref(oc), C.byref(ol),
+                                      C.byref(cnt), C.byref(n)))
+    return (_take(oc, np.int32, n.value), _take(ol, np.int64, n.value),
+            _take(cnt, LOCUS_COUNTS_DTYPE, n.value * batch.n_samples).reshape(n.value, batch.n_samples))
+
+
+def pileup_elements(batch: ReadBatch, reference: Reference, ranges, skip_empty=True):
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    r = make_ranges(ranges)
+    oc, ol, off, els, order, n = i32p(), i64p(), i64p(), C.POINTER(ElementC)(), i64p(), C.c_int64()
+    _check(lib().oracle_pileup_elements(C.byref(b), cs, nc, r, len(ranges), int(skip_empty), C.byref(oc), C.byref(ol),
+                                        C.byref(off), C.byref(els), C.byref(order), C.byref(n)))
+    offsets = _take(off, np.int64, n.value + 1)
+    total = int(offsets[-1])
+    return (_take(oc, np.int32, n.value), _take(ol, np.int64, n.value), offsets, _take(els, ELEMENT_DTYPE, total),
+            _take(order, np.int64, total))
+
+
+def pileup_alleles(batch: ReadBatch, reference: Reference, contig: str, locus: int, sample: int = 0):
+    """[(ref, alt, kind, qualityScore)] of every element of `sample` at `locus`, in batch order."""
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    text = C.c_void_p()
+    _check(lib().oracle_pileup_alleles(C.byref(b), cs, nc, batch.contig_names.index(contig), C.c_int64(locus), sample,
+                                       C.byref(text)))
+    s = C.string_at(text).decode()
+    lib().oracle_free(text)
+    out = []
+    for line in s.split("\n"):
+        if line:
+            ref, alt, kind, q = line.split("\t")
+            out.append((ref, alt, int(kind), int(q)))
+    return out
+
+
+def likelihoods_of_genotypes(batch, reference, contig, locus, genotypes, sample=0, include_alignment=False,
+                             log_space=False, normalize=False):
+    """genotypes: list of lists of ((ref, alt), fraction)."""
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    n_alleles = np.array([len(g) for g in genotypes], np.int32)
+    text = b"".join(a[0].encode() + b"\0" + a[1].encode() + b"\0" for g in genotypes for a, _ in g)
+    fr = np.array([f for g in genotypes for _, f in g], np.float64)
+    out = np.zeros(len(genotypes), np.float64)
+    _check(lib().oracle_likelihoods_of_genotypes(C.byref(b), cs, nc, batch.contig_names.index(contig), C.c_int64(locus), sample,
+                                                 len(genotypes), ptr(n_alleles, i32p), text, fr.ctypes.data_as(C.POINTER(C.c_double)),
+                                                 int(include_alignment), int(log_space), int(normalize),
+                                                 out.ctypes.data_as(C.POINTER(C.c_double))))
+    return out
+
+
+def all_genotypes(batch, reference, contig, locus, sample=0, include_alignment=False, log_space=False):
+    """[((ref1, alt1), (ref2, alt2), value)] — probabilitiesOfAllPossibleGenotypesFromPileup."""
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    text = C.c_void_p()
+    _check(lib().oracle_all_genotypes(C.byref(b), cs, nc, batch.contig_names.index(contig), C.c_int64(locus), sample,
+                                      int(include_alignment), int(log_space), C.byref(text)))
+    s = C.string_at(text).decode()
+    lib().oracle_free(text)
+    out = []
+    for line in s.split("\n"):
+        if line:
+            r1, a1, r2, a2, v = line.split("\t")
+            out.append(((r1, a1), (r2, a2), float(v)))
+    return out
+
+
+def somatic_standard(batch: ReadBatch, reference: Reference, ranges, params: Optional[SSParamsC] = None, n_threads=1,
+                     want_summary=False):
+    params = params or ss_params()
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    r = make_ranges(ranges)
+    calls, n, arena, alen = C.POINTER(SSCallC)(), C.c_int64(), C.c_void_p(), C.c_int64()
+    summ, nv = C.POINTER(LocusSummaryC)(), C.c_int64()
+    _check(lib().oracle_somatic_standard(C.byref(b), cs, nc, C.byref(params), r, len(ranges), n_threads, C.byref(calls),
+                                         C.byref(n), C.byref(arena), C.byref(alen), C.byref(summ) if want_summary else None,
+                                         C.byref(nv)))
+    arena_b = C.string_at(arena, alen.value)
+    lib().oracle_free(arena)
+    out = dict(calls=_take(calls, SS_CALL_DTYPE, n.value), arena=arena_b, n_visited=nv.value)
+    if want_summary:
+        out["summary"] = _take(summ, LOCUS_SUMMARY_DTYPE, nv.value * 2).reshape(nv.value, 2)
+    return out
+
+
+def phred_to_success_probability(q: int) -> float:
+    return lib().oracle_phred_to_success_probability(q)
+
+
+def success_probability_to_phred(p: float) -> int:
+    return lib().oracle_success_probability_to_phred(p)
