@@ -1,0 +1,698 @@
+// guac_b200.cu — C ABI (include/guac_b200.h) and host-side planning for libguac_b200.so.
+// Everything that touches per-locus data runs in the CUDA kernels of kernels.cuh /
+// tile_kernels.cuh; this file owns device memory, the stream, error translation and the
+// sparse result assembly.  There is no CPU fallback.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "../../include/guac_b200.h"
+#include "kernels.cuh"
+#include "scan.cuh"
+
+using namespace guac;
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  template <class T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct ContigDev {
+  int64_t offset = 0, len = 0;
+  uint8_t* bases = nullptr;
+  int ref_index = -1;
+};
+
+}  // namespace
+
+struct guac_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  int64_t launches = 0;
+  std::map<int32_t, ContigDev> contigs;
+  DevBuf d_refs;  // RefView table
+  bool refs_dirty = true;
+  // reads
+  bool have_reads = false;
+  int64_t n_reads = 0;
+  int32_t n_samples = 0;
+  ReadsView R{};
+  DevBuf b_start, b_end, b_key, b_runmax, b_contig, b_cigar_off, b_cigar, b_seq_off, b_bases2, b_nmask, b_exc_pos, b_exc_base,
+      b_qual, b_mapq, b_flags, b_sample, b_scan_tmp;
+  std::vector<std::pair<int32_t, std::pair<int64_t, int64_t>>> contig_spans;  // contig -> [lo, hi) read indices
+  // plan / scratch
+  DevBuf b_ranges, b_tiles, b_visited, b_vis_idx, b_counts, b_totals, b_elem_off, b_summary, b_calls, b_ncalls, b_err, b_arena;
+  std::set<void*> host_allocs;
+};
+
+namespace {
+
+#define CUDA_TRY(ctx, expr)                                                                       \
+  do {                                                                                            \
+    cudaError_t _e = (expr);                                                                      \
+    if (_e != cudaSuccess) {                                                                      \
+      (ctx)->err = std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " #expr;           \
+      return GUAC_E_CUDA;                                                                         \
+    }                                                                                             \
+  } while (0)
+
+#define GUAC_TRY(expr)          \
+  do {                          \
+    int _s = (expr);            \
+    if (_s != GUAC_OK) return _s; \
+  } while (0)
+
+int fail(guac_ctx* ctx, int status, const std::string& msg) {
+  ctx->err = msg;
+  return status;
+}
+
+int ensure(guac_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap && b.p) return GUAC_OK;
+  if (b.p) CUDA_TRY(ctx, cudaFree(b.p));
+  b.p = nullptr;
+  b.cap = 0;
+  size_t want = std::max<size_t>(bytes, 256);
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return fail(ctx, GUAC_E_OOM, std::string("cudaMalloc of ") + std::to_string(want) + " bytes failed: " + cudaGetErrorString(e));
+  }
+  b.cap = want;
+  return GUAC_OK;
+}
+
+template <class T>
+int upload(guac_ctx* ctx, DevBuf& b, const T* host, size_t n, size_t extra_elems = 0) {
+  GUAC_TRY(ensure(ctx, b, (n + extra_elems) * sizeof(T) + 16));
+  if (n) CUDA_TRY(ctx, cudaMemcpyAsync(b.p, host, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  return GUAC_OK;
+}
+
+template <class T>
+int host_out(guac_ctx* ctx, T** out, const void* dev, size_t n) {
+  void* h = nullptr;
+  CUDA_TRY(ctx, cudaMallocHost(&h, std::max<size_t>(n * sizeof(T), 16)));
+  ctx->host_allocs.insert(h);
+  if (n) CUDA_TRY(ctx, cudaMemcpyAsync(h, dev, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+  *out = reinterpret_cast<T*>(h);
+  return GUAC_OK;
+}
+
+inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+// device-wide scan (three phases), T = int64_t
+template <bool EXCLUSIVE, class TIn, class Op>
+int device_scan(guac_ctx* ctx, const TIn* in, int64_t* out, int64_t n, Op op, int64_t* grand_total_dev = nullptr) {
+  if (n == 0) return GUAC_OK;
+  int64_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  GUAC_TRY(ensure(ctx, ctx->b_scan_tmp, (size_t)(n_tiles + 1) * sizeof(int64_t)));
+  int64_t* totals = ctx->b_scan_tmp.as<int64_t>();
+  scan_reduce_kernel<TIn, int64_t, Op><<<(unsigned)n_tiles, SCAN_THREADS, 0, ctx->stream>>>(in, totals, n, op);
+  scan_totals_kernel<int64_t, Op><<<1, SCAN_THREADS, 0, ctx->stream>>>(totals, n_tiles, op);
+  scan_apply_kernel<EXCLUSIVE, TIn, int64_t, Op><<<(unsigned)n_tiles, SCAN_THREADS, 0, ctx->stream>>>(in, out, totals, n, op);
+  ctx->launches += 3;
+  CUDA_TRY(ctx, cudaGetLastError());
+  if (grand_total_dev)
+    CUDA_TRY(ctx, cudaMemcpyAsync(grand_total_dev, totals + n_tiles, sizeof(int64_t), cudaMemcpyDeviceToDevice, ctx->stream));
+  return GUAC_OK;
+}
+
+int sync_refs(guac_ctx* ctx) {
+  if (!ctx->refs_dirty) return GUAC_OK;
+  std::vector<RefView> v;
+  int idx = 0;
+  for (auto& kv : ctx->contigs) {
+    kv.second.ref_index = idx++;
+    RefView r;
+    r.bases = kv.second.bases;
+    r.offset = kv.second.offset;
+    r.len = kv.second.len;
+    v.push_back(r);
+  }
+  GUAC_TRY(upload(ctx, ctx->d_refs, v.data(), v.size()));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `v` is a temporary
+  ctx->refs_dirty = false;
+  return GUAC_OK;
+}
+
+struct Plan {
+  int64_t n_slots = 0;
+  int64_t n_tiles = 0;
+};
+
+// Validates the ranges, builds the device range table and the tile descriptors.
+int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& plan) {
+  if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
+  if (n_ranges < 0 || (n_ranges > 0 && !loci)) return fail(ctx, GUAC_E_INVALID_INPUT, "bad loci ranges");
+  GUAC_TRY(sync_refs(ctx));
+  std::vector<RangeDev> rs;
+  int64_t slot = 0, tile = 0;
+  for (int i = 0; i < n_ranges; ++i) {
+    const guac_range& g = loci[i];
+    if (g.end < g.start || g.start < 0) return fail(ctx, GUAC_E_INVALID_INPUT, "loci range with end < start or negative start");
+    if (i > 0 && (g.contig_id == loci[i - 1].contig_id) && g.start < loci[i - 1].end)
+      return fail(ctx, GUAC_E_INVALID_INPUT, "loci ranges must be sorted and disjoint within a contig");
+    if (g.end == g.start) continue;
+    RangeDev r;
+    r.start = g.start;
+    r.end = g.end;
+    r.slot0 = slot;
+    r.tile0 = tile;
+    r.contig_id = g.contig_id;
+    r.read_clo = r.read_chi = 0;
+    for (auto& sp : ctx->contig_spans)
+      if (sp.first == g.contig_id) {
+        r.read_clo = sp.second.first;
+        r.read_chi = sp.second.second;
+      }
+    auto it = ctx->contigs.find(g.contig_id);
+    if (it == ctx->contigs.end()) {
+      if (r.read_chi > r.read_clo)
+        return fail(ctx, GUAC_E_INVALID_INPUT, "Contig " + std::to_string(g.contig_id) + " does not exist in the current reference");
+      continue;  // no reads and no reference: nothing can be visited
+    }
+    r.ref_index = it->second.ref_index;
+    slot += g.end - g.start;
+    tile += (g.end - g.start + TILE_LOCI - 1) / TILE_LOCI;
+    rs.push_back(r);
+  }
+  if (slot >= (int64_t)1 << 31) return fail(ctx, GUAC_E_UNSUPPORTED, "more than 2^31-1 loci in one call: split the LociPartitioning");
+  plan.n_slots = slot;
+  plan.n_tiles = tile;
+  if (tile == 0) return GUAC_OK;
+  GUAC_TRY(upload(ctx, ctx->b_ranges, rs.data(), rs.size()));
+  GUAC_TRY(ensure(ctx, ctx->b_tiles, (size_t)tile * sizeof(Tile)));
+  build_tiles_kernel<<<blocks_for(tile, 256), 256, 0, ctx->stream>>>(ctx->b_ranges.as<RangeDev>(), (int)rs.size(), tile, ctx->R,
+                                                                      ctx->b_tiles.as<Tile>());
+  ctx->launches += 1;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `rs` is a temporary
+  return GUAC_OK;
+}
+
+int reset_error(guac_ctx* ctx) {
+  GUAC_TRY(ensure(ctx, ctx->b_err, sizeof(DeviceError)));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_err.p, 0, sizeof(DeviceError), ctx->stream));
+  return GUAC_OK;
+}
+
+// Translates a device-side error into the reference's wording.
+int check_device_error(guac_ctx* ctx) {
+  DeviceError e;
+  CUDA_TRY(ctx, cudaMemcpyAsync(&e, ctx->b_err.p, sizeof e, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (e.code == DERR_NONE) return GUAC_OK;
+  char buf[256];
+  switch (e.code) {
+    case DERR_REF_MISSING:
+      snprintf(buf, sizeof buf, "Position %d:%lld missing from reference", e.contig_id, e.locus);
+      return fail(ctx, GUAC_E_INVALID_INPUT, buf);
+    case DERR_INSERTION_ELEMENT:
+      snprintf(buf, sizeof buf, "Should not have a PileupElement at non-reference-consuming cigar-operator I. Locus: %lld (read %lld)",
+               e.locus, e.read_index);
+      return fail(ctx, GUAC_E_INVALID_INPUT, buf);
+    case DERR_DELETION_PRECEDED:
+      snprintf(buf, sizeof buf, "Found deletion preceded by a non-aligned cigar operator at PileupElement for read %lld at locus %lld",
+               e.read_index, e.locus);
+      return fail(ctx, GUAC_E_INVALID_INPUT, buf);
+    case DERR_PADDING:
+      return fail(ctx, GUAC_E_INVALID_INPUT, "`P` CIGAR-ops should have been ignored earlier in `findNextCigarElement`");
+    case DERR_EMPTY_MAXBY:
+      snprintf(buf, sizeof buf, "empty.maxBy: every non-match tumor element at %d:%lld is Clipped", e.contig_id, e.locus);
+      return fail(ctx, GUAC_E_INVALID_INPUT, buf);
+    case DERR_CURSOR:
+      snprintf(buf, sizeof buf, "CIGAR of read %lld does not reach locus %lld", e.read_index, e.locus);
+      return fail(ctx, GUAC_E_INVALID_INPUT, buf);
+    case DERR_ALLELE_TABLE_FULL:
+      snprintf(buf, sizeof buf, "more than 32 distinct variant alleles at %d:%lld (library limit)", e.contig_id, e.locus);
+      return fail(ctx, GUAC_E_UNSUPPORTED, buf);
+    case DERR_MISMATCH_HIST:
+      snprintf(buf, sizeof buf, "read %lld has more than %d mismatches (library limit)", e.read_index, MM_BINS - 1);
+      return fail(ctx, GUAC_E_UNSUPPORTED, buf);
+  }
+  return fail(ctx, GUAC_E_CUDA, "unknown device error");
+}
+
+// visited flags -> compact indices; returns the number of visited loci.
+int compact_visited(guac_ctx* ctx, const Plan& plan, int skip_empty, int64_t& n_visited) {
+  GUAC_TRY(ensure(ctx, ctx->b_vis_idx, (size_t)(plan.n_slots + 1) * sizeof(int64_t)));
+  if (!skip_empty) CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_visited.p, 1, (size_t)plan.n_slots, ctx->stream));
+  int64_t* total_dev = ctx->b_vis_idx.as<int64_t>() + plan.n_slots;
+  GUAC_TRY((device_scan<true, uint8_t>(ctx, ctx->b_visited.as<uint8_t>(), ctx->b_vis_idx.as<int64_t>(), plan.n_slots, OpSum(), total_dev)));
+  CUDA_TRY(ctx, cudaMemcpyAsync(&n_visited, total_dev, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return GUAC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int guac_ctx_create(int device, guac_ctx** out) {
+  if (!out) return GUAC_E_INVALID_INPUT;
+  *out = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) {
+    (void)cudaGetLastError();
+    return GUAC_E_NO_DEVICE;
+  }
+  if (cudaSetDevice(device) != cudaSuccess) return GUAC_E_CUDA;
+  guac_ctx* ctx = new guac_ctx();
+  ctx->device = device;
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete ctx;
+    return GUAC_E_CUDA;
+  }
+  // ADAM PhredUtils table: 1 - 10^(-q/10)
+  double table[256];
+  for (int q = 0; q < 256; ++q) table[q] = 1.0 - std::pow(10.0, -q / 10.0);
+  if (cudaMemcpyToSymbol(c_success_probability, table, sizeof table) != cudaSuccess) {
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return GUAC_E_CUDA;
+  }
+  *out = ctx;
+  return GUAC_OK;
+}
+
+void guac_ctx_destroy(guac_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  DevBuf* bufs[] = {&ctx->d_refs, &ctx->b_start, &ctx->b_end, &ctx->b_key, &ctx->b_runmax, &ctx->b_contig, &ctx->b_cigar_off,
+                    &ctx->b_cigar, &ctx->b_seq_off, &ctx->b_bases2, &ctx->b_nmask, &ctx->b_exc_pos, &ctx->b_exc_base, &ctx->b_qual,
+                    &ctx->b_mapq, &ctx->b_flags, &ctx->b_sample, &ctx->b_scan_tmp, &ctx->b_ranges, &ctx->b_tiles, &ctx->b_visited,
+                    &ctx->b_vis_idx, &ctx->b_counts, &ctx->b_totals, &ctx->b_elem_off, &ctx->b_summary, &ctx->b_calls,
+                    &ctx->b_ncalls, &ctx->b_err, &ctx->b_arena};
+  for (DevBuf* b : bufs)
+    if (b->p) cudaFree(b->p);
+  for (auto& kv : ctx->contigs)
+    if (kv.second.bases) cudaFree(kv.second.bases);
+  for (void* h : ctx->host_allocs) cudaFreeHost(h);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+const char* guac_last_error(guac_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+void guac_free(guac_ctx* ctx, void* p) {
+  if (!ctx || !p) return;
+  auto it = ctx->host_allocs.find(p);
+  if (it != ctx->host_allocs.end()) {
+    cudaFreeHost(p);
+    ctx->host_allocs.erase(it);
+  }
+}
+
+int64_t guac_kernel_launches(guac_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int guac_pack_bases(const uint8_t* ascii, int64_t n, uint64_t base_index0, uint8_t* bases2, uint8_t* nmask, uint64_t* exc_pos,
+                    uint8_t* exc_base, int64_t exc_cap, int64_t* n_exc) {
+  if (!ascii || !bases2 || !nmask || !n_exc || (base_index0 & 7)) return GUAC_E_INVALID_INPUT;
+  int64_t ne = 0;
+  std::memset(bases2, 0, (size_t)((n + 3) / 4));
+  std::memset(nmask, 0, (size_t)((n + 7) / 8));
+  for (int64_t i = 0; i < n; ++i) {
+    uint8_t b = ascii[i];
+    int code;
+    switch (b) {
+      case 'A': code = 0; break;
+      case 'C': code = 1; break;
+      case 'G': code = 2; break;
+      case 'T': code = 3; break;
+      default: code = -1;
+    }
+    if (code >= 0) {
+      bases2[i >> 2] |= (uint8_t)(code << ((i & 3) * 2));
+    } else {
+      nmask[i >> 3] |= (uint8_t)(1u << (i & 7));
+      if (ne < exc_cap) {
+        exc_pos[ne] = base_index0 + (uint64_t)i;
+        exc_base[ne] = b;
+      }
+      ++ne;
+    }
+  }
+  *n_exc = ne;
+  return ne > exc_cap ? GUAC_E_OOM : GUAC_OK;
+}
+
+int guac_ref_reserve(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t len) {
+  if (!ctx) return GUAC_E_INVALID_INPUT;
+  if (len < 0 || offset < 0 || contig_id < 0 || contig_id >= (1 << 22)) return fail(ctx, GUAC_E_INVALID_INPUT, "bad reference window");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  ContigDev& c = ctx->contigs[contig_id];
+  if (c.bases) CUDA_TRY(ctx, cudaFree(c.bases));
+  c.bases = nullptr;
+  c.offset = offset;
+  c.len = len;
+  cudaError_t e = cudaMalloc(&c.bases, (size_t)std::max<int64_t>(len, 16));
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    ctx->contigs.erase(contig_id);
+    return fail(ctx, GUAC_E_OOM, "cudaMalloc failed for reference window");
+  }
+  CUDA_TRY(ctx, cudaMemsetAsync(c.bases, 0, (size_t)std::max<int64_t>(len, 16), ctx->stream));
+  ctx->refs_dirty = true;
+  return GUAC_OK;
+}
+
+int guac_ref_upload(guac_ctx* ctx, int32_t contig_id, const uint8_t* bases, int64_t len, int64_t offset) {
+  if (!ctx) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  auto it = ctx->contigs.find(contig_id);
+  if (it == ctx->contigs.end()) {
+    GUAC_TRY(guac_ref_reserve(ctx, contig_id, offset, len));
+    it = ctx->contigs.find(contig_id);
+  }
+  ContigDev& c = it->second;
+  if (offset < c.offset || offset + len > c.offset + c.len)
+    return fail(ctx, GUAC_E_INVALID_INPUT, "Illegal reference slice: outside the reserved window");
+  if (len > 0) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(c.bases + (offset - c.offset), bases, (size_t)len, cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return GUAC_OK;
+}
+
+int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* b) {
+  if (!ctx || !b) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  ctx->have_reads = false;
+  const int64_t n = b->n_reads;
+  if (n < 0 || b->n_samples <= 0 || b->n_samples > 255) return fail(ctx, GUAC_E_INVALID_INPUT, "bad read batch header");
+  // Host-side validation of the ordering contract (SlidingWindow.scala:36-37 "Regions must be sorted by start locus";
+  // RegionsByContig.scala:22 "Regions are not sorted by contig") and the per-contig spans.
+  ctx->contig_spans.clear();
+  for (int64_t i = 0; i < n; ++i) {
+    if (i == 0 || b->contig_id[i] != b->contig_id[i - 1]) {
+      for (auto& sp : ctx->contig_spans)
+        if (sp.first == b->contig_id[i]) return fail(ctx, GUAC_E_INVALID_INPUT, "Regions are not sorted by contig");
+      if (!ctx->contig_spans.empty()) ctx->contig_spans.back().second.second = i;
+      ctx->contig_spans.push_back({b->contig_id[i], {i, n}});
+      if (b->contig_id[i] < 0 || b->contig_id[i] >= (1 << 22)) return fail(ctx, GUAC_E_INVALID_INPUT, "contig_id out of range");
+    } else if (b->start[i] < b->start[i - 1]) {
+      return fail(ctx, GUAC_E_INVALID_INPUT, "Regions must be sorted by start locus");
+    }
+    if (b->sample_id[i] >= b->n_samples) return fail(ctx, GUAC_E_INVALID_INPUT, "sample_id >= n_samples");
+    if (b->start[i] < 0 || b->start[i] >= ((int64_t)1 << 39)) return fail(ctx, GUAC_E_INVALID_INPUT, "read start out of range");
+  }
+  const uint64_t n_bases = n ? b->seq_off[n] : 0;
+  const uint32_t n_cigar = n ? b->cigar_off[n] : 0;
+  GUAC_TRY(upload(ctx, ctx->b_start, b->start, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->b_contig, b->contig_id, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->b_cigar_off, b->cigar_off, (size_t)n + 1));
+  GUAC_TRY(upload(ctx, ctx->b_cigar, b->cigar, (size_t)n_cigar));
+  GUAC_TRY(upload(ctx, ctx->b_seq_off, b->seq_off, (size_t)n + 1));
+  GUAC_TRY(upload(ctx, ctx->b_bases2, b->bases2, (size_t)((n_bases + 3) / 4)));
+  GUAC_TRY(upload(ctx, ctx->b_nmask, b->nmask, (size_t)((n_bases + 7) / 8)));
+  GUAC_TRY(upload(ctx, ctx->b_exc_pos, b->exc_pos, (size_t)b->n_exc));
+  GUAC_TRY(upload(ctx, ctx->b_exc_base, b->exc_base, (size_t)b->n_exc));
+  GUAC_TRY(upload(ctx, ctx->b_qual, b->qual, (size_t)n_bases));
+  GUAC_TRY(upload(ctx, ctx->b_mapq, b->mapq, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->b_flags, b->flags, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->b_sample, b->sample_id, (size_t)n));
+  GUAC_TRY(ensure(ctx, ctx->b_end, (size_t)(n + 1) * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, ctx->b_key, (size_t)(n + 1) * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, ctx->b_runmax, (size_t)(n + 1) * sizeof(int64_t)));
+  if (n > 0) {
+    read_ends_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->b_start.as<int64_t>(), ctx->b_contig.as<int32_t>(),
+                                                                  ctx->b_cigar_off.as<uint32_t>(), ctx->b_cigar.as<uint32_t>(),
+                                                                  ctx->b_end.as<int64_t>(), ctx->b_key.as<int64_t>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    GUAC_TRY((device_scan<false, int64_t>(ctx, ctx->b_key.as<int64_t>(), ctx->b_runmax.as<int64_t>(), n, OpMax())));
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // caller's buffers may go away after return
+  ReadsView& R = ctx->R;
+  R.n_reads = n;
+  R.start = ctx->b_start.as<int64_t>();
+  R.end = ctx->b_end.as<int64_t>();
+  R.runmax_key = ctx->b_runmax.as<int64_t>();
+  R.cigar_off = ctx->b_cigar_off.as<uint32_t>();
+  R.cigar = ctx->b_cigar.as<uint32_t>();
+  R.seq_off = ctx->b_seq_off.as<uint64_t>();
+  R.bases2 = ctx->b_bases2.as<uint8_t>();
+  R.nmask = ctx->b_nmask.as<uint8_t>();
+  R.n_exc = b->n_exc;
+  R.exc_pos = ctx->b_exc_pos.as<uint64_t>();
+  R.exc_base = ctx->b_exc_base.as<uint8_t>();
+  R.qual = ctx->b_qual.as<uint8_t>();
+  R.mapq = ctx->b_mapq.as<uint8_t>();
+  R.flags = ctx->b_flags.as<uint8_t>();
+  R.sample_id = ctx->b_sample.as<uint8_t>();
+  ctx->n_reads = n;
+  ctx->n_samples = b->n_samples;
+  ctx->have_reads = true;
+  return GUAC_OK;
+}
+
+int guac_pileup_counts(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, int32_t skip_empty, int32_t** out_contig,
+                       int64_t** out_locus, guac_locus_counts** out_counts, int64_t* n_out) {
+  if (!ctx || !out_contig || !out_locus || !out_counts || !n_out) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Plan plan;
+  GUAC_TRY(make_plan(ctx, loci, n_ranges, plan));
+  const int S = ctx->n_samples;
+  *n_out = 0;
+  if (plan.n_tiles == 0) {
+    GUAC_TRY(host_out(ctx, out_contig, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_locus, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_counts, nullptr, 0));
+    return GUAC_OK;
+  }
+  GUAC_TRY(reset_error(ctx));
+  GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
+  GUAC_TRY(ensure(ctx, ctx->b_counts, (size_t)plan.n_slots * S * sizeof(guac_locus_counts)));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_counts.p, 0, (size_t)plan.n_slots * S * sizeof(guac_locus_counts), ctx->stream));
+  pileup_counts_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
+      ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), S, ctx->b_visited.as<uint8_t>(),
+      ctx->b_counts.as<guac_locus_counts>(), ctx->b_err.as<DeviceError>());
+  ctx->launches += 1;
+  CUDA_TRY(ctx, cudaGetLastError());
+  GUAC_TRY(check_device_error(ctx));
+  int64_t nv = 0;
+  GUAC_TRY(compact_visited(ctx, plan, skip_empty, nv));
+  DevBuf oc, ol, ocnt;
+  GUAC_TRY(ensure(ctx, oc, (size_t)nv * sizeof(int32_t)));
+  GUAC_TRY(ensure(ctx, ol, (size_t)nv * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, ocnt, (size_t)nv * S * sizeof(guac_locus_counts)));
+  compact_loci_kernel<<<(unsigned)plan.n_tiles, 64, 0, ctx->stream>>>(ctx->b_tiles.as<Tile>(), ctx->b_visited.as<uint8_t>(),
+                                                                      ctx->b_vis_idx.as<int64_t>(), oc.as<int32_t>(), ol.as<int64_t>());
+  gather_rows_kernel<guac_locus_counts><<<blocks_for(plan.n_slots * S, 256), 256, 0, ctx->stream>>>(
+      ctx->b_counts.as<guac_locus_counts>(), ctx->b_visited.as<uint8_t>(), ctx->b_vis_idx.as<int64_t>(), plan.n_slots, S,
+      ocnt.as<guac_locus_counts>());
+  ctx->launches += 2;
+  CUDA_TRY(ctx, cudaGetLastError());
+  GUAC_TRY(host_out(ctx, out_contig, oc.p, (size_t)nv));
+  GUAC_TRY(host_out(ctx, out_locus, ol.p, (size_t)nv));
+  GUAC_TRY(host_out(ctx, out_counts, ocnt.p, (size_t)nv * S));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  cudaFree(oc.p);
+  cudaFree(ol.p);
+  cudaFree(ocnt.p);
+  *n_out = nv;
+  return GUAC_OK;
+}
+
+int guac_pileup_elements(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, int32_t skip_empty, int32_t** out_contig,
+                         int64_t** out_locus, int64_t** out_offsets, guac_element** out_elements, int64_t* n_out) {
+  if (!ctx || !out_contig || !out_locus || !out_offsets || !out_elements || !n_out) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Plan plan;
+  GUAC_TRY(make_plan(ctx, loci, n_ranges, plan));
+  const int S = ctx->n_samples;
+  *n_out = 0;
+  if (plan.n_tiles == 0) {
+    GUAC_TRY(host_out(ctx, out_contig, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_locus, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_elements, nullptr, 0));
+    int64_t zero = 0;
+    void* h = nullptr;
+    CUDA_TRY(ctx, cudaMallocHost(&h, 16));
+    ctx->host_allocs.insert(h);
+    std::memcpy(h, &zero, sizeof zero);
+    *out_offsets = (int64_t*)h;
+    return GUAC_OK;
+  }
+  GUAC_TRY(reset_error(ctx));
+  GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
+  GUAC_TRY(ensure(ctx, ctx->b_totals, (size_t)plan.n_slots * sizeof(int32_t)));
+  GUAC_TRY(ensure(ctx, ctx->b_elem_off, (size_t)(plan.n_slots + 1) * sizeof(int64_t)));
+  depth_total_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(ctx->R, ctx->b_tiles.as<Tile>(), S,
+                                                                             ctx->b_visited.as<uint8_t>(), ctx->b_totals.as<int32_t>());
+  ctx->launches += 1;
+  CUDA_TRY(ctx, cudaGetLastError());
+  int64_t* total_dev = ctx->b_elem_off.as<int64_t>() + plan.n_slots;
+  GUAC_TRY((device_scan<true, int32_t>(ctx, ctx->b_totals.as<int32_t>(), ctx->b_elem_off.as<int64_t>(), plan.n_slots, OpSum(), total_dev)));
+  int64_t n_elems = 0;
+  CUDA_TRY(ctx, cudaMemcpyAsync(&n_elems, total_dev, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  int64_t nv = 0;
+  GUAC_TRY(compact_visited(ctx, plan, skip_empty, nv));
+  DevBuf oc, ol, oo, oe;
+  GUAC_TRY(ensure(ctx, oc, (size_t)nv * sizeof(int32_t)));
+  GUAC_TRY(ensure(ctx, ol, (size_t)nv * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, oo, (size_t)(nv + 1) * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, oe, (size_t)n_elems * sizeof(guac_element)));
+  write_elements_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
+      ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), S, skip_empty, ctx->b_elem_off.as<int64_t>(),
+      oe.as<guac_element>(), ctx->b_err.as<DeviceError>());
+  compact_loci_kernel<<<(unsigned)plan.n_tiles, 64, 0, ctx->stream>>>(ctx->b_tiles.as<Tile>(), ctx->b_visited.as<uint8_t>(),
+                                                                      ctx->b_vis_idx.as<int64_t>(), oc.as<int32_t>(), ol.as<int64_t>());
+  gather_offsets_kernel<<<blocks_for(plan.n_slots, 256), 256, 0, ctx->stream>>>(
+      ctx->b_elem_off.as<int64_t>(), ctx->b_visited.as<uint8_t>(), ctx->b_vis_idx.as<int64_t>(), plan.n_slots, oo.as<int64_t>());
+  ctx->launches += 3;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaMemcpyAsync(oo.as<int64_t>() + nv, &n_elems, sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+  int st = check_device_error(ctx);
+  if (st == GUAC_OK) st = host_out(ctx, out_contig, oc.p, (size_t)nv);
+  if (st == GUAC_OK) st = host_out(ctx, out_locus, ol.p, (size_t)nv);
+  if (st == GUAC_OK) st = host_out(ctx, out_offsets, oo.p, (size_t)nv + 1);
+  if (st == GUAC_OK) st = host_out(ctx, out_elements, oe.p, (size_t)n_elems);
+  cudaStreamSynchronize(ctx->stream);
+  cudaFree(oc.p);
+  cudaFree(ol.p);
+  cudaFree(oo.p);
+  cudaFree(oe.p);
+  if (st != GUAC_OK) return st;
+  *n_out = nv;
+  return GUAC_OK;
+}
+
+int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const guac_range* loci, int32_t n_ranges,
+                          guac_ss_call** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
+                          guac_locus_summary** out_summary, int64_t* out_n_visited) {
+  if (!ctx || !params || !out_calls || !n_calls || !out_arena || !arena_len) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Plan plan;
+  GUAC_TRY(make_plan(ctx, loci, n_ranges, plan));
+  *n_calls = 0;
+  *arena_len = 0;
+  if (out_n_visited) *out_n_visited = 0;
+  SSParamsDev P;
+  P.normal_sample = params->normal_sample_id;
+  P.tumor_sample = params->tumor_sample_id;
+  P.n_samples = std::max(params->normal_sample_id, params->tumor_sample_id) + 1;
+  P.normal_odds = params->normal_odds_threshold;
+  P.tumor_odds = params->tumor_odds_threshold;
+  P.max_read_depth = params->max_read_depth;
+  P.max_normal_alt = params->max_normal_alternate_read_depth;
+  P.min_vaf = (double)params->min_tumor_variant_allele_frequency;
+  if (P.normal_sample < 0 || P.tumor_sample < 0 || P.normal_sample == P.tumor_sample || P.n_samples > ctx->n_samples)
+    return fail(ctx, GUAC_E_INVALID_INPUT, "bad normal/tumor sample ids");
+  if (plan.n_tiles == 0) {
+    GUAC_TRY(host_out(ctx, out_calls, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_arena, nullptr, 0));
+    if (out_summary) GUAC_TRY(host_out(ctx, out_summary, nullptr, 0));
+    return GUAC_OK;
+  }
+  GUAC_TRY(reset_error(ctx));
+  GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
+  if (out_summary) GUAC_TRY(ensure(ctx, ctx->b_summary, (size_t)plan.n_slots * 2 * sizeof(guac_locus_summary)));
+  GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(int)));
+  int max_calls = (int)std::max<size_t>(ctx->b_calls.cap / sizeof(SSCallDev), 1 << 16);
+  int nc = 0;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(SSCallDev)));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
+    somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
+        ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), P, ctx->b_visited.as<uint8_t>(),
+        out_summary ? ctx->b_summary.as<guac_locus_summary>() : nullptr, ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(),
+        max_calls, ctx->b_err.as<DeviceError>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    GUAC_TRY(check_device_error(ctx));  // synchronises
+    if (nc <= max_calls) break;
+    max_calls = nc;  // rerun with room for every call
+  }
+  // sparse part: sort by slot (= range order, locus), lay out the allele arena, compute the evidence
+  std::vector<SSCallDev> calls((size_t)nc);
+  if (nc > 0) {
+    ss_allele_lengths_kernel<<<blocks_for(nc, 128), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(),
+                                                                           ctx->b_calls.as<SSCallDev>(), nc);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(calls.data(), ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    std::sort(calls.begin(), calls.end(), [](const SSCallDev& a, const SSCallDev& b) { return a.slot < b.slot; });
+    uint32_t off = 0;
+    for (auto& c : calls) {
+      c.ref_off = off;
+      off += c.ref_len;
+      c.alt_off = off;
+      off += c.alt_len;
+    }
+    *arena_len = off;
+    GUAC_TRY(ensure(ctx, ctx->b_arena, off + 16));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->b_calls.p, calls.data(), (size_t)nc * sizeof(SSCallDev), cudaMemcpyHostToDevice, ctx->stream));
+    ss_evidence_kernel<<<(unsigned)nc, 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(),
+                                                              ctx->b_arena.as<char>(), ctx->b_err.as<DeviceError>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(calls.data(), ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
+    GUAC_TRY(check_device_error(ctx));
+  }
+  void* h = nullptr;
+  CUDA_TRY(ctx, cudaMallocHost(&h, std::max<size_t>((size_t)nc * sizeof(guac_ss_call), 16)));
+  ctx->host_allocs.insert(h);
+  guac_ss_call* oc = (guac_ss_call*)h;
+  for (int i = 0; i < nc; ++i) {
+    const SSCallDev& c = calls[i];
+    guac_ss_call g;
+    std::memset(&g, 0, sizeof g);
+    g.contig_id = c.contig_id;
+    g.start = c.locus;
+    g.ref_off = c.ref_off;
+    g.ref_len = c.ref_len;
+    g.alt_off = c.alt_off;
+    g.alt_len = c.alt_len;
+    g.somatic_log_odds = c.tumor_alt_lp - c.tumor_ref_lp;
+    g.tumor_ref_log_prob = c.tumor_ref_lp;
+    g.tumor_alt_log_prob = c.tumor_alt_lp;
+    g.normal_ref_log_prob = c.normal_ref_lp;
+    g.normal_alt_log_prob = c.normal_alt_lp;
+    g.tumor_variant_evidence = c.tumor_ev;
+    g.normal_reference_evidence = c.normal_ev;
+    oc[i] = g;
+  }
+  *out_calls = oc;
+  *n_calls = nc;
+  GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)*arena_len));
+  int64_t nv = 0;
+  if (out_summary || out_n_visited) {
+    GUAC_TRY(compact_visited(ctx, plan, 1, nv));
+    if (out_n_visited) *out_n_visited = nv;
+  }
+  if (out_summary) {
+    DevBuf os;
+    GUAC_TRY(ensure(ctx, os, (size_t)nv * 2 * sizeof(guac_locus_summary)));
+    // one uint64 per (locus, sample) record; rows of 2
+    gather_rows_kernel<unsigned long long><<<blocks_for(plan.n_slots * 2, 256), 256, 0, ctx->stream>>>(
+        ctx->b_summary.as<unsigned long long>(), ctx->b_visited.as<uint8_t>(), ctx->b_vis_idx.as<int64_t>(), plan.n_slots, 2,
+        os.as<unsigned long long>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    int st = host_out(ctx, out_summary, os.p, (size_t)nv * 2);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(os.p);
+    if (st != GUAC_OK) return st;
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return GUAC_OK;
+}
+
+}  // extern "C"

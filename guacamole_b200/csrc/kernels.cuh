@@ -1,0 +1,579 @@
+// kernels.cuh — per-locus kernels, generic ("gather") formulation: one warp per locus, lanes
+// stride over the reads that can overlap the locus's tile.  These serve the element-materialising
+// operator (arbitrary host closures), the counting closure, and the first fused somatic-standard
+// path.  The streaming tile kernel of tile_kernels.cuh replaces them on the benchmarked path.
+#pragma once
+#include "device_model.cuh"
+
+namespace guac {
+
+constexpr int TILE_LOCI = 64;
+constexpr int WARPS_PER_CTA = 8;
+constexpr int CTA_THREADS = WARPS_PER_CTA * 32;
+
+__constant__ double c_success_probability[256];  // ADAM PhredUtils.phredToSuccessProbability table
+
+// One range of loci as the planner hands it to the device.
+struct RangeDev {
+  int64_t start, end;
+  int64_t slot0;     // dense slot of `start`
+  int64_t tile0;     // index of the range's first tile
+  int64_t read_clo;  // reads of this contig are [read_clo, read_chi)
+  int64_t read_chi;
+  int32_t contig_id;
+  int32_t ref_index;
+};
+
+// One thread per tile: locate the tile's range, then binary-search the span of reads that can
+// overlap it — start < tile end (reads are sorted by start) and running-max end > tile start.
+__global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ranges, int64_t n_tiles, ReadsView R,
+                                   Tile* __restrict__ tiles) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tiles) return;
+  int lo = 0, hi = n_ranges - 1;
+  while (lo < hi) {  // last range with tile0 <= t
+    int mid = (lo + hi + 1) >> 1;
+    if (ranges[mid].tile0 <= t) lo = mid; else hi = mid - 1;
+  }
+  const RangeDev rg = ranges[lo];
+  Tile tl;
+  int64_t k = t - rg.tile0;
+  tl.locus0 = rg.start + k * TILE_LOCI;
+  tl.n_loci = (int32_t)min((long long)TILE_LOCI, (long long)(rg.end - tl.locus0));
+  tl.contig_id = rg.contig_id;
+  tl.slot0 = rg.slot0 + k * TILE_LOCI;
+  tl.ref_index = rg.ref_index;
+  tl._pad = 0;
+  const int64_t tile_end = tl.locus0 + tl.n_loci;
+  int64_t a = rg.read_clo, b = rg.read_chi;
+  while (a < b) {  // first read with start >= tile_end
+    int64_t m = (a + b) >> 1;
+    if (__ldg(R.start + m) < tile_end) a = m + 1; else b = m;
+  }
+  tl.read_hi = a;
+  const int64_t key = ((int64_t)rg.contig_id << 40) | tl.locus0;
+  a = rg.read_clo;
+  b = tl.read_hi;
+  while (a < b) {  // first read whose running-max end exceeds locus0
+    int64_t m = (a + b) >> 1;
+    if (__ldg(R.runmax_key + m) > key) b = m; else a = m + 1;
+  }
+  tl.read_lo = a;
+  tiles[t] = tl;
+}
+
+// read.end = start + getPaddedReferenceLength (MappedRead.scala:75): M D N = X and P count.
+__global__ void read_ends_kernel(int64_t n, const int64_t* __restrict__ start, const int32_t* __restrict__ contig_id,
+                                 const uint32_t* __restrict__ cigar_off, const uint32_t* __restrict__ cigar,
+                                 int64_t* __restrict__ end, int64_t* __restrict__ key) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  int64_t len = 0;
+  for (uint32_t c = cigar_off[r]; c < cigar_off[r + 1]; ++c) {
+    uint32_t w = cigar[c];
+    int op = w & 15;
+    if (consumes_ref(op) || op == OPC_P) len += w >> 4;
+  }
+  int64_t e = start[r] + len;
+  end[r] = e;
+  key[r] = ((int64_t)contig_id[r] << 40) | e;
+}
+
+// ASCII reference -> stays ASCII (1 B/locus); nothing to convert.  Present so that the
+// reference upload is a single kernel-free memcpy.
+
+// ---- counting closure: Pileup.depth / referenceDepth / positiveDepth + alignment classes ------
+__global__ void __launch_bounds__(CTA_THREADS)
+pileup_counts_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles, int n_samples,
+                     uint8_t* __restrict__ visited, guac_locus_counts* __restrict__ counts, DeviceError* err) {
+  const Tile tile = tiles[blockIdx.x];
+  const RefView ref = refs[tile.ref_index];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int li = warp; li < tile.n_loci; li += WARPS_PER_CTA) {
+    const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
+    bool any = false;
+    for (int64_t base = tile.read_lo; base < tile.read_hi; base += 32) {
+      const int64_t r = base + lane;
+      bool ov = false;
+      if (r < tile.read_hi) ov = __ldg(R.start + r) <= x && x < __ldg(R.end + r);
+      int smp = ov ? (int)__ldg(R.sample_id + r) : 0;
+      if (ov && smp >= n_samples) ov = false;
+      if (ov) {
+        Elem e;
+        int ec = element_at(R, r, x, ref, e);
+        if (ec != DERR_NONE) {
+          report_error(err, ec, tile.contig_id, x, r);
+        } else {
+          uint32_t* c = reinterpret_cast<uint32_t*>(counts + slot * n_samples + smp);
+          atomicAdd(c + 0, 1u);
+          if (e.kind == GUAC_ALN_MATCH) atomicAdd(c + 1, 1u);
+          if (__ldg(R.flags + r) & GUAC_READ_POSITIVE_STRAND) atomicAdd(c + 2, 1u);
+          if (e.kind != GUAC_ALN_MATCH) atomicAdd(c + 2 + e.kind, 1u);  // mismatches.. clipped
+        }
+      }
+      any = any || __any_sync(0xffffffffu, ov);
+    }
+    if (lane == 0) visited[slot] = any ? 1 : 0;
+  }
+}
+
+// ---- element materialisation: per-locus totals, then records in read order ------------------
+__global__ void __launch_bounds__(CTA_THREADS)
+depth_total_kernel(ReadsView R, const Tile* __restrict__ tiles, int n_samples, uint8_t* __restrict__ visited,
+                   int32_t* __restrict__ totals) {
+  const Tile tile = tiles[blockIdx.x];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int li = warp; li < tile.n_loci; li += WARPS_PER_CTA) {
+    const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
+    int n = 0;
+    for (int64_t base = tile.read_lo; base < tile.read_hi; base += 32) {
+      const int64_t r = base + lane;
+      bool ov = false;
+      if (r < tile.read_hi) ov = __ldg(R.start + r) <= x && x < __ldg(R.end + r) && __ldg(R.sample_id + r) < n_samples;
+      n += __popc(__ballot_sync(0xffffffffu, ov));
+    }
+    if (lane == 0) {
+      totals[slot] = n;
+      visited[slot] = n > 0;
+    }
+  }
+}
+
+// elements of visited locus i go to out[elem_off[vis_idx[slot]] ...), ordered by read index
+__global__ void __launch_bounds__(CTA_THREADS)
+write_elements_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles, int n_samples,
+                      int skip_empty, const int64_t* __restrict__ elem_off /*per slot, exclusive*/,
+                      guac_element* __restrict__ out, DeviceError* err) {
+  const Tile tile = tiles[blockIdx.x];
+  const RefView ref = refs[tile.ref_index];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int li = warp; li < tile.n_loci; li += WARPS_PER_CTA) {
+    const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
+    int64_t o = elem_off[slot];
+    for (int64_t base = tile.read_lo; base < tile.read_hi; base += 32) {
+      const int64_t r = base + lane;
+      bool ov = false;
+      if (r < tile.read_hi) ov = __ldg(R.start + r) <= x && x < __ldg(R.end + r) && __ldg(R.sample_id + r) < n_samples;
+      unsigned m = __ballot_sync(0xffffffffu, ov);
+      if (ov) {
+        Elem e;
+        int ec = element_at(R, r, x, ref, e);
+        if (ec != DERR_NONE) report_error(err, ec, tile.contig_id, x, r);
+        guac_element g;
+        g.read_index = r;
+        g.read_position = e.read_position;
+        g.cigar_element_index = e.cigar_element_index;
+        g.cigar_element_locus = e.cigar_element_locus;
+        g.index_within_cigar_element = e.index_within_cigar_element;
+        g.kind = e.kind;
+        g.base = e.base;
+        g.quality = e.quality;
+        g.sample_id = __ldg(R.sample_id + r);
+        g.indel_length = e.indel_length;
+        g._pad = 0;
+        out[o + __popc(m & ((1u << lane) - 1))] = g;
+      }
+      o += __popc(m);
+    }
+  }
+}
+
+// slot -> (contig, locus) for visited loci, at their compacted index
+__global__ void compact_loci_kernel(const Tile* __restrict__ tiles, const uint8_t* __restrict__ visited,
+                                    const int64_t* __restrict__ vis_idx, int32_t* __restrict__ out_contig,
+                                    int64_t* __restrict__ out_locus) {
+  const Tile tile = tiles[blockIdx.x];
+  for (int li = threadIdx.x; li < tile.n_loci; li += blockDim.x) {
+    int64_t slot = tile.slot0 + li;
+    if (visited[slot]) {
+      int64_t d = vis_idx[slot];
+      out_contig[d] = tile.contig_id;
+      out_locus[d] = tile.locus0 + li;
+    }
+  }
+}
+
+template <class T>
+__global__ void gather_rows_kernel(const T* __restrict__ in, const uint8_t* __restrict__ visited,
+                                   const int64_t* __restrict__ vis_idx, int64_t n_slots, int row, T* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_slots * row) return;
+  int64_t slot = i / row;
+  if (visited[slot]) out[vis_idx[slot] * row + (i - slot * row)] = in[i];
+}
+
+// per-slot element offsets for the compacted (visited-only or all) loci: elem_cnt -> exclusive scan done by caller.
+__global__ void gather_offsets_kernel(const int64_t* __restrict__ elem_off, const uint8_t* __restrict__ visited,
+                                      const int64_t* __restrict__ vis_idx, int64_t n_slots, int64_t* __restrict__ out) {
+  int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= n_slots) return;
+  if (visited[slot]) out[vis_idx[slot]] = elem_off[slot];
+}
+
+// ---- somatic-standard (SomaticStandardCaller.scala:155-253), generic gather formulation ------
+struct SSParamsDev {
+  int normal_sample, tumor_sample, n_samples;
+  int normal_odds, tumor_odds;
+  int max_read_depth, max_normal_alt;
+  double min_vaf;  // float widened to double (SomaticStandardCaller.scala:97,189)
+};
+
+struct SSCallDev {
+  int64_t slot;
+  int64_t locus;
+  int64_t read_lo, read_hi;  // span of the locus's tile
+  uint64_t key;              // allele_key of the called allele
+  int64_t rep_read;          // first supporting read (lowest index)
+  int32_t contig_id, ref_index;
+  double tumor_ref_lp, tumor_alt_lp, normal_ref_lp, normal_alt_lp;
+  // filled by ss_evidence_kernel
+  uint32_t ref_off, ref_len, alt_off, alt_len;
+  guac_allele_evidence tumor_ev, normal_ev;
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+// breeze logNormalize over two values (likelihood/Likelihood.scala:136-143)
+__device__ __forceinline__ void log_normalize2(double a, double b, double& na, double& nb) {
+  double mx = fmax(a, b);
+  double sm;
+  if (isinf(mx)) {
+    sm = mx;
+  } else {
+    double acc = 0.0;
+    acc += exp(a - mx);
+    acc += exp(b - mx);
+    sm = mx + log(acc);
+  }
+  na = a - sm;
+  nb = b - sm;
+}
+
+__global__ void __launch_bounds__(CTA_THREADS)
+somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles, SSParamsDev P,
+                        uint8_t* __restrict__ visited, guac_locus_summary* __restrict__ summary, SSCallDev* __restrict__ calls,
+                        int* __restrict__ n_calls, int max_calls, DeviceError* err) {
+  const Tile tile = tiles[blockIdx.x];
+  const RefView ref = refs[tile.ref_index];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu;
+  for (int li = warp; li < tile.n_loci; li += WARPS_PER_CTA) {
+    const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
+    int depthN = 0, depthT = 0, refN = 0, refT = 0;
+    bool any = false;
+    // distinct variant alleles of the tumor pileup, one table entry per lane
+    uint64_t tkey = 0;
+    int tcnt = 0;
+    int64_t tfirst = 0;
+    int ntab = 0;
+    for (int64_t base = tile.read_lo; base < tile.read_hi; base += 32) {
+      const int64_t r = base + lane;
+      bool ov = false;
+      if (r < tile.read_hi) ov = __ldg(R.start + r) <= x && x < __ldg(R.end + r);
+      int smp = ov ? (int)__ldg(R.sample_id + r) : -1;
+      if (ov && smp >= P.n_samples) ov = false;
+      any = any || __any_sync(FULL, ov);
+      Elem e;
+      e.kind = GUAC_ALN_CLIPPED;
+      const bool mine = ov && (smp == P.normal_sample || smp == P.tumor_sample);
+      if (mine) {
+        int ec = element_at(R, r, x, ref, e);
+        if (ec != DERR_NONE) report_error(err, ec, tile.contig_id, x, r);
+      }
+      const bool isN = mine && smp == P.normal_sample, isT = mine && smp == P.tumor_sample;
+      depthN += __popc(__ballot_sync(FULL, isN));
+      depthT += __popc(__ballot_sync(FULL, isT));
+      refN += __popc(__ballot_sync(FULL, isN && e.kind == GUAC_ALN_MATCH));
+      refT += __popc(__ballot_sync(FULL, isT && e.kind == GUAC_ALN_MATCH));
+      const bool var = isT && e.kind != GUAC_ALN_MATCH && e.kind != GUAC_ALN_CLIPPED;  // allele.isVariant
+      uint64_t key = var ? allele_key(R, r, e) : 0;
+      unsigned vm = __ballot_sync(FULL, var);
+      while (vm) {
+        const int L = __ffs(vm) - 1;
+        const uint64_t k = __shfl_sync(FULL, key, L);
+        const unsigned same = __ballot_sync(FULL, var && key == k);
+        const int c = __popc(same);
+        const unsigned hit = __ballot_sync(FULL, lane < ntab && tkey == k);
+        if (hit) {
+          if (lane == __ffs(hit) - 1) tcnt += c;
+        } else if (ntab < 32) {
+          if (lane == ntab) {
+            tkey = k;
+            tcnt = c;
+            tfirst = base + L;
+          }
+          ++ntab;
+        } else if (lane == 0) {
+          report_error(err, DERR_ALLELE_TABLE_FULL, tile.contig_id, x, base + L);
+        }
+        vm &= ~same;
+      }
+    }
+    // most frequent variant allele; ties -> lowest first supporting read (documented canonical order)
+    int bcnt = lane < ntab ? tcnt : -1;
+    int64_t bfirst = lane < ntab ? tfirst : INT64_MAX;
+    uint64_t bkey = tkey;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      int oc = __shfl_xor_sync(FULL, bcnt, d);
+      int64_t of = __shfl_xor_sync(FULL, bfirst, d);
+      uint64_t ok = __shfl_xor_sync(FULL, bkey, d);
+      if (oc > bcnt || (oc == bcnt && of < bfirst)) {
+        bcnt = oc;
+        bfirst = of;
+        bkey = ok;
+      }
+    }
+    // early outs (SomaticStandardCaller.scala:164-172)
+    const bool candidate = depthT > 0 && depthN > 0 && depthT <= P.max_read_depth && depthN <= P.max_read_depth &&
+                           refT != depthT && (depthN - refN) <= P.max_normal_alt;
+    if (lane == 0) visited[slot] = any ? 1 : 0;
+    if (candidate && ntab == 0) {
+      if (lane == 0) report_error(err, DERR_EMPTY_MAXBY, tile.contig_id, x, -1);
+    }
+    const bool evaluate = candidate && ntab > 0;
+    int normalAlt = 0;
+    bool called = false;
+    if (evaluate) {
+      const double f = fmax(P.min_vaf, (double)bcnt / (double)depthT);  // :189
+      double aTR = 0, aTA = 0, aNR = 0, aNA = 0;
+      for (int64_t base = tile.read_lo; base < tile.read_hi; base += 32) {
+        const int64_t r = base + lane;
+        bool ov = false;
+        if (r < tile.read_hi) ov = __ldg(R.start + r) <= x && x < __ldg(R.end + r);
+        int smp = ov ? (int)__ldg(R.sample_id + r) : -1;
+        const bool mine = ov && (smp == P.normal_sample || smp == P.tumor_sample);
+        bool isAlt = false;
+        if (mine) {
+          Elem e;
+          if (element_at(R, r, x, ref, e) == DERR_NONE) {
+            const double p = c_success_probability[e.quality];  // probabilityCorrectIgnoringAlignment
+            const bool isRef = e.kind == GUAC_ALN_MATCH;
+            isAlt = e.kind != GUAC_ALN_MATCH && e.kind != GUAC_ALN_CLIPPED && allele_key(R, r, e) == bkey;
+            const double pr = isRef ? p : 1 - p;  // Likelihood.scala:199-204
+            const double pa = isAlt ? p : 1 - p;
+            if (smp == P.tumor_sample) {
+              aTR += log(pr * 1.0);
+              aTA += log(pr * (1.0 - f) + pa * f);
+            } else {
+              aNR += log(pr * 1.0);
+              aNA += log(pr * 0.5 + pa * 0.5);
+            }
+          }
+        }
+        normalAlt += __popc(__ballot_sync(FULL, mine && smp == P.normal_sample && isAlt));
+      }
+      aTR = warp_sum(aTR);
+      aTA = warp_sum(aTA);
+      aNR = warp_sum(aNR);
+      aNA = warp_sum(aNA);
+      double tR, tA, nR, nA;
+      log_normalize2(aTR, aTA, tR, tA);
+      log_normalize2(aNR, aNA, nR, nA);
+      const double tumorAltLOD = tA - tR, normalRefLOD = nR - nA;
+      // :231-233; MidDeletion has empty alt bases
+      called = tumorAltLOD > P.tumor_odds && normalRefLOD > P.normal_odds && (bkey >> 60) != 4;
+      if (called && lane == 0) {
+        int idx = atomicAdd(n_calls, 1);
+        if (idx < max_calls) {
+          SSCallDev c;
+          c.slot = slot;
+          c.locus = x;
+          c.read_lo = tile.read_lo;
+          c.read_hi = tile.read_hi;
+          c.key = bkey;
+          c.rep_read = bfirst;
+          c.contig_id = tile.contig_id;
+          c.ref_index = tile.ref_index;
+          c.tumor_ref_lp = tR;
+          c.tumor_alt_lp = tA;
+          c.normal_ref_lp = nR;
+          c.normal_alt_lp = nA;
+          c.ref_off = c.ref_len = c.alt_off = c.alt_len = 0;
+          calls[idx] = c;
+        }
+      }
+    }
+    if (summary != nullptr && lane == 0) {
+      const uint16_t fl = (evaluate ? 1 : 0) | (called ? 2 : 0);
+      guac_locus_summary sn, st;
+      sn.depth = (uint16_t)min(depthN, 65535);
+      sn.reference_depth = (uint16_t)min(refN, 65535);
+      sn.top_alt_count = (uint16_t)min(evaluate ? normalAlt : 0, 65535);
+      sn.flags = fl;
+      st.depth = (uint16_t)min(depthT, 65535);
+      st.reference_depth = (uint16_t)min(refT, 65535);
+      st.top_alt_count = (uint16_t)min(evaluate ? bcnt : 0, 65535);
+      st.flags = fl;
+      summary[slot * 2 + 0] = sn;
+      summary[slot * 2 + 1] = st;
+    }
+  }
+}
+
+// MappedRead.countOfMismatches (MappedRead.scala:53-64): Mismatch elements over the whole read.
+__device__ inline int count_of_mismatches(const ReadsView& R, int64_t r, const RefView& ref, DeviceError* err, int contig) {
+  const int64_t s = __ldg(R.start + r), en = __ldg(R.end + r);
+  int n = 0;
+  for (int64_t x = s; x < en; ++x) {
+    Elem e;
+    int ec = element_at(R, r, x, ref, e);
+    if (ec != DERR_NONE) {
+      report_error(err, ec, contig, x, r);
+      return n;
+    }
+    n += e.kind == GUAC_ALN_MISMATCH;
+  }
+  return n;
+}
+
+constexpr int MM_BINS = 1024;
+
+// lower/upper middle of a histogram with n entries -> (a, b): values at ranks (n-1)/2 and n/2
+__device__ inline void hist_middle(const unsigned* h, int bins, int n, int& a, int& b) {
+  int ra = (n - 1) / 2, rb = n / 2;
+  int acc = 0;
+  a = b = 0;
+  bool gotA = false;
+  for (int v = 0; v < bins; ++v) {
+    acc += (int)h[v];
+    if (!gotA && acc > ra) {
+      a = v;
+      gotA = true;
+    }
+    if (acc > rb) {
+      b = v;
+      return;
+    }
+  }
+}
+
+// AlleleEvidence.apply (variants/AlleleEvidence.scala:42-85) for both evidences of one call:
+// tumor with the called allele, normal with the reference allele.  One CTA per call.
+// Also writes the allele strings (variants/Allele.scala) into the arena.
+__global__ void __launch_bounds__(128)
+ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P, SSCallDev* __restrict__ calls,
+                   char* __restrict__ arena, DeviceError* err) {
+  __shared__ unsigned h_mapq[256], h_bq[256], h_mm[MM_BINS];
+  __shared__ unsigned s_depth, s_pos, s_adepth, s_apos;
+  SSCallDev& c = calls[blockIdx.x];
+  const RefView ref = refs[c.ref_index];
+  const int64_t x = c.locus;
+  for (int which = 0; which < 2; ++which) {
+    const int target = which == 0 ? P.tumor_sample : P.normal_sample;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) h_mapq[i] = h_bq[i] = 0;
+    for (int i = threadIdx.x; i < MM_BINS; i += blockDim.x) h_mm[i] = 0;
+    if (threadIdx.x == 0) s_depth = s_pos = s_adepth = s_apos = 0;
+    __syncthreads();
+    for (int64_t r = c.read_lo + threadIdx.x; r < c.read_hi; r += blockDim.x) {
+      if (!(__ldg(R.start + r) <= x && x < __ldg(R.end + r)) || __ldg(R.sample_id + r) != target) continue;
+      Elem e;
+      if (element_at(R, r, x, ref, e) != DERR_NONE) continue;
+      const bool pos = __ldg(R.flags + r) & GUAC_READ_POSITIVE_STRAND;
+      atomicAdd(&s_depth, 1u);
+      if (pos) atomicAdd(&s_pos, 1u);
+      bool isAllele;
+      if (which == 0)
+        isAllele = e.kind != GUAC_ALN_MATCH && e.kind != GUAC_ALN_CLIPPED && allele_key(R, r, e) == c.key;
+      else
+        isAllele = e.kind == GUAC_ALN_MATCH;
+      if (isAllele) {
+        atomicAdd(&s_adepth, 1u);
+        if (pos) atomicAdd(&s_apos, 1u);
+        atomicAdd(&h_mapq[__ldg(R.mapq + r)], 1u);
+        atomicAdd(&h_bq[e.quality], 1u);
+        int mm = count_of_mismatches(R, r, ref, err, c.contig_id);
+        if (mm >= MM_BINS) {
+          report_error(err, DERR_MISMATCH_HIST, c.contig_id, x, r);
+          mm = MM_BINS - 1;
+        }
+        atomicAdd(&h_mm[mm], 1u);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      guac_allele_evidence ev;
+      const double lp = which == 0 ? c.tumor_alt_lp : c.normal_ref_lp;
+      ev.probability = exp(-lp);  // SomaticStandardCaller.scala:237-238 (sic)
+      ev.read_depth = (int)s_depth;
+      ev.allele_read_depth = (int)s_adepth;
+      ev.forward_depth = (int)s_pos;
+      ev.allele_forward_depth = (int)s_apos;
+      const int n = (int)s_adepth;
+      if (n == 0) {
+        const double nan = __longlong_as_double(0x7ff8000000000000ll);
+        ev.mean_mapping_quality = ev.median_mapping_quality = ev.mean_base_quality = ev.median_base_quality =
+            ev.median_mismatches_per_read = nan;
+      } else {
+        double sm = 0, sq = 0;
+        for (int v = 0; v < 256; ++v) {
+          sm += (double)v * h_mapq[v];
+          sq += (double)v * h_bq[v];
+        }
+        ev.mean_mapping_quality = sm / n;
+        ev.mean_base_quality = sq / n;
+        int a, b;
+        hist_middle(h_mapq, 256, n, a, b);
+        ev.median_mapping_quality = (n & 1) ? (double)a : ((double)a + (double)b) / 2;
+        hist_middle(h_bq, 256, n, a, b);
+        ev.median_base_quality = (n & 1) ? (double)a : ((double)a + (double)b) / 2;
+        hist_middle(h_mm, MM_BINS, n, a, b);
+        ev.median_mismatches_per_read = (n & 1) ? (double)a : (double)((a + b) / 2);  // DenseVector[Int] median
+      }
+      if (which == 0) c.tumor_ev = ev; else c.normal_ev = ev;
+    }
+    __syncthreads();
+  }
+  // allele strings
+  if (threadIdx.x == 0) {
+    const int kind = (int)(c.key >> 60);
+    char* rp = arena + c.ref_off;
+    char* ap = arena + c.alt_off;
+    const uint8_t rb = ref.at(x);
+    if (kind == 1) {  // Mismatch
+      rp[0] = (char)rb;
+      ap[0] = (char)(c.key & 0xff);
+    } else if (kind == 3) {  // Deletion: ref = ref[x .. x+len], alt = ref[x]
+      for (uint32_t k = 0; k < c.ref_len; ++k) rp[k] = (char)ref.at(x + k);
+      ap[0] = (char)rb;
+    } else if (kind == 2 || kind == 5) {  // Insertion: ref = seq[0], alt = seq
+      Elem e;
+      if (element_at(R, c.rep_read, x, ref, e) == DERR_NONE) {
+        const uint64_t s0 = __ldg(R.seq_off + c.rep_read);
+        for (uint32_t k = 0; k < c.alt_len; ++k) ap[k] = (char)read_base(R, s0 + e.read_position + k);
+        rp[0] = ap[0];
+      }
+    }
+  }
+}
+
+// lengths of the allele strings of a call (host lays out the arena)
+__global__ void ss_allele_lengths_kernel(ReadsView R, const RefView* __restrict__ refs, SSCallDev* __restrict__ calls, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  SSCallDev& c = calls[i];
+  const int kind = (int)(c.key >> 60);
+  if (kind == 1) {
+    c.ref_len = 1;
+    c.alt_len = 1;
+  } else if (kind == 3) {
+    c.ref_len = (uint32_t)(c.key & 0xffffffffu) + 1;
+    c.alt_len = 1;
+  } else {
+    Elem e;
+    const RefView ref = refs[c.ref_index];
+    c.ref_len = 1;
+    c.alt_len = 1;
+    if (element_at(R, c.rep_read, c.locus, ref, e) == DERR_NONE) {
+      const uint64_t s0 = __ldg(R.seq_off + c.rep_read);
+      const int32_t read_len = (int32_t)(__ldg(R.seq_off + c.rep_read + 1) - s0);
+      c.alt_len = (uint32_t)(min(e.read_position + e.indel_length + 1, read_len) - e.read_position);
+    }
+  }
+}
+
+}  // namespace guac
