@@ -16,6 +16,7 @@
 #include "../../include/guac_b200.h"
 #include "kernels.cuh"
 #include "scan.cuh"
+#include "synth_kernels.cuh"
 
 using namespace guac;
 
@@ -55,6 +56,10 @@ struct guac_ctx {
   // plan / scratch
   DevBuf b_ranges, b_tiles, b_visited, b_vis_idx, b_counts, b_totals, b_elem_off, b_summary, b_calls, b_ncalls, b_err, b_arena;
   std::set<void*> host_allocs;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool have_timing = false;
+  int64_t timed_loci = 0;
+  DevBuf b_nops;
 };
 
 namespace {
@@ -257,6 +262,43 @@ int compact_visited(guac_ctx* ctx, const Plan& plan, int skip_empty, int64_t& n_
   return GUAC_OK;
 }
 
+// Derives end / running-max keys and publishes the device view (shared by upload and synth).
+int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
+  GUAC_TRY(ensure(ctx, ctx->b_end, (size_t)(n + 1) * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, ctx->b_key, (size_t)(n + 1) * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, ctx->b_runmax, (size_t)(n + 1) * sizeof(int64_t)));
+  if (n > 0) {
+    read_ends_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->b_start.as<int64_t>(), ctx->b_contig.as<int32_t>(),
+                                                                  ctx->b_cigar_off.as<uint32_t>(), ctx->b_cigar.as<uint32_t>(),
+                                                                  ctx->b_end.as<int64_t>(), ctx->b_key.as<int64_t>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    GUAC_TRY((device_scan<false, int64_t>(ctx, ctx->b_key.as<int64_t>(), ctx->b_runmax.as<int64_t>(), n, OpMax())));
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // caller's buffers may go away after return
+  ReadsView& R = ctx->R;
+  R.n_reads = n;
+  R.start = ctx->b_start.as<int64_t>();
+  R.end = ctx->b_end.as<int64_t>();
+  R.runmax_key = ctx->b_runmax.as<int64_t>();
+  R.cigar_off = ctx->b_cigar_off.as<uint32_t>();
+  R.cigar = ctx->b_cigar.as<uint32_t>();
+  R.seq_off = ctx->b_seq_off.as<uint64_t>();
+  R.bases2 = ctx->b_bases2.as<uint8_t>();
+  R.nmask = ctx->b_nmask.as<uint8_t>();
+  R.n_exc = n_exc;
+  R.exc_pos = ctx->b_exc_pos.as<uint64_t>();
+  R.exc_base = ctx->b_exc_base.as<uint8_t>();
+  R.qual = ctx->b_qual.as<uint8_t>();
+  R.mapq = ctx->b_mapq.as<uint8_t>();
+  R.flags = ctx->b_flags.as<uint8_t>();
+  R.sample_id = ctx->b_sample.as<uint8_t>();
+  ctx->n_reads = n;
+  ctx->n_samples = n_samples;
+  ctx->have_reads = true;
+  return GUAC_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -284,6 +326,8 @@ int guac_ctx_create(int device, guac_ctx** out) {
     delete ctx;
     return GUAC_E_CUDA;
   }
+  cudaEventCreate(&ctx->ev0);
+  cudaEventCreate(&ctx->ev1);
   *out = ctx;
   return GUAC_OK;
 }
@@ -302,6 +346,9 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   for (auto& kv : ctx->contigs)
     if (kv.second.bases) cudaFree(kv.second.bases);
   for (void* h : ctx->host_allocs) cudaFreeHost(h);
+  if (ctx->b_nops.p) cudaFree(ctx->b_nops.p);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -425,39 +472,7 @@ int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* b) {
   GUAC_TRY(upload(ctx, ctx->b_mapq, b->mapq, (size_t)n));
   GUAC_TRY(upload(ctx, ctx->b_flags, b->flags, (size_t)n));
   GUAC_TRY(upload(ctx, ctx->b_sample, b->sample_id, (size_t)n));
-  GUAC_TRY(ensure(ctx, ctx->b_end, (size_t)(n + 1) * sizeof(int64_t)));
-  GUAC_TRY(ensure(ctx, ctx->b_key, (size_t)(n + 1) * sizeof(int64_t)));
-  GUAC_TRY(ensure(ctx, ctx->b_runmax, (size_t)(n + 1) * sizeof(int64_t)));
-  if (n > 0) {
-    read_ends_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->b_start.as<int64_t>(), ctx->b_contig.as<int32_t>(),
-                                                                  ctx->b_cigar_off.as<uint32_t>(), ctx->b_cigar.as<uint32_t>(),
-                                                                  ctx->b_end.as<int64_t>(), ctx->b_key.as<int64_t>());
-    ctx->launches += 1;
-    CUDA_TRY(ctx, cudaGetLastError());
-    GUAC_TRY((device_scan<false, int64_t>(ctx, ctx->b_key.as<int64_t>(), ctx->b_runmax.as<int64_t>(), n, OpMax())));
-  }
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // caller's buffers may go away after return
-  ReadsView& R = ctx->R;
-  R.n_reads = n;
-  R.start = ctx->b_start.as<int64_t>();
-  R.end = ctx->b_end.as<int64_t>();
-  R.runmax_key = ctx->b_runmax.as<int64_t>();
-  R.cigar_off = ctx->b_cigar_off.as<uint32_t>();
-  R.cigar = ctx->b_cigar.as<uint32_t>();
-  R.seq_off = ctx->b_seq_off.as<uint64_t>();
-  R.bases2 = ctx->b_bases2.as<uint8_t>();
-  R.nmask = ctx->b_nmask.as<uint8_t>();
-  R.n_exc = b->n_exc;
-  R.exc_pos = ctx->b_exc_pos.as<uint64_t>();
-  R.exc_base = ctx->b_exc_base.as<uint8_t>();
-  R.qual = ctx->b_qual.as<uint8_t>();
-  R.mapq = ctx->b_mapq.as<uint8_t>();
-  R.flags = ctx->b_flags.as<uint8_t>();
-  R.sample_id = ctx->b_sample.as<uint8_t>();
-  ctx->n_reads = n;
-  ctx->n_samples = b->n_samples;
-  ctx->have_reads = true;
-  return GUAC_OK;
+  return finish_reads(ctx, n, b->n_samples, b->n_exc);
 }
 
 int guac_pileup_counts(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, int32_t skip_empty, int32_t** out_contig,
@@ -601,17 +616,22 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   }
   GUAC_TRY(reset_error(ctx));
   GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
-  if (out_summary) GUAC_TRY(ensure(ctx, ctx->b_summary, (size_t)plan.n_slots * 2 * sizeof(guac_locus_summary)));
+  // the dense per-(locus, sample) summary is part of the kernel's output contract; it stays in HBM unless asked for
+  GUAC_TRY(ensure(ctx, ctx->b_summary, (size_t)plan.n_slots * 2 * sizeof(guac_locus_summary)));
   GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(int)));
   int max_calls = (int)std::max<size_t>(ctx->b_calls.cap / sizeof(SSCallDev), 1 << 16);
   int nc = 0;
   for (int attempt = 0; attempt < 2; ++attempt) {
     GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(SSCallDev)));
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
+    cudaEventRecord(ctx->ev0, ctx->stream);
     somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
         ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), P, ctx->b_visited.as<uint8_t>(),
-        out_summary ? ctx->b_summary.as<guac_locus_summary>() : nullptr, ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(),
+        ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(),
         max_calls, ctx->b_err.as<DeviceError>());
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    ctx->have_timing = true;
+    ctx->timed_loci = plan.n_slots;
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
     CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
@@ -691,6 +711,134 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     cudaFree(os.p);
     if (st != GUAC_OK) return st;
   }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return GUAC_OK;
+}
+
+void* guac_stream(guac_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci) {
+  if (!ctx || !ms) return GUAC_E_INVALID_INPUT;
+  if (!ctx->have_timing) return fail(ctx, GUAC_E_STATE, "no timed kernel yet");
+  CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev1));
+  CUDA_TRY(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+  if (n_loci) *n_loci = ctx->timed_loci;
+  return GUAC_OK;
+}
+
+int guac_synth_generate(guac_ctx* ctx, int32_t contig_id, int64_t contig_len, int32_t n_samples, const int32_t* depths,
+                        const uint8_t* tumor, uint64_t seed) {
+  if (!ctx || !depths || !tumor) return GUAC_E_INVALID_INPUT;
+  if (n_samples <= 0 || n_samples > 16 || contig_len <= 2 * synth::MARGIN) return fail(ctx, GUAC_E_INVALID_INPUT, "bad synth shape");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  ctx->have_reads = false;
+  synth::Params P;
+  std::memset(&P, 0, sizeof P);
+  P.seed = seed;
+  P.contig_len = contig_len;
+  P.n_samples = n_samples;
+  // interleaving pattern proportional to depths: round-robin, largest first (synth.py sample_pattern)
+  int64_t total_depth = 0;
+  int g = 0;
+  for (int s = 0; s < n_samples; ++s) {
+    if (depths[s] <= 0) return fail(ctx, GUAC_E_INVALID_INPUT, "depths must be positive");
+    total_depth += depths[s];
+    int a = depths[s], b = g;
+    while (b) { int t = a % b; a = b; b = t; }
+    g = a;
+    P.is_tumor[s] = tumor[s] ? 1 : 0;
+  }
+  std::vector<int> counts(n_samples), order(n_samples);
+  int plen = 0;
+  for (int s = 0; s < n_samples; ++s) { counts[s] = depths[s] / g; plen += counts[s]; order[s] = s; }
+  if (plen > 64) return fail(ctx, GUAC_E_UNSUPPORTED, "depth ratio pattern longer than 64");
+  std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return counts[x] > counts[y]; });
+  std::vector<int> remaining = counts;
+  int k = 0;
+  while (k < plen)
+    for (int s : order)
+      if (remaining[s]) { P.pattern[k++] = (uint8_t)s; --remaining[s]; }
+  P.pattern_len = plen;
+  const int64_t n = total_depth * contig_len / synth::READ_LEN;
+  P.n_reads = n;
+  // reference
+  GUAC_TRY(guac_ref_reserve(ctx, contig_id, 0, contig_len));
+  synth::reference_kernel<<<blocks_for(contig_len, 256), 256, 0, ctx->stream>>>(seed, contig_len, ctx->contigs[contig_id].bases);
+  // reads
+  const int64_t n_bases = n * synth::READ_LEN;
+  GUAC_TRY(ensure(ctx, ctx->b_start, (size_t)n * 8 + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_contig, (size_t)n * 4 + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_mapq, (size_t)n + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_flags, (size_t)n + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_sample, (size_t)n + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_seq_off, (size_t)(n + 1) * 8 + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_nops, (size_t)n + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_cigar_off, (size_t)(n + 1) * 4 + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_cigar, (size_t)n * 3 * 4 + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_bases2, (size_t)(n_bases / 4) + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_nmask, (size_t)(n_bases / 8) + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_qual, (size_t)n_bases + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_exc_pos, 16));
+  GUAC_TRY(ensure(ctx, ctx->b_exc_base, 16));
+  GUAC_TRY(ensure(ctx, ctx->b_elem_off, (size_t)(n + 2) * sizeof(int64_t)));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_nmask.p, 0, (size_t)(n_bases / 8) + 16, ctx->stream));
+  synth::read_headers_kernel<<<blocks_for(n + 1, 256), 256, 0, ctx->stream>>>(
+      P, ctx->b_start.as<int64_t>(), ctx->b_contig.as<int32_t>(), contig_id, ctx->b_mapq.as<uint8_t>(), ctx->b_flags.as<uint8_t>(),
+      ctx->b_sample.as<uint8_t>(), ctx->b_seq_off.as<uint64_t>(), ctx->b_nops.as<uint8_t>());
+  int64_t* off64 = ctx->b_elem_off.as<int64_t>();
+  GUAC_TRY((device_scan<true, uint8_t>(ctx, ctx->b_nops.as<uint8_t>(), off64, n, OpSum(), off64 + n)));
+  synth::read_cigars_kernel<<<blocks_for(n + 1, 256), 256, 0, ctx->stream>>>(P, off64, ctx->b_cigar_off.as<uint32_t>(),
+                                                                             ctx->b_cigar.as<uint32_t>());
+  synth::read_bases_kernel<<<blocks_for(n_bases / 4, 256), 256, 0, ctx->stream>>>(P, ctx->b_bases2.as<uint8_t>(),
+                                                                                  ctx->b_qual.as<uint8_t>());
+  ctx->launches += 4;
+  CUDA_TRY(ctx, cudaGetLastError());
+  ctx->contig_spans.clear();
+  ctx->contig_spans.push_back({contig_id, {0, n}});
+  return finish_reads(ctx, n, n_samples, 0);
+}
+
+int guac_reads_export(guac_ctx* ctx, guac_read_batch* out) {
+  if (!ctx || !out) return GUAC_E_INVALID_INPUT;
+  if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int64_t n = ctx->n_reads;
+  std::memset(out, 0, sizeof *out);
+  out->n_reads = n;
+  out->n_samples = ctx->n_samples;
+  uint64_t n_bases = 0;
+  uint32_t n_cigar = 0;
+  if (n) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_bases, ctx->R.seq_off + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_cigar, ctx->R.cigar_off + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  GUAC_TRY(host_out(ctx, const_cast<int32_t**>(&out->contig_id), ctx->b_contig.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<int64_t**>(&out->start), ctx->b_start.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->cigar_off), ctx->b_cigar_off.p, (size_t)n + 1));
+  GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->cigar), ctx->b_cigar.p, (size_t)n_cigar));
+  GUAC_TRY(host_out(ctx, const_cast<uint64_t**>(&out->seq_off), ctx->b_seq_off.p, (size_t)n + 1));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->bases2), ctx->b_bases2.p, (size_t)((n_bases + 3) / 4)));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->nmask), ctx->b_nmask.p, (size_t)((n_bases + 7) / 8)));
+  out->n_exc = ctx->R.n_exc;
+  GUAC_TRY(host_out(ctx, const_cast<uint64_t**>(&out->exc_pos), ctx->b_exc_pos.p, (size_t)ctx->R.n_exc));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->exc_base), ctx->b_exc_base.p, (size_t)ctx->R.n_exc));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->qual), ctx->b_qual.p, (size_t)n_bases));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->mapq), ctx->b_mapq.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->flags), ctx->b_flags.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->sample_id), ctx->b_sample.p, (size_t)n));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return GUAC_OK;
+}
+
+int guac_ref_export(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t len, uint8_t* dst) {
+  if (!ctx || !dst) return GUAC_E_INVALID_INPUT;
+  auto it = ctx->contigs.find(contig_id);
+  if (it == ctx->contigs.end()) return fail(ctx, GUAC_E_INVALID_INPUT, "contig not found");
+  const ContigDev& c = it->second;
+  if (offset < c.offset || offset + len > c.offset + c.len) return fail(ctx, GUAC_E_INVALID_INPUT, "Illegal reference slice");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst, c.bases + (offset - c.offset), (size_t)len, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return GUAC_OK;
 }

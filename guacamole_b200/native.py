@@ -245,6 +245,85 @@ class Context:
         self._check(self.lib.guac_reads_upload(self.ctx, C.byref(b)))
         self._batch = batch  # keep host arrays alive
 
+    def upload_reads_struct(self, b: ReadBatchC, n_samples: int):
+        """Uploads an already packed batch (e.g. pinned buffers from export_reads_struct)."""
+        self._check(self.lib.guac_reads_upload(self.ctx, C.byref(b)))
+        self._batch = type("B", (), {"n_samples": n_samples})()
+
+    # -- measurement support -----------------------------------------------------
+    def synth_generate(self, contig_len: int, depths: Sequence[int], tumor: Sequence[bool], seed: int, contig_id: int = 0,
+                       contig_name: str = "synth1"):
+        d = np.asarray(depths, np.int32)
+        t = np.asarray(tumor, np.uint8)
+        self._check(self.lib.guac_synth_generate(self.ctx, C.c_int32(contig_id), C.c_int64(contig_len), C.c_int32(len(d)),
+                                                 ptr(d, i32p), ptr(t, u8p), C.c_uint64(seed)))
+        self.contig_names = [contig_name]
+        self._batch = type("B", (), {"n_samples": len(d)})()
+
+    def export_reads_struct(self) -> ReadBatchC:
+        """Device batch -> library-owned pinned host buffers (still packed)."""
+        b = ReadBatchC()
+        self._check(self.lib.guac_reads_export(self.ctx, C.byref(b)))
+        return b
+
+    def free_reads_struct(self, b: ReadBatchC):
+        for name, _ in ReadBatchC._fields_:
+            v = getattr(b, name)
+            if not isinstance(v, int) and v:
+                self.lib.guac_free(self.ctx, C.cast(v, C.c_void_p))
+
+    def export_reads(self, contig_names: Optional[List[str]] = None, lo: int = 0, hi: Optional[int] = None) -> ReadBatch:
+        """Reads [lo, hi) of the device batch as a host ReadBatch (ASCII bases unpacked)."""
+        b = self.export_reads_struct()
+        try:
+            n = b.n_reads
+            hi = n if hi is None else min(hi, n)
+            lo = max(0, min(lo, hi))
+
+            def arr(p, dtype, count, off=0):
+                if count == 0:
+                    return np.zeros(0, dtype)
+                a = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=((off + count) * np.dtype(dtype).itemsize,))
+                return a.view(dtype)[off:off + count].copy()
+
+            seq_off = arr(b.seq_off, np.uint64, hi - lo + 1, lo)
+            cigar_off = arr(b.cigar_off, np.uint32, hi - lo + 1, lo)
+            s0, s1 = int(seq_off[0]), int(seq_off[-1])
+            c0, c1 = int(cigar_off[0]), int(cigar_off[-1])
+            assert s0 % 8 == 0, "export window must start on an 8-base boundary"
+            bases2 = arr(b.bases2, np.uint8, (s1 - s0 + 3) // 4, s0 // 4)
+            codes = ((bases2[:, None] >> np.array([0, 2, 4, 6], np.uint8)[None, :]) & 3).reshape(-1)[:s1 - s0]
+            ascii_bases = np.frombuffer(b"ACGT", np.uint8)[codes].copy()
+            if b.n_exc:
+                pos = arr(b.exc_pos, np.uint64, b.n_exc).astype(np.int64)
+                eb = arr(b.exc_base, np.uint8, b.n_exc)
+                m = (pos >= s0) & (pos < s1)
+                ascii_bases[pos[m] - s0] = eb[m]
+            return ReadBatch(n_samples=b.n_samples, contig_names=list(contig_names or self.contig_names),
+                             contig_id=arr(b.contig_id, np.int32, hi - lo, lo), start=arr(b.start, np.int64, hi - lo, lo),
+                             cigar_off=(cigar_off - np.uint32(c0)).astype(np.uint32), cigar=arr(b.cigar, np.uint32, c1 - c0, c0),
+                             seq_off=seq_off - np.uint64(s0), bases_ascii=ascii_bases, qual=arr(b.qual, np.uint8, s1 - s0, s0),
+                             mapq=arr(b.mapq, np.uint8, hi - lo, lo), flags=arr(b.flags, np.uint8, hi - lo, lo),
+                             sample_id=arr(b.sample_id, np.uint8, hi - lo, lo))
+        finally:
+            self.free_reads_struct(b)
+
+    def export_reference(self, contig_id: int, offset: int, length: int) -> np.ndarray:
+        out = np.zeros(length, np.uint8)
+        self._check(self.lib.guac_ref_export(self.ctx, C.c_int32(contig_id), C.c_int64(offset), C.c_int64(length), ptr(out, u8p)))
+        return out
+
+    @property
+    def stream(self) -> int:
+        self.lib.guac_stream.restype = C.c_void_p
+        self.lib.guac_stream.argtypes = [C.c_void_p]
+        return int(self.lib.guac_stream(self.ctx) or 0)
+
+    def last_kernel_ms(self) -> Tuple[float, int]:
+        ms, n = C.c_float(), C.c_int64()
+        self._check(self.lib.guac_last_kernel_ms(self.ctx, C.byref(ms), C.byref(n)))
+        return float(ms.value), int(n.value)
+
     # -- pileup ------------------------------------------------------------------
     def pileup_counts(self, ranges: Sequence[Tuple[int, int, int]], skip_empty: bool = True):
         r = make_ranges(ranges)

@@ -101,7 +101,8 @@ def generate_reads(contig_len: int, depths: Sequence[int], tumor: Sequence[bool]
     span = contig_len - MARGIN
     # start = floor((j + u) * span / N), u in [0,1) on 16 bits -> monotone in j
     u16 = (rnd(seed, S_START, ju) & U64(0xFFFF)).astype(np.int64)
-    start = ((j * 65536 + u16) * span) // (N * 65536)
+    js = j * span  # floor((j * 65536 + u16) * span / (N * 65536)) without int64 overflow
+    start = js // N + ((js % N) * 65536 + u16 * span) // (N * 65536)
     hr = rnd(seed, S_READ, ju)
     positive = (hr & U64(1)).astype(bool)
     hap = ((hr >> U64(1)) & U64(1)).astype(np.uint8)

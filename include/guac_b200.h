@@ -242,6 +242,31 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
                           guac_ss_call** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
                           guac_locus_summary** out_summary, int64_t* out_n_visited);
 
+/* ---- measurement support ----------------------------------------------------
+ * These have no counterpart in the reference: they exist so that bench.py and the
+ * tests can generate SURVEY.md 8(d)'s seeded synthetic reads directly in HBM, read them
+ * back, and time the kernels on the library's own stream. */
+
+/* CUDA stream (cudaStream_t) every kernel of this context is launched on. */
+void* guac_stream(guac_ctx* ctx);
+/* Device time in ms (CUDA events on the context's stream) of the dominant per-locus kernel
+ * of the most recent caller invocation, and how many loci it processed. */
+int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci);
+
+/* Generates the synthetic batch (guacamole_b200/synth.py is the specification) for one
+ * contig directly on the device, as if guac_ref_upload + guac_reads_upload had been
+ * called: reference of contig_len loci, sum(depths)*contig_len/100 reads of 100 bases,
+ * samples interleaved proportionally to depths[0..n_samples), tumor[s] != 0 marks samples
+ * that carry the planted somatic SNVs. */
+int guac_synth_generate(guac_ctx* ctx, int32_t contig_id, int64_t contig_len, int32_t n_samples, const int32_t* depths,
+                        const uint8_t* tumor, uint64_t seed);
+
+/* Copies the uploaded (or generated) batch back into library-owned pinned host memory;
+ * every pointer of *out is released with guac_free. */
+int guac_reads_export(guac_ctx* ctx, guac_read_batch* out);
+/* Copies [offset, offset+len) of a contig's reference window to `dst` (host). */
+int guac_ref_export(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t len, uint8_t* dst);
+
 #ifdef __cplusplus
 }
 #endif

@@ -445,3 +445,65 @@ int oracle_success_probability_to_phred(double p) { return successProbabilityToP
 double oracle_phred_to_success_probability(int q) { return phredToSuccessProbability(q); }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------
+// C twin of the synthetic-read generator (guacamole_b200/synth.py is the specification;
+// arithmetic shared with the CUDA twin through csrc/synth_model.h).  Produces reads
+// [read_lo, read_hi) of the batch into caller-allocated arrays, ASCII bases.
+// ---------------------------------------------------------------------------------
+#include "../guacamole_b200/csrc/synth_model.h"
+
+extern "C" int oracle_synth_generate(int64_t contig_len, int32_t n_samples, const int32_t* depths, const uint8_t* tumor,
+                                     const uint8_t* pattern, int32_t pattern_len, uint64_t seed, int64_t read_lo,
+                                     int64_t read_hi, int64_t* start, uint32_t* cigar_off, uint32_t* cigar, uint8_t* bases_ascii,
+                                     uint8_t* qual, uint8_t* mapq, uint8_t* flags, uint8_t* sample, int n_threads) {
+  using namespace guac::synth;
+  Params P;
+  std::memset(&P, 0, sizeof P);
+  P.seed = seed;
+  P.contig_len = contig_len;
+  P.n_samples = n_samples;
+  P.pattern_len = pattern_len;
+  int64_t total = 0;
+  for (int s = 0; s < n_samples; ++s) {
+    total += depths[s];
+    P.is_tumor[s] = tumor[s];
+  }
+  for (int i = 0; i < pattern_len; ++i) P.pattern[i] = pattern[i];
+  P.n_reads = total * contig_len / READ_LEN;
+  const int64_t n = read_hi - read_lo;
+  uint32_t off = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    ReadHeader h = read_header(P, read_lo + i);
+    cigar_off[i] = off;
+    write_cigar(h, cigar + off);
+    off += h.n_ops;
+    start[i] = h.start;
+    mapq[i] = h.mapq;
+    flags[i] = h.flags;
+    sample[i] = (uint8_t)h.sample;
+  }
+  cigar_off[n] = off;
+  std::vector<std::thread> th;
+  int T = std::max(1, n_threads);
+  for (int t = 0; t < T; ++t)
+    th.emplace_back([&, t] {
+      for (int64_t i = t; i < n; i += T) {
+        ReadHeader h = read_header(P, read_lo + i);
+        for (int k = 0; k < READ_LEN; ++k) {
+          int code;
+          uint8_t q;
+          base_and_qual(P, h, read_lo + i, k, code, q);
+          bases_ascii[i * READ_LEN + k] = (uint8_t)"ACGT"[code];
+          qual[i * READ_LEN + k] = q;
+        }
+      }
+    });
+  for (auto& x : th) x.join();
+  return 0;
+}
+
+extern "C" void oracle_synth_reference(uint64_t seed, int64_t lo, int64_t hi, uint8_t* out) {
+  using namespace guac::synth;
+  for (int64_t i = lo; i < hi; ++i) out[i - lo] = (uint8_t)"ACGT"[rnd_k(stream_key(seed, S_REF), (uint64_t)i) & 3];
+}

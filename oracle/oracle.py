@@ -192,3 +192,36 @@ def phred_to_success_probability(q: int) -> float:
 
 def success_probability_to_phred(p: float) -> int:
     return lib().oracle_success_probability_to_phred(p)
+
+
+def synth_generate(contig_len: int, depths, tumor, seed: int, read_lo: int = 0, read_hi=None, contig_name="synth1",
+                   n_threads: int = 0) -> ReadBatch:
+    """C twin of guacamole_b200.synth.generate_reads (fast; used for large CPU-side samples)."""
+    from guacamole_b200 import synth
+    N = synth.n_reads_total(contig_len, depths)
+    read_hi = N if read_hi is None else min(read_hi, N)
+    read_lo = max(0, read_lo)
+    n = max(0, read_hi - read_lo)
+    pat = synth.sample_pattern(depths)
+    d = np.asarray(depths, np.int32)
+    t = np.asarray(tumor, np.uint8)
+    start = np.zeros(n, np.int64)
+    cigar_off = np.zeros(n + 1, np.uint32)
+    cigar = np.zeros(3 * n + 1, np.uint32)
+    bases = np.zeros(100 * n, np.uint8)
+    qual = np.zeros(100 * n, np.uint8)
+    mapq, flags, sample = np.zeros(n, np.uint8), np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+    lib().oracle_synth_generate(C.c_int64(contig_len), C.c_int32(len(d)), ptr(d, i32p), ptr(t, u8p), ptr(pat, u8p),
+                                C.c_int32(len(pat)), C.c_uint64(seed), C.c_int64(read_lo), C.c_int64(read_hi), ptr(start, i64p),
+                                ptr(cigar_off, u32p), ptr(cigar, u32p), ptr(bases, u8p), ptr(qual, u8p), ptr(mapq, u8p),
+                                ptr(flags, u8p), ptr(sample, u8p), C.c_int(n_threads or (os.cpu_count() or 1)))
+    return ReadBatch(n_samples=len(d), contig_names=[contig_name], contig_id=np.zeros(n, np.int32), start=start,
+                     cigar_off=cigar_off, cigar=cigar[:int(cigar_off[-1])].copy(),
+                     seq_off=np.arange(n + 1, dtype=np.uint64) * np.uint64(100), bases_ascii=bases, qual=qual, mapq=mapq,
+                     flags=flags, sample_id=sample)
+
+
+def synth_reference(seed: int, lo: int, hi: int) -> np.ndarray:
+    out = np.zeros(hi - lo, np.uint8)
+    lib().oracle_synth_reference(C.c_uint64(seed), C.c_int64(lo), C.c_int64(hi), ptr(out, u8p))
+    return out
