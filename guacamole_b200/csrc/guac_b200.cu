@@ -17,6 +17,7 @@
 #include "kernels.cuh"
 #include "scan.cuh"
 #include "synth_kernels.cuh"
+#include "tile_kernels.cuh"
 
 using namespace guac;
 
@@ -59,7 +60,10 @@ struct guac_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool have_timing = false;
   int64_t timed_loci = 0;
-  DevBuf b_nops;
+  DevBuf b_nops, b_rflags, b_logtab, b_fallback;
+  int64_t opt_ss_impl = 0;            // 0 = streaming tile kernel (+ gather fallback), 1 = gather kernel only
+  int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
+  int64_t last_fallback_tiles = 0;
 };
 
 namespace {
@@ -159,7 +163,7 @@ struct Plan {
 };
 
 // Validates the ranges, builds the device range table and the tile descriptors.
-int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& plan) {
+int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& plan, int tile_loci = TILE_LOCI) {
   if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
   if (n_ranges < 0 || (n_ranges > 0 && !loci)) return fail(ctx, GUAC_E_INVALID_INPUT, "bad loci ranges");
   GUAC_TRY(sync_refs(ctx));
@@ -191,7 +195,7 @@ int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& pla
     }
     r.ref_index = it->second.ref_index;
     slot += g.end - g.start;
-    tile += (g.end - g.start + TILE_LOCI - 1) / TILE_LOCI;
+    tile += (g.end - g.start + tile_loci - 1) / tile_loci;
     rs.push_back(r);
   }
   if (slot >= (int64_t)1 << 31) return fail(ctx, GUAC_E_UNSUPPORTED, "more than 2^31-1 loci in one call: split the LociPartitioning");
@@ -200,8 +204,8 @@ int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& pla
   if (tile == 0) return GUAC_OK;
   GUAC_TRY(upload(ctx, ctx->b_ranges, rs.data(), rs.size()));
   GUAC_TRY(ensure(ctx, ctx->b_tiles, (size_t)tile * sizeof(Tile)));
-  build_tiles_kernel<<<blocks_for(tile, 256), 256, 0, ctx->stream>>>(ctx->b_ranges.as<RangeDev>(), (int)rs.size(), tile, ctx->R,
-                                                                      ctx->b_tiles.as<Tile>());
+  build_tiles_kernel<<<blocks_for(tile, 256), 256, 0, ctx->stream>>>(ctx->b_ranges.as<RangeDev>(), (int)rs.size(), tile, tile_loci,
+                                                                      ctx->R, ctx->b_tiles.as<Tile>());
   ctx->launches += 1;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `rs` is a temporary
@@ -293,6 +297,13 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   R.mapq = ctx->b_mapq.as<uint8_t>();
   R.flags = ctx->b_flags.as<uint8_t>();
   R.sample_id = ctx->b_sample.as<uint8_t>();
+  GUAC_TRY(ensure(ctx, ctx->b_rflags, (size_t)n + 16));
+  if (n > 0) {
+    read_fast_flags_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
   ctx->n_reads = n;
   ctx->n_samples = n_samples;
   ctx->have_reads = true;
@@ -328,6 +339,14 @@ int guac_ctx_create(int device, guac_ctx** out) {
   }
   cudaEventCreate(&ctx->ev0);
   cudaEventCreate(&ctx->ev1);
+  if (cudaMalloc(&ctx->b_logtab.p, sizeof(LogTables)) != cudaSuccess) {
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return GUAC_E_OOM;
+  }
+  ctx->b_logtab.cap = sizeof(LogTables);
+  init_log_tables_kernel<<<1, 256, 0, ctx->stream>>>(ctx->b_logtab.as<LogTables>());
+  ctx->launches += 1;
   *out = ctx;
   return GUAC_OK;
 }
@@ -347,6 +366,9 @@ void guac_ctx_destroy(guac_ctx* ctx) {
     if (kv.second.bases) cudaFree(kv.second.bases);
   for (void* h : ctx->host_allocs) cudaFreeHost(h);
   if (ctx->b_nops.p) cudaFree(ctx->b_nops.p);
+  if (ctx->b_rflags.p) cudaFree(ctx->b_rflags.p);
+  if (ctx->b_logtab.p) cudaFree(ctx->b_logtab.p);
+  if (ctx->b_fallback.p) cudaFree(ctx->b_fallback.p);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);
@@ -592,8 +614,14 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
                           guac_locus_summary** out_summary, int64_t* out_n_visited) {
   if (!ctx || !params || !out_calls || !n_calls || !out_arena || !arena_len) return GUAC_E_INVALID_INPUT;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  using TCfg = TileCfg<512>;
+  // The streaming tile kernel serves the pileupFlatMapTwoSamples shape (sample ids {0, 1});
+  // anything else, or opt_ss_impl = 1, takes the generic gather kernel.
+  const bool two_samples = (params->normal_sample_id == 0 && params->tumor_sample_id == 1) ||
+                           (params->normal_sample_id == 1 && params->tumor_sample_id == 0);
+  const bool use_tiles = ctx->opt_ss_impl == 0 && two_samples;
   Plan plan;
-  GUAC_TRY(make_plan(ctx, loci, n_ranges, plan));
+  GUAC_TRY(make_plan(ctx, loci, n_ranges, plan, use_tiles ? TCfg::TL : TILE_LOCI));
   *n_calls = 0;
   *arena_len = 0;
   if (out_n_visited) *out_n_visited = 0;
@@ -624,16 +652,50 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   for (int attempt = 0; attempt < 2; ++attempt) {
     GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(SSCallDev)));
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
-    cudaEventRecord(ctx->ev0, ctx->stream);
-    somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
-        ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), P, ctx->b_visited.as<uint8_t>(),
-        ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(),
-        max_calls, ctx->b_err.as<DeviceError>());
-    cudaEventRecord(ctx->ev1, ctx->stream);
+    if (use_tiles) {
+      GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 1) * sizeof(int)));
+      int* fb_count = ctx->b_fallback.as<int>();
+      int* fb_list = fb_count + 1;
+      CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
+      static bool attr_set = false;
+      if (!attr_set) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(ss_tile_kernel<TCfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)sizeof(TileSmem<TCfg>)));
+        attr_set = true;
+      }
+      cudaEventRecord(ctx->ev0, ctx->stream);
+      ss_tile_kernel<TCfg><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(
+          ctx->R, ctx->b_rflags.as<uint8_t>(), ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), P,
+          ctx->b_logtab.as<LogTables>(), ctx->b_visited.as<uint8_t>(), ctx->b_summary.as<guac_locus_summary>(),
+          ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls, fb_list, fb_count,
+          (int)ctx->opt_force_fallback_mod, ctx->b_err.as<DeviceError>());
+      cudaEventRecord(ctx->ev1, ctx->stream);
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+      int n_fb = 0;
+      CUDA_TRY(ctx, cudaMemcpyAsync(&n_fb, fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+      ctx->last_fallback_tiles = n_fb;
+      if (n_fb > 0) {  // tiles beyond a shared-memory capacity: generic kernel, still on the GPU
+        somatic_standard_kernel<<<(unsigned)n_fb, CTA_THREADS, 0, ctx->stream>>>(
+            ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, P, ctx->b_visited.as<uint8_t>(),
+            ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
+            ctx->b_err.as<DeviceError>());
+        ctx->launches += 1;
+        CUDA_TRY(ctx, cudaGetLastError());
+      }
+    } else {
+      cudaEventRecord(ctx->ev0, ctx->stream);
+      somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), nullptr, P, ctx->b_visited.as<uint8_t>(),
+          ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
+          ctx->b_err.as<DeviceError>());
+      cudaEventRecord(ctx->ev1, ctx->stream);
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+    }
     ctx->have_timing = true;
     ctx->timed_loci = plan.n_slots;
-    ctx->launches += 1;
-    CUDA_TRY(ctx, cudaGetLastError());
     CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     GUAC_TRY(check_device_error(ctx));  // synchronises
     if (nc <= max_calls) break;
@@ -716,6 +778,22 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
 }
 
 void* guac_stream(guac_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
+  if (!ctx || !name) return GUAC_E_INVALID_INPUT;
+  const std::string n(name);
+  if (n == "ss_impl") {
+    if (value != 0 && value != 1) return fail(ctx, GUAC_E_INVALID_INPUT, "ss_impl must be 0 (tile) or 1 (gather)");
+    ctx->opt_ss_impl = value;
+  } else if (n == "ss_force_fallback_mod") {
+    ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
+  } else {
+    return fail(ctx, GUAC_E_INVALID_INPUT, "unknown option " + n);
+  }
+  return GUAC_OK;
+}
+
+int64_t guac_last_fallback_tiles(guac_ctx* ctx) { return ctx ? ctx->last_fallback_tiles : 0; }
 
 int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci) {
   if (!ctx || !ms) return GUAC_E_INVALID_INPUT;

@@ -26,8 +26,8 @@ struct RangeDev {
 
 // One thread per tile: locate the tile's range, then binary-search the span of reads that can
 // overlap it — start < tile end (reads are sorted by start) and running-max end > tile start.
-__global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ranges, int64_t n_tiles, ReadsView R,
-                                   Tile* __restrict__ tiles) {
+__global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ranges, int64_t n_tiles, int tile_loci,
+                                   ReadsView R, Tile* __restrict__ tiles) {
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_tiles) return;
   int lo = 0, hi = n_ranges - 1;
@@ -38,10 +38,10 @@ __global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ra
   const RangeDev rg = ranges[lo];
   Tile tl;
   int64_t k = t - rg.tile0;
-  tl.locus0 = rg.start + k * TILE_LOCI;
-  tl.n_loci = (int32_t)min((long long)TILE_LOCI, (long long)(rg.end - tl.locus0));
+  tl.locus0 = rg.start + k * tile_loci;
+  tl.n_loci = (int32_t)min((long long)tile_loci, (long long)(rg.end - tl.locus0));
   tl.contig_id = rg.contig_id;
-  tl.slot0 = rg.slot0 + k * TILE_LOCI;
+  tl.slot0 = rg.slot0 + k * tile_loci;
   tl.ref_index = rg.ref_index;
   tl._pad = 0;
   const int64_t tile_end = tl.locus0 + tl.n_loci;
@@ -254,10 +254,11 @@ __device__ __forceinline__ void log_normalize2(double a, double b, double& na, d
 }
 
 __global__ void __launch_bounds__(CTA_THREADS)
-somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles, SSParamsDev P,
+somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles,
+                        const int* __restrict__ tile_list /* nullptr: tile = blockIdx.x */, SSParamsDev P,
                         uint8_t* __restrict__ visited, guac_locus_summary* __restrict__ summary, SSCallDev* __restrict__ calls,
                         int* __restrict__ n_calls, int max_calls, DeviceError* err) {
-  const Tile tile = tiles[blockIdx.x];
+  const Tile tile = tiles[tile_list ? tile_list[blockIdx.x] : blockIdx.x];
   const RefView ref = refs[tile.ref_index];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned FULL = 0xffffffffu;

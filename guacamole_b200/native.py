@@ -319,6 +319,15 @@ class Context:
         self.lib.guac_stream.argtypes = [C.c_void_p]
         return int(self.lib.guac_stream(self.ctx) or 0)
 
+    def set_option(self, name: str, value: int):
+        self._check(self.lib.guac_set_option(self.ctx, name.encode(), C.c_int64(value)))
+
+    @property
+    def last_fallback_tiles(self) -> int:
+        self.lib.guac_last_fallback_tiles.restype = C.c_int64
+        self.lib.guac_last_fallback_tiles.argtypes = [C.c_void_p]
+        return int(self.lib.guac_last_fallback_tiles(self.ctx))
+
     def last_kernel_ms(self) -> Tuple[float, int]:
         ms, n = C.c_float(), C.c_int64()
         self._check(self.lib.guac_last_kernel_ms(self.ctx, C.byref(ms), C.byref(n)))

@@ -249,6 +249,12 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
 
 /* CUDA stream (cudaStream_t) every kernel of this context is launched on. */
 void* guac_stream(guac_ctx* ctx);
+/* Implementation switches for tests and A/B measurements:
+ *   "ss_impl"               0 = streaming tile kernel with gather fallback (default), 1 = gather kernel only
+ *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook) */
+int guac_set_option(guac_ctx* ctx, const char* name, int64_t value);
+/* Tiles of the most recent guac_somatic_standard call that took the fallback path. */
+int64_t guac_last_fallback_tiles(guac_ctx* ctx);
 /* Device time in ms (CUDA events on the context's stream) of the dominant per-locus kernel
  * of the most recent caller invocation, and how many loci it processed. */
 int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci);

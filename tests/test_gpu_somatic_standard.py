@@ -8,6 +8,17 @@ from oracle import oracle
 
 pytestmark = pytest.mark.gpu
 
+
+@pytest.fixture(params=["tile", "gather", "tile+fallback"])
+def impl(request, gpu_ctx):
+    """Every parity case runs through the streaming tile kernel, the generic gather kernel, and the
+    tile kernel with every third tile forced through its fallback path."""
+    gpu_ctx.set_option("ss_impl", 1 if request.param == "gather" else 0)
+    gpu_ctx.set_option("ss_force_fallback_mod", 3 if request.param == "tile+fallback" else 0)
+    yield request.param
+    gpu_ctx.set_option("ss_impl", 0)
+    gpu_ctx.set_option("ss_force_fallback_mod", 0)
+
 EV_INT = ["read_depth", "allele_read_depth", "forward_depth", "allele_forward_depth"]
 EV_F = ["probability", "mean_mapping_quality", "median_mapping_quality", "mean_base_quality", "median_base_quality",
         "median_mismatches_per_read"]
@@ -36,7 +47,7 @@ def assert_ss_equal(got, want):
 
 
 @pytest.mark.parametrize("seed,contig_len", [(12, 20000), (11, 60000)])
-def test_synthetic_tumor_normal(gpu_ctx, seed, contig_len):
+def test_synthetic_tumor_normal(gpu_ctx, impl, seed, contig_len):
     ref, batch = synth.make_tumor_normal(contig_len=contig_len, seed=seed)
     ranges = [(0, 0, contig_len)]
     gpu_ctx.upload_reference(ref, batch.contig_names)
@@ -45,9 +56,13 @@ def test_synthetic_tumor_normal(gpu_ctx, seed, contig_len):
     want = oracle.somatic_standard(batch, ref, ranges, want_summary=True)
     assert len(want["calls"]) > 0
     assert_ss_equal(got, want)
+    if impl == "tile+fallback":
+        assert gpu_ctx.last_fallback_tiles > 0
+    elif impl == "tile":
+        assert gpu_ctx.last_fallback_tiles == 0
 
 
-def test_partition_invariance(gpu_ctx):
+def test_partition_invariance(gpu_ctx, impl):
     """UniformPartitioner(1) vs many partitions must give identical output
     (reference: PileupFlatMapUtilsSuite.scala:214-241)."""
     ref, batch = synth.make_tumor_normal(contig_len=30000, seed=5)
@@ -59,7 +74,7 @@ def test_partition_invariance(gpu_ctx):
     assert_ss_equal(many, one)
 
 
-def test_thresholds_and_params(gpu_ctx):
+def test_thresholds_and_params(gpu_ctx, impl):
     ref, batch = synth.make_tumor_normal(contig_len=20000, seed=13)
     gpu_ctx.upload_reference(ref, batch.contig_names)
     gpu_ctx.upload_reads(batch)
