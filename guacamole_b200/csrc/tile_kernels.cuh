@@ -53,7 +53,10 @@ __global__ void init_log_tables_kernel(LogTables* t) {
 }
 
 // per-read derived flags, computed once per upload
-enum : uint8_t { RF_FAST = 1 };  // single M/=/X operator and no non-ACGT base: bit-parallel path applies
+enum : uint8_t {
+  RF_FAST = 1,  // single M/=/X operator and no non-ACGT base: the bit-parallel path applies
+  RF_HIQ = 2    // every base quality >= 4, i.e. P(correct) >= 0.60 > 1/2 (licenses the LOD bound)
+};
 
 __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags) {
   int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -72,7 +75,9 @@ __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags
       if (m) fast = false;
     }
   }
-  rflags[r] = fast ? RF_FAST : 0;
+  bool hiq = true;
+  for (uint64_t i = R.seq_off[r]; i < R.seq_off[r + 1]; ++i) hiq = hiq && R.qual[i] >= 4;
+  rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0);
 }
 
 __device__ __forceinline__ uint32_t spread16(uint32_t x) {  // bit i -> bit 2i
@@ -139,6 +144,7 @@ struct TileSmem {
   int diff[2][CFG::TL + 1];        // -> depth after the scan
   int nonref[2][CFG::TL];          // non-Match elements per sample
   int starts[CFG::TL + 1];         // -> reads with start <= locus after the scan
+  int lowq[CFG::TL + 1];           // -> tumor reads over the locus that carry a base quality < 4
   int ev_off[CFG::TL + 1];         // events per locus -> offsets
   int cursor[CFG::TL];
   int r_start[CFG::R_MAX];         // relative to the tile's first locus
@@ -185,6 +191,7 @@ ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* _
   for (int i = tid; i < TL + 1; i += CFG::THREADS) {
     S.diff[0][i] = S.diff[1][i] = 0;
     S.starts[i] = 0;
+    S.lowq[i] = 0;
     S.ev_off[i] = 0;
   }
   for (int i = tid; i < TL; i += CFG::THREADS) {
@@ -229,6 +236,10 @@ ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* _
     atomicMax(&S.max_span, en - st);
     atomicAdd(&S.diff[slot][a], 1);
     atomicAdd(&S.diff[slot][b], -1);
+    if (slot == 1 && !(rf & RF_HIQ)) {
+      atomicAdd(&S.lowq[a], 1);
+      atomicAdd(&S.lowq[b], -1);
+    }
     if (!(rf & RF_FAST)) {
       const int i = atomicAdd(&S.n_slow, 1);
       if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)rl; else S.overflow = 1;
@@ -292,6 +303,7 @@ ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* _
   block_scan_inplace<CFG::THREADS>(S.diff[0], n_loci, S.warp_tot);
   block_scan_inplace<CFG::THREADS>(S.diff[1], n_loci, S.warp_tot);
   block_scan_inplace<CFG::THREADS>(S.starts, n_loci, S.warp_tot);
+  block_scan_inplace<CFG::THREADS>(S.lowq, n_loci, S.warp_tot);
   block_scan_inplace<CFG::THREADS>(S.ev_off, n_loci + 1, S.warp_tot);
   // bucket the events by locus
   const int n_events = S.n_events;
@@ -414,6 +426,62 @@ ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* _
       continue;
     }
     const double f = fmax(P.min_vaf, (double)bcnt / (double)dT);  // :189
+
+    // Exact pruning.  tumorAltLOD = sum over tumor elements of log(P(e|mix)) - log(P(e|ref)):
+    //   element of the reference allele:  log(1 - f + f (1-p)/p)  <= 0 whenever p >= 1/2,
+    //   element of the called allele:     log(1 - f + f p/(1-p)),
+    //   any other element:                log(1) = 0.
+    // When every tumor read over the locus has all base qualities >= 4 (p >= 0.60; tracked by
+    // lowq[]), the sum over the called allele's elements — known from the events — bounds the
+    // LOD from above, and a locus whose bound is below the threshold (minus a 0.5 margin that
+    // dwarfs any rounding) cannot be called (:231), so its qualities are never gathered.
+    double bsum = 0;
+    int normalAltEv = 0;
+    for (int base = e0; base < e1; base += 32) {
+      const int i = base + lane;
+      const bool has = i < e1;
+      const uint32_t ev = has ? S.ev_sorted[i] : 0;
+      const int rl = (ev >> 11) & 0xFFF, eslot = (ev >> 23) & 1, kind = (ev >> 24) & 7, code = (ev >> 27) & 7;
+      const bool var = has && kind != GUAC_ALN_CLIPPED;
+      uint64_t key = 0;
+      int q = 0;
+      if (var) {
+        if (S.r_flags[rl] & 2) {  // fast read: a mismatch with an ACGT base
+          key = (1ull << 60) | (uint8_t)("ACGT"[code]);
+          if (eslot == 1 && key == bkey) q = __ldg(R.qual + seq_base + S.r_s0[rl] + (uint64_t)(l - S.r_start[rl]));
+        } else {
+          Elem e;
+          const int64_t r = tile.read_lo + rl;
+          if (element_at(R, r, x, ref, e) == DERR_NONE) {
+            key = allele_key(R, r, e);
+            q = e.quality;
+          }
+        }
+      }
+      const bool is_alt = var && key == bkey;
+      normalAltEv += __popc(__ballot_sync(FULL, is_alt && eslot == 0));
+      if (is_alt && eslot == 1) {
+        const double p = c_success_probability[q];
+        bsum += log(1.0 - f + f * (p / (1.0 - p)));
+      }
+    }
+    bsum = warp_sum(bsum);
+    if (S.lowq[l] == 0 && bsum < (double)P.tumor_odds - 0.5) {
+      if (lane == 0) {
+        guac_locus_summary sn, st;
+        sn.depth = (uint16_t)min(dN, 65535);
+        sn.reference_depth = (uint16_t)min(dN - nrN, 65535);
+        sn.top_alt_count = (uint16_t)min(normalAltEv, 65535);
+        sn.flags = 1;
+        st.depth = (uint16_t)min(dT, 65535);
+        st.reference_depth = (uint16_t)min(dT - nrT, 65535);
+        st.top_alt_count = (uint16_t)min(bcnt, 65535);
+        st.flags = 1;
+        summary[slot * 2 + 0] = sn;
+        summary[slot * 2 + 1] = st;
+      }
+      continue;
+    }
     const bool best_snv = (bkey >> 60) == 1;
     const int best_code = best_snv ? base_code((uint8_t)(bkey & 0xFF)) : 5;
     const int ref_code = (S.ref2[l >> 4] >> (2 * (l & 15))) & 3;
