@@ -63,7 +63,9 @@ struct guac_ctx {
   DevBuf b_nops, b_rflags, b_logtab, b_fallback;
   int64_t opt_ss_impl = 0;            // 0 = streaming tile kernel (+ gather fallback), 1 = gather kernel only
   int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
-  int64_t last_fallback_tiles = 0;
+  int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
+  DevBuf b_heavy, b_boundtab;
+  double bound_tab_vaf = -1;
 };
 
 namespace {
@@ -339,14 +341,6 @@ int guac_ctx_create(int device, guac_ctx** out) {
   }
   cudaEventCreate(&ctx->ev0);
   cudaEventCreate(&ctx->ev1);
-  if (cudaMalloc(&ctx->b_logtab.p, sizeof(LogTables)) != cudaSuccess) {
-    cudaStreamDestroy(ctx->stream);
-    delete ctx;
-    return GUAC_E_OOM;
-  }
-  ctx->b_logtab.cap = sizeof(LogTables);
-  init_log_tables_kernel<<<1, 256, 0, ctx->stream>>>(ctx->b_logtab.as<LogTables>());
-  ctx->launches += 1;
   *out = ctx;
   return GUAC_OK;
 }
@@ -369,6 +363,8 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_rflags.p) cudaFree(ctx->b_rflags.p);
   if (ctx->b_logtab.p) cudaFree(ctx->b_logtab.p);
   if (ctx->b_fallback.p) cudaFree(ctx->b_fallback.p);
+  if (ctx->b_heavy.p) cudaFree(ctx->b_heavy.p);
+  if (ctx->b_boundtab.p) cudaFree(ctx->b_boundtab.p);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);
@@ -653,7 +649,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(SSCallDev)));
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
     if (use_tiles) {
-      GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 1) * sizeof(int)));
+      GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 2) * sizeof(int)));
       int* fb_count = ctx->b_fallback.as<int>();
       int* fb_list = fb_count + 1;
       CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
@@ -663,33 +659,77 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
                                            (int)sizeof(TileSmem<TCfg>)));
         attr_set = true;
       }
+      // LOD-bound table for f = the VAF floor (see `prune` in tile_kernels.cuh)
+      if (ctx->bound_tab_vaf != P.min_vaf || !ctx->b_boundtab.p) {
+        double tab[256];
+        for (int q = 0; q < 256; ++q) {
+          const double p = 1.0 - std::pow(10.0, -q / 10.0);
+          tab[q] = std::log(1.0 - P.min_vaf + P.min_vaf * (p / (1.0 - p)));
+        }
+        GUAC_TRY(upload(ctx, ctx->b_boundtab, tab, 256));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->bound_tab_vaf = P.min_vaf;
+      }
+      const int max_heavy = (int)std::min<int64_t>(plan.n_slots, plan.n_slots / 16 + 65536);
+      GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
+      int* heavy_count = fb_count + 1 + plan.n_tiles;
+      CUDA_TRY(ctx, cudaMemsetAsync(heavy_count, 0, sizeof(int), ctx->stream));
+      TileArgs TA;
+      TA.rflags = ctx->b_rflags.as<uint8_t>();
+      TA.refs = ctx->d_refs.as<RefView>();
+      TA.tiles = ctx->b_tiles.as<Tile>();
+      TA.bound_tab = ctx->b_boundtab.as<double>();
+      TA.visited = ctx->b_visited.as<uint8_t>();
+      TA.summary = ctx->b_summary.as<guac_locus_summary>();
+      TA.heavy = ctx->b_heavy.as<Tile>();
+      TA.n_heavy = heavy_count;
+      TA.max_heavy = max_heavy;
+      TA.fallback_tiles = fb_list;
+      TA.n_fallback = fb_count;
+      TA.force_fallback_mod = (int)ctx->opt_force_fallback_mod;
+      TA.err = ctx->b_err.as<DeviceError>();
       cudaEventRecord(ctx->ev0, ctx->stream);
-      ss_tile_kernel<TCfg><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(
-          ctx->R, ctx->b_rflags.as<uint8_t>(), ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), P,
-          ctx->b_logtab.as<LogTables>(), ctx->b_visited.as<uint8_t>(), ctx->b_summary.as<guac_locus_summary>(),
-          ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls, fb_list, fb_count,
-          (int)ctx->opt_force_fallback_mod, ctx->b_err.as<DeviceError>());
-      cudaEventRecord(ctx->ev1, ctx->stream);
+      ss_tile_kernel<TCfg><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
-      int n_fb = 0;
-      CUDA_TRY(ctx, cudaMemcpyAsync(&n_fb, fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      int counts[2] = {0, 0};
+      CUDA_TRY(ctx, cudaMemcpyAsync(&counts[0], fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&counts[1], heavy_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
       CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+      const int n_fb = counts[0], n_heavy = counts[1];
       ctx->last_fallback_tiles = n_fb;
-      if (n_fb > 0) {  // tiles beyond a shared-memory capacity: generic kernel, still on the GPU
-        somatic_standard_kernel<<<(unsigned)n_fb, CTA_THREADS, 0, ctx->stream>>>(
-            ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, P, ctx->b_visited.as<uint8_t>(),
+      ctx->last_heavy_loci = n_heavy;
+      if (n_heavy > max_heavy) {
+        // more heavy loci than the list holds (pathological input): redo the call with the generic kernel
+        ctx->opt_ss_impl = 1;
+        int st = guac_somatic_standard(ctx, params, loci, n_ranges, out_calls, n_calls, out_arena, arena_len, out_summary,
+                                       out_n_visited);
+        ctx->opt_ss_impl = 0;
+        return st;
+      }
+      if (n_heavy > 0) {  // loci that need the full likelihood: one warp each
+        somatic_standard_kernel<<<blocks_for(n_heavy, WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
+            ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, n_heavy, 1, P, ctx->b_visited.as<uint8_t>(),
             ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
             ctx->b_err.as<DeviceError>());
         ctx->launches += 1;
         CUDA_TRY(ctx, cudaGetLastError());
       }
+      if (n_fb > 0) {  // tiles beyond a shared-memory capacity: generic kernel, still on the GPU
+        somatic_standard_kernel<<<(unsigned)n_fb, CTA_THREADS, 0, ctx->stream>>>(
+            ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, n_fb, 0, P, ctx->b_visited.as<uint8_t>(),
+            ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
+            ctx->b_err.as<DeviceError>());
+        ctx->launches += 1;
+        CUDA_TRY(ctx, cudaGetLastError());
+      }
+      cudaEventRecord(ctx->ev1, ctx->stream);
     } else {
       cudaEventRecord(ctx->ev0, ctx->stream);
       somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
-          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), nullptr, P, ctx->b_visited.as<uint8_t>(),
-          ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
-          ctx->b_err.as<DeviceError>());
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), nullptr, (int)plan.n_tiles, 0, P,
+          ctx->b_visited.as<uint8_t>(), ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(),
+          ctx->b_ncalls.as<int>(), max_calls, ctx->b_err.as<DeviceError>());
       cudaEventRecord(ctx->ev1, ctx->stream);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
@@ -794,6 +834,7 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
 }
 
 int64_t guac_last_fallback_tiles(guac_ctx* ctx) { return ctx ? ctx->last_fallback_tiles : 0; }
+int64_t guac_last_heavy_loci(guac_ctx* ctx) { return ctx ? ctx->last_heavy_loci : 0; }
 
 int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci) {
   if (!ctx || !ms) return GUAC_E_INVALID_INPUT;

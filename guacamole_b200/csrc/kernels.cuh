@@ -255,14 +255,17 @@ __device__ __forceinline__ void log_normalize2(double a, double b, double& na, d
 
 __global__ void __launch_bounds__(CTA_THREADS)
 somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles,
-                        const int* __restrict__ tile_list /* nullptr: tile = blockIdx.x */, SSParamsDev P,
-                        uint8_t* __restrict__ visited, guac_locus_summary* __restrict__ summary, SSCallDev* __restrict__ calls,
-                        int* __restrict__ n_calls, int max_calls, DeviceError* err) {
-  const Tile tile = tiles[tile_list ? tile_list[blockIdx.x] : blockIdx.x];
-  const RefView ref = refs[tile.ref_index];
+                        const int* __restrict__ tile_list /* nullptr: identity */, int n_tiles,
+                        int tile_per_warp /* 0: the CTA's warps share tile blockIdx.x; 1: one (single-locus) tile per warp */,
+                        SSParamsDev P, uint8_t* __restrict__ visited, guac_locus_summary* __restrict__ summary,
+                        SSCallDev* __restrict__ calls, int* __restrict__ n_calls, int max_calls, DeviceError* err) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tsel = tile_per_warp ? (int)blockIdx.x * WARPS_PER_CTA + warp : (int)blockIdx.x;
+  if (tsel >= n_tiles) return;  // no block-wide barrier below
+  const Tile tile = tiles[tile_list ? tile_list[tsel] : tsel];
+  const RefView ref = refs[tile.ref_index];
   const unsigned FULL = 0xffffffffu;
-  for (int li = warp; li < tile.n_loci; li += WARPS_PER_CTA) {
+  for (int li = tile_per_warp ? 0 : warp; li < tile.n_loci; li += tile_per_warp ? 1 : WARPS_PER_CTA) {
     const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
     int depthN = 0, depthT = 0, refN = 0, refT = 0;
     bool any = false;

@@ -1,23 +1,25 @@
 // tile_kernels.cuh — streaming tile kernel for somatic-standard (the benchmarked path).
 //
-// One CTA owns a tile of TL consecutive loci and everything about it stays in shared memory:
-//   A. read-parallel pass: every read that can overlap the tile is visited ONCE; its coverage
-//      goes into per-sample difference arrays (+1 at start, -1 at end), and its bases are
-//      compared with the reference 32 bits (16 bases) at a time in 2-bit space — only
-//      non-matching elements (mismatches, indel anchors, mid-deletions, N-skips) become events.
-//      Reads with a multi-operator CIGAR or non-ACGT bases (~3 %) take the exact per-locus
-//      cursor (element_at), one warp per read, one lane per locus.
-//   B. block prefix scans turn the difference arrays into Pileup.depth per sample, give
-//      referenceDepth = depth - non-match events, bucket the events by locus, and index the
-//      reads by start so that a locus finds its overlapping reads without a search.
-//   C. loci that survive findPotentialVariantAtLocus's early-outs (SomaticStandardCaller.scala:
-//      164-172; ~20 % of loci at 1 % error, depth 60/30) are evaluated one warp per locus: the
-//      most frequent tumor variant allele comes from the locus's events, the likelihood sums
-//      from a gather of the overlapping reads' qualities.  Log terms that do not depend on the
-//      locus's allele fraction come from tables; the f-dependent tumor mixture terms are
-//      histogrammed by (class, quality) so that one warp-wide FP64 log pass serves the locus.
-// Tiles that exceed a shared-memory capacity are appended to a fallback list and re-run by
-// the generic gather kernel (kernels.cuh) — still on the GPU.
+// One CTA owns a tile of TL consecutive loci; everything about the tile lives in shared memory.
+//   A. read-parallel pass, one thread per read: every read that can overlap the tile is visited
+//      ONCE.  Its coverage goes into per-sample difference arrays (+1 at start, -1 at end); its
+//      aligned segments are compared with the reference 16 bases (32 bits) at a time in 2-bit
+//      space, so only NON-matching elements (mismatches, insertion / deletion anchors,
+//      mid-deletion loci) cost anything: each becomes an event (locus, read, kind, base, quality).
+//      The CIGAR is walked per operator, never per base.  Reads that need the exact per-locus
+//      cursor (N skips, padding, non-ACGT bases, a leading insertion at locus 0) are rare and are
+//      handled one warp per read by element_at().
+//   B. block prefix scans turn the difference arrays into Pileup.depth per sample,
+//      referenceDepth = depth - events, and bucket the events by locus.
+//   C. one thread per locus applies findPotentialVariantAtLocus's early-outs
+//      (SomaticStandardCaller.scala:164-172).  For a surviving locus the most frequent tumor
+//      variant allele and an exact upper bound of the tumor log-odds come from the events alone
+//      (see `prune` below); only loci whose bound reaches the threshold — or whose alleles are
+//      not plain SNVs — are appended to a list of "heavy" loci, which the generic gather kernel
+//      (kernels.cuh) evaluates in full afterwards.  Qualities of matching bases are therefore
+//      read only where a call is possible.
+// Tiles that exceed a shared-memory capacity go to a fallback list and are re-run whole by the
+// generic kernel — still on the GPU.
 #pragma once
 #include "kernels.cuh"
 
@@ -25,59 +27,51 @@ namespace guac {
 
 template <int TL_>
 struct TileCfg {
-  static constexpr int TL = TL_;           // loci per tile
+  static constexpr int TL = TL_;  // loci per tile
   static constexpr int THREADS = 256;
   static constexpr int WARPS = THREADS / 32;
-  static constexpr int R_MAX = TL * 2 + 256;  // reads staged per tile
-  static constexpr int E_MAX = TL * 4;        // non-match events per tile
-  static constexpr int SLOW_MAX = 512;
-  static constexpr int QB = 64;               // quality bins of the tumor histogram
+  static constexpr int R_MAX = 4095;     // reads per tile (12-bit read index in an event)
+  static constexpr int E_MAX = TL * 4;   // non-match events per tile
+  static constexpr int SLOW_MAX = 256;
+  static constexpr int EV_SIMPLE = 24;   // a locus with more events goes to the heavy path
 };
-
-// log tables indexed [cls][q], cls 0 = element allele is the reference allele, 1 = is the called
-// allele, 2 = anything else; filled by init_log_tables_kernel with the device's own log().
-struct LogTables {
-  double ref[3][256];  // log(P(e | ref genotype))           (Likelihood.scala:199-204, f = 1)
-  double het[3][256];  // log(0.5 P(e|ref) + 0.5 P(e|alt))   (germlineVariantGenotype, SomaticStandardCaller.scala:212-218)
-};
-
-__global__ void init_log_tables_kernel(LogTables* t) {
-  const int q = threadIdx.x;
-  const double p = c_success_probability[q];
-  for (int cls = 0; cls < 3; ++cls) {
-    const double pr = cls == 0 ? p : 1 - p;
-    const double pa = cls == 1 ? p : 1 - p;
-    t->ref[cls][q] = log(pr * 1.0);
-    t->het[cls][q] = log(pr * 0.5 + pa * 0.5);
-  }
-}
 
 // per-read derived flags, computed once per upload
 enum : uint8_t {
-  RF_FAST = 1,  // single M/=/X operator and no non-ACGT base: the bit-parallel path applies
-  RF_HIQ = 2    // every base quality >= 4, i.e. P(correct) >= 0.60 > 1/2 (licenses the LOD bound)
+  RF_FAST = 1,    // single M/=/X operator, ACGT only
+  RF_HIQ = 2,     // every base quality >= 4, i.e. P(correct) >= 0.60 > 1/2 (licenses the LOD bound)
+  RF_MEDIUM = 4   // operators within {M,=,X,I,D,S,H}, ACGT only, CIGAR consistent with the sequence
 };
 
 __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags) {
   int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R.n_reads) return;
   const uint32_t c0 = R.cigar_off[r], c1 = R.cigar_off[r + 1];
-  bool fast = false;
-  if (c1 - c0 == 1) {
-    const uint32_t w = R.cigar[c0];
-    const int op = w & 15;
-    const uint64_t s0 = R.seq_off[r], s1 = R.seq_off[r + 1];
-    fast = (op == OPC_M || op == OPC_EQ || op == OPC_X) && (uint64_t)(w >> 4) == s1 - s0 && s1 > s0;
-    for (uint64_t i = s0 >> 3; fast && i <= ((s1 - 1) >> 3); ++i) {
-      uint8_t m = R.nmask[i];
-      if (i == (s0 >> 3)) m &= (uint8_t)(0xFFu << (s0 & 7));
-      if (i == ((s1 - 1) >> 3)) m &= (uint8_t)(0xFFu >> (7 - ((s1 - 1) & 7)));
-      if (m) fast = false;
-    }
+  const uint64_t s0 = R.seq_off[r], s1 = R.seq_off[r + 1];
+  bool acgt = s1 > s0;
+  for (uint64_t i = s0 >> 3; acgt && i <= ((s1 - 1) >> 3); ++i) {
+    uint8_t m = R.nmask[i];
+    if (i == (s0 >> 3)) m &= (uint8_t)(0xFFu << (s0 & 7));
+    if (i == ((s1 - 1) >> 3)) m &= (uint8_t)(0xFFu >> (7 - ((s1 - 1) & 7)));
+    if (m) acgt = false;
   }
+  bool ops_ok = c1 > c0;
+  uint64_t read_len = 0;
+  bool seen_ref_op = false, leading_ins_at_zero = false;
+  for (uint32_t c = c0; c < c1; ++c) {
+    const uint32_t w = R.cigar[c];
+    const int op = w & 15;
+    if (!(op == OPC_M || op == OPC_EQ || op == OPC_X || op == OPC_I || op == OPC_D || op == OPC_S || op == OPC_H)) ops_ok = false;
+    if ((w >> 4) == 0) ops_ok = false;  // zero-length operators: leave to the exact cursor
+    if (consumes_read(op)) read_len += w >> 4;
+    if (op == OPC_I && !seen_ref_op && R.start[r] == 0) leading_ins_at_zero = true;  // PE.scala:88-89
+    if (consumes_ref(op)) seen_ref_op = true;
+  }
+  const bool medium = acgt && ops_ok && !leading_ins_at_zero && read_len == s1 - s0 && seen_ref_op;
+  const bool fast = medium && (c1 - c0 == 1);
   bool hiq = true;
-  for (uint64_t i = R.seq_off[r]; i < R.seq_off[r + 1]; ++i) hiq = hiq && R.qual[i] >= 4;
-  rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0);
+  for (uint64_t i = s0; i < s1; ++i) hiq = hiq && R.qual[i] >= 4;
+  rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0) | (medium ? RF_MEDIUM : 0);
 }
 
 __device__ __forceinline__ uint32_t spread16(uint32_t x) {  // bit i -> bit 2i
@@ -89,10 +83,9 @@ __device__ __forceinline__ uint32_t spread16(uint32_t x) {  // bit i -> bit 2i
   return x;
 }
 
-// 32 bits starting at bit `bit` of a little-endian word stream in global memory
+// 32 bits starting at bit `bit` of a little-endian word stream
 __device__ __forceinline__ uint32_t load_bits32_g(const uint8_t* __restrict__ bytes, uint64_t bit) {
-  const uint64_t byte = bit >> 3;
-  const uint32_t* w = reinterpret_cast<const uint32_t*>(bytes) + (byte >> 2);
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(bytes) + (bit >> 5);
   const int sh = (int)(bit & 31);
   const uint32_t lo = __ldg(w);
   if (sh == 0) return lo;
@@ -130,67 +123,69 @@ __device__ __forceinline__ void block_scan_inplace(int* a, int n, int* warp_tot 
   __syncthreads();
 }
 
-// event word: [0,11) locus in tile | [11,23) read in tile | 23 sample slot | [24,27) kind | [27,30) base code (4 = non-ACGT)
+// event word: [0,11) locus in tile | [11,23) read in tile | 23 sample slot | [24,27) kind | [27,30) base code (4 = not ACGT)
 __device__ __forceinline__ uint32_t pack_event(int l, int rl, int slot, int kind, int code) {
   return (uint32_t)l | ((uint32_t)rl << 11) | ((uint32_t)slot << 23) | ((uint32_t)kind << 24) | ((uint32_t)code << 27);
 }
-
 __device__ __forceinline__ int base_code(uint8_t b) { return b == 'A' ? 0 : b == 'C' ? 1 : b == 'G' ? 2 : b == 'T' ? 3 : 4; }
 
 template <class CFG>
 struct TileSmem {
   uint32_t ref2[CFG::TL / 16 + 2];
   uint32_t refmask[CFG::TL / 32 + 2];
-  int diff[2][CFG::TL + 1];        // -> depth after the scan
-  int nonref[2][CFG::TL];          // non-Match elements per sample
-  int starts[CFG::TL + 1];         // -> reads with start <= locus after the scan
-  int lowq[CFG::TL + 1];           // -> tumor reads over the locus that carry a base quality < 4
-  int ev_off[CFG::TL + 1];         // events per locus -> offsets
+  int diff[2][CFG::TL + 1];   // -> depth after the scan
+  int nonref[2][CFG::TL];     // non-Match elements per sample
+  int lowq[CFG::TL + 1];      // -> tumor reads over the locus that carry a base quality < 4
+  int ev_off[CFG::TL + 1];    // events per locus -> offsets
   int cursor[CFG::TL];
-  int r_start[CFG::R_MAX];         // relative to the tile's first locus
-  int r_end[CFG::R_MAX];
-  uint32_t r_s0[CFG::R_MAX];       // seq_off relative to the tile's first read
-  uint8_t r_flags[CFG::R_MAX];     // bit0 sample slot (0 normal, 1 tumor), bit1 fast, bit2 relevant sample
   uint32_t ev[CFG::E_MAX];
   uint32_t ev_sorted[CFG::E_MAX];
+  uint16_t evq[CFG::E_MAX];       // low byte: qualityScore of the element; high byte: allele detail
+  uint16_t evq_sorted[CFG::E_MAX];  // (Deletion: deleted length, Insertion: 8-bit hash of the inserted bases)
   uint16_t slow[CFG::SLOW_MAX];
-  uint16_t cand[CFG::TL];
-  unsigned hist[CFG::WARPS][3 * CFG::QB];
-  unsigned clist[CFG::WARPS][3 * CFG::QB];  // compacted non-empty bins: bin << 24 | count
   int warp_tot[CFG::WARPS];
-  int n_events, n_slow, n_cand, max_span, overflow;
+  int n_events, n_slow, overflow;
+};
+
+struct TileArgs {
+  const uint8_t* rflags;
+  const RefView* refs;
+  const Tile* tiles;
+  const double* bound_tab;  // [256] log(1 - f0 + f0 p/(1-p)) for f0 = min VAF: LOD term of one called-allele element
+  uint8_t* visited;
+  guac_locus_summary* summary;
+  Tile* heavy;              // heavy loci as single-locus tiles
+  int* n_heavy;
+  int max_heavy;
+  int* fallback_tiles;
+  int* n_fallback;
+  int force_fallback_mod;
+  DeviceError* err;
 };
 
 template <class CFG>
-__global__ void __launch_bounds__(CFG::THREADS)
-ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* __restrict__ refs, const Tile* __restrict__ tiles,
-               SSParamsDev P, const LogTables* __restrict__ LT, uint8_t* __restrict__ visited,
-               guac_locus_summary* __restrict__ summary, SSCallDev* __restrict__ calls, int* __restrict__ n_calls, int max_calls,
-               int* __restrict__ fallback_tiles, int* __restrict__ n_fallback, int force_fallback_mod, DeviceError* err) {
+__global__ void __launch_bounds__(CFG::THREADS, 4)
+ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TileSmem<CFG>& S = *reinterpret_cast<TileSmem<CFG>*>(smem_raw);
   constexpr int TL = CFG::TL;
-  const unsigned FULL = 0xffffffffu;
-  const Tile tile = tiles[blockIdx.x];
-  const RefView ref = refs[tile.ref_index];
+  const Tile tile = A.tiles[blockIdx.x];
+  const RefView ref = A.refs[tile.ref_index];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n_loci = tile.n_loci;
   const int64_t t0 = tile.locus0;
   const int64_t n_reads_tile = tile.read_hi - tile.read_lo;
-  const uint64_t seq_base = n_reads_tile > 0 ? __ldg(R.seq_off + tile.read_lo) : 0;
 
   bool too_big = n_reads_tile > CFG::R_MAX;
-  if (!too_big && n_reads_tile > 0) too_big = (__ldg(R.seq_off + tile.read_hi) - seq_base) >= (1ull << 31);
-  if (force_fallback_mod > 0 && blockIdx.x % force_fallback_mod == 0) too_big = true;  // test hook
+  if (A.force_fallback_mod > 0 && blockIdx.x % A.force_fallback_mod == 0) too_big = true;  // test hook
   if (too_big) {  // uniform across the CTA
-    if (tid == 0) fallback_tiles[atomicAdd(n_fallback, 1)] = blockIdx.x;
+    if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
     return;
   }
 
   // ---- init ------------------------------------------------------------------------------
   for (int i = tid; i < TL + 1; i += CFG::THREADS) {
     S.diff[0][i] = S.diff[1][i] = 0;
-    S.starts[i] = 0;
     S.lowq[i] = 0;
     S.ev_off[i] = 0;
   }
@@ -198,9 +193,8 @@ ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* _
     S.nonref[0][i] = S.nonref[1][i] = 0;
     S.cursor[i] = 0;
   }
-  for (int i = tid; i < CFG::WARPS * 3 * CFG::QB; i += CFG::THREADS) (&S.hist[0][0])[i] = 0;
-  if (tid == 0) S.n_events = S.n_slow = S.n_cand = S.max_span = S.overflow = 0;
-  // reference tile -> 2-bit words (16 loci per word) and a non-ACGT mask (32 loci per word)
+  if (tid == 0) S.n_events = S.n_slow = S.overflow = 0;
+  // reference tile -> 2-bit words (16 loci per word) and a not-ACGT mask (16 bits per half word)
   for (int w = tid; w < TL / 16 + 2; w += CFG::THREADS) {
     uint32_t bits = 0, mask = 0;
 #pragma unroll 4
@@ -211,89 +205,145 @@ ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* _
       if (c < 4) bits |= (uint32_t)c << (2 * k); else mask |= 1u << k;
     }
     S.ref2[w] = bits;
-    // two consecutive 16-bit halves share a mask word
     reinterpret_cast<uint16_t*>(S.refmask)[w] = (uint16_t)mask;
   }
   __syncthreads();
 
+  // code: Mismatch -> base code (4 = not ACGT); other kinds -> 4 = allele identified by `detail`, 5 = needs the exact path
+  auto add_event = [&](int l, int rl, int slot, int kind, int code, int q, int detail = 0) {
+    atomicAdd(&S.nonref[slot][l], 1);
+    const int e = atomicAdd(&S.n_events, 1);
+    if (e < CFG::E_MAX) {
+      S.ev[e] = pack_event(l, rl, slot, kind, code);
+      S.evq[e] = (uint16_t)((q & 0xFF) | ((detail & 0xFF) << 8));
+    } else {
+      S.overflow = 1;
+    }
+  };
+
   // ---- A. read-parallel pass ---------------------------------------------------------------
   for (int rl = tid; rl < (int)n_reads_tile; rl += CFG::THREADS) {
     const int64_t r = tile.read_lo + rl;
-    const int64_t st64 = __ldg(R.start + r), en64 = __ldg(R.end + r);
     const int smp = (int)__ldg(R.sample_id + r);
-    const bool relevant = smp == P.normal_sample || smp == P.tumor_sample;
+    if (smp != P.normal_sample && smp != P.tumor_sample) continue;
     const int slot = smp == P.tumor_sample ? 1 : 0;
-    const uint8_t rf = __ldg(rflags + r);
+    const int64_t st64 = __ldg(R.start + r), en64 = __ldg(R.end + r);
     const int st = (int)max((long long)(st64 - t0), -(1ll << 30)), en = (int)min((long long)(en64 - t0), (1ll << 30));
-    S.r_start[rl] = st;
-    S.r_end[rl] = en;
-    S.r_s0[rl] = (uint32_t)(__ldg(R.seq_off + r) - seq_base);
-    S.r_flags[rl] = (uint8_t)(slot | ((rf & RF_FAST) ? 2 : 0) | (relevant ? 4 : 0));
-    atomicAdd(&S.starts[max(st, 0)], 1);  // st < n_loci by construction of read_hi
-    if (!relevant) continue;
     const int a = max(st, 0), b = min(en, n_loci);  // overlap [a, b) in tile coordinates
     if (a >= b) continue;
-    atomicMax(&S.max_span, en - st);
+    const uint8_t rf = __ldg(A.rflags + r);
     atomicAdd(&S.diff[slot][a], 1);
     atomicAdd(&S.diff[slot][b], -1);
     if (slot == 1 && !(rf & RF_HIQ)) {
       atomicAdd(&S.lowq[a], 1);
       atomicAdd(&S.lowq[b], -1);
     }
-    if (!(rf & RF_FAST)) {
+    if (!(rf & RF_MEDIUM)) {
       const int i = atomicAdd(&S.n_slow, 1);
       if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)rl; else S.overflow = 1;
       continue;
     }
-    // fast read: single M/=/X operator, ACGT only.  Compare 16 bases at a time.
-    const uint64_t s0 = seq_base + S.r_s0[rl];
-    for (int l = a; l < b; l += 16) {
-      const int k = l - st;  // read position of locus l
-      const uint32_t rd = load_bits32_g(R.bases2, 2 * (s0 + (uint64_t)k));
-      const uint32_t rfw = load_bits32_s(S.ref2, 2 * l);
-      uint32_t x = rd ^ rfw;
-      uint32_t m = (x | (x >> 1)) & 0x55555555u;
-      const uint32_t rmask = (load_bits32_s(S.refmask, l)) & 0xFFFFu;
-      m |= spread16(rmask);  // a non-ACGT reference base never equals an ACGT read base
-      const int nb = b - l;
-      if (nb < 16) m &= (1u << (2 * nb)) - 1;
-      while (m) {
-        const int bit = __ffs(m) - 1;
-        m &= m - 1;
-        const int i16 = bit >> 1;
-        const int code = (rd >> bit) & 3;
-        const int ll = l + i16;
-        atomicAdd(&S.nonref[slot][ll], 1);
-        const int e = atomicAdd(&S.n_events, 1);
-        if (e < CFG::E_MAX) S.ev[e] = pack_event(ll, rl, slot, GUAC_ALN_MISMATCH, code); else S.overflow = 1;
+    const uint64_t s0 = __ldg(R.seq_off + r);
+    // aligned segment: loci [lb, le) (tile coordinates, unclipped) hold read positions rp0..; 16 bases per step
+    auto compare_segment = [&](int lb, int le, int rp0) {
+      const int ca = max(lb, 0), cb = min(le, n_loci);
+      for (int l = ca; l < cb; l += 16) {
+        const int k = rp0 + (l - lb);
+        const uint32_t rd = load_bits32_g(R.bases2, 2 * (s0 + (uint64_t)k));
+        const uint32_t rfw = load_bits32_s(S.ref2, 2 * l);
+        const uint32_t x = rd ^ rfw;
+        uint32_t m = (x | (x >> 1)) & 0x55555555u;
+        m |= spread16(load_bits32_s(S.refmask, l) & 0xFFFFu);  // a not-ACGT reference base never equals an ACGT read base
+        const int nb = cb - l;
+        if (nb < 16) m &= (1u << (2 * nb)) - 1;
+        while (m) {
+          const int bit = __ffs(m) - 1;
+          m &= m - 1;
+          const int i16 = bit >> 1;
+          add_event(l + i16, rl, slot, GUAC_ALN_MISMATCH, (rd >> bit) & 3, __ldg(R.qual + s0 + k + i16));
+        }
+      }
+    };
+    if (rf & RF_FAST) {
+      compare_segment(st, en, 0);
+      continue;
+    }
+    // operator walk (PE.scala:59-117 per operator instead of per base)
+    const uint32_t c0 = __ldg(R.cigar_off + r), c1 = __ldg(R.cigar_off + r + 1);
+    const int read_len = (int)(__ldg(R.seq_off + r + 1) - s0);
+    int cl = st, rp = 0;
+    for (uint32_t ci = c0; ci < c1; ++ci) {
+      const uint32_t w = __ldg(R.cigar + ci);
+      const int op = w & 15, len = (int)(w >> 4);
+      if (op == OPC_M || op == OPC_EQ || op == OPC_X) {
+        int nop = -1, nlen = 0;
+        if (ci + 1 < c1) {
+          const uint32_t nw = __ldg(R.cigar + ci + 1);
+          nop = nw & 15;
+          nlen = (int)(nw >> 4);
+        }
+        // the final base of the operator anchors a following insertion (M/= only) or deletion
+        const bool special_last = nop == OPC_D || (nop == OPC_I && op != OPC_X);
+        compare_segment(cl, cl + len - (special_last ? 1 : 0), rp);
+        if (special_last) {
+          const int ll = cl + len - 1, k = rp + len - 1;
+          if (ll >= 0 && ll < n_loci) {
+            if (ref.at(t0 + ll) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + ll, r);
+            if (nop == OPC_I) {  // qualityScore = min over anchor + inserted qualities (PE.scala:153)
+              const int until = min(k + nlen + 1, read_len);
+              int q = 255;
+              uint32_t h = 2166136261u ^ (uint32_t)(until - k);  // identity hint of the inserted sequence
+              for (int j = k; j < until; ++j) {
+                q = min(q, (int)__ldg(R.qual + s0 + j));
+                const uint64_t gi = s0 + (uint64_t)j;
+                h = (h ^ ((__ldg(R.bases2 + (gi >> 2)) >> ((gi & 3) * 2)) & 3)) * 16777619u;
+              }
+              add_event(ll, rl, slot, GUAC_ALN_INSERTION, 4, q, (int)((h ^ (h >> 8) ^ (h >> 16) ^ (h >> 24)) & 0xFF));
+            } else {  // Deletion: the deleted reference bases must exist (PE.scala:95)
+              for (int j = 1; j <= nlen; ++j)
+                if (ref.at(t0 + ll + j) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + ll + j, r);
+              add_event(ll, rl, slot, GUAC_ALN_DELETION, nlen < 255 ? 4 : 5, __ldg(R.qual + s0 + k), nlen);
+            }
+          }
+        }
+        cl += len;
+        rp += len;
+      } else if (op == OPC_D) {
+        const int mq = __ldg(R.mapq + r);
+        for (int ll = max(cl, 0); ll < min(cl + len, n_loci); ++ll) add_event(ll, rl, slot, GUAC_ALN_MID_DELETION, 4, mq);
+        cl += len;
+      } else if (op == OPC_I || op == OPC_S) {
+        rp += len;
       }
     }
   }
   __syncthreads();
-  // slow reads: one warp per read, one lane per locus, exact cursor
+  // reads that need the exact cursor: one warp per read, one lane per locus
   {
     const int n_slow = min(S.n_slow, CFG::SLOW_MAX);
     for (int si = warp; si < n_slow; si += CFG::WARPS) {
       const int rl = S.slow[si];
       const int64_t r = tile.read_lo + rl;
-      const int slot = S.r_flags[rl] & 1;
-      const int a = max(S.r_start[rl], 0), b = min(S.r_end[rl], n_loci);
+      const int slot = (int)__ldg(R.sample_id + r) == P.tumor_sample ? 1 : 0;
+      const int a = (int)max((long long)(__ldg(R.start + r) - t0), 0ll);
+      const int b = (int)min((long long)(__ldg(R.end + r) - t0), (long long)n_loci);
       for (int l = a + lane; l < b; l += 32) {
         Elem e;
         const int ec = element_at(R, r, t0 + l, ref, e);
         if (ec != DERR_NONE) {
-          report_error(err, ec, tile.contig_id, t0 + l, r);
+          report_error(A.err, ec, tile.contig_id, t0 + l, r);
         } else if (e.kind != GUAC_ALN_MATCH) {
-          atomicAdd(&S.nonref[slot][l], 1);
-          const int i = atomicAdd(&S.n_events, 1);
-          if (i < CFG::E_MAX) S.ev[i] = pack_event(l, rl, slot, e.kind, e.kind == GUAC_ALN_MISMATCH ? base_code(e.base) : 4); else S.overflow = 1;
+          // indel alleles met on the exact path are resolved by the heavy kernel (code 5)
+          const int code = e.kind == GUAC_ALN_MISMATCH ? base_code(e.base)
+                           : (e.kind == GUAC_ALN_INSERTION || e.kind == GUAC_ALN_DELETION) ? 5 : 4;
+          add_event(l, rl, slot, e.kind, code, e.quality);
         }
       }
     }
   }
   __syncthreads();
   if (S.overflow) {  // a capacity was exceeded: hand the whole tile to the generic kernel
-    if (tid == 0) fallback_tiles[atomicAdd(n_fallback, 1)] = blockIdx.x;
+    if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
     return;
   }
 
@@ -302,313 +352,146 @@ ss_tile_kernel(ReadsView R, const uint8_t* __restrict__ rflags, const RefView* _
   __syncthreads();
   block_scan_inplace<CFG::THREADS>(S.diff[0], n_loci, S.warp_tot);
   block_scan_inplace<CFG::THREADS>(S.diff[1], n_loci, S.warp_tot);
-  block_scan_inplace<CFG::THREADS>(S.starts, n_loci, S.warp_tot);
   block_scan_inplace<CFG::THREADS>(S.lowq, n_loci, S.warp_tot);
   block_scan_inplace<CFG::THREADS>(S.ev_off, n_loci + 1, S.warp_tot);
-  // bucket the events by locus
   const int n_events = S.n_events;
-  for (int i = tid; i < n_events; i += CFG::THREADS) {
+  for (int i = tid; i < n_events; i += CFG::THREADS) {  // bucket the events by locus
     const uint32_t ev = S.ev[i];
     const int l = ev & 0x7FF;
-    S.ev_sorted[S.ev_off[l] + atomicAdd(&S.cursor[l], 1)] = ev;
-  }
-  // per-locus early-outs (SomaticStandardCaller.scala:164-172) and the dense summary of
-  // loci that need no likelihood
-  for (int l = tid; l < n_loci; l += CFG::THREADS) {
-    const int dN = S.diff[0][l], dT = S.diff[1][l];
-    const int nrN = S.nonref[0][l], nrT = S.nonref[1][l];
-    const int64_t slot = tile.slot0 + l;
-    // visited: any sample's window is non-empty.  Reads of other samples (< n_samples) count too.
-    bool any = dN + dT > 0;
-    if (P.n_samples > 2 && !any) {
-      // rare configuration (normal/tumor ids not {0,1}): test the staged reads directly
-      const int hi = S.starts[l];
-      for (int i = 0; i < hi && !any; ++i) any = S.r_start[i] <= l && l < S.r_end[i];
-    }
-    visited[slot] = any ? 1 : 0;
-    if (dN + dT > 0 && ref.at(t0 + l) == 0) report_error(err, DERR_REF_MISSING, tile.contig_id, t0 + l, -1);
-    const bool candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
-    if (candidate) {
-      S.cand[atomicAdd(&S.n_cand, 1)] = (uint16_t)l;
-    } else {
-      guac_locus_summary sn, st;
-      sn.depth = (uint16_t)min(dN, 65535);
-      sn.reference_depth = (uint16_t)min(dN - nrN, 65535);
-      sn.top_alt_count = 0;
-      sn.flags = 0;
-      st.depth = (uint16_t)min(dT, 65535);
-      st.reference_depth = (uint16_t)min(dT - nrT, 65535);
-      st.top_alt_count = 0;
-      st.flags = 0;
-      summary[slot * 2 + 0] = sn;
-      summary[slot * 2 + 1] = st;
-    }
+    const int d = S.ev_off[l] + atomicAdd(&S.cursor[l], 1);
+    S.ev_sorted[d] = ev;
+    S.evq_sorted[d] = S.evq[i];
   }
   __syncthreads();
 
-  // ---- C. candidate loci, one warp each --------------------------------------------------------
-  const int n_cand = S.n_cand;
-  const int max_span = S.max_span;
-  unsigned* hist = S.hist[warp];
-  for (int ci = warp; ci < n_cand; ci += CFG::WARPS) {
-    const int l = S.cand[ci];
-    const int64_t x = t0 + l, slot = tile.slot0 + l;
+  // ---- C. one thread per locus ------------------------------------------------------------------
+  for (int l = tid; l < n_loci; l += CFG::THREADS) {
     const int dN = S.diff[0][l], dT = S.diff[1][l];
     const int nrN = S.nonref[0][l], nrT = S.nonref[1][l];
-    // most frequent tumor variant allele from the locus's events
-    uint64_t tkey = 0;
-    int tcnt = 0, ntab = 0;
-    int64_t tfirst = 0;
-    const int e0 = S.ev_off[l], e1 = S.ev_off[l + 1];
-    for (int base = e0; base < e1; base += 32) {
-      const int i = base + lane;
-      const bool has = i < e1;
-      const uint32_t ev = has ? S.ev_sorted[i] : 0;
-      const int rl = (ev >> 11) & 0xFFF, eslot = (ev >> 23) & 1, kind = (ev >> 24) & 7, code = (ev >> 27) & 7;
-      const bool var = has && eslot == 1 && kind != GUAC_ALN_CLIPPED;
-      const int64_t r = tile.read_lo + rl;
-      uint64_t key = 0;
-      if (var) {
-        if (kind == GUAC_ALN_MISMATCH && code < 4) {
-          key = (1ull << 60) | (uint8_t)("ACGT"[code]);
-        } else if (kind == GUAC_ALN_MID_DELETION) {
-          key = 4ull << 60;
-        } else {
-          Elem e;
-          element_at(R, r, x, ref, e);
-          key = allele_key(R, r, e);
-        }
-      }
-      unsigned vm = __ballot_sync(FULL, var);
-      while (vm) {
-        const int L = __ffs(vm) - 1;
-        const uint64_t k = __shfl_sync(FULL, key, L);
-        const unsigned same = __ballot_sync(FULL, var && key == k);
-        const int c = __popc(same);
-        long long mn = (var && key == k) ? (long long)r : LLONG_MAX;
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) mn = min(mn, __shfl_xor_sync(FULL, mn, d));
-        const unsigned hit = __ballot_sync(FULL, lane < ntab && tkey == k);
-        if (hit) {
-          if (lane == __ffs(hit) - 1) {
-            tcnt += c;
-            tfirst = min((long long)tfirst, mn);
+    const int64_t slot = tile.slot0 + l, x = t0 + l;
+    A.visited[slot] = dN + dT > 0 ? 1 : 0;
+    if (dN + dT > 0 && ref.at(x) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x, -1);
+    // early-outs (SomaticStandardCaller.scala:164-172)
+    const bool candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
+    int top_t = 0, top_n = 0, flags = 0;
+    if (candidate) {
+      const int e0 = S.ev_off[l], e1 = S.ev_off[l + 1];
+      bool simple = e1 - e0 <= CFG::EV_SIMPLE;
+      // Distinct tumor variant alleles of the locus, straight from its (few) events.  An allele is
+      // identified by (kind, base) for SNVs, (kind, length) for deletions, kind alone for mid-deletions
+      // and (kind, 8-bit hash) for insertions — the last only when no other insertion shares the hash.
+      auto akey = [&](int i, uint32_t ev) {
+        const int kind = (ev >> 24) & 7, code = (ev >> 27) & 7;
+        return (kind << 8) | (kind == GUAC_ALN_MISMATCH ? code : (kind == GUAC_ALN_MID_DELETION ? 0 : (S.evq_sorted[i] >> 8)));
+      };
+      int best = -1, bcnt = 0, bfirst = INT_MAX;
+      if (simple)
+        for (int i = e0; i < e1; ++i) {
+          const uint32_t ev = S.ev_sorted[i];
+          const int eslot = (ev >> 23) & 1, kind = (ev >> 24) & 7, code = (ev >> 27) & 7;
+          if (code == 5 || (kind == GUAC_ALN_MISMATCH && code == 4)) {  // either sample: allele not identified here
+            simple = false;
+            break;
           }
-        } else if (ntab < 32) {
-          if (lane == ntab) {
-            tkey = k;
-            tcnt = c;
-            tfirst = mn;
+          if (eslot != 1 || kind == GUAC_ALN_CLIPPED) continue;  // Clipped is not a variant allele
+          const int key = akey(i, ev);
+          int c = 0, first = INT_MAX;
+          bool seen_before = false;
+          for (int j = e0; j < e1; ++j) {
+            const uint32_t ej = S.ev_sorted[j];
+            if (((ej >> 23) & 1) != 1 || ((ej >> 24) & 7) == GUAC_ALN_CLIPPED || akey(j, ej) != key) continue;
+            if (j < i) seen_before = true;
+            ++c;
+            first = min(first, (int)((ej >> 11) & 0xFFF));
           }
-          ++ntab;
-        } else if (lane == 0) {
-          report_error(err, DERR_ALLELE_TABLE_FULL, tile.contig_id, x, mn);
-        }
-        vm &= ~same;
-      }
-    }
-    int bcnt = lane < ntab ? tcnt : -1;
-    int64_t bfirst = lane < ntab ? tfirst : INT64_MAX;
-    uint64_t bkey = tkey;
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-      const int oc = __shfl_xor_sync(FULL, bcnt, d);
-      const int64_t of = __shfl_xor_sync(FULL, bfirst, d);
-      const uint64_t ok = __shfl_xor_sync(FULL, bkey, d);
-      if (oc > bcnt || (oc == bcnt && of < bfirst)) {
-        bcnt = oc;
-        bfirst = of;
-        bkey = ok;
-      }
-    }
-    if (ntab == 0) {  // every non-match tumor element is Clipped: maxBy on an empty map (:188)
-      if (lane == 0) report_error(err, DERR_EMPTY_MAXBY, tile.contig_id, x, -1);
-      continue;
-    }
-    const double f = fmax(P.min_vaf, (double)bcnt / (double)dT);  // :189
-
-    // Exact pruning.  tumorAltLOD = sum over tumor elements of log(P(e|mix)) - log(P(e|ref)):
-    //   element of the reference allele:  log(1 - f + f (1-p)/p)  <= 0 whenever p >= 1/2,
-    //   element of the called allele:     log(1 - f + f p/(1-p)),
-    //   any other element:                log(1) = 0.
-    // When every tumor read over the locus has all base qualities >= 4 (p >= 0.60; tracked by
-    // lowq[]), the sum over the called allele's elements — known from the events — bounds the
-    // LOD from above, and a locus whose bound is below the threshold (minus a 0.5 margin that
-    // dwarfs any rounding) cannot be called (:231), so its qualities are never gathered.
-    double bsum = 0;
-    int normalAltEv = 0;
-    for (int base = e0; base < e1; base += 32) {
-      const int i = base + lane;
-      const bool has = i < e1;
-      const uint32_t ev = has ? S.ev_sorted[i] : 0;
-      const int rl = (ev >> 11) & 0xFFF, eslot = (ev >> 23) & 1, kind = (ev >> 24) & 7, code = (ev >> 27) & 7;
-      const bool var = has && kind != GUAC_ALN_CLIPPED;
-      uint64_t key = 0;
-      int q = 0;
-      if (var) {
-        if (S.r_flags[rl] & 2) {  // fast read: a mismatch with an ACGT base
-          key = (1ull << 60) | (uint8_t)("ACGT"[code]);
-          if (eslot == 1 && key == bkey) q = __ldg(R.qual + seq_base + S.r_s0[rl] + (uint64_t)(l - S.r_start[rl]));
-        } else {
-          Elem e;
-          const int64_t r = tile.read_lo + rl;
-          if (element_at(R, r, x, ref, e) == DERR_NONE) {
-            key = allele_key(R, r, e);
-            q = e.quality;
+          if (seen_before) continue;
+          // most frequent allele; ties -> lowest first supporting read (documented canonical order)
+          if (c > bcnt || (c == bcnt && first < bfirst)) {
+            best = key;
+            bcnt = c;
+            bfirst = first;
           }
         }
+      if (simple && best < 0) simple = false;  // maxBy over an empty map (:188): the heavy path reports it
+      if (simple && (best >> 8) == GUAC_ALN_INSERTION) {
+        int same = 0;
+        for (int j = e0; j < e1; ++j) {
+          const uint32_t ej = S.ev_sorted[j];
+          same += ((ej >> 24) & 7) == GUAC_ALN_INSERTION && akey(j, ej) == best;
+        }
+        if (same > 1) simple = false;  // equal hashes: the exact path compares the sequences
       }
-      const bool is_alt = var && key == bkey;
-      normalAltEv += __popc(__ballot_sync(FULL, is_alt && eslot == 0));
-      if (is_alt && eslot == 1) {
-        const double p = c_success_probability[q];
-        bsum += log(1.0 - f + f * (p / (1.0 - p)));
-      }
-    }
-    bsum = warp_sum(bsum);
-    if (S.lowq[l] == 0 && bsum < (double)P.tumor_odds - 0.5) {
-      if (lane == 0) {
-        guac_locus_summary sn, st;
-        sn.depth = (uint16_t)min(dN, 65535);
-        sn.reference_depth = (uint16_t)min(dN - nrN, 65535);
-        sn.top_alt_count = (uint16_t)min(normalAltEv, 65535);
-        sn.flags = 1;
-        st.depth = (uint16_t)min(dT, 65535);
-        st.reference_depth = (uint16_t)min(dT - nrT, 65535);
-        st.top_alt_count = (uint16_t)min(bcnt, 65535);
-        st.flags = 1;
-        summary[slot * 2 + 0] = sn;
-        summary[slot * 2 + 1] = st;
-      }
-      continue;
-    }
-    const bool best_snv = (bkey >> 60) == 1;
-    const int best_code = best_snv ? base_code((uint8_t)(bkey & 0xFF)) : 5;
-    const int ref_code = (S.ref2[l >> 4] >> (2 * (l & 15))) & 3;
-    const bool ref_is_acgt = !((S.refmask[l >> 5] >> (l & 31)) & 1);
-
-    // likelihood gather over the reads that can overlap the locus
-    const int hi = S.starts[l];
-    const int lo = l - max_span >= 0 ? S.starts[l - max_span] : 0;
-    double aTR = 0, aNR = 0, aNA = 0, aTAx = 0;  // aTAx: tumor mixture terms of elements with q >= QB
-    int normalAlt = 0;
-    for (int base = lo; base < hi; base += 32) {
-      const int i = base + lane;
-      bool ov = false;
-      int cls = 2, q = 0, eslot = 0;
-      if (i < hi) {
-        const int st = S.r_start[i], en = S.r_end[i];
-        const int fl = S.r_flags[i];
-        ov = st <= l && l < en && (fl & 4);
-        if (ov) {
-          eslot = fl & 1;
-          if (fl & 2) {  // fast read: Match or Mismatch
-            const uint64_t gi = seq_base + S.r_s0[i] + (uint64_t)(l - st);
-            q = __ldg(R.qual + gi);
-            const int code = (__ldg(R.bases2 + (gi >> 2)) >> ((gi & 3) * 2)) & 3;
-            cls = (ref_is_acgt && code == ref_code) ? 0 : (code == best_code ? 1 : 2);
+      if (simple) {
+        const double f = fmax(P.min_vaf, (double)bcnt / (double)dT);  // :189
+        // prune: tumorAltLOD = sum over tumor elements of log P(e|mix) - log P(e|ref), where an element
+        //   of the reference allele contributes log(1 - f + f (1-p)/p)  <= 0 whenever p >= 1/2,
+        //   of the called allele             log(1 - f + f p/(1-p)),
+        //   of anything else                 log(1) = 0.
+        // If every tumor read over the locus has all base qualities >= 4 (lowq == 0) the called allele's
+        // terms bound the LOD from above; a bound below the threshold (minus a 0.5 margin that dwarfs
+        // rounding) means no call is possible (:231) and the matching bases' qualities are never read.
+        double bound = 0;
+        int n_alt_normal = 0;
+        const bool at_floor = f == P.min_vaf;
+        for (int i = e0; i < e1; ++i) {
+          const uint32_t ev = S.ev_sorted[i];
+          const int eslot = (ev >> 23) & 1, kind = (ev >> 24) & 7;
+          if (kind == GUAC_ALN_CLIPPED || akey(i, ev) != best) continue;
+          if (eslot == 0) {
+            ++n_alt_normal;
           } else {
-            Elem e;
-            const int64_t r = tile.read_lo + i;
-            if (element_at(R, r, x, ref, e) == DERR_NONE) {
-              q = e.quality;
-              if (e.kind == GUAC_ALN_MATCH) cls = 0;
-              else if (e.kind != GUAC_ALN_CLIPPED && allele_key(R, r, e) == bkey) cls = 1;
-              else cls = 2;
+            const int q = S.evq_sorted[i] & 0xFF;
+            if (at_floor) {
+              bound += __ldg(A.bound_tab + q);
             } else {
-              ov = false;
+              const double p = c_success_probability[q];
+              bound += log(1.0 - f + f * (p / (1.0 - p)));
             }
           }
         }
-      }
-      if (ov) {
-        if (eslot == 1) {
-          aTR += __ldg(&LT->ref[cls][q]);
-          if (q < CFG::QB) {
-            atomicAdd(&hist[cls * CFG::QB + q], 1u);
-          } else {
-            const double p = c_success_probability[q];
-            const double pr = cls == 0 ? p : 1 - p, pa = cls == 1 ? p : 1 - p;
-            aTAx += log(pr * (1.0 - f) + pa * f);
-          }
+        // a mid-deletion allele has empty alt bases and is never called (:233)
+        const bool never_called = (best >> 8) == GUAC_ALN_MID_DELETION;
+        if (never_called || (S.lowq[l] == 0 && bound < (double)P.tumor_odds - 0.5)) {
+          top_t = bcnt;
+          top_n = n_alt_normal;
+          flags = 1;
         } else {
-          aNR += __ldg(&LT->ref[cls][q]);
-          aNA += __ldg(&LT->het[cls][q]);
+          simple = false;
         }
       }
-      normalAlt += __popc(__ballot_sync(FULL, ov && eslot == 0 && cls == 1));
+      if (!simple) {  // full evaluation by the generic kernel
+        const int h = atomicAdd(A.n_heavy, 1);
+        if (h < A.max_heavy) {
+          Tile t;
+          t.locus0 = x;
+          t.n_loci = 1;
+          t.contig_id = tile.contig_id;
+          t.slot0 = slot;
+          t.read_lo = tile.read_lo;
+          t.read_hi = tile.read_hi;
+          t.ref_index = tile.ref_index;
+          t._pad = 0;
+          A.heavy[h] = t;
+        }
+        continue;  // the heavy kernel writes this locus's summary
+      }
     }
-    __syncwarp();
-    // tumor mixture terms: compact the non-empty (class, quality) bins, then one log per bin
-    double aTA = aTAx;
-    {
-      unsigned* clist = S.clist[warp];
-      int nb = 0;
-      for (int s = 0; s < 3 * CFG::QB; s += 32) {
-        const unsigned n = hist[s + lane];
-        const unsigned nz = __ballot_sync(FULL, n != 0);
-        if (n) {
-          hist[s + lane] = 0;
-          clist[nb + __popc(nz & ((1u << lane) - 1))] = ((unsigned)(s + lane) << 24) | n;
-        }
-        nb += __popc(nz);
-      }
-      __syncwarp();
-      for (int base = 0; base < nb; base += 32) {
-        if (base + lane < nb) {
-          const unsigned w = clist[base + lane];
-          const int bin = (int)(w >> 24), n = (int)(w & 0xFFFFFF);
-          const int cls = bin / CFG::QB, q = bin - cls * CFG::QB;
-          const double p = c_success_probability[q];
-          const double pr = cls == 0 ? p : 1 - p, pa = cls == 1 ? p : 1 - p;
-          aTA += (double)n * log(pr * (1.0 - f) + pa * f);
-        }
-      }
-      __syncwarp();
-    }
-    aTR = warp_sum(aTR);
-    aTA = warp_sum(aTA);
-    aNR = warp_sum(aNR);
-    aNA = warp_sum(aNA);
-    double tR, tA, nR, nA;
-    log_normalize2(aTR, aTA, tR, tA);
-    log_normalize2(aNR, aNA, nR, nA);
-    const double tumorAltLOD = tA - tR, normalRefLOD = nR - nA;
-    const bool called = tumorAltLOD > P.tumor_odds && normalRefLOD > P.normal_odds && (bkey >> 60) != 4;  // :231-233
-    if (lane == 0) {
-      if (called) {
-        const int idx = atomicAdd(n_calls, 1);
-        if (idx < max_calls) {
-          SSCallDev c;
-          c.slot = slot;
-          c.locus = x;
-          c.read_lo = tile.read_lo;
-          c.read_hi = tile.read_hi;
-          c.key = bkey;
-          c.rep_read = bfirst;
-          c.contig_id = tile.contig_id;
-          c.ref_index = tile.ref_index;
-          c.tumor_ref_lp = tR;
-          c.tumor_alt_lp = tA;
-          c.normal_ref_lp = nR;
-          c.normal_alt_lp = nA;
-          c.ref_off = c.ref_len = c.alt_off = c.alt_len = 0;
-          calls[idx] = c;
-        }
-      }
-      const uint16_t fl = 1 | (called ? 2 : 0);
-      guac_locus_summary sn, st;
-      sn.depth = (uint16_t)min(dN, 65535);
-      sn.reference_depth = (uint16_t)min(dN - nrN, 65535);
-      sn.top_alt_count = (uint16_t)min(normalAlt, 65535);
-      sn.flags = fl;
-      st.depth = (uint16_t)min(dT, 65535);
-      st.reference_depth = (uint16_t)min(dT - nrT, 65535);
-      st.top_alt_count = (uint16_t)min(bcnt, 65535);
-      st.flags = fl;
-      summary[slot * 2 + 0] = sn;
-      summary[slot * 2 + 1] = st;
-    }
+    guac_locus_summary sn, st;
+    sn.depth = (uint16_t)min(dN, 65535);
+    sn.reference_depth = (uint16_t)min(dN - nrN, 65535);
+    sn.top_alt_count = (uint16_t)min(top_n, 65535);
+    sn.flags = (uint16_t)flags;
+    st.depth = (uint16_t)min(dT, 65535);
+    st.reference_depth = (uint16_t)min(dT - nrT, 65535);
+    st.top_alt_count = (uint16_t)min(top_t, 65535);
+    st.flags = (uint16_t)flags;
+    // one 16-byte store per locus
+    uint4 v;
+    v.x = (uint32_t)sn.depth | ((uint32_t)sn.reference_depth << 16);
+    v.y = (uint32_t)sn.top_alt_count | ((uint32_t)sn.flags << 16);
+    v.z = (uint32_t)st.depth | ((uint32_t)st.reference_depth << 16);
+    v.w = (uint32_t)st.top_alt_count | ((uint32_t)st.flags << 16);
+    reinterpret_cast<uint4*>(A.summary)[slot] = v;
   }
 }
 

@@ -255,6 +255,8 @@ void* guac_stream(guac_ctx* ctx);
 int guac_set_option(guac_ctx* ctx, const char* name, int64_t value);
 /* Tiles of the most recent guac_somatic_standard call that took the fallback path. */
 int64_t guac_last_fallback_tiles(guac_ctx* ctx);
+/* Loci of that call whose likelihoods had to be evaluated in full (not excluded by the LOD bound). */
+int64_t guac_last_heavy_loci(guac_ctx* ctx);
 /* Device time in ms (CUDA events on the context's stream) of the dominant per-locus kernel
  * of the most recent caller invocation, and how many loci it processed. */
 int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci);
