@@ -2,22 +2,22 @@
 //
 // One CTA owns a tile of TL consecutive loci; everything about the tile lives in shared memory.
 //   A. read-parallel pass, one thread per read: every read that can overlap the tile is visited
-//      ONCE.  Its coverage goes into per-sample difference arrays (+1 at start, -1 at end); its
-//      aligned segments are compared with the reference 16 bases (32 bits) at a time in 2-bit
-//      space, so only NON-matching elements (mismatches, insertion / deletion anchors,
-//      mid-deletion loci) cost anything: each becomes an event (locus, read, kind, base, quality).
-//      The CIGAR is walked per operator, never per base.  Reads that need the exact per-locus
-//      cursor (N skips, padding, non-ACGT bases, a leading insertion at locus 0) are rare and are
-//      handled one warp per read by element_at().
-//   B. block prefix scans turn the difference arrays into Pileup.depth per sample,
-//      referenceDepth = depth - events, and bucket the events by locus.
+//      ONCE.  Its coverage goes into a packed per-sample difference array (+1 at start, -1 at
+//      end); its aligned segments are compared with the reference 16 bases (32 bits) at a time in
+//      2-bit space, so only NON-matching elements (mismatches, insertion / deletion anchors,
+//      mid-deletion loci) cost anything: each becomes an event (locus, read, kind, base, where to
+//      find its quality).  The CIGAR is walked per operator, never per base.  Reads that need the
+//      exact per-locus cursor (N skips, padding, non-ACGT bases, a leading insertion at locus 0)
+//      are rare and are handled one warp per read by element_at().
+//   B. ONE block prefix scan over two packed arrays turns the differences into Pileup.depth per
+//      sample and buckets the events by locus; referenceDepth = depth - events.
 //   C. one thread per locus applies findPotentialVariantAtLocus's early-outs
 //      (SomaticStandardCaller.scala:164-172).  For a surviving locus the most frequent tumor
 //      variant allele and an exact upper bound of the tumor log-odds come from the events alone
-//      (see `prune` below); only loci whose bound reaches the threshold — or whose alleles are
-//      not plain SNVs — are appended to a list of "heavy" loci, which the generic gather kernel
-//      (kernels.cuh) evaluates in full afterwards.  Qualities of matching bases are therefore
-//      read only where a call is possible.
+//      (see `prune` below); only loci whose bound reaches the threshold — or whose alleles cannot
+//      be identified from the events — are appended to a list of "heavy" loci, which the generic
+//      gather kernel (kernels.cuh) evaluates in full afterwards.  Qualities of matching bases
+//      are therefore read only where a call is possible.
 // Tiles that exceed a shared-memory capacity go to a fallback list and are re-run whole by the
 // generic kernel — still on the GPU.
 #pragma once
@@ -30,7 +30,7 @@ struct TileCfg {
   static constexpr int TL = TL_;  // loci per tile
   static constexpr int THREADS = 256;
   static constexpr int WARPS = THREADS / 32;
-  static constexpr int R_MAX = 4095;     // reads per tile (12-bit read index in an event)
+  static constexpr int R_MAX = 4095;     // reads per tile (12-bit read index in an event; depth < 2^16 follows)
   static constexpr int E_MAX = TL * 4;   // non-match events per tile
   static constexpr int SLOW_MAX = 256;
   static constexpr int EV_SIMPLE = 24;   // a locus with more events goes to the heavy path
@@ -86,44 +86,18 @@ __device__ __forceinline__ uint32_t spread16(uint32_t x) {  // bit i -> bit 2i
 // 32 bits starting at bit `bit` of a little-endian word stream
 __device__ __forceinline__ uint32_t load_bits32_g(const uint8_t* __restrict__ bytes, uint64_t bit) {
   const uint32_t* w = reinterpret_cast<const uint32_t*>(bytes) + (bit >> 5);
-  const int sh = (int)(bit & 31);
-  const uint32_t lo = __ldg(w);
-  if (sh == 0) return lo;
-  return __funnelshift_r(lo, __ldg(w + 1), sh);
+  return __funnelshift_r(__ldg(w), __ldg(w + 1), (int)(bit & 31));
 }
 __device__ __forceinline__ uint32_t load_bits32_s(const uint32_t* words, int bit) {
-  const int sh = bit & 31;
-  const uint32_t lo = words[bit >> 5];
-  if (sh == 0) return lo;
-  return __funnelshift_r(lo, words[(bit >> 5) + 1], sh);
+  return __funnelshift_r(words[bit >> 5], words[(bit >> 5) + 1], bit & 31);
 }
 
-// in-place inclusive prefix sum of a shared int array (all threads of the CTA participate)
-template <int THREADS>
-__device__ __forceinline__ void block_scan_inplace(int* a, int n, int* warp_tot /*[THREADS/32]*/) {
-  const int per = (n + THREADS - 1) / THREADS;
-  const int b = threadIdx.x * per, e = min(n, b + per);
-  int s = 0;
-  for (int i = b; i < e; ++i) s += a[i];
-  int inc = s;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    int o = __shfl_up_sync(0xffffffffu, inc, d);
-    if ((threadIdx.x & 31) >= d) inc += o;
-  }
-  if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
-  __syncthreads();
-  int carry = 0;
-  for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) carry += warp_tot[w];
-  int run = carry + inc - s;
-  for (int i = b; i < e; ++i) {
-    run += a[i];
-    a[i] = run;
-  }
-  __syncthreads();
-}
-
-// event word: [0,11) locus in tile | [11,23) read in tile | 23 sample slot | [24,27) kind | [27,30) base code (4 = not ACGT)
+// event word: [0,11) locus in tile | [11,23) read in tile | 23 sample slot | [24,27) kind | [27,30) code
+//   code: Mismatch -> base code (4 = not ACGT); other kinds -> 4 = allele identified by the detail byte,
+//         5 = allele must be resolved by the exact path
+// second word: Mismatch of an aligned segment -> index of the base's quality relative to the tile's first
+//   read (fetched only if the event matters); otherwise bit 31 | detail << 8 | qualityScore
+//   (detail: Deletion = deleted length, Insertion = 8-bit hash of the inserted bases).
 __device__ __forceinline__ uint32_t pack_event(int l, int rl, int slot, int kind, int code) {
   return (uint32_t)l | ((uint32_t)rl << 11) | ((uint32_t)slot << 23) | ((uint32_t)kind << 24) | ((uint32_t)code << 27);
 }
@@ -133,18 +107,15 @@ template <class CFG>
 struct TileSmem {
   uint32_t ref2[CFG::TL / 16 + 2];
   uint32_t refmask[CFG::TL / 32 + 2];
-  int diff[2][CFG::TL + 1];   // -> depth after the scan
-  int nonref[2][CFG::TL];     // non-Match elements per sample
-  int lowq[CFG::TL + 1];      // -> tumor reads over the locus that carry a base quality < 4
-  int ev_off[CFG::TL + 1];    // events per locus -> offsets
+  int cov[CFG::TL + 1];     // packed differences: normal | tumor << 16  -> depths after the scan
+  int aux[CFG::TL + 1];     // low-quality tumor read differences | event count << 16 -> lowq | event end offset
+  int nonref[CFG::TL];      // non-Match elements: normal | tumor << 16
   int cursor[CFG::TL];
-  uint32_t ev[CFG::E_MAX];
-  uint32_t ev_sorted[CFG::E_MAX];
-  uint16_t evq[CFG::E_MAX];       // low byte: qualityScore of the element; high byte: allele detail
-  uint16_t evq_sorted[CFG::E_MAX];  // (Deletion: deleted length, Insertion: 8-bit hash of the inserted bases)
+  uint2 ev[CFG::E_MAX];
+  uint2 ev_sorted[CFG::E_MAX];
   uint16_t slow[CFG::SLOW_MAX];
-  int warp_tot[CFG::WARPS];
-  int n_events, n_slow, overflow;
+  int warp_tot[2][CFG::WARPS];
+  int n_events, n_slow, overflow, ref_has_mask;
 };
 
 struct TileArgs {
@@ -169,6 +140,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TileSmem<CFG>& S = *reinterpret_cast<TileSmem<CFG>*>(smem_raw);
   constexpr int TL = CFG::TL;
+  const unsigned FULL = 0xffffffffu;
   const Tile tile = A.tiles[blockIdx.x];
   const RefView ref = A.refs[tile.ref_index];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -178,48 +150,48 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
 
   bool too_big = n_reads_tile > CFG::R_MAX;
   if (A.force_fallback_mod > 0 && blockIdx.x % A.force_fallback_mod == 0) too_big = true;  // test hook
+  const uint64_t seq_base = n_reads_tile > 0 ? __ldg(R.seq_off + tile.read_lo) : 0;
+  if (!too_big && n_reads_tile > 0) too_big = (__ldg(R.seq_off + tile.read_hi) - seq_base) >= (1ull << 31);
   if (too_big) {  // uniform across the CTA
     if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
     return;
   }
 
   // ---- init ------------------------------------------------------------------------------
-  for (int i = tid; i < TL + 1; i += CFG::THREADS) {
-    S.diff[0][i] = S.diff[1][i] = 0;
-    S.lowq[i] = 0;
-    S.ev_off[i] = 0;
-  }
-  for (int i = tid; i < TL; i += CFG::THREADS) {
-    S.nonref[0][i] = S.nonref[1][i] = 0;
-    S.cursor[i] = 0;
-  }
-  if (tid == 0) S.n_events = S.n_slow = S.overflow = 0;
-  // reference tile -> 2-bit words (16 loci per word) and a not-ACGT mask (16 bits per half word)
-  for (int w = tid; w < TL / 16 + 2; w += CFG::THREADS) {
-    uint32_t bits = 0, mask = 0;
-#pragma unroll 4
-    for (int k = 0; k < 16; ++k) {
-      const int l = w * 16 + k;
-      const uint8_t b = l < n_loci ? ref.at(t0 + l) : (uint8_t)'A';
-      const int c = base_code(b);
-      if (c < 4) bits |= (uint32_t)c << (2 * k); else mask |= 1u << k;
-    }
-    S.ref2[w] = bits;
-    reinterpret_cast<uint16_t*>(S.refmask)[w] = (uint16_t)mask;
+  for (int i = tid; i < TL + 1; i += CFG::THREADS) S.cov[i] = S.aux[i] = 0;
+  for (int i = tid; i < TL; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
+  if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = 0;
+  if (tid < 4) {  // padding words behind the tile
+    S.ref2[TL / 16 + (tid & 1)] = 0;
+    S.refmask[TL / 32 + (tid & 1)] = 0;
   }
   __syncthreads();
-
-  // code: Mismatch -> base code (4 = not ACGT); other kinds -> 4 = allele identified by `detail`, 5 = needs the exact path
-  auto add_event = [&](int l, int rl, int slot, int kind, int code, int q, int detail = 0) {
-    atomicAdd(&S.nonref[slot][l], 1);
-    const int e = atomicAdd(&S.n_events, 1);
-    if (e < CFG::E_MAX) {
-      S.ev[e] = pack_event(l, rl, slot, kind, code);
-      S.evq[e] = (uint16_t)((q & 0xFF) | ((detail & 0xFF) << 8));
-    } else {
-      S.overflow = 1;
+  // reference tile -> 2-bit words (16 loci per word) and a not-ACGT mask (32 loci per word): one
+  // coalesced byte per thread, packed with warp-wide OR reductions
+  for (int base = 0; base < TL; base += CFG::THREADS) {
+    const int l = base + tid;
+    const uint8_t b = l < n_loci ? ref.at(t0 + l) : (uint8_t)'A';
+    const int c = base_code(b);
+    const uint32_t bits = c < 4 ? (uint32_t)c << (2 * (lane & 15)) : 0u;
+    const uint32_t lo = __reduce_or_sync(FULL, lane < 16 ? bits : 0u);
+    const uint32_t hi = __reduce_or_sync(FULL, lane >= 16 ? bits : 0u);
+    const uint32_t mask = __ballot_sync(FULL, c == 4);
+    if (lane == 0) {
+      S.ref2[(base >> 4) + 2 * warp] = lo;
+      S.ref2[(base >> 4) + 2 * warp + 1] = hi;
+      S.refmask[(base >> 5) + warp] = mask;
+      if (mask) S.ref_has_mask = 1;
     }
+  }
+  __syncthreads();
+  const bool ref_has_mask = S.ref_has_mask != 0;
+
+  auto push_event = [&](int l, int rl, int slot, int kind, int code, uint32_t second) {
+    atomicAdd(&S.nonref[l], slot ? 65536 : 1);
+    const int e = atomicAdd(&S.n_events, 1);
+    if (e < CFG::E_MAX) S.ev[e] = make_uint2(pack_event(l, rl, slot, kind, code), second); else S.overflow = 1;
   };
+  auto direct = [](int q, int detail) { return 0x80000000u | ((uint32_t)(detail & 0xFF) << 8) | (uint32_t)(q & 0xFF); };
 
   // ---- A. read-parallel pass ---------------------------------------------------------------
   for (int rl = tid; rl < (int)n_reads_tile; rl += CFG::THREADS) {
@@ -232,11 +204,12 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const int a = max(st, 0), b = min(en, n_loci);  // overlap [a, b) in tile coordinates
     if (a >= b) continue;
     const uint8_t rf = __ldg(A.rflags + r);
-    atomicAdd(&S.diff[slot][a], 1);
-    atomicAdd(&S.diff[slot][b], -1);
+    const int one = slot ? 65536 : 1;
+    atomicAdd(&S.cov[a], one);
+    atomicAdd(&S.cov[b], -one);
     if (slot == 1 && !(rf & RF_HIQ)) {
-      atomicAdd(&S.lowq[a], 1);
-      atomicAdd(&S.lowq[b], -1);
+      atomicAdd(&S.aux[a], 1);
+      atomicAdd(&S.aux[b], -1);
     }
     if (!(rf & RF_MEDIUM)) {
       const int i = atomicAdd(&S.n_slow, 1);
@@ -244,23 +217,21 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       continue;
     }
     const uint64_t s0 = __ldg(R.seq_off + r);
+    const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     // aligned segment: loci [lb, le) (tile coordinates, unclipped) hold read positions rp0..; 16 bases per step
     auto compare_segment = [&](int lb, int le, int rp0) {
       const int ca = max(lb, 0), cb = min(le, n_loci);
       for (int l = ca; l < cb; l += 16) {
         const int k = rp0 + (l - lb);
         const uint32_t rd = load_bits32_g(R.bases2, 2 * (s0 + (uint64_t)k));
-        const uint32_t rfw = load_bits32_s(S.ref2, 2 * l);
-        const uint32_t x = rd ^ rfw;
+        const uint32_t x = rd ^ load_bits32_s(S.ref2, 2 * l);
         uint32_t m = (x | (x >> 1)) & 0x55555555u;
-        m |= spread16(load_bits32_s(S.refmask, l) & 0xFFFFu);  // a not-ACGT reference base never equals an ACGT read base
-        const int nb = cb - l;
-        if (nb < 16) m &= (1u << (2 * nb)) - 1;
+        if (ref_has_mask) m |= spread16(load_bits32_s(S.refmask, l));  // a not-ACGT reference base never equals an ACGT read base
+        if (cb - l < 16) m &= (1u << (2 * (cb - l))) - 1;
         while (m) {
           const int bit = __ffs(m) - 1;
           m &= m - 1;
-          const int i16 = bit >> 1;
-          add_event(l + i16, rl, slot, GUAC_ALN_MISMATCH, (rd >> bit) & 3, __ldg(R.qual + s0 + k + i16));
+          push_event(l + (bit >> 1), rl, slot, GUAC_ALN_MISMATCH, (rd >> bit) & 3, s0_rel + (uint32_t)(k + (bit >> 1)));
         }
       }
     };
@@ -288,7 +259,6 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         if (special_last) {
           const int ll = cl + len - 1, k = rp + len - 1;
           if (ll >= 0 && ll < n_loci) {
-            if (ref.at(t0 + ll) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + ll, r);
             if (nop == OPC_I) {  // qualityScore = min over anchor + inserted qualities (PE.scala:153)
               const int until = min(k + nlen + 1, read_len);
               int q = 255;
@@ -298,11 +268,11 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
                 const uint64_t gi = s0 + (uint64_t)j;
                 h = (h ^ ((__ldg(R.bases2 + (gi >> 2)) >> ((gi & 3) * 2)) & 3)) * 16777619u;
               }
-              add_event(ll, rl, slot, GUAC_ALN_INSERTION, 4, q, (int)((h ^ (h >> 8) ^ (h >> 16) ^ (h >> 24)) & 0xFF));
+              push_event(ll, rl, slot, GUAC_ALN_INSERTION, 4, direct(q, (int)((h ^ (h >> 8) ^ (h >> 16) ^ (h >> 24)) & 0xFF)));
             } else {  // Deletion: the deleted reference bases must exist (PE.scala:95)
               for (int j = 1; j <= nlen; ++j)
                 if (ref.at(t0 + ll + j) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + ll + j, r);
-              add_event(ll, rl, slot, GUAC_ALN_DELETION, nlen < 255 ? 4 : 5, __ldg(R.qual + s0 + k), nlen);
+              push_event(ll, rl, slot, GUAC_ALN_DELETION, nlen < 255 ? 4 : 5, direct(__ldg(R.qual + s0 + k), nlen));
             }
           }
         }
@@ -310,7 +280,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         rp += len;
       } else if (op == OPC_D) {
         const int mq = __ldg(R.mapq + r);
-        for (int ll = max(cl, 0); ll < min(cl + len, n_loci); ++ll) add_event(ll, rl, slot, GUAC_ALN_MID_DELETION, 4, mq);
+        for (int ll = max(cl, 0); ll < min(cl + len, n_loci); ++ll) push_event(ll, rl, slot, GUAC_ALN_MID_DELETION, 4, direct(mq, 0));
         cl += len;
       } else if (op == OPC_I || op == OPC_S) {
         rp += len;
@@ -336,7 +306,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
           // indel alleles met on the exact path are resolved by the heavy kernel (code 5)
           const int code = e.kind == GUAC_ALN_MISMATCH ? base_code(e.base)
                            : (e.kind == GUAC_ALN_INSERTION || e.kind == GUAC_ALN_DELETION) ? 5 : 4;
-          add_event(l, rl, slot, e.kind, code, e.quality);
+          push_event(l, rl, slot, e.kind, code, direct(e.quality, 0));
         }
       }
     }
@@ -347,27 +317,63 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     return;
   }
 
-  // ---- B. scans -----------------------------------------------------------------------------
-  for (int i = tid; i < n_loci; i += CFG::THREADS) S.ev_off[i + 1] = S.nonref[0][i] + S.nonref[1][i];
-  __syncthreads();
-  block_scan_inplace<CFG::THREADS>(S.diff[0], n_loci, S.warp_tot);
-  block_scan_inplace<CFG::THREADS>(S.diff[1], n_loci, S.warp_tot);
-  block_scan_inplace<CFG::THREADS>(S.lowq, n_loci, S.warp_tot);
-  block_scan_inplace<CFG::THREADS>(S.ev_off, n_loci + 1, S.warp_tot);
+  // ---- B. one scan over both packed arrays ----------------------------------------------------
+  {
+    constexpr int PER = (TL + CFG::THREADS) / CFG::THREADS;  // covers TL + 1 entries
+    const int b0 = tid * PER, e0 = min(n_loci + 1, b0 + PER);
+    int s_cov = 0, s_aux = 0;
+    for (int i = b0; i < e0; ++i) {
+      if (i < n_loci) {  // add the locus's event count to the high half of aux
+        const int nr = S.nonref[i];
+        S.aux[i] += ((nr & 0xFFFF) + (nr >> 16)) << 16;
+      }
+      s_cov += S.cov[i];
+      s_aux += S.aux[i];
+    }
+    int i_cov = s_cov, i_aux = s_aux;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int oc = __shfl_up_sync(FULL, i_cov, d), oa = __shfl_up_sync(FULL, i_aux, d);
+      if (lane >= d) {
+        i_cov += oc;
+        i_aux += oa;
+      }
+    }
+    if (lane == 31) {
+      S.warp_tot[0][warp] = i_cov;
+      S.warp_tot[1][warp] = i_aux;
+    }
+    __syncthreads();
+    int c_cov = 0, c_aux = 0;
+    for (int w = 0; w < warp; ++w) {
+      c_cov += S.warp_tot[0][w];
+      c_aux += S.warp_tot[1][w];
+    }
+    int r_cov = c_cov + i_cov - s_cov, r_aux = c_aux + i_aux - s_aux;
+    for (int i = b0; i < e0; ++i) {
+      r_cov += S.cov[i];
+      r_aux += S.aux[i];
+      S.cov[i] = r_cov;
+      S.aux[i] = r_aux;
+    }
+    __syncthreads();
+  }
+  // bucket the events by locus: events of locus l occupy [end(l) - count(l), end(l))
   const int n_events = S.n_events;
-  for (int i = tid; i < n_events; i += CFG::THREADS) {  // bucket the events by locus
-    const uint32_t ev = S.ev[i];
-    const int l = ev & 0x7FF;
-    const int d = S.ev_off[l] + atomicAdd(&S.cursor[l], 1);
-    S.ev_sorted[d] = ev;
-    S.evq_sorted[d] = S.evq[i];
+  for (int i = tid; i < n_events; i += CFG::THREADS) {
+    const uint2 ev = S.ev[i];
+    const int l = ev.x & 0x7FF;
+    const int nr = S.nonref[l];
+    const int first = (S.aux[l] >> 16) - ((nr & 0xFFFF) + (nr >> 16));
+    S.ev_sorted[first + atomicAdd(&S.cursor[l], 1)] = ev;
   }
   __syncthreads();
 
   // ---- C. one thread per locus ------------------------------------------------------------------
   for (int l = tid; l < n_loci; l += CFG::THREADS) {
-    const int dN = S.diff[0][l], dT = S.diff[1][l];
-    const int nrN = S.nonref[0][l], nrT = S.nonref[1][l];
+    const int cv = S.cov[l], nr = S.nonref[l];
+    const int dN = cv & 0xFFFF, dT = cv >> 16;
+    const int nrN = nr & 0xFFFF, nrT = nr >> 16;
     const int64_t slot = tile.slot0 + l, x = t0 + l;
     A.visited[slot] = dN + dT > 0 ? 1 : 0;
     if (dN + dT > 0 && ref.at(x) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x, -1);
@@ -375,34 +381,34 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const bool candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
     int top_t = 0, top_n = 0, flags = 0;
     if (candidate) {
-      const int e0 = S.ev_off[l], e1 = S.ev_off[l + 1];
+      const int e1 = S.aux[l] >> 16, e0 = e1 - (nrN + nrT);
       bool simple = e1 - e0 <= CFG::EV_SIMPLE;
       // Distinct tumor variant alleles of the locus, straight from its (few) events.  An allele is
       // identified by (kind, base) for SNVs, (kind, length) for deletions, kind alone for mid-deletions
       // and (kind, 8-bit hash) for insertions — the last only when no other insertion shares the hash.
-      auto akey = [&](int i, uint32_t ev) {
-        const int kind = (ev >> 24) & 7, code = (ev >> 27) & 7;
-        return (kind << 8) | (kind == GUAC_ALN_MISMATCH ? code : (kind == GUAC_ALN_MID_DELETION ? 0 : (S.evq_sorted[i] >> 8)));
+      auto akey = [&](uint2 ev) {
+        const int kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7;
+        return (kind << 8) | (kind == GUAC_ALN_MISMATCH ? code : (kind == GUAC_ALN_MID_DELETION ? 0 : (int)((ev.y >> 8) & 0xFF)));
       };
       int best = -1, bcnt = 0, bfirst = INT_MAX;
       if (simple)
         for (int i = e0; i < e1; ++i) {
-          const uint32_t ev = S.ev_sorted[i];
-          const int eslot = (ev >> 23) & 1, kind = (ev >> 24) & 7, code = (ev >> 27) & 7;
+          const uint2 ev = S.ev_sorted[i];
+          const int eslot = (ev.x >> 23) & 1, kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7;
           if (code == 5 || (kind == GUAC_ALN_MISMATCH && code == 4)) {  // either sample: allele not identified here
             simple = false;
             break;
           }
           if (eslot != 1 || kind == GUAC_ALN_CLIPPED) continue;  // Clipped is not a variant allele
-          const int key = akey(i, ev);
+          const int key = akey(ev);
           int c = 0, first = INT_MAX;
           bool seen_before = false;
           for (int j = e0; j < e1; ++j) {
-            const uint32_t ej = S.ev_sorted[j];
-            if (((ej >> 23) & 1) != 1 || ((ej >> 24) & 7) == GUAC_ALN_CLIPPED || akey(j, ej) != key) continue;
+            const uint2 ej = S.ev_sorted[j];
+            if (((ej.x >> 23) & 1) != 1 || ((ej.x >> 24) & 7) == GUAC_ALN_CLIPPED || akey(ej) != key) continue;
             if (j < i) seen_before = true;
             ++c;
-            first = min(first, (int)((ej >> 11) & 0xFFF));
+            first = min(first, (int)((ej.x >> 11) & 0xFFF));
           }
           if (seen_before) continue;
           // most frequent allele; ties -> lowest first supporting read (documented canonical order)
@@ -416,8 +422,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       if (simple && (best >> 8) == GUAC_ALN_INSERTION) {
         int same = 0;
         for (int j = e0; j < e1; ++j) {
-          const uint32_t ej = S.ev_sorted[j];
-          same += ((ej >> 24) & 7) == GUAC_ALN_INSERTION && akey(j, ej) == best;
+          const uint2 ej = S.ev_sorted[j];
+          same += ((ej.x >> 24) & 7) == GUAC_ALN_INSERTION && akey(ej) == best;
         }
         if (same > 1) simple = false;  // equal hashes: the exact path compares the sequences
       }
@@ -434,13 +440,13 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         int n_alt_normal = 0;
         const bool at_floor = f == P.min_vaf;
         for (int i = e0; i < e1; ++i) {
-          const uint32_t ev = S.ev_sorted[i];
-          const int eslot = (ev >> 23) & 1, kind = (ev >> 24) & 7;
-          if (kind == GUAC_ALN_CLIPPED || akey(i, ev) != best) continue;
+          const uint2 ev = S.ev_sorted[i];
+          const int eslot = (ev.x >> 23) & 1, kind = (ev.x >> 24) & 7;
+          if (kind == GUAC_ALN_CLIPPED || akey(ev) != best) continue;
           if (eslot == 0) {
             ++n_alt_normal;
           } else {
-            const int q = S.evq_sorted[i] & 0xFF;
+            const int q = (ev.y >> 31) ? (int)(ev.y & 0xFF) : (int)__ldg(R.qual + seq_base + ev.y);
             if (at_floor) {
               bound += __ldg(A.bound_tab + q);
             } else {
@@ -451,7 +457,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         }
         // a mid-deletion allele has empty alt bases and is never called (:233)
         const bool never_called = (best >> 8) == GUAC_ALN_MID_DELETION;
-        if (never_called || (S.lowq[l] == 0 && bound < (double)P.tumor_odds - 0.5)) {
+        if (never_called || ((S.aux[l] & 0xFFFF) == 0 && bound < (double)P.tumor_odds - 0.5)) {
           top_t = bcnt;
           top_n = n_alt_normal;
           flags = 1;
@@ -476,21 +482,12 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         continue;  // the heavy kernel writes this locus's summary
       }
     }
-    guac_locus_summary sn, st;
-    sn.depth = (uint16_t)min(dN, 65535);
-    sn.reference_depth = (uint16_t)min(dN - nrN, 65535);
-    sn.top_alt_count = (uint16_t)min(top_n, 65535);
-    sn.flags = (uint16_t)flags;
-    st.depth = (uint16_t)min(dT, 65535);
-    st.reference_depth = (uint16_t)min(dT - nrT, 65535);
-    st.top_alt_count = (uint16_t)min(top_t, 65535);
-    st.flags = (uint16_t)flags;
-    // one 16-byte store per locus
+    // dense summary (normal, tumor): one 16-byte store per locus
     uint4 v;
-    v.x = (uint32_t)sn.depth | ((uint32_t)sn.reference_depth << 16);
-    v.y = (uint32_t)sn.top_alt_count | ((uint32_t)sn.flags << 16);
-    v.z = (uint32_t)st.depth | ((uint32_t)st.reference_depth << 16);
-    v.w = (uint32_t)st.top_alt_count | ((uint32_t)st.flags << 16);
+    v.x = (uint32_t)min(dN, 65535) | ((uint32_t)min(dN - nrN, 65535) << 16);
+    v.y = (uint32_t)min(top_n, 65535) | ((uint32_t)flags << 16);
+    v.z = (uint32_t)min(dT, 65535) | ((uint32_t)min(dT - nrT, 65535) << 16);
+    v.w = (uint32_t)min(top_t, 65535) | ((uint32_t)flags << 16);
     reinterpret_cast<uint4*>(A.summary)[slot] = v;
   }
 }
