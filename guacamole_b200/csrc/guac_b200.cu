@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
+#include <cstdlib>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -56,7 +58,9 @@ struct guac_ctx {
   std::vector<std::pair<int32_t, std::pair<int64_t, int64_t>>> contig_spans;  // contig -> [lo, hi) read indices
   // plan / scratch
   DevBuf b_ranges, b_tiles, b_visited, b_vis_idx, b_counts, b_totals, b_elem_off, b_summary, b_calls, b_ncalls, b_err, b_arena;
-  std::set<void*> host_allocs;
+  std::map<void*, size_t> host_allocs;            // live pinned output buffers -> capacity
+  std::multimap<size_t, void*> pinned_free;        // released buffers kept for reuse
+  size_t pinned_free_bytes = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool have_timing = false;
   int64_t timed_loci = 0;
@@ -64,7 +68,7 @@ struct guac_ctx {
   int64_t opt_ss_impl = 0;            // 0 = streaming tile kernel (+ gather fallback), 1 = gather kernel only
   int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
-  DevBuf b_heavy, b_boundtab;
+  DevBuf b_heavy, b_boundtab, b_vcount;
   double bound_tab_vaf = -1;
 };
 
@@ -84,6 +88,21 @@ namespace {
     int _s = (expr);            \
     if (_s != GUAC_OK) return _s; \
   } while (0)
+
+// GUAC_TRACE=1: host-side timestamps of the phases of a call, on stderr
+struct Trace {
+  bool on;
+  std::chrono::steady_clock::time_point t0, last;
+  Trace() : on(std::getenv("GUAC_TRACE") != nullptr), t0(std::chrono::steady_clock::now()), last(t0) {}
+  void mark(const char* what) {
+    if (!on) return;
+    auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[guac trace] %-28s +%8.3f ms (total %8.3f)\n", what,
+                 std::chrono::duration<double, std::milli>(now - last).count(),
+                 std::chrono::duration<double, std::milli>(now - t0).count());
+    last = now;
+  }
+};
 
 int fail(guac_ctx* ctx, int status, const std::string& msg) {
   ctx->err = msg;
@@ -112,11 +131,30 @@ int upload(guac_ctx* ctx, DevBuf& b, const T* host, size_t n, size_t extra_elems
   return GUAC_OK;
 }
 
+// Pinned host memory for outputs comes from a per-context pool: cudaMallocHost / cudaFreeHost cost
+// about a millisecond each, more than a whole kernel pass here.
+int pinned_alloc(guac_ctx* ctx, void** out, size_t bytes) {
+  size_t want = 4096;
+  while (want < bytes) want <<= 1;
+  auto it = ctx->pinned_free.lower_bound(want);
+  if (it != ctx->pinned_free.end() && it->first <= want * 2) {
+    *out = it->second;
+    ctx->host_allocs[*out] = it->first;
+    ctx->pinned_free_bytes -= it->first;
+    ctx->pinned_free.erase(it);
+    return GUAC_OK;
+  }
+  void* h = nullptr;
+  CUDA_TRY(ctx, cudaMallocHost(&h, want));
+  ctx->host_allocs[h] = want;
+  *out = h;
+  return GUAC_OK;
+}
+
 template <class T>
 int host_out(guac_ctx* ctx, T** out, const void* dev, size_t n) {
   void* h = nullptr;
-  CUDA_TRY(ctx, cudaMallocHost(&h, std::max<size_t>(n * sizeof(T), 16)));
-  ctx->host_allocs.insert(h);
+  GUAC_TRY(pinned_alloc(ctx, &h, std::max<size_t>(n * sizeof(T), 16)));
   if (n) CUDA_TRY(ctx, cudaMemcpyAsync(h, dev, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
   *out = reinterpret_cast<T*>(h);
   return GUAC_OK;
@@ -358,12 +396,14 @@ void guac_ctx_destroy(guac_ctx* ctx) {
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
     if (kv.second.bases) cudaFree(kv.second.bases);
-  for (void* h : ctx->host_allocs) cudaFreeHost(h);
+  for (auto& kv : ctx->host_allocs) cudaFreeHost(kv.first);
+  for (auto& kv : ctx->pinned_free) cudaFreeHost(kv.second);
   if (ctx->b_nops.p) cudaFree(ctx->b_nops.p);
   if (ctx->b_rflags.p) cudaFree(ctx->b_rflags.p);
   if (ctx->b_logtab.p) cudaFree(ctx->b_logtab.p);
   if (ctx->b_fallback.p) cudaFree(ctx->b_fallback.p);
   if (ctx->b_heavy.p) cudaFree(ctx->b_heavy.p);
+  if (ctx->b_vcount.p) cudaFree(ctx->b_vcount.p);
   if (ctx->b_boundtab.p) cudaFree(ctx->b_boundtab.p);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -376,9 +416,14 @@ const char* guac_last_error(guac_ctx* ctx) { return ctx ? ctx->err.c_str() : "nu
 void guac_free(guac_ctx* ctx, void* p) {
   if (!ctx || !p) return;
   auto it = ctx->host_allocs.find(p);
-  if (it != ctx->host_allocs.end()) {
+  if (it == ctx->host_allocs.end()) return;
+  const size_t cap = it->second;
+  ctx->host_allocs.erase(it);
+  if (ctx->pinned_free_bytes + cap <= ((size_t)2 << 30)) {  // keep up to 2 GiB of pinned blocks for reuse
+    ctx->pinned_free.insert({cap, p});
+    ctx->pinned_free_bytes += cap;
+  } else {
     cudaFreeHost(p);
-    ctx->host_allocs.erase(it);
   }
 }
 
@@ -555,8 +600,7 @@ int guac_pileup_elements(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges
     GUAC_TRY(host_out(ctx, out_elements, nullptr, 0));
     int64_t zero = 0;
     void* h = nullptr;
-    CUDA_TRY(ctx, cudaMallocHost(&h, 16));
-    ctx->host_allocs.insert(h);
+    GUAC_TRY(pinned_alloc(ctx, &h, 16));
     std::memcpy(h, &zero, sizeof zero);
     *out_offsets = (int64_t*)h;
     return GUAC_OK;
@@ -610,6 +654,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
                           guac_locus_summary** out_summary, int64_t* out_n_visited) {
   if (!ctx || !params || !out_calls || !n_calls || !out_arena || !arena_len) return GUAC_E_INVALID_INPUT;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Trace trace;
   using TCfg = TileCfg<512>;
   // The streaming tile kernel serves the pileupFlatMapTwoSamples shape (sample ids {0, 1});
   // anything else, or opt_ss_impl = 1, takes the generic gather kernel.
@@ -618,6 +663,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   const bool use_tiles = ctx->opt_ss_impl == 0 && two_samples;
   Plan plan;
   GUAC_TRY(make_plan(ctx, loci, n_ranges, plan, use_tiles ? TCfg::TL : TILE_LOCI));
+  trace.mark("plan");
   *n_calls = 0;
   *arena_len = 0;
   if (out_n_visited) *out_n_visited = 0;
@@ -674,6 +720,9 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
       int* heavy_count = fb_count + 1 + plan.n_tiles;
       CUDA_TRY(ctx, cudaMemsetAsync(heavy_count, 0, sizeof(int), ctx->stream));
+      GUAC_TRY(ensure(ctx, ctx->b_vcount, sizeof(unsigned long long)));
+      unsigned long long* visited_count = ctx->b_vcount.as<unsigned long long>();
+      CUDA_TRY(ctx, cudaMemsetAsync(visited_count, 0, sizeof(unsigned long long), ctx->stream));
       TileArgs TA;
       TA.rflags = ctx->b_rflags.as<uint8_t>();
       TA.refs = ctx->d_refs.as<RefView>();
@@ -687,6 +736,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       TA.fallback_tiles = fb_list;
       TA.n_fallback = fb_count;
       TA.force_fallback_mod = (int)ctx->opt_force_fallback_mod;
+      TA.n_visited = visited_count;
       TA.err = ctx->b_err.as<DeviceError>();
       cudaEventRecord(ctx->ev0, ctx->stream);
       ss_tile_kernel<TCfg><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
@@ -711,7 +761,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         somatic_standard_kernel<<<blocks_for(n_heavy, WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
             ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, n_heavy, 1, P, ctx->b_visited.as<uint8_t>(),
             ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
-            ctx->b_err.as<DeviceError>());
+            nullptr, ctx->b_err.as<DeviceError>());
         ctx->launches += 1;
         CUDA_TRY(ctx, cudaGetLastError());
       }
@@ -719,7 +769,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         somatic_standard_kernel<<<(unsigned)n_fb, CTA_THREADS, 0, ctx->stream>>>(
             ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, n_fb, 0, P, ctx->b_visited.as<uint8_t>(),
             ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
-            ctx->b_err.as<DeviceError>());
+            visited_count, ctx->b_err.as<DeviceError>());
         ctx->launches += 1;
         CUDA_TRY(ctx, cudaGetLastError());
       }
@@ -729,11 +779,12 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
           ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), nullptr, (int)plan.n_tiles, 0, P,
           ctx->b_visited.as<uint8_t>(), ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(),
-          ctx->b_ncalls.as<int>(), max_calls, ctx->b_err.as<DeviceError>());
+          ctx->b_ncalls.as<int>(), max_calls, nullptr, ctx->b_err.as<DeviceError>());
       cudaEventRecord(ctx->ev1, ctx->stream);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
     }
+    trace.mark("per-locus kernels launched");
     ctx->have_timing = true;
     ctx->timed_loci = plan.n_slots;
     CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
@@ -741,6 +792,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     if (nc <= max_calls) break;
     max_calls = nc;  // rerun with room for every call
   }
+  trace.mark("per-locus kernels done");
   // sparse part: sort by slot (= range order, locus), lay out the allele arena, compute the evidence
   std::vector<SSCallDev> calls((size_t)nc);
   if (nc > 0) {
@@ -768,9 +820,9 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     CUDA_TRY(ctx, cudaMemcpyAsync(calls.data(), ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
     GUAC_TRY(check_device_error(ctx));
   }
+  trace.mark("evidence");
   void* h = nullptr;
-  CUDA_TRY(ctx, cudaMallocHost(&h, std::max<size_t>((size_t)nc * sizeof(guac_ss_call), 16)));
-  ctx->host_allocs.insert(h);
+  GUAC_TRY(pinned_alloc(ctx, &h, std::max<size_t>((size_t)nc * sizeof(guac_ss_call), 16)));
   guac_ss_call* oc = (guac_ss_call*)h;
   for (int i = 0; i < nc; ++i) {
     const SSCallDev& c = calls[i];
@@ -794,10 +846,16 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   *out_calls = oc;
   *n_calls = nc;
   GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)*arena_len));
+  trace.mark("calls out");
   int64_t nv = 0;
-  if (out_summary || out_n_visited) {
+  if (out_summary || (out_n_visited && !use_tiles)) {
     GUAC_TRY(compact_visited(ctx, plan, 1, nv));
     if (out_n_visited) *out_n_visited = nv;
+  } else if (out_n_visited) {  // counted by the tile kernel itself
+    unsigned long long v = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&v, ctx->b_vcount.p, sizeof v, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    *out_n_visited = (int64_t)v;
   }
   if (out_summary) {
     DevBuf os;
@@ -814,6 +872,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     if (st != GUAC_OK) return st;
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  trace.mark("visited / summary");
   return GUAC_OK;
 }
 

@@ -258,7 +258,8 @@ somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Til
                         const int* __restrict__ tile_list /* nullptr: identity */, int n_tiles,
                         int tile_per_warp /* 0: the CTA's warps share tile blockIdx.x; 1: one (single-locus) tile per warp */,
                         SSParamsDev P, uint8_t* __restrict__ visited, guac_locus_summary* __restrict__ summary,
-                        SSCallDev* __restrict__ calls, int* __restrict__ n_calls, int max_calls, DeviceError* err) {
+                        SSCallDev* __restrict__ calls, int* __restrict__ n_calls, int max_calls,
+                        unsigned long long* __restrict__ n_visited /* optional */, DeviceError* err) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tsel = tile_per_warp ? (int)blockIdx.x * WARPS_PER_CTA + warp : (int)blockIdx.x;
   if (tsel >= n_tiles) return;  // no block-wide barrier below
@@ -335,7 +336,10 @@ somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Til
     // early outs (SomaticStandardCaller.scala:164-172)
     const bool candidate = depthT > 0 && depthN > 0 && depthT <= P.max_read_depth && depthN <= P.max_read_depth &&
                            refT != depthT && (depthN - refN) <= P.max_normal_alt;
-    if (lane == 0) visited[slot] = any ? 1 : 0;
+    if (lane == 0) {
+      visited[slot] = any ? 1 : 0;
+      if (any && n_visited) atomicAdd(n_visited, 1ull);
+    }
     if (candidate && ntab == 0) {
       if (lane == 0) report_error(err, DERR_EMPTY_MAXBY, tile.contig_id, x, -1);
     }
@@ -423,6 +427,23 @@ somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Til
 __device__ inline int count_of_mismatches(const ReadsView& R, int64_t r, const RefView& ref, DeviceError* err, int contig) {
   const int64_t s = __ldg(R.start + r), en = __ldg(R.end + r);
   int n = 0;
+  const uint32_t c0 = __ldg(R.cigar_off + r), c1 = __ldg(R.cigar_off + r + 1);
+  if (c1 - c0 == 1) {  // a single aligned operator: every element is a Match or a Mismatch
+    const uint32_t w = __ldg(R.cigar + c0);
+    const int op = w & 15;
+    if (op == OPC_M || op == OPC_EQ || op == OPC_X) {
+      const uint64_t s0 = __ldg(R.seq_off + r);
+      for (int64_t x = s; x < en; ++x) {
+        const uint8_t rb = ref.at(x);
+        if (rb == 0) {
+          report_error(err, DERR_REF_MISSING, contig, x, r);
+          return n;
+        }
+        n += read_base(R, s0 + (uint64_t)(x - s)) != rb;
+      }
+      return n;
+    }
+  }
   for (int64_t x = s; x < en; ++x) {
     Elem e;
     int ec = element_at(R, r, x, ref, e);

@@ -131,6 +131,7 @@ struct TileArgs {
   int* fallback_tiles;
   int* n_fallback;
   int force_fallback_mod;
+  unsigned long long* n_visited;  // loci with at least one read in either sample
   DeviceError* err;
 };
 
@@ -370,12 +371,14 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   __syncthreads();
 
   // ---- C. one thread per locus ------------------------------------------------------------------
+  int my_visited = 0;
   for (int l = tid; l < n_loci; l += CFG::THREADS) {
     const int cv = S.cov[l], nr = S.nonref[l];
     const int dN = cv & 0xFFFF, dT = cv >> 16;
     const int nrN = nr & 0xFFFF, nrT = nr >> 16;
     const int64_t slot = tile.slot0 + l, x = t0 + l;
     A.visited[slot] = dN + dT > 0 ? 1 : 0;
+    my_visited += dN + dT > 0;
     if (dN + dT > 0 && ref.at(x) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x, -1);
     // early-outs (SomaticStandardCaller.scala:164-172)
     const bool candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
@@ -490,6 +493,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     v.w = (uint32_t)min(top_t, 65535) | ((uint32_t)flags << 16);
     reinterpret_cast<uint4*>(A.summary)[slot] = v;
   }
+  my_visited = __reduce_add_sync(FULL, my_visited);
+  if (lane == 0 && my_visited) atomicAdd(A.n_visited, (unsigned long long)my_visited);
 }
 
 }  // namespace guac
