@@ -549,7 +549,14 @@ void pileupFlatMapMultipleSamples(const std::vector<MappedRead>& reads, int numS
     const ContigSequence* cs = nullptr;
     for (auto& c : reference)
       if (c.contig_id == contig) cs = &c;
-    if (!cs) throw InvalidInput("contig " + std::to_string(contig) + " not found in reference");
+    if (!cs) {
+      // reference.getContig is only reached from the per-locus closure (PileupFlatMapUtils.scala:60,93):
+      // a contig without reads is never visited when skipEmpty, so its absence goes unnoticed.
+      bool anyRead = false;
+      for (auto& r : reads) anyRead = anyRead || r.contig == contig;
+      if (skipEmpty && !anyRead) continue;
+      throw InvalidInput("contig " + std::to_string(contig) + " not found in reference");
+    }
     // SplitIterator.split by sampleId + RegionsByContig (WindowFlatMapUtils.scala:93-106,128-135)
     std::vector<std::vector<const MappedRead*>> perSample(numSamples);
     int64_t lastStart = 0;
