@@ -243,8 +243,14 @@ def main():
     k_ms = sum(kernel_ms) / len(kernel_ms)
     abytes = algorithmic_bytes_per_locus(sum(DEPTHS), len(DEPTHS))
     achieved = abytes * loci_step / (k_ms / 1000.0) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": "somatic_standard_kernel", "kernel_ms": k_ms, "algorithmic_bytes_per_locus": abytes,
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    if os.path.exists(tpath) and args.contig_mbp == 50:
+        tj = json.load(open(tpath))
+        traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": traffic_src, "kernel": "ss_tile_kernel<TileCfg<512>> (+ heavy-locus gather kernel)",
+                "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes * loci_step, "algorithmic_bytes_per_locus": abytes,
                 "peak_source": peak_src}
 
     # end to end: pinned host buffers -> guac_reads_upload -> guac_somatic_standard -> call records on host

@@ -92,6 +92,9 @@ __device__ __forceinline__ uint32_t load_bits32_s(const uint32_t* words, int bit
   return __funnelshift_r(words[bit >> 5], words[(bit >> 5) + 1], bit & 31);
 }
 
+// kept out of line so that the (rare) masked-reference case is a real branch, not predicated code in the hot loop
+__device__ __noinline__ uint32_t ref_mask_bits(const uint32_t* refmask, int l) { return spread16(load_bits32_s(refmask, l)); }
+
 // event word: [0,11) locus in tile | [11,23) read in tile | 23 sample slot | [24,27) kind | [27,30) code
 //   code: Mismatch -> base code (4 = not ACGT); other kinds -> 4 = allele identified by the detail byte,
 //         5 = allele must be resolved by the exact path
@@ -222,12 +225,23 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     // aligned segment: loci [lb, le) (tile coordinates, unclipped) hold read positions rp0..; 16 bases per step
     auto compare_segment = [&](int lb, int le, int rp0) {
       const int ca = max(lb, 0), cb = min(le, n_loci);
-      for (int l = ca; l < cb; l += 16) {
-        const int k = rp0 + (l - lb);
-        const uint32_t rd = load_bits32_g(R.bases2, 2 * (s0 + (uint64_t)k));
-        const uint32_t x = rd ^ load_bits32_s(S.ref2, 2 * l);
+      if (ca >= cb) return;
+      // both streams advance by exactly one 32-bit word per step, so the shifts are loop invariant and
+      // each step loads one new word per stream
+      const uint64_t rbit = 2 * (s0 + (uint64_t)(rp0 + (ca - lb)));
+      const uint32_t* rw = reinterpret_cast<const uint32_t*>(R.bases2) + (rbit >> 5);
+      const int rsh = (int)(rbit & 31), fsh = (2 * ca) & 31;
+      const uint32_t* fw = S.ref2 + ((2 * ca) >> 5);
+      uint32_t rlo = __ldg(rw), flo = fw[0];
+      int k = rp0 + (ca - lb);
+      for (int l = ca; l < cb; l += 16, k += 16) {
+        const uint32_t rhi = __ldg(++rw), fhi = *++fw;
+        const uint32_t rd = __funnelshift_r(rlo, rhi, rsh);
+        const uint32_t x = rd ^ __funnelshift_r(flo, fhi, fsh);
+        rlo = rhi;
+        flo = fhi;
         uint32_t m = (x | (x >> 1)) & 0x55555555u;
-        if (ref_has_mask) m |= spread16(load_bits32_s(S.refmask, l));  // a not-ACGT reference base never equals an ACGT read base
+        if (ref_has_mask) m |= ref_mask_bits(S.refmask, l);  // a not-ACGT reference base never equals an ACGT read base
         if (cb - l < 16) m &= (1u << (2 * (cb - l))) - 1;
         while (m) {
           const int bit = __ffs(m) - 1;
