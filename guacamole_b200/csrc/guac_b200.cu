@@ -506,6 +506,8 @@ int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* b) {
   if (n < 0 || b->n_samples <= 0 || b->n_samples > 255) return fail(ctx, GUAC_E_INVALID_INPUT, "bad read batch header");
   // Host-side validation of the ordering contract (SlidingWindow.scala:36-37 "Regions must be sorted by start locus";
   // RegionsByContig.scala:22 "Regions are not sorted by contig") and the per-contig spans.
+  // It runs on the host while the asynchronous H2D copies below are in flight.
+  auto validate = [&]() -> int {
   ctx->contig_spans.clear();
   for (int64_t i = 0; i < n; ++i) {
     if (i == 0 || b->contig_id[i] != b->contig_id[i - 1]) {
@@ -520,6 +522,8 @@ int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* b) {
     if (b->sample_id[i] >= b->n_samples) return fail(ctx, GUAC_E_INVALID_INPUT, "sample_id >= n_samples");
     if (b->start[i] < 0 || b->start[i] >= ((int64_t)1 << 39)) return fail(ctx, GUAC_E_INVALID_INPUT, "read start out of range");
   }
+  return GUAC_OK;
+  };
   const uint64_t n_bases = n ? b->seq_off[n] : 0;
   const uint32_t n_cigar = n ? b->cigar_off[n] : 0;
   GUAC_TRY(upload(ctx, ctx->b_start, b->start, (size_t)n));
@@ -535,6 +539,11 @@ int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* b) {
   GUAC_TRY(upload(ctx, ctx->b_mapq, b->mapq, (size_t)n));
   GUAC_TRY(upload(ctx, ctx->b_flags, b->flags, (size_t)n));
   GUAC_TRY(upload(ctx, ctx->b_sample, b->sample_id, (size_t)n));
+  const int vst = validate();
+  if (vst != GUAC_OK) {
+    cudaStreamSynchronize(ctx->stream);
+    return vst;
+  }
   return finish_reads(ctx, n, b->n_samples, b->n_exc);
 }
 
