@@ -1031,3 +1031,166 @@ int guac_ref_export(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t le
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// guac_pileup_counts_noalloc — the counting closure for callers that must not allocate.
+//
+// Some hosts of this library may not call cudaMalloc at the moment they need a pileup: a plugin
+// running inside an executor whose whole device memory is owned by the host framework's pool
+// allocator (an allocation behind its back fails or fragments the pool), or code that is already
+// between cudaStreamBeginCapture and cudaStreamEndCapture, where allocating is not allowed.  For
+// them this entry point does the work of guac_pileup_counts (dense, skip_empty = 0, one range of
+// one contig) with every byte of working memory taken from the fixed array below; inputs and the
+// output are device buffers the caller already owns.
+//
+// The working memory holds the per-read end loci, the running maximum used to find a tile's first
+// read, the scan's partial totals, the tile descriptors, the visited flags, the one-entry reference
+// table, the range record and the device error record.  It is ONE array per device, shared by
+// every call: it keeps the previous call's contents (everything that must start from zero is
+// cleared by the call itself), and two calls whose GPU work overlaps — different streams or
+// different host threads — would race on it.  Every GPU that loads the library holds the array
+// (NOALLOC_SCRATCH_BYTES, about 3.9 MiB) until the process exits.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int64_t NOALLOC_MAX_READS = 1 << 17;  // 131 072 reads per call
+constexpr int64_t NOALLOC_MAX_LOCI = 1 << 19;   // 524 288 loci per call
+constexpr int64_t NOALLOC_MAX_TILES = NOALLOC_MAX_LOCI / TILE_LOCI;
+constexpr int64_t NOALLOC_SCAN_TILES = NOALLOC_MAX_READS / SCAN_TILE + 2;
+
+struct NoAllocScratch {
+  int64_t end[NOALLOC_MAX_READS];
+  int64_t key[NOALLOC_MAX_READS];
+  int64_t runmax[NOALLOC_MAX_READS];
+  int64_t scan_totals[NOALLOC_SCAN_TILES];
+  Tile tiles[NOALLOC_MAX_TILES];
+  uint8_t visited[NOALLOC_MAX_LOCI];
+  RefView ref;
+  RangeDev range;
+  DeviceError err;
+};
+constexpr size_t NOALLOC_SCRATCH_BYTES = sizeof(NoAllocScratch);
+
+// File-scope device array.  In host code this name is only a stand-in for the symbol: its device
+// address is obtained once per device with cudaGetSymbolAddress (below) and passed to the kernels.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+NoAllocScratch* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+thread_local std::string g_noalloc_error;
+
+int noalloc_fail(int status, const std::string& msg) {
+  g_noalloc_error = msg;
+  return status;
+}
+
+#define NA_CUDA(expr)                                                                                     \
+  do {                                                                                                    \
+    cudaError_t _e = (expr);                                                                              \
+    if (_e != cudaSuccess) return noalloc_fail(GUAC_E_CUDA, std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " #expr); \
+  } while (0)
+
+}  // namespace
+
+extern "C" {
+
+const char* guac_noalloc_last_error(void) { return g_noalloc_error.c_str(); }
+
+int64_t guac_noalloc_max_reads(void) { return NOALLOC_MAX_READS; }
+int64_t guac_noalloc_max_loci(void) { return NOALLOC_MAX_LOCI; }
+
+int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const uint8_t* d_ref_bases, int64_t ref_offset,
+                               int64_t ref_len, int32_t contig_id, int64_t range_start, int64_t range_end,
+                               guac_locus_counts* d_out_counts, void* stream_handle) {
+  if (!d_batch || !d_ref_bases || !d_out_counts) return noalloc_fail(GUAC_E_INVALID_INPUT, "null argument");
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) return noalloc_fail(GUAC_E_INVALID_INPUT, "device index out of range");
+  const int64_t n = d_batch->n_reads, n_loci = range_end - range_start;
+  const int S = d_batch->n_samples;
+  if (n < 0 || S <= 0 || S > 255 || range_start < 0 || n_loci < 0 || contig_id < 0 || contig_id >= (1 << 22))
+    return noalloc_fail(GUAC_E_INVALID_INPUT, "bad read batch header or loci range");
+  if (n > NOALLOC_MAX_READS)
+    return noalloc_fail(GUAC_E_UNSUPPORTED, "guac_pileup_counts_noalloc: " + std::to_string(n) + " reads exceed the fixed working memory (" +
+                                                std::to_string(NOALLOC_MAX_READS) + " reads per call); split the batch or use guac_pileup_counts");
+  if (n_loci > NOALLOC_MAX_LOCI)
+    return noalloc_fail(GUAC_E_UNSUPPORTED, "guac_pileup_counts_noalloc: " + std::to_string(n_loci) + " loci exceed the fixed working memory (" +
+                                                std::to_string(NOALLOC_MAX_LOCI) + " loci per call); split the range or use guac_pileup_counts");
+  NA_CUDA(cudaSetDevice(device));
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_handle);
+  // Set-up, once per device and with that device current: resolve the symbol to its device address.
+  // (The first call on a device therefore does a little extra work; make it before any stream capture.)
+  if (g_noalloc_ptr[device] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return noalloc_fail(GUAC_E_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_scratch) failed: ") + cudaGetErrorString(e));
+    g_noalloc_ptr[device] = reinterpret_cast<NoAllocScratch*>(p);
+  }
+  NoAllocScratch* W = g_noalloc_ptr[device];
+  if (n_loci == 0) return GUAC_OK;
+
+  // everything that must start from zero: the caller's output (the kernel accumulates with atomics)
+  // and the error record; stale ends / tiles / flags of earlier calls are overwritten before use.
+  NA_CUDA(cudaMemsetAsync(d_out_counts, 0, (size_t)n_loci * S * sizeof(guac_locus_counts), stream));
+  NA_CUDA(cudaMemsetAsync(&W->err, 0, sizeof(DeviceError), stream));
+
+  ReadsView R;
+  R.n_reads = n;
+  R.start = d_batch->start;
+  R.end = W->end;
+  R.runmax_key = W->runmax;
+  R.cigar_off = d_batch->cigar_off;
+  R.cigar = d_batch->cigar;
+  R.seq_off = d_batch->seq_off;
+  R.bases2 = d_batch->bases2;
+  R.nmask = d_batch->nmask;
+  R.n_exc = d_batch->n_exc;
+  R.exc_pos = d_batch->exc_pos;
+  R.exc_base = d_batch->exc_base;
+  R.qual = d_batch->qual;
+  R.mapq = d_batch->mapq;
+  R.flags = d_batch->flags;
+  R.sample_id = d_batch->sample_id;
+  if (n > 0) {
+    read_ends_kernel<<<blocks_for(n, 256), 256, 0, stream>>>(n, d_batch->start, d_batch->contig_id, d_batch->cigar_off, d_batch->cigar,
+                                                            W->end, W->key);
+    const int64_t scan_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    scan_reduce_kernel<int64_t, int64_t, OpMax><<<(unsigned)scan_tiles, SCAN_THREADS, 0, stream>>>(W->key, W->scan_totals, n, OpMax());
+    scan_totals_kernel<int64_t, OpMax><<<1, SCAN_THREADS, 0, stream>>>(W->scan_totals, scan_tiles, OpMax());
+    scan_apply_kernel<false, int64_t, int64_t, OpMax><<<(unsigned)scan_tiles, SCAN_THREADS, 0, stream>>>(W->key, W->runmax,
+                                                                                                       W->scan_totals, n, OpMax());
+  }
+  RefView ref;
+  ref.bases = d_ref_bases;
+  ref.offset = ref_offset;
+  ref.len = ref_len;
+  RangeDev rg;
+  rg.start = range_start;
+  rg.end = range_end;
+  rg.slot0 = 0;
+  rg.tile0 = 0;
+  rg.read_clo = 0;
+  rg.read_chi = n;  // the batch holds one contig
+  rg.contig_id = contig_id;
+  rg.ref_index = 0;
+  NA_CUDA(cudaMemcpyAsync(&W->ref, &ref, sizeof ref, cudaMemcpyHostToDevice, stream));
+  NA_CUDA(cudaMemcpyAsync(&W->range, &rg, sizeof rg, cudaMemcpyHostToDevice, stream));
+  NA_CUDA(cudaStreamSynchronize(stream));  // `ref` and `rg` live on this stack frame
+  const int64_t n_tiles = (n_loci + TILE_LOCI - 1) / TILE_LOCI;
+  build_tiles_kernel<<<blocks_for(n_tiles, 256), 256, 0, stream>>>(&W->range, 1, n_tiles, TILE_LOCI, R, W->tiles);
+  pileup_counts_kernel<<<(unsigned)n_tiles, CTA_THREADS, 0, stream>>>(R, &W->ref, W->tiles, S, W->visited, d_out_counts, &W->err);
+  NA_CUDA(cudaGetLastError());
+  DeviceError err;
+  NA_CUDA(cudaMemcpyAsync(&err, &W->err, sizeof err, cudaMemcpyDeviceToHost, stream));
+  NA_CUDA(cudaStreamSynchronize(stream));
+  if (err.code != DERR_NONE) {
+    char buf[192];
+    if (err.code == DERR_REF_MISSING)
+      snprintf(buf, sizeof buf, "Position %d:%lld missing from reference", err.contig_id, err.locus);
+    else
+      snprintf(buf, sizeof buf, "invalid CIGAR / element (device error %d) for read %lld at locus %lld", err.code, err.read_index, err.locus);
+    return noalloc_fail(GUAC_E_INVALID_INPUT, buf);
+  }
+  return GUAC_OK;
+}
+
+}  // extern "C"
