@@ -271,6 +271,72 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
                           guac_ss_call** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
                           guac_locus_summary** out_summary, int64_t* out_n_visited);
 
+/* ---- somatic-joint ----------------------------------------------------------
+ * M/jointcaller/Parameters.scala:10-25 plus the inputs (M/jointcaller/Input.scala, InputCollection.scala:55-101)
+ * and the flags of M/commands/SomaticJointCaller.scala:154-163. */
+enum { GUAC_SJ_NORMAL_DNA = 0, GUAC_SJ_TUMOR_DNA = 1, GUAC_SJ_TUMOR_RNA = 2 };
+#define GUAC_SJ_MAX_SAMPLES 16
+#define GUAC_SJ_MAX_DEPTH_ENTRIES 8
+typedef struct {
+  int32_t n_samples;                          /* = n_samples of the uploaded batch */
+  int32_t sample_kind[GUAC_SJ_MAX_SAMPLES];   /* GUAC_SJ_* per sample id (tissue type x analyte) */
+  int32_t max_alleles_per_site;               /* 4 (<= GUAC_SJ_MAX_DEPTH_ENTRIES - 1) */
+  int32_t any_allele_min_supporting_reads;    /* 2 */
+  double any_allele_min_supporting_percent;   /* 2.0 */
+  double germline_neg_log10_het_prior;        /* 4 */
+  double germline_neg_log10_hom_alt_prior;    /* 5 */
+  double somatic_neg_log10_variant_prior;     /* 6 */
+  double somatic_neg_log10_variant_prior_rna; /* 1 */
+  double somatic_neg_log10_variant_prior_with_rna_evidence; /* 1 */
+  double somatic_vaf_floor;                   /* 0.05 */
+  double filter_strand_bias_phred;            /* 60 */
+  double filter_somatic_normal_nonreference_percent; /* 3.0 */
+  int32_t filter_somatic_normal_depth;        /* 30 */
+  int32_t only_somatic;
+  int32_t include_filtered;
+  int32_t _pad;
+} guac_sj_params;
+
+typedef struct {
+  uint32_t seq_off, seq_len; /* allele string in the arena */
+  int32_t count;
+  int32_t _pad;
+} guac_sj_depth_entry;
+
+/* One SingleSampleSingleAlleleEvidence (M/jointcaller/evidence/{NormalDNA,TumorDNA,TumorRNA}SingleSampleSingleAlleleEvidence.scala)
+ * with its annotations (M/jointcaller/annotation/StrandBias.scala:22-58). */
+typedef struct {
+  int32_t kind;              /* GUAC_SJ_* */
+  int32_t total_depth;       /* PileupStats.totalDepthIncludingReadsContributingNoAlleles */
+  int32_t n_depths;          /* truncatedAllelicDepths(maxAllelesPerSite + 1), most frequent first */
+  int32_t n_likelihoods;     /* 3 for normal DNA: ref/ref, ref/alt, alt/alt; 2 for tumor: {ref}, {alt: vaf, ref: 1 - vaf} */
+  guac_sj_depth_entry depths[GUAC_SJ_MAX_DEPTH_ENTRIES];
+  double log_likelihoods[3]; /* log10 */
+  double posteriors[3];      /* likelihood - prior */
+  double alt_vaf;            /* tumor: max(somaticVafFloor, vaf(alt)) */
+  int32_t sb_variant_forward, sb_variant_reverse, sb_total_forward, sb_total_reverse;
+  double sb_phred;
+  int32_t sb_filtered;
+  int32_t triggered;         /* tumor DNA: sample triggered the call; tumor RNA: expressed */
+} guac_sj_sample_evidence;
+
+/* One MultiSampleSingleAlleleEvidence (M/jointcaller/evidence/MultiSampleSingleAlleleEvidence.scala:24-342).
+ * Its per-sample evidences are sample_evidence[first_sample_evidence .. + n_samples + 2):
+ * the samples in order, then pooled normal DNA, then pooled tumor DNA. */
+typedef struct {
+  int32_t contig_id;
+  int32_t site_index;        /* evidences of one MultiSampleMultiAlleleEvidence share it */
+  int64_t start;             /* allele.start (0-based) = pileup locus + 1 */
+  uint32_t ref_off, ref_len, alt_off, alt_len;
+  int32_t is_germline_call, is_somatic_call;
+  int32_t germline_genotype; /* argmax of the pooled germline posteriors: 0 ref/ref, 1 ref/alt, 2 alt/alt */
+  int32_t tumor_rna_expressed;
+  int32_t has_insufficient_normal, in_reference_reads, in_total_reads, in_filtered;
+  uint32_t failing_filters;  /* bit 0 STRAND_BIAS, bit 1 INSUFFICIENT_NORMAL */
+  int32_t forced;            /* site was force-called */
+  int64_t first_sample_evidence;
+} guac_sj_allele_evidence;
+
 /* ---- measurement support ----------------------------------------------------
  * These have no counterpart in the reference: they exist so that bench.py and the
  * tests can generate SURVEY.md 8(d)'s seeded synthetic reads directly in HBM, read them

@@ -507,3 +507,199 @@ extern "C" void oracle_synth_reference(uint64_t seed, int64_t lo, int64_t hi, ui
   using namespace guac::synth;
   for (int64_t i = lo; i < hi; ++i) out[i - lo] = (uint8_t)"ACGT"[rnd_k(stream_key(seed, S_REF), (uint64_t)i) & 3];
 }
+
+// ---------------------------------------------------------------------------------
+// somatic-joint: SomaticJoint.makeCalls (M/commands/SomaticJointCaller.scala:143-203) over one partition.
+// `loci` are the caller's loci (the function applies lociSetMinusOne itself); a site is force-called
+// when pileup locus + 1 lies in `force_loci`.
+// ---------------------------------------------------------------------------------
+#include "guac_oracle_joint.hpp"
+
+extern "C" int oracle_somatic_joint(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, const guac_sj_params* params,
+                                    const guac_range* loci, int n_loci, const guac_range* force_loci, int n_force,
+                                    guac_sj_allele_evidence** out_alleles, int64_t* n_alleles, guac_sj_sample_evidence** out_samples,
+                                    int64_t* n_samples_out, char** out_arena, int64_t* arena_len, int64_t* out_n_visited) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    JointParameters P;
+    for (int s = 0; s < params->n_samples; ++s) P.sampleKind.push_back(params->sample_kind[s]);
+    P.maxAllelesPerSite = params->max_alleles_per_site;
+    P.anyAlleleMinSupportingReads = params->any_allele_min_supporting_reads;
+    P.anyAlleleMinSupportingPercent = params->any_allele_min_supporting_percent;
+    P.germlineNegativeLog10HeterozygousPrior = params->germline_neg_log10_het_prior;
+    P.germlineNegativeLog10HomozygousAlternatePrior = params->germline_neg_log10_hom_alt_prior;
+    P.somaticNegativeLog10VariantPrior = params->somatic_neg_log10_variant_prior;
+    P.somaticNegativeLog10VariantPriorRna = params->somatic_neg_log10_variant_prior_rna;
+    P.somaticNegativeLog10VariantPriorWithRnaEvidence = params->somatic_neg_log10_variant_prior_with_rna_evidence;
+    P.somaticVafFloor = params->somatic_vaf_floor;
+    P.filterStrandBiasPhred = params->filter_strand_bias_phred;
+    P.filterSomaticNormalNonreferencePercent = params->filter_somatic_normal_nonreference_percent;
+    P.filterSomaticNormalDepth = params->filter_somatic_normal_depth;
+    P.onlySomatic = params->only_somatic != 0;
+    P.includeFiltered = params->include_filtered != 0;
+    // lociSetMinusOne (SomaticJointCaller.scala:143-152)
+    std::vector<Range> shifted;
+    for (int i = 0; i < n_loci; ++i) {
+      Range r{loci[i].contig_id, std::max<int64_t>(0, loci[i].start - 1), loci[i].end - 1};
+      if (r.end > r.start) shifted.push_back(r);
+    }
+    std::vector<guac_sj_allele_evidence> alleles;
+    std::vector<guac_sj_sample_evidence> samples;
+    std::string arena;
+    int64_t visited = 0;
+    int site = 0;
+    auto intern = [&](const std::string& s, uint32_t& off, uint32_t& len) {
+      off = (uint32_t)arena.size();
+      len = (uint32_t)s.size();
+      arena += s;
+    };
+    pileupFlatMapMultipleSamples(reads, params->n_samples, shifted, cs, true, [&](const std::vector<Pileup>& pileups) {
+      ++visited;
+      const int64_t locus = pileups[0].locus;
+      bool forceCall = false;
+      for (int i = 0; i < n_force; ++i)
+        forceCall = forceCall || (force_loci[i].contig_id == pileups[0].contig && force_loci[i].start <= locus + 1 && locus + 1 < force_loci[i].end);
+      auto evs = makeMultiAlleleEvidence(pileups, P, forceCall);
+      if (evs.empty()) return;
+      for (auto& e : evs) {
+        guac_sj_allele_evidence a;
+        std::memset(&a, 0, sizeof a);
+        a.contig_id = e.allele.contig;
+        a.site_index = site;
+        a.start = e.allele.start;
+        intern(e.allele.ref, a.ref_off, a.ref_len);
+        intern(e.allele.alt, a.alt_off, a.alt_len);
+        a.is_germline_call = e.isGermlineCall;
+        a.is_somatic_call = e.isSomaticCall;
+        a.germline_genotype = e.germlineGenotype;
+        a.tumor_rna_expressed = e.tumorRnaExpressed;
+        a.has_insufficient_normal = e.hasInsufficientNormal;
+        a.in_reference_reads = e.inReferenceReads;
+        a.in_total_reads = e.inTotalReads;
+        a.in_filtered = e.inFiltered;
+        a.failing_filters = e.failingFilters;
+        a.forced = forceCall;
+        a.first_sample_evidence = (int64_t)samples.size();
+        for (auto& se : e.samples) {
+          guac_sj_sample_evidence g;
+          std::memset(&g, 0, sizeof g);
+          g.kind = se.kind;
+          g.total_depth = se.totalDepth;
+          g.n_depths = (int)se.allelicDepths.size();
+          for (int k = 0; k < g.n_depths; ++k) {
+            intern(se.allelicDepths[k].allele, g.depths[k].seq_off, g.depths[k].seq_len);
+            g.depths[k].count = se.allelicDepths[k].count;
+          }
+          g.n_likelihoods = (int)se.logLikelihoods.size();
+          for (int k = 0; k < g.n_likelihoods; ++k) {
+            g.log_likelihoods[k] = se.logLikelihoods[k];
+            g.posteriors[k] = k < (int)se.posteriors.size() ? se.posteriors[k] : NAN;
+          }
+          g.alt_vaf = se.altVaf;
+          g.sb_variant_forward = se.sbVariantForward;
+          g.sb_variant_reverse = se.sbVariantReverse;
+          g.sb_total_forward = se.sbTotalForward;
+          g.sb_total_reverse = se.sbTotalReverse;
+          g.sb_phred = se.sbPhred;
+          g.sb_filtered = se.sbFiltered;
+          g.triggered = se.triggered;
+          samples.push_back(g);
+        }
+        alleles.push_back(a);
+      }
+      ++site;
+    });
+    *out_alleles = toC(alleles);
+    *n_alleles = (int64_t)alleles.size();
+    *out_samples = toC(samples);
+    *n_samples_out = (int64_t)samples.size();
+    *out_arena = (char*)std::malloc(arena.size() + 1);
+    std::memcpy(*out_arena, arena.c_str(), arena.size() + 1);
+    *arena_len = (int64_t)arena.size();
+    if (out_n_visited) *out_n_visited = visited;
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// ReadSubsequence / PileupStats probes for the unit vectors of ReadSubsequenceSuite and PileupStatsSuite:
+// text lines "kind\tsequence\tstartLocus\tendLocus" per element of `sample` at `locus`
+// (kind F = ofFixedReferenceLength(length), A = ofNextAltAllele; "-" when None).
+extern "C" int oracle_read_subsequences(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, int32_t contig,
+                                        int64_t locus, int sample, int length, char** out_text) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    const ContigSequence* c = nullptr;
+    for (auto& x : cs)
+      if (x.contig_id == contig) c = &x;
+    if (!c) throw InvalidInput("contig not found");
+    std::string text;
+    for (auto& r : reads)
+      if (r.contig == contig && r.sampleId == sample && r.overlapsLocus(locus)) {
+        PileupElement pe = PileupElement::make(r, locus, *c);
+        ReadSubsequence s;
+        if (ofFixedReferenceLength(pe, length, &s))
+          text += "F\t" + s.sequence() + "\t" + std::to_string(s.startLocus) + "\t" + std::to_string(s.endLocus) + "\n";
+        else
+          text += "F\t-\t0\t0\n";
+        if (ofNextAltAllele(pe, &s))
+          text += "A\t" + s.sequence() + "\t" + std::to_string(s.startLocus) + "\t" + std::to_string(s.endLocus) + "\n";
+        else
+          text += "A\t-\t0\t0\n";
+      }
+    *out_text = (char*)std::malloc(text.size() + 1);
+    std::memcpy(*out_text, text.c_str(), text.size() + 1);
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// PileupStats over the elements of `sample` at `locus` with reference sequence `ref_seq`:
+// allelic depths as "allele=count" lines, then "LL\t<value>" per requested mixture
+// (mixtures: NUL-separated "allele\0" keys + fractions, n_keys[m] keys each).
+extern "C" int oracle_pileup_stats(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, int32_t contig, int64_t locus,
+                                   int sample, const char* ref_seq, int n_mixtures, const int32_t* n_keys, const char* keys_text,
+                                   const double* fractions, char** out_text) {
+  try {
+    auto reads = buildReads(b);
+    auto cs = buildContigs(contigs, n_contigs);
+    const ContigSequence* c = nullptr;
+    for (auto& x : cs)
+      if (x.contig_id == contig) c = &x;
+    if (!c) throw InvalidInput("contig not found");
+    std::vector<const MappedRead*> rs;
+    for (auto& r : reads)
+      if (r.contig == contig && r.sampleId == sample && r.overlapsLocus(locus)) rs.push_back(&r);
+    Pileup p = Pileup::make(rs, sample, contig, locus, *c);
+    std::vector<const Element*> els;
+    for (auto& e : p.elements) els.push_back(&e);
+    PileupStats st(els, ref_seq);
+    std::string text = "total=" + std::to_string(st.totalDepthIncludingReadsContributingNoAlleles()) + "\n";
+    for (auto& d : st.allelicDepthsSorted) text += d.allele + "=" + std::to_string(d.count) + "\n";
+    const char* t = keys_text;
+    int k = 0;
+    char buf[64];
+    for (int m = 0; m < n_mixtures; ++m) {
+      AlleleMixture mix;
+      for (int j = 0; j < n_keys[m]; ++j) {
+        std::string key(t);
+        t += key.size() + 1;
+        mix.push_back({key, fractions[k++]});
+      }
+      snprintf(buf, sizeof buf, "%.17g", st.logLikelihoodPileup(mix));
+      text += std::string("LL\t") + buf + "\n";
+    }
+    *out_text = (char*)std::malloc(text.size() + 1);
+    std::memcpy(*out_text, text.c_str(), text.size() + 1);
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}

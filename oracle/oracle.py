@@ -35,7 +35,8 @@ class OracleContig(C.Structure):
 
 def build(force: bool = False) -> str:
     if force or not os.path.exists(LIB_PATH) or any(
-            os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(LIB_PATH) for f in ("guac_oracle.cpp", "guac_oracle.hpp")):
+            os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(LIB_PATH)
+            for f in ("guac_oracle.cpp", "guac_oracle.hpp", "guac_oracle_joint.hpp")):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return LIB_PATH
 
@@ -225,3 +226,61 @@ def synth_reference(seed: int, lo: int, hi: int) -> np.ndarray:
     out = np.zeros(hi - lo, np.uint8)
     lib().oracle_synth_reference(C.c_uint64(seed), C.c_int64(lo), C.c_int64(hi), ptr(out, u8p))
     return out
+
+
+def somatic_joint(batch: ReadBatch, reference: Reference, loci, params, force_loci=()):
+    """SomaticJoint.makeCalls over one partition -> list of per-allele evidence dicts
+    (guacamole_b200.commands.somatic_joint.decode form) plus the number of loci visited."""
+    from guacamole_b200.commands import somatic_joint as sj
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    r, f = make_ranges(loci), make_ranges(force_loci)
+    al, na, sm, ns, arena, alen, nv = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_int64()
+    _check(lib().oracle_somatic_joint(C.byref(b), cs, nc, C.byref(params), r, len(loci), f, len(force_loci), C.byref(al), C.byref(na),
+                                      C.byref(sm), C.byref(ns), C.byref(arena), C.byref(alen), C.byref(nv)))
+    arena_b = C.string_at(arena, alen.value)
+    lib().oracle_free(arena)
+    alleles = _take(al, sj.ALLELE_EVIDENCE_DTYPE, na.value)
+    samples = _take(sm, sj.SAMPLE_EVIDENCE_DTYPE, ns.value)
+    return sj.decode(alleles, samples, arena_b, batch.n_samples), nv.value
+
+
+def read_subsequences(batch, reference, contig, locus, length=1, sample=0):
+    """[(fixed_length_sequence or None, next_alt_sequence or None)] per element (ReadSubsequence probes)."""
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    text = C.c_void_p()
+    _check(lib().oracle_read_subsequences(C.byref(b), cs, nc, batch.contig_names.index(contig), C.c_int64(locus), sample, length,
+                                          C.byref(text)))
+    s = C.string_at(text).decode()
+    lib().oracle_free(text)
+    rows = [l.split("\t") for l in s.split("\n") if l]
+    out = []
+    for i in range(0, len(rows), 2):
+        fx, al = rows[i], rows[i + 1]
+        out.append((None if fx[1] == "-" else fx[1], None if al[1] == "-" else al[1]))
+    return out
+
+
+def pileup_stats(batch, reference, contig, locus, ref_seq, mixtures=(), sample=0):
+    """(total depth, [(allele, depth)...] most frequent first, [log10 likelihood per mixture])."""
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    n_keys = np.array([len(m) for m in mixtures] or [0], np.int32)
+    keys = b"".join(k.encode() + b"\0" for m in mixtures for k, _ in m)
+    fr = np.array([f for m in mixtures for _, f in m] or [0.0], np.float64)
+    text = C.c_void_p()
+    _check(lib().oracle_pileup_stats(C.byref(b), cs, nc, batch.contig_names.index(contig), C.c_int64(locus), sample, ref_seq.encode(),
+                                     len(mixtures), ptr(n_keys, i32p), keys, fr.ctypes.data_as(C.POINTER(C.c_double)), C.byref(text)))
+    s = C.string_at(text).decode()
+    lib().oracle_free(text)
+    total, depths, lls = 0, [], []
+    for l in s.split("\n"):
+        if l.startswith("total="):
+            total = int(l[6:])
+        elif l.startswith("LL\t"):
+            lls.append(float(l[3:]))
+        elif l:
+            a, c = l.rsplit("=", 1)
+            depths.append((a, int(c)))
+    return total, depths, lls
