@@ -120,6 +120,8 @@ struct Elem {
   uint8_t base;     // Match/Mismatch: sequenced base
   uint8_t quality;  // qualityScore
   uint8_t ref_base;
+  // isFinalCigarBase and the operator of the following cigar element (-1 if none); only meaningful for it
+  bool followed_by_ref_skip;  // final base of its element and the next element consumes reference but not read (D, N)
 };
 
 // PileupElement.apply(read, locus, contig) = cursor at read.start . advanceToLocus(locus)
@@ -176,6 +178,7 @@ __device__ inline int element_at(const ReadsView& R, int64_t r, int64_t locus, c
     }
   }
   const uint8_t mapq = __ldg(R.mapq + r);
+  e.followed_by_ref_skip = is_final && (nop == OPC_D || nop == OPC_N);  // ReadSubsequence.scala:108-112
   if ((op == OPC_M || op == OPC_EQ) && nop == OPC_I) {  // PE.scala:82-83
     e.kind = GUAC_ALN_INSERTION;
     e.indel_length = nlen;

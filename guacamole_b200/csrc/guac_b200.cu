@@ -20,6 +20,7 @@
 #include "scan.cuh"
 #include "synth_kernels.cuh"
 #include "tile_kernels.cuh"
+#include "joint_host.hpp"
 
 using namespace guac;
 
@@ -68,7 +69,7 @@ struct guac_ctx {
   int64_t opt_ss_impl = 0;            // 0 = streaming tile kernel (+ gather fallback), 1 = gather kernel only
   int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
-  DevBuf b_heavy, b_boundtab, b_vcount;
+  DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites;
   double bound_tab_vaf = -1;
 };
 
@@ -404,6 +405,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_fallback.p) cudaFree(ctx->b_fallback.p);
   if (ctx->b_heavy.p) cudaFree(ctx->b_heavy.p);
   if (ctx->b_vcount.p) cudaFree(ctx->b_vcount.p);
+  if (ctx->b_sj_sites.p) cudaFree(ctx->b_sj_sites.p);
   if (ctx->b_boundtab.p) cudaFree(ctx->b_boundtab.p);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -882,6 +884,186 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   trace.mark("visited / summary");
+  return GUAC_OK;
+}
+
+int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_range* loci, int32_t n_ranges,
+                       const guac_range* force_loci, int32_t n_force, guac_sj_allele_evidence** out_alleles, int64_t* n_alleles,
+                       guac_sj_sample_evidence** out_samples, int64_t* n_sample_evidences, char** out_arena, int64_t* arena_len,
+                       int64_t* out_n_visited) {
+  if (!ctx || !params || !out_alleles || !n_alleles || !out_samples || !n_sample_evidences || !out_arena || !arena_len)
+    return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
+  const int S = params->n_samples;
+  if (S != ctx->n_samples || S <= 0 || S > GUAC_SJ_MAX_SAMPLES)
+    return fail(ctx, GUAC_E_INVALID_INPUT, "guac_sj_params.n_samples must equal the uploaded batch's n_samples (<= 16)");
+  if (params->max_alleles_per_site < 1 || params->max_alleles_per_site > SJ_MAX_ALLELES)
+    return fail(ctx, GUAC_E_UNSUPPORTED, "max_alleles_per_site must be in 1..7");
+  if (n_force < 0 || (n_force > 0 && !force_loci)) return fail(ctx, GUAC_E_INVALID_INPUT, "bad force-call loci");
+  SJParamsDev P;
+  std::memset(&P, 0, sizeof P);
+  P.n_samples = S;
+  for (int s = 0; s < S; ++s) {
+    P.kind[s] = params->sample_kind[s];
+    if (P.kind[s] < GUAC_SJ_NORMAL_DNA || P.kind[s] > GUAC_SJ_TUMOR_RNA) return fail(ctx, GUAC_E_INVALID_INPUT, "bad sample kind");
+  }
+  for (int s = 0; s < S; ++s)
+    if (P.kind[s] == GUAC_SJ_NORMAL_DNA) P.discovery[P.n_discovery++] = s;
+  const int n_normal = P.n_discovery;
+  for (int s = 0; s < S; ++s)
+    if (P.kind[s] == GUAC_SJ_TUMOR_DNA) P.discovery[P.n_discovery++] = s;
+  if (n_normal == 0) return fail(ctx, GUAC_E_INVALID_INPUT, "at least one normal DNA sample is required");  // normalPileups.head (:88)
+  P.max_alleles = params->max_alleles_per_site;
+  P.min_reads = params->any_allele_min_supporting_reads;
+  P.min_percent = params->any_allele_min_supporting_percent;
+  P.vaf_floor = params->somatic_vaf_floor;
+  // lociSetMinusOne (commands/SomaticJointCaller.scala:143-152): pileups are taken one locus before the alleles
+  std::vector<guac_range> shifted;
+  for (int i = 0; i < n_ranges; ++i) {
+    guac_range r = loci[i];
+    r.start = std::max<int64_t>(0, r.start - 1);
+    r.end = r.end - 1;
+    if (r.end > r.start) shifted.push_back(r);
+  }
+  Plan plan;
+  GUAC_TRY(make_plan(ctx, shifted.data(), (int32_t)shifted.size(), plan));
+  *n_alleles = 0;
+  *n_sample_evidences = 0;
+  *arena_len = 0;
+  if (out_n_visited) *out_n_visited = 0;
+  if (plan.n_tiles == 0) {
+    GUAC_TRY(host_out(ctx, out_alleles, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_samples, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_arena, nullptr, 0));
+    return GUAC_OK;
+  }
+  GUAC_TRY(reset_error(ctx));
+  GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
+  GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(int)));
+  DevBuf d_force;
+  GUAC_TRY(upload(ctx, d_force, force_loci, (size_t)n_force));
+  int max_sites = (int)std::max<size_t>(ctx->b_sj_sites.cap / sizeof(SJSiteDev), 1 << 14);
+  int n_sites = 0;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    GUAC_TRY(ensure(ctx, ctx->b_sj_sites, (size_t)max_sites * sizeof(SJSiteDev)));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    sj_discover_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
+        ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), P, d_force.as<guac_range>(), n_force, ctx->b_visited.as<uint8_t>(),
+        ctx->b_sj_sites.as<SJSiteDev>(), ctx->b_ncalls.as<int>(), max_sites, ctx->b_err.as<DeviceError>());
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    ctx->launches += 1;
+    ctx->have_timing = true;
+    ctx->timed_loci = plan.n_slots;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_sites, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    int st = check_device_error(ctx);
+    if (st != GUAC_OK) {
+      cudaFree(d_force.p);
+      return st;
+    }
+    if (n_sites <= max_sites) break;
+    max_sites = n_sites;
+  }
+  cudaFree(d_force.p);
+  std::vector<SJSiteDev> sites((size_t)n_sites);
+  std::vector<SJEvidenceDev> raw;
+  std::vector<int2> jobs;
+  if (n_sites > 0) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(sites.data(), ctx->b_sj_sites.p, (size_t)n_sites * sizeof(SJSiteDev), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    std::sort(sites.begin(), sites.end(), [](const SJSiteDev& a, const SJSiteDev& b) { return a.slot < b.slot; });
+    for (int i = 0; i < n_sites; ++i)
+      for (int a = 0; a < sites[i].n_alleles; ++a) jobs.push_back(make_int2(i, a));
+    DevBuf d_jobs, d_raw;
+    GUAC_TRY(upload(ctx, d_jobs, jobs.data(), jobs.size()));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->b_sj_sites.p, sites.data(), (size_t)n_sites * sizeof(SJSiteDev), cudaMemcpyHostToDevice, ctx->stream));
+    GUAC_TRY(ensure(ctx, d_raw, jobs.size() * sizeof(SJEvidenceDev)));
+    sj_evidence_kernel<<<(unsigned)jobs.size(), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_sj_sites.as<SJSiteDev>(),
+                                                                         d_jobs.as<int2>(), d_raw.as<SJEvidenceDev>(),
+                                                                         ctx->b_err.as<DeviceError>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    raw.resize(jobs.size());
+    CUDA_TRY(ctx, cudaMemcpyAsync(raw.data(), d_raw.p, jobs.size() * sizeof(SJEvidenceDev), cudaMemcpyDeviceToHost, ctx->stream));
+    int st = check_device_error(ctx);
+    cudaFree(d_jobs.p);
+    cudaFree(d_raw.p);
+    if (st != GUAC_OK) return st;
+  }
+  // host: posteriors, calls, annotations, emit policy; then lay out the strings
+  std::vector<guac_sj_allele_evidence> alleles;
+  std::vector<guac_sj_sample_evidence> samples;
+  std::vector<SJStringJob> strings;
+  uint32_t arena_off = 0;
+  auto add_string = [&](int kind, int64_t a, int32_t b, int32_t len, uint32_t& off, uint32_t& out_len) {
+    SJStringJob j;
+    j.a = a;
+    j.b = b;
+    j.len = len;
+    j.arena_off = arena_off;
+    j.kind = kind;
+    strings.push_back(j);
+    off = arena_off;
+    out_len = (uint32_t)len;
+    arena_off += (uint32_t)len;
+  };
+  size_t job_i = 0;
+  int site_index = 0;
+  for (int i = 0; i < n_sites; ++i) {
+    std::vector<joint::Record> all;
+    for (int a = 0; a < sites[i].n_alleles; ++a, ++job_i) all.push_back(joint::evaluate(*params, sites[i], a, raw[job_i]));
+    std::vector<joint::Record> emitted = joint::emit(*params, sites[i].forced != 0, all);
+    if (emitted.empty()) continue;
+    for (auto& rec : emitted) {
+      const SJAlleleDev& al = sites[i].alleles[rec.raw->allele];
+      rec.allele.site_index = site_index;
+      add_string(1, sites[i].locus + 1, sites[i].ref_index, al.span, rec.allele.ref_off, rec.allele.ref_len);
+      if (al.key == 0) add_string(2, 0, 0, 1, rec.allele.alt_off, rec.allele.alt_len);
+      else add_string(0, al.rep_read, al.rep_start_rp, al.alt_len, rec.allele.alt_off, rec.allele.alt_len);
+      rec.allele.first_sample_evidence = (int64_t)samples.size();
+      for (int s = 0; s < S + 2; ++s) {
+        guac_sj_sample_evidence& e = rec.samples[s];
+        const SJSlotDev& r = rec.raw->slots[s];
+        for (int k = 0; k < r.n_depths; ++k)
+          add_string(0, r.depths[k].rep_read, r.depths[k].rep_start_rp, r.depths[k].len, e.depths[k].seq_off, e.depths[k].seq_len);
+        samples.push_back(e);
+      }
+      alleles.push_back(rec.allele);
+    }
+    ++site_index;
+  }
+  *arena_len = arena_off;
+  if (!strings.empty()) {
+    DevBuf d_strings;
+    GUAC_TRY(upload(ctx, d_strings, strings.data(), strings.size()));
+    GUAC_TRY(ensure(ctx, ctx->b_arena, arena_off + 16));
+    sj_strings_kernel<<<blocks_for((int64_t)strings.size(), 128), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(),
+                                                                                         d_strings.as<SJStringJob>(), (int)strings.size(),
+                                                                                         ctx->b_arena.as<char>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_strings.p);
+  }
+  GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)arena_off));
+  void* ha = nullptr;
+  void* hs = nullptr;
+  GUAC_TRY(pinned_alloc(ctx, &ha, std::max<size_t>(alleles.size() * sizeof(guac_sj_allele_evidence), 16)));
+  GUAC_TRY(pinned_alloc(ctx, &hs, std::max<size_t>(samples.size() * sizeof(guac_sj_sample_evidence), 16)));
+  if (!alleles.empty()) std::memcpy(ha, alleles.data(), alleles.size() * sizeof(guac_sj_allele_evidence));
+  if (!samples.empty()) std::memcpy(hs, samples.data(), samples.size() * sizeof(guac_sj_sample_evidence));
+  *out_alleles = (guac_sj_allele_evidence*)ha;
+  *out_samples = (guac_sj_sample_evidence*)hs;
+  *n_alleles = (int64_t)alleles.size();
+  *n_sample_evidences = (int64_t)samples.size();
+  if (out_n_visited) {
+    int64_t nv = 0;
+    GUAC_TRY(compact_visited(ctx, plan, 1, nv));
+    *out_n_visited = nv;
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return GUAC_OK;
 }
 

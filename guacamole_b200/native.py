@@ -353,6 +353,21 @@ class Context:
         return (_take(self.lib, self.ctx, oc, np.int32, n.value), _take(self.lib, self.ctx, ol, np.int64, n.value), offsets,
                 _take(self.lib, self.ctx, els, ELEMENT_DTYPE, total))
 
+    def somatic_joint(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
+        """guac_somatic_joint -> (list of per-allele evidence dicts, loci visited); see commands/somatic_joint.py."""
+        from .commands import somatic_joint as sj
+        r, f = make_ranges(loci), make_ranges(force_loci)
+        al, na, sm, ns, arena, alen, nv = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_int64()
+        self._check(self.lib.guac_somatic_joint(self.ctx, C.byref(params), r, C.c_int32(len(loci)), f, C.c_int32(len(force_loci)),
+                                                C.byref(al), C.byref(na), C.byref(sm), C.byref(ns), C.byref(arena), C.byref(alen),
+                                                C.byref(nv)))
+        arena_b = C.string_at(arena, alen.value) if arena else b""
+        if arena:
+            self.lib.guac_free(self.ctx, arena)
+        alleles = _take(self.lib, self.ctx, al, sj.ALLELE_EVIDENCE_DTYPE, na.value)
+        samples = _take(self.lib, self.ctx, sm, sj.SAMPLE_EVIDENCE_DTYPE, ns.value)
+        return sj.decode(alleles, samples, arena_b, params.n_samples), nv.value
+
     # -- callers -----------------------------------------------------------------
     def somatic_standard(self, ranges: Sequence[Tuple[int, int, int]], params: Optional[SSParamsC] = None,
                          want_summary: bool = False):

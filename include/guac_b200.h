@@ -337,6 +337,23 @@ typedef struct {
   int64_t first_sample_evidence;
 } guac_sj_allele_evidence;
 
+/*
+ * somatic-joint: SomaticJoint.makeCalls (M/commands/SomaticJointCaller.scala:154-203) =
+ * pileupFlatMapMultipleSamples(skipEmpty = true, MultiSampleMultiAlleleEvidence.make) over the loci shifted
+ * by -1 (lociSetMinusOne :143-152; the function does the shift itself).  A site is force-called when
+ * pileup locus + 1 lies in `force_loci` (:181).  Per-element work — ReadSubsequence, AlleleAtLocus,
+ * PileupStats and the mixture likelihoods (M/jointcaller/pileup_summarization/*, AlleleAtLocus.scala:85-149,
+ * evidence/*SingleSampleSingleAlleleEvidence.scala) — runs on the device; posteriors, call logic, annotations
+ * (M/jointcaller/evidence/MultiSampleSingleAlleleEvidence.scala:66-341, annotation/*.scala) and the emit
+ * policy (MultiSampleMultiAlleleEvidence.scala:131-177) on the host side of the library.
+ * Output: one guac_sj_allele_evidence per emitted allele, in (range order, locus, allele) order, each with
+ * n_samples + 2 guac_sj_sample_evidence records; strings in the arena.
+ */
+int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_range* loci, int32_t n_ranges,
+                       const guac_range* force_loci, int32_t n_force, guac_sj_allele_evidence** out_alleles, int64_t* n_alleles,
+                       guac_sj_sample_evidence** out_samples, int64_t* n_sample_evidences, char** out_arena, int64_t* arena_len,
+                       int64_t* out_n_visited);
+
 /* ---- measurement support ----------------------------------------------------
  * These have no counterpart in the reference: they exist so that bench.py and the
  * tests can generate SURVEY.md 8(d)'s seeded synthetic reads directly in HBM, read them
