@@ -21,6 +21,7 @@
 #include "synth_kernels.cuh"
 #include "tile_kernels.cuh"
 #include "joint_host.hpp"
+#include "germline_kernels.cuh"
 
 using namespace guac;
 
@@ -687,6 +688,8 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   P.max_read_depth = params->max_read_depth;
   P.max_normal_alt = params->max_normal_alternate_read_depth;
   P.min_vaf = (double)params->min_tumor_variant_allele_frequency;
+  P.min_alt_reads = 0;
+  P._pad = 0;
   if (P.normal_sample < 0 || P.tumor_sample < 0 || P.normal_sample == P.tumor_sample || P.n_samples > ctx->n_samples)
     return fail(ctx, GUAC_E_INVALID_INPUT, "bad normal/tumor sample ids");
   if (plan.n_tiles == 0) {
@@ -712,7 +715,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
       static bool attr_set = false;
       if (!attr_set) {
-        CUDA_TRY(ctx, cudaFuncSetAttribute(ss_tile_kernel<TCfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        CUDA_TRY(ctx, cudaFuncSetAttribute(ss_tile_kernel<TCfg, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)sizeof(TileSmem<TCfg>)));
         attr_set = true;
       }
@@ -750,7 +753,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       TA.n_visited = visited_count;
       TA.err = ctx->b_err.as<DeviceError>();
       cudaEventRecord(ctx->ev0, ctx->stream);
-      ss_tile_kernel<TCfg><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+      ss_tile_kernel<TCfg, 0><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
       int counts[2] = {0, 0};
@@ -1062,6 +1065,247 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     int64_t nv = 0;
     GUAC_TRY(compact_visited(ctx, plan, 1, nv));
     *out_n_visited = nv;
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return GUAC_OK;
+}
+
+int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const guac_range* loci, int32_t n_ranges,
+                           guac_called_allele** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
+                           int64_t** out_active_loci, int64_t* n_active, int64_t* out_n_visited) {
+  if (!ctx || !params || !out_calls || !n_calls || !out_arena || !arena_len || !out_active_loci || !n_active) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  using TCfg = TileCfg<512>;
+  if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
+  if (params->sample_id < 0 || params->sample_id >= ctx->n_samples) return fail(ctx, GUAC_E_INVALID_INPUT, "bad sample id");
+  Plan plan;
+  GUAC_TRY(make_plan(ctx, loci, n_ranges, plan, TCfg::TL));
+  *n_calls = 0;
+  *arena_len = 0;
+  *n_active = 0;
+  if (out_n_visited) *out_n_visited = 0;
+  if (plan.n_tiles == 0) {
+    GUAC_TRY(host_out(ctx, out_calls, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_arena, nullptr, 0));
+    GUAC_TRY(host_out(ctx, out_active_loci, nullptr, 0));
+    return GUAC_OK;
+  }
+  GLParamsDev G;
+  G.sample = params->sample_id;
+  G.min_alt_reads = params->min_alt_reads;
+  G.respect_active_regions = params->respect_active_regions;
+  G.min_area_vaf = params->min_area_vaf;
+  SSParamsDev P;
+  std::memset(&P, 0, sizeof P);
+  P.normal_sample = -1;
+  P.tumor_sample = params->sample_id;
+  P.n_samples = ctx->n_samples;
+  P.min_alt_reads = params->min_alt_reads;
+  GUAC_TRY(reset_error(ctx));
+  GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
+  GUAC_TRY(ensure(ctx, ctx->b_summary, (size_t)plan.n_slots * 2 * sizeof(guac_locus_summary)));
+  GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 2) * sizeof(int)));
+  GUAC_TRY(ensure(ctx, ctx->b_vcount, sizeof(unsigned long long)));
+  GUAC_TRY(ensure(ctx, ctx->b_boundtab, 256 * sizeof(double)));
+  GUAC_TRY(ensure(ctx, ctx->b_ncalls, 2 * sizeof(int)));
+  int* fb_count = ctx->b_fallback.as<int>();
+  int* fb_list = fb_count + 1;
+  int* heavy_count = fb_count + 1 + plan.n_tiles;
+  const int max_heavy = (int)std::min<int64_t>(plan.n_slots, plan.n_slots / 8 + 65536);
+  GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
+  CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(heavy_count, 0, sizeof(int), ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_vcount.p, 0, sizeof(unsigned long long), ctx->stream));
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(ctx, cudaFuncSetAttribute(ss_tile_kernel<TCfg, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<TCfg>)));
+    attr_set = true;
+  }
+  TileArgs TA;
+  TA.rflags = ctx->b_rflags.as<uint8_t>();
+  TA.refs = ctx->d_refs.as<RefView>();
+  TA.tiles = ctx->b_tiles.as<Tile>();
+  TA.bound_tab = ctx->b_boundtab.as<double>();
+  TA.visited = ctx->b_visited.as<uint8_t>();
+  TA.summary = ctx->b_summary.as<guac_locus_summary>();
+  TA.heavy = ctx->b_heavy.as<Tile>();
+  TA.n_heavy = heavy_count;
+  TA.max_heavy = max_heavy;
+  TA.fallback_tiles = fb_list;
+  TA.n_fallback = fb_count;
+  TA.force_fallback_mod = (int)ctx->opt_force_fallback_mod;
+  TA.n_visited = ctx->b_vcount.as<unsigned long long>();
+  TA.err = ctx->b_err.as<DeviceError>();
+  cudaEventRecord(ctx->ev0, ctx->stream);
+  ss_tile_kernel<TCfg, 1><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+  ctx->launches += 1;
+  CUDA_TRY(ctx, cudaGetLastError());
+  int counts[2] = {0, 0};
+  CUDA_TRY(ctx, cudaMemcpyAsync(&counts[0], fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->last_fallback_tiles = counts[0];
+  if (counts[0] > 0) {
+    germline_dense_fallback_kernel<<<(unsigned)counts[0], CTA_THREADS, 0, ctx->stream>>>(
+        ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, G, ctx->b_visited.as<uint8_t>(),
+        ctx->b_summary.as<guac_locus_summary>(), ctx->b_heavy.as<Tile>(), heavy_count, max_heavy,
+        ctx->b_vcount.as<unsigned long long>(), ctx->b_err.as<DeviceError>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+  }
+  CUDA_TRY(ctx, cudaMemcpyAsync(&counts[1], heavy_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  const int n_heavy = counts[1];
+  ctx->last_heavy_loci = n_heavy;
+  if (n_heavy > max_heavy) return fail(ctx, GUAC_E_UNSUPPORTED, "more candidate loci than the heavy-locus list holds; split the loci ranges");
+  int nc = 0, na = 0;
+  int* d_nc = ctx->b_ncalls.as<int>();
+  const int max_calls = std::max(n_heavy, 1);
+  GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(GLCallDev)));
+  DevBuf d_active;
+  GUAC_TRY(ensure(ctx, d_active, (size_t)max_calls * 2 * sizeof(long long)));
+  CUDA_TRY(ctx, cudaMemsetAsync(d_nc, 0, 2 * sizeof(int), ctx->stream));
+  if (n_heavy > 0) {
+    germline_locus_kernel<<<blocks_for(n_heavy, WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
+        ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), n_heavy, G, ctx->b_calls.as<GLCallDev>(), d_nc, max_calls,
+        d_active.as<long long>(), d_nc + 1, max_calls, ctx->b_err.as<DeviceError>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+  }
+  cudaEventRecord(ctx->ev1, ctx->stream);
+  ctx->have_timing = true;
+  ctx->timed_loci = plan.n_slots;
+  int both[2] = {0, 0};
+  CUDA_TRY(ctx, cudaMemcpyAsync(both, d_nc, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  {
+    int st = check_device_error(ctx);
+    if (st != GUAC_OK) {
+      cudaFree(d_active.p);
+      return st;
+    }
+  }
+  nc = both[0];
+  na = both[1];
+  std::vector<GLCallDev> calls((size_t)nc);
+  std::vector<long long> active((size_t)na * 2);
+  if (nc) CUDA_TRY(ctx, cudaMemcpyAsync(calls.data(), ctx->b_calls.p, (size_t)nc * sizeof(GLCallDev), cudaMemcpyDeviceToHost, ctx->stream));
+  if (na) CUDA_TRY(ctx, cudaMemcpyAsync(active.data(), d_active.p, (size_t)na * 2 * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  cudaFree(d_active.p);
+  std::sort(calls.begin(), calls.end(), [](const GLCallDev& a, const GLCallDev& b) { return a.slot < b.slot; });
+  // active loci sorted by (contig, locus) like the visiting order within a contig
+  {
+    std::vector<std::pair<long long, long long>> v;
+    for (int i = 0; i < na; ++i) v.push_back({active[2 * i], active[2 * i + 1]});
+    std::sort(v.begin(), v.end());
+    for (int i = 0; i < na; ++i) {
+      active[2 * i] = v[i].first;
+      active[2 * i + 1] = v[i].second;
+    }
+  }
+  // AlleleEvidence of every called allele
+  std::vector<EvidenceJob> jobs;
+  for (auto& c : calls)
+    for (int t = 0; t < c.n_called; ++t) {
+      EvidenceJob j;
+      j.locus = c.locus;
+      j.read_lo = c.read_lo;
+      j.read_hi = c.read_hi;
+      j.key = c.called[t].key;
+      j.contig_id = c.contig_id;
+      j.ref_index = c.ref_index;
+      j.sample = params->sample_id;
+      j._pad = 0;
+      j.probability = std::exp(c.log_probability);  // :247
+      jobs.push_back(j);
+    }
+  std::vector<guac_allele_evidence> evs(jobs.size());
+  if (!jobs.empty()) {
+    DevBuf d_jobs, d_evs;
+    GUAC_TRY(upload(ctx, d_jobs, jobs.data(), jobs.size()));
+    GUAC_TRY(ensure(ctx, d_evs, jobs.size() * sizeof(guac_allele_evidence)));
+    allele_evidence_kernel<<<(unsigned)jobs.size(), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), d_jobs.as<EvidenceJob>(),
+                                                                             d_evs.as<guac_allele_evidence>(), ctx->b_err.as<DeviceError>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(evs.data(), d_evs.p, jobs.size() * sizeof(guac_allele_evidence), cudaMemcpyDeviceToHost, ctx->stream));
+    int st = check_device_error(ctx);
+    cudaFree(d_jobs.p);
+    cudaFree(d_evs.p);
+    if (st != GUAC_OK) return st;
+  }
+  // keep calls with phredScaledLikelihood > min (:147); lay out the allele strings
+  auto phred = [](double probability) {  // util/PhredUtils.scala:7-14 over ADAM's successProbabilityToPhred
+    const double p = std::min(1 - 1e-16, probability);
+    return (int)std::floor(-10.0 * std::log10(1.0 - p) + 0.5);
+  };
+  std::vector<guac_called_allele> out;
+  std::vector<SJStringJob> strings;
+  uint32_t arena_off = 0;
+  auto add_string = [&](int kind, int64_t a, int32_t b, int32_t len, uint32_t& off, uint32_t& out_len) {
+    SJStringJob j;
+    j.a = a;
+    j.b = b;
+    j.len = len;
+    j.arena_off = arena_off;
+    j.kind = kind;
+    strings.push_back(j);
+    off = arena_off;
+    out_len = (uint32_t)len;
+    arena_off += (uint32_t)len;
+  };
+  size_t ji = 0;
+  for (auto& c : calls)
+    for (int t = 0; t < c.n_called; ++t, ++ji) {
+      if (!(phred(evs[ji].probability) > params->min_phred_scaled_likelihood)) continue;
+      const GLAlleleDev& a = c.called[t];
+      guac_called_allele g;
+      std::memset(&g, 0, sizeof g);
+      g.contig_id = c.contig_id;
+      g.n_genotypes = c.n_genotypes;
+      g.start = c.locus;
+      g.genotype_log_probability = c.log_probability;
+      g.evidence = evs[ji];
+      if (a.kind == GUAC_ALN_MISMATCH) {
+        add_string(1, c.locus, c.ref_index, 1, g.ref_off, g.ref_len);
+        add_string(3, 0, a.base, 1, g.alt_off, g.alt_len);
+      } else if (a.kind == GUAC_ALN_INSERTION) {
+        add_string(0, a.rep_read, a.rep_rp, 1, g.ref_off, g.ref_len);
+        add_string(0, a.rep_read, a.rep_rp, a.indel_len + 1, g.alt_off, g.alt_len);
+      } else {  // Deletion
+        add_string(1, c.locus, c.ref_index, a.indel_len + 1, g.ref_off, g.ref_len);
+        add_string(1, c.locus, c.ref_index, 1, g.alt_off, g.alt_len);
+      }
+      out.push_back(g);
+    }
+  *arena_len = arena_off;
+  if (!strings.empty()) {
+    DevBuf d_strings;
+    GUAC_TRY(upload(ctx, d_strings, strings.data(), strings.size()));
+    GUAC_TRY(ensure(ctx, ctx->b_arena, arena_off + 16));
+    sj_strings_kernel<<<blocks_for((int64_t)strings.size(), 128), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(),
+                                                                                         d_strings.as<SJStringJob>(), (int)strings.size(),
+                                                                                         ctx->b_arena.as<char>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_strings.p);
+  }
+  GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)arena_off));
+  void* hc = nullptr;
+  void* hact = nullptr;
+  GUAC_TRY(pinned_alloc(ctx, &hc, std::max<size_t>(out.size() * sizeof(guac_called_allele), 16)));
+  GUAC_TRY(pinned_alloc(ctx, &hact, std::max<size_t>(active.size() * sizeof(int64_t), 16)));
+  if (!out.empty()) std::memcpy(hc, out.data(), out.size() * sizeof(guac_called_allele));
+  if (!active.empty()) std::memcpy(hact, active.data(), active.size() * sizeof(int64_t));
+  *out_calls = (guac_called_allele*)hc;
+  *n_calls = (int64_t)out.size();
+  *out_active_loci = (int64_t*)hact;
+  *n_active = na;
+  if (out_n_visited) {
+    unsigned long long v = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&v, ctx->b_vcount.p, sizeof v, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    *out_n_visited = (int64_t)v;
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return GUAC_OK;

@@ -605,7 +605,7 @@ struct SJStringJob {
   int32_t b;         // read position, or reference table index
   int32_t len;
   uint32_t arena_off;
-  int32_t kind;      // 0 read bases, 1 reference slice, 2 the literal "N"
+  int32_t kind;      // 0 read bases, 1 reference slice, 2 the literal "N", 3 the single character `b`
 };
 
 __global__ void sj_strings_kernel(ReadsView R, const RefView* __restrict__ refs, const SJStringJob* __restrict__ jobs, int n,
@@ -620,6 +620,8 @@ __global__ void sj_strings_kernel(ReadsView R, const RefView* __restrict__ refs,
   } else if (j.kind == 1) {
     const RefView ref = refs[j.b];
     for (int k = 0; k < j.len; ++k) dst[k] = (char)ref.at(j.a + k);
+  } else if (j.kind == 3) {
+    dst[0] = (char)j.b;
   } else {
     dst[0] = 'N';
   }

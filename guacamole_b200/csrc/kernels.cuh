@@ -215,6 +215,7 @@ struct SSParamsDev {
   int normal_sample, tumor_sample, n_samples;
   int normal_odds, tumor_odds;
   int max_read_depth, max_normal_alt;
+  int min_alt_reads, _pad;  // germline mode of the tile kernel
   double min_vaf;  // float widened to double (SomaticStandardCaller.scala:97,189)
 };
 

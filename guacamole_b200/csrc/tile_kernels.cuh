@@ -138,7 +138,10 @@ struct TileArgs {
   DeviceError* err;
 };
 
-template <class CFG>
+// MODE 0: somatic-standard (two samples).  MODE 1: germline toy caller's dense half — one sample (the "tumor"
+// slot; normal_sample = -1), a locus is heavy when depth - referenceDepth >= P.min_alt_reads
+// (commands/GermlineAssemblyCaller.scala:135-138).
+template <class CFG, int MODE>
 __global__ void __launch_bounds__(CFG::THREADS, 4)
 ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -395,9 +398,26 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     my_visited += dN + dT > 0;
     if (dN + dT > 0 && ref.at(x) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x, -1);
     // early-outs (SomaticStandardCaller.scala:164-172)
-    const bool candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
+    const bool candidate = MODE == 0 ? (dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt)
+                                     : (dT > 0 && nrT >= P.min_alt_reads);
     int top_t = 0, top_n = 0, flags = 0;
-    if (candidate) {
+    if (MODE == 1 && candidate) {  // every candidate locus gets the full genotype likelihoods
+      const int h = atomicAdd(A.n_heavy, 1);
+      if (h < A.max_heavy) {
+        Tile t;
+        t.locus0 = x;
+        t.n_loci = 1;
+        t.contig_id = tile.contig_id;
+        t.slot0 = slot;
+        t.read_lo = tile.read_lo;
+        t.read_hi = tile.read_hi;
+        t.ref_index = tile.ref_index;
+        t._pad = 0;
+        A.heavy[h] = t;
+      }
+      flags = 1;
+    }
+    if (MODE == 0 && candidate) {
       const int e1 = S.aux[l] >> 16, e0 = e1 - (nrN + nrT);
       bool simple = e1 - e0 <= CFG::EV_SIMPLE;
       // Distinct tumor variant alleles of the locus, straight from its (few) events.  An allele is

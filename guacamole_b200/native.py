@@ -80,6 +80,21 @@ class LocusSummaryC(C.Structure):
     _fields_ = [("depth", C.c_uint16), ("reference_depth", C.c_uint16), ("top_alt_count", C.c_uint16), ("flags", C.c_uint16)]
 
 
+class GSParamsC(C.Structure):
+    _fields_ = [("sample_id", C.c_int32), ("min_alt_reads", C.c_int32), ("min_phred_scaled_likelihood", C.c_int32),
+                ("respect_active_regions", C.c_int32), ("min_area_vaf", C.c_float), ("_pad", C.c_int32)]
+
+
+def gs_params(sample_id=0, min_alt_reads=2, min_phred_scaled_likelihood=0, respect_active_regions=0, min_area_vaf_percent=5):
+    """Defaults of GermlineAssemblyCaller (commands/GermlineAssemblyCaller.scala:40-47,92) and AssemblyArgs
+    (assembly/AssemblyArgs.scala:33); minAreaVaf is percent / 100.0f as a float (:70)."""
+    p = GSParamsC()
+    p.sample_id, p.min_alt_reads, p.min_phred_scaled_likelihood = sample_id, min_alt_reads, min_phred_scaled_likelihood
+    p.respect_active_regions = int(respect_active_regions)
+    p.min_area_vaf = float(np.float32(min_area_vaf_percent) / np.float32(100.0))
+    return p
+
+
 LOCUS_COUNTS_DTYPE = np.dtype([(n, np.uint32) for n, _ in LocusCountsC._fields_])
 ELEMENT_DTYPE = np.dtype([("read_index", np.int64), ("read_position", np.int32), ("cigar_element_index", np.int32),
                           ("cigar_element_locus", np.int64), ("index_within_cigar_element", np.int32), ("kind", np.uint8),
@@ -96,6 +111,9 @@ SS_CALL_DTYPE = np.dtype([("contig_id", np.int32), ("_pad", np.int32), ("start",
                           ("normal_reference_evidence", np.dtype(_EV))])
 LOCUS_SUMMARY_DTYPE = np.dtype([("depth", np.uint16), ("reference_depth", np.uint16), ("top_alt_count", np.uint16),
                                 ("flags", np.uint16)])
+CALLED_ALLELE_DTYPE = np.dtype([("contig_id", np.int32), ("n_genotypes", np.int32), ("start", np.int64), ("ref_off", np.uint32),
+                                ("ref_len", np.uint32), ("alt_off", np.uint32), ("alt_len", np.uint32),
+                                ("genotype_log_probability", np.float64), ("evidence", np.dtype(_EV))])
 assert LOCUS_COUNTS_DTYPE.itemsize == C.sizeof(LocusCountsC)
 assert ELEMENT_DTYPE.itemsize == C.sizeof(ElementC)
 assert SS_CALL_DTYPE.itemsize == C.sizeof(SSCallC)
@@ -352,6 +370,21 @@ class Context:
         total = int(offsets[-1]) if offsets.shape[0] else 0
         return (_take(self.lib, self.ctx, oc, np.int32, n.value), _take(self.lib, self.ctx, ol, np.int64, n.value), offsets,
                 _take(self.lib, self.ctx, els, ELEMENT_DTYPE, total))
+
+    def germline_standard(self, ranges: Sequence[Tuple[int, int, int]], params: Optional["GSParamsC"] = None):
+        """guac_germline_standard -> dict(calls, arena, active_loci [(contig, locus)], n_visited)."""
+        params = params or gs_params()
+        r = make_ranges(ranges)
+        calls, n, arena, alen = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64()
+        act, na, nv = C.c_void_p(), C.c_int64(), C.c_int64()
+        self._check(self.lib.guac_germline_standard(self.ctx, C.byref(params), r, C.c_int32(len(ranges)), C.byref(calls), C.byref(n),
+                                                    C.byref(arena), C.byref(alen), C.byref(act), C.byref(na), C.byref(nv)))
+        arena_b = C.string_at(arena, alen.value) if arena else b""
+        if arena:
+            self.lib.guac_free(self.ctx, arena)
+        active = _take(self.lib, self.ctx, act, np.int64, na.value * 2).reshape(-1, 2)
+        return dict(calls=_take(self.lib, self.ctx, calls, CALLED_ALLELE_DTYPE, n.value), arena=arena_b,
+                    active_loci=[(int(a), int(b)) for a, b in active], n_visited=nv.value)
 
     def somatic_joint(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
         """guac_somatic_joint -> (list of per-allele evidence dicts, loci visited); see commands/somatic_joint.py."""

@@ -271,6 +271,41 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
                           guac_ss_call** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
                           guac_locus_summary** out_summary, int64_t* out_n_visited);
 
+/* ---- germline toy caller ------------------------------------------------------
+ * The "germline-standard" path that survives in the reference: the shortcut branch of
+ * GermlineAssemblyCaller.discoverGermlineVariants (M/commands/GermlineAssemblyCaller.scala:103-153). */
+typedef struct {
+  int32_t sample_id;
+  int32_t min_alt_reads;               /* minAltReads, default 2 (:92) */
+  int32_t min_phred_scaled_likelihood; /* --min-likelihood, default 0 (:46) */
+  int32_t respect_active_regions;      /* 1: loci whose region isActiveRegion (M/assembly/AssemblyUtils.scala:28-39) are
+                                          returned uncalled for the assembler, as with --shortcut-assembly; 0: call them too */
+  float min_area_vaf;                  /* --min-area-vaf percent / 100.0f (:70), default 0.05f */
+  int32_t _pad;
+} guac_gs_params;
+
+/* M/variants/CalledAllele.scala:24-31 */
+typedef struct {
+  int32_t contig_id;
+  int32_t n_genotypes;             /* genotypes enumerated at the locus */
+  int64_t start;
+  uint32_t ref_off, ref_len, alt_off, alt_len;
+  double genotype_log_probability; /* normalised natural-log probability of the called genotype */
+  guac_allele_evidence evidence;
+} guac_called_allele;
+
+/*
+ * windowFlatMapWithState over one sample with the closure: if depth - referenceDepth >= minAltReads then
+ * callPileupVariant (M/commands/GermlineAssemblyCaller.scala:135-153,233-261), i.e.
+ * Likelihood.probabilitiesOfAllPossibleGenotypesFromPileup (M/likelihood/Likelihood.scala:31-63), the most
+ * probable genotype's non-reference alleles with their AlleleEvidence, kept when
+ * phredScaledLikelihood > min_phred_scaled_likelihood.  out_active_loci (contig, locus pairs) lists the loci
+ * left to the assembler when respect_active_regions is set.
+ */
+int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const guac_range* loci, int32_t n_ranges,
+                           guac_called_allele** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
+                           int64_t** out_active_loci, int64_t* n_active, int64_t* out_n_visited);
+
 /* ---- somatic-joint ----------------------------------------------------------
  * M/jointcaller/Parameters.scala:10-25 plus the inputs (M/jointcaller/Input.scala, InputCollection.scala:55-101)
  * and the flags of M/commands/SomaticJointCaller.scala:154-163. */

@@ -703,3 +703,88 @@ extern "C" int oracle_pileup_stats(const oracle_reads* b, const oracle_contig* c
     return -1;
   }
 }
+
+// ---------------------------------------------------------------------------------
+// germline toy caller: the shortcut branch of GermlineAssemblyCaller.discoverGermlineVariants
+// (M/commands/GermlineAssemblyCaller.scala:103-153) with callPileupVariant (:233-261) and
+// AssemblyUtils.isActiveRegion (M/assembly/AssemblyUtils.scala:28-39).
+// A locus whose region is "active" would be assembled by the reference; it is reported in
+// out_active and not called here.  respect_active_regions = 0 calls every candidate locus.
+// ---------------------------------------------------------------------------------
+extern "C" int oracle_germline_standard(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, const guac_gs_params* params,
+                                        const guac_range* loci, int n_loci, guac_called_allele** out_calls, int64_t* n_calls,
+                                        char** out_arena, int64_t* arena_len, int64_t** out_active, int64_t* n_active,
+                                        int64_t* out_n_visited) {
+  try {
+    auto all_reads = buildReads(b);
+    std::vector<MappedRead> reads;
+    for (auto& r : all_reads)
+      if (r.sampleId == params->sample_id) {
+        reads.push_back(r);
+        reads.back().sampleId = 0;
+      }
+    auto cs = buildContigs(contigs, n_contigs);
+    std::vector<guac_called_allele> calls;
+    std::vector<int64_t> active;
+    std::string arena;
+    int64_t visited = 0;
+    pileupFlatMapMultipleSamples(reads, 1, buildRanges(loci, n_loci), cs, true, [&](const std::vector<Pileup>& pileups) {
+      const Pileup& pileup = pileups[0];
+      ++visited;
+      const int pileupAltReads = pileup.depth() - pileup.referenceDepth();  // :135
+      if (pileup.elements.empty() || pileupAltReads < params->min_alt_reads) return;
+      if (params->respect_active_regions) {  // isActiveRegion (AssemblyUtils.scala:28-39)
+        int n = 0;
+        for (auto& e : pileup.elements)
+          n += e.pe.read->countOfMismatches(*pileup.contigSequence) > 1 || e.pe.read->cigarElements.size() > 1;
+        if ((float)n / (float)pileup.elements.size() > params->min_area_vaf) {
+          active.push_back(pileup.contig);
+          active.push_back(pileup.locus);
+          return;
+        }
+      }
+      // callPileupVariant (:233-261)
+      auto gp = probabilitiesOfAllPossibleGenotypesFromPileup(pileup, false, true);
+      if (gp.empty()) return;
+      size_t best = 0;
+      for (size_t i = 1; i < gp.size(); ++i)
+        if (gp[i].second > gp[best].second) best = i;  // maxBy: first of equal maxima
+      const double probability = std::exp(gp[best].second);
+      std::vector<Allele> seen;
+      for (auto& af : gp[best].first.alleleMixture) {
+        const Allele& a = af.first;
+        if (!a.isVariant() || a.altBases.empty()) continue;
+        if (std::find(seen.begin(), seen.end(), a) != seen.end()) continue;
+        seen.push_back(a);
+        AlleleEvidence ev = makeAlleleEvidence(probability, a, pileup);
+        if (!(ev.phredScaledLikelihood() > params->min_phred_scaled_likelihood)) continue;  // :147
+        guac_called_allele c;
+        std::memset(&c, 0, sizeof c);
+        c.contig_id = pileup.contig;
+        c.start = pileup.locus;
+        c.ref_off = (uint32_t)arena.size();
+        c.ref_len = (uint32_t)a.refBases.size();
+        arena += a.refBases;
+        c.alt_off = (uint32_t)arena.size();
+        c.alt_len = (uint32_t)a.altBases.size();
+        arena += a.altBases;
+        c.genotype_log_probability = gp[best].second;
+        c.n_genotypes = (int32_t)gp.size();
+        c.evidence = toC(ev);
+        calls.push_back(c);
+      }
+    });
+    *out_calls = toC(calls);
+    *n_calls = (int64_t)calls.size();
+    *out_arena = (char*)std::malloc(arena.size() + 1);
+    std::memcpy(*out_arena, arena.c_str(), arena.size() + 1);
+    *arena_len = (int64_t)arena.size();
+    *out_active = toC(active);
+    *n_active = (int64_t)active.size() / 2;
+    if (out_n_visited) *out_n_visited = visited;
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}

@@ -284,3 +284,21 @@ def pileup_stats(batch, reference, contig, locus, ref_seq, mixtures=(), sample=0
             a, c = l.rsplit("=", 1)
             depths.append((a, int(c)))
     return total, depths, lls
+
+
+def germline_standard(batch: ReadBatch, reference: Reference, ranges, params=None):
+    """The germline toy caller (shortcut branch of discoverGermlineVariants) over one partition."""
+    from guacamole_b200.native import CALLED_ALLELE_DTYPE, gs_params
+    params = params or gs_params()
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    r = make_ranges(ranges)
+    calls, n, arena, alen, act, na, nv = (C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(),
+                                          C.c_int64())
+    _check(lib().oracle_germline_standard(C.byref(b), cs, nc, C.byref(params), r, len(ranges), C.byref(calls), C.byref(n),
+                                          C.byref(arena), C.byref(alen), C.byref(act), C.byref(na), C.byref(nv)))
+    arena_b = C.string_at(arena, alen.value)
+    lib().oracle_free(arena)
+    active = _take(act, np.int64, na.value * 2).reshape(-1, 2)
+    return dict(calls=_take(calls, CALLED_ALLELE_DTYPE, n.value), arena=arena_b,
+                active_loci=[(int(a), int(b)) for a, b in active], n_visited=nv.value)

@@ -95,3 +95,20 @@ def test_joint_calls_on_synthetic_four_samples_are_partition_invariant():
         parts += oracle.somatic_joint(batch, ref, [(0, a, b)], sj.sj_params(kinds))[0]
     key = lambda e: (e["start"], e["ref"], e["alt"], e["is_germline_call"], e["is_somatic_call"])
     assert [key(e) for e in parts] == [key(e) for e in whole]
+
+
+def test_germline_toy_caller_finds_planted_variants():
+    """callPileupVariant (GermlineAssemblyCaller.scala:233-261) on a seeded 30x sample: planted germline SNVs
+    (1 per kbp) are called, and the called genotype probability is a normalised probability."""
+    from guacamole_b200 import synth
+    from guacamole_b200.commands.somatic_standard import alleles_of
+    contig_len, seed = 30000, 2000
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, (30,), (False,), seed)
+    out = oracle.germline_standard(batch, ref, [(0, 0, contig_len)])
+    gk, _, _, _ = synth.site_info(seed, np.arange(contig_len))
+    planted = set(np.flatnonzero(gk > 0)[np.flatnonzero(gk > 0) < contig_len - 300].tolist())
+    called = set(int(x) for x in out["calls"]["start"])
+    assert len(planted) > 10 and len(planted - called) <= 2  # a het site can lose by chance at 30x
+    assert np.all(out["calls"]["genotype_log_probability"] <= 1e-12)
+    assert all(len(r) == 1 and len(a) >= 1 for r, a in alleles_of(out) if len(r) == 1)
