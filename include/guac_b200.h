@@ -306,6 +306,21 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
                            guac_called_allele** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
                            int64_t** out_active_loci, int64_t* n_active, int64_t* out_n_visited);
 
+/* ---- germline-assembly ---------------------------------------------------------
+ * M/assembly/AssemblyArgs.scala:13-45 and GermlineAssemblyCaller.Arguments (M/commands/GermlineAssemblyCaller.scala:33-47). */
+typedef struct {
+  int32_t sample_id;
+  int32_t kmer_size;                   /* --kmer-size, default 45 */
+  int32_t assembly_window_range;       /* --assembly-window-range (= halfWindowSize), default 20; must exceed kmer_size */
+  int32_t min_occurrence;              /* --min-occurrence, default 3 */
+  int32_t min_mean_kmer_quality;       /* --min-mean-kmer-quality, default 0 */
+  int32_t min_alt_reads;               /* 2 */
+  int32_t min_phred_scaled_likelihood; /* --min-likelihood, default 0 */
+  int32_t shortcut_assembly;           /* --shortcut-assembly */
+  float min_area_vaf;                  /* --min-area-vaf percent / 100.0f */
+  int32_t _pad;
+} guac_ga_params;
+
 /* ---- somatic-joint ----------------------------------------------------------
  * M/jointcaller/Parameters.scala:10-25 plus the inputs (M/jointcaller/Input.scala, InputCollection.scala:55-101)
  * and the flags of M/commands/SomaticJointCaller.scala:154-163. */

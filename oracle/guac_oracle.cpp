@@ -788,3 +788,215 @@ extern "C" int oracle_germline_standard(const oracle_reads* b, const oracle_cont
     return -1;
   }
 }
+
+// ---------------------------------------------------------------------------------
+// germline-assembly: De Bruijn graph, alignment and the caller closure
+// ---------------------------------------------------------------------------------
+#include "guac_oracle_assembly.hpp"
+
+namespace {
+std::vector<MappedRead> readsFromText(const char* seqs, int n, const uint8_t* quals /* may be null: Phred 31 */) {
+  std::vector<MappedRead> reads((size_t)n);
+  const char* t = seqs;
+  size_t qoff = 0;
+  for (int i = 0; i < n; ++i) {
+    reads[i].sequence = t;
+    t += reads[i].sequence.size() + 1;
+    const size_t L = reads[i].sequence.size();
+    if (quals) reads[i].baseQualities.assign(quals + qoff, quals + qoff + L);
+    else reads[i].baseQualities.assign(L, 31);
+    qoff += L;
+    reads[i].index = i;
+  }
+  return reads;
+}
+char* dupText(const std::string& s) {
+  char* p = (char*)std::malloc(s.size() + 1);
+  std::memcpy(p, s.c_str(), s.size() + 1);
+  return p;
+}
+}  // namespace
+
+// De Bruijn graph probe.  op: 0 kmerCounts ("kmer=count" lines), 1 depthFirstSearch(source, sink) merged path sequences,
+// 2 mergeForward(source) k-mers, 3 mergeBackward(source) k-mers, 4 mergeIndex of every k-mer of `source` ("kmer=merged:idx").
+extern "C" int oracle_debruijn(const char* seqs, int n_reads, const uint8_t* quals, int kmer_size, int min_occurrence,
+                               int min_mean_kmer_quality, int merge_nodes, int op, const char* source, const char* sink, int max_paths,
+                               char** out_text) {
+  try {
+    auto reads = readsFromText(seqs, n_reads, quals);
+    std::vector<const MappedRead*> rp;
+    for (auto& r : reads) rp.push_back(&r);
+    DeBruijnGraph g = buildGraph(rp, kmer_size, min_occurrence, min_mean_kmer_quality, merge_nodes != 0);
+    std::string text;
+    if (op == 0) {
+      for (auto& kv : g.kmerCounts) text += kv.first + "=" + std::to_string(kv.second) + "\n";
+    } else if (op == 1) {
+      for (auto& p : g.depthFirstSearch(source, sink, 1, std::numeric_limits<int>::max(), max_paths))
+        text += DeBruijnGraph::mergeOverlappingSequences(p, kmer_size) + "\n";
+    } else if (op == 2 || op == 3) {
+      for (auto& k : (op == 2 ? g.mergeForward(source) : g.mergeBackward(source))) text += k + "\n";
+    } else if (op == 4) {
+      std::string s(source);
+      for (size_t i = 0; i + kmer_size <= s.size(); ++i) {
+        auto it = g.mergeIndex.find(s.substr(i, kmer_size));
+        text += s.substr(i, kmer_size) + "=" + (it == g.mergeIndex.end() ? std::string("-") : it->second.first + ":" + std::to_string(it->second.second)) + "\n";
+      }
+    }
+    *out_text = dupText(text);
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// ReadAlignment(sequence, reference): "cigar\trefStartIdx\trefEndIdx\talignmentScore\trawScore"
+extern "C" int oracle_read_alignment(const char* sequence, const char* reference, double mismatch_p, double open_gap_p, double close_gap_p,
+                                     char** out_text) {
+  try {
+    ReadAlignmentResult r = mismatch_p > 0 ? readAlignment(sequence, reference, mismatch_p, open_gap_p, close_gap_p) : readAlignment(sequence, reference);
+    char buf[64];
+    snprintf(buf, sizeof buf, "%.17g", r.rawScore);
+    *out_text = dupText(r.toCigarString() + "\t" + std::to_string(r.refStartIdx) + "\t" + std::to_string(r.refEndIdx) + "\t" +
+                        std::to_string(r.alignmentScore) + "\t" + buf);
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+// GermlineAssemblyCaller.discoverGermlineVariants (M/commands/GermlineAssemblyCaller.scala:84-230) over one partition, one sample.
+// Output text, one line per emitted CalledAllele in emission order (variants of a window sorted by (locus, ref, alt)):
+//   "A\tcontig\tlocus\tref\talt\tdepth\tmeanMapq\tmedianMapq\tmeanBaseQ\tmedianBaseQ"   assembled
+//   "P\tcontig\tlocus\tref\talt\tprobability\tdepth\talleleDepth"                         toy caller (shortcut)
+//   "W\tcontig\tlocus\tnPaths"                                                             every assembled window
+extern "C" int oracle_germline_assembly(const oracle_reads* b, const oracle_contig* contigs, int n_contigs, const guac_ga_params* P,
+                                        const guac_range* loci, int n_loci, char** out_text) {
+  try {
+    auto all_reads = buildReads(b);
+    std::vector<MappedRead> reads;
+    for (auto& r : all_reads)
+      if (r.sampleId == P->sample_id) reads.push_back(r);
+    auto cs = buildContigs(contigs, n_contigs);
+    auto ranges = buildRanges(loci, n_loci);
+    std::string text;
+    char buf[256];
+    std::vector<int32_t> contigOrder;
+    for (auto& r : ranges)
+      if (std::find(contigOrder.begin(), contigOrder.end(), r.contig) == contigOrder.end()) contigOrder.push_back(r.contig);
+    const int W = P->assembly_window_range, K = P->kmer_size;
+    for (int32_t contig : contigOrder) {
+      std::vector<std::pair<int64_t, int64_t>> rs;
+      for (auto& r : ranges)
+        if (r.contig == contig) rs.push_back({r.start, r.end});
+      std::sort(rs.begin(), rs.end());
+      const ContigSequence* c = nullptr;
+      for (auto& x : cs)
+        if (x.contig_id == contig) c = &x;
+      std::vector<const MappedRead*> sampleReads;
+      for (auto& r : reads)
+        if (r.contig == contig) sampleReads.push_back(&r);
+      if (!c) {
+        if (sampleReads.empty()) continue;
+        throw InvalidInput("contig not found in reference");
+      }
+      std::vector<SlidingWindow> windows(1);
+      windows[0].halfWindowSize = W;
+      windows[0].sortedRegions = &sampleReads;
+      LociIterator it(rs);
+      bool haveLast = false;
+      int64_t lastCalledLocus = 0;
+      while (advanceMultipleWindows(windows, it, true) >= 0) {
+        SlidingWindow& window = windows[0];
+        const int64_t locus = window.currentLocus;
+        const int referenceStart = (int)(locus - W), referenceEnd = (int)(locus + W);
+        auto regionReads = window.currentRegions();
+        std::vector<const MappedRead*> currentLocusReads;
+        for (auto* r : regionReads)
+          if (r->overlapsLocus(locus)) currentLocusReads.push_back(r);
+        if (currentLocusReads.empty()) continue;
+        const std::string currentReference = c->slice(referenceStart, referenceEnd);  // :108-116 (evaluated before the early outs)
+        Pileup pileup = Pileup::make(currentLocusReads, 0, contig, locus, *c);
+        const int pileupAltReads = pileup.depth() - pileup.referenceDepth();
+        if (pileupAltReads < P->min_alt_reads) continue;
+        bool active = true;
+        if (P->shortcut_assembly) {  // isActiveRegion (AssemblyUtils.scala:28-39)
+          int n = 0;
+          for (auto* r : currentLocusReads) n += r->countOfMismatches(*c) > 1 || r->cigarElements.size() > 1;
+          active = (float)n / (float)currentLocusReads.size() > P->min_area_vaf;
+        }
+        if (!active) {  // callPileupVariant (:139-153)
+          auto gp = probabilitiesOfAllPossibleGenotypesFromPileup(pileup, false, true);
+          if (gp.empty()) continue;
+          size_t best = 0;
+          for (size_t i = 1; i < gp.size(); ++i)
+            if (gp[i].second > gp[best].second) best = i;
+          const double probability = std::exp(gp[best].second);
+          std::vector<Allele> seen;
+          bool any = false;
+          for (auto& af : gp[best].first.alleleMixture) {
+            const Allele& a = af.first;
+            if (!a.isVariant() || a.altBases.empty() || std::find(seen.begin(), seen.end(), a) != seen.end()) continue;
+            seen.push_back(a);
+            AlleleEvidence ev = makeAlleleEvidence(probability, a, pileup);
+            if (!(ev.phredScaledLikelihood() > P->min_phred_scaled_likelihood)) continue;
+            snprintf(buf, sizeof buf, "P\t%d\t%lld\t%s\t%s\t%.17g\t%d\t%d\n", contig, (long long)locus, a.refBases.c_str(), a.altBases.c_str(),
+                     probability, ev.readDepth, ev.alleleReadDepth);
+            text += buf;
+            any = true;
+          }
+          if (any) {
+            haveLast = true;
+            lastCalledLocus = locus;
+          }
+          continue;
+        }
+        // discoverHaplotypes over the whole window's reads (AssemblyUtils.scala:50-114)
+        auto paths = discoverHaplotypes(regionReads, currentReference, K, P->min_occurrence, P->min_mean_kmer_quality);
+        snprintf(buf, sizeof buf, "W\t%d\t%lld\t%d\n", contig, (long long)locus, (int)paths.size());
+        text += buf;
+        if (paths.empty()) continue;
+        std::set<AssemblyVariant> variants;
+        for (auto& path : paths)
+          for (auto& v : buildVariantsFromPath(path, referenceStart, *c, currentReference))
+            if (!haveLast || lastCalledLocus < v.locus) variants.insert(v);  // :205-209
+        // window-wide evidence (:162-192): Float means / medians over all reads' mapq and all bases' qualities
+        std::vector<double> mq, bq;
+        for (auto* r : regionReads) {
+          mq.push_back((float)r->alignmentQuality);
+          for (uint8_t q : r->baseQualities) bq.push_back((float)q);
+        }
+        auto meanF = [](const std::vector<double>& v) {
+          float mu = 0;
+          long n = 0;
+          for (double y : v) {
+            n += 1;
+            mu = mu + 1.0f / n * ((float)y - mu);
+          }
+          return (double)mu;
+        };
+        auto medianF = [](std::vector<double> v) {
+          std::sort(v.begin(), v.end());
+          const size_t n = v.size();
+          return n % 2 ? v[(n - 1) / 2] : (double)(((float)v[n / 2 - 1] + (float)v[n / 2]) / 2);
+        };
+        for (auto& v : variants) {
+          snprintf(buf, sizeof buf, "A\t%d\t%lld\t%s\t%s\t%d\t%.9g\t%.9g\t%.9g\t%.9g\n", contig, (long long)v.locus, v.ref.c_str(), v.alt.c_str(),
+                   (int)regionReads.size(), meanF(mq), medianF(mq), meanF(bq), medianF(bq));
+          text += buf;
+          if (!haveLast || v.locus > lastCalledLocus) {
+            haveLast = true;
+            lastCalledLocus = std::max(lastCalledLocus, v.locus);
+          }
+        }
+        window.setCurrentLocus(window.currentLocus + W - K);  // :213 (throws when W < K: "window can only move forward")
+      }
+    }
+    *out_text = dupText(text);
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}

@@ -302,3 +302,65 @@ def germline_standard(batch: ReadBatch, reference: Reference, ranges, params=Non
     active = _take(act, np.int64, na.value * 2).reshape(-1, 2)
     return dict(calls=_take(calls, CALLED_ALLELE_DTYPE, n.value), arena=arena_b,
                 active_loci=[(int(a), int(b)) for a, b in active], n_visited=nv.value)
+
+
+class GAParamsC(C.Structure):
+    _fields_ = [("sample_id", C.c_int32), ("kmer_size", C.c_int32), ("assembly_window_range", C.c_int32), ("min_occurrence", C.c_int32),
+                ("min_mean_kmer_quality", C.c_int32), ("min_alt_reads", C.c_int32), ("min_phred_scaled_likelihood", C.c_int32),
+                ("shortcut_assembly", C.c_int32), ("min_area_vaf", C.c_float), ("_pad", C.c_int32)]
+
+
+def ga_params(sample_id=0, kmer_size=45, assembly_window_range=20, min_occurrence=3, min_mean_kmer_quality=0, min_alt_reads=2,
+              min_phred_scaled_likelihood=0, shortcut_assembly=False, min_area_vaf_percent=5):
+    p = GAParamsC()
+    p.sample_id, p.kmer_size, p.assembly_window_range = sample_id, kmer_size, assembly_window_range
+    p.min_occurrence, p.min_mean_kmer_quality, p.min_alt_reads = min_occurrence, min_mean_kmer_quality, min_alt_reads
+    p.min_phred_scaled_likelihood, p.shortcut_assembly = min_phred_scaled_likelihood, int(shortcut_assembly)
+    p.min_area_vaf = float(np.float32(min_area_vaf_percent) / np.float32(100.0))
+    return p
+
+
+def _text_call(fn, *args):
+    text = C.c_void_p()
+    _check(fn(*args, C.byref(text)))
+    s = C.string_at(text).decode()
+    lib().oracle_free(text)
+    return [l for l in s.split("\n") if l]
+
+
+def debruijn(sequences, kmer_size, op, min_occurrence=1, min_mean_kmer_quality=0, merge_nodes=False, qualities=None, source="",
+             sink="", max_paths=10):
+    """De Bruijn graph probe: op 'counts' | 'dfs' | 'forward' | 'backward' | 'merge_index'."""
+    ops = {"counts": 0, "dfs": 1, "forward": 2, "backward": 3, "merge_index": 4}
+    seqs = b"".join(s.encode() + b"\0" for s in sequences)
+    q = None
+    if qualities is not None:
+        qa = np.array([x for qs in qualities for x in qs], np.uint8)
+        q = ptr(qa, u8p)
+    lines = _text_call(lib().oracle_debruijn, seqs, len(sequences), q, kmer_size, min_occurrence, min_mean_kmer_quality, int(merge_nodes),
+                       ops[op], source.encode(), sink.encode(), max_paths)
+    if op == "counts":
+        return {l.split("=")[0]: int(l.split("=")[1]) for l in lines}
+    if op == "merge_index":
+        return [(l.split("=")[0], l.split("=")[1]) for l in lines]
+    return lines
+
+
+def read_alignment(sequence, reference, mismatch_probability=0.0, open_gap_probability=0.0, close_gap_probability=0.0):
+    """ReadAlignment(sequence, reference) -> (cigar, refStartIdx, refEndIdx, alignmentScore, rawScore); zeros = defaults."""
+    l = _text_call(lib().oracle_read_alignment, sequence.encode(), reference.encode(), C.c_double(mismatch_probability),
+                   C.c_double(open_gap_probability), C.c_double(close_gap_probability))
+    f = (l[0] if l else "\t0\t0\t0\t0").split("\t")
+    return f[0], int(f[1]), int(f[2]), int(f[3]), float(f[4])
+
+
+def germline_assembly(batch: ReadBatch, reference: Reference, ranges, params):
+    """discoverGermlineVariants -> list of tuples: ('A', contig, locus, ref, alt, depth, ...), ('P', ...), ('W', contig, locus, nPaths)."""
+    cs, nc = _contigs(reference, batch.contig_names)
+    b = _reads(batch)
+    r = make_ranges(ranges)
+    out = []
+    for l in _text_call(lib().oracle_germline_assembly, C.byref(b), cs, nc, C.byref(params), r, len(ranges)):
+        f = l.split("\t")
+        out.append(tuple([f[0], int(f[1]), int(f[2])] + f[3:]))
+    return out
