@@ -13,6 +13,7 @@
 #include <map>
 #include <set>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../include/guac_b200.h"
@@ -22,6 +23,7 @@
 #include "tile_kernels.cuh"
 #include "joint_host.hpp"
 #include "germline_kernels.cuh"
+#include "assembly_kernels.cuh"
 
 using namespace guac;
 
@@ -293,6 +295,19 @@ int check_device_error(guac_ctx* ctx) {
     case DERR_MISMATCH_HIST:
       snprintf(buf, sizeof buf, "read %lld has more than %d mismatches (library limit)", e.read_index, MM_BINS - 1);
       return fail(ctx, GUAC_E_UNSUPPORTED, buf);
+    case DERR_ASM_BASE:
+      snprintf(buf, sizeof buf, "read %lld in the assembly window at %d:%lld has a base other than A, C, G, T, N (library limit)", e.read_index,
+               e.contig_id, e.locus);
+      return fail(ctx, GUAC_E_UNSUPPORTED, buf);
+    case DERR_ASM_COLLISION:
+      snprintf(buf, sizeof buf, "two k-mers of the assembly window at %d:%lld share a 64-bit hash (library limit)", e.contig_id, e.locus);
+      return fail(ctx, GUAC_E_UNSUPPORTED, buf);
+    case DERR_ASM_CAPACITY:
+      snprintf(buf, sizeof buf, "the assembly graph of the window at %d:%lld exceeds the per-window scratch (library limit)", e.contig_id,
+               e.locus);
+      return fail(ctx, GUAC_E_UNSUPPORTED, buf);
+    case DERR_ASM_CIGAR:
+      return fail(ctx, GUAC_E_UNSUPPORTED, "a haplotype alignment has more than 64 CIGAR elements (library limit)");
   }
   return fail(ctx, GUAC_E_CUDA, "unknown device error");
 }
@@ -1620,3 +1635,5 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 }
 
 }  // extern "C"
+
+#include "assembly_entry.inl"

@@ -109,6 +109,27 @@ SS_CALL_DTYPE = np.dtype([("contig_id", np.int32), ("_pad", np.int32), ("start",
                           ("tumor_alt_log_prob", np.float64), ("normal_ref_log_prob", np.float64),
                           ("normal_alt_log_prob", np.float64), ("tumor_variant_evidence", np.dtype(_EV)),
                           ("normal_reference_evidence", np.dtype(_EV))])
+class GAParamsC(C.Structure):
+    _fields_ = [("sample_id", C.c_int32), ("kmer_size", C.c_int32), ("assembly_window_range", C.c_int32), ("min_occurrence", C.c_int32),
+                ("min_mean_kmer_quality", C.c_int32), ("min_alt_reads", C.c_int32), ("min_phred_scaled_likelihood", C.c_int32),
+                ("shortcut_assembly", C.c_int32), ("min_area_vaf", C.c_float), ("_pad", C.c_int32)]
+
+
+def ga_params(sample_id=0, kmer_size=45, assembly_window_range=20, min_occurrence=3, min_mean_kmer_quality=0, min_alt_reads=2,
+              min_phred_scaled_likelihood=0, shortcut_assembly=False, min_area_vaf_percent=5):
+    """Defaults of AssemblyArgs (assembly/AssemblyArgs.scala:13-45) and GermlineAssemblyCaller.Arguments
+    (commands/GermlineAssemblyCaller.scala:33-47,92).  The reference's own defaults (range 20 < k-mer 45) make its window
+    jump move backward after the first assembled window; its tests run with range 120, k-mer 47."""
+    p = GAParamsC()
+    p.sample_id, p.kmer_size, p.assembly_window_range = sample_id, kmer_size, assembly_window_range
+    p.min_occurrence, p.min_mean_kmer_quality, p.min_alt_reads = min_occurrence, min_mean_kmer_quality, min_alt_reads
+    p.min_phred_scaled_likelihood, p.shortcut_assembly = min_phred_scaled_likelihood, int(shortcut_assembly)
+    p.min_area_vaf = float(np.float32(min_area_vaf_percent) / np.float32(100.0))
+    return p
+
+
+ASSEMBLED_WINDOW_DTYPE = np.dtype([("contig_id", np.int32), ("n_paths", np.int32), ("locus", np.int64), ("n_graph_nodes", np.int32),
+                                   ("consumed", np.int32)])
 LOCUS_SUMMARY_DTYPE = np.dtype([("depth", np.uint16), ("reference_depth", np.uint16), ("top_alt_count", np.uint16),
                                 ("flags", np.uint16)])
 CALLED_ALLELE_DTYPE = np.dtype([("contig_id", np.int32), ("n_genotypes", np.int32), ("start", np.int64), ("ref_off", np.uint32),
@@ -385,6 +406,20 @@ class Context:
         active = _take(self.lib, self.ctx, act, np.int64, na.value * 2).reshape(-1, 2)
         return dict(calls=_take(self.lib, self.ctx, calls, CALLED_ALLELE_DTYPE, n.value), arena=arena_b,
                     active_loci=[(int(a), int(b)) for a, b in active], n_visited=nv.value)
+
+    def germline_assembly(self, ranges: Sequence[Tuple[int, int, int]], params: Optional["GAParamsC"] = None):
+        """guac_germline_assembly -> dict(calls, arena, windows, n_visited); assembled calls have n_genotypes == 0."""
+        params = params or ga_params()
+        r = make_ranges(ranges)
+        calls, n, arena, alen = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64()
+        wins, nw, nv = C.c_void_p(), C.c_int64(), C.c_int64()
+        self._check(self.lib.guac_germline_assembly(self.ctx, C.byref(params), r, C.c_int32(len(ranges)), C.byref(calls), C.byref(n),
+                                                    C.byref(arena), C.byref(alen), C.byref(wins), C.byref(nw), C.byref(nv)))
+        arena_b = C.string_at(arena, alen.value) if arena else b""
+        if arena:
+            self.lib.guac_free(self.ctx, arena)
+        return dict(calls=_take(self.lib, self.ctx, calls, CALLED_ALLELE_DTYPE, n.value), arena=arena_b,
+                    windows=_take(self.lib, self.ctx, wins, ASSEMBLED_WINDOW_DTYPE, nw.value), n_visited=nv.value)
 
     def somatic_joint(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
         """guac_somatic_joint -> (list of per-allele evidence dicts, loci visited); see commands/somatic_joint.py."""

@@ -311,7 +311,7 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
 typedef struct {
   int32_t sample_id;
   int32_t kmer_size;                   /* --kmer-size, default 45 */
-  int32_t assembly_window_range;       /* --assembly-window-range (= halfWindowSize), default 20; must exceed kmer_size */
+  int32_t assembly_window_range;       /* --assembly-window-range (= halfWindowSize), default 20; must be >= kmer_size */
   int32_t min_occurrence;              /* --min-occurrence, default 3 */
   int32_t min_mean_kmer_quality;       /* --min-mean-kmer-quality, default 0 */
   int32_t min_alt_reads;               /* 2 */
@@ -320,6 +320,34 @@ typedef struct {
   float min_area_vaf;                  /* --min-area-vaf percent / 100.0f */
   int32_t _pad;
 } guac_ga_params;
+
+/* One assembled window (the half-open reference slice [locus - range, locus + range) around a candidate locus). */
+typedef struct {
+  int32_t contig_id;
+  int32_t n_paths;       /* haplotypes AssemblyUtils.discoverHaplotypes returns: 0 = no path, or more than 16 */
+  int64_t locus;
+  int32_t n_graph_nodes; /* k-mers with count >= min_occurrence */
+  int32_t consumed;      /* 1: the reference's walk visits this window; 0: assembled speculatively, then skipped by
+                            the window jump of an earlier successful assembly */
+} guac_assembled_window;
+
+/*
+ * germline-assembly: windowFlatMapWithState(halfWindowSize = assembly_window_range, skipEmpty = true) over one
+ * sample with the closure of GermlineAssemblyCaller.discoverGermlineVariants
+ * (M/commands/GermlineAssemblyCaller.scala:84-219): loci with fewer than min_alt_reads non-reference reads are
+ * skipped; with shortcut_assembly, loci whose reads are not an active region (M/assembly/AssemblyUtils.scala:28-39)
+ * go to the toy caller (guac_germline_standard); the others are assembled — De Bruijn graph of the window's reads
+ * (M/assembly/DeBruijnGraph.scala:342-373), unipath merge (:91-126), depth-first search from the first to the last
+ * reference k-mer (:183-300), paths scored against the reads when there are more than two
+ * (M/assembly/AssemblyUtils.scala:50-114), each kept path aligned to the reference slice
+ * (M/alignment/ReadAlignment.scala:64-195) and turned into variants (AssemblyUtils.scala:127-174).
+ * Assembled calls carry n_genotypes = 0 and the window-wide evidence of :162-192.  The partition state
+ * (lastCalledLocus, the jump by range - kmer_size) is that of one partition per contig: call once per
+ * LociPartitioning partition to reproduce a partitioned run.
+ */
+int guac_germline_assembly(guac_ctx* ctx, const guac_ga_params* params, const guac_range* loci, int32_t n_ranges,
+                           guac_called_allele** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
+                           guac_assembled_window** out_windows, int64_t* n_windows, int64_t* out_n_visited);
 
 /* ---- somatic-joint ----------------------------------------------------------
  * M/jointcaller/Parameters.scala:10-25 plus the inputs (M/jointcaller/Input.scala, InputCollection.scala:55-101)

@@ -1,0 +1,100 @@
+"""GPU parity for the germline-assembly caller (De Bruijn graph + DFS + affine-gap alignment per active window),
+through the C ABI, against the oracle's restatement of GermlineAssemblyCaller.discoverGermlineVariants.
+
+The reference's own end-to-end suite (GermlineAssemblyCallerSuite) needs a BAM and a FASTA that are not in the
+checkout, so the closure is compared on seeded synthetic reads with planted SNVs and indels; the graph and
+alignment pieces are pinned to the reference's unit vectors in tests/test_oracle_assembly.py.
+"""
+import numpy as np
+import pytest
+
+from guacamole_b200 import synth
+from guacamole_b200.native import ga_params
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+
+# GermlineAssemblyCallerSuite.verifyVariantsAtLocus parameters (kmerSize 47, assemblyWindowRange 120, minOccurrence 5,
+# minMeanKmerQuality 20, minAreaVaf 0.1)
+SUITE = dict(kmer_size=47, assembly_window_range=120, min_occurrence=5, min_mean_kmer_quality=20, min_area_vaf_percent=10)
+
+
+def decode(result):
+    arena = result["arena"]
+    rows = []
+    for c in result["calls"]:
+        ref = arena[c["ref_off"]:c["ref_off"] + c["ref_len"]].decode()
+        alt = arena[c["alt_off"]:c["alt_off"] + c["alt_len"]].decode()
+        rows.append((int(c["n_genotypes"]) == 0, int(c["contig_id"]), int(c["start"]), ref, alt, c))
+    return rows
+
+
+def assert_assembly_equal(got, want):
+    want_windows = [(w[1], w[2], int(w[3])) for w in want if w[0] == "W"]
+    got_windows = [(int(w["contig_id"]), int(w["locus"]), int(w["n_paths"])) for w in got["windows"] if w["consumed"]]
+    assert got_windows == want_windows
+    rows = decode(got)
+    want_a = [w for w in want if w[0] == "A"]
+    got_a = [r for r in rows if r[0]]
+    assert [(r[1], r[2], r[3], r[4]) for r in got_a] == [(w[1], w[2], w[3], w[4]) for w in want_a]
+    for r, w in zip(got_a, want_a):
+        ev = r[5]["evidence"]
+        assert ev["probability"] == 1.0 and ev["median_mismatches_per_read"] == 0.0
+        assert ev["read_depth"] == ev["allele_read_depth"] == ev["forward_depth"] == ev["allele_forward_depth"] == int(w[5])
+        # breeze's Float running means depend on the order of the window queue (a heap in the reference, batch order
+        # here): equal to Float rounding; the medians are order-free and exact
+        np.testing.assert_allclose(ev["mean_mapping_quality"], float(w[6]), rtol=2e-5)
+        assert ev["median_mapping_quality"] == float(w[7])
+        np.testing.assert_allclose(ev["mean_base_quality"], float(w[8]), rtol=2e-5)
+        assert ev["median_base_quality"] == float(w[9])
+    want_p = [w for w in want if w[0] == "P"]
+    got_p = [r for r in rows if not r[0]]
+    assert [(r[1], r[2], r[3], r[4]) for r in got_p] == [(w[1], w[2], w[3], w[4]) for w in want_p]
+    for r, w in zip(got_p, want_p):
+        np.testing.assert_allclose(r[5]["evidence"]["probability"], float(w[5]), rtol=1e-9)
+        assert (r[5]["evidence"]["read_depth"], r[5]["evidence"]["allele_read_depth"]) == (int(w[6]), int(w[7]))
+
+
+@pytest.mark.parametrize("shortcut", [False, True])
+@pytest.mark.parametrize("seed,coverage", [(2000, 30), (2001, 60)])
+def test_synthetic_single_sample(gpu_ctx, seed, coverage, shortcut):
+    contig_len = 20000
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, (coverage,), (False,), seed)
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    p = ga_params(shortcut_assembly=shortcut, **SUITE)
+    ranges = [(0, 200, contig_len - 200)]
+    want = oracle.germline_assembly(batch, ref, ranges, p)
+    assert sum(1 for w in want if w[0] == "A") >= 5 and sum(1 for w in want if w[0] == "W") >= 20
+    got = gpu_ctx.germline_assembly(ranges, p)
+    assert_assembly_equal(got, want)
+    # speculative windows: everything the reference's walk consumed was assembled, plus the ones its jumps skip
+    assert len(got["windows"]) >= sum(1 for w in want if w[0] == "W")
+
+
+def test_small_kmer_many_paths(gpu_ctx):
+    """A short k-mer and minOccurrence 1 keep sequencing errors in the graph: several paths per window, so the
+    read-vs-path scoring of AssemblyUtils.scala:92-104 and the too-many-paths cut-off are exercised."""
+    contig_len, seed = 6000, 2100
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, (30,), (False,), seed)
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    p = ga_params(kmer_size=21, assembly_window_range=60, min_occurrence=1, min_mean_kmer_quality=0, min_area_vaf_percent=10)
+    ranges = [(0, 100, contig_len - 100)]
+    want = oracle.germline_assembly(batch, ref, ranges, p)
+    n_paths = [int(w[3]) for w in want if w[0] == "W"]
+    assert any(n == 2 for n in n_paths)
+    got = gpu_ctx.germline_assembly(ranges, p)
+    assert_assembly_equal(got, want)
+
+
+def test_rejects_backward_jump(gpu_ctx):
+    contig_len, seed = 2000, 2000
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, (30,), (False,), seed)
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    with pytest.raises(Exception, match="can only move forward"):
+        gpu_ctx.germline_assembly([(0, 200, 1800)], ga_params())  # the reference's defaults: range 20 < k-mer 45
