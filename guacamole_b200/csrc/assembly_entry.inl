@@ -83,7 +83,7 @@ __global__ void asm_score_jobs_kernel(ReadsView R, const AsmWindow* __restrict__
   const AsmWindow& w = wins[which[i]];
   int64_t j = job_base[i];
   for (int64_t r = w.read_lo; r < w.read_hi; ++r) {
-    if (!asm_in_window(R, r, P.sample, w.locus, P.W)) continue;
+    if (!asm_in_window(R, r, P, w.locus)) continue;
     for (int p = 0; p < w.n_paths; ++p) {
       AsmAlignJob job;
       job.seq = r;
@@ -102,16 +102,25 @@ __global__ void asm_score_jobs_kernel(ReadsView R, const AsmWindow* __restrict__
 
 size_t asm_align_smem(int S) { return (size_t)3 * (S + 1) * (sizeof(double) + sizeof(int32_t) + 1) + S + 16; }
 
-// Assembles windows [w0, w1) of `windows`; results appended to `results`.
-int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmWindow>& windows, size_t w0, size_t w1,
-                   std::vector<AsmWindowResult>& results) {
+struct AsmStage {  // device and host state of one batch of windows once their graphs have been walked
   DevTmp tmp;
-  const int n = (int)(w1 - w0);
-  const int K = params->kmer_size, W = params->assembly_window_range;
-  AsmParams P{params->sample_id, K, W, params->min_occurrence, params->min_mean_kmer_quality, ASM_MAX_PATHS};
+  AsmParams P{};
   AsmWindow* d_win = nullptr;
+  uint8_t* d_strings = nullptr;  // [path strings | window reference slices, each preceded by one base]
+  int64_t path_bytes = 0;
+  int ref_stride = 0;
+  std::vector<uint8_t> strings;  // host copy of d_strings
+  std::vector<AsmEvidence> ev;
+};
+
+// k-mer tables -> ranked graph -> unipath merge + DFS for the n windows at `h` (updated in place with the path lengths).
+// `custom_ref` (P.ref_len bytes) replaces the contig's reference slice for a single window given by the caller.
+int build_paths(guac_ctx* ctx, AsmStage& st, AsmWindow* h, int n, const uint8_t* custom_ref) {
+  DevTmp& tmp = st.tmp;
+  const AsmParams& P = st.P;
+  const int K = P.K;
+  AsmWindow*& d_win = st.d_win;
   GUAC_TRY(tmp.alloc(ctx, &d_win, (size_t)n));
-  AsmWindow* h = windows.data() + w0;
   const size_t win_bytes = (size_t)n * sizeof(AsmWindow);
   DeviceError* d_err = ctx->b_err.as<DeviceError>();
   CUDA_TRY(ctx, cudaMemcpyAsync(d_win, h, win_bytes, cudaMemcpyHostToDevice, ctx->stream));
@@ -150,8 +159,9 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
     path_bytes += (int64_t)ASM_MAX_PATHS * h[i].path_cap;
     h[i].n_paths = 0;
   }
-  const int ref_stride = 2 * W + 1;
-  uint8_t* d_strings = nullptr;  // [path strings | window reference slices, each preceded by one base]
+  st.path_bytes = path_bytes;
+  const int ref_stride = st.ref_stride = P.ref_len + 1;
+  uint8_t*& d_strings = st.d_strings;
   GUAC_TRY(tmp.alloc(ctx, &d_strings, (size_t)path_bytes + (size_t)n * ref_stride + 16));
   uint8_t* d_ref1 = d_strings + path_bytes;
   AsmGraph G;
@@ -186,20 +196,66 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
   GUAC_TRY(tmp.alloc(ctx, &X.branch, 2 * (2 * N + 8 * NW + 8)));
   X.paths = d_strings;
   CUDA_TRY(ctx, cudaMemcpyAsync(d_win, h, win_bytes, cudaMemcpyHostToDevice, ctx->stream));
-  asm_refwin_kernel<<<blocks_for((int64_t)n * ref_stride, 256), 256, 0, ctx->stream>>>(ctx->d_refs.as<RefView>(), d_win, n, W, d_ref1, d_err);
+  if (custom_ref) {
+    CUDA_TRY(ctx, cudaMemsetAsync(d_ref1, 0, 1, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_ref1 + 1, custom_ref, (size_t)P.ref_len, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    asm_refwin_kernel<<<blocks_for((int64_t)n * ref_stride, 256), 256, 0, ctx->stream>>>(ctx->d_refs.as<RefView>(), d_win, n, P.W, d_ref1, d_err);
+    ctx->launches += 1;
+  }
   asm_nodes_kernel<<<(unsigned)n, 256, 0, ctx->stream>>>(ctx->R, d_win, T, G, P);
   asm_walk_kernel<<<blocks_for((int64_t)n * 32, 128), 128, 0, ctx->stream>>>(d_win, n, T, G, X, P, d_ref1, d_err);
   AsmEvidence* d_ev = nullptr;
   GUAC_TRY(tmp.alloc(ctx, &d_ev, (size_t)n));
   asm_evidence_kernel<<<blocks_for(n, 4), 128, 0, ctx->stream>>>(ctx->R, d_win, n, P, d_ev);
-  ctx->launches += 4;
+  ctx->launches += 3;
   CUDA_TRY(ctx, cudaGetLastError());
-  std::vector<AsmEvidence> ev((size_t)n);
-  std::vector<uint8_t> strings((size_t)path_bytes + (size_t)n * ref_stride);
+  st.ev.resize((size_t)n);
+  st.strings.resize((size_t)path_bytes + (size_t)n * ref_stride);
   CUDA_TRY(ctx, cudaMemcpyAsync(h, d_win, win_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(ev.data(), d_ev, (size_t)n * sizeof(AsmEvidence), cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(strings.data(), d_strings, strings.size(), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(st.ev.data(), d_ev, (size_t)n * sizeof(AsmEvidence), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(st.strings.data(), d_strings, st.strings.size(), cudaMemcpyDeviceToHost, ctx->stream));
   GUAC_TRY(check_device_error(ctx));
+  return GUAC_OK;
+}
+
+AsmPenalties asm_penalties(double mismatch_probability, double open_gap_probability, double close_gap_probability) {  // ReadAlignment.scala:98-104
+  AsmPenalties Q;
+  Q.mismatch = -std::log(mismatch_probability);
+  Q.open_gap = -std::log(open_gap_probability);
+  Q.no_gap = -std::log(1 - open_gap_probability);
+  Q.close_gap = -std::log(close_gap_probability);
+  Q.continue_gap = -std::log(1 - close_gap_probability);
+  return Q;
+}
+
+int asm_align_prepare(guac_ctx* ctx) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(ctx, cudaFuncSetAttribute(asm_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_align_smem(ASM_ALIGN_MAX_S)));
+    attr_set = true;
+  }
+  return GUAC_OK;
+}
+
+// Assembles windows [w0, w1) of `windows`; results appended to `results`.
+int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmWindow>& windows, size_t w0, size_t w1,
+                   std::vector<AsmWindowResult>& results) {
+  AsmStage st;
+  const int n = (int)(w1 - w0);
+  const int K = params->kmer_size, W = params->assembly_window_range;
+  st.P = AsmParams{params->sample_id, K, W, params->min_occurrence, params->min_mean_kmer_quality, ASM_MAX_PATHS, 2 * W, 0};
+  AsmWindow* h = windows.data() + w0;
+  GUAC_TRY(build_paths(ctx, st, h, n, nullptr));
+  DevTmp& tmp = st.tmp;
+  const AsmParams P = st.P;
+  AsmWindow* d_win = st.d_win;
+  uint8_t* d_strings = st.d_strings;
+  const int64_t path_bytes = st.path_bytes;
+  const int ref_stride = st.ref_stride;
+  const std::vector<uint8_t>& strings = st.strings;
+  const std::vector<AsmEvidence>& ev = st.ev;
+  DeviceError* d_err = ctx->b_err.as<DeviceError>();
   // discoverHaplotypes (AssemblyUtils.scala:79-114): score when there are more paths than the ploidy
   const int expected_ploidy = 2, max_paths_to_score = ASM_MAX_PATHS - 1;
   std::vector<int32_t> which, sum_base;
@@ -215,20 +271,8 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
       n_jobs += (int64_t)h[i].n_reads * h[i].n_paths;
       n_sums += h[i].n_paths;
     }
-  AsmPenalties Q;  // ReadAlignment.scala:64-70 defaults, :98-104
-  {
-    const double mismatch_probability = std::exp(-4.0), open_gap_probability = std::exp(-6.0), close_gap_probability = 1 - std::exp(-1.0);
-    Q.mismatch = -std::log(mismatch_probability);
-    Q.open_gap = -std::log(open_gap_probability);
-    Q.no_gap = -std::log(1 - open_gap_probability);
-    Q.close_gap = -std::log(close_gap_probability);
-    Q.continue_gap = -std::log(1 - close_gap_probability);
-  }
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(ctx, cudaFuncSetAttribute(asm_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_align_smem(ASM_ALIGN_MAX_S)));
-    attr_set = true;
-  }
+  const AsmPenalties Q = asm_penalties(std::exp(-4.0), std::exp(-6.0), 1 - std::exp(-1.0));  // ReadAlignment.scala:64-70 defaults
+  GUAC_TRY(asm_align_prepare(ctx));
   std::vector<long long> sums((size_t)n_sums, 0);
   if (n_jobs > 0) {
     int32_t* d_which = nullptr;
@@ -481,5 +525,94 @@ int guac_germline_assembly(guac_ctx* ctx, const guac_ga_params* params, const gu
   *out_arena = (char*)ha;
   *arena_len = (int64_t)arena.size();
   if (out_n_visited) *out_n_visited = n_visited;
+  return GUAC_OK;
+}
+
+int guac_discover_paths(guac_ctx* ctx, int32_t sample_id, const char* reference_sequence, int32_t reference_len, int32_t kmer_size,
+                        int32_t min_occurrence, int32_t max_paths, int32_t min_mean_kmer_quality, char** out_paths, int64_t* out_len,
+                        int32_t* n_paths) {
+  if (!ctx || !reference_sequence || !out_paths || !out_len || !n_paths) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
+  if (kmer_size < 2 || kmer_size > ASM_MAX_K)
+    return fail(ctx, GUAC_E_UNSUPPORTED, "kmer_size must be in [2, " + std::to_string(ASM_MAX_K) + "] (library limit)");
+  if (max_paths < 1 || max_paths > ASM_MAX_PATHS)
+    return fail(ctx, GUAC_E_UNSUPPORTED, "max_paths must be in [1, " + std::to_string(ASM_MAX_PATHS) + "] (library limit)");
+  if (reference_len < kmer_size) return fail(ctx, GUAC_E_INVALID_INPUT, "Source kmer has size != kmerSize");  // DeBruijnGraph.scala:190-191
+  GUAC_TRY(reset_error(ctx));
+  AsmStage st;
+  st.P = AsmParams{sample_id, kmer_size, 0, min_occurrence, min_mean_kmer_quality, max_paths, reference_len, 1};
+  AsmWindow w;
+  std::memset(&w, 0, sizeof w);
+  w.read_clo = 0;
+  w.read_chi = ctx->n_reads;
+  GUAC_TRY(build_paths(ctx, st, &w, 1, reinterpret_cast<const uint8_t*>(reference_sequence)));
+  std::string text;
+  for (int p = w.n_paths - 1; p >= 0; --p) {  // the reference prepends each new path to its list
+    text.append((const char*)st.strings.data() + w.path_off + (int64_t)p * w.path_cap, (size_t)w.path_len[p]);
+    text.push_back('\0');
+  }
+  void* h = nullptr;
+  GUAC_TRY(pinned_alloc(ctx, &h, std::max<size_t>(text.size(), 16)));
+  std::memcpy(h, text.data(), text.size());
+  *out_paths = (char*)h;
+  *out_len = (int64_t)text.size();
+  *n_paths = w.n_paths;
+  return GUAC_OK;
+}
+
+int guac_read_alignment(guac_ctx* ctx, const char* sequence, int32_t sequence_len, const char* reference, int32_t reference_len,
+                        double mismatch_probability, double open_gap_probability, double close_gap_probability, char* out_cigar,
+                        int32_t cigar_cap, int32_t* ref_start, int32_t* ref_end, int32_t* alignment_score, double* raw_score) {
+  if (!ctx || !sequence || !reference || !out_cigar || cigar_cap < 1 || sequence_len < 0 || reference_len < 0) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (sequence_len > ASM_ALIGN_MAX_S || sequence_len > 65535 || reference_len > 65535)
+    return fail(ctx, GUAC_E_UNSUPPORTED, "sequence longer than " + std::to_string(ASM_ALIGN_MAX_S) + " or reference longer than 65535 bases (library limit)");
+  out_cigar[0] = 0;
+  GUAC_TRY(reset_error(ctx));
+  GUAC_TRY(asm_align_prepare(ctx));
+  const AsmPenalties Q = asm_penalties(mismatch_probability > 0 ? mismatch_probability : std::exp(-4.0),
+                                       open_gap_probability > 0 ? open_gap_probability : std::exp(-6.0),
+                                       close_gap_probability > 0 ? close_gap_probability : 1 - std::exp(-1.0));
+  DevTmp tmp;
+  uint8_t* d_strings = nullptr;
+  uint8_t* d_heads = nullptr;
+  AsmAlignJob* d_job = nullptr;
+  AsmCigar* d_cigar = nullptr;
+  GUAC_TRY(tmp.alloc(ctx, &d_strings, (size_t)sequence_len + reference_len + 16));
+  GUAC_TRY(tmp.alloc(ctx, &d_heads, (size_t)sequence_len * (reference_len + 1) + 16));
+  GUAC_TRY(tmp.alloc(ctx, &d_job, 1));
+  GUAC_TRY(tmp.alloc(ctx, &d_cigar, 1, 0));
+  AsmAlignJob job;
+  std::memset(&job, 0, sizeof job);
+  job.seq = 0;
+  job.ref = sequence_len;
+  job.seq_len = sequence_len;
+  job.ref_len = reference_len;
+  job.seq_kind = 1;
+  job.sum_slot = -1;
+  job.trace = 0;
+  job.head_off = 0;
+  if (sequence_len) CUDA_TRY(ctx, cudaMemcpyAsync(d_strings, sequence, (size_t)sequence_len, cudaMemcpyHostToDevice, ctx->stream));
+  if (reference_len) CUDA_TRY(ctx, cudaMemcpyAsync(d_strings + sequence_len, reference, (size_t)reference_len, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(d_job, &job, sizeof job, cudaMemcpyHostToDevice, ctx->stream));
+  AsmCigar c;
+  std::memset(&c, 0, sizeof c);
+  if (sequence_len > 0) {
+    asm_align_kernel<<<1, ASM_ALIGN_THREADS, asm_align_smem(sequence_len), ctx->stream>>>(ctx->R, d_job, Q, d_strings, d_heads, nullptr, d_cigar,
+                                                                                        ctx->b_err.as<DeviceError>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(&c, d_cigar, sizeof c, cudaMemcpyDeviceToHost, ctx->stream));
+    GUAC_TRY(check_device_error(ctx));
+  }
+  std::string text;  // toCigarString (:22-43)
+  for (int i = 0; i < c.n_elements; ++i) text += std::to_string(c.len[i]) + "=XID"[c.op[i]];
+  if ((int)text.size() + 1 > cigar_cap) return fail(ctx, GUAC_E_INVALID_INPUT, "cigar buffer too small");
+  std::memcpy(out_cigar, text.c_str(), text.size() + 1);
+  if (ref_start) *ref_start = c.ref_start;
+  if (ref_end) *ref_end = c.ref_end;
+  if (alignment_score) *alignment_score = c.score;
+  if (raw_score) *raw_score = c.raw_score;
   return GUAC_OK;
 }

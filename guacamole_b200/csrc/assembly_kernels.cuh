@@ -49,6 +49,8 @@ struct AsmWindow {
 
 struct AsmParams {
   int sample, K, W, min_occurrence, min_mean_kmer_quality, max_paths;
+  int ref_len;    // bases of a window's reference slice (2 W for the caller's windows)
+  int all_reads;  // 1: the window is every read of the sample (DeBruijnGraph.discoverPathsFromReads over a given read set)
 };
 
 // ---- 3-bit packed k-mers, first base in the most significant bits so that word order is string order ----
@@ -116,8 +118,9 @@ struct Kmer {
   }
 };
 
-__device__ __forceinline__ bool asm_in_window(const ReadsView& R, int64_t r, int sample, int64_t locus, int W) {
-  return __ldg(R.sample_id + r) == sample && __ldg(R.start + r) <= locus + W && __ldg(R.end + r) > locus - W;
+__device__ __forceinline__ bool asm_in_window(const ReadsView& R, int64_t r, const AsmParams& P, int64_t locus) {
+  if (__ldg(R.sample_id + r) != P.sample) return false;
+  return P.all_reads || (__ldg(R.start + r) <= locus + P.W && __ldg(R.end + r) > locus - P.W);
 }
 __device__ __forceinline__ int asm_read_len(const ReadsView& R, int64_t r) { return (int)(__ldg(R.seq_off + r + 1) - __ldg(R.seq_off + r)); }
 
@@ -133,7 +136,7 @@ __global__ void asm_window_kernel(ReadsView R, AsmWindow* __restrict__ wins, int
     int64_t m = (a + b) >> 1;
     if (__ldg(R.start + m) <= locus + P.W) a = m + 1; else b = m;
   }
-  const int64_t hi = a;
+  int64_t hi = a;
   const int64_t key = ((int64_t)w.contig_id << 40) | (locus - P.W);
   a = w.read_clo;
   b = hi;
@@ -141,11 +144,12 @@ __global__ void asm_window_kernel(ReadsView R, AsmWindow* __restrict__ wins, int
     int64_t m = (a + b) >> 1;
     if (__ldg(R.runmax_key + m) > key) b = m; else a = m + 1;
   }
-  const int64_t lo = a;
+  const int64_t lo = P.all_reads ? w.read_clo : a;
+  if (P.all_reads) hi = w.read_chi;
   int n_reads = 0, n_inst = 0, max_len = 0;
   long long n_bases = 0;
   for (int64_t r = lo + lane; r < hi; r += 32) {
-    if (!asm_in_window(R, r, P.sample, locus, P.W)) continue;
+    if (!asm_in_window(R, r, P, locus)) continue;
     const int len = asm_read_len(R, r);
     n_reads += 1;
     n_inst += max(len - P.K + 1, 0);
@@ -238,7 +242,7 @@ __global__ void __launch_bounds__(256) asm_count_kernel(ReadsView R, AsmWindow* 
   if (threadIdx.x == 0) s_nodes = 0;
   for (int pass = 0; pass < 2; ++pass) {
     for (int64_t r = w.read_lo + warp; r < w.read_hi; r += n_warps) {
-      if (!asm_in_window(R, r, P.sample, w.locus, P.W)) continue;
+      if (!asm_in_window(R, r, P, w.locus)) continue;
       const int n_at = asm_read_len(R, r) - P.K + 1;
       for (int at = lane; at < n_at; at += 32) {
         if (!(asm_mean_quality(R, r, at, P.K) > (float)P.min_mean_kmer_quality)) continue;
@@ -459,13 +463,13 @@ __global__ void asm_walk_kernel(AsmWindow* __restrict__ wins, int n_windows, Asm
   const int pool_cap = 4 * n + 64, front_cap = 10 * n + 64, stack_cap = 2 * n + 8, node_cap = 2 * n + 2;
   AsmWalkCtx C{G, X, no, mo, po, n, K};
   auto capacity = [&]() { report_error(err, DERR_ASM_CAPACITY, w.contig_id, w.locus, -1); };
-  const uint8_t* ref = win_ref + (int64_t)wi * (2 * P.W + 1) + 1;
+  const uint8_t* ref = win_ref + (int64_t)wi * (P.ref_len + 1) + 1;
   Kmer source, sink;
   source.clear();
   sink.clear();
   bool ends_ok = true;
   for (int p = 0; p < K; ++p) {
-    const int a = asm_base_code(ref[p]), b = asm_base_code(ref[2 * P.W - K + p]);
+    const int a = asm_base_code(ref[p]), b = asm_base_code(ref[P.ref_len - K + p]);
     if (a < 0 || b < 0) {
       ends_ok = false;
       break;
@@ -894,7 +898,7 @@ __global__ void __launch_bounds__(128) asm_evidence_kernel(ReadsView R, const As
   float mean_m = 0.0f, mean_b = 0.0f;
   long long n_m = 0, n_b = 0;
   for (int64_t r = w.read_lo; r < w.read_hi; ++r) {
-    if (!asm_in_window(R, r, P.sample, w.locus, P.W)) continue;
+    if (!asm_in_window(R, r, P, w.locus)) continue;
     const uint64_t b0 = __ldg(R.seq_off + r);
     const int len = asm_read_len(R, r);
     for (int i = lane; i < len; i += 32) atomicAdd(&hb[__ldg(R.qual + b0 + i)], 1u);

@@ -421,6 +421,29 @@ class Context:
         return dict(calls=_take(self.lib, self.ctx, calls, CALLED_ALLELE_DTYPE, n.value), arena=arena_b,
                     windows=_take(self.lib, self.ctx, wins, ASSEMBLED_WINDOW_DTYPE, nw.value), n_visited=nv.value)
 
+    def discover_paths(self, reference_sequence: str, kmer_size: int, min_occurrence: int = 1, max_paths: int = 10,
+                       min_mean_kmer_quality: int = 0, sample_id: int = 0):
+        """guac_discover_paths over the uploaded reads -> haplotype strings, most recently found first."""
+        ref = reference_sequence.encode()
+        out, n, npaths = C.c_void_p(), C.c_int64(), C.c_int32()
+        self._check(self.lib.guac_discover_paths(self.ctx, C.c_int32(sample_id), ref, C.c_int32(len(ref)), C.c_int32(kmer_size),
+                                                 C.c_int32(min_occurrence), C.c_int32(max_paths), C.c_int32(min_mean_kmer_quality),
+                                                 C.byref(out), C.byref(n), C.byref(npaths)))
+        text = C.string_at(out, n.value) if n.value else b""
+        self.lib.guac_free(self.ctx, out)
+        return [t.decode() for t in text.split(b"\0")[:npaths.value]]
+
+    def read_alignment(self, sequence: str, reference: str, mismatch_probability: float = 0.0, open_gap_probability: float = 0.0,
+                       close_gap_probability: float = 0.0):
+        """guac_read_alignment -> (cigar, refStartIdx, refEndIdx, alignmentScore, rawScore)."""
+        s, r = sequence.encode(), reference.encode()
+        buf = C.create_string_buffer(4096)
+        rs, re_, sc, raw = C.c_int32(), C.c_int32(), C.c_int32(), C.c_double()
+        self._check(self.lib.guac_read_alignment(self.ctx, s, C.c_int32(len(s)), r, C.c_int32(len(r)), C.c_double(mismatch_probability),
+                                                 C.c_double(open_gap_probability), C.c_double(close_gap_probability), buf, C.c_int32(4096),
+                                                 C.byref(rs), C.byref(re_), C.byref(sc), C.byref(raw)))
+        return buf.value.decode(), rs.value, re_.value, sc.value, raw.value
+
     def somatic_joint(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
         """guac_somatic_joint -> (list of per-allele evidence dicts, loci visited); see commands/somatic_joint.py."""
         from .commands import somatic_joint as sj

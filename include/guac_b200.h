@@ -349,6 +349,27 @@ int guac_germline_assembly(guac_ctx* ctx, const guac_ga_params* params, const gu
                            guac_called_allele** out_calls, int64_t* n_calls, char** out_arena, int64_t* arena_len,
                            guac_assembled_window** out_windows, int64_t* n_windows, int64_t* out_n_visited);
 
+/*
+ * DeBruijnGraph.discoverPathsFromReads (M/assembly/DeBruijnGraph.scala:437-464) over every uploaded read of one
+ * sample — graph with mergeNodes = true, depthFirstSearch from the first to the last kmer_size bases of
+ * reference_sequence — followed by mergeOverlappingSequences of each path (M/assembly/AssemblyUtils.scala:84).
+ * out_paths receives the haplotypes in the reference's list order (most recently found first), each NUL-terminated;
+ * max_paths <= 17.  This is the assembler of guac_germline_assembly applied to a caller-chosen read set.
+ */
+int guac_discover_paths(guac_ctx* ctx, int32_t sample_id, const char* reference_sequence, int32_t reference_len, int32_t kmer_size,
+                        int32_t min_occurrence, int32_t max_paths, int32_t min_mean_kmer_quality, char** out_paths, int64_t* out_len,
+                        int32_t* n_paths);
+
+/*
+ * ReadAlignment(sequence, reference, mismatchProbability, openGapProbability, closeGapProbability)
+ * (M/alignment/ReadAlignment.scala:64-90, scoreAlignmentPaths :92-195): the best affine-gap alignment of the whole
+ * sequence to any stretch of the reference; a probability <= 0 selects the reference's default (e^-4, e^-6, 1 - e^-1).
+ * out_cigar receives toCigarString (:22-43, operators = X I D).
+ */
+int guac_read_alignment(guac_ctx* ctx, const char* sequence, int32_t sequence_len, const char* reference, int32_t reference_len,
+                        double mismatch_probability, double open_gap_probability, double close_gap_probability, char* out_cigar,
+                        int32_t cigar_cap, int32_t* ref_start, int32_t* ref_end, int32_t* alignment_score, double* raw_score);
+
 /* ---- somatic-joint ----------------------------------------------------------
  * M/jointcaller/Parameters.scala:10-25 plus the inputs (M/jointcaller/Input.scala, InputCollection.scala:55-101)
  * and the flags of M/commands/SomaticJointCaller.scala:154-163. */

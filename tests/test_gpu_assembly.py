@@ -98,3 +98,96 @@ def test_rejects_backward_jump(gpu_ctx):
     gpu_ctx.upload_reads(batch)
     with pytest.raises(Exception, match="can only move forward"):
         gpu_ctx.germline_assembly([(0, 200, 1800)], ga_params())  # the reference's defaults: range 20 < k-mer 45
+
+
+# ---- the reference's unit vectors through the device kernels ---------------------------------------------------------
+from guacamole_b200.reads import ReadBatch, make_read  # noqa: E402
+from tests import test_oracle_assembly as vectors  # noqa: E402
+
+
+def upload_sequences(ctx, sequences, qualities=None):
+    reads = [make_read(s, f"{len(s)}M", start=i, quality_scores=None if qualities is None else qualities[i])
+             for i, s in enumerate(sequences)]
+    ctx.upload_reads(ReadBatch.from_reads(reads))
+
+
+@pytest.mark.parametrize("extra", [(), (vectors.REF52[19:41] + "TCGAA",), (vectors.REF52[19:41] + "TCGAA", vectors.REF52[19:41] + "TCGTA")])
+def test_depth_first_search_vectors(gpu_ctx, extra):  # DeBruijnGraphSuite.scala:284-425 (merged graph)
+    ref = vectors.REF52
+    upload_sequences(gpu_ctx, vectors._reads(extra))
+    assert gpu_ctx.discover_paths(ref, 15) == [ref]
+    # only the first and last k-mer of the reference matter
+    assert gpu_ctx.discover_paths(ref[:15] + "A" * 7 + ref[-15:], 15) == [ref]
+
+
+def test_two_alleles_and_counts(gpu_ctx):
+    ref = vectors.REF52
+    alt = ref[:26] + "T" + ref[27:]
+    reads = [ref[i:i + 30] for i in range(0, 23, 2)] + [alt[i:i + 30] for i in range(0, 23, 2)]
+    upload_sequences(gpu_ctx, reads)
+    want = oracle.debruijn(reads, 15, "dfs", merge_nodes=True, source=ref[:15], sink=ref[-15:], max_paths=17)
+    assert gpu_ctx.discover_paths(ref, 15, max_paths=17) == want and sorted(want) == sorted([ref, alt])
+    # minOccurrence prunes the alternate allele's k-mers when only two reads carry it
+    few = reads[:12] + reads[12:14]
+    upload_sequences(gpu_ctx, few)
+    assert gpu_ctx.discover_paths(ref, 15, min_occurrence=3) == oracle.debruijn(few, 15, "dfs", min_occurrence=3, merge_nodes=True,
+                                                                             source=ref[:15], sink=ref[-15:])
+    # maxPaths stops the search
+    upload_sequences(gpu_ctx, reads)
+    assert gpu_ctx.discover_paths(ref, 15, max_paths=1) == oracle.debruijn(reads, 15, "dfs", merge_nodes=True, source=ref[:15],
+                                                                         sink=ref[-15:], max_paths=1)
+
+
+def test_kmer_quality_gate_vectors(gpu_ctx):  # DeBruijnGraphSuite.scala:62-104: low-quality k-mers do not reach minOccurrence
+    seq = "TCATCTTAAAAGACATAAACCGGTTGCA"
+    mixed = [30] * 9 + [5] * 6 + [30] * (len(seq) - 15)
+    for threshold in (0, 15, 25):
+        quals = [[30] * len(seq), mixed]
+        upload_sequences(gpu_ctx, [seq, seq], quals)
+        want = oracle.debruijn([seq, seq], 5, "dfs", min_occurrence=2, min_mean_kmer_quality=threshold, merge_nodes=True, qualities=quals,
+                               source=seq[:5], sink=seq[-5:])
+        assert gpu_ctx.discover_paths(seq, 5, min_occurrence=2, min_mean_kmer_quality=threshold) == want
+
+
+def test_real_reads_vector(gpu_ctx):  # DeBruijnGraphSuite.scala:427-457
+    z = np.load(vectors.os.path.join(vectors.os.path.dirname(vectors.__file__), "golden", "assemble_reads_set3.npz"))
+    seqs = [str(s) for s in z["seqs"]]
+    reference = ("GAGGATCTGCCATGGCCGGGCGAGCTGGAGGAGGAGGAGGAGGAGGAGGAGGAGGAGGAGGAGGAAGAGGAGGAGGCTGCAGCGGCGGCGGCGGCGAACGTGGACGACGTAGTGGTCGTGGAGGAGGTGGAGGAAGAGGCGGG"
+                 "GCG")
+    upload_sequences(gpu_ctx, seqs)
+    got = gpu_ctx.discover_paths(reference, 55, min_occurrence=3)
+    assert len(got) == 1
+    assert got == oracle.debruijn(seqs, 55, "dfs", min_occurrence=3, merge_nodes=True, source=reference[:55], sink=reference[-55:])
+
+
+def test_alignment_vectors(gpu_ctx):  # ReadAlignmentSuite.scala:78-158
+    assert gpu_ctx.read_alignment("TCGA", "TCGA", 1e-2, 1e-3, 1e-2)[3] == 0
+    assert round(gpu_ctx.read_alignment("TCGA", "TCCA", 1e-2, 1e-3, 1e-2)[4]) == 5
+    for seq, ref, cigar in vectors.test_alignment_cigars.pytestmark[0].args[1]:  # the suite's (sequence, reference, cigar) table
+        got = gpu_ctx.read_alignment(seq, ref)
+        want = oracle.read_alignment(seq, ref)
+        assert got[0] == cigar
+        assert got[:4] == tuple(want[:4]) and got[4] == want[4]  # the raw FP64 score bit for bit
+
+
+def test_alignment_random_pairs(gpu_ctx):
+    rng = np.random.default_rng(7)
+    for _ in range(40):
+        n = int(rng.integers(5, 120))
+        ref = "".join(rng.choice(list("ACGT"), n + int(rng.integers(0, 40))))
+        at = int(rng.integers(0, len(ref) - n + 1))
+        seq = list(ref[at:at + n])
+        for _ in range(int(rng.integers(0, 4))):  # a few edits
+            i = int(rng.integers(0, len(seq)))
+            kind = int(rng.integers(0, 3))
+            if kind == 0:
+                seq[i] = "ACGT"[int(rng.integers(0, 4))]
+            elif kind == 1:
+                seq[i:i] = list("ACGT"[int(rng.integers(0, 4))] * int(rng.integers(1, 4)))
+            else:
+                del seq[i:i + int(rng.integers(1, 4))]
+        seq = "".join(seq)
+        if not seq:
+            continue
+        got, want = gpu_ctx.read_alignment(seq, ref), oracle.read_alignment(seq, ref)
+        assert got[:4] == tuple(want[:4]) and got[4] == want[4]
