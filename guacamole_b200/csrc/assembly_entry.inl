@@ -9,21 +9,37 @@
 
 namespace {
 
-struct DevTmp {  // device scratch of one call, released on every return path
-  std::vector<void*> blocks;
+// Device scratch of one call: bump allocation out of blocks the context keeps between calls (cudaMalloc / cudaFree
+// per stage cost more than the kernels of a window batch).  Strict stack discipline: one DevTmp alive at a time.
+struct DevTmp {
+  guac_ctx* owner = nullptr;
   ~DevTmp() {
-    for (void* p : blocks) cudaFree(p);
+    if (owner) {
+      owner->asm_block = 0;
+      owner->asm_off = 0;
+    }
   }
   template <class T>
   int alloc(guac_ctx* ctx, T** out, size_t n, int fill = -1) {
-    void* p = nullptr;
-    const size_t bytes = std::max<size_t>(n * sizeof(T), 256);
-    cudaError_t e = cudaMalloc(&p, bytes);
-    if (e != cudaSuccess) {
-      (void)cudaGetLastError();
-      return fail(ctx, GUAC_E_OOM, std::string("cudaMalloc of ") + std::to_string(bytes) + " bytes failed: " + cudaGetErrorString(e));
+    owner = ctx;
+    const size_t bytes = (std::max<size_t>(n * sizeof(T), 256) + 255) & ~(size_t)255;
+    while (ctx->asm_block < ctx->asm_blocks.size() && ctx->asm_off + bytes > ctx->asm_blocks[ctx->asm_block].second) {
+      ctx->asm_block += 1;
+      ctx->asm_off = 0;
     }
-    blocks.push_back(p);
+    if (ctx->asm_block == ctx->asm_blocks.size()) {
+      void* p = nullptr;
+      const size_t want = std::max<size_t>(bytes, (size_t)64 << 20);
+      cudaError_t e = cudaMalloc(&p, want);
+      if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(ctx, GUAC_E_OOM, std::string("cudaMalloc of ") + std::to_string(want) + " bytes failed: " + cudaGetErrorString(e));
+      }
+      ctx->asm_blocks.push_back({p, want});
+      ctx->asm_off = 0;
+    }
+    void* p = static_cast<char*>(ctx->asm_blocks[ctx->asm_block].first) + ctx->asm_off;
+    ctx->asm_off += bytes;
     if (fill >= 0) CUDA_TRY(ctx, cudaMemsetAsync(p, fill, bytes, ctx->stream));
     *out = reinterpret_cast<T*>(p);
     return GUAC_OK;
@@ -109,7 +125,11 @@ struct AsmStage {  // device and host state of one batch of windows once their g
   uint8_t* d_strings = nullptr;  // [path strings | window reference slices, each preceded by one base]
   int64_t path_bytes = 0;
   int ref_stride = 0;
-  std::vector<uint8_t> strings;  // host copy of d_strings
+  uint8_t* strings = nullptr;    // pinned host copy of d_strings
+  guac_ctx* ctx = nullptr;
+  ~AsmStage() {
+    if (strings) guac_free(ctx, strings);
+  }
   std::vector<AsmEvidence> ev;
 };
 
@@ -211,10 +231,15 @@ int build_paths(guac_ctx* ctx, AsmStage& st, AsmWindow* h, int n, const uint8_t*
   ctx->launches += 3;
   CUDA_TRY(ctx, cudaGetLastError());
   st.ev.resize((size_t)n);
-  st.strings.resize((size_t)path_bytes + (size_t)n * ref_stride);
+  st.ctx = ctx;
+  {
+    void* hp = nullptr;
+    GUAC_TRY(pinned_alloc(ctx, &hp, (size_t)path_bytes + (size_t)n * ref_stride + 16));
+    st.strings = static_cast<uint8_t*>(hp);
+  }
   CUDA_TRY(ctx, cudaMemcpyAsync(h, d_win, win_bytes, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(st.ev.data(), d_ev, (size_t)n * sizeof(AsmEvidence), cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(st.strings.data(), d_strings, st.strings.size(), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(st.strings, d_strings, (size_t)path_bytes + (size_t)n * ref_stride, cudaMemcpyDeviceToHost, ctx->stream));
   GUAC_TRY(check_device_error(ctx));
   return GUAC_OK;
 }
@@ -253,7 +278,7 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
   uint8_t* d_strings = st.d_strings;
   const int64_t path_bytes = st.path_bytes;
   const int ref_stride = st.ref_stride;
-  const std::vector<uint8_t>& strings = st.strings;
+  const uint8_t* strings = st.strings;
   const std::vector<AsmEvidence>& ev = st.ev;
   DeviceError* d_err = ctx->b_err.as<DeviceError>();
   // discoverHaplotypes (AssemblyUtils.scala:79-114): score when there are more paths than the ploidy
@@ -364,8 +389,8 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
   for (size_t c = 0; c < chosen.size(); ++c) {
     const int i = chosen[c].window;
     const AsmWindow& w = h[i];
-    const std::string path((const char*)strings.data() + w.path_off + (int64_t)chosen[c].path * w.path_cap, (size_t)w.path_len[chosen[c].path]);
-    const std::string ref1((const char*)strings.data() + path_bytes + (int64_t)i * ref_stride, (size_t)ref_stride);
+    const std::string path((const char*)strings + w.path_off + (int64_t)chosen[c].path * w.path_cap, (size_t)w.path_len[chosen[c].path]);
+    const std::string ref1((const char*)strings + path_bytes + (int64_t)i * ref_stride, (size_t)ref_stride);
     GUAC_TRY(variants_from_cigar(ctx, cigars[c], path, ref1, w.locus - W, w.contig_id, sets[(size_t)i]));
   }
   for (int i = 0; i < n; ++i) {
@@ -427,7 +452,7 @@ int guac_germline_assembly(guac_ctx* ctx, const guac_ga_params* params, const gu
   guac_free(ctx, active);
   // 2. every candidate window assembled on the device
   std::vector<AsmWindowResult> results;
-  const size_t chunk = 1024;
+  const size_t chunk = 4096;
   cudaEventRecord(ctx->ev0, ctx->stream);
   for (size_t w0 = 0; w0 < windows.size(); w0 += chunk)
     GUAC_TRY(assemble_chunk(ctx, params, windows, w0, std::min(windows.size(), w0 + chunk), results));
@@ -549,7 +574,7 @@ int guac_discover_paths(guac_ctx* ctx, int32_t sample_id, const char* reference_
   GUAC_TRY(build_paths(ctx, st, &w, 1, reinterpret_cast<const uint8_t*>(reference_sequence)));
   std::string text;
   for (int p = w.n_paths - 1; p >= 0; --p) {  // the reference prepends each new path to its list
-    text.append((const char*)st.strings.data() + w.path_off + (int64_t)p * w.path_cap, (size_t)w.path_len[p]);
+    text.append((const char*)st.strings + w.path_off + (int64_t)p * w.path_cap, (size_t)w.path_len[p]);
     text.push_back('\0');
   }
   void* h = nullptr;

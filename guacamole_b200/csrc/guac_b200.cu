@@ -74,6 +74,8 @@ struct guac_ctx {
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites;
   double bound_tab_vaf = -1;
+  std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
+  size_t asm_block = 0, asm_off = 0;
 };
 
 namespace {
@@ -423,6 +425,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_vcount.p) cudaFree(ctx->b_vcount.p);
   if (ctx->b_sj_sites.p) cudaFree(ctx->b_sj_sites.p);
   if (ctx->b_boundtab.p) cudaFree(ctx->b_boundtab.p);
+  for (auto& b : ctx->asm_blocks) cudaFree(b.first);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);
