@@ -130,7 +130,6 @@ struct AsmStage {  // device and host state of one batch of windows once their g
   ~AsmStage() {
     if (strings) guac_free(ctx, strings);
   }
-  std::vector<AsmEvidence> ev;
 };
 
 // k-mer tables -> ranked graph -> unipath merge + DFS for the n windows at `h` (updated in place with the path lengths).
@@ -153,14 +152,14 @@ int build_paths(guac_ctx* ctx, AsmStage& st, AsmWindow* h, int n, const uint8_t*
   int64_t slots = 0;
   for (int i = 0; i < n; ++i) {
     int cap = 16;
-    while (cap < 2 * h[i].n_instances) cap <<= 1;
+    while (cap < h[i].n_instances + 1) cap <<= 1;  // distinct k-mers <= instances: probing always terminates
     h[i].table_off = slots;
     h[i].table_cap = cap;
     slots += cap;
   }
   AsmTable T;
   GUAC_TRY(tmp.alloc(ctx, &T.tag, (size_t)slots, 0));
-  GUAC_TRY(tmp.alloc(ctx, &T.rep, (size_t)slots, 0xFF));
+  GUAC_TRY(tmp.alloc(ctx, &T.key, (size_t)slots));
   GUAC_TRY(tmp.alloc(ctx, &T.count, (size_t)slots, 0));
   GUAC_TRY(tmp.alloc(ctx, &T.node, (size_t)slots, 0xFF));
   CUDA_TRY(ctx, cudaMemcpyAsync(d_win, h, win_bytes, cudaMemcpyHostToDevice, ctx->stream));
@@ -225,12 +224,8 @@ int build_paths(guac_ctx* ctx, AsmStage& st, AsmWindow* h, int n, const uint8_t*
   }
   asm_nodes_kernel<<<(unsigned)n, 256, 0, ctx->stream>>>(ctx->R, d_win, T, G, P);
   asm_walk_kernel<<<blocks_for((int64_t)n * 32, 128), 128, 0, ctx->stream>>>(d_win, n, T, G, X, P, d_ref1, d_err);
-  AsmEvidence* d_ev = nullptr;
-  GUAC_TRY(tmp.alloc(ctx, &d_ev, (size_t)n));
-  asm_evidence_kernel<<<blocks_for(n, 4), 128, 0, ctx->stream>>>(ctx->R, d_win, n, P, d_ev);
-  ctx->launches += 3;
+  ctx->launches += 2;
   CUDA_TRY(ctx, cudaGetLastError());
-  st.ev.resize((size_t)n);
   st.ctx = ctx;
   {
     void* hp = nullptr;
@@ -238,7 +233,6 @@ int build_paths(guac_ctx* ctx, AsmStage& st, AsmWindow* h, int n, const uint8_t*
     st.strings = static_cast<uint8_t*>(hp);
   }
   CUDA_TRY(ctx, cudaMemcpyAsync(h, d_win, win_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(st.ev.data(), d_ev, (size_t)n * sizeof(AsmEvidence), cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(st.strings, d_strings, (size_t)path_bytes + (size_t)n * ref_stride, cudaMemcpyDeviceToHost, ctx->stream));
   GUAC_TRY(check_device_error(ctx));
   return GUAC_OK;
@@ -279,7 +273,6 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
   const int64_t path_bytes = st.path_bytes;
   const int ref_stride = st.ref_stride;
   const uint8_t* strings = st.strings;
-  const std::vector<AsmEvidence>& ev = st.ev;
   DeviceError* d_err = ctx->b_err.as<DeviceError>();
   // discoverHaplotypes (AssemblyUtils.scala:79-114): score when there are more paths than the ploidy
   const int expected_ploidy = 2, max_paths_to_score = ASM_MAX_PATHS - 1;
@@ -392,6 +385,26 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
     const std::string path((const char*)strings + w.path_off + (int64_t)chosen[c].path * w.path_cap, (size_t)w.path_len[chosen[c].path]);
     const std::string ref1((const char*)strings + path_bytes + (int64_t)i * ref_stride, (size_t)ref_stride);
     GUAC_TRY(variants_from_cigar(ctx, cigars[c], path, ref1, w.locus - W, w.contig_id, sets[(size_t)i]));
+  }
+  // window-wide evidence, only where variants came out
+  std::vector<int32_t> with_variants;
+  for (int i = 0; i < n; ++i)
+    if (!sets[(size_t)i].empty()) with_variants.push_back(i);
+  std::vector<AsmEvidence> ev((size_t)n);
+  if (!with_variants.empty()) {
+    int32_t* d_which = nullptr;
+    AsmEvidence* d_ev = nullptr;
+    const size_t m = with_variants.size();
+    std::vector<AsmEvidence> packed(m);
+    GUAC_TRY(tmp.alloc(ctx, &d_which, m));
+    GUAC_TRY(tmp.alloc(ctx, &d_ev, m));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_which, with_variants.data(), m * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    asm_evidence_kernel<<<blocks_for((int64_t)m, 4), 128, 0, ctx->stream>>>(ctx->R, d_win, d_which, (int)m, P, d_ev);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(packed.data(), d_ev, m * sizeof(AsmEvidence), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t j = 0; j < m; ++j) ev[(size_t)with_variants[j]] = packed[j];
   }
   for (int i = 0; i < n; ++i) {
     AsmWindowResult r;

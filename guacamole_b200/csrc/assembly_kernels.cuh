@@ -187,13 +187,15 @@ __global__ void asm_refwin_kernel(const RefView* __restrict__ refs, const AsmWin
 }
 
 struct AsmTable {
-  unsigned long long* tag;  // 0 = empty
-  unsigned long long* rep;  // smallest (read << 16 | offset) instance of the k-mer
+  unsigned long long* tag;  // 64-bit hash of the k-mer, 0 = empty
+  Kmer* key;                // written once by the thread that claimed the slot
   uint32_t* count;
   uint32_t* node;           // node id after ranking, 0xFFFFFFFF = pruned
 };
 
-// k-mer of read r at offset `at`, and the breeze running mean of its qualities (DeBruijnGraph.scala:357-358)
+constexpr int ASM_STAGE = 512;  // bases of a read staged in shared memory per warp (longer reads take the direct path)
+
+// k-mer of read r at offset `at` straight from the packed batch
 __device__ __forceinline__ bool asm_pack(const ReadsView& R, int64_t r, int at, int K, Kmer& k) {
   const uint64_t base0 = __ldg(R.seq_off + r) + at;
   k.clear();
@@ -204,13 +206,10 @@ __device__ __forceinline__ bool asm_pack(const ReadsView& R, int64_t r, int at, 
   }
   return true;
 }
-__device__ __forceinline__ float asm_mean_quality(const ReadsView& R, int64_t r, int at, int K) {
-  const uint64_t base0 = __ldg(R.seq_off + r) + at;
+// breeze's mean over the k-mer's qualities as Floats (DeBruijnGraph.scala:357-358): mu += (1 / n) * (q - mu)
+__device__ __forceinline__ float asm_mean_quality(const uint8_t* q, int K, const float* inv) {
   float mu = 0.0f;
-  for (int p = 0; p < K; ++p) {
-    const float d = __fsub_rn((float)__ldg(R.qual + base0 + p), mu);
-    mu = __fadd_rn(mu, __fmul_rn(__fdiv_rn(1.0f, (float)(p + 1)), d));
-  }
+  for (int p = 0; p < K; ++p) mu = __fadd_rn(mu, __fmul_rn(inv[p], __fsub_rn((float)q[p], mu)));
   return mu;
 }
 
@@ -226,8 +225,9 @@ __device__ __forceinline__ int asm_find(const AsmTable& T, int64_t off, int cap,
   return -1;
 }
 
-// One CTA per window: count the k-mers that pass the quality gate, then check every instance against
-// the table entry's representative so that a hash collision can never merge two k-mers silently.
+// One CTA per window, one warp per read, each lane a contiguous run of the read's k-mers (rolled base by base out of
+// a shared-memory copy of the read).  Pass 0 counts the k-mers that pass the quality gate; pass 1 compares every
+// instance with the key stored in its slot, so a 64-bit hash collision is reported, never a silent merge.
 __global__ void __launch_bounds__(256) asm_count_kernel(ReadsView R, AsmWindow* __restrict__ wins, AsmTable T, AsmParams P,
                                                         DeviceError* err) {
   AsmWindow& w = wins[blockIdx.x];
@@ -237,39 +237,76 @@ __global__ void __launch_bounds__(256) asm_count_kernel(ReadsView R, AsmWindow* 
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, n_warps = blockDim.x >> 5;
   const int64_t off = w.table_off;
-  const int cap = w.table_cap;
+  const int cap = w.table_cap, K = P.K;
   __shared__ int s_nodes;
+  __shared__ float s_inv[ASM_MAX_K];
+  __shared__ uint8_t s_code[8][ASM_STAGE];
+  __shared__ uint8_t s_qual[8][ASM_STAGE];
   if (threadIdx.x == 0) s_nodes = 0;
+  for (int p = threadIdx.x; p < K; p += blockDim.x) s_inv[p] = __fdiv_rn(1.0f, (float)(p + 1));
+  __syncthreads();
+  auto visit = [&](int pass, const Kmer& k, int64_t r) {
+    if (pass == 0) {
+      const unsigned long long tag = k.hash();
+      int slot = (int)(tag & (unsigned long long)(cap - 1));
+      while (true) {
+        const unsigned long long old = atomicCAS(T.tag + off + slot, 0ull, tag);
+        if (old == 0ull) {
+          T.key[off + slot] = k;
+          break;
+        }
+        if (old == tag) break;
+        slot = (slot + 1) & (cap - 1);
+      }
+      atomicAdd(T.count + off + slot, 1u);
+    } else {
+      const int slot = asm_find(T, off, cap, k);
+      if (!(T.key[off + slot] == k)) report_error(err, DERR_ASM_COLLISION, w.contig_id, w.locus, r);
+    }
+  };
   for (int pass = 0; pass < 2; ++pass) {
     for (int64_t r = w.read_lo + warp; r < w.read_hi; r += n_warps) {
       if (!asm_in_window(R, r, P, w.locus)) continue;
-      const int n_at = asm_read_len(R, r) - P.K + 1;
-      for (int at = lane; at < n_at; at += 32) {
-        if (!(asm_mean_quality(R, r, at, P.K) > (float)P.min_mean_kmer_quality)) continue;
-        Kmer k;
-        if (!asm_pack(R, r, at, P.K, k)) {
-          report_error(err, DERR_ASM_BASE, w.contig_id, w.locus, r);
-          continue;
+      const int len = asm_read_len(R, r), n_at = len - K + 1;
+      if (n_at <= 0) continue;
+      const uint64_t base0 = __ldg(R.seq_off + r);
+      if (len <= ASM_STAGE) {
+        bool bad = false;
+        for (int i = lane; i < len; i += 32) {
+          const int c = asm_base_code(read_base(R, base0 + i));
+          bad |= c < 0;
+          s_code[warp][i] = (uint8_t)c;
+          s_qual[warp][i] = __ldg(R.qual + base0 + i);
         }
-        const unsigned long long me = ((unsigned long long)r << 16) | (unsigned)at;
-        if (pass == 0) {
-          const unsigned long long tag = k.hash();
-          int slot = (int)(tag & (unsigned long long)(cap - 1));
-          while (true) {
-            const unsigned long long old = atomicCAS(T.tag + off + slot, 0ull, tag);
-            if (old == 0ull || old == tag) break;
-            slot = (slot + 1) & (cap - 1);
-          }
-          atomicAdd(T.count + off + slot, 1u);
-          atomicMin(T.rep + off + slot, me);
+        bad = __any_sync(0xffffffffu, bad);
+        __syncwarp();
+        if (bad) {
+          if (lane == 0) report_error(err, DERR_ASM_BASE, w.contig_id, w.locus, r);
         } else {
-          const int slot = asm_find(T, off, cap, k);
-          const unsigned long long rep = T.rep[off + slot];
-          if (rep != me) {
-            Kmer other;
-            asm_pack(R, (int64_t)(rep >> 16), (int)(rep & 0xFFFF), P.K, other);
-            if (!(other == k)) report_error(err, DERR_ASM_COLLISION, w.contig_id, w.locus, r);
+          const int per = (n_at + 31) / 32, a0 = lane * per, a1 = min(n_at, a0 + per);
+          Kmer k;
+          for (int at = a0; at < a1; ++at) {
+            if (at == a0) {
+              k.clear();
+              for (int p = 0; p < K; ++p) k.set(p, s_code[warp][at + p]);
+            } else {
+              k = k.shifted_left(K, s_code[warp][at + K - 1]);
+            }
+            if (asm_mean_quality(s_qual[warp] + at, K, s_inv) > (float)P.min_mean_kmer_quality) visit(pass, k, r);
           }
+        }
+        __syncwarp();
+      } else {
+        for (int at = lane; at < n_at; at += 32) {
+          float mu = 0.0f;
+          for (int p = 0; p < K; ++p) mu = __fadd_rn(mu, __fmul_rn(s_inv[p], __fsub_rn((float)__ldg(R.qual + base0 + at + p), mu)));
+          if (!(mu > (float)P.min_mean_kmer_quality)) continue;
+          Kmer k;
+          if (!asm_pack(R, r, at, K, k)) {
+            report_error(err, DERR_ASM_BASE, w.contig_id, w.locus, r);
+            continue;
+          }
+          visit(pass, k, r);
         }
       }
     }
@@ -312,10 +349,7 @@ __global__ void __launch_bounds__(256) asm_nodes_kernel(ReadsView R, AsmWindow* 
   for (int s = threadIdx.x; s < cap; s += blockDim.x) {
     if (T.tag[off + s] == 0 || T.count[off + s] < (uint32_t)P.min_occurrence) continue;
     const int i = atomicAdd(&s_next, 1);
-    const unsigned long long rep = T.rep[off + s];
-    Kmer k;
-    asm_pack(R, (int64_t)(rep >> 16), (int)(rep & 0xFFFF), K, k);
-    G.tmp_key[no + i] = k;
+    G.tmp_key[no + i] = T.key[off + s];
     G.tmp_slot[no + i] = s;
   }
   __syncthreads();
@@ -884,13 +918,13 @@ struct AsmEvidence {
 
 // One warp per window. Medians come from histograms (exact); the two breeze means are running float means,
 // taken in batch order (the reference's order is the window queue's heap order).
-__global__ void __launch_bounds__(128) asm_evidence_kernel(ReadsView R, const AsmWindow* __restrict__ wins, int n_windows, AsmParams P,
-                                                           AsmEvidence* __restrict__ out) {
+__global__ void __launch_bounds__(128) asm_evidence_kernel(ReadsView R, const AsmWindow* __restrict__ wins, const int32_t* __restrict__ which,
+                                                           int n_windows, AsmParams P, AsmEvidence* __restrict__ out) {
   __shared__ uint32_t s_hist[4][2][256];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wi = blockIdx.x * 4 + warp;
+  const int wi = blockIdx.x * 4 + warp;  // index into `which`: only windows that produced variants need evidence
   if (wi >= n_windows) return;
-  const AsmWindow w = wins[wi];
+  const AsmWindow w = wins[which[wi]];
   uint32_t* hm = s_hist[warp][0];
   uint32_t* hb = s_hist[warp][1];
   for (int i = lane; i < 256; i += 32) hm[i] = hb[i] = 0;
