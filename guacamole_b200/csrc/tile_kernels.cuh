@@ -23,6 +23,17 @@
 #pragma once
 #include "kernels.cuh"
 
+// A/B knobs (tools/build_variant.sh): resident CTAs per SM the register allocation aims for, events per locus of capacity
+#ifndef GUAC_TK_MINB
+#define GUAC_TK_MINB 7
+#endif
+#ifndef GUAC_TK_EMUL
+#define GUAC_TK_EMUL 3
+#endif
+#ifndef GUAC_TK_UNROLL
+#define GUAC_TK_UNROLL 1
+#endif
+
 namespace guac {
 
 template <int TL_>
@@ -31,7 +42,7 @@ struct TileCfg {
   static constexpr int THREADS = 256;
   static constexpr int WARPS = THREADS / 32;
   static constexpr int R_MAX = 4095;     // reads per tile (12-bit read index in an event; depth < 2^16 follows)
-  static constexpr int E_MAX = TL * 4;   // non-match events per tile
+  static constexpr int E_MAX = TL * GUAC_TK_EMUL;   // non-match events per tile
   static constexpr int SLOW_MAX = 256;
   static constexpr int EV_SIMPLE = 24;   // a locus with more events goes to the heavy path
 };
@@ -115,10 +126,10 @@ struct TileSmem {
   int nonref[CFG::TL];      // non-Match elements: normal | tumor << 16
   int cursor[CFG::TL];
   uint2 ev[CFG::E_MAX];
-  uint2 ev_sorted[CFG::E_MAX];
+  uint16_t ev_order[CFG::E_MAX];  // event indices bucketed by locus (2 B per event instead of a second copy)
   uint16_t slow[CFG::SLOW_MAX];
   int warp_tot[2][CFG::WARPS];
-  int n_events, n_slow, overflow, ref_has_mask;
+  int n_events, n_slow, overflow, ref_has_mask, n_cand;
 };
 
 struct TileArgs {
@@ -142,7 +153,7 @@ struct TileArgs {
 // slot; normal_sample = -1), a locus is heavy when depth - referenceDepth >= P.min_alt_reads
 // (commands/GermlineAssemblyCaller.scala:135-138).
 template <class CFG, int MODE>
-__global__ void __launch_bounds__(CFG::THREADS, 4)
+__global__ void __launch_bounds__(CFG::THREADS, GUAC_TK_MINB)
 ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TileSmem<CFG>& S = *reinterpret_cast<TileSmem<CFG>*>(smem_raw);
@@ -167,7 +178,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   // ---- init ------------------------------------------------------------------------------
   for (int i = tid; i < TL + 1; i += CFG::THREADS) S.cov[i] = S.aux[i] = 0;
   for (int i = tid; i < TL; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
-  if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = 0;
+  if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = 0;
   if (tid < 4) {  // padding words behind the tile
     S.ref2[TL / 16 + (tid & 1)] = 0;
     S.refmask[TL / 32 + (tid & 1)] = 0;
@@ -201,16 +212,37 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   auto direct = [](int q, int detail) { return 0x80000000u | ((uint32_t)(detail & 0xFF) << 8) | (uint32_t)(q & 0xFF); };
 
   // ---- A. read-parallel pass ---------------------------------------------------------------
+  // The five header loads of a read are independent: issue them together, one read ahead of the one being processed,
+  // so the compare work of read i hides the latency of read i + 256's header.
+  struct Hdr {
+    int64_t st64, en64;
+    uint64_t s0;
+    int smp, rf;
+  };
+  auto load_hdr = [&](int rl) {
+    const int64_t r = tile.read_lo + rl;
+    Hdr h;
+    h.smp = (int)__ldg(R.sample_id + r);
+    h.st64 = __ldg(R.start + r);
+    h.en64 = __ldg(R.end + r);
+    h.rf = (int)__ldg(A.rflags + r);
+    h.s0 = __ldg(R.seq_off + r);
+    return h;
+  };
+  Hdr next_hdr{};
+  if (tid < (int)n_reads_tile) next_hdr = load_hdr(tid);
   for (int rl = tid; rl < (int)n_reads_tile; rl += CFG::THREADS) {
     const int64_t r = tile.read_lo + rl;
-    const int smp = (int)__ldg(R.sample_id + r);
+    const Hdr hdr = next_hdr;
+    if (rl + CFG::THREADS < (int)n_reads_tile) next_hdr = load_hdr(rl + CFG::THREADS);
+    const int smp = hdr.smp;
+    const int64_t st64 = hdr.st64, en64 = hdr.en64;
+    const uint8_t rf = (uint8_t)hdr.rf;
     if (smp != P.normal_sample && smp != P.tumor_sample) continue;
     const int slot = smp == P.tumor_sample ? 1 : 0;
-    const int64_t st64 = __ldg(R.start + r), en64 = __ldg(R.end + r);
     const int st = (int)max((long long)(st64 - t0), -(1ll << 30)), en = (int)min((long long)(en64 - t0), (1ll << 30));
     const int a = max(st, 0), b = min(en, n_loci);  // overlap [a, b) in tile coordinates
     if (a >= b) continue;
-    const uint8_t rf = __ldg(A.rflags + r);
     const int one = slot ? 65536 : 1;
     atomicAdd(&S.cov[a], one);
     atomicAdd(&S.cov[b], -one);
@@ -223,7 +255,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)rl; else S.overflow = 1;
       continue;
     }
-    const uint64_t s0 = __ldg(R.seq_off + r);
+    const uint64_t s0 = hdr.s0;
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     // aligned segment: loci [lb, le) (tile coordinates, unclipped) hold read positions rp0..; 16 bases per step
     auto compare_segment = [&](int lb, int le, int rp0) {
@@ -236,22 +268,26 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       const int rsh = (int)(rbit & 31), fsh = (2 * ca) & 31;
       const uint32_t* fw = S.ref2 + ((2 * ca) >> 5);
       uint32_t rlo = __ldg(rw), flo = fw[0];
-      int k = rp0 + (ca - lb);
-      for (int l = ca; l < cb; l += 16, k += 16) {
+      const uint32_t q_rel = s0_rel + (uint32_t)(rp0 - lb);  // quality index of locus l = q_rel + l
+      auto step = [&](int l, uint32_t keep) {
         const uint32_t rhi = __ldg(++rw), fhi = *++fw;
         const uint32_t rd = __funnelshift_r(rlo, rhi, rsh);
         const uint32_t x = rd ^ __funnelshift_r(flo, fhi, fsh);
         rlo = rhi;
         flo = fhi;
-        uint32_t m = (x | (x >> 1)) & 0x55555555u;
-        if (ref_has_mask) m |= ref_mask_bits(S.refmask, l);  // a not-ACGT reference base never equals an ACGT read base
-        if (cb - l < 16) m &= (1u << (2 * (cb - l))) - 1;
+        uint32_t m = (x | (x >> 1)) & keep;
+        if (ref_has_mask) m |= ref_mask_bits(S.refmask, l) & keep;  // a not-ACGT reference base never equals an ACGT read base
         while (m) {
           const int bit = __ffs(m) - 1;
           m &= m - 1;
-          push_event(l + (bit >> 1), rl, slot, GUAC_ALN_MISMATCH, (rd >> bit) & 3, s0_rel + (uint32_t)(k + (bit >> 1)));
+          push_event(l + (bit >> 1), rl, slot, GUAC_ALN_MISMATCH, (rd >> bit) & 3, q_rel + (uint32_t)(l + (bit >> 1)));
         }
-      }
+      };
+      int l = ca;
+      constexpr int kUnroll = GUAC_TK_UNROLL;
+#pragma unroll kUnroll
+      for (; l + 16 <= cb; l += 16) step(l, 0x55555555u);
+      if (l < cb) step(l, ((1u << (2 * (cb - l))) - 1) & 0x55555555u);  // the tail word, masked once
     };
     if (rf & RF_FAST) {
       compare_segment(st, en, 0);
@@ -383,7 +419,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const int l = ev.x & 0x7FF;
     const int nr = S.nonref[l];
     const int first = (S.aux[l] >> 16) - ((nr & 0xFFFF) + (nr >> 16));
-    S.ev_sorted[first + atomicAdd(&S.cursor[l], 1)] = ev;
+    S.ev_order[first + atomicAdd(&S.cursor[l], 1)] = (uint16_t)i;
   }
   __syncthreads();
 
@@ -400,7 +436,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     // early-outs (SomaticStandardCaller.scala:164-172)
     const bool candidate = MODE == 0 ? (dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt)
                                      : (dT > 0 && nrT >= P.min_alt_reads);
-    int top_t = 0, top_n = 0, flags = 0;
+    int flags = 0;
     if (MODE == 1 && candidate) {  // every candidate locus gets the full genotype likelihoods
       const int h = atomicAdd(A.n_heavy, 1);
       if (h < A.max_heavy) {
@@ -417,7 +453,31 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       }
       flags = 1;
     }
-    if (MODE == 0 && candidate) {
+    if (MODE == 0 && candidate) {  // the few candidate loci are examined densely in a second pass
+      S.cursor[atomicAdd(&S.n_cand, 1)] = l;
+      continue;
+    }
+    // dense summary (normal, tumor): one 16-byte store per locus
+    uint4 v;
+    v.x = (uint32_t)min(dN, 65535) | ((uint32_t)min(dN - nrN, 65535) << 16);
+    v.y = (uint32_t)flags << 16;
+    v.z = (uint32_t)min(dT, 65535) | ((uint32_t)min(dT - nrT, 65535) << 16);
+    v.w = (uint32_t)flags << 16;
+    reinterpret_cast<uint4*>(A.summary)[slot] = v;
+  }
+  my_visited = __reduce_add_sync(FULL, my_visited);
+  if (lane == 0 && my_visited) atomicAdd(A.n_visited, (unsigned long long)my_visited);
+  if (MODE != 0) return;
+  __syncthreads();
+  const int n_cand = S.n_cand;
+  for (int ci = tid; ci < n_cand; ci += CFG::THREADS) {
+    const int l = S.cursor[ci];
+    const int cv = S.cov[l], nr = S.nonref[l];
+    const int dN = cv & 0xFFFF, dT = cv >> 16;
+    const int nrN = nr & 0xFFFF, nrT = nr >> 16;
+    const int64_t slot = tile.slot0 + l, x = t0 + l;
+    int top_t = 0, top_n = 0, flags = 0;
+    {
       const int e1 = S.aux[l] >> 16, e0 = e1 - (nrN + nrT);
       bool simple = e1 - e0 <= CFG::EV_SIMPLE;
       // Distinct tumor variant alleles of the locus, straight from its (few) events.  An allele is
@@ -430,7 +490,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       int best = -1, bcnt = 0, bfirst = INT_MAX;
       if (simple)
         for (int i = e0; i < e1; ++i) {
-          const uint2 ev = S.ev_sorted[i];
+          const uint2 ev = S.ev[S.ev_order[i]];
           const int eslot = (ev.x >> 23) & 1, kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7;
           if (code == 5 || (kind == GUAC_ALN_MISMATCH && code == 4)) {  // either sample: allele not identified here
             simple = false;
@@ -441,7 +501,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
           int c = 0, first = INT_MAX;
           bool seen_before = false;
           for (int j = e0; j < e1; ++j) {
-            const uint2 ej = S.ev_sorted[j];
+            const uint2 ej = S.ev[S.ev_order[j]];
             if (((ej.x >> 23) & 1) != 1 || ((ej.x >> 24) & 7) == GUAC_ALN_CLIPPED || akey(ej) != key) continue;
             if (j < i) seen_before = true;
             ++c;
@@ -459,7 +519,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       if (simple && (best >> 8) == GUAC_ALN_INSERTION) {
         int same = 0;
         for (int j = e0; j < e1; ++j) {
-          const uint2 ej = S.ev_sorted[j];
+          const uint2 ej = S.ev[S.ev_order[j]];
           same += ((ej.x >> 24) & 7) == GUAC_ALN_INSERTION && akey(ej) == best;
         }
         if (same > 1) simple = false;  // equal hashes: the exact path compares the sequences
@@ -477,7 +537,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         int n_alt_normal = 0;
         const bool at_floor = f == P.min_vaf;
         for (int i = e0; i < e1; ++i) {
-          const uint2 ev = S.ev_sorted[i];
+          const uint2 ev = S.ev[S.ev_order[i]];
           const int eslot = (ev.x >> 23) & 1, kind = (ev.x >> 24) & 7;
           if (kind == GUAC_ALN_CLIPPED || akey(ev) != best) continue;
           if (eslot == 0) {
@@ -527,8 +587,6 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     v.w = (uint32_t)min(top_t, 65535) | ((uint32_t)flags << 16);
     reinterpret_cast<uint4*>(A.summary)[slot] = v;
   }
-  my_visited = __reduce_add_sync(FULL, my_visited);
-  if (lane == 0 && my_visited) atomicAdd(A.n_visited, (unsigned long long)my_visited);
 }
 
 }  // namespace guac

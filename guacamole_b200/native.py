@@ -16,7 +16,7 @@ from .io import Reference
 from .reads import ReadBatch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libguac_b200.so")
+LIB_PATH = os.environ.get("GUAC_B200_LIB") or os.path.join(_HERE, "csrc", "libguac_b200.so")  # override: kernel A/B builds
 
 
 class GuacError(RuntimeError):
