@@ -72,7 +72,7 @@ struct guac_ctx {
   int64_t opt_ss_impl = 0;            // 0 = streaming tile kernel (+ gather fallback), 1 = gather kernel only
   int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
-  DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites;
+  DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used;
   double bound_tab_vaf = -1;
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
@@ -425,6 +425,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_vcount.p) cudaFree(ctx->b_vcount.p);
   if (ctx->b_sj_sites.p) cudaFree(ctx->b_sj_sites.p);
   if (ctx->b_boundtab.p) cudaFree(ctx->b_boundtab.p);
+  if (ctx->b_arena_used.p) cudaFree(ctx->b_arena_used.p);
   for (auto& b : ctx->asm_blocks) cudaFree(b.first);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -825,32 +826,41 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     max_calls = nc;  // rerun with room for every call
   }
   trace.mark("per-locus kernels done");
-  // sparse part: sort by slot (= range order, locus), lay out the allele arena, compute the evidence
-  std::vector<SSCallDev> calls((size_t)nc);
+  // sparse part: one kernel fills the evidence and the allele strings of every call; the records come back through
+  // pinned memory and are put in (range order, locus) order on the host
+  SSCallDev* calls = nullptr;
+  {
+    void* hp = nullptr;
+    GUAC_TRY(pinned_alloc(ctx, &hp, std::max<size_t>((size_t)nc * sizeof(SSCallDev), 16)));
+    calls = static_cast<SSCallDev*>(hp);
+  }
+  *arena_len = 0;
   if (nc > 0) {
-    ss_allele_lengths_kernel<<<blocks_for(nc, 128), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(),
-                                                                           ctx->b_calls.as<SSCallDev>(), nc);
-    ctx->launches += 1;
-    CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaMemcpyAsync(calls.data(), ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    std::sort(calls.begin(), calls.end(), [](const SSCallDev& a, const SSCallDev& b) { return a.slot < b.slot; });
-    uint32_t off = 0;
-    for (auto& c : calls) {
-      c.ref_off = off;
-      off += c.ref_len;
-      c.alt_off = off;
-      off += c.alt_len;
+    GUAC_TRY(ensure(ctx, ctx->b_arena_used, sizeof(unsigned int)));
+    GUAC_TRY(ensure(ctx, ctx->b_arena, (size_t)nc * 32 + 4096));
+    for (int attempt = 0; attempt < 2; ++attempt) {
+      unsigned int used = 0;
+      CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_arena_used.p, 0, sizeof(unsigned int), ctx->stream));
+      ss_evidence_kernel<<<(unsigned)nc, 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(),
+                                                                ctx->b_arena.as<char>(), ctx->b_arena_used.as<unsigned int>(),
+                                                                (unsigned int)std::min<size_t>(ctx->b_arena.cap, 0xFFFFFFFFu),
+                                                                ctx->b_err.as<DeviceError>());
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+      CUDA_TRY(ctx, cudaMemcpyAsync(calls, ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&used, ctx->b_arena_used.p, sizeof used, cudaMemcpyDeviceToHost, ctx->stream));
+      {
+        int st = check_device_error(ctx);  // synchronises
+        if (st != GUAC_OK) {
+          guac_free(ctx, calls);
+          return st;
+        }
+      }
+      *arena_len = used;
+      if ((size_t)used <= ctx->b_arena.cap) break;
+      GUAC_TRY(ensure(ctx, ctx->b_arena, (size_t)used + 16));  // long indel alleles: grow and redo
     }
-    *arena_len = off;
-    GUAC_TRY(ensure(ctx, ctx->b_arena, off + 16));
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->b_calls.p, calls.data(), (size_t)nc * sizeof(SSCallDev), cudaMemcpyHostToDevice, ctx->stream));
-    ss_evidence_kernel<<<(unsigned)nc, 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(),
-                                                              ctx->b_arena.as<char>(), ctx->b_err.as<DeviceError>());
-    ctx->launches += 1;
-    CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaMemcpyAsync(calls.data(), ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
-    GUAC_TRY(check_device_error(ctx));
+    std::sort(calls, calls + nc, [](const SSCallDev& a, const SSCallDev& b) { return a.slot < b.slot; });
   }
   trace.mark("evidence");
   void* h = nullptr;
@@ -875,6 +885,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     g.normal_reference_evidence = c.normal_ev;
     oc[i] = g;
   }
+  guac_free(ctx, calls);
   *out_calls = oc;
   *n_calls = nc;
   GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)*arena_len));

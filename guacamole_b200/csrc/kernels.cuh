@@ -483,121 +483,137 @@ __device__ inline void hist_middle(const unsigned* h, int bins, int n, int& a, i
 // Also writes the allele strings (variants/Allele.scala) into the arena.
 __global__ void __launch_bounds__(128)
 ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P, SSCallDev* __restrict__ calls,
-                   char* __restrict__ arena, DeviceError* err) {
-  __shared__ unsigned h_mapq[256], h_bq[256], h_mm[MM_BINS];
-  __shared__ unsigned s_depth, s_pos, s_adepth, s_apos;
+                   char* __restrict__ arena, unsigned int* __restrict__ arena_used, unsigned int arena_cap, DeviceError* err) {
+  // [0] tumor with the called allele, [1] normal with the reference allele
+  __shared__ unsigned h_mapq[2][256], h_bq[2][256], h_mm[2][MM_BINS];
+  __shared__ unsigned s_depth[2], s_pos[2], s_adepth[2], s_apos[2];
+  __shared__ int s_list[1024];  // reads of either sample that overlap the locus (read offset << 1 | which)
+  __shared__ int s_n;
   SSCallDev& c = calls[blockIdx.x];
   const RefView ref = refs[c.ref_index];
   const int64_t x = c.locus;
-  for (int which = 0; which < 2; ++which) {
-    const int target = which == 0 ? P.tumor_sample : P.normal_sample;
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) h_mapq[i] = h_bq[i] = 0;
-    for (int i = threadIdx.x; i < MM_BINS; i += blockDim.x) h_mm[i] = 0;
-    if (threadIdx.x == 0) s_depth = s_pos = s_adepth = s_apos = 0;
-    __syncthreads();
-    for (int64_t r = c.read_lo + threadIdx.x; r < c.read_hi; r += blockDim.x) {
-      if (!(__ldg(R.start + r) <= x && x < __ldg(R.end + r)) || __ldg(R.sample_id + r) != target) continue;
-      Elem e;
-      if (element_at(R, r, x, ref, e) != DERR_NONE) continue;
-      const bool pos = __ldg(R.flags + r) & GUAC_READ_POSITIVE_STRAND;
-      atomicAdd(&s_depth, 1u);
-      if (pos) atomicAdd(&s_pos, 1u);
-      bool isAllele;
-      if (which == 0)
-        isAllele = e.kind != GUAC_ALN_MATCH && e.kind != GUAC_ALN_CLIPPED && allele_key(R, r, e) == c.key;
-      else
-        isAllele = e.kind == GUAC_ALN_MATCH;
-      if (isAllele) {
-        atomicAdd(&s_adepth, 1u);
-        if (pos) atomicAdd(&s_apos, 1u);
-        atomicAdd(&h_mapq[__ldg(R.mapq + r)], 1u);
-        atomicAdd(&h_bq[e.quality], 1u);
-        int mm = count_of_mismatches(R, r, ref, err, c.contig_id);
-        if (mm >= MM_BINS) {
-          report_error(err, DERR_MISMATCH_HIST, c.contig_id, x, r);
-          mm = MM_BINS - 1;
-        }
-        atomicAdd(&h_mm[mm], 1u);
-      }
+  for (int i = threadIdx.x; i < 512; i += blockDim.x) (&h_mapq[0][0])[i] = (&h_bq[0][0])[i] = 0;
+  for (int i = threadIdx.x; i < 2 * MM_BINS; i += blockDim.x) (&h_mm[0][0])[i] = 0;
+  if (threadIdx.x < 2) s_depth[threadIdx.x] = s_pos[threadIdx.x] = s_adepth[threadIdx.x] = s_apos[threadIdx.x] = 0;
+  if (threadIdx.x == 0) s_n = 0;
+  __syncthreads();
+  // reads are sorted by start: nothing at or after the first read that starts beyond the locus can overlap it
+  int64_t hi = c.read_hi;
+  {
+    int64_t a = c.read_lo, b = c.read_hi;
+    while (a < b) {
+      const int64_t m = (a + b) >> 1;
+      if (__ldg(R.start + m) <= x) a = m + 1; else b = m;
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      guac_allele_evidence ev;
-      const double lp = which == 0 ? c.tumor_alt_lp : c.normal_ref_lp;
-      ev.probability = exp(-lp);  // SomaticStandardCaller.scala:237-238 (sic)
-      ev.read_depth = (int)s_depth;
-      ev.allele_read_depth = (int)s_adepth;
-      ev.forward_depth = (int)s_pos;
-      ev.allele_forward_depth = (int)s_apos;
-      const int n = (int)s_adepth;
-      if (n == 0) {
-        const double nan = __longlong_as_double(0x7ff8000000000000ll);
-        ev.mean_mapping_quality = ev.median_mapping_quality = ev.mean_base_quality = ev.median_base_quality =
-            ev.median_mismatches_per_read = nan;
-      } else {
-        double sm = 0, sq = 0;
-        for (int v = 0; v < 256; ++v) {
-          sm += (double)v * h_mapq[v];
-          sq += (double)v * h_bq[v];
-        }
-        ev.mean_mapping_quality = sm / n;
-        ev.mean_base_quality = sq / n;
-        int a, b;
-        hist_middle(h_mapq, 256, n, a, b);
-        ev.median_mapping_quality = (n & 1) ? (double)a : ((double)a + (double)b) / 2;
-        hist_middle(h_bq, 256, n, a, b);
-        ev.median_base_quality = (n & 1) ? (double)a : ((double)a + (double)b) / 2;
-        hist_middle(h_mm, MM_BINS, n, a, b);
-        ev.median_mismatches_per_read = (n & 1) ? (double)a : (double)((a + b) / 2);  // DenseVector[Int] median
-      }
-      if (which == 0) c.tumor_ev = ev; else c.normal_ev = ev;
-    }
-    __syncthreads();
+    hi = a;
   }
-  // allele strings
+  auto visit = [&](int64_t r, int which) {
+    Elem e;
+    if (element_at(R, r, x, ref, e) != DERR_NONE) return;
+    const bool pos = __ldg(R.flags + r) & GUAC_READ_POSITIVE_STRAND;
+    atomicAdd(&s_depth[which], 1u);
+    if (pos) atomicAdd(&s_pos[which], 1u);
+    bool isAllele;
+    if (which == 0)
+      isAllele = e.kind != GUAC_ALN_MATCH && e.kind != GUAC_ALN_CLIPPED && allele_key(R, r, e) == c.key;
+    else
+      isAllele = e.kind == GUAC_ALN_MATCH;
+    if (isAllele) {
+      atomicAdd(&s_adepth[which], 1u);
+      if (pos) atomicAdd(&s_apos[which], 1u);
+      atomicAdd(&h_mapq[which][__ldg(R.mapq + r)], 1u);
+      atomicAdd(&h_bq[which][e.quality], 1u);
+      int mm = count_of_mismatches(R, r, ref, err, c.contig_id);
+      if (mm >= MM_BINS) {
+        report_error(err, DERR_MISMATCH_HIST, c.contig_id, x, r);
+        mm = MM_BINS - 1;
+      }
+      atomicAdd(&h_mm[which][mm], 1u);
+    }
+  };
+  // pass 1: which reads overlap the locus (cheap, coalesced); pass 2: one thread per overlapping read
+  for (int64_t r = c.read_lo + threadIdx.x; r < hi; r += blockDim.x) {
+    if (x >= __ldg(R.end + r)) continue;
+    const int smp = __ldg(R.sample_id + r);
+    if (smp != P.tumor_sample && smp != P.normal_sample) continue;
+    const int which = smp == P.tumor_sample ? 0 : 1;
+    const int i = atomicAdd(&s_n, 1);
+    if (i < 1024) s_list[i] = (int)((r - c.read_lo) << 1) | which; else visit(r, which);  // deeper than the list: in place
+  }
+  __syncthreads();
+  const int n_list = min(s_n, 1024);
+  for (int i = threadIdx.x; i < n_list; i += blockDim.x) visit(c.read_lo + (s_list[i] >> 1), s_list[i] & 1);
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    const int which = threadIdx.x;
+    guac_allele_evidence ev;
+    const double lp = which == 0 ? c.tumor_alt_lp : c.normal_ref_lp;
+    ev.probability = exp(-lp);  // SomaticStandardCaller.scala:237-238 (sic)
+    ev.read_depth = (int)s_depth[which];
+    ev.allele_read_depth = (int)s_adepth[which];
+    ev.forward_depth = (int)s_pos[which];
+    ev.allele_forward_depth = (int)s_apos[which];
+    const int n = (int)s_adepth[which];
+    if (n == 0) {
+      const double nan = __longlong_as_double(0x7ff8000000000000ll);
+      ev.mean_mapping_quality = ev.median_mapping_quality = ev.mean_base_quality = ev.median_base_quality =
+          ev.median_mismatches_per_read = nan;
+    } else {
+      double sm = 0, sq = 0;
+      for (int v = 0; v < 256; ++v) {
+        sm += (double)v * h_mapq[which][v];
+        sq += (double)v * h_bq[which][v];
+      }
+      ev.mean_mapping_quality = sm / n;
+      ev.mean_base_quality = sq / n;
+      int a, b;
+      hist_middle(h_mapq[which], 256, n, a, b);
+      ev.median_mapping_quality = (n & 1) ? (double)a : ((double)a + (double)b) / 2;
+      hist_middle(h_bq[which], 256, n, a, b);
+      ev.median_base_quality = (n & 1) ? (double)a : ((double)a + (double)b) / 2;
+      hist_middle(h_mm[which], MM_BINS, n, a, b);
+      ev.median_mismatches_per_read = (n & 1) ? (double)a : (double)((a + b) / 2);  // DenseVector[Int] median
+    }
+    if (which == 0) c.tumor_ev = ev; else c.normal_ev = ev;
+  }
+  // allele strings: lengths, a slice of the arena (claimed with one atomic; the host grows the arena and re-runs
+  // this kernel in the rare case the slices do not fit), then the bases
   if (threadIdx.x == 0) {
     const int kind = (int)(c.key >> 60);
-    char* rp = arena + c.ref_off;
-    char* ap = arena + c.alt_off;
-    const uint8_t rb = ref.at(x);
-    if (kind == 1) {  // Mismatch
-      rp[0] = (char)rb;
-      ap[0] = (char)(c.key & 0xff);
-    } else if (kind == 3) {  // Deletion: ref = ref[x .. x+len], alt = ref[x]
-      for (uint32_t k = 0; k < c.ref_len; ++k) rp[k] = (char)ref.at(x + k);
-      ap[0] = (char)rb;
-    } else if (kind == 2 || kind == 5) {  // Insertion: ref = seq[0], alt = seq
-      Elem e;
-      if (element_at(R, c.rep_read, x, ref, e) == DERR_NONE) {
-        const uint64_t s0 = __ldg(R.seq_off + c.rep_read);
-        for (uint32_t k = 0; k < c.alt_len; ++k) ap[k] = (char)read_base(R, s0 + e.read_position + k);
-        rp[0] = ap[0];
+    Elem e;
+    bool have_elem = false;
+    uint32_t ref_len = 1, alt_len = 1;
+    if (kind == 3) {
+      ref_len = (uint32_t)(c.key & 0xffffffffu) + 1;
+    } else if (kind != 1) {
+      have_elem = element_at(R, c.rep_read, x, ref, e) == DERR_NONE;
+      if (have_elem) {
+        const int32_t read_len = (int32_t)(__ldg(R.seq_off + c.rep_read + 1) - __ldg(R.seq_off + c.rep_read));
+        alt_len = (uint32_t)(min(e.read_position + e.indel_length + 1, read_len) - e.read_position);
       }
     }
-  }
-}
-
-// lengths of the allele strings of a call (host lays out the arena)
-__global__ void ss_allele_lengths_kernel(ReadsView R, const RefView* __restrict__ refs, SSCallDev* __restrict__ calls, int n) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  SSCallDev& c = calls[i];
-  const int kind = (int)(c.key >> 60);
-  if (kind == 1) {
-    c.ref_len = 1;
-    c.alt_len = 1;
-  } else if (kind == 3) {
-    c.ref_len = (uint32_t)(c.key & 0xffffffffu) + 1;
-    c.alt_len = 1;
-  } else {
-    Elem e;
-    const RefView ref = refs[c.ref_index];
-    c.ref_len = 1;
-    c.alt_len = 1;
-    if (element_at(R, c.rep_read, c.locus, ref, e) == DERR_NONE) {
-      const uint64_t s0 = __ldg(R.seq_off + c.rep_read);
-      const int32_t read_len = (int32_t)(__ldg(R.seq_off + c.rep_read + 1) - s0);
-      c.alt_len = (uint32_t)(min(e.read_position + e.indel_length + 1, read_len) - e.read_position);
+    const unsigned int off = atomicAdd(arena_used, ref_len + alt_len);
+    c.ref_len = ref_len;
+    c.alt_len = alt_len;
+    c.ref_off = off;
+    c.alt_off = off + ref_len;
+    if (off + ref_len + alt_len <= arena_cap) {
+      char* rp = arena + c.ref_off;
+      char* ap = arena + c.alt_off;
+      const uint8_t rb = ref.at(x);
+      if (kind == 1) {  // Mismatch
+        rp[0] = (char)rb;
+        ap[0] = (char)(c.key & 0xff);
+      } else if (kind == 3) {  // Deletion: ref = ref[x .. x+len], alt = ref[x]
+        for (uint32_t k = 0; k < ref_len; ++k) rp[k] = (char)ref.at(x + k);
+        ap[0] = (char)rb;
+      } else if (kind == 2 || kind == 5) {  // Insertion: ref = seq[0], alt = seq
+        if (have_elem) {
+          const uint64_t s0 = __ldg(R.seq_off + c.rep_read);
+          for (uint32_t k = 0; k < alt_len; ++k) ap[k] = (char)read_base(R, s0 + e.read_position + k);
+          rp[0] = ap[0];
+        }
+      }
     }
   }
 }
