@@ -553,7 +553,7 @@ int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* b) {
   GUAC_TRY(upload(ctx, ctx->b_cigar_off, b->cigar_off, (size_t)n + 1));
   GUAC_TRY(upload(ctx, ctx->b_cigar, b->cigar, (size_t)n_cigar));
   GUAC_TRY(upload(ctx, ctx->b_seq_off, b->seq_off, (size_t)n + 1));
-  GUAC_TRY(upload(ctx, ctx->b_bases2, b->bases2, (size_t)((n_bases + 3) / 4)));
+  GUAC_TRY(upload(ctx, ctx->b_bases2, b->bases2, (size_t)((n_bases + 3) / 4), 64));  // padding: word read-ahead / 16-byte bulk copies
   GUAC_TRY(upload(ctx, ctx->b_nmask, b->nmask, (size_t)((n_bases + 7) / 8)));
   GUAC_TRY(upload(ctx, ctx->b_exc_pos, b->exc_pos, (size_t)b->n_exc));
   GUAC_TRY(upload(ctx, ctx->b_exc_base, b->exc_base, (size_t)b->n_exc));
@@ -708,7 +708,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   P.max_normal_alt = params->max_normal_alternate_read_depth;
   P.min_vaf = (double)params->min_tumor_variant_allele_frequency;
   P.min_alt_reads = 0;
-  P._pad = 0;
+  P.sample_mask = 0;
   if (P.normal_sample < 0 || P.tumor_sample < 0 || P.normal_sample == P.tumor_sample || P.n_samples > ctx->n_samples)
     return fail(ctx, GUAC_E_INVALID_INPUT, "bad normal/tumor sample ids");
   if (plan.n_tiles == 0) {
@@ -958,8 +958,10 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     r.end = r.end - 1;
     if (r.end > r.start) shifted.push_back(r);
   }
+  Trace trace;
+  using TCfg = TileCfg<512>;
   Plan plan;
-  GUAC_TRY(make_plan(ctx, shifted.data(), (int32_t)shifted.size(), plan));
+  GUAC_TRY(make_plan(ctx, shifted.data(), (int32_t)shifted.size(), plan, TCfg::TL));
   *n_alleles = 0;
   *n_sample_evidences = 0;
   *arena_len = 0;
@@ -973,19 +975,76 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
   GUAC_TRY(reset_error(ctx));
   GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
   GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(int)));
+  GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 2) * sizeof(int)));
+  GUAC_TRY(ensure(ctx, ctx->b_vcount, sizeof(unsigned long long)));
   DevBuf d_force;
   GUAC_TRY(upload(ctx, d_force, force_loci, (size_t)n_force));
+  // Dense half: the streaming tile kernel marks the visited loci and lists the pileup loci where an alternate allele can
+  // start (>= any_allele_min_supporting_reads reads of the discovery samples with a non-Match element at the next
+  // locus, or a force-called locus); only those go to the per-locus discovery kernel.
+  SSParamsDev SP;
+  std::memset(&SP, 0, sizeof SP);
+  SP.normal_sample = SP.tumor_sample = -1;
+  SP.n_samples = S;
+  SP.min_alt_reads = std::max(1, params->any_allele_min_supporting_reads);
+  for (int d = 0; d < P.n_discovery; ++d) SP.sample_mask |= 1u << P.discovery[d];
+  int* fb_count = ctx->b_fallback.as<int>();
+  int* fb_list = fb_count + 1;
+  int* heavy_count = fb_count + 1 + plan.n_tiles;
+  int max_heavy = (int)std::min<int64_t>(plan.n_slots, plan.n_slots / 4 + 65536);
+  int counts[2] = {0, 0};
+  cudaEventRecord(ctx->ev0, ctx->stream);
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
+    CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(heavy_count, 0, sizeof(int), ctx->stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_vcount.p, 0, sizeof(unsigned long long), ctx->stream));
+    TileArgs TA;
+    std::memset(&TA, 0, sizeof TA);
+    TA.rflags = ctx->b_rflags.as<uint8_t>();
+    TA.refs = ctx->d_refs.as<RefView>();
+    TA.tiles = ctx->b_tiles.as<Tile>();
+    TA.visited = ctx->b_visited.as<uint8_t>();
+    TA.heavy = ctx->b_heavy.as<Tile>();
+    TA.n_heavy = heavy_count;
+    TA.max_heavy = max_heavy;
+    TA.fallback_tiles = fb_list;
+    TA.n_fallback = fb_count;
+    TA.force_fallback_mod = (int)ctx->opt_force_fallback_mod;
+    TA.n_visited = ctx->b_vcount.as<unsigned long long>();
+    TA.err = ctx->b_err.as<DeviceError>();
+    TA.force = d_force.as<guac_range>();
+    TA.n_force = n_force;
+    ss_tile_kernel<TCfg, 2><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, SP, TA);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(&counts[0], fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&counts[1], heavy_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (counts[1] <= max_heavy) break;
+    max_heavy = counts[1];  // rerun with room for every candidate locus
+  }
+  ctx->last_fallback_tiles = counts[0];
+  ctx->last_heavy_loci = counts[1];
+  trace.mark("dense prefilter");
   int max_sites = (int)std::max<size_t>(ctx->b_sj_sites.cap / sizeof(SJSiteDev), 1 << 14);
   int n_sites = 0;
   for (int attempt = 0; attempt < 2; ++attempt) {
     GUAC_TRY(ensure(ctx, ctx->b_sj_sites, (size_t)max_sites * sizeof(SJSiteDev)));
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
-    cudaEventRecord(ctx->ev0, ctx->stream);
-    sj_discover_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
-        ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), P, d_force.as<guac_range>(), n_force, ctx->b_visited.as<uint8_t>(),
-        ctx->b_sj_sites.as<SJSiteDev>(), ctx->b_ncalls.as<int>(), max_sites, ctx->b_err.as<DeviceError>());
+    if (counts[0] > 0) {  // whole tiles the streaming kernel declined
+      sj_discover_kernel<<<(unsigned)counts[0], CTA_THREADS, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, counts[0], 0, P, d_force.as<guac_range>(), n_force,
+          ctx->b_visited.as<uint8_t>(), ctx->b_sj_sites.as<SJSiteDev>(), ctx->b_ncalls.as<int>(), max_sites, ctx->b_err.as<DeviceError>());
+      ctx->launches += 1;
+    }
+    if (counts[1] > 0) {  // candidate loci, one warp each
+      sj_discover_kernel<<<blocks_for(counts[1], WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, counts[1], 1, P, d_force.as<guac_range>(), n_force, nullptr,
+          ctx->b_sj_sites.as<SJSiteDev>(), ctx->b_ncalls.as<int>(), max_sites, ctx->b_err.as<DeviceError>());
+      ctx->launches += 1;
+    }
     cudaEventRecord(ctx->ev1, ctx->stream);
-    ctx->launches += 1;
     ctx->have_timing = true;
     ctx->timed_loci = plan.n_slots;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -999,31 +1058,48 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     max_sites = n_sites;
   }
   cudaFree(d_force.p);
-  std::vector<SJSiteDev> sites((size_t)n_sites);
-  std::vector<SJEvidenceDev> raw;
+  trace.mark("discover");
+  // sites stay on the device in discovery order; the host walks them in (range order, locus) order through `order`
+  const size_t raw_stride = offsetof(SJEvidenceDev, slots) + (size_t)(S + 2) * sizeof(SJSlotDev);
+  SJSiteDev* sites = nullptr;
+  unsigned char* raw = nullptr;
+  std::vector<int> order((size_t)n_sites);
   std::vector<int2> jobs;
+  struct PinnedGuard {  // pinned staging goes back to the pool on every return path
+    guac_ctx* ctx;
+    void* p[2] = {nullptr, nullptr};
+    ~PinnedGuard() {
+      for (void* q : p)
+        if (q) guac_free(ctx, q);
+    }
+  } staging{ctx};
   if (n_sites > 0) {
-    CUDA_TRY(ctx, cudaMemcpyAsync(sites.data(), ctx->b_sj_sites.p, (size_t)n_sites * sizeof(SJSiteDev), cudaMemcpyDeviceToHost, ctx->stream));
+    GUAC_TRY(pinned_alloc(ctx, &staging.p[0], (size_t)n_sites * sizeof(SJSiteDev)));
+    sites = static_cast<SJSiteDev*>(staging.p[0]);
+    CUDA_TRY(ctx, cudaMemcpyAsync(sites, ctx->b_sj_sites.p, (size_t)n_sites * sizeof(SJSiteDev), cudaMemcpyDeviceToHost, ctx->stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    std::sort(sites.begin(), sites.end(), [](const SJSiteDev& a, const SJSiteDev& b) { return a.slot < b.slot; });
+    for (int i = 0; i < n_sites; ++i) order[(size_t)i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return sites[a].slot < sites[b].slot; });
     for (int i = 0; i < n_sites; ++i)
-      for (int a = 0; a < sites[i].n_alleles; ++a) jobs.push_back(make_int2(i, a));
+      for (int a = 0; a < sites[order[(size_t)i]].n_alleles; ++a) jobs.push_back(make_int2(order[(size_t)i], a));
     DevBuf d_jobs, d_raw;
     GUAC_TRY(upload(ctx, d_jobs, jobs.data(), jobs.size()));
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->b_sj_sites.p, sites.data(), (size_t)n_sites * sizeof(SJSiteDev), cudaMemcpyHostToDevice, ctx->stream));
-    GUAC_TRY(ensure(ctx, d_raw, jobs.size() * sizeof(SJEvidenceDev)));
+    GUAC_TRY(ensure(ctx, d_raw, jobs.size() * raw_stride));
+    GUAC_TRY(pinned_alloc(ctx, &staging.p[1], jobs.size() * raw_stride));
+    raw = static_cast<unsigned char*>(staging.p[1]);
     sj_evidence_kernel<<<(unsigned)jobs.size(), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_sj_sites.as<SJSiteDev>(),
-                                                                         d_jobs.as<int2>(), d_raw.as<SJEvidenceDev>(),
+                                                                         d_jobs.as<int2>(), d_raw.as<unsigned char>(), raw_stride,
                                                                          ctx->b_err.as<DeviceError>());
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
-    raw.resize(jobs.size());
-    CUDA_TRY(ctx, cudaMemcpyAsync(raw.data(), d_raw.p, jobs.size() * sizeof(SJEvidenceDev), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(raw, d_raw.p, jobs.size() * raw_stride, cudaMemcpyDeviceToHost, ctx->stream));
     int st = check_device_error(ctx);
     cudaFree(d_jobs.p);
     cudaFree(d_raw.p);
     if (st != GUAC_OK) return st;
   }
+  trace.mark("evidence kernel");
+  if (trace.on) std::fprintf(stderr, "[guac trace] sites %d jobs %zu\n", n_sites, jobs.size());
   // host: posteriors, calls, annotations, emit policy; then lay out the strings
   std::vector<guac_sj_allele_evidence> alleles;
   std::vector<guac_sj_sample_evidence> samples;
@@ -1043,15 +1119,17 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
   };
   size_t job_i = 0;
   int site_index = 0;
-  for (int i = 0; i < n_sites; ++i) {
+  for (int oi = 0; oi < n_sites; ++oi) {
+    const SJSiteDev& site = sites[order[(size_t)oi]];
     std::vector<joint::Record> all;
-    for (int a = 0; a < sites[i].n_alleles; ++a, ++job_i) all.push_back(joint::evaluate(*params, sites[i], a, raw[job_i]));
-    std::vector<joint::Record> emitted = joint::emit(*params, sites[i].forced != 0, all);
+    for (int a = 0; a < site.n_alleles; ++a, ++job_i)
+      all.push_back(joint::evaluate(*params, site, a, *reinterpret_cast<const SJEvidenceDev*>(raw + job_i * raw_stride)));
+    std::vector<joint::Record> emitted = joint::emit(*params, site.forced != 0, all);
     if (emitted.empty()) continue;
     for (auto& rec : emitted) {
-      const SJAlleleDev& al = sites[i].alleles[rec.raw->allele];
+      const SJAlleleDev& al = site.alleles[rec.raw->allele];
       rec.allele.site_index = site_index;
-      add_string(1, sites[i].locus + 1, sites[i].ref_index, al.span, rec.allele.ref_off, rec.allele.ref_len);
+      add_string(1, site.locus + 1, site.ref_index, al.span, rec.allele.ref_off, rec.allele.ref_len);
       if (al.key == 0) add_string(2, 0, 0, 1, rec.allele.alt_off, rec.allele.alt_len);
       else add_string(0, al.rep_read, al.rep_start_rp, al.alt_len, rec.allele.alt_off, rec.allele.alt_len);
       rec.allele.first_sample_evidence = (int64_t)samples.size();
@@ -1066,6 +1144,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     }
     ++site_index;
   }
+  trace.mark("host evaluate");
   *arena_len = arena_off;
   if (!strings.empty()) {
     DevBuf d_strings;
@@ -1417,7 +1496,7 @@ int guac_synth_generate(guac_ctx* ctx, int32_t contig_id, int64_t contig_len, in
   GUAC_TRY(ensure(ctx, ctx->b_nops, (size_t)n + 16));
   GUAC_TRY(ensure(ctx, ctx->b_cigar_off, (size_t)(n + 1) * 4 + 16));
   GUAC_TRY(ensure(ctx, ctx->b_cigar, (size_t)n * 3 * 4 + 16));
-  GUAC_TRY(ensure(ctx, ctx->b_bases2, (size_t)(n_bases / 4) + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_bases2, (size_t)(n_bases / 4) + 64));
   GUAC_TRY(ensure(ctx, ctx->b_nmask, (size_t)(n_bases / 8) + 16));
   GUAC_TRY(ensure(ctx, ctx->b_qual, (size_t)n_bases + 16));
   GUAC_TRY(ensure(ctx, ctx->b_exc_pos, 16));

@@ -135,14 +135,18 @@ __device__ inline bool locus_forced(const guac_range* force, int n_force, int co
 }
 
 __global__ void __launch_bounds__(CTA_THREADS)
-sj_discover_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles, SJParamsDev P,
-                   const guac_range* __restrict__ force, int n_force, uint8_t* __restrict__ visited, SJSiteDev* __restrict__ sites,
-                   int* __restrict__ n_sites, int max_sites, DeviceError* err) {
-  const Tile tile = tiles[blockIdx.x];
-  const RefView ref = refs[tile.ref_index];
+sj_discover_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles,
+                   const int* __restrict__ tile_list /* nullptr: identity */, int n_tiles,
+                   int tile_per_warp /* 0: the CTA's warps share one tile; 1: one (single-locus) tile per warp */, SJParamsDev P,
+                   const guac_range* __restrict__ force, int n_force, uint8_t* __restrict__ visited /* nullptr: already written */,
+                   SJSiteDev* __restrict__ sites, int* __restrict__ n_sites, int max_sites, DeviceError* err) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tsel = tile_per_warp ? (int)blockIdx.x * WARPS_PER_CTA + warp : (int)blockIdx.x;
+  if (tsel >= n_tiles) return;  // no block-wide barrier below
+  const Tile tile = tiles[tile_list ? tile_list[tsel] : tsel];
+  const RefView ref = refs[tile.ref_index];
   const unsigned FULL = 0xffffffffu;
-  for (int li = warp; li < tile.n_loci; li += WARPS_PER_CTA) {
+  for (int li = tile_per_warp ? 0 : warp; li < tile.n_loci; li += tile_per_warp ? 1 : WARPS_PER_CTA) {
     const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
     // visited: any sample's window is non-empty (skipEmpty = true)
     bool any = false;
@@ -151,7 +155,7 @@ sj_discover_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __
       const bool ov = r < tile.read_hi && __ldg(R.start + r) <= x && x < __ldg(R.end + r) && __ldg(R.sample_id + r) < P.n_samples;
       any = __any_sync(FULL, ov);
     }
-    if (lane == 0) visited[slot] = any ? 1 : 0;
+    if (lane == 0 && visited) visited[slot] = any ? 1 : 0;
     if (!any) continue;
     const uint8_t rb1 = ref.at(x + 1);
     if (rb1 == 0) {  // reference.getReferenceBase(contig, locus + 1) (MultiSampleMultiAlleleEvidence.scala:93)
@@ -393,7 +397,7 @@ __device__ inline int sj_table_find(SJTableEntry* tab, uint64_t key, int sample,
 
 __global__ void __launch_bounds__(128)
 sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P, const SJSiteDev* __restrict__ sites,
-                   const int2* __restrict__ jobs /* (site, allele) */, SJEvidenceDev* __restrict__ out, DeviceError* err) {
+                   const int2* __restrict__ jobs /* (site, allele) */, unsigned char* __restrict__ out, size_t out_stride, DeviceError* err) {
   __shared__ SJTableEntry tab[SJ_TABLE];
   __shared__ int total_depth[SJ_MAX_SLOTS];
   __shared__ double vaf[SJ_MAX_SLOTS];
@@ -524,7 +528,8 @@ sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P,
   __syncthreads();
   if (threadIdx.x != 0) return;
   // assemble: per-sample slots, then the pools (MultiplePileupStats.scala:12-18)
-  SJEvidenceDev& E = out[blockIdx.x];
+  // records are packed with only the S + 2 slots in use (out_stride bytes each)
+  SJEvidenceDev& E = *reinterpret_cast<SJEvidenceDev*>(out + (size_t)blockIdx.x * out_stride);
   E.site = job.x;
   E.allele = job.y;
   for (int slot_i = 0; slot_i < S + 2; ++slot_i) {

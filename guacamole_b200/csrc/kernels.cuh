@@ -215,7 +215,8 @@ struct SSParamsDev {
   int normal_sample, tumor_sample, n_samples;
   int normal_odds, tumor_odds;
   int max_read_depth, max_normal_alt;
-  int min_alt_reads, _pad;  // germline mode of the tile kernel
+  int min_alt_reads;          // germline / joint-prefilter modes of the tile kernel
+  unsigned int sample_mask;   // joint-prefilter mode: samples whose reads can start an allele (the discovery samples)
   double min_vaf;  // float widened to double (SomaticStandardCaller.scala:97,189)
 };
 

@@ -30,9 +30,6 @@
 #ifndef GUAC_TK_EMUL
 #define GUAC_TK_EMUL 3
 #endif
-#ifndef GUAC_TK_UNROLL
-#define GUAC_TK_UNROLL 1
-#endif
 
 namespace guac {
 
@@ -85,14 +82,6 @@ __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags
   rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0) | (medium ? RF_MEDIUM : 0);
 }
 
-__device__ __forceinline__ uint32_t spread16(uint32_t x) {  // bit i -> bit 2i
-  x &= 0xFFFF;
-  x = (x | (x << 8)) & 0x00FF00FF;
-  x = (x | (x << 4)) & 0x0F0F0F0F;
-  x = (x | (x << 2)) & 0x33333333;
-  x = (x | (x << 1)) & 0x55555555;
-  return x;
-}
 
 // 32 bits starting at bit `bit` of a little-endian word stream
 __device__ __forceinline__ uint32_t load_bits32_g(const uint8_t* __restrict__ bytes, uint64_t bit) {
@@ -103,8 +92,6 @@ __device__ __forceinline__ uint32_t load_bits32_s(const uint32_t* words, int bit
   return __funnelshift_r(words[bit >> 5], words[(bit >> 5) + 1], bit & 31);
 }
 
-// kept out of line so that the (rare) masked-reference case is a real branch, not predicated code in the hot loop
-__device__ __noinline__ uint32_t ref_mask_bits(const uint32_t* refmask, int l) { return spread16(load_bits32_s(refmask, l)); }
 
 // event word: [0,11) locus in tile | [11,23) read in tile | 23 sample slot | [24,27) kind | [27,30) code
 //   code: Mismatch -> base code (4 = not ACGT); other kinds -> 4 = allele identified by the detail byte,
@@ -120,7 +107,6 @@ __device__ __forceinline__ int base_code(uint8_t b) { return b == 'A' ? 0 : b ==
 template <class CFG>
 struct TileSmem {
   uint32_t ref2[CFG::TL / 16 + 2];
-  uint32_t refmask[CFG::TL / 32 + 2];
   int cov[CFG::TL + 1];     // packed differences: normal | tumor << 16  -> depths after the scan
   int aux[CFG::TL + 1];     // low-quality tumor read differences | event count << 16 -> lowq | event end offset
   int nonref[CFG::TL];      // non-Match elements: normal | tumor << 16
@@ -147,11 +133,17 @@ struct TileArgs {
   int force_fallback_mod;
   unsigned long long* n_visited;  // loci with at least one read in either sample
   DeviceError* err;
+  const guac_range* force;        // MODE 2: force-call ranges (allele loci); a site one locus before is always a candidate
+  int n_force;
 };
 
 // MODE 0: somatic-standard (two samples).  MODE 1: germline toy caller's dense half — one sample (the "tumor"
 // slot; normal_sample = -1), a locus is heavy when depth - referenceDepth >= P.min_alt_reads
-// (commands/GermlineAssemblyCaller.scala:135-138).
+// (commands/GermlineAssemblyCaller.scala:135-138).  MODE 2: somatic-joint prefilter — every sample below P.n_samples
+// counts for the visit, the samples of P.sample_mask (slot 1) for the events; pileup locus x is heavy when at least
+// P.min_alt_reads of their reads have a non-Match element at x + 1 (an alternate allele can only start there,
+// jointcaller/pileup_summarization/ReadSubsequence.scala:106-135), when x + 1 is force-called, or when x + 1 lies
+// in the next tile.
 template <class CFG, int MODE>
 __global__ void __launch_bounds__(CFG::THREADS, GUAC_TK_MINB)
 ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
@@ -181,7 +173,6 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = 0;
   if (tid < 4) {  // padding words behind the tile
     S.ref2[TL / 16 + (tid & 1)] = 0;
-    S.refmask[TL / 32 + (tid & 1)] = 0;
   }
   __syncthreads();
   // reference tile -> 2-bit words (16 loci per word) and a not-ACGT mask (32 loci per word): one
@@ -197,12 +188,14 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     if (lane == 0) {
       S.ref2[(base >> 4) + 2 * warp] = lo;
       S.ref2[(base >> 4) + 2 * warp + 1] = hi;
-      S.refmask[(base >> 5) + warp] = mask;
       if (mask) S.ref_has_mask = 1;
     }
   }
   __syncthreads();
-  const bool ref_has_mask = S.ref_has_mask != 0;
+  if (S.ref_has_mask) {  // a reference base that is not A C G T (or is missing) in the tile: rare, generic kernel
+    if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
+    return;
+  }
 
   auto push_event = [&](int l, int rl, int slot, int kind, int code, uint32_t second) {
     atomicAdd(&S.nonref[l], slot ? 65536 : 1);
@@ -238,8 +231,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const int smp = hdr.smp;
     const int64_t st64 = hdr.st64, en64 = hdr.en64;
     const uint8_t rf = (uint8_t)hdr.rf;
-    if (smp != P.normal_sample && smp != P.tumor_sample) continue;
-    const int slot = smp == P.tumor_sample ? 1 : 0;
+    if (MODE == 2 ? smp >= P.n_samples : (smp != P.normal_sample && smp != P.tumor_sample)) continue;
+    const int slot = MODE == 2 ? (int)((P.sample_mask >> smp) & 1u) : (smp == P.tumor_sample ? 1 : 0);
     const int st = (int)max((long long)(st64 - t0), -(1ll << 30)), en = (int)min((long long)(en64 - t0), (1ll << 30));
     const int a = max(st, 0), b = min(en, n_loci);  // overlap [a, b) in tile coordinates
     if (a >= b) continue;
@@ -276,7 +269,6 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         rlo = rhi;
         flo = fhi;
         uint32_t m = (x | (x >> 1)) & keep;
-        if (ref_has_mask) m |= ref_mask_bits(S.refmask, l) & keep;  // a not-ACGT reference base never equals an ACGT read base
         while (m) {
           const int bit = __ffs(m) - 1;
           m &= m - 1;
@@ -284,8 +276,6 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         }
       };
       int l = ca;
-      constexpr int kUnroll = GUAC_TK_UNROLL;
-#pragma unroll kUnroll
       for (; l + 16 <= cb; l += 16) step(l, 0x55555555u);
       if (l < cb) step(l, ((1u << (2 * (cb - l))) - 1) & 0x55555555u);  // the tail word, masked once
     };
@@ -348,7 +338,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     for (int si = warp; si < n_slow; si += CFG::WARPS) {
       const int rl = S.slow[si];
       const int64_t r = tile.read_lo + rl;
-      const int slot = (int)__ldg(R.sample_id + r) == P.tumor_sample ? 1 : 0;
+      const int smp = (int)__ldg(R.sample_id + r);
+      const int slot = MODE == 2 ? (int)((P.sample_mask >> smp) & 1u) : (smp == P.tumor_sample ? 1 : 0);
       const int a = (int)max((long long)(__ldg(R.start + r) - t0), 0ll);
       const int b = (int)min((long long)(__ldg(R.end + r) - t0), (long long)n_loci);
       for (int l = a + lane; l < b; l += 32) {
@@ -432,12 +423,24 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const int64_t slot = tile.slot0 + l, x = t0 + l;
     A.visited[slot] = dN + dT > 0 ? 1 : 0;
     my_visited += dN + dT > 0;
-    if (dN + dT > 0 && ref.at(x) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x, -1);
-    // early-outs (SomaticStandardCaller.scala:164-172)
-    const bool candidate = MODE == 0 ? (dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt)
-                                     : (dT > 0 && nrT >= P.min_alt_reads);
+    if (MODE != 2 && dN + dT > 0 && ref.at(x) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x, -1);
+    bool candidate;
+    if (MODE == 0) {  // early-outs (SomaticStandardCaller.scala:164-172)
+      candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
+    } else if (MODE == 1) {
+      candidate = dT > 0 && nrT >= P.min_alt_reads;
+    } else {
+      candidate = false;
+      if (dN + dT > 0) {
+        // reference.getReferenceBase(contig, locus + 1) (jointcaller/evidence/MultiSampleMultiAlleleEvidence.scala:93)
+        if (ref.at(x + 1) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x + 1, -1);
+        candidate = l + 1 >= n_loci || (S.nonref[l + 1] >> 16) >= P.min_alt_reads;
+        for (int i = 0; i < A.n_force && !candidate; ++i)
+          candidate = A.force[i].contig_id == tile.contig_id && A.force[i].start <= x + 1 && x + 1 < A.force[i].end;
+      }
+    }
     int flags = 0;
-    if (MODE == 1 && candidate) {  // every candidate locus gets the full genotype likelihoods
+    if (MODE != 0 && candidate) {  // every candidate locus goes to the per-locus kernel
       const int h = atomicAdd(A.n_heavy, 1);
       if (h < A.max_heavy) {
         Tile t;
@@ -457,6 +460,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       S.cursor[atomicAdd(&S.n_cand, 1)] = l;
       continue;
     }
+    if (MODE == 2) continue;  // no per-locus summary in the joint caller
     // dense summary (normal, tumor): one 16-byte store per locus
     uint4 v;
     v.x = (uint32_t)min(dN, 65535) | ((uint32_t)min(dN - nrN, 65535) << 16);

@@ -226,7 +226,8 @@ def _take(lib, ctx, p, dtype, n) -> np.ndarray:
         out = np.zeros(0, dtype)
     else:
         nbytes = int(n) * np.dtype(dtype).itemsize
-        out = np.frombuffer(C.string_at(C.cast(p, C.c_void_p), nbytes), dtype=dtype).copy()
+        addr = C.cast(p, C.c_void_p).value
+        out = np.frombuffer((C.c_char * nbytes).from_address(addr), dtype=dtype).copy()  # one copy out of the pinned buffer
     if p:
         lib.guac_free(ctx, C.cast(p, C.c_void_p))
     return out
@@ -444,8 +445,8 @@ class Context:
                                                  C.byref(rs), C.byref(re_), C.byref(sc), C.byref(raw)))
         return buf.value.decode(), rs.value, re_.value, sc.value, raw.value
 
-    def somatic_joint(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
-        """guac_somatic_joint -> (list of per-allele evidence dicts, loci visited); see commands/somatic_joint.py."""
+    def somatic_joint_records(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
+        """guac_somatic_joint -> (allele records, sample-evidence records, arena bytes, loci visited) as numpy arrays."""
         from .commands import somatic_joint as sj
         r, f = make_ranges(loci), make_ranges(force_loci)
         al, na, sm, ns, arena, alen, nv = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_int64()
@@ -457,7 +458,13 @@ class Context:
             self.lib.guac_free(self.ctx, arena)
         alleles = _take(self.lib, self.ctx, al, sj.ALLELE_EVIDENCE_DTYPE, na.value)
         samples = _take(self.lib, self.ctx, sm, sj.SAMPLE_EVIDENCE_DTYPE, ns.value)
-        return sj.decode(alleles, samples, arena_b, params.n_samples), nv.value
+        return alleles, samples, arena_b, nv.value
+
+    def somatic_joint(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
+        """guac_somatic_joint -> (list of per-allele evidence dicts, loci visited); see commands/somatic_joint.py."""
+        from .commands import somatic_joint as sj
+        alleles, samples, arena_b, nv = self.somatic_joint_records(loci, params, force_loci)
+        return sj.decode(alleles, samples, arena_b, params.n_samples), nv
 
     # -- callers -----------------------------------------------------------------
     def somatic_standard(self, ranges: Sequence[Tuple[int, int, int]], params: Optional[SSParamsC] = None,
