@@ -686,7 +686,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   if (!ctx || !params || !out_calls || !n_calls || !out_arena || !arena_len) return GUAC_E_INVALID_INPUT;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   Trace trace;
-  using TCfg = TileCfg<512>;
+  using TCfg = TileCfg<GUAC_TK_TL>;
   // The streaming tile kernel serves the pileupFlatMapTwoSamples shape (sample ids {0, 1});
   // anything else, or opt_ss_impl = 1, takes the generic gather kernel.
   const bool two_samples = (params->normal_sample_id == 0 && params->tumor_sample_id == 1) ||
@@ -959,7 +959,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     if (r.end > r.start) shifted.push_back(r);
   }
   Trace trace;
-  using TCfg = TileCfg<512>;
+  using TCfg = TileCfg<GUAC_TK_TL>;
   Plan plan;
   GUAC_TRY(make_plan(ctx, shifted.data(), (int32_t)shifted.size(), plan, TCfg::TL));
   *n_alleles = 0;
@@ -1183,7 +1183,7 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
                            int64_t** out_active_loci, int64_t* n_active, int64_t* out_n_visited) {
   if (!ctx || !params || !out_calls || !n_calls || !out_arena || !arena_len || !out_active_loci || !n_active) return GUAC_E_INVALID_INPUT;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  using TCfg = TileCfg<512>;
+  using TCfg = TileCfg<GUAC_TK_TL>;
   if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
   if (params->sample_id < 0 || params->sample_id >= ctx->n_samples) return fail(ctx, GUAC_E_INVALID_INPUT, "bad sample id");
   Plan plan;

@@ -27,6 +27,9 @@
 #ifndef GUAC_TK_MINB
 #define GUAC_TK_MINB 7
 #endif
+#ifndef GUAC_TK_TL
+#define GUAC_TK_TL 512  // loci per tile
+#endif
 #ifndef GUAC_TK_EMUL
 #define GUAC_TK_EMUL 3
 #endif
