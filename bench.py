@@ -253,19 +253,22 @@ def main():
                 "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes * loci_step, "algorithmic_bytes_per_locus": abytes,
                 "peak_source": peak_src}
 
-    # end to end: pinned host buffers -> guac_reads_upload -> guac_somatic_standard -> call records on host
+    # end to end: pinned host buffers in the compact wire form -> guac_reads_upload_compact (PCIe copy + on-device
+    # expansion) -> guac_somatic_standard -> call records on host
     e2e = None
     if not args.no_e2e:
-        hb = ctx.export_reads_struct()
-        n = hb.n_reads
+        hb = ctx.export_reads_compact_struct()
+        n = int(hb.n_reads)
         n_bases = n * 100
-        n_cigar = int(C.cast(hb.cigar_off, C.POINTER(C.c_uint32))[n])
-        # start, contig_id, mapq, flags, sample_id; cigar_off, seq_off; cigar words; bases2, nmask, qual
-        h2d = n * (8 + 4 + 1 + 1 + 1) + (n + 1) * (4 + 8) + n_cigar * 4 + n_bases // 4 + n_bases // 8 + n_bases
+        n_cigar = n  # the generator's reads: one operator each unless they carry an indel; counted exactly below
+        n_cigar = int(np.frombuffer((C.c_uint16 * n).from_address(C.cast(hb.n_cigar_ops, C.c_void_p).value), dtype=np.uint16).sum())
+        # start, read_len, n_cigar_ops, mapq, flags, sample_id; cigar words; bases2; qualities (4-bit codes or bytes); exceptions
+        qual_bytes = (n_bases + 1) // 2 if hb.qual_bits == 4 else n_bases
+        h2d = n * (8 + 2 + 2 + 1 + 1 + 1) + n_cigar * 4 + (n_bases + 3) // 4 + qual_bytes + int(hb.n_exc) * 9 + int(hb.n_contig_runs) * 12 + 8
         d2h_box = [0]
 
         def step_e2e():
-            ctx.upload_reads_struct(hb, len(DEPTHS))
+            ctx.upload_reads_compact(hb)
             out = ctx.somatic_standard(ranges)
             d2h_box[0] = out["calls"].nbytes + len(out["arena"]) + 8
             return out["n_visited"], len(out["calls"])
@@ -275,8 +278,10 @@ def main():
         if world > 1:
             dist.all_reduce(e_loci, op=dist.ReduceOp.SUM)
         e2e = {"value": float(e_loci.item()) / (e_ms / 1000.0), "unit": "loci/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h_box[0]), "note": "reads from pinned host memory each step; reference genome resident"}
-        ctx.free_reads_struct(hb)
+               "d2h_bytes_per_step": int(d2h_box[0]),
+               "note": f"reads in the compact wire form (guac_read_batch_compact, {hb.qual_bits}-bit qualities) from pinned host "
+                       "memory each step; reference genome resident"}
+        ctx.free_reads_compact_struct(hb)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

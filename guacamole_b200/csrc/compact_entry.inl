@@ -1,0 +1,194 @@
+// compact_entry.inl — guac_reads_upload_compact / guac_reads_export_compact (included at the end of guac_b200.cu).
+
+int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
+  if (!ctx || !b) return GUAC_E_INVALID_INPUT;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  ctx->have_reads = false;
+  const int64_t n = b->n_reads;
+  if (n < 0 || b->n_samples <= 0 || b->n_samples > 255 || b->n_contig_runs < 0 || (b->qual_bits != 4 && b->qual_bits != 8))
+    return fail(ctx, GUAC_E_INVALID_INPUT, "bad compact read batch header");
+  // contig runs: distinct contigs, increasing read indices (RegionsByContig.scala:22 "Regions are not sorted by contig")
+  ctx->contig_spans.clear();
+  for (int i = 0; i < b->n_contig_runs; ++i) {
+    const int32_t c = b->run_contig_id[i];
+    const int64_t lo = b->run_first_read[i], hi = b->run_first_read[i + 1];
+    if (c < 0 || c >= (1 << 22)) return fail(ctx, GUAC_E_INVALID_INPUT, "contig_id out of range");
+    if (lo > hi || (i == 0 && lo != 0) || hi > n) return fail(ctx, GUAC_E_INVALID_INPUT, "bad contig runs");
+    for (auto& sp : ctx->contig_spans)
+      if (sp.first == c) return fail(ctx, GUAC_E_INVALID_INPUT, "Regions are not sorted by contig");
+    if (hi > lo) ctx->contig_spans.push_back({c, {lo, hi}});
+  }
+  if (n > 0 && (b->n_contig_runs == 0 || b->run_first_read[b->n_contig_runs] != n))
+    return fail(ctx, GUAC_E_INVALID_INPUT, "contig runs do not cover the batch");
+  DevBuf d_len, d_ops, d_runs_c, d_runs_f, d_tmp, d_qpacked, d_bad;
+  struct Free {
+    std::vector<DevBuf*> v;
+    ~Free() {
+      for (DevBuf* d : v)
+        if (d->p) cudaFree(d->p);
+    }
+  } fr{{&d_len, &d_ops, &d_runs_c, &d_runs_f, &d_tmp, &d_qpacked, &d_bad}};
+  GUAC_TRY(upload(ctx, ctx->b_start, b->start, (size_t)n));
+  GUAC_TRY(upload(ctx, d_len, b->read_len, (size_t)n));
+  GUAC_TRY(upload(ctx, d_ops, b->n_cigar_ops, (size_t)n));
+  GUAC_TRY(upload(ctx, d_runs_c, b->run_contig_id, (size_t)b->n_contig_runs));
+  GUAC_TRY(upload(ctx, d_runs_f, b->run_first_read, (size_t)b->n_contig_runs + 1));
+  GUAC_TRY(upload(ctx, ctx->b_mapq, b->mapq, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->b_flags, b->flags, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->b_sample, b->sample_id, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->b_exc_pos, b->exc_pos, (size_t)b->n_exc));
+  GUAC_TRY(upload(ctx, ctx->b_exc_base, b->exc_base, (size_t)b->n_exc));
+  // offsets = prefix sums of the lengths (the last entry is the total)
+  GUAC_TRY(ensure(ctx, ctx->b_seq_off, (size_t)(n + 1) * sizeof(uint64_t)));
+  GUAC_TRY(ensure(ctx, ctx->b_cigar_off, (size_t)(n + 1) * sizeof(uint32_t)));
+  GUAC_TRY(ensure(ctx, ctx->b_contig, (size_t)std::max<int64_t>(n, 1) * sizeof(int32_t)));
+  GUAC_TRY(ensure(ctx, d_tmp, (size_t)(n + 1) * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, d_bad, sizeof(int)));
+  CUDA_TRY(ctx, cudaMemsetAsync(d_bad.p, 0, sizeof(int), ctx->stream));
+  uint64_t n_bases = 0;
+  int64_t n_cigar = 0;
+  if (n > 0) {
+    int64_t* seq_off = ctx->b_seq_off.as<int64_t>();
+    GUAC_TRY((device_scan<true, uint16_t>(ctx, d_len.as<uint16_t>(), seq_off, n, OpSum(), seq_off + n)));
+    GUAC_TRY((device_scan<true, uint16_t>(ctx, d_ops.as<uint16_t>(), d_tmp.as<int64_t>(), n, OpSum(), d_tmp.as<int64_t>() + n)));
+    compact::narrow_offsets_kernel<<<blocks_for(n + 1, 256), 256, 0, ctx->stream>>>(n + 1, d_tmp.as<int64_t>(), ctx->b_cigar_off.as<uint32_t>());
+    compact::contig_from_runs_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, d_runs_c.as<int32_t>(), d_runs_f.as<int64_t>(),
+                                                                                 b->n_contig_runs, ctx->b_contig.as<int32_t>());
+    compact::validate_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->b_start.as<int64_t>(), ctx->b_contig.as<int32_t>(),
+                                                                         ctx->b_sample.as<uint8_t>(), b->n_samples, d_bad.as<int>());
+    ctx->launches += 3;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_bases, seq_off + n, sizeof n_bases, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_cigar, d_tmp.as<int64_t>() + n, sizeof n_cigar, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (n_cigar >= ((int64_t)1 << 32)) return fail(ctx, GUAC_E_UNSUPPORTED, "more than 2^32-1 CIGAR operators in one batch");
+  } else {
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_seq_off.p, 0, sizeof(uint64_t), ctx->stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_cigar_off.p, 0, sizeof(uint32_t), ctx->stream));
+  }
+  GUAC_TRY(upload(ctx, ctx->b_cigar, b->cigar, (size_t)n_cigar));
+  GUAC_TRY(upload(ctx, ctx->b_bases2, b->bases2, (size_t)((n_bases + 3) / 4), 64));
+  GUAC_TRY(ensure(ctx, ctx->b_nmask, (size_t)((n_bases + 7) / 8) + 16));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_nmask.p, 0, (size_t)((n_bases + 7) / 8) + 16, ctx->stream));
+  if (b->n_exc > 0) {
+    compact::nmask_from_exceptions_kernel<<<blocks_for(b->n_exc, 256), 256, 0, ctx->stream>>>(b->n_exc, ctx->b_exc_pos.as<uint64_t>(),
+                                                                                             ctx->b_nmask.as<uint8_t>());
+    ctx->launches += 1;
+  }
+  if (b->qual_bits == 8) {
+    GUAC_TRY(upload(ctx, ctx->b_qual, b->qual, (size_t)n_bases));
+  } else {
+    GUAC_TRY(upload(ctx, d_qpacked, b->qual, (size_t)((n_bases + 1) / 2), 32));
+    GUAC_TRY(ensure(ctx, ctx->b_qual, (size_t)n_bases + 32));
+    if (n_bases > 0) {
+      compact::QualTable T;
+      std::memcpy(T.q, b->qual_table, 16);
+      compact::expand_qual4_kernel<<<blocks_for((int64_t)((n_bases + 15) / 16), 256), 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T,
+                                                                                                           ctx->b_qual.as<uint8_t>());
+      ctx->launches += 1;
+    }
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  int bad = 0;
+  CUDA_TRY(ctx, cudaMemcpyAsync(&bad, d_bad.p, sizeof bad, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (bad & 1) return fail(ctx, GUAC_E_INVALID_INPUT, "Regions must be sorted by start locus");
+  if (bad & 2) return fail(ctx, GUAC_E_INVALID_INPUT, "sample_id >= n_samples");
+  if (bad & 4) return fail(ctx, GUAC_E_INVALID_INPUT, "read start out of range");
+  return finish_reads(ctx, n, b->n_samples, b->n_exc);
+}
+
+int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out) {
+  if (!ctx || !out) return GUAC_E_INVALID_INPUT;
+  if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int64_t n = ctx->n_reads;
+  std::memset(out, 0, sizeof *out);
+  out->n_reads = n;
+  out->n_samples = ctx->n_samples;
+  uint64_t n_bases = 0;
+  uint32_t n_cigar = 0;
+  if (n) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_bases, ctx->R.seq_off + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&n_cigar, ctx->R.cigar_off + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  // contig runs from the spans recorded at upload
+  auto spans = ctx->contig_spans;
+  std::sort(spans.begin(), spans.end(), [](const auto& a, const auto& b) { return a.second.first < b.second.first; });
+  out->n_contig_runs = (int32_t)spans.size();
+  void* hc = nullptr;
+  void* hf = nullptr;
+  GUAC_TRY(pinned_alloc(ctx, &hc, std::max<size_t>(spans.size() * sizeof(int32_t), 16)));
+  GUAC_TRY(pinned_alloc(ctx, &hf, (spans.size() + 1) * sizeof(int64_t)));
+  for (size_t i = 0; i < spans.size(); ++i) {
+    static_cast<int32_t*>(hc)[i] = spans[i].first;
+    static_cast<int64_t*>(hf)[i] = spans[i].second.first;
+  }
+  static_cast<int64_t*>(hf)[spans.size()] = n;
+  out->run_contig_id = static_cast<int32_t*>(hc);
+  out->run_first_read = static_cast<int64_t*>(hf);
+  DevBuf d_len, d_ops, d_flag, d_present, d_qpacked;
+  struct Free {
+    std::vector<DevBuf*> v;
+    ~Free() {
+      for (DevBuf* d : v)
+        if (d->p) cudaFree(d->p);
+    }
+  } fr{{&d_len, &d_ops, &d_flag, &d_present, &d_qpacked}};
+  GUAC_TRY(ensure(ctx, d_len, (size_t)std::max<int64_t>(n, 1) * sizeof(uint16_t)));
+  GUAC_TRY(ensure(ctx, d_ops, (size_t)std::max<int64_t>(n, 1) * sizeof(uint16_t)));
+  GUAC_TRY(ensure(ctx, d_flag, sizeof(int)));
+  GUAC_TRY(ensure(ctx, d_present, 256 * sizeof(unsigned int)));
+  CUDA_TRY(ctx, cudaMemsetAsync(d_flag.p, 0, sizeof(int), ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(d_present.p, 0, 256 * sizeof(unsigned int), ctx->stream));
+  unsigned int present[256] = {0};
+  int too_long = 0;
+  if (n) {
+    compact::lengths_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->R.seq_off, ctx->R.cigar_off, d_len.as<uint16_t>(),
+                                                                        d_ops.as<uint16_t>(), d_flag.as<int>());
+    compact::qual_histogram_kernel<<<148 * 8, 256, 0, ctx->stream>>>(n_bases, ctx->R.qual, d_present.as<unsigned int>());
+    ctx->launches += 2;
+    CUDA_TRY(ctx, cudaGetLastError());
+    CUDA_TRY(ctx, cudaMemcpyAsync(present, d_present.p, sizeof present, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&too_long, d_flag.p, sizeof too_long, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (too_long) return fail(ctx, GUAC_E_UNSUPPORTED, "a read has more than 65535 bases or CIGAR operators: use guac_reads_export");
+  }
+  GUAC_TRY(host_out(ctx, const_cast<int64_t**>(&out->start), ctx->b_start.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->read_len), d_len.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->n_cigar_ops), d_ops.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->cigar), ctx->b_cigar.p, (size_t)n_cigar));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->bases2), ctx->b_bases2.p, (size_t)((n_bases + 3) / 4)));
+  out->n_exc = ctx->R.n_exc;
+  GUAC_TRY(host_out(ctx, const_cast<uint64_t**>(&out->exc_pos), ctx->b_exc_pos.p, (size_t)ctx->R.n_exc));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->exc_base), ctx->b_exc_base.p, (size_t)ctx->R.n_exc));
+  int distinct = 0;
+  compact::QualCodes codes;
+  std::memset(&codes, 0, sizeof codes);
+  for (int q = 0; q < 256; ++q)
+    if (present[q]) {
+      if (distinct < 16) {
+        out->qual_table[distinct] = (uint8_t)q;
+        codes.code[q] = (uint8_t)distinct;
+      }
+      ++distinct;
+    }
+  if (distinct <= 16 && n_bases > 0) {
+    out->qual_bits = 4;
+    const size_t packed = (size_t)((n_bases + 1) / 2);
+    GUAC_TRY(ensure(ctx, d_qpacked, packed + 16));
+    compact::pack_qual4_kernel<<<blocks_for((int64_t)packed, 256), 256, 0, ctx->stream>>>(n_bases, ctx->R.qual, codes, d_qpacked.as<uint8_t>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->qual), d_qpacked.p, packed));
+  } else {
+    out->qual_bits = 8;
+    GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->qual), ctx->b_qual.p, (size_t)n_bases));
+  }
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->mapq), ctx->b_mapq.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->flags), ctx->b_flags.p, (size_t)n));
+  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->sample_id), ctx->b_sample.p, (size_t)n));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return GUAC_OK;
+}

@@ -1,0 +1,112 @@
+// compact_kernels.cuh — expansion / compaction between guac_read_batch_compact (the PCIe wire form) and the
+// columnar batch the kernels read.  All of it is streaming byte work: one pass per column.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace guac {
+namespace compact {
+
+// per-read contig id from the runs (binary search over a handful of runs)
+__global__ void contig_from_runs_kernel(int64_t n, const int32_t* __restrict__ run_contig, const int64_t* __restrict__ run_first,
+                                        int n_runs, int32_t* __restrict__ contig_id) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  int lo = 0, hi = n_runs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (run_first[mid] <= r) lo = mid; else hi = mid - 1;
+  }
+  contig_id[r] = run_contig[lo];
+}
+
+__global__ void narrow_offsets_kernel(int64_t n, const int64_t* __restrict__ in, uint32_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (uint32_t)in[i];
+}
+
+// not-ACGT mask from the exception list (the mask buffer is zeroed first)
+__global__ void nmask_from_exceptions_kernel(int64_t n_exc, const uint64_t* __restrict__ exc_pos, uint8_t* __restrict__ nmask) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_exc) return;
+  const uint64_t p = exc_pos[i];
+  unsigned int* w = reinterpret_cast<unsigned int*>(nmask) + (p >> 5);
+  atomicOr(w, 1u << (p & 31));
+}
+
+struct QualTable {
+  uint8_t q[16];
+};
+
+// 4-bit codes -> one byte per base; each thread expands 8 packed bytes (16 bases)
+__global__ void expand_qual4_kernel(uint64_t n_bases, const uint8_t* __restrict__ packed, QualTable T, uint8_t* __restrict__ qual) {
+  __shared__ uint8_t s_q[16];
+  if (threadIdx.x < 16) s_q[threadIdx.x] = T.q[threadIdx.x];
+  __syncthreads();
+  const uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (i >= n_bases) return;
+  const uint2 w = *reinterpret_cast<const uint2*>(packed + (i >> 1));  // buffers are padded to 16 bytes
+  uint32_t o[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t src = (k < 2 ? w.x : w.y) >> ((k & 1) * 16);
+    o[k] = (uint32_t)s_q[src & 15] | ((uint32_t)s_q[(src >> 4) & 15] << 8) | ((uint32_t)s_q[(src >> 8) & 15] << 16) |
+           ((uint32_t)s_q[(src >> 12) & 15] << 24);
+  }
+  if (i + 16 <= n_bases) {
+    *reinterpret_cast<uint4*>(qual + i) = make_uint4(o[0], o[1], o[2], o[3]);
+  } else {
+    for (uint64_t k = i; k < n_bases; ++k) qual[k] = (uint8_t)(o[(k - i) >> 2] >> (8 * ((k - i) & 3)));
+  }
+}
+
+// ---- the other direction (export) ----
+__global__ void lengths_kernel(int64_t n, const uint64_t* __restrict__ seq_off, const uint32_t* __restrict__ cigar_off,
+                               uint16_t* __restrict__ read_len, uint16_t* __restrict__ n_ops, int* __restrict__ too_long) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const uint64_t len = seq_off[r + 1] - seq_off[r];
+  const uint32_t ops = cigar_off[r + 1] - cigar_off[r];
+  if (len > 65535 || ops > 65535) *too_long = 1;
+  read_len[r] = (uint16_t)len;
+  n_ops[r] = (uint16_t)ops;
+}
+
+__global__ void qual_histogram_kernel(uint64_t n_bases, const uint8_t* __restrict__ qual, unsigned int* __restrict__ present) {
+  __shared__ unsigned int s_present[256];
+  s_present[threadIdx.x] = 0;
+  __syncthreads();
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_bases; i += (uint64_t)gridDim.x * blockDim.x)
+    s_present[qual[i]] = 1;  // benign race: every writer stores 1
+  __syncthreads();
+  if (s_present[threadIdx.x]) present[threadIdx.x] = 1;
+}
+
+struct QualCodes {
+  uint8_t code[256];
+};
+
+__global__ void pack_qual4_kernel(uint64_t n_bases, const uint8_t* __restrict__ qual, QualCodes C, uint8_t* __restrict__ packed) {
+  __shared__ uint8_t s_code[256];
+  s_code[threadIdx.x] = C.code[threadIdx.x];  // 256 threads per block
+  __syncthreads();
+  const uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;  // output byte
+  if (2 * b >= n_bases) return;
+  const uint8_t lo = s_code[qual[2 * b]];
+  const uint8_t hi = 2 * b + 1 < n_bases ? s_code[qual[2 * b + 1]] : 0;
+  packed[b] = (uint8_t)(lo | (hi << 4));
+}
+
+// start-sortedness within each contig run, sample ids in range (SlidingWindow.scala:36-37)
+__global__ void validate_kernel(int64_t n, const int64_t* __restrict__ start, const int32_t* __restrict__ contig_id,
+                                const uint8_t* __restrict__ sample_id, int n_samples, int* __restrict__ bad) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const int64_t s = start[r];
+  if (s < 0 || s >= ((int64_t)1 << 39)) atomicOr(bad, 4);
+  if (sample_id[r] >= n_samples) atomicOr(bad, 2);
+  if (r > 0 && contig_id[r] == contig_id[r - 1] && s < start[r - 1]) atomicOr(bad, 1);
+}
+
+}  // namespace compact
+}  // namespace guac

@@ -24,6 +24,7 @@
 #include "joint_host.hpp"
 #include "germline_kernels.cuh"
 #include "assembly_kernels.cuh"
+#include "compact_kernels.cuh"
 
 using namespace guac;
 
@@ -1730,3 +1731,4 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 }  // extern "C"
 
 #include "assembly_entry.inl"
+#include "compact_entry.inl"

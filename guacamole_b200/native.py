@@ -220,6 +220,58 @@ def batch_struct(batch: ReadBatch) -> ReadBatchC:
     return b
 
 
+u16p = C.POINTER(C.c_uint16)
+
+
+class ReadBatchCompactC(C.Structure):
+    """guac_read_batch_compact: the PCIe wire form (lengths instead of offsets, contig runs, 4-bit quality codes)."""
+    _fields_ = [("n_reads", C.c_int64), ("n_samples", C.c_int32), ("n_contig_runs", C.c_int32), ("run_contig_id", i32p),
+                ("run_first_read", i64p), ("start", i64p), ("read_len", u16p), ("n_cigar_ops", u16p), ("cigar", u32p),
+                ("bases2", u8p), ("n_exc", C.c_int64), ("exc_pos", u64p), ("exc_base", u8p), ("qual_bits", C.c_int32),
+                ("_pad", C.c_int32), ("qual_table", C.c_uint8 * 16), ("qual", u8p), ("mapq", u8p), ("flags", u8p),
+                ("sample_id", u8p)]
+
+
+def compact_struct(batch: ReadBatch) -> ReadBatchCompactC:
+    """Host-side packer of the compact wire form (numpy); keeps the arrays alive on the returned struct."""
+    if batch.packed is None:
+        batch.packed = pack_bases(batch.bases_ascii)
+    p = batch.packed
+    n = batch.n_reads
+    keep = {}
+    b = ReadBatchCompactC()
+    b.n_reads, b.n_samples = n, batch.n_samples
+    change = np.flatnonzero(np.diff(batch.contig_id)) + 1 if n else np.zeros(0, np.int64)
+    first = np.concatenate([[0], change, [n]]).astype(np.int64) if n else np.zeros(1, np.int64)
+    keep["run_first"] = first
+    keep["run_contig"] = np.ascontiguousarray(batch.contig_id[first[:-1]], np.int32) if n else np.zeros(0, np.int32)
+    b.n_contig_runs = len(keep["run_contig"])
+    keep["read_len"] = np.diff(batch.seq_off.astype(np.int64)).astype(np.uint16)
+    keep["n_ops"] = np.diff(batch.cigar_off.astype(np.int64)).astype(np.uint16)
+    assert n == 0 or (np.diff(batch.seq_off.astype(np.int64)).max() <= 65535 and np.diff(batch.cigar_off.astype(np.int64)).max() <= 65535)
+    values = np.unique(batch.qual)
+    if 0 < len(values) <= 16:
+        codes = np.zeros(256, np.uint8)
+        codes[values] = np.arange(len(values), dtype=np.uint8)
+        c = codes[batch.qual]
+        if len(c) % 2:
+            c = np.concatenate([c, np.zeros(1, np.uint8)])
+        keep["qual"] = np.ascontiguousarray(c[0::2] | (c[1::2] << 4))
+        b.qual_bits = 4
+        for i, v in enumerate(values):
+            b.qual_table[i] = int(v)
+    else:
+        keep["qual"] = batch.qual
+        b.qual_bits = 8
+    b.run_contig_id, b.run_first_read = ptr(keep["run_contig"], i32p), ptr(keep["run_first"], i64p)
+    b.start, b.read_len, b.n_cigar_ops = ptr(batch.start, i64p), ptr(keep["read_len"], u16p), ptr(keep["n_ops"], u16p)
+    b.cigar, b.bases2 = ptr(batch.cigar, u32p), ptr(p["bases2"], u8p)
+    b.n_exc, b.exc_pos, b.exc_base = p["n_exc"], ptr(p["exc_pos"], u64p), ptr(p["exc_base"], u8p)
+    b.qual, b.mapq, b.flags, b.sample_id = ptr(keep["qual"], u8p), ptr(batch.mapq, u8p), ptr(batch.flags, u8p), ptr(batch.sample_id, u8p)
+    b._keep = keep
+    return b
+
+
 def _take(lib, ctx, p, dtype, n) -> np.ndarray:
     """Copies a library-owned output buffer into numpy and releases it."""
     if n == 0 or not p:
@@ -289,6 +341,25 @@ class Context:
         """Uploads an already packed batch (e.g. pinned buffers from export_reads_struct)."""
         self._check(self.lib.guac_reads_upload(self.ctx, C.byref(b)))
         self._batch = type("B", (), {"n_samples": n_samples})()
+
+    def upload_reads_compact(self, batch):
+        """guac_reads_upload_compact: a ReadBatch (packed here) or an already packed ReadBatchCompactC."""
+        b = batch if isinstance(batch, ReadBatchCompactC) else compact_struct(batch)
+        self._check(self.lib.guac_reads_upload_compact(self.ctx, C.byref(b)))
+        self._batch = batch if not isinstance(batch, ReadBatchCompactC) else type("B", (), {"n_samples": b.n_samples})()
+
+    def export_reads_compact_struct(self) -> ReadBatchCompactC:
+        """Device batch -> compact wire form in library-owned pinned host buffers."""
+        b = ReadBatchCompactC()
+        self._check(self.lib.guac_reads_export_compact(self.ctx, C.byref(b)))
+        return b
+
+    def free_reads_compact_struct(self, b: ReadBatchCompactC):
+        for name in ("run_contig_id", "run_first_read", "start", "read_len", "n_cigar_ops", "cigar", "bases2", "exc_pos", "exc_base",
+                     "qual", "mapq", "flags", "sample_id"):
+            v = getattr(b, name)
+            if v:
+                self.lib.guac_free(self.ctx, C.cast(v, C.c_void_p))
 
     # -- measurement support -----------------------------------------------------
     def synth_generate(self, contig_len: int, depths: Sequence[int], tumor: Sequence[bool], seed: int, contig_id: int = 0,

@@ -1,0 +1,89 @@
+"""The compact wire form (guac_read_batch_compact) is lossless: a batch uploaded through it is, on the device, the very
+batch guac_reads_upload would have produced, and the callers return the same records."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from guacamole_b200 import synth
+from guacamole_b200.native import GuacError, compact_struct, ss_params
+from guacamole_b200.reads import ReadBatch, make_read
+from tests.golden import fixtures
+
+pytestmark = pytest.mark.gpu
+
+COLUMNS = ["contig_id", "start", "cigar_off", "cigar", "seq_off", "bases_ascii", "qual", "mapq", "flags", "sample_id"]
+
+
+def assert_same_batch(a: ReadBatch, b: ReadBatch):
+    assert a.n_reads == b.n_reads and a.n_samples == b.n_samples
+    for name in COLUMNS:
+        assert np.array_equal(getattr(a, name), getattr(b, name)), name
+
+
+def device_copy(ctx, names):
+    return ctx.export_reads(names)
+
+
+@pytest.mark.parametrize("name", ["tough", "tiny_sjc", "testrna"])
+def test_real_reads_round_trip(gpu_ctx, name):
+    """Real reads: > 16 distinct qualities (one byte per base on the wire), N bases, soft clips, indels, several contigs."""
+    batch, ref, _ = fixtures.load(name)
+    if ref is not None:  # the RNA fixture has no reference; uploads do not need one
+        gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    plain = device_copy(gpu_ctx, batch.contig_names)
+    gpu_ctx.upload_reads_compact(batch)
+    assert_same_batch(device_copy(gpu_ctx, batch.contig_names), plain)
+    assert_same_batch(plain, batch)
+
+
+def test_binned_qualities_travel_as_nibbles(gpu_ctx):
+    contig_len, seed = 30000, 4005
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, (30, 60), (False, True), seed)
+    c = compact_struct(batch)
+    assert c.qual_bits == 4 and sorted(c.qual_table[:4]) == [10, 20, 30, 40]
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    want = gpu_ctx.somatic_standard([(0, 0, contig_len)], ss_params())
+    gpu_ctx.upload_reads_compact(c)
+    assert_same_batch(device_copy(gpu_ctx, batch.contig_names), batch)
+    got = gpu_ctx.somatic_standard([(0, 0, contig_len)], ss_params())
+    assert len(want["calls"]) > 0 and got["arena"] == want["arena"] and got["n_visited"] == want["n_visited"]
+    assert got["calls"].tobytes() == want["calls"].tobytes()
+    # and the way back: the device batch exported in compact form is the host packer's output
+    e = gpu_ctx.export_reads_compact_struct()
+    try:
+        assert (e.n_reads, e.n_samples, e.n_contig_runs, e.qual_bits, e.n_exc) == (c.n_reads, c.n_samples, c.n_contig_runs, 4, c.n_exc)
+        assert list(e.qual_table[:4]) == list(c.qual_table[:4])
+        n, n_bases = int(c.n_reads), int(batch.seq_off[-1])
+        for field, count, width in (("start", n, 8), ("read_len", n, 2), ("n_cigar_ops", n, 2), ("cigar", len(batch.cigar), 4),
+                                    ("bases2", (n_bases + 3) // 4, 1), ("qual", (n_bases + 1) // 2, 1), ("mapq", n, 1),
+                                    ("flags", n, 1), ("sample_id", n, 1)):
+            a = C.string_at(C.cast(getattr(e, field), C.c_void_p), count * width)
+            b = C.string_at(C.cast(getattr(c, field), C.c_void_p), count * width)
+            assert a == b, field
+        gpu_ctx.upload_reads_compact(e)  # pinned buffers straight back in, as the e2e bench does
+        assert_same_batch(device_copy(gpu_ctx, batch.contig_names), batch)
+    finally:
+        gpu_ctx.free_reads_compact_struct(e)
+
+
+def test_odd_base_count_and_empty_batch(gpu_ctx):
+    reads = [make_read("ACGTA", "5M", start=3, quality_scores=[7, 9, 7, 9, 11]), make_read("TTGCATG", "3M1I3M", start=4, sample_id=1)]
+    batch = ReadBatch.from_reads(reads)
+    gpu_ctx.upload_reads_compact(batch)
+    assert_same_batch(device_copy(gpu_ctx, batch.contig_names), batch)
+    empty = ReadBatch.from_reads([], contig_names=["chr1"], n_samples=1)
+    gpu_ctx.upload_reads_compact(empty)
+    assert device_copy(gpu_ctx, ["chr1"]).n_reads == 0
+
+
+def test_ordering_contract(gpu_ctx):
+    batch = ReadBatch.from_reads([make_read("ACGT", "4M", start=10), make_read("ACGT", "4M", start=20)])
+    c = compact_struct(batch)
+    c._keep["start_swapped"] = np.array([20, 10], np.int64)
+    c.start = c._keep["start_swapped"].ctypes.data_as(C.POINTER(C.c_int64))
+    with pytest.raises(GuacError, match="Regions must be sorted by start locus"):  # windowing/SlidingWindow.scala:36-37
+        gpu_ctx.upload_reads_compact(c)
