@@ -263,7 +263,7 @@ def main():
         n_cigar = n  # the generator's reads: one operator each unless they carry an indel; counted exactly below
         n_cigar = int(np.frombuffer((C.c_uint16 * n).from_address(C.cast(hb.n_cigar_ops, C.c_void_p).value), dtype=np.uint16).sum())
         # start, read_len, n_cigar_ops, mapq, flags, sample_id; cigar words; bases2; qualities (4-bit codes or bytes); exceptions
-        qual_bytes = (n_bases + 1) // 2 if hb.qual_bits == 4 else n_bases
+        qual_bytes = (n_bases * int(hb.qual_bits) + 7) // 8
         h2d = n * (8 + 2 + 2 + 1 + 1 + 1) + n_cigar * 4 + (n_bases + 3) // 4 + qual_bytes + int(hb.n_exc) * 9 + int(hb.n_contig_runs) * 12 + 8
         d2h_box = [0]
 

@@ -5,7 +5,7 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   ctx->have_reads = false;
   const int64_t n = b->n_reads;
-  if (n < 0 || b->n_samples <= 0 || b->n_samples > 255 || b->n_contig_runs < 0 || (b->qual_bits != 4 && b->qual_bits != 8))
+  if (n < 0 || b->n_samples <= 0 || b->n_samples > 255 || b->n_contig_runs < 0 || (b->qual_bits != 2 && b->qual_bits != 4 && b->qual_bits != 8))
     return fail(ctx, GUAC_E_INVALID_INPUT, "bad compact read batch header");
   // contig runs: distinct contigs, increasing read indices (RegionsByContig.scala:22 "Regions are not sorted by contig")
   ctx->contig_spans.clear();
@@ -78,13 +78,17 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   if (b->qual_bits == 8) {
     GUAC_TRY(upload(ctx, ctx->b_qual, b->qual, (size_t)n_bases));
   } else {
-    GUAC_TRY(upload(ctx, d_qpacked, b->qual, (size_t)((n_bases + 1) / 2), 32));
+    const int per_byte = 8 / b->qual_bits;
+    GUAC_TRY(upload(ctx, d_qpacked, b->qual, (size_t)((n_bases + per_byte - 1) / per_byte), 32));
     GUAC_TRY(ensure(ctx, ctx->b_qual, (size_t)n_bases + 32));
     if (n_bases > 0) {
       compact::QualTable T;
       std::memcpy(T.q, b->qual_table, 16);
-      compact::expand_qual4_kernel<<<blocks_for((int64_t)((n_bases + 15) / 16), 256), 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T,
-                                                                                                           ctx->b_qual.as<uint8_t>());
+      const unsigned blocks = blocks_for((int64_t)((n_bases + 15) / 16), 256);
+      if (b->qual_bits == 4)
+        compact::expand_qual_kernel<4><<<blocks, 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
+      else
+        compact::expand_qual_kernel<2><<<blocks, 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
       ctx->launches += 1;
     }
   }
@@ -175,10 +179,14 @@ int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out) {
       ++distinct;
     }
   if (distinct <= 16 && n_bases > 0) {
-    out->qual_bits = 4;
-    const size_t packed = (size_t)((n_bases + 1) / 2);
+    out->qual_bits = distinct <= 4 ? 2 : 4;
+    const int per_byte = 8 / out->qual_bits;
+    const size_t packed = (size_t)((n_bases + per_byte - 1) / per_byte);
     GUAC_TRY(ensure(ctx, d_qpacked, packed + 16));
-    compact::pack_qual4_kernel<<<blocks_for((int64_t)packed, 256), 256, 0, ctx->stream>>>(n_bases, ctx->R.qual, codes, d_qpacked.as<uint8_t>());
+    if (out->qual_bits == 4)
+      compact::pack_qual_kernel<4><<<blocks_for((int64_t)packed, 256), 256, 0, ctx->stream>>>(n_bases, ctx->R.qual, codes, d_qpacked.as<uint8_t>());
+    else
+      compact::pack_qual_kernel<2><<<blocks_for((int64_t)packed, 256), 256, 0, ctx->stream>>>(n_bases, ctx->R.qual, codes, d_qpacked.as<uint8_t>());
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
     GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->qual), d_qpacked.p, packed));

@@ -38,20 +38,25 @@ struct QualTable {
   uint8_t q[16];
 };
 
-// 4-bit codes -> one byte per base; each thread expands 8 packed bytes (16 bases)
-__global__ void expand_qual4_kernel(uint64_t n_bases, const uint8_t* __restrict__ packed, QualTable T, uint8_t* __restrict__ qual) {
+// BITS-bit codes (2 or 4) -> one byte per base; each thread expands 16 bases
+template <int BITS>
+__global__ void expand_qual_kernel(uint64_t n_bases, const uint8_t* __restrict__ packed, QualTable T, uint8_t* __restrict__ qual) {
   __shared__ uint8_t s_q[16];
   if (threadIdx.x < 16) s_q[threadIdx.x] = T.q[threadIdx.x];
   __syncthreads();
   const uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
   if (i >= n_bases) return;
-  const uint2 w = *reinterpret_cast<const uint2*>(packed + (i >> 1));  // buffers are padded to 16 bytes
+  constexpr uint32_t MASK = (1u << BITS) - 1;
+  // 16 bases = 64 bits (4-bit codes) or 32 bits (2-bit codes); buffers are padded to 16 bytes
+  unsigned long long w;
+  if (BITS == 4) w = *reinterpret_cast<const unsigned long long*>(packed + (i >> 1));
+  else w = *reinterpret_cast<const uint32_t*>(packed + (i >> 2));
   uint32_t o[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const uint32_t src = (k < 2 ? w.x : w.y) >> ((k & 1) * 16);
-    o[k] = (uint32_t)s_q[src & 15] | ((uint32_t)s_q[(src >> 4) & 15] << 8) | ((uint32_t)s_q[(src >> 8) & 15] << 16) |
-           ((uint32_t)s_q[(src >> 12) & 15] << 24);
+    const uint32_t src = (uint32_t)(w >> (4 * BITS * k));
+    o[k] = (uint32_t)s_q[src & MASK] | ((uint32_t)s_q[(src >> BITS) & MASK] << 8) | ((uint32_t)s_q[(src >> (2 * BITS)) & MASK] << 16) |
+           ((uint32_t)s_q[(src >> (3 * BITS)) & MASK] << 24);
   }
   if (i + 16 <= n_bases) {
     *reinterpret_cast<uint4*>(qual + i) = make_uint4(o[0], o[1], o[2], o[3]);
@@ -86,15 +91,19 @@ struct QualCodes {
   uint8_t code[256];
 };
 
-__global__ void pack_qual4_kernel(uint64_t n_bases, const uint8_t* __restrict__ qual, QualCodes C, uint8_t* __restrict__ packed) {
+template <int BITS>
+__global__ void pack_qual_kernel(uint64_t n_bases, const uint8_t* __restrict__ qual, QualCodes C, uint8_t* __restrict__ packed) {
   __shared__ uint8_t s_code[256];
   s_code[threadIdx.x] = C.code[threadIdx.x];  // 256 threads per block
   __syncthreads();
+  constexpr int PER = 8 / BITS;  // bases per output byte, lowest bits = lowest base index
   const uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;  // output byte
-  if (2 * b >= n_bases) return;
-  const uint8_t lo = s_code[qual[2 * b]];
-  const uint8_t hi = 2 * b + 1 < n_bases ? s_code[qual[2 * b + 1]] : 0;
-  packed[b] = (uint8_t)(lo | (hi << 4));
+  if (PER * b >= n_bases) return;
+  uint32_t v = 0;
+#pragma unroll
+  for (int k = 0; k < PER; ++k)
+    if (PER * b + k < n_bases) v |= (uint32_t)s_code[qual[PER * b + k]] << (BITS * k);
+  packed[b] = (uint8_t)v;
 }
 
 // start-sortedness within each contig run, sample ids in range (SlidingWindow.scala:36-37)

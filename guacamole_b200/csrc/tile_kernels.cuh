@@ -80,8 +80,19 @@ __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags
   }
   const bool medium = acgt && ops_ok && !leading_ins_at_zero && read_len == s1 - s0 && seen_ref_op;
   const bool fast = medium && (c1 - c0 == 1);
+  // every quality >= 4  <=>  no byte with (q & 0xFC) == 0; four qualities per aligned word, the bytes outside
+  // [s0, s1) forced high
   bool hiq = true;
-  for (uint64_t i = s0; i < s1; ++i) hiq = hiq && R.qual[i] >= 4;
+  if (s1 > s0) {
+    const uint32_t* qw = reinterpret_cast<const uint32_t*>(R.qual);
+    for (uint64_t w = s0 >> 2; w <= ((s1 - 1) >> 2); ++w) {
+      uint32_t v = __ldg(qw + w);
+      if (w == (s0 >> 2)) v |= (1u << (8 * (s0 & 3))) - 1;
+      if (w == ((s1 - 1) >> 2) && ((s1 & 3) != 0)) v |= ~((1u << (8 * (s1 & 3))) - 1);
+      const uint32_t t = v & 0xFCFCFCFCu;
+      if ((t - 0x01010101u) & ~t & 0x80808080u) hiq = false;
+    }
+  }
   rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0) | (medium ? RF_MEDIUM : 0);
 }
 

@@ -251,13 +251,18 @@ def compact_struct(batch: ReadBatch) -> ReadBatchCompactC:
     assert n == 0 or (np.diff(batch.seq_off.astype(np.int64)).max() <= 65535 and np.diff(batch.cigar_off.astype(np.int64)).max() <= 65535)
     values = np.unique(batch.qual)
     if 0 < len(values) <= 16:
+        bits = 2 if len(values) <= 4 else 4
+        per = 8 // bits
         codes = np.zeros(256, np.uint8)
         codes[values] = np.arange(len(values), dtype=np.uint8)
         c = codes[batch.qual]
-        if len(c) % 2:
-            c = np.concatenate([c, np.zeros(1, np.uint8)])
-        keep["qual"] = np.ascontiguousarray(c[0::2] | (c[1::2] << 4))
-        b.qual_bits = 4
+        if len(c) % per:
+            c = np.concatenate([c, np.zeros(per - len(c) % per, np.uint8)])
+        packed = np.zeros(len(c) // per, np.uint8)
+        for k in range(per):  # lowest bits = lowest base index
+            packed |= c[k::per] << (bits * k)
+        keep["qual"] = packed
+        b.qual_bits = bits
         for i, v in enumerate(values):
             b.qual_table[i] = int(v)
     else:

@@ -487,8 +487,8 @@ int guac_reads_export(guac_ctx* ctx, guac_read_batch* out);
  * Compact wire form of a read batch for hosts that ship a partition over PCIe every call: the same reads as
  * guac_read_batch with everything derivable left out — offsets become lengths (prefix sums run on the device),
  * the per-read contig id becomes runs, the not-ACGT mask is rebuilt from the exception list, and base qualities
- * travel as 4-bit codes into a 16-entry table when the batch holds at most 16 distinct qualities (binned
- * Illumina qualities; otherwise one byte per base as before).  100-base single-operator reads: 94 B per read
+ * travel as 2- or 4-bit codes into a table when the batch holds at most 4 / 16 distinct qualities (binned
+ * Illumina qualities; otherwise one byte per base as before).  100-base single-operator reads: 69 / 94 B per read
  * instead of 168.5.  Lossless; replaces the same `Iterator[MappedRead]` as guac_reads_upload.
  */
 typedef struct {
@@ -505,9 +505,9 @@ typedef struct {
   int64_t n_exc;
   const uint64_t* exc_pos;        /* sorted batch-global base indices of the bases that are not A C G T */
   const uint8_t* exc_base;
-  int32_t qual_bits;              /* 8: one byte per base; 4: two bases per byte (low nibble = even base index) */
+  int32_t qual_bits;              /* 8: one byte per base; 4 / 2: two / four bases per byte, lowest bits = lowest base index */
   int32_t _pad;
-  uint8_t qual_table[16];         /* qual_bits == 4: code -> quality */
+  uint8_t qual_table[16];         /* qual_bits < 8: code -> quality */
   const uint8_t* qual;
   const uint8_t* mapq;            /* [n_reads] */
   const uint8_t* flags;           /* [n_reads] */

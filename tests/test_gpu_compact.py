@@ -38,12 +38,12 @@ def test_real_reads_round_trip(gpu_ctx, name):
     assert_same_batch(plain, batch)
 
 
-def test_binned_qualities_travel_as_nibbles(gpu_ctx):
+def test_binned_qualities_travel_as_codes(gpu_ctx):
     contig_len, seed = 30000, 4005
     ref = synth.make_reference(contig_len, seed)
     batch = synth.generate_reads(contig_len, (30, 60), (False, True), seed)
     c = compact_struct(batch)
-    assert c.qual_bits == 4 and sorted(c.qual_table[:4]) == [10, 20, 30, 40]
+    assert c.qual_bits == 2 and sorted(c.qual_table[:4]) == [10, 20, 30, 40]  # four quality bins: 2 bits per base
     gpu_ctx.upload_reference(ref, batch.contig_names)
     gpu_ctx.upload_reads(batch)
     want = gpu_ctx.somatic_standard([(0, 0, contig_len)], ss_params())
@@ -55,11 +55,11 @@ def test_binned_qualities_travel_as_nibbles(gpu_ctx):
     # and the way back: the device batch exported in compact form is the host packer's output
     e = gpu_ctx.export_reads_compact_struct()
     try:
-        assert (e.n_reads, e.n_samples, e.n_contig_runs, e.qual_bits, e.n_exc) == (c.n_reads, c.n_samples, c.n_contig_runs, 4, c.n_exc)
+        assert (e.n_reads, e.n_samples, e.n_contig_runs, e.qual_bits, e.n_exc) == (c.n_reads, c.n_samples, c.n_contig_runs, 2, c.n_exc)
         assert list(e.qual_table[:4]) == list(c.qual_table[:4])
         n, n_bases = int(c.n_reads), int(batch.seq_off[-1])
         for field, count, width in (("start", n, 8), ("read_len", n, 2), ("n_cigar_ops", n, 2), ("cigar", len(batch.cigar), 4),
-                                    ("bases2", (n_bases + 3) // 4, 1), ("qual", (n_bases + 1) // 2, 1), ("mapq", n, 1),
+                                    ("bases2", (n_bases + 3) // 4, 1), ("qual", (n_bases + 3) // 4, 1), ("mapq", n, 1),
                                     ("flags", n, 1), ("sample_id", n, 1)):
             a = C.string_at(C.cast(getattr(e, field), C.c_void_p), count * width)
             b = C.string_at(C.cast(getattr(c, field), C.c_void_p), count * width)
@@ -71,10 +71,15 @@ def test_binned_qualities_travel_as_nibbles(gpu_ctx):
 
 
 def test_odd_base_count_and_empty_batch(gpu_ctx):
-    reads = [make_read("ACGTA", "5M", start=3, quality_scores=[7, 9, 7, 9, 11]), make_read("TTGCATG", "3M1I3M", start=4, sample_id=1)]
-    batch = ReadBatch.from_reads(reads)
-    gpu_ctx.upload_reads_compact(batch)
-    assert_same_batch(device_copy(gpu_ctx, batch.contig_names), batch)
+    # 4 distinct qualities (2-bit codes), then 7 (4-bit codes), neither filling the last byte
+    for quals in ([7, 9, 7, 9, 11], [7, 9, 12, 13, 14]):
+        reads = [make_read("ACGTA", "5M", start=3, quality_scores=quals), make_read("TTGCATG", "3M1I3M", start=4, sample_id=1),
+                 make_read("GGNAC", "5M", start=9, quality_scores=[2, 2, 2, 2, 2] if len(set(quals)) > 3 else None)]
+        batch = ReadBatch.from_reads(reads)
+        c = compact_struct(batch)
+        assert c.qual_bits == (2 if len(np.unique(batch.qual)) <= 4 else 4)
+        gpu_ctx.upload_reads_compact(c)
+        assert_same_batch(device_copy(gpu_ctx, batch.contig_names), batch)
     empty = ReadBatch.from_reads([], contig_names=["chr1"], n_samples=1)
     gpu_ctx.upload_reads_compact(empty)
     assert device_copy(gpu_ctx, ["chr1"]).n_reads == 0
