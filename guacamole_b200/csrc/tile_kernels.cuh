@@ -120,7 +120,7 @@ __device__ __forceinline__ int base_code(uint8_t b) { return b == 'A' ? 0 : b ==
 
 template <class CFG>
 struct TileSmem {
-  uint32_t ref2[CFG::TL / 16 + 2];
+  uint32_t ref2[((CFG::TL + CFG::THREADS - 1) / CFG::THREADS) * (CFG::THREADS / 16) + 2];  // whole passes of the loader + read-ahead
   int cov[CFG::TL + 1];     // packed differences: normal | tumor << 16  -> depths after the scan
   int aux[CFG::TL + 1];     // low-quality tumor read differences | event count << 16 -> lowq | event end offset
   int nonref[CFG::TL];      // non-Match elements: normal | tumor << 16

@@ -28,5 +28,5 @@ def load(name: str):
                 o += int(l)
             contigs[str(n)] = ContigWindow(str(n), lo, arr, int(z[f"ref_{i}_length"]))
         ref = Reference(contigs)
-    extras = {k: z[k] for k in z.files if k in ("golden_vcf", "force_call_vcf")}
+    extras = {k: z[k] for k in z.files if k in ("golden_vcf", "force_call_vcf", "positions")}
     return batch, ref, extras

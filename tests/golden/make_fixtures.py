@@ -74,6 +74,23 @@ def main():
     golden = [l.rstrip("\n") for l in open(RES + "tiny-sjc-output/all.vcf") if not l.startswith("##")]
     force = [l.rstrip("\n") for l in open(RES + "tiny.vcf") if not l.startswith("#")]
     np.savez_compressed(os.path.join(OUT, "tiny_sjc.npz"), **pack(batch, ref, golden_vcf=golden, force_call_vcf=force))
+    # 4. SomaticStandardCallerRealDataSuite.scala:79-150: tumor / normal SAM pairs and the positions they are probed at
+    #    (loadTumorNormalReads: nonDuplicate, passedVendorQualityChecks; only reads over a probed position are kept)
+    real = {
+        "syn1fp": ("synthetic.challenge.set1.tumor.v2.withMDTags.chr2.syn1fp.sam", "synthetic.challenge.set1.normal.v2.withMDTags.chr2.syn1fp.sam",
+                   [216094721, 3529313, 8789794, 104043280, 104175801, 126651101, 241901237, 57270796, 120757852]),
+        "complexvar": ("synthetic.challenge.set1.tumor.v2.withMDTags.chr2.complexvar.sam",
+                       "synthetic.challenge.set1.normal.v2.withMDTags.chr2.complexvar.sam",
+                       [134307261, 90376213, 3638733, 109347468, 82949713, 130919744]),
+        "simplefp": ("tumor.chr20.simplefp.sam", "normal.chr20.simplefp.sam", [13046318, 25939088, 26211835, 29652479, 54495768]),
+    }
+    ref = Reference.from_partial_fasta(RES + "grch37.partial.fasta")
+    for name, (tumor_sam, normal_sam, positions) in real.items():
+        normal, contigs = read_sam(RES + normal_sam, 0)
+        tumor, _ = read_sam(RES + tumor_sam, 1)
+        reads = [r for r in filter_reads(normal + tumor) if any(r.start <= p < r.end for p in positions)]
+        batch = ReadBatch.from_reads(reads, [c for c, _ in contigs], 2)
+        np.savez_compressed(os.path.join(OUT, f"real_{name}.npz"), **pack(batch, ref, positions=np.array(positions, np.int64)))
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(OUT, f)))
