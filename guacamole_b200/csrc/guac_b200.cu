@@ -392,7 +392,13 @@ int guac_ctx_create(int device, guac_ctx** out) {
   // ADAM PhredUtils table: 1 - 10^(-q/10)
   double table[256];
   for (int q = 0; q < 256; ++q) table[q] = 1.0 - std::pow(10.0, -q / 10.0);
-  if (cudaMemcpyToSymbol(c_success_probability, table, sizeof table) != cudaSuccess) {
+  float odds_m1[256];
+  for (int q = 0; q < 256; ++q) {
+    const double o = table[q] / (1.0 - table[q]) - 1.0;  // +inf once 1 - p underflows: such a locus goes to the exact path
+    odds_m1[q] = std::nextafter((float)o, INFINITY);      // never below the exact value: the sum stays an upper bound
+  }
+  if (cudaMemcpyToSymbol(c_success_probability, table, sizeof table) != cudaSuccess ||
+      cudaMemcpyToSymbol(c_odds_minus_one, odds_m1, sizeof odds_m1) != cudaSuccess) {
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return GUAC_E_CUDA;
@@ -740,16 +746,6 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         attr_set = true;
       }
       // LOD-bound table for f = the VAF floor (see `prune` in tile_kernels.cuh)
-      if (ctx->bound_tab_vaf != P.min_vaf || !ctx->b_boundtab.p) {
-        double tab[256];
-        for (int q = 0; q < 256; ++q) {
-          const double p = 1.0 - std::pow(10.0, -q / 10.0);
-          tab[q] = std::log(1.0 - P.min_vaf + P.min_vaf * (p / (1.0 - p)));
-        }
-        GUAC_TRY(upload(ctx, ctx->b_boundtab, tab, 256));
-        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-        ctx->bound_tab_vaf = P.min_vaf;
-      }
       const int max_heavy = (int)std::min<int64_t>(plan.n_slots, plan.n_slots / 16 + 65536);
       GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
       int* heavy_count = fb_count + 1 + plan.n_tiles;
@@ -761,7 +757,6 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       TA.rflags = ctx->b_rflags.as<uint8_t>();
       TA.refs = ctx->d_refs.as<RefView>();
       TA.tiles = ctx->b_tiles.as<Tile>();
-      TA.bound_tab = ctx->b_boundtab.as<double>();
       TA.visited = ctx->b_visited.as<uint8_t>();
       TA.summary = ctx->b_summary.as<guac_locus_summary>();
       TA.heavy = ctx->b_heavy.as<Tile>();
@@ -1234,7 +1229,6 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   TA.rflags = ctx->b_rflags.as<uint8_t>();
   TA.refs = ctx->d_refs.as<RefView>();
   TA.tiles = ctx->b_tiles.as<Tile>();
-  TA.bound_tab = ctx->b_boundtab.as<double>();
   TA.visited = ctx->b_visited.as<uint8_t>();
   TA.summary = ctx->b_summary.as<guac_locus_summary>();
   TA.heavy = ctx->b_heavy.as<Tile>();

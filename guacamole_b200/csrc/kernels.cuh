@@ -12,6 +12,7 @@ constexpr int WARPS_PER_CTA = 8;
 constexpr int CTA_THREADS = WARPS_PER_CTA * 32;
 
 __constant__ double c_success_probability[256];  // ADAM PhredUtils.phredToSuccessProbability table
+__constant__ float c_odds_minus_one[256];         // p / (1 - p) - 1 of the same table, rounded up (LOD upper bound of the tile kernel)
 
 // One range of loci as the planner hands it to the device.
 struct RangeDev {

@@ -136,7 +136,6 @@ struct TileArgs {
   const uint8_t* rflags;
   const RefView* refs;
   const Tile* tiles;
-  const double* bound_tab;  // [256] log(1 - f0 + f0 p/(1-p)) for f0 = min VAF: LOD term of one called-allele element
   uint8_t* visited;
   guac_locus_summary* summary;
   Tile* heavy;              // heavy loci as single-locus tiles
@@ -191,10 +190,16 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   __syncthreads();
   // reference tile -> 2-bit words (16 loci per word) and a not-ACGT mask (32 loci per word): one
   // coalesced byte per thread, packed with warp-wide OR reductions
+  // the part of the tile the reference window holds, in tile coordinates (the rest reads as missing)
+  const long long rel0 = (long long)t0 - (long long)ref.offset;
+  const int l_min = (int)min(max(-rel0, 0ll), (long long)n_loci), l_max = (int)max(min((long long)ref.len - rel0, (long long)n_loci), 0ll);
+  const uint8_t* ref_tile = ref.bases + rel0;
   for (int base = 0; base < TL; base += CFG::THREADS) {
     const int l = base + tid;
-    const uint8_t b = l < n_loci ? ref.at(t0 + l) : (uint8_t)'A';
-    const int c = base_code(b);
+    const uint8_t b = (l >= l_min && l < l_max) ? __ldg(ref_tile + l) : (l < n_loci ? (uint8_t)0 : (uint8_t)'A');
+    const uint32_t d = (uint32_t)b - 65u;  // A C G T are 65 + {0, 2, 6, 19}; their 2-bit code is ((b >> 1) ^ (b >> 2)) & 3
+    const bool acgt = d < 20u && ((0x80045u >> d) & 1u);
+    const int c = acgt ? (int)(((b >> 1) ^ (b >> 2)) & 3u) : 4;
     const uint32_t bits = c < 4 ? (uint32_t)c << (2 * (lane & 15)) : 0u;
     const uint32_t lo = __reduce_or_sync(FULL, lane < 16 ? bits : 0u);
     const uint32_t hi = __reduce_or_sync(FULL, lane >= 16 ? bits : 0u);
@@ -551,9 +556,11 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         // If every tumor read over the locus has all base qualities >= 4 (lowq == 0) the called allele's
         // terms bound the LOD from above; a bound below the threshold (minus a 0.5 margin that dwarfs
         // rounding) means no call is possible (:231) and the matching bases' qualities are never read.
-        double bound = 0;
+        // The bound is summed in single precision (error < 1e-3 over a pileup, far inside the 0.5 margin):
+        // log(1 - f + f p/(1-p)) = log(1 + f (odds - 1)), odds - 1 from a constant table indexed by the quality.
+        float bound = 0.0f;
         int n_alt_normal = 0;
-        const bool at_floor = f == P.min_vaf;
+        const float ff = (float)f;
         for (int i = e0; i < e1; ++i) {
           const uint2 ev = S.ev[S.ev_order[i]];
           const int eslot = (ev.x >> 23) & 1, kind = (ev.x >> 24) & 7;
@@ -562,17 +569,12 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
             ++n_alt_normal;
           } else {
             const int q = (ev.y >> 31) ? (int)(ev.y & 0xFF) : (int)__ldg(R.qual + seq_base + ev.y);
-            if (at_floor) {
-              bound += __ldg(A.bound_tab + q);
-            } else {
-              const double p = c_success_probability[q];
-              bound += log(1.0 - f + f * (p / (1.0 - p)));
-            }
+            bound += __logf(fmaf(ff, c_odds_minus_one[q], 1.0f));
           }
         }
         // a mid-deletion allele has empty alt bases and is never called (:233)
         const bool never_called = (best >> 8) == GUAC_ALN_MID_DELETION;
-        if (never_called || ((S.aux[l] & 0xFFFF) == 0 && bound < (double)P.tumor_odds - 0.5)) {
+        if (never_called || ((S.aux[l] & 0xFFFF) == 0 && bound < (float)P.tumor_odds - 0.5f)) {
           top_t = bcnt;
           top_n = n_alt_normal;
           flags = 1;

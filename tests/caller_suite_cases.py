@@ -92,3 +92,24 @@ def check_real_data_case(name, batch, ref, positions, run):
         result = run(batch, ref, [(cid, pos, pos + 1)], p)
         found = len(test_somatic_genotype_filter(result["calls"])) > 0
         assert found == (pos in REAL_POSITIVE[name]), (name, pos, alleles_of(result))
+
+
+# ---- AlleleEvidenceSuite.scala:14-58 through callPileupVariant ----------------------------------------------------------
+# reads (sequence, cigar, mapping quality) at start 1 over "NTAGATCGA"; evidence of A -> C at locus 2:
+# (meanMappingQuality, medianMappingQuality, medianMismatchesPerRead).  The suite's third case (no supporting read: NaN
+# everywhere) cannot come out of a caller, which only reports alleles some read carries.
+ALLELE_EVIDENCE_CASES = [
+    ([("TCGATCGA", "8M", 30), ("TCGATCGA", "8M", 30), ("TCGACCCTCGA", "4M3I4M", 60)], (40.0, 30.0, 1.0)),
+    ([("TAGATCGA", "8M", 30), ("TCGATCGA", "8M", 60), ("TAGACCCTCGA", "4M3I4M", 60)], (60.0, 60.0, 1.0)),
+]
+
+
+def check_allele_evidence_case(case, run):
+    """run(batch, reference, ranges, params) -> germline_standard result."""
+    from guacamole_b200.native import gs_params
+    reads, (mean_mq, median_mq, median_mm) = case
+    batch = ReadBatch.from_reads([make_read(s, c, start=1, alignment_quality=q) for s, c, q in reads], ["chr1"], 1)
+    out = run(batch, make_reference(("chr1", 0, "NTAGATCGA")), [(0, 2, 3)], gs_params(min_alt_reads=0))
+    assert alleles_of(out) == [(b"A", b"C")]
+    ev = out["calls"]["evidence"][0]
+    assert (ev["mean_mapping_quality"], ev["median_mapping_quality"], ev["median_mismatches_per_read"]) == (mean_mq, median_mq, median_mm)

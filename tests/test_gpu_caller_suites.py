@@ -53,3 +53,13 @@ def test_somatic_standard_caller_real_data_suite(gpu_ctx, name, impl):
         cases.check_real_data_case(name, batch, ref, extra["positions"], lambda b, r, ranges, p: gpu_ctx.somatic_standard(ranges, p))
     finally:
         gpu_ctx.set_option("ss_impl", 0)
+
+
+@pytest.mark.parametrize("case", cases.ALLELE_EVIDENCE_CASES, ids=["all reads support", "one read supports"])
+def test_allele_evidence_suite(gpu_ctx, case):
+    def run(batch, ref, ranges, params):
+        gpu_ctx.upload_reference(ref, batch.contig_names)
+        gpu_ctx.upload_reads(batch)
+        return gpu_ctx.germline_standard(ranges, params)
+
+    cases.check_allele_evidence_case(case, run)

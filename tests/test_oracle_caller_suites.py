@@ -21,3 +21,8 @@ def test_somatic_joint_caller_suite():
 def test_somatic_standard_caller_real_data_suite(name):
     batch, ref, extra = fixtures.load("real_" + name)
     cases.check_real_data_case(name, batch, ref, extra["positions"], oracle.somatic_standard)
+
+
+@pytest.mark.parametrize("case", cases.ALLELE_EVIDENCE_CASES, ids=["all reads support", "one read supports"])
+def test_allele_evidence_suite(case):
+    cases.check_allele_evidence_case(case, oracle.germline_standard)
