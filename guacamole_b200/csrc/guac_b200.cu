@@ -73,7 +73,7 @@ struct guac_ctx {
   int64_t opt_ss_impl = 0;            // 0 = streaming tile kernel (+ gather fallback), 1 = gather kernel only
   int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
-  DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used;
+  DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;
   double bound_tab_vaf = -1;
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
@@ -358,9 +358,11 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   R.flags = ctx->b_flags.as<uint8_t>();
   R.sample_id = ctx->b_sample.as<uint8_t>();
   GUAC_TRY(ensure(ctx, ctx->b_rflags, (size_t)n + 16));
+  GUAC_TRY(ensure(ctx, ctx->b_hdr, ((size_t)n + 1) * sizeof(uint4)));
   if (n > 0) {
     read_fast_flags_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>());
-    ctx->launches += 1;
+    read_headers_pack_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>(), ctx->b_hdr.as<uint4>());
+    ctx->launches += 2;
     CUDA_TRY(ctx, cudaGetLastError());
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   }
@@ -433,6 +435,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_sj_sites.p) cudaFree(ctx->b_sj_sites.p);
   if (ctx->b_boundtab.p) cudaFree(ctx->b_boundtab.p);
   if (ctx->b_arena_used.p) cudaFree(ctx->b_arena_used.p);
+  if (ctx->b_hdr.p) cudaFree(ctx->b_hdr.p);
   for (auto& b : ctx->asm_blocks) cudaFree(b.first);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -755,6 +758,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       CUDA_TRY(ctx, cudaMemsetAsync(visited_count, 0, sizeof(unsigned long long), ctx->stream));
       TileArgs TA;
       TA.rflags = ctx->b_rflags.as<uint8_t>();
+    TA.hdr = ctx->b_hdr.as<uint4>();
       TA.refs = ctx->d_refs.as<RefView>();
       TA.tiles = ctx->b_tiles.as<Tile>();
       TA.visited = ctx->b_visited.as<uint8_t>();
@@ -998,6 +1002,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     TileArgs TA;
     std::memset(&TA, 0, sizeof TA);
     TA.rflags = ctx->b_rflags.as<uint8_t>();
+    TA.hdr = ctx->b_hdr.as<uint4>();
     TA.refs = ctx->d_refs.as<RefView>();
     TA.tiles = ctx->b_tiles.as<Tile>();
     TA.visited = ctx->b_visited.as<uint8_t>();
@@ -1227,6 +1232,7 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   }
   TileArgs TA;
   TA.rflags = ctx->b_rflags.as<uint8_t>();
+    TA.hdr = ctx->b_hdr.as<uint4>();
   TA.refs = ctx->d_refs.as<RefView>();
   TA.tiles = ctx->b_tiles.as<Tile>();
   TA.visited = ctx->b_visited.as<uint8_t>();

@@ -98,6 +98,21 @@ __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags
 
 
 // 32 bits starting at bit `bit` of a little-endian word stream
+// One 16-byte header per read for the tile kernels: x = low 32 bits of the start, y = reference span (16 bits, 0xFFFF =
+// longer: look it up) | sample << 16 | rflags << 24, (z, w) = sequence offset.  One LDG.128 instead of five loads.
+__global__ void read_headers_pack_kernel(ReadsView R, const uint8_t* __restrict__ rflags, uint4* __restrict__ hdr) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R.n_reads) return;
+  const int64_t st = R.start[r], span = R.end[r] - st;
+  const uint64_t s0 = R.seq_off[r];
+  uint4 h;
+  h.x = (uint32_t)st;
+  h.y = (uint32_t)min((long long)span, 0xFFFFll) | ((uint32_t)R.sample_id[r] << 16) | ((uint32_t)rflags[r] << 24);
+  h.z = (uint32_t)s0;
+  h.w = (uint32_t)(s0 >> 32);
+  hdr[r] = h;
+}
+
 __device__ __forceinline__ uint32_t load_bits32_g(const uint8_t* __restrict__ bytes, uint64_t bit) {
   const uint32_t* w = reinterpret_cast<const uint32_t*>(bytes) + (bit >> 5);
   return __funnelshift_r(__ldg(w), __ldg(w + 1), (int)(bit & 31));
@@ -134,6 +149,7 @@ struct TileSmem {
 
 struct TileArgs {
   const uint8_t* rflags;
+  const uint4* hdr;               // packed per-read headers (read_headers_pack_kernel)
   const RefView* refs;
   const Tile* tiles;
   uint8_t* visited;
@@ -226,33 +242,22 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   // ---- A. read-parallel pass ---------------------------------------------------------------
   // The five header loads of a read are independent: issue them together, one read ahead of the one being processed,
   // so the compare work of read i hides the latency of read i + 256's header.
-  struct Hdr {
-    int64_t st64, en64;
-    uint64_t s0;
-    int smp, rf;
-  };
-  auto load_hdr = [&](int rl) {
-    const int64_t r = tile.read_lo + rl;
-    Hdr h;
-    h.smp = (int)__ldg(R.sample_id + r);
-    h.st64 = __ldg(R.start + r);
-    h.en64 = __ldg(R.end + r);
-    h.rf = (int)__ldg(A.rflags + r);
-    h.s0 = __ldg(R.seq_off + r);
-    return h;
-  };
-  Hdr next_hdr{};
-  if (tid < (int)n_reads_tile) next_hdr = load_hdr(tid);
+  const uint4* hdrs = A.hdr + tile.read_lo;
+  const uint32_t t0_lo = (uint32_t)t0;
+  uint4 next_hdr = make_uint4(0, 0, 0, 0);
+  if (tid < (int)n_reads_tile) next_hdr = __ldg(hdrs + tid);
   for (int rl = tid; rl < (int)n_reads_tile; rl += CFG::THREADS) {
     const int64_t r = tile.read_lo + rl;
-    const Hdr hdr = next_hdr;
-    if (rl + CFG::THREADS < (int)n_reads_tile) next_hdr = load_hdr(rl + CFG::THREADS);
-    const int smp = hdr.smp;
-    const int64_t st64 = hdr.st64, en64 = hdr.en64;
-    const uint8_t rf = (uint8_t)hdr.rf;
+    const uint4 hdr = next_hdr;
+    if (rl + CFG::THREADS < (int)n_reads_tile) next_hdr = __ldg(hdrs + rl + CFG::THREADS);
+    const int smp = (int)((hdr.y >> 16) & 0xFF);
+    const uint8_t rf = (uint8_t)(hdr.y >> 24);
     if (MODE == 2 ? smp >= P.n_samples : (smp != P.normal_sample && smp != P.tumor_sample)) continue;
     const int slot = MODE == 2 ? (int)((P.sample_mask >> smp) & 1u) : (smp == P.tumor_sample ? 1 : 0);
-    const int st = (int)max((long long)(st64 - t0), -(1ll << 30)), en = (int)min((long long)(en64 - t0), (1ll << 30));
+    // the reads of a tile start within 2^31 loci of it, so 32-bit wrap-around arithmetic gives the exact offset
+    const int st = (int)(hdr.x - t0_lo);
+    int en = st + (int)(hdr.y & 0xFFFF);
+    if ((hdr.y & 0xFFFF) == 0xFFFF) en = (int)min((long long)(__ldg(R.end + r) - t0), (1ll << 30));  // a span beyond 16 bits
     const int a = max(st, 0), b = min(en, n_loci);  // overlap [a, b) in tile coordinates
     if (a >= b) continue;
     const int one = slot ? 65536 : 1;
@@ -267,7 +272,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)rl; else S.overflow = 1;
       continue;
     }
-    const uint64_t s0 = hdr.s0;
+    const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     // aligned segment: loci [lb, le) (tile coordinates, unclipped) hold read positions rp0..; 16 bases per step
     auto compare_segment = [&](int lb, int le, int rp0) {
