@@ -447,6 +447,45 @@ __device__ inline int count_of_mismatches(const ReadsView& R, int64_t r, const R
       return n;
     }
   }
+  // Several operators out of {M,=,X,I,D,S,H}: walk them.  Only bases of aligned operators can be Mismatch elements, and
+  // the last base of an operator that anchors a following insertion (M/= only) or deletion is an Insertion / Deletion
+  // element whatever its base (PE.scala:59-117) — the same rule the tile kernel applies.
+  {
+    bool plain = !(s == 0 && (__ldg(R.cigar + c0) & 15) == OPC_I);  // PE.scala:88-89: leave to the exact cursor
+    for (uint32_t ci = c0; plain && ci < c1; ++ci) {
+      const uint32_t w = __ldg(R.cigar + ci);
+      const int op = w & 15;
+      plain = (w >> 4) != 0 && (op == OPC_M || op == OPC_EQ || op == OPC_X || op == OPC_I || op == OPC_D || op == OPC_S || op == OPC_H);
+    }
+    if (plain) {
+      const uint64_t s0 = __ldg(R.seq_off + r);
+      int64_t cl = s;
+      uint64_t rp = 0;
+      for (uint32_t ci = c0; ci < c1; ++ci) {
+        const uint32_t w = __ldg(R.cigar + ci);
+        const int op = w & 15, len = (int)(w >> 4);
+        if (op == OPC_M || op == OPC_EQ || op == OPC_X) {
+          const int nop = ci + 1 < c1 ? (int)(__ldg(R.cigar + ci + 1) & 15) : -1;
+          const int plain_len = len - ((nop == OPC_D || (nop == OPC_I && op != OPC_X)) ? 1 : 0);
+          for (int k = 0; k < plain_len; ++k) {
+            const uint8_t rb = ref.at(cl + k);
+            if (rb == 0) {
+              report_error(err, DERR_REF_MISSING, contig, cl + k, r);
+              return n;
+            }
+            n += read_base(R, s0 + rp + (uint64_t)k) != rb;
+          }
+          cl += len;
+          rp += (uint64_t)len;
+        } else if (op == OPC_D) {
+          cl += len;
+        } else if (op == OPC_I || op == OPC_S) {
+          rp += (uint64_t)len;
+        }
+      }
+      return n;
+    }
+  }
   for (int64_t x = s; x < en; ++x) {
     Elem e;
     int ec = element_at(R, r, x, ref, e);
@@ -490,14 +529,15 @@ ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P,
   __shared__ unsigned h_mapq[2][256], h_bq[2][256], h_mm[2][MM_BINS];
   __shared__ unsigned s_depth[2], s_pos[2], s_adepth[2], s_apos[2];
   __shared__ int s_list[1024];  // reads of either sample that overlap the locus (read offset << 1 | which)
-  __shared__ int s_n;
+  __shared__ int s_mm_read[512], s_mm_cnt[512];  // reads whose mismatches are to be counted, and the counts
+  __shared__ int s_n, s_nmm;
   SSCallDev& c = calls[blockIdx.x];
   const RefView ref = refs[c.ref_index];
   const int64_t x = c.locus;
   for (int i = threadIdx.x; i < 512; i += blockDim.x) (&h_mapq[0][0])[i] = (&h_bq[0][0])[i] = 0;
   for (int i = threadIdx.x; i < 2 * MM_BINS; i += blockDim.x) (&h_mm[0][0])[i] = 0;
   if (threadIdx.x < 2) s_depth[threadIdx.x] = s_pos[threadIdx.x] = s_adepth[threadIdx.x] = s_apos[threadIdx.x] = 0;
-  if (threadIdx.x == 0) s_n = 0;
+  if (threadIdx.x == 0) s_n = s_nmm = 0;
   __syncthreads();
   // reads are sorted by start: nothing at or after the first read that starts beyond the locus can overlap it
   int64_t hi = c.read_hi;
@@ -525,12 +565,19 @@ ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P,
       if (pos) atomicAdd(&s_apos[which], 1u);
       atomicAdd(&h_mapq[which][__ldg(R.mapq + r)], 1u);
       atomicAdd(&h_bq[which][e.quality], 1u);
-      int mm = count_of_mismatches(R, r, ref, err, c.contig_id);
-      if (mm >= MM_BINS) {
-        report_error(err, DERR_MISMATCH_HIST, c.contig_id, x, r);
-        mm = MM_BINS - 1;
+      // countOfMismatches walks the whole read: queued, and shared out over all threads below
+      const int j = atomicAdd(&s_nmm, 1);
+      if (j < 512) {
+        s_mm_read[j] = (int)((r - c.read_lo) << 1) | which;
+        s_mm_cnt[j] = 0;
+      } else {  // deeper than the queue: in place
+        int mm = count_of_mismatches(R, r, ref, err, c.contig_id);
+        if (mm >= MM_BINS) {
+          report_error(err, DERR_MISMATCH_HIST, c.contig_id, x, r);
+          mm = MM_BINS - 1;
+        }
+        atomicAdd(&h_mm[which][mm], 1u);
       }
-      atomicAdd(&h_mm[which][mm], 1u);
     }
   };
   // pass 1: which reads overlap the locus (cheap, coalesced); pass 2: one thread per overlapping read
@@ -545,6 +592,41 @@ ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P,
   __syncthreads();
   const int n_list = min(s_n, 1024);
   for (int i = threadIdx.x; i < n_list; i += blockDim.x) visit(c.read_lo + (s_list[i] >> 1), s_list[i] & 1);
+  __syncthreads();
+  // MappedRead.countOfMismatches (MappedRead.scala:53-64) of the queued reads: 16 loci of a single-operator read per
+  // work item, so a call's ~45 reads x 100 bases keep all 128 threads busy instead of 45 threads for 100 iterations
+  const int n_mm = min(s_nmm, 512);
+  for (int item = threadIdx.x; item < n_mm * 16; item += blockDim.x) {
+    const int j = item >> 4, chunk = item & 15;
+    const int64_t r = c.read_lo + (s_mm_read[j] >> 1);
+    const uint32_t c0 = __ldg(R.cigar_off + r), c1 = __ldg(R.cigar_off + r + 1);
+    const int64_t s = __ldg(R.start + r), en = __ldg(R.end + r);
+    const int op = c1 - c0 == 1 ? (int)(__ldg(R.cigar + c0) & 15) : -1;
+    if ((op == OPC_M || op == OPC_EQ || op == OPC_X) && en - s <= 256) {
+      const uint64_t s0 = __ldg(R.seq_off + r);
+      int n = 0;
+      for (int64_t l = s + 16 * chunk; l < min(en, s + 16 * chunk + 16); ++l) {
+        const uint8_t rb = ref.at(l);
+        if (rb == 0) {
+          report_error(err, DERR_REF_MISSING, c.contig_id, l, r);
+          break;
+        }
+        n += read_base(R, s0 + (uint64_t)(l - s)) != rb;
+      }
+      if (n) atomicAdd(&s_mm_cnt[j], n);
+    } else if (chunk == 0) {  // several operators, or a very long read: one thread takes the whole read
+      atomicAdd(&s_mm_cnt[j], count_of_mismatches(R, r, ref, err, c.contig_id));
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < n_mm; j += blockDim.x) {
+    int mm = s_mm_cnt[j];
+    if (mm >= MM_BINS) {
+      report_error(err, DERR_MISMATCH_HIST, c.contig_id, x, c.read_lo + (s_mm_read[j] >> 1));
+      mm = MM_BINS - 1;
+    }
+    atomicAdd(&h_mm[s_mm_read[j] & 1][mm], 1u);
+  }
   __syncthreads();
   if (threadIdx.x < 2) {
     const int which = threadIdx.x;

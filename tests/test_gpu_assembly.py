@@ -191,3 +191,77 @@ def test_alignment_random_pairs(gpu_ctx):
             continue
         got, want = gpu_ctx.read_alignment(seq, ref), oracle.read_alignment(seq, ref)
         assert got[:4] == tuple(want[:4]) and got[4] == want[4]
+
+
+# ---- planted indels (BASELINE configs[4]: germline-assembly on reads with planted indels, k = 31) -----------------------
+def simulate_haplotype_reads(reference: str, edits, n_reads, read_len, rng, alt_fraction=1.0, first=0):
+    """Reads of `read_len` bases drawn from the reference or (with probability alt_fraction) from the haplotype that
+    carries `edits` = [(ref_pos, deleted_len, inserted_bases)], aligned with the CIGAR the edits imply."""
+    reads = []
+    span = len(reference) - 2 * read_len
+    for i in range(n_reads):
+        start = first + int(rng.integers(0, span))
+        use_alt = rng.random() < alt_fraction
+        seq, ops, pos = [], [], start
+        todo = [e for e in edits if use_alt and e[0] > start]  # an edit right at the read's first base is not representable
+
+        def push(op, n):
+            if n <= 0:
+                return
+            if ops and ops[-1][0] == op:
+                ops[-1][1] += n
+            else:
+                ops.append([op, n])
+
+        while len(seq) < read_len:
+            nxt = todo[0] if todo else None
+            if nxt is not None and nxt[0] == pos:
+                _, dlen, ins = todo.pop(0)
+                if len(seq) + len(ins) >= read_len:  # the read would end inside the insertion: stop before it
+                    break
+                if ins:
+                    seq.extend(ins)
+                    push("I", len(ins))
+                if dlen:
+                    push("D", dlen)
+                    pos += dlen
+                continue
+            stop = min(nxt[0] if nxt is not None else len(reference), pos + read_len - len(seq))
+            seq.extend(reference[pos:stop])
+            push("M", stop - pos)
+            pos = stop
+        while ops and ops[-1][0] != "M":  # no trailing indel operators
+            op, n = ops.pop()
+            if op == "I":
+                del seq[-n:]
+        cigar = "".join(f"{n}{op}" for op, n in ops)
+        reads.append(make_read("".join(seq), cigar, start=start, chr="chr1", quality_scores=[30] * len(seq),
+                               is_positive_strand=bool(i & 1)))
+    return reads
+
+
+@pytest.mark.parametrize("shortcut", [False, True])
+def test_planted_indels_k31(gpu_ctx, shortcut):
+    from guacamole_b200.io import make_reference
+    rng = np.random.default_rng(31)
+    n = 6000
+    reference = "".join(rng.choice(list("ACGT"), n))
+    # a 3-base deletion, a 2-base insertion, a 1-base deletion next to an SNV-free stretch; anchors are the base before
+    edits = [(1500, 3, ""), (3000, 0, "GT"), (4500, 1, "")]
+    reads = simulate_haplotype_reads(reference, edits, n_reads=1800, read_len=100, rng=rng, alt_fraction=1.0)
+    reads += simulate_haplotype_reads(reference, [(2200, 0, "ACA")], n_reads=900, read_len=100, rng=rng, alt_fraction=0.5)  # het insertion
+    batch = ReadBatch.from_reads(reads, ["chr1"], 1)
+    ref = make_reference(("chr1", 0, reference), contig_length=n)
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    p = ga_params(kmer_size=31, assembly_window_range=100, min_occurrence=3, min_mean_kmer_quality=0, min_area_vaf_percent=10,
+                  shortcut_assembly=shortcut)
+    ranges = [(0, 150, n - 150)]
+    want = oracle.germline_assembly(batch, ref, ranges, p)
+    got = gpu_ctx.germline_assembly(ranges, p)
+    assert_assembly_equal(got, want)
+    # every planted indel is called: same length change, anchored at the base before it (an insertion inside a short
+    # repeat is reported at its left-most equivalent position, a base or two earlier)
+    called = [(r[2], len(r[3]) - len(r[4])) for r in decode(got) if r[0]]
+    for pos, change in ((1499, 3), (2199, -3), (2999, -2), (4499, 1)):
+        assert any(c == change and pos - 3 <= q <= pos for q, c in called), (pos, change, called)
