@@ -21,6 +21,7 @@
 #include "scan.cuh"
 #include "synth_kernels.cuh"
 #include "tile_kernels.cuh"
+#include "stream_kernels.cuh"
 #include "joint_host.hpp"
 #include "germline_kernels.cuh"
 #include "assembly_kernels.cuh"
@@ -41,6 +42,8 @@ struct ContigDev {
   int64_t offset = 0, len = 0;
   uint8_t* bases = nullptr;
   int ref_index = -1;
+  uint32_t* ref2 = nullptr;  // 2-bit copy for the stream path (16 loci per word), rebuilt when the window changes
+  bool ref2_dirty = true;
 };
 
 }  // namespace
@@ -75,6 +78,7 @@ struct guac_ctx {
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;
   double bound_tab_vaf = -1;
+  DevBuf b_bins, b_bin_count;  // stream path: per-read event slots and counts
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
 };
@@ -259,6 +263,30 @@ int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& pla
   return GUAC_OK;
 }
 
+// Stream path: 2-bit copies of the reference windows, rebuilt for the windows that changed.
+int sync_ref2(guac_ctx* ctx) {
+  for (auto& kv : ctx->contigs) {
+    ContigDev& c = kv.second;
+    if (!c.ref2_dirty && c.ref2) continue;
+    if (c.ref2) CUDA_TRY(ctx, cudaFree(c.ref2));
+    c.ref2 = nullptr;
+    const size_t words = (size_t)(c.len / 16) + 4;  // read-ahead of the compare loop
+    cudaError_t e = cudaMalloc(&c.ref2, words * sizeof(uint32_t));
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return fail(ctx, GUAC_E_OOM, "cudaMalloc failed for the 2-bit reference");
+    }
+    CUDA_TRY(ctx, cudaMemsetAsync(c.ref2, 0, words * sizeof(uint32_t), ctx->stream));
+    if (c.len > 0) {
+      ref2_pack_kernel<<<blocks_for((c.len + 15) / 16, 256), 256, 0, ctx->stream>>>(c.bases, c.len, c.ref2);
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+    }
+    c.ref2_dirty = false;
+  }
+  return GUAC_OK;
+}
+
 int reset_error(guac_ctx* ctx) {
   GUAC_TRY(ensure(ctx, ctx->b_err, sizeof(DeviceError)));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_err.p, 0, sizeof(DeviceError), ctx->stream));
@@ -437,6 +465,10 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_arena_used.p) cudaFree(ctx->b_arena_used.p);
   if (ctx->b_hdr.p) cudaFree(ctx->b_hdr.p);
   for (auto& b : ctx->asm_blocks) cudaFree(b.first);
+  for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count})
+    if (b->p) cudaFree(b->p);
+  for (auto& kv : ctx->contigs)
+    if (kv.second.ref2) cudaFree(kv.second.ref2);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);
@@ -501,6 +533,7 @@ int guac_ref_reserve(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t l
   c.bases = nullptr;
   c.offset = offset;
   c.len = len;
+  c.ref2_dirty = true;
   cudaError_t e = cudaMalloc(&c.bases, (size_t)std::max<int64_t>(len, 16));
   if (e != cudaSuccess) {
     (void)cudaGetLastError();
@@ -525,6 +558,7 @@ int guac_ref_upload(guac_ctx* ctx, int32_t contig_id, const uint8_t* bases, int6
     return fail(ctx, GUAC_E_INVALID_INPUT, "Illegal reference slice: outside the reserved window");
   if (len > 0) {
     CUDA_TRY(ctx, cudaMemcpyAsync(c.bases + (offset - c.offset), bases, (size_t)len, cudaMemcpyHostToDevice, ctx->stream));
+    c.ref2_dirty = true;
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   }
   return GUAC_OK;
@@ -701,7 +735,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   // anything else, or opt_ss_impl = 1, takes the generic gather kernel.
   const bool two_samples = (params->normal_sample_id == 0 && params->tumor_sample_id == 1) ||
                            (params->normal_sample_id == 1 && params->tumor_sample_id == 0);
-  const bool use_tiles = ctx->opt_ss_impl == 0 && two_samples;
+  const bool use_tiles = ctx->opt_ss_impl != 1 && two_samples;
   Plan plan;
   GUAC_TRY(make_plan(ctx, loci, n_ranges, plan, use_tiles ? TCfg::TL : TILE_LOCI));
   trace.mark("plan");
@@ -757,8 +791,9 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       unsigned long long* visited_count = ctx->b_vcount.as<unsigned long long>();
       CUDA_TRY(ctx, cudaMemsetAsync(visited_count, 0, sizeof(unsigned long long), ctx->stream));
       TileArgs TA;
+      std::memset(&TA, 0, sizeof TA);
       TA.rflags = ctx->b_rflags.as<uint8_t>();
-    TA.hdr = ctx->b_hdr.as<uint4>();
+      TA.hdr = ctx->b_hdr.as<uint4>();
       TA.refs = ctx->d_refs.as<RefView>();
       TA.tiles = ctx->b_tiles.as<Tile>();
       TA.visited = ctx->b_visited.as<uint8_t>();
@@ -771,8 +806,37 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       TA.force_fallback_mod = (int)ctx->opt_force_fallback_mod;
       TA.n_visited = visited_count;
       TA.err = ctx->b_err.as<DeviceError>();
-      cudaEventRecord(ctx->ev0, ctx->stream);
-      ss_tile_kernel<TCfg, 0><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+      if (ctx->opt_ss_impl == 2) {
+        // stream implementation: the reads are compared with the reference by a kernel of their own, then the locus pass
+        GUAC_TRY(sync_ref2(ctx));
+        GUAC_TRY(ensure(ctx, ctx->b_bins, (size_t)(ctx->n_reads + 1) * STREAM_EV_CAP * sizeof(uint2)));
+        GUAC_TRY(ensure(ctx, ctx->b_bin_count, (size_t)ctx->n_reads + 16));
+        TA.ev_by_read = ctx->b_bins.as<uint2>();
+        TA.ev_count = ctx->b_bin_count.as<uint8_t>();
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_bin_count.p, 0, (size_t)ctx->n_reads + 16, ctx->stream));  // contigs without a reference
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        for (auto& sp : ctx->contig_spans) {  // one launch per contig of the batch: its reference rides in the arguments
+          auto it = ctx->contigs.find(sp.first);
+          if (it == ctx->contigs.end() || sp.second.second <= sp.second.first) continue;
+          StreamArgs SA;
+          SA.hdr = ctx->b_hdr.as<uint4>();
+          SA.read_lo = sp.second.first;
+          SA.read_hi = sp.second.second;
+          SA.ref.bases = it->second.bases;
+          SA.ref.offset = it->second.offset;
+          SA.ref.len = it->second.len;
+          SA.ref2 = it->second.ref2;
+          SA.events = ctx->b_bins.as<uint2>();
+          SA.n_events = ctx->b_bin_count.as<uint8_t>();
+          ss_read_events_kernel<<<blocks_for(SA.read_hi - SA.read_lo, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
+          ctx->launches += 1;
+        }
+        CUDA_TRY(ctx, cudaGetLastError());
+        ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+      } else {
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        ss_tile_kernel<TCfg, 0><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+      }
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
       int counts[2] = {0, 0};
@@ -784,10 +848,11 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       ctx->last_heavy_loci = n_heavy;
       if (n_heavy > max_heavy) {
         // more heavy loci than the list holds (pathological input): redo the call with the generic kernel
+        const int64_t impl = ctx->opt_ss_impl;
         ctx->opt_ss_impl = 1;
         int st = guac_somatic_standard(ctx, params, loci, n_ranges, out_calls, n_calls, out_arena, arena_len, out_summary,
                                        out_n_visited);
-        ctx->opt_ss_impl = 0;
+        ctx->opt_ss_impl = impl;
         return st;
       }
       if (n_heavy > 0) {  // loci that need the full likelihood: one warp each
@@ -1426,7 +1491,7 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
   if (!ctx || !name) return GUAC_E_INVALID_INPUT;
   const std::string n(name);
   if (n == "ss_impl") {
-    if (value != 0 && value != 1) return fail(ctx, GUAC_E_INVALID_INPUT, "ss_impl must be 0 (tile) or 1 (gather)");
+    if (value < 0 || value > 2) return fail(ctx, GUAC_E_INVALID_INPUT, "ss_impl must be 0 (tile), 1 (gather) or 2 (stream)");
     ctx->opt_ss_impl = value;
   } else if (n == "ss_force_fallback_mod") {
     ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
@@ -1486,6 +1551,7 @@ int guac_synth_generate(guac_ctx* ctx, int32_t contig_id, int64_t contig_len, in
   // reference
   GUAC_TRY(guac_ref_reserve(ctx, contig_id, 0, contig_len));
   synth::reference_kernel<<<blocks_for(contig_len, 256), 256, 0, ctx->stream>>>(seed, contig_len, ctx->contigs[contig_id].bases);
+  ctx->contigs[contig_id].ref2_dirty = true;
   // reads
   const int64_t n_bases = n * synth::READ_LEN;
   GUAC_TRY(ensure(ctx, ctx->b_start, (size_t)n * 8 + 16));

@@ -1,0 +1,149 @@
+// stream_kernels.cuh — read-streaming front half of the tile path ("stream" implementation of somatic-standard).
+//
+// The tile kernel (tile_kernels.cuh) compares every read with the reference once per tile it overlaps, inside the
+// CTA's chain of barriers.  Here that comparison is a kernel of its own: one thread per read, every read visited
+// exactly once, no shared memory, no barrier and no atomic.  A read compares its aligned segments, 16 bases per step,
+// with a 2-bit copy of the reference kept in HBM (12.5 MB for a 50 Mbp contig: L2-resident) and leaves its non-Match
+// elements in its own slot of a per-read event table.  The locus pass (ss_tile_kernel<..., STREAM = true>) then only
+// reads the headers and the event slots of the tile's reads.
+#pragma once
+#include "tile_kernels.cuh"
+
+namespace guac {
+
+// ASCII reference window -> 2 bits per locus, 16 loci per word; anything but A C G T packs as 0 (tiles holding such a
+// locus are handed to the generic kernel by the locus pass, so the value never matters).
+__global__ void ref2_pack_kernel(const uint8_t* __restrict__ bases, int64_t len, uint32_t* __restrict__ ref2) {
+  const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (16 * w >= len) return;
+  uint32_t v = 0;
+  for (int k = 0; k < 16 && 16 * w + k < len; ++k) {
+    const uint8_t b = bases[16 * w + k];
+    const uint32_t d = (uint32_t)b - 65u;
+    if (d < 20u && ((0x80045u >> d) & 1u)) v |= (((uint32_t)(b >> 1) ^ (uint32_t)(b >> 2)) & 3u) << (2 * k);
+  }
+  ref2[w] = v;
+}
+
+constexpr int STREAM_EV_CAP = 8;  // event records kept per read; a read with more sends its tiles to the generic kernel
+
+struct StreamArgs {
+  const uint4* hdr;     // packed read headers
+  int64_t read_lo, read_hi;  // the reads of one contig
+  RefView ref;          // that contig's reference window
+  const uint32_t* ref2; // and its 2-bit copy
+  uint2* events;        // [n_reads][STREAM_EV_CAP]
+  uint8_t* n_events;    // [n_reads] (255: more than the cap)
+};
+
+// Read-event record (per read, independent of the loci of the call):
+//   x = reference offset from the read's start (16 bits) | kind << 16 | code << 19 (codes as in the tile kernel's events)
+//   y = read position of the mismatching base, or bit 31 | detail << 8 | qualityScore for the other kinds
+__device__ __forceinline__ uint32_t pack_read_event(int off, int kind, int code) {
+  return (uint32_t)off | ((uint32_t)kind << 16) | ((uint32_t)code << 19);
+}
+
+// One thread per read: the read's non-Match elements against the 2-bit reference.  No shared memory, no barrier, no atomic.
+__global__ void __launch_bounds__(256) ss_read_events_kernel(ReadsView R, const __grid_constant__ StreamArgs A) {
+  const int64_t r = A.read_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= A.read_hi) return;
+  const uint4 hdr = __ldg(A.hdr + r);
+  const uint8_t rf = (uint8_t)(hdr.y >> 24);
+  int n_ev = 0;
+  uint2* mine = A.events + r * STREAM_EV_CAP;
+  auto push = [&](int off, int kind, int code, uint32_t second) {
+    if (n_ev < STREAM_EV_CAP && off < 65536) mine[n_ev] = make_uint2(pack_read_event(off, kind, code), second);
+    else if (off >= 65536) n_ev = 256;  // not representable: treated like an overflow
+    ++n_ev;
+  };
+  auto direct = [](int q, int detail) { return 0x80000000u | ((uint32_t)(detail & 0xFF) << 8) | (uint32_t)(q & 0xFF); };
+  {
+    const RefView& ref = A.ref;
+    const uint32_t* ref2 = A.ref2;
+    const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
+    // reads and windows lie within 2^31 loci of each other on a contig: 32-bit wrap-around arithmetic is exact
+    const int span = (hdr.y & 0xFFFF) == 0xFFFF ? (int)min((long long)(__ldg(R.end + r) - __ldg(R.start + r)), (1ll << 30)) : (int)(hdr.y & 0xFFFF);
+    if (rf & RF_MEDIUM) {  // the others need the exact cursor: the locus pass handles them, one warp per read
+      const long long ref_rel = (long long)(int)(hdr.x - (uint32_t)ref.offset);  // reference-window index of the read's first locus
+      // aligned segment: loci [lb, le) (offsets from the read's start) hold read positions rp0..
+      auto compare_segment = [&](int lb, int le, int rp0) {
+        const int ca = (int)max((long long)lb, -ref_rel), cb = (int)min((long long)le, (long long)ref.len - ref_rel);  // inside the window
+        if (ca >= cb) return;
+        const uint64_t rbit = 2 * (s0 + (uint64_t)(rp0 + (ca - lb)));
+        const uint32_t* rw = reinterpret_cast<const uint32_t*>(R.bases2) + (rbit >> 5);
+        const uint64_t fbit = 2 * (uint64_t)(ref_rel + ca);
+        const uint32_t* fw = ref2 + (fbit >> 5);
+        const int rsh = (int)(rbit & 31), fsh = (int)(fbit & 31);
+        uint32_t rlo = __ldg(rw), flo = __ldg(fw);
+        const int q_rel = rp0 - lb;  // read position of offset l = q_rel + l
+        auto step = [&](int l, uint32_t keep) {
+          const uint32_t rhi = __ldg(++rw), fhi = __ldg(++fw);
+          const uint32_t rd = __funnelshift_r(rlo, rhi, rsh);
+          const uint32_t x = rd ^ __funnelshift_r(flo, fhi, fsh);
+          rlo = rhi;
+          flo = fhi;
+          uint32_t m = (x | (x >> 1)) & keep;
+          while (m) {
+            const int bit = __ffs(m) - 1;
+            m &= m - 1;
+            push(l + (bit >> 1), GUAC_ALN_MISMATCH, (rd >> bit) & 3, (uint32_t)(q_rel + l + (bit >> 1)));
+          }
+        };
+        int l = ca;
+        for (; l + 16 <= cb; l += 16) step(l, 0x55555555u);
+        if (l < cb) step(l, ((1u << (2 * (cb - l))) - 1) & 0x55555555u);
+      };
+      if (rf & RF_FAST) {
+        compare_segment(0, span, 0);
+      } else {  // operator walk (PE.scala:59-117 per operator instead of per base)
+        const uint32_t c0 = __ldg(R.cigar_off + r), c1 = __ldg(R.cigar_off + r + 1);
+        const int read_len = (int)(__ldg(R.seq_off + r + 1) - s0);
+        int cl = 0, rp = 0;
+        for (uint32_t ci = c0; ci < c1; ++ci) {
+          const uint32_t w = __ldg(R.cigar + ci);
+          const int op = w & 15, len = (int)(w >> 4);
+          if (op == OPC_M || op == OPC_EQ || op == OPC_X) {
+            int nop = -1, nlen = 0;
+            if (ci + 1 < c1) {
+              const uint32_t nw = __ldg(R.cigar + ci + 1);
+              nop = nw & 15;
+              nlen = (int)(nw >> 4);
+            }
+            const bool special_last = nop == OPC_D || (nop == OPC_I && op != OPC_X);
+            compare_segment(cl, cl + len - (special_last ? 1 : 0), rp);
+            if (special_last) {
+              const int ll = cl + len - 1, k = rp + len - 1;
+              if (nop == OPC_I) {  // qualityScore = min over anchor + inserted qualities (PE.scala:153)
+                const int until = min(k + nlen + 1, read_len);
+                int q = 255;
+                uint32_t h = 2166136261u ^ (uint32_t)(until - k);
+                for (int j = k; j < until; ++j) {
+                  q = min(q, (int)__ldg(R.qual + s0 + j));
+                  const uint64_t gi = s0 + (uint64_t)j;
+                  h = (h ^ ((__ldg(R.bases2 + (gi >> 2)) >> ((gi & 3) * 2)) & 3)) * 16777619u;
+                }
+                push(ll, GUAC_ALN_INSERTION, 4, direct(q, (int)((h ^ (h >> 8) ^ (h >> 16) ^ (h >> 24)) & 0xFF)));
+              } else {
+                // (the locus pass checks that the deleted reference bases exist, PE.scala:95, when the anchor is inside a tile)
+                push(ll, GUAC_ALN_DELETION, nlen < 255 ? 4 : 5, direct(__ldg(R.qual + s0 + k), nlen));
+              }
+            }
+            cl += len;
+            rp += len;
+          } else if (op == OPC_D) {
+            // one record per run of deleted loci: bits 16..30 of y carry the run length
+            const int mq = __ldg(R.mapq + r);
+            for (int done = 0; done < len; done += 0x7FFF)
+              push(cl + done, GUAC_ALN_MID_DELETION, 4, direct(mq, 0) | ((uint32_t)min(len - done, 0x7FFF) << 16));
+            cl += len;
+          } else if (op == OPC_I || op == OPC_S) {
+            rp += len;
+          }
+        }
+      }
+    }
+  }
+  A.n_events[r] = (uint8_t)min(n_ev, 255);
+}
+
+}  // namespace guac

@@ -164,6 +164,9 @@ struct TileArgs {
   DeviceError* err;
   const guac_range* force;        // MODE 2: force-call ranges (allele loci); a site one locus before is always a candidate
   int n_force;
+  // STREAM variant (stream_kernels.cuh): the reads were compared with the reference by a kernel of their own
+  const uint2* ev_by_read;        // [n_reads][STREAM_EV_CAP] read-event records
+  const uint8_t* ev_count;        // [n_reads] (more than the cap: the tile goes to the generic kernel)
 };
 
 // MODE 0: somatic-standard (two samples).  MODE 1: germline toy caller's dense half — one sample (the "tumor"
@@ -173,7 +176,7 @@ struct TileArgs {
 // P.min_alt_reads of their reads have a non-Match element at x + 1 (an alternate allele can only start there,
 // jointcaller/pileup_summarization/ReadSubsequence.scala:106-135), when x + 1 is force-called, or when x + 1 lies
 // in the next tile.
-template <class CFG, int MODE>
+template <class CFG, int MODE, bool STREAM = false>
 __global__ void __launch_bounds__(CFG::THREADS, GUAC_TK_MINB)
 ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -215,6 +218,10 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const uint8_t b = (l >= l_min && l < l_max) ? __ldg(ref_tile + l) : (l < n_loci ? (uint8_t)0 : (uint8_t)'A');
     const uint32_t d = (uint32_t)b - 65u;  // A C G T are 65 + {0, 2, 6, 19}; their 2-bit code is ((b >> 1) ^ (b >> 2)) & 3
     const bool acgt = d < 20u && ((0x80045u >> d) & 1u);
+    if (STREAM) {  // the compare already happened in the read pass: only the not-ACGT test is needed here
+      if (__any_sync(FULL, !acgt) && lane == 0) S.ref_has_mask = 1;
+      continue;
+    }
     const int c = acgt ? (int)(((b >> 1) ^ (b >> 2)) & 3u) : 4;
     const uint32_t bits = c < 4 ? (uint32_t)c << (2 * (lane & 15)) : 0u;
     const uint32_t lo = __reduce_or_sync(FULL, lane < 16 ? bits : 0u);
@@ -231,7 +238,6 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
     return;
   }
-
   auto push_event = [&](int l, int rl, int slot, int kind, int code, uint32_t second) {
     atomicAdd(&S.nonref[l], slot ? 65536 : 1);
     const int e = atomicAdd(&S.n_events, 1);
@@ -274,6 +280,35 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     }
     const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
+    if (STREAM) {  // the read was compared by ss_read_events_kernel: take the events that fall inside the tile
+      const int cnt = (int)__ldg(A.ev_count + r);
+      if (cnt > 8) {
+        S.overflow = 1;
+        continue;
+      }
+      const uint2* evs = A.ev_by_read + r * 8;
+      for (int j = 0; j < cnt; ++j) {
+        const uint2 ev = __ldg(evs + j);
+        const int l = st + (int)(ev.x & 0xFFFF);
+        const int kind = (int)((ev.x >> 16) & 7), code = (int)((ev.x >> 19) & 7);
+        if (kind == GUAC_ALN_MID_DELETION) {  // a run of deleted loci
+          const int run = (int)((ev.y >> 16) & 0x7FFF);
+          for (int ll = max(l, 0); ll < min(l + run, n_loci); ++ll) push_event(ll, rl, slot, kind, code, ev.y & 0x8000FFFFu);
+          continue;
+        }
+        if (l < 0 || l >= n_loci) continue;
+        uint32_t second = ev.y;
+        if (kind == GUAC_ALN_MISMATCH) {
+          second = s0_rel + ev.y;  // quality index relative to the tile's first base
+        } else if (kind == GUAC_ALN_DELETION && code == 4) {  // the deleted reference bases must exist (PE.scala:95)
+          const int nlen = (int)((ev.y >> 8) & 0xFF);
+          for (int k = 1; k <= nlen; ++k)
+            if (ref.at(t0 + l + k) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + l + k, r);
+        }
+        push_event(l, rl, slot, kind, code, second);
+      }
+      continue;
+    }
     // aligned segment: loci [lb, le) (tile coordinates, unclipped) hold read positions rp0..; 16 bases per step
     auto compare_segment = [&](int lb, int le, int rp0) {
       const int ca = max(lb, 0), cb = min(le, n_loci);

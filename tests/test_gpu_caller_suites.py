@@ -7,7 +7,7 @@ from tests.golden import fixtures
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("impl", ["tile", "gather"])
+@pytest.mark.parametrize("impl", ["tile", "gather", "stream"])
 @pytest.mark.parametrize("case", cases.SS_CASES, ids=[c[0] for c in cases.SS_CASES])
 def test_somatic_standard_caller_suite(gpu_ctx, case, impl):
     def run(batch, ref, ranges, params):
@@ -15,7 +15,7 @@ def test_somatic_standard_caller_suite(gpu_ctx, case, impl):
         gpu_ctx.upload_reads(batch)
         return gpu_ctx.somatic_standard(ranges, params)
 
-    gpu_ctx.set_option("ss_impl", 1 if impl == "gather" else 0)
+    gpu_ctx.set_option("ss_impl", {"tile": 0, "gather": 1, "stream": 2}[impl])
     try:
         cases.check_ss_case(case, run)
     finally:
@@ -42,13 +42,13 @@ def test_somatic_joint_caller_suite(gpu_ctx, fallback_mod):
         gpu_ctx.set_option("ss_force_fallback_mod", 0)
 
 
-@pytest.mark.parametrize("impl", ["tile", "gather"])
+@pytest.mark.parametrize("impl", ["tile", "gather", "stream"])
 @pytest.mark.parametrize("name", ["syn1fp", "complexvar", "simplefp"])
 def test_somatic_standard_caller_real_data_suite(gpu_ctx, name, impl):
     batch, ref, extra = fixtures.load("real_" + name)
     gpu_ctx.upload_reference(ref, batch.contig_names)
     gpu_ctx.upload_reads(batch)
-    gpu_ctx.set_option("ss_impl", 1 if impl == "gather" else 0)
+    gpu_ctx.set_option("ss_impl", {"tile": 0, "gather": 1, "stream": 2}[impl])
     try:
         cases.check_real_data_case(name, batch, ref, extra["positions"], lambda b, r, ranges, p: gpu_ctx.somatic_standard(ranges, p))
     finally:

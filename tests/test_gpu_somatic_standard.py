@@ -9,12 +9,12 @@ from oracle import oracle
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["tile", "gather", "tile+fallback"])
+@pytest.fixture(params=["tile", "gather", "tile+fallback", "stream", "stream+fallback"])
 def impl(request, gpu_ctx):
-    """Every parity case runs through the streaming tile kernel, the generic gather kernel, and the
-    tile kernel with every third tile forced through its fallback path."""
-    gpu_ctx.set_option("ss_impl", 1 if request.param == "gather" else 0)
-    gpu_ctx.set_option("ss_force_fallback_mod", 3 if request.param == "tile+fallback" else 0)
+    """Every parity case runs through the tile kernel, the generic gather kernel, the tile kernel with every third
+    tile forced through its fallback path, and the stream implementation (read pass as a kernel of its own)."""
+    gpu_ctx.set_option("ss_impl", {"gather": 1, "stream": 2, "stream+fallback": 2}.get(request.param, 0))
+    gpu_ctx.set_option("ss_force_fallback_mod", 3 if request.param.endswith("+fallback") else 0)
     yield request.param
     gpu_ctx.set_option("ss_impl", 0)
     gpu_ctx.set_option("ss_force_fallback_mod", 0)
@@ -56,9 +56,9 @@ def test_synthetic_tumor_normal(gpu_ctx, impl, seed, contig_len):
     want = oracle.somatic_standard(batch, ref, ranges, want_summary=True)
     assert len(want["calls"]) > 0
     assert_ss_equal(got, want)
-    if impl == "tile+fallback":
+    if impl.endswith("+fallback"):
         assert gpu_ctx.last_fallback_tiles > 0
-    elif impl == "tile":
+    elif impl in ("tile", "stream"):
         assert gpu_ctx.last_fallback_tiles == 0
 
 

@@ -4,6 +4,8 @@ from guacamole_b200.native import Context
 ctx = Context(0)
 L = 50_000_000
 ctx.synth_generate(L, (30, 60), (False, True), 3000)
+if len(sys.argv) > 1:
+    ctx.set_option("ss_impl", int(sys.argv[1]))
 for i in range(4):
     t=time.perf_counter(); out = ctx.somatic_standard([(0,0,L)]); dt=time.perf_counter()-t
-    print("step", i, dt*1e3, "ms kernel", ctx.last_kernel_ms()[0], "heavy", ctx.lib.guac_last_heavy_loci(ctx.ctx), "fallback", ctx.last_fallback_tiles, file=sys.stderr)
+    print("step", i, dt*1e3, "ms kernel", ctx.last_kernel_ms()[0], "heavy", ctx.lib.guac_last_heavy_loci(ctx.ctx), "fallback", ctx.last_fallback_tiles, "calls", len(out["calls"]), file=sys.stderr)
