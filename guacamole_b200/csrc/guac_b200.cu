@@ -78,7 +78,8 @@ struct guac_ctx {
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;
   double bound_tab_vaf = -1;
-  DevBuf b_bins, b_bin_count;  // stream path: per-read event slots and counts
+  DevBuf b_bins, b_bin_count, b_medium;  // stream path: per-read event slots and counts; list of multi-operator reads
+  int64_t n_medium = 0;
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
 };
@@ -390,7 +391,12 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   if (n > 0) {
     read_fast_flags_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>());
     read_headers_pack_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>(), ctx->b_hdr.as<uint4>());
-    ctx->launches += 2;
+    GUAC_TRY(ensure(ctx, ctx->b_medium, ((size_t)n + 2) * sizeof(int64_t)));  // [0] = count, then the list
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_medium.p, 0, sizeof(int64_t), ctx->stream));
+    medium_reads_list_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->b_rflags.as<uint8_t>(), n, ctx->b_medium.as<int64_t>() + 1,
+                                                                           ctx->b_medium.as<unsigned long long>());
+    CUDA_TRY(ctx, cudaMemcpyAsync(&ctx->n_medium, ctx->b_medium.p, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   }
@@ -465,7 +471,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_arena_used.p) cudaFree(ctx->b_arena_used.p);
   if (ctx->b_hdr.p) cudaFree(ctx->b_hdr.p);
   for (auto& b : ctx->asm_blocks) cudaFree(b.first);
-  for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count})
+  for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium})
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
     if (kv.second.ref2) cudaFree(kv.second.ref2);
@@ -828,8 +834,17 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
           SA.ref2 = it->second.ref2;
           SA.events = ctx->b_bins.as<uint2>();
           SA.n_events = ctx->b_bin_count.as<uint8_t>();
+          SA.list = nullptr;
+          SA.inline_medium = ctx->contig_spans.size() == 1 ? 0 : 1;
           ss_read_events_kernel<<<blocks_for(SA.read_hi - SA.read_lo, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
           ctx->launches += 1;
+          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {  // the multi-operator reads, densely
+            SA.list = ctx->b_medium.as<int64_t>() + 1;
+            SA.read_lo = 0;
+            SA.read_hi = ctx->n_medium;
+            ss_read_events_kernel<<<blocks_for(ctx->n_medium, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
+            ctx->launches += 1;
+          }
         }
         CUDA_TRY(ctx, cudaGetLastError());
         ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);

@@ -25,6 +25,16 @@ __global__ void ref2_pack_kernel(const uint8_t* __restrict__ bases, int64_t len,
   ref2[w] = v;
 }
 
+// Reads with several CIGAR operators (RF_MEDIUM but not RF_FAST), listed once per upload so that their longer walk runs
+// in full warps of its own instead of one lane in many warps of the single-operator reads.
+__global__ void medium_reads_list_kernel(const uint8_t* __restrict__ rflags, int64_t n, int64_t* __restrict__ list,
+                                         unsigned long long* __restrict__ count) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const uint8_t rf = rflags[r];
+  if ((rf & RF_MEDIUM) && !(rf & RF_FAST)) list[atomicAdd(count, 1ull)] = r;
+}
+
 constexpr int STREAM_EV_CAP = 8;  // event records kept per read; a read with more sends its tiles to the generic kernel
 
 struct StreamArgs {
@@ -34,6 +44,8 @@ struct StreamArgs {
   const uint32_t* ref2; // and its 2-bit copy
   uint2* events;        // [n_reads][STREAM_EV_CAP]
   uint8_t* n_events;    // [n_reads] (255: more than the cap)
+  int inline_medium;    // 1: no list launch follows (several contigs in the batch): walk multi-operator reads in place
+  const int64_t* list;  // non-null: the reads to visit (the multi-operator ones); null: reads [read_lo, read_hi), single-operator only
 };
 
 // Read-event record (per read, independent of the loci of the call):
@@ -45,10 +57,12 @@ __device__ __forceinline__ uint32_t pack_read_event(int off, int kind, int code)
 
 // One thread per read: the read's non-Match elements against the 2-bit reference.  No shared memory, no barrier, no atomic.
 __global__ void __launch_bounds__(256) ss_read_events_kernel(ReadsView R, const __grid_constant__ StreamArgs A) {
-  const int64_t r = A.read_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= A.read_hi) return;
+  const int64_t i = A.read_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.read_hi) return;
+  const int64_t r = A.list ? __ldg(A.list + i) : i;
   const uint4 hdr = __ldg(A.hdr + r);
   const uint8_t rf = (uint8_t)(hdr.y >> 24);
+  if (!A.list && !A.inline_medium && (rf & RF_MEDIUM) && !(rf & RF_FAST)) return;  // visited through the list by a launch of their own
   int n_ev = 0;
   uint2* mine = A.events + r * STREAM_EV_CAP;
   auto push = [&](int off, int kind, int code, uint32_t second) {
