@@ -249,7 +249,7 @@ def main():
         tj = json.load(open(tpath))
         traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": traffic_src, "kernel": "ss_tile_kernel<TileCfg<512>> (+ heavy-locus gather kernel)",
+                "traffic_source": traffic_src, "kernel": "ss_read_events_kernel + ss_tile_kernel<TileCfg<512>, 0, STREAM> (+ heavy-locus gather kernel): the per-locus kernels of one step",
                 "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes * loci_step, "algorithmic_bytes_per_locus": abytes,
                 "peak_source": peak_src}
 

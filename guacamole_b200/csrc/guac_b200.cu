@@ -73,7 +73,7 @@ struct guac_ctx {
   bool have_timing = false;
   int64_t timed_loci = 0;
   DevBuf b_nops, b_rflags, b_logtab, b_fallback;
-  int64_t opt_ss_impl = 0;            // 0 = streaming tile kernel (+ gather fallback), 1 = gather kernel only
+  int64_t opt_ss_impl = 2;            // 2 = stream (read pass + locus pass; the default), 0 = single tile kernel, 1 = gather kernel only
   int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;

@@ -251,11 +251,19 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   const uint4* hdrs = A.hdr + tile.read_lo;
   const uint32_t t0_lo = (uint32_t)t0;
   uint4 next_hdr = make_uint4(0, 0, 0, 0);
-  if (tid < (int)n_reads_tile) next_hdr = __ldg(hdrs + tid);
+  int next_cnt = 0;  // STREAM: the read's event count travels with its header
+  if (tid < (int)n_reads_tile) {
+    next_hdr = __ldg(hdrs + tid);
+    if (STREAM) next_cnt = (int)__ldg(A.ev_count + tile.read_lo + tid);
+  }
   for (int rl = tid; rl < (int)n_reads_tile; rl += CFG::THREADS) {
     const int64_t r = tile.read_lo + rl;
     const uint4 hdr = next_hdr;
-    if (rl + CFG::THREADS < (int)n_reads_tile) next_hdr = __ldg(hdrs + rl + CFG::THREADS);
+    const int cnt = next_cnt;
+    if (rl + CFG::THREADS < (int)n_reads_tile) {
+      next_hdr = __ldg(hdrs + rl + CFG::THREADS);
+      if (STREAM) next_cnt = (int)__ldg(A.ev_count + r + CFG::THREADS);
+    }
     const int smp = (int)((hdr.y >> 16) & 0xFF);
     const uint8_t rf = (uint8_t)(hdr.y >> 24);
     if (MODE == 2 ? smp >= P.n_samples : (smp != P.normal_sample && smp != P.tumor_sample)) continue;
@@ -281,7 +289,6 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     if (STREAM) {  // the read was compared by ss_read_events_kernel: take the events that fall inside the tile
-      const int cnt = (int)__ldg(A.ev_count + r);
       if (cnt > 8) {
         S.overflow = 1;
         continue;

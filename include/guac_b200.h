@@ -461,7 +461,8 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
 /* CUDA stream (cudaStream_t) every kernel of this context is launched on. */
 void* guac_stream(guac_ctx* ctx);
 /* Implementation switches for tests and A/B measurements:
- *   "ss_impl"               0 = streaming tile kernel with gather fallback (default), 1 = gather kernel only
+ *   "ss_impl"               somatic-standard: 2 = read pass + locus pass as two kernels (default), 0 = both in one tile
+ *                           kernel, 1 = generic gather kernel only; all three fall back to the gather kernel per tile
  *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook) */
 int guac_set_option(guac_ctx* ctx, const char* name, int64_t value);
 /* Tiles of the most recent guac_somatic_standard call that took the fallback path. */

@@ -19,7 +19,7 @@ def test_somatic_standard_caller_suite(gpu_ctx, case, impl):
     try:
         cases.check_ss_case(case, run)
     finally:
-        gpu_ctx.set_option("ss_impl", 0)
+        gpu_ctx.set_option("ss_impl", 2)
 
 
 def joint_run(gpu_ctx):
@@ -52,7 +52,7 @@ def test_somatic_standard_caller_real_data_suite(gpu_ctx, name, impl):
     try:
         cases.check_real_data_case(name, batch, ref, extra["positions"], lambda b, r, ranges, p: gpu_ctx.somatic_standard(ranges, p))
     finally:
-        gpu_ctx.set_option("ss_impl", 0)
+        gpu_ctx.set_option("ss_impl", 2)
 
 
 @pytest.mark.parametrize("case", cases.ALLELE_EVIDENCE_CASES, ids=["all reads support", "one read supports"])

@@ -29,17 +29,17 @@ def check_pileups(ctx, batch, ref, ranges):
     return gl
 
 
-@pytest.mark.parametrize("impl", ["tile", "gather"])
+@pytest.mark.parametrize("impl", ["tile", "gather", "stream"])
 def test_tough_golden_vcf_on_gpu(gpu_ctx, impl):
     batch, ref, extra = fixtures.load("tough")
-    gpu_ctx.set_option("ss_impl", 1 if impl == "gather" else 0)
+    gpu_ctx.set_option("ss_impl", {"tile": 0, "gather": 1, "stream": 2}[impl])
     try:
         gpu_ctx.upload_reference(ref, batch.contig_names)
         gpu_ctx.upload_reads(batch)
         ranges = ss.covered_ranges(batch)
         out = gpu_ctx.somatic_standard(ranges, want_summary=True)
     finally:
-        gpu_ctx.set_option("ss_impl", 0)
+        gpu_ctx.set_option("ss_impl", 2)
     rows = ss.vcf_rows(out, batch.contig_names, ss.somatic_genotype_filter(out["calls"]))
     assert rows == [str(x) for x in extra["golden_vcf"]]
     want = oracle.somatic_standard(batch, ref, ranges, want_summary=True)

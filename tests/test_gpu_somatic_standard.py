@@ -16,7 +16,7 @@ def impl(request, gpu_ctx):
     gpu_ctx.set_option("ss_impl", {"gather": 1, "stream": 2, "stream+fallback": 2}.get(request.param, 0))
     gpu_ctx.set_option("ss_force_fallback_mod", 3 if request.param.endswith("+fallback") else 0)
     yield request.param
-    gpu_ctx.set_option("ss_impl", 0)
+    gpu_ctx.set_option("ss_impl", 2)  # the default
     gpu_ctx.set_option("ss_force_fallback_mod", 0)
 
 EV_INT = ["read_depth", "allele_read_depth", "forward_depth", "allele_forward_depth"]
