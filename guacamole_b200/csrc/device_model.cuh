@@ -54,6 +54,8 @@ struct Tile {
   int64_t read_hi;
   int32_t ref_index; // index into the RefView table
   int32_t _pad;
+  uint64_t seq_base; // sequence offset of read_lo's first base, and of read_hi's (tiles built by build_tiles_kernel only)
+  uint64_t seq_end;
 };
 
 enum : int { OPC_M = 0, OPC_I = 1, OPC_D = 2, OPC_N = 3, OPC_S = 4, OPC_H = 5, OPC_P = 6, OPC_EQ = 7, OPC_X = 8 };

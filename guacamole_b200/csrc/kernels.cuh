@@ -60,6 +60,8 @@ __global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ra
     if (__ldg(R.runmax_key + m) > key) b = m; else a = m + 1;
   }
   tl.read_lo = a;
+  tl.seq_base = tl.read_hi > tl.read_lo ? __ldg(R.seq_off + tl.read_lo) : 0;
+  tl.seq_end = tl.read_hi > tl.read_lo ? __ldg(R.seq_off + tl.read_hi) : 0;
   tiles[t] = tl;
 }
 

@@ -192,8 +192,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
 
   bool too_big = n_reads_tile > CFG::R_MAX;
   if (A.force_fallback_mod > 0 && blockIdx.x % A.force_fallback_mod == 0) too_big = true;  // test hook
-  const uint64_t seq_base = n_reads_tile > 0 ? __ldg(R.seq_off + tile.read_lo) : 0;
-  if (!too_big && n_reads_tile > 0) too_big = (__ldg(R.seq_off + tile.read_hi) - seq_base) >= (1ull << 31);
+  const uint64_t seq_base = tile.seq_base;  // filled in by build_tiles_kernel
+  if (!too_big && n_reads_tile > 0) too_big = (tile.seq_end - seq_base) >= (1ull << 31);
   if (too_big) {  // uniform across the CTA
     if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
     return;
@@ -489,7 +489,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const int64_t slot = tile.slot0 + l, x = t0 + l;
     A.visited[slot] = dN + dT > 0 ? 1 : 0;
     my_visited += dN + dT > 0;
-    if (MODE != 2 && dN + dT > 0 && ref.at(x) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x, -1);
+    // (a tile with a missing reference base never gets here: it went to the generic kernel, which reports the error)
     bool candidate;
     if (MODE == 0) {  // early-outs (SomaticStandardCaller.scala:164-172)
       candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
@@ -518,6 +518,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         t.read_hi = tile.read_hi;
         t.ref_index = tile.ref_index;
         t._pad = 0;
+        t.seq_base = t.seq_end = 0;
         A.heavy[h] = t;
       }
       flags = 1;
@@ -641,6 +642,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
           t.read_hi = tile.read_hi;
           t.ref_index = tile.ref_index;
           t._pad = 0;
+          t.seq_base = t.seq_end = 0;
+        t.seq_base = t.seq_end = 0;
           A.heavy[h] = t;
         }
         continue;  // the heavy kernel writes this locus's summary
