@@ -43,6 +43,8 @@ struct ContigDev {
   uint8_t* bases = nullptr;
   int ref_index = -1;
   uint32_t* ref2 = nullptr;  // 2-bit copy for the stream path (16 loci per word), rebuilt when the window changes
+  uint32_t* refbad = nullptr;  // one bit per 16 loci: the group holds a base that is not A C G T (or is missing)
+  size_t ref2_words = 0;
   bool ref2_dirty = true;
 };
 
@@ -191,7 +193,10 @@ int device_scan(guac_ctx* ctx, const TIn* in, int64_t* out, int64_t n, Op op, in
   return GUAC_OK;
 }
 
+int sync_ref2(guac_ctx* ctx);
+
 int sync_refs(guac_ctx* ctx) {
+  GUAC_TRY(sync_ref2(ctx));  // 2-bit copies and bad-group bitmaps of the windows that changed
   if (!ctx->refs_dirty) return GUAC_OK;
   std::vector<RefView> v;
   int idx = 0;
@@ -201,6 +206,7 @@ int sync_refs(guac_ctx* ctx) {
     r.bases = kv.second.bases;
     r.offset = kv.second.offset;
     r.len = kv.second.len;
+    r.bad = kv.second.refbad;
     v.push_back(r);
   }
   GUAC_TRY(upload(ctx, ctx->d_refs, v.data(), v.size()));
@@ -268,18 +274,23 @@ int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& pla
 int sync_ref2(guac_ctx* ctx) {
   for (auto& kv : ctx->contigs) {
     ContigDev& c = kv.second;
-    if (!c.ref2_dirty && c.ref2) continue;
-    if (c.ref2) CUDA_TRY(ctx, cudaFree(c.ref2));
-    c.ref2 = nullptr;
     const size_t words = (size_t)(c.len / 16) + 4;  // read-ahead of the compare loop
-    cudaError_t e = cudaMalloc(&c.ref2, words * sizeof(uint32_t));
-    if (e != cudaSuccess) {
-      (void)cudaGetLastError();
-      return fail(ctx, GUAC_E_OOM, "cudaMalloc failed for the 2-bit reference");
+    if (!c.ref2_dirty && c.ref2 && c.ref2_words == words) continue;
+    if (!c.ref2 || c.ref2_words != words) {  // the allocation is kept while the window keeps its size: RefView tables stay valid
+      if (c.ref2) CUDA_TRY(ctx, cudaFree(c.ref2));
+      if (c.refbad) CUDA_TRY(ctx, cudaFree(c.refbad));
+      c.ref2 = c.refbad = nullptr;
+      if (cudaMalloc(&c.ref2, words * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&c.refbad, (words / 32 + 4) * sizeof(uint32_t)) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(ctx, GUAC_E_OOM, "cudaMalloc failed for the 2-bit reference");
+      }
+      c.ref2_words = words;
+      ctx->refs_dirty = true;
     }
     CUDA_TRY(ctx, cudaMemsetAsync(c.ref2, 0, words * sizeof(uint32_t), ctx->stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(c.refbad, 0, (words / 32 + 4) * sizeof(uint32_t), ctx->stream));
     if (c.len > 0) {
-      ref2_pack_kernel<<<blocks_for((c.len + 15) / 16, 256), 256, 0, ctx->stream>>>(c.bases, c.len, c.ref2);
+      ref2_pack_kernel<<<blocks_for((c.len + 15) / 16, 256), 256, 0, ctx->stream>>>(c.bases, c.len, c.ref2, c.refbad);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
     }
@@ -475,6 +486,8 @@ void guac_ctx_destroy(guac_ctx* ctx) {
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
     if (kv.second.ref2) cudaFree(kv.second.ref2);
+  for (auto& kv : ctx->contigs)
+    if (kv.second.refbad) cudaFree(kv.second.refbad);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);
@@ -831,6 +844,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
           SA.ref.bases = it->second.bases;
           SA.ref.offset = it->second.offset;
           SA.ref.len = it->second.len;
+          SA.ref.bad = it->second.refbad;
           SA.ref2 = it->second.ref2;
           SA.events = ctx->b_bins.as<uint2>();
           SA.n_events = ctx->b_bin_count.as<uint8_t>();
@@ -1779,6 +1793,7 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
   ref.bases = d_ref_bases;
   ref.offset = ref_offset;
   ref.len = ref_len;
+  ref.bad = nullptr;
   RangeDev rg;
   rg.start = range_start;
   rg.end = range_end;

@@ -13,16 +13,19 @@ namespace guac {
 
 // ASCII reference window -> 2 bits per locus, 16 loci per word; anything but A C G T packs as 0 (tiles holding such a
 // locus are handed to the generic kernel by the locus pass, so the value never matters).
-__global__ void ref2_pack_kernel(const uint8_t* __restrict__ bases, int64_t len, uint32_t* __restrict__ ref2) {
+__global__ void ref2_pack_kernel(const uint8_t* __restrict__ bases, int64_t len, uint32_t* __restrict__ ref2, uint32_t* __restrict__ bad) {
   const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (16 * w >= len) return;
   uint32_t v = 0;
+  bool any_bad = false;
   for (int k = 0; k < 16 && 16 * w + k < len; ++k) {
     const uint8_t b = bases[16 * w + k];
     const uint32_t d = (uint32_t)b - 65u;
     if (d < 20u && ((0x80045u >> d) & 1u)) v |= (((uint32_t)(b >> 1) ^ (uint32_t)(b >> 2)) & 3u) << (2 * k);
+    else any_bad = true;
   }
   ref2[w] = v;
+  if (any_bad) atomicOr(bad + (w >> 5), 1u << (w & 31));  // one bit per 16-locus group
 }
 
 // Reads with several CIGAR operators (RF_MEDIUM but not RF_FAST), listed once per upload so that their longer walk runs

@@ -213,15 +213,28 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   const long long rel0 = (long long)t0 - (long long)ref.offset;
   const int l_min = (int)min(max(-rel0, 0ll), (long long)n_loci), l_max = (int)max(min((long long)ref.len - rel0, (long long)n_loci), 0ll);
   const uint8_t* ref_tile = ref.bases + rel0;
-  for (int base = 0; base < TL; base += CFG::THREADS) {
+  if (STREAM) {
+    // the read pass already compared against the reference; here only "is every base of the tile A C G T" matters, and
+    // one bit per 16 loci (ref.bad, built with the 2-bit copy) answers it from two or three words
+    if (tid == 0) {
+      bool bad = l_min > 0 || l_max < n_loci;  // part of the tile lies outside the reference window
+      if (!bad) {
+        const long long g0 = rel0 >> 4, g1 = (rel0 + n_loci - 1) >> 4;
+        for (long long w = g0 >> 5; w <= (g1 >> 5) && !bad; ++w) {
+          uint32_t bits = __ldg(ref.bad + w);
+          if (w == (g0 >> 5)) bits &= 0xFFFFFFFFu << (g0 & 31);
+          if (w == (g1 >> 5)) bits &= 0xFFFFFFFFu >> (31 - (g1 & 31));
+          bad = bits != 0;
+        }
+      }
+      if (bad) S.ref_has_mask = 1;
+    }
+  }
+  for (int base = 0; !STREAM && base < TL; base += CFG::THREADS) {
     const int l = base + tid;
     const uint8_t b = (l >= l_min && l < l_max) ? __ldg(ref_tile + l) : (l < n_loci ? (uint8_t)0 : (uint8_t)'A');
     const uint32_t d = (uint32_t)b - 65u;  // A C G T are 65 + {0, 2, 6, 19}; their 2-bit code is ((b >> 1) ^ (b >> 2)) & 3
     const bool acgt = d < 20u && ((0x80045u >> d) & 1u);
-    if (STREAM) {  // the compare already happened in the read pass: only the not-ACGT test is needed here
-      if (__any_sync(FULL, !acgt) && lane == 0) S.ref_has_mask = 1;
-      continue;
-    }
     const int c = acgt ? (int)(((b >> 1) ^ (b >> 2)) & 3u) : 4;
     const uint32_t bits = c < 4 ? (uint32_t)c << (2 * (lane & 15)) : 0u;
     const uint32_t lo = __reduce_or_sync(FULL, lane < 16 ? bits : 0u);
