@@ -402,12 +402,26 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   if (n > 0) {
     read_fast_flags_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>());
     read_headers_pack_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>(), ctx->b_hdr.as<uint4>());
-    GUAC_TRY(ensure(ctx, ctx->b_medium, ((size_t)n + 2) * sizeof(int64_t)));  // [0] = count, then the list
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_medium.p, 0, sizeof(int64_t), ctx->stream));
-    medium_reads_list_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->b_rflags.as<uint8_t>(), n, ctx->b_medium.as<int64_t>() + 1,
-                                                                           ctx->b_medium.as<unsigned long long>());
-    CUDA_TRY(ctx, cudaMemcpyAsync(&ctx->n_medium, ctx->b_medium.p, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    ctx->launches += 3;
+    {  // the multi-operator reads, listed in read order: flags -> exclusive scan -> scatter
+      DevBuf d_flag, d_off;
+      GUAC_TRY(ensure(ctx, d_flag, (size_t)n + 16));
+      GUAC_TRY(ensure(ctx, d_off, ((size_t)n + 2) * sizeof(int64_t)));
+      medium_reads_flag_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->b_rflags.as<uint8_t>(), n, d_flag.as<uint8_t>());
+      int st = device_scan<true, uint8_t>(ctx, d_flag.as<uint8_t>(), d_off.as<int64_t>(), n, OpSum(), d_off.as<int64_t>() + n);
+      if (st == GUAC_OK) {
+        cudaMemcpyAsync(&ctx->n_medium, d_off.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+        st = ensure(ctx, ctx->b_medium, ((size_t)ctx->n_medium + 2) * sizeof(int64_t));
+      }
+      if (st == GUAC_OK)
+        medium_reads_scatter_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(d_flag.as<uint8_t>(), d_off.as<int64_t>(), n,
+                                                                              ctx->b_medium.as<int64_t>());
+      cudaStreamSynchronize(ctx->stream);
+      cudaFree(d_flag.p);
+      cudaFree(d_off.p);
+      GUAC_TRY(st);
+    }
+    ctx->launches += 7;
     CUDA_TRY(ctx, cudaGetLastError());
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   }
@@ -853,7 +867,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
           ss_read_events_kernel<<<blocks_for(SA.read_hi - SA.read_lo, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
           ctx->launches += 1;
           if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {  // the multi-operator reads, densely
-            SA.list = ctx->b_medium.as<int64_t>() + 1;
+            SA.list = ctx->b_medium.as<int64_t>();
             SA.read_lo = 0;
             SA.read_hi = ctx->n_medium;
             ss_read_events_kernel<<<blocks_for(ctx->n_medium, 256), 256, 0, ctx->stream>>>(ctx->R, SA);

@@ -30,12 +30,17 @@ __global__ void ref2_pack_kernel(const uint8_t* __restrict__ bases, int64_t len,
 
 // Reads with several CIGAR operators (RF_MEDIUM but not RF_FAST), listed once per upload so that their longer walk runs
 // in full warps of its own instead of one lane in many warps of the single-operator reads.
-__global__ void medium_reads_list_kernel(const uint8_t* __restrict__ rflags, int64_t n, int64_t* __restrict__ list,
-                                         unsigned long long* __restrict__ count) {
+__global__ void medium_reads_flag_kernel(const uint8_t* __restrict__ rflags, int64_t n, uint8_t* __restrict__ flag) {
   const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= n) return;
   const uint8_t rf = rflags[r];
-  if ((rf & RF_MEDIUM) && !(rf & RF_FAST)) list[atomicAdd(count, 1ull)] = r;
+  flag[r] = ((rf & RF_MEDIUM) && !(rf & RF_FAST)) ? 1 : 0;
+}
+// flag + exclusive scan -> the list in ascending read order (neighbouring list entries touch neighbouring memory)
+__global__ void medium_reads_scatter_kernel(const uint8_t* __restrict__ flag, const int64_t* __restrict__ offset, int64_t n,
+                                            int64_t* __restrict__ list) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n && flag[r]) list[offset[r]] = r;
 }
 
 constexpr int STREAM_EV_CAP = 8;  // event records kept per read; a read with more sends its tiles to the generic kernel
