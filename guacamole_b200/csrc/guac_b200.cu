@@ -80,6 +80,8 @@ struct guac_ctx {
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;
   double bound_tab_vaf = -1;
+  cudaStream_t stream2 = nullptr;  // side stream of the stream path
+  cudaEvent_t fork = nullptr, join = nullptr;
   DevBuf b_bins, b_bin_count, b_medium;  // stream path: per-read event slots and counts; list of multi-operator reads
   int64_t n_medium = 0;
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
@@ -496,6 +498,9 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->b_arena_used.p) cudaFree(ctx->b_arena_used.p);
   if (ctx->b_hdr.p) cudaFree(ctx->b_hdr.p);
   for (auto& b : ctx->asm_blocks) cudaFree(b.first);
+  if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+  if (ctx->fork) cudaEventDestroy(ctx->fork);
+  if (ctx->join) cudaEventDestroy(ctx->join);
   for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium})
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
@@ -864,15 +869,27 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
           SA.n_events = ctx->b_bin_count.as<uint8_t>();
           SA.list = nullptr;
           SA.inline_medium = ctx->contig_spans.size() == 1 ? 0 : 1;
-          ss_read_events_kernel<<<blocks_for(SA.read_hi - SA.read_lo, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
-          ctx->launches += 1;
-          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {  // the multi-operator reads, densely
-            SA.list = ctx->b_medium.as<int64_t>();
-            SA.read_lo = 0;
-            SA.read_hi = ctx->n_medium;
-            ss_read_events_kernel<<<blocks_for(ctx->n_medium, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
+          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {
+            // the multi-operator reads, densely: a latency-bound launch (scattered reads), run on a second stream under
+            // the bandwidth-bound launch over the single-operator reads; the two write disjoint slots
+            if (!ctx->stream2) {
+              CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+              CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming));
+              CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->join, cudaEventDisableTiming));
+            }
+            StreamArgs SL = SA;
+            SL.list = ctx->b_medium.as<int64_t>();
+            SL.read_lo = 0;
+            SL.read_hi = ctx->n_medium;
+            CUDA_TRY(ctx, cudaEventRecord(ctx->fork, ctx->stream));
+            CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->fork, 0));
+            ss_read_events_kernel<<<blocks_for(ctx->n_medium, 256), 256, 0, ctx->stream2>>>(ctx->R, SL);
+            CUDA_TRY(ctx, cudaEventRecord(ctx->join, ctx->stream2));
             ctx->launches += 1;
           }
+          ss_read_events_kernel<<<blocks_for(SA.read_hi - SA.read_lo, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
+          ctx->launches += 1;
+          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->join, 0));
         }
         CUDA_TRY(ctx, cudaGetLastError());
         ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
