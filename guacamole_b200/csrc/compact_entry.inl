@@ -20,14 +20,10 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   }
   if (n > 0 && (b->n_contig_runs == 0 || b->run_first_read[b->n_contig_runs] != n))
     return fail(ctx, GUAC_E_INVALID_INPUT, "contig runs do not cover the batch");
-  DevBuf d_len, d_ops, d_runs_c, d_runs_f, d_tmp, d_qpacked, d_bad;
-  struct Free {
-    std::vector<DevBuf*> v;
-    ~Free() {
-      for (DevBuf* d : v)
-        if (d->p) cudaFree(d->p);
-    }
-  } fr{{&d_len, &d_ops, &d_runs_c, &d_runs_f, &d_tmp, &d_qpacked, &d_bad}};
+  // scratch kept in the context: a cudaMalloc / cudaFree pair per column and call costs more than the kernels here
+  DevBuf &d_len = ctx->u_len, &d_ops = ctx->u_ops, &d_runs_c = ctx->u_runs_c, &d_runs_f = ctx->u_runs_f, &d_tmp = ctx->u_tmp,
+         &d_qpacked = ctx->u_qpacked, &d_bad = ctx->u_bad;
+  GUAC_TRY(side_stream(ctx));
   GUAC_TRY(upload(ctx, ctx->b_start, b->start, (size_t)n));
   GUAC_TRY(upload(ctx, d_len, b->read_len, (size_t)n));
   GUAC_TRY(upload(ctx, d_ops, b->n_cigar_ops, (size_t)n));
@@ -67,7 +63,7 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_cigar_off.p, 0, sizeof(uint32_t), ctx->stream));
   }
   GUAC_TRY(upload(ctx, ctx->b_cigar, b->cigar, (size_t)n_cigar));
-  GUAC_TRY(upload(ctx, ctx->b_bases2, b->bases2, (size_t)((n_bases + 3) / 4), 64));
+  GUAC_TRY(ensure(ctx, ctx->b_bases2, (size_t)((n_bases + 3) / 4) + 64 + 16));
   GUAC_TRY(ensure(ctx, ctx->b_nmask, (size_t)((n_bases + 7) / 8) + 16));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_nmask.p, 0, (size_t)((n_bases + 7) / 8) + 16, ctx->stream));
   if (b->n_exc > 0) {
@@ -75,31 +71,54 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
                                                                                              ctx->b_nmask.as<uint8_t>());
     ctx->launches += 1;
   }
+  // The qualities travel before the bases: nothing of the on-device preparation below (quality expansion, read ends,
+  // flags, headers, the multi-operator list) reads a base, so the copy of the bases, queued on the second stream
+  // behind the copy of the qualities, runs under those kernels.
   if (b->qual_bits == 8) {
     GUAC_TRY(upload(ctx, ctx->b_qual, b->qual, (size_t)n_bases));
   } else {
     const int per_byte = 8 / b->qual_bits;
     GUAC_TRY(upload(ctx, d_qpacked, b->qual, (size_t)((n_bases + per_byte - 1) / per_byte), 32));
     GUAC_TRY(ensure(ctx, ctx->b_qual, (size_t)n_bases + 32));
-    if (n_bases > 0) {
-      compact::QualTable T;
-      std::memcpy(T.q, b->qual_table, 16);
-      const unsigned blocks = blocks_for((int64_t)((n_bases + 15) / 16), 256);
-      if (b->qual_bits == 4)
-        compact::expand_qual_kernel<4><<<blocks, 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
-      else
-        compact::expand_qual_kernel<2><<<blocks, 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
-      ctx->launches += 1;
-    }
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ctx->fork, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->fork, 0));
+  if (n_bases > 0)
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->b_bases2.p, b->bases2, (size_t)((n_bases + 3) / 4), cudaMemcpyHostToDevice, ctx->stream2));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->join, ctx->stream2));
+  if (b->qual_bits != 8 && n_bases > 0) {
+    compact::QualTable T;
+    std::memcpy(T.q, b->qual_table, 16);
+    const unsigned blocks = blocks_for((int64_t)((n_bases + 15) / 16), 256);
+    if (b->qual_bits == 4)
+      compact::expand_qual_kernel<4><<<blocks, 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
+    else
+      compact::expand_qual_kernel<2><<<blocks, 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
+    ctx->launches += 1;
   }
   CUDA_TRY(ctx, cudaGetLastError());
   int bad = 0;
   CUDA_TRY(ctx, cudaMemcpyAsync(&bad, d_bad.p, sizeof bad, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  if (bad & 1) return fail(ctx, GUAC_E_INVALID_INPUT, "Regions must be sorted by start locus");
-  if (bad & 2) return fail(ctx, GUAC_E_INVALID_INPUT, "sample_id >= n_samples");
-  if (bad & 4) return fail(ctx, GUAC_E_INVALID_INPUT, "read start out of range");
-  return finish_reads(ctx, n, b->n_samples, b->n_exc);
+  int st = GUAC_OK;
+  {
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) {
+      ctx->err = std::string("CUDA error: ") + cudaGetErrorString(e);
+      st = GUAC_E_CUDA;
+    }
+  }
+  if (st == GUAC_OK && (bad & 1)) st = fail(ctx, GUAC_E_INVALID_INPUT, "Regions must be sorted by start locus");
+  if (st == GUAC_OK && (bad & 2)) st = fail(ctx, GUAC_E_INVALID_INPUT, "sample_id >= n_samples");
+  if (st == GUAC_OK && (bad & 4)) st = fail(ctx, GUAC_E_INVALID_INPUT, "read start out of range");
+  if (st == GUAC_OK) st = finish_reads(ctx, n, b->n_samples, b->n_exc);
+  // the caller's buffers may go away after return, whatever the outcome: the copy of the bases must have ended
+  const cudaError_t e2 = cudaEventSynchronize(ctx->join);
+  if (st == GUAC_OK && e2 != cudaSuccess) {
+    ctx->err = std::string("CUDA error: ") + cudaGetErrorString(e2);
+    ctx->have_reads = false;
+    st = GUAC_E_CUDA;
+  }
+  return st;
 }
 
 int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out) {

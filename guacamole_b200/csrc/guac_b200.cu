@@ -80,10 +80,11 @@ struct guac_ctx {
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;
   double bound_tab_vaf = -1;
-  cudaStream_t stream2 = nullptr;  // side stream of the stream path
+  cudaStream_t stream2 = nullptr;  // second stream: the copy of the bases in guac_reads_upload_compact
   cudaEvent_t fork = nullptr, join = nullptr;
   DevBuf b_bins, b_bin_count, b_medium;  // stream path: per-read event slots and counts; list of multi-operator reads
   int64_t n_medium = 0;
+  DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
 };
@@ -369,6 +370,15 @@ int compact_visited(guac_ctx* ctx, const Plan& plan, int skip_empty, int64_t& n_
 }
 
 // Derives end / running-max keys and publishes the device view (shared by upload and synth).
+// The context's second stream with its fork / join events, made on first use.
+int side_stream(guac_ctx* ctx) {
+  if (ctx->stream2) return GUAC_OK;
+  CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+  CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming));
+  CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->join, cudaEventDisableTiming));
+  return GUAC_OK;
+}
+
 int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   GUAC_TRY(ensure(ctx, ctx->b_end, (size_t)(n + 1) * sizeof(int64_t)));
   GUAC_TRY(ensure(ctx, ctx->b_key, (size_t)(n + 1) * sizeof(int64_t)));
@@ -405,23 +415,17 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
     read_fast_flags_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>());
     read_headers_pack_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>(), ctx->b_hdr.as<uint4>());
     {  // the multi-operator reads, listed in read order: flags -> exclusive scan -> scatter
-      DevBuf d_flag, d_off;
+      DevBuf& d_flag = ctx->u_flag;
+      DevBuf& d_off = ctx->u_off;
       GUAC_TRY(ensure(ctx, d_flag, (size_t)n + 16));
       GUAC_TRY(ensure(ctx, d_off, ((size_t)n + 2) * sizeof(int64_t)));
       medium_reads_flag_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(ctx->b_rflags.as<uint8_t>(), n, d_flag.as<uint8_t>());
-      int st = device_scan<true, uint8_t>(ctx, d_flag.as<uint8_t>(), d_off.as<int64_t>(), n, OpSum(), d_off.as<int64_t>() + n);
-      if (st == GUAC_OK) {
-        cudaMemcpyAsync(&ctx->n_medium, d_off.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream);
-        cudaStreamSynchronize(ctx->stream);
-        st = ensure(ctx, ctx->b_medium, ((size_t)ctx->n_medium + 2) * sizeof(int64_t));
-      }
-      if (st == GUAC_OK)
-        medium_reads_scatter_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(d_flag.as<uint8_t>(), d_off.as<int64_t>(), n,
-                                                                              ctx->b_medium.as<int64_t>());
-      cudaStreamSynchronize(ctx->stream);
-      cudaFree(d_flag.p);
-      cudaFree(d_off.p);
-      GUAC_TRY(st);
+      GUAC_TRY((device_scan<true, uint8_t>(ctx, d_flag.as<uint8_t>(), d_off.as<int64_t>(), n, OpSum(), d_off.as<int64_t>() + n)));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&ctx->n_medium, d_off.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+      GUAC_TRY(ensure(ctx, ctx->b_medium, ((size_t)ctx->n_medium + 2) * sizeof(int64_t)));
+      medium_reads_scatter_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(d_flag.as<uint8_t>(), d_off.as<int64_t>(), n,
+                                                                            ctx->b_medium.as<int64_t>());
     }
     ctx->launches += 7;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -501,7 +505,8 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
   if (ctx->fork) cudaEventDestroy(ctx->fork);
   if (ctx->join) cudaEventDestroy(ctx->join);
-  for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium})
+  for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
+                    &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off})
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
     if (kv.second.ref2) cudaFree(kv.second.ref2);
@@ -868,28 +873,19 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
           SA.events = ctx->b_bins.as<uint2>();
           SA.n_events = ctx->b_bin_count.as<uint8_t>();
           SA.list = nullptr;
+          SA.n_list = 0;
+          SA.list_blocks = SA.list_period = 0;
           SA.inline_medium = ctx->contig_spans.size() == 1 ? 0 : 1;
-          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {
-            // the multi-operator reads, densely: a latency-bound launch (scattered reads), run on a second stream under
-            // the bandwidth-bound launch over the single-operator reads; the two write disjoint slots
-            if (!ctx->stream2) {
-              CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
-              CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming));
-              CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->join, cudaEventDisableTiming));
-            }
-            StreamArgs SL = SA;
-            SL.list = ctx->b_medium.as<int64_t>();
-            SL.read_lo = 0;
-            SL.read_hi = ctx->n_medium;
-            CUDA_TRY(ctx, cudaEventRecord(ctx->fork, ctx->stream));
-            CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->fork, 0));
-            ss_read_events_kernel<<<blocks_for(ctx->n_medium, 256), 256, 0, ctx->stream2>>>(ctx->R, SL);
-            CUDA_TRY(ctx, cudaEventRecord(ctx->join, ctx->stream2));
-            ctx->launches += 1;
+          unsigned blocks = blocks_for(SA.read_hi - SA.read_lo, 256);
+          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {  // the multi-operator reads ride in the same launch
+            SA.list = ctx->b_medium.as<int64_t>();
+            SA.n_list = ctx->n_medium;
+            SA.list_blocks = blocks_for(ctx->n_medium, 256);
+            SA.list_period = std::max(1u, blocks / SA.list_blocks) + 1;
+            blocks += SA.list_blocks;
           }
-          ss_read_events_kernel<<<blocks_for(SA.read_hi - SA.read_lo, 256), 256, 0, ctx->stream>>>(ctx->R, SA);
+          ss_read_events_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->R, SA);
           ctx->launches += 1;
-          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->join, 0));
         }
         CUDA_TRY(ctx, cudaGetLastError());
         ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
@@ -899,6 +895,15 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       }
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
+      // loci that need the full likelihood: one warp each.  Their number stays on the device: the launch is sized for a
+      // full machine and strides over the list, so no host round trip separates it from the locus pass.
+      somatic_standard_kernel<<<(unsigned)std::min<int64_t>(blocks_for(max_heavy, WARPS_PER_CTA), 148 * 8), CTA_THREADS, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, max_heavy, 1, P, ctx->b_visited.as<uint8_t>(),
+          ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls, nullptr,
+          ctx->b_err.as<DeviceError>(), heavy_count);
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+      cudaEventRecord(ctx->ev1, ctx->stream);
       int counts[2] = {0, 0};
       CUDA_TRY(ctx, cudaMemcpyAsync(&counts[0], fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
       CUDA_TRY(ctx, cudaMemcpyAsync(&counts[1], heavy_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
@@ -915,14 +920,6 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         ctx->opt_ss_impl = impl;
         return st;
       }
-      if (n_heavy > 0) {  // loci that need the full likelihood: one warp each
-        somatic_standard_kernel<<<blocks_for(n_heavy, WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
-            ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, n_heavy, 1, P, ctx->b_visited.as<uint8_t>(),
-            ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
-            nullptr, ctx->b_err.as<DeviceError>());
-        ctx->launches += 1;
-        CUDA_TRY(ctx, cudaGetLastError());
-      }
       if (n_fb > 0) {  // tiles beyond a shared-memory capacity: generic kernel, still on the GPU
         somatic_standard_kernel<<<(unsigned)n_fb, CTA_THREADS, 0, ctx->stream>>>(
             ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, n_fb, 0, P, ctx->b_visited.as<uint8_t>(),
@@ -930,8 +927,8 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
             visited_count, ctx->b_err.as<DeviceError>());
         ctx->launches += 1;
         CUDA_TRY(ctx, cudaGetLastError());
+        cudaEventRecord(ctx->ev1, ctx->stream);  // the timed span then ends here
       }
-      cudaEventRecord(ctx->ev1, ctx->stream);
     } else {
       cudaEventRecord(ctx->ev0, ctx->stream);
       somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(

@@ -258,19 +258,50 @@ __device__ __forceinline__ void log_normalize2(double a, double b, double& na, d
   nb = b - sm;
 }
 
+
+// First index in [lo, hi) where the monotone predicate turns true (hi if it never does), by the whole warp: every round
+// the lanes probe 32 evenly spaced indices and one ballot narrows the bracket 32-fold.
+template <class Pred>
+__device__ __forceinline__ int64_t warp_partition_point(int64_t lo, int64_t hi, int lane, Pred pred) {
+  while (lo < hi) {
+    const int64_t step = (hi - lo + 31) >> 5;
+    const int64_t i = lo + lane * step;
+    const unsigned m = __ballot_sync(0xffffffffu, i >= hi || pred(i));
+    if (m & 1u) return lo;
+    if (m == 0) {
+      lo += 31 * step + 1;
+    } else {
+      const int L = __ffs(m) - 1;
+      hi = min(hi, lo + L * step);
+      lo += (L - 1) * step + 1;
+    }
+  }
+  return lo;
+}
+
 __global__ void __launch_bounds__(CTA_THREADS)
 somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles,
                         const int* __restrict__ tile_list /* nullptr: identity */, int n_tiles,
                         int tile_per_warp /* 0: the CTA's warps share tile blockIdx.x; 1: one (single-locus) tile per warp */,
                         SSParamsDev P, uint8_t* __restrict__ visited, guac_locus_summary* __restrict__ summary,
                         SSCallDev* __restrict__ calls, int* __restrict__ n_calls, int max_calls,
-                        unsigned long long* __restrict__ n_visited /* optional */, DeviceError* err) {
+                        unsigned long long* __restrict__ n_visited /* optional */, DeviceError* err,
+                        const int* __restrict__ n_tiles_dev = nullptr /* optional: the tile count lives on the device (capped by n_tiles) */) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tsel = tile_per_warp ? (int)blockIdx.x * WARPS_PER_CTA + warp : (int)blockIdx.x;
-  if (tsel >= n_tiles) return;  // no block-wide barrier below
-  const Tile tile = tiles[tile_list ? tile_list[tsel] : tsel];
+  if (n_tiles_dev) n_tiles = min(n_tiles, __ldg(n_tiles_dev));
+  // grid-stride over the tiles: with a device-side count the launch is sized before the count is known
+  for (int tsel = tile_per_warp ? (int)blockIdx.x * WARPS_PER_CTA + warp : (int)blockIdx.x; tsel < n_tiles;  // no block-wide barrier below
+       tsel += (int)gridDim.x * (tile_per_warp ? WARPS_PER_CTA : 1)) {
+  Tile tile = tiles[tile_list ? tile_list[tsel] : tsel];
   const RefView ref = refs[tile.ref_index];
   const unsigned FULL = 0xffffffffu;
+  if (tile_per_warp && tile.n_loci == 1) {
+    // a single-locus tile arrives with the read span of the tile it came from: narrow it to the reads that can overlap
+    // the locus (start <= x, running-max end > x), two 32-ary searches by the whole warp
+    const int64_t x = tile.locus0, key = ((int64_t)tile.contig_id << 40) | x;
+    tile.read_hi = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.start + i) > x; });
+    tile.read_lo = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.runmax_key + i) > key; });
+  }
   for (int li = tile_per_warp ? 0 : warp; li < tile.n_loci; li += tile_per_warp ? 1 : WARPS_PER_CTA) {
     const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
     int depthN = 0, depthT = 0, refN = 0, refT = 0;
@@ -425,6 +456,7 @@ somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Til
       summary[slot * 2 + 0] = sn;
       summary[slot * 2 + 1] = st;
     }
+  }
   }
 }
 

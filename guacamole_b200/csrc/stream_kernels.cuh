@@ -52,8 +52,13 @@ struct StreamArgs {
   const uint32_t* ref2; // and its 2-bit copy
   uint2* events;        // [n_reads][STREAM_EV_CAP]
   uint8_t* n_events;    // [n_reads] (255: more than the cap)
-  int inline_medium;    // 1: no list launch follows (several contigs in the batch): walk multi-operator reads in place
-  const int64_t* list;  // non-null: the reads to visit (the multi-operator ones); null: reads [read_lo, read_hi), single-operator only
+  int inline_medium;    // 1: no list is given (several contigs in the batch): walk multi-operator reads in place
+  // The multi-operator reads of the batch, listed at upload.  Their longer, latency-bound walk runs in CTAs of its own
+  // (full warps of such reads), one of them after every `list_period - 1` CTAs of single-operator reads, so that the
+  // two kinds share every SM all through the launch.
+  const int64_t* list;
+  int64_t n_list;
+  unsigned list_blocks, list_period;  // list_blocks = 0: no list
 };
 
 // Read-event record (per read, independent of the loci of the call):
@@ -65,12 +70,30 @@ __device__ __forceinline__ uint32_t pack_read_event(int off, int kind, int code)
 
 // One thread per read: the read's non-Match elements against the 2-bit reference.  No shared memory, no barrier, no atomic.
 __global__ void __launch_bounds__(256) ss_read_events_kernel(ReadsView R, const __grid_constant__ StreamArgs A) {
-  const int64_t i = A.read_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= A.read_hi) return;
-  const int64_t r = A.list ? __ldg(A.list + i) : i;
+  // block -> a block of the list or a block of the read range (see StreamArgs)
+  unsigned b = blockIdx.x;
+  bool from_list = false;
+  if (A.list_blocks) {
+    const unsigned g = b / A.list_period, k = b % A.list_period;
+    if (g < A.list_blocks) {
+      from_list = k == A.list_period - 1;
+      b = from_list ? g : g * (A.list_period - 1) + k;
+    } else {
+      b -= A.list_blocks;
+    }
+  }
+  int64_t r;
+  if (from_list) {
+    const int64_t i = (int64_t)b * blockDim.x + threadIdx.x;
+    if (i >= A.n_list) return;
+    r = __ldg(A.list + i);
+  } else {
+    r = A.read_lo + (int64_t)b * blockDim.x + threadIdx.x;
+    if (r >= A.read_hi) return;
+  }
   const uint4 hdr = __ldg(A.hdr + r);
   const uint8_t rf = (uint8_t)(hdr.y >> 24);
-  if (!A.list && !A.inline_medium && (rf & RF_MEDIUM) && !(rf & RF_FAST)) return;  // visited through the list by a launch of their own
+  if (!from_list && !A.inline_medium && (rf & RF_MEDIUM) && !(rf & RF_FAST)) return;  // visited through the list
   int n_ev = 0;
   uint2* mine = A.events + r * STREAM_EV_CAP;
   auto push = [&](int off, int kind, int code, uint32_t second) {
@@ -165,6 +188,15 @@ __global__ void __launch_bounds__(256) ss_read_events_kernel(ReadsView R, const 
       }
     }
   }
+#ifndef GUAC_K1_PAD
+#define GUAC_K1_PAD 1
+#endif
+#if GUAC_K1_PAD
+  // a 32-byte sector of the slot that holds an event is written whole (zeros behind the last record): L2 then owns
+  // every byte of the sector and evicts it without first fetching the rest from HBM
+  if (n_ev < STREAM_EV_CAP)
+    for (int k = n_ev; k & 3; ++k) mine[k] = make_uint2(0u, 0u);
+#endif
   A.n_events[r] = (uint8_t)min(n_ev, 255);
 }
 
