@@ -957,6 +957,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     calls = static_cast<SSCallDev*>(hp);
   }
   *arena_len = 0;
+  std::vector<std::pair<int64_t, int>> order((size_t)nc);
   if (nc > 0) {
     GUAC_TRY(ensure(ctx, ctx->b_arena_used, sizeof(unsigned int)));
     GUAC_TRY(ensure(ctx, ctx->b_arena, (size_t)nc * 32 + 4096));
@@ -969,6 +970,15 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
                                                                 ctx->b_err.as<DeviceError>());
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
+      if (attempt == 0) {
+        // (range order, locus) order = slot order.  The slots are final before this kernel ran: they come over on the second
+        // stream and the host sorts their indices while the kernel works (the 200-byte records are never moved).
+        GUAC_TRY(side_stream(ctx));
+        CUDA_TRY(ctx, cudaMemcpyAsync(calls, ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream2));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream2));
+        for (int i = 0; i < nc; ++i) order[(size_t)i] = {calls[i].slot, i};
+        std::sort(order.begin(), order.end());
+      }
       CUDA_TRY(ctx, cudaMemcpyAsync(calls, ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
       CUDA_TRY(ctx, cudaMemcpyAsync(&used, ctx->b_arena_used.p, sizeof used, cudaMemcpyDeviceToHost, ctx->stream));
       {
@@ -982,14 +992,14 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       if ((size_t)used <= ctx->b_arena.cap) break;
       GUAC_TRY(ensure(ctx, ctx->b_arena, (size_t)used + 16));  // long indel alleles: grow and redo
     }
-    std::sort(calls, calls + nc, [](const SSCallDev& a, const SSCallDev& b) { return a.slot < b.slot; });
+    trace.mark("evidence kernel + copy");
   }
   trace.mark("evidence");
   void* h = nullptr;
   GUAC_TRY(pinned_alloc(ctx, &h, std::max<size_t>((size_t)nc * sizeof(guac_ss_call), 16)));
   guac_ss_call* oc = (guac_ss_call*)h;
   for (int i = 0; i < nc; ++i) {
-    const SSCallDev& c = calls[i];
+    const SSCallDev& c = calls[order[(size_t)i].second];
     guac_ss_call g;
     std::memset(&g, 0, sizeof g);
     g.contig_id = c.contig_id;

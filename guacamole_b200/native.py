@@ -284,7 +284,8 @@ def _take(lib, ctx, p, dtype, n) -> np.ndarray:
     else:
         nbytes = int(n) * np.dtype(dtype).itemsize
         addr = C.cast(p, C.c_void_p).value
-        out = np.frombuffer((C.c_char * nbytes).from_address(addr), dtype=dtype).copy()  # one copy out of the pinned buffer
+        # one copy out of the pinned buffer, as bytes: numpy copies a structured dtype field by field, 15x slower
+        out = np.frombuffer((C.c_char * nbytes).from_address(addr), dtype=np.uint8).copy().view(dtype)
     if p:
         lib.guac_free(ctx, C.cast(p, C.c_void_p))
     return out
