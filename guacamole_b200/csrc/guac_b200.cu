@@ -948,76 +948,68 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     max_calls = nc;  // rerun with room for every call
   }
   trace.mark("per-locus kernels done");
-  // sparse part: one kernel fills the evidence and the allele strings of every call; the records come back through
-  // pinned memory and are put in (range order, locus) order on the host
-  SSCallDev* calls = nullptr;
+  // sparse part: the calls are ranked by slot (= (range order, locus) order), then one kernel fills the evidence and the
+  // allele strings of every call and writes the finished guac_ss_call records in that order; they come back through
+  // pinned memory as they are
+  *arena_len = 0;
+  const bool have_events = use_tiles && ctx->opt_ss_impl == 2;  // the read pass ran in this call: its Mismatch records are usable
+  guac_ss_call* oc = nullptr;
   {
     void* hp = nullptr;
-    GUAC_TRY(pinned_alloc(ctx, &hp, std::max<size_t>((size_t)nc * sizeof(SSCallDev), 16)));
-    calls = static_cast<SSCallDev*>(hp);
+    GUAC_TRY(pinned_alloc(ctx, &hp, std::max<size_t>((size_t)nc * sizeof(guac_ss_call), 16)));
+    oc = static_cast<guac_ss_call*>(hp);
   }
-  *arena_len = 0;
-  std::vector<std::pair<int64_t, int>> order((size_t)nc);
   if (nc > 0) {
-    GUAC_TRY(ensure(ctx, ctx->b_arena_used, sizeof(unsigned int)));
-    GUAC_TRY(ensure(ctx, ctx->b_arena, (size_t)nc * 32 + 4096));
-    for (int attempt = 0; attempt < 2; ++attempt) {
-      unsigned int used = 0;
-      CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_arena_used.p, 0, sizeof(unsigned int), ctx->stream));
-      ss_evidence_kernel<<<(unsigned)nc, 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(),
-                                                                ctx->b_arena.as<char>(), ctx->b_arena_used.as<unsigned int>(),
-                                                                (unsigned int)std::min<size_t>(ctx->b_arena.cap, 0xFFFFFFFFu),
-                                                                ctx->b_err.as<DeviceError>());
-      ctx->launches += 1;
-      CUDA_TRY(ctx, cudaGetLastError());
-      if (attempt == 0) {
-        // (range order, locus) order = slot order.  The slots are final before this kernel ran: they come over on the second
-        // stream and the host sorts their indices while the kernel works (the 200-byte records are never moved).
-        GUAC_TRY(side_stream(ctx));
-        CUDA_TRY(ctx, cudaMemcpyAsync(calls, ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream2));
-        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream2));
-        for (int i = 0; i < nc; ++i) order[(size_t)i] = {calls[i].slot, i};
+    int st = ensure(ctx, ctx->b_arena_used, sizeof(unsigned int));
+    if (st == GUAC_OK) st = ensure(ctx, ctx->b_arena, (size_t)nc * 32 + 4096);
+    if (st == GUAC_OK) st = ensure(ctx, ctx->u_flag, (size_t)nc * sizeof(int));
+    if (st == GUAC_OK) st = ensure(ctx, ctx->u_off, (size_t)nc * sizeof(guac_ss_call));
+    if (st == GUAC_OK) {
+      if (nc <= SS_RANK_MAX) {
+        ss_call_rank_kernel<<<blocks_for(nc, 256), 256, 0, ctx->stream>>>(ctx->b_calls.as<SSCallDev>(), nc, ctx->u_flag.as<int>());
+        ctx->launches += 1;
+      } else {  // too many for the quadratic kernel: the host sorts the slots
+        std::vector<SSCallDev> tmp((size_t)nc);
+        std::vector<std::pair<int64_t, int>> order((size_t)nc);
+        std::vector<int> rank((size_t)nc);
+        if (cudaMemcpyAsync(tmp.data(), ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+            cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+          st = fail(ctx, GUAC_E_CUDA, "copy of the call records failed");
+        for (int i = 0; i < nc; ++i) order[(size_t)i] = {tmp[(size_t)i].slot, i};
         std::sort(order.begin(), order.end());
+        for (int i = 0; i < nc; ++i) rank[(size_t)order[(size_t)i].second] = i;
+        if (st == GUAC_OK && (cudaMemcpyAsync(ctx->u_flag.p, rank.data(), (size_t)nc * sizeof(int), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
+                              cudaStreamSynchronize(ctx->stream) != cudaSuccess))
+          st = fail(ctx, GUAC_E_CUDA, "upload of the call order failed");
       }
-      CUDA_TRY(ctx, cudaMemcpyAsync(calls, ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream));
-      CUDA_TRY(ctx, cudaMemcpyAsync(&used, ctx->b_arena_used.p, sizeof used, cudaMemcpyDeviceToHost, ctx->stream));
-      {
-        int st = check_device_error(ctx);  // synchronises
-        if (st != GUAC_OK) {
-          guac_free(ctx, calls);
-          return st;
-        }
+    }
+    for (int attempt = 0; st == GUAC_OK && attempt < 2; ++attempt) {
+      unsigned int used = 0;
+      cudaMemsetAsync(ctx->b_arena_used.p, 0, sizeof(unsigned int), ctx->stream);
+      ss_evidence_kernel<<<(unsigned)nc, 128, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(), ctx->b_arena.as<char>(), ctx->b_arena_used.as<unsigned int>(),
+          (unsigned int)std::min<size_t>(ctx->b_arena.cap, 0xFFFFFFFFu), ctx->b_err.as<DeviceError>(),
+          have_events ? ctx->b_hdr.as<uint4>() : nullptr, have_events ? ctx->b_bins.as<uint2>() : nullptr,
+          have_events ? ctx->b_bin_count.as<uint8_t>() : nullptr, STREAM_EV_CAP, ctx->u_flag.as<int>(), ctx->u_off.as<guac_ss_call>());
+      ctx->launches += 1;
+      if (cudaGetLastError() != cudaSuccess ||
+          cudaMemcpyAsync(oc, ctx->u_off.p, (size_t)nc * sizeof(guac_ss_call), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+          cudaMemcpyAsync(&used, ctx->b_arena_used.p, sizeof used, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) {
+        st = fail(ctx, GUAC_E_CUDA, "launch of the evidence kernel failed");
+        break;
       }
+      st = check_device_error(ctx);  // synchronises
+      if (st != GUAC_OK) break;
       *arena_len = used;
       if ((size_t)used <= ctx->b_arena.cap) break;
-      GUAC_TRY(ensure(ctx, ctx->b_arena, (size_t)used + 16));  // long indel alleles: grow and redo
+      st = ensure(ctx, ctx->b_arena, (size_t)used + 16);  // long indel alleles: grow and redo
     }
-    trace.mark("evidence kernel + copy");
+    if (st != GUAC_OK) {
+      guac_free(ctx, oc);
+      return st;
+    }
   }
   trace.mark("evidence");
-  void* h = nullptr;
-  GUAC_TRY(pinned_alloc(ctx, &h, std::max<size_t>((size_t)nc * sizeof(guac_ss_call), 16)));
-  guac_ss_call* oc = (guac_ss_call*)h;
-  for (int i = 0; i < nc; ++i) {
-    const SSCallDev& c = calls[order[(size_t)i].second];
-    guac_ss_call g;
-    std::memset(&g, 0, sizeof g);
-    g.contig_id = c.contig_id;
-    g.start = c.locus;
-    g.ref_off = c.ref_off;
-    g.ref_len = c.ref_len;
-    g.alt_off = c.alt_off;
-    g.alt_len = c.alt_len;
-    g.somatic_log_odds = c.tumor_alt_lp - c.tumor_ref_lp;
-    g.tumor_ref_log_prob = c.tumor_ref_lp;
-    g.tumor_alt_log_prob = c.tumor_alt_lp;
-    g.normal_ref_log_prob = c.normal_ref_lp;
-    g.normal_alt_log_prob = c.normal_alt_lp;
-    g.tumor_variant_evidence = c.tumor_ev;
-    g.normal_reference_evidence = c.normal_ev;
-    oc[i] = g;
-  }
-  guac_free(ctx, calls);
   *out_calls = oc;
   *n_calls = nc;
   GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)*arena_len));

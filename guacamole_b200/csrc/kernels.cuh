@@ -532,6 +532,24 @@ __device__ inline int count_of_mismatches(const ReadsView& R, int64_t r, const R
   return n;
 }
 
+// Position of every call in (range order, locus) order = the number of calls with a smaller slot (slots are distinct: one
+// call per locus).  Quadratic, for the few thousand calls of a partition; the host sorts instead beyond SS_RANK_MAX.
+constexpr int SS_RANK_MAX = 32768;
+__global__ void __launch_bounds__(256) ss_call_rank_kernel(const SSCallDev* __restrict__ calls, int n, int* __restrict__ rank) {
+  __shared__ int64_t s_slot[256];
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int64_t mine = i < n ? calls[i].slot : 0;
+  int below = 0;
+  for (int base = 0; base < n; base += 256) {
+    __syncthreads();
+    s_slot[threadIdx.x] = base + threadIdx.x < n ? calls[base + threadIdx.x].slot : INT64_MAX;
+    __syncthreads();
+#pragma unroll 8
+    for (int k = 0; k < 256; ++k) below += s_slot[k] < mine;
+  }
+  if (i < n) rank[i] = below;
+}
+
 constexpr int MM_BINS = 1024;
 
 // lower/upper middle of a histogram with n entries -> (a, b): values at ranks (n-1)/2 and n/2
@@ -558,12 +576,16 @@ __device__ inline void hist_middle(const unsigned* h, int bins, int n, int& a, i
 // Also writes the allele strings (variants/Allele.scala) into the arena.
 __global__ void __launch_bounds__(128)
 ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P, SSCallDev* __restrict__ calls,
-                   char* __restrict__ arena, unsigned int* __restrict__ arena_used, unsigned int arena_cap, DeviceError* err) {
+                   char* __restrict__ arena, unsigned int* __restrict__ arena_used, unsigned int arena_cap, DeviceError* err,
+                   const uint4* __restrict__ hdr /* the three below: null unless the read pass of this call left its events */,
+                   const uint2* __restrict__ ev_by_read, const uint8_t* __restrict__ ev_count, int ev_cap,
+                   const int* __restrict__ rank /* position of each call in the output */, guac_ss_call* __restrict__ out) {
   // [0] tumor with the called allele, [1] normal with the reference allele
   __shared__ unsigned h_mapq[2][256], h_bq[2][256], h_mm[2][MM_BINS];
   __shared__ unsigned s_depth[2], s_pos[2], s_adepth[2], s_apos[2];
   __shared__ int s_list[1024];  // reads of either sample that overlap the locus (read offset << 1 | which)
   __shared__ int s_mm_read[512], s_mm_cnt[512];  // reads whose mismatches are to be counted, and the counts
+  __shared__ unsigned char s_mm_slow[512];       // 1: not countable from the read pass's events
   __shared__ int s_n, s_nmm;
   SSCallDev& c = calls[blockIdx.x];
   const RefView ref = refs[c.ref_index];
@@ -630,8 +652,30 @@ ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P,
   // MappedRead.countOfMismatches (MappedRead.scala:53-64) of the queued reads: 16 loci of a single-operator read per
   // work item, so a call's ~45 reads x 100 bases keep all 128 threads busy instead of 45 threads for 100 iterations
   const int n_mm = min(s_nmm, 512);
+  if (ev_count != nullptr) {
+    // The read pass of this call (ss_read_events_kernel) already compared every such read with the reference: the
+    // Mismatch records of its slot are the count, provided the slot is complete (no overflow), the read lies inside the
+    // reference window and none of its loci has a reference base outside A C G T (those the walk below must see).
+    for (int j = threadIdx.x; j < n_mm; j += blockDim.x) {
+      const int64_t r = c.read_lo + (s_mm_read[j] >> 1);
+      const int cnt = __ldg(ev_count + r);
+      const int64_t s = __ldg(R.start + r), en = __ldg(R.end + r);
+      bool ok = ((__ldg(hdr + r).y >> 24) & 4 /* RF_MEDIUM */) && cnt != 255 && s >= ref.offset && en <= ref.offset + ref.len && en > s;
+      if (ok && ref.bad != nullptr)
+        for (int64_t g = (s - ref.offset) >> 4; ok && g <= (en - 1 - ref.offset) >> 4; ++g) ok = !((__ldg(ref.bad + (g >> 5)) >> (g & 31)) & 1u);
+      int n = -1;
+      if (ok) {
+        n = 0;
+        for (int k = 0; k < cnt; ++k) n += ((__ldg(&ev_by_read[r * ev_cap + k].x) >> 16) & 7) == GUAC_ALN_MISMATCH;
+      }
+      s_mm_cnt[j] = max(n, 0);
+      s_mm_slow[j] = n < 0;
+    }
+    __syncthreads();
+  }
   for (int item = threadIdx.x; item < n_mm * 16; item += blockDim.x) {
     const int j = item >> 4, chunk = item & 15;
+    if (ev_count != nullptr && !s_mm_slow[j]) continue;  // counted from the events
     const int64_t r = c.read_lo + (s_mm_read[j] >> 1);
     const uint32_t c0 = __ldg(R.cigar_off + r), c1 = __ldg(R.cigar_off + r + 1);
     const int64_t s = __ldg(R.start + r), en = __ldg(R.end + r);
@@ -733,6 +777,24 @@ ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P,
         }
       }
     }
+  }
+  __syncthreads();  // both evidences and the string offsets are in the record
+  if (threadIdx.x == 0) {  // the finished record, at its place in (range order, locus) order
+    guac_ss_call g = {};
+    g.contig_id = c.contig_id;
+    g.start = c.locus;
+    g.ref_off = c.ref_off;
+    g.ref_len = c.ref_len;
+    g.alt_off = c.alt_off;
+    g.alt_len = c.alt_len;
+    g.somatic_log_odds = c.tumor_alt_lp - c.tumor_ref_lp;
+    g.tumor_ref_log_prob = c.tumor_ref_lp;
+    g.tumor_alt_log_prob = c.tumor_alt_lp;
+    g.normal_ref_log_prob = c.normal_ref_lp;
+    g.normal_alt_log_prob = c.normal_alt_lp;
+    g.tumor_variant_evidence = c.tumor_ev;
+    g.normal_reference_evidence = c.normal_ev;
+    out[rank[blockIdx.x]] = g;
   }
 }
 

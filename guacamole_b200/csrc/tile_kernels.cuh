@@ -53,6 +53,7 @@ enum : uint8_t {
   RF_HIQ = 2,     // every base quality >= 4, i.e. P(correct) >= 0.60 > 1/2 (licenses the LOD bound)
   RF_MEDIUM = 4   // operators within {M,=,X,I,D,S,H}, ACGT only, CIGAR consistent with the sequence
 };
+static_assert(RF_MEDIUM == 4, "ss_evidence_kernel (kernels.cuh) tests this bit of the packed header");
 
 __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags) {
   int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
