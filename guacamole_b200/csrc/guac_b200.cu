@@ -266,7 +266,7 @@ int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& pla
   GUAC_TRY(upload(ctx, ctx->b_ranges, rs.data(), rs.size()));
   GUAC_TRY(ensure(ctx, ctx->b_tiles, (size_t)tile * sizeof(Tile)));
   build_tiles_kernel<<<blocks_for(tile, 256), 256, 0, ctx->stream>>>(ctx->b_ranges.as<RangeDev>(), (int)rs.size(), tile, tile_loci,
-                                                                      ctx->R, ctx->b_tiles.as<Tile>());
+                                                                      ctx->R, ctx->b_tiles.as<Tile>(), ctx->d_refs.as<RefView>());
   ctx->launches += 1;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `rs` is a temporary
@@ -1355,8 +1355,9 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
     attr_set = true;
   }
   TileArgs TA;
+  std::memset(&TA, 0, sizeof TA);
   TA.rflags = ctx->b_rflags.as<uint8_t>();
-    TA.hdr = ctx->b_hdr.as<uint4>();
+  TA.hdr = ctx->b_hdr.as<uint4>();
   TA.refs = ctx->d_refs.as<RefView>();
   TA.tiles = ctx->b_tiles.as<Tile>();
   TA.visited = ctx->b_visited.as<uint8_t>();

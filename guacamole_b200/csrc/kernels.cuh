@@ -28,7 +28,7 @@ struct RangeDev {
 // One thread per tile: locate the tile's range, then binary-search the span of reads that can
 // overlap it — start < tile end (reads are sorted by start) and running-max end > tile start.
 __global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ranges, int64_t n_tiles, int tile_loci,
-                                   ReadsView R, Tile* __restrict__ tiles) {
+                                   ReadsView R, Tile* __restrict__ tiles, const RefView* __restrict__ refs = nullptr) {
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_tiles) return;
   int lo = 0, hi = n_ranges - 1;
@@ -44,7 +44,26 @@ __global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ra
   tl.contig_id = rg.contig_id;
   tl.slot0 = rg.slot0 + k * tile_loci;
   tl.ref_index = rg.ref_index;
+  // _pad = 1: some locus of the tile has no A C G T reference base (outside the window, or flagged in the window's
+  // one-bit-per-16-loci map): the locus pass of the stream form hands such a tile to the generic kernel without looking
   tl._pad = 0;
+  if (refs != nullptr) {
+    const RefView ref = refs[rg.ref_index];
+    if (ref.bad != nullptr) {
+      const int64_t rel0 = tl.locus0 - ref.offset;
+      bool bad = rel0 < 0 || rel0 + tl.n_loci > ref.len;
+      if (!bad) {
+        const int64_t g0 = rel0 >> 4, g1 = (rel0 + tl.n_loci - 1) >> 4;
+        for (int64_t w = g0 >> 5; w <= (g1 >> 5) && !bad; ++w) {
+          uint32_t bits = __ldg(ref.bad + w);
+          if (w == (g0 >> 5)) bits &= 0xFFFFFFFFu << (g0 & 31);
+          if (w == (g1 >> 5)) bits &= 0xFFFFFFFFu >> (31 - (g1 & 31));
+          bad = bits != 0;
+        }
+      }
+      tl._pad = bad ? 1 : 0;
+    }
+  }
   const int64_t tile_end = tl.locus0 + tl.n_loci;
   int64_t a = rg.read_clo, b = rg.read_chi;
   while (a < b) {  // first read with start >= tile_end

@@ -200,6 +200,21 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     return;
   }
 
+  // The first header of every thread (and, STREAM, its event count) depends on the tile descriptor alone: the loads go
+  // out here, ahead of the set-up and its barriers, instead of starting a new round trip behind them.
+#ifndef GUAC_TK_EARLY
+#define GUAC_TK_EARLY 1
+#endif
+  const uint4* hdrs = A.hdr + tile.read_lo;
+  uint4 next_hdr = make_uint4(0, 0, 0, 0);
+  int next_cnt = 0;  // STREAM: the read's event count travels with its header
+#if GUAC_TK_EARLY
+  if (tid < (int)n_reads_tile) {
+    next_hdr = __ldg(hdrs + tid);
+    if (STREAM) next_cnt = (int)__ldg(A.ev_count + tile.read_lo + tid);
+  }
+#endif
+
   // ---- init ------------------------------------------------------------------------------
   for (int i = tid; i < TL + 1; i += CFG::THREADS) S.cov[i] = S.aux[i] = 0;
   for (int i = tid; i < TL; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
@@ -216,19 +231,10 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   const uint8_t* ref_tile = ref.bases + rel0;
   if (STREAM) {
     // the read pass already compared against the reference; here only "is every base of the tile A C G T" matters, and
-    // one bit per 16 loci (ref.bad, built with the 2-bit copy) answers it from two or three words
-    if (tid == 0) {
-      bool bad = l_min > 0 || l_max < n_loci;  // part of the tile lies outside the reference window
-      if (!bad) {
-        const long long g0 = rel0 >> 4, g1 = (rel0 + n_loci - 1) >> 4;
-        for (long long w = g0 >> 5; w <= (g1 >> 5) && !bad; ++w) {
-          uint32_t bits = __ldg(ref.bad + w);
-          if (w == (g0 >> 5)) bits &= 0xFFFFFFFFu << (g0 & 31);
-          if (w == (g1 >> 5)) bits &= 0xFFFFFFFFu >> (31 - (g1 & 31));
-          bad = bits != 0;
-        }
-      }
-      if (bad) S.ref_has_mask = 1;
+    // build_tiles_kernel answered that from the window's one-bit-per-16-loci map (Tile::_pad)
+    if (tile._pad) {  // rare, uniform across the CTA: generic kernel
+      if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
+      return;
     }
   }
   for (int base = 0; !STREAM && base < TL; base += CFG::THREADS) {
@@ -247,10 +253,12 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       if (mask) S.ref_has_mask = 1;
     }
   }
-  __syncthreads();
-  if (S.ref_has_mask) {  // a reference base that is not A C G T (or is missing) in the tile: rare, generic kernel
-    if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
-    return;
+  if (!STREAM) {
+    __syncthreads();
+    if (S.ref_has_mask) {  // a reference base that is not A C G T (or is missing) in the tile: rare, generic kernel
+      if (tid == 0) A.fallback_tiles[atomicAdd(A.n_fallback, 1)] = blockIdx.x;
+      return;
+    }
   }
   auto push_event = [&](int l, int rl, int slot, int kind, int code, uint32_t second) {
     atomicAdd(&S.nonref[l], slot ? 65536 : 1);
@@ -262,14 +270,13 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   // ---- A. read-parallel pass ---------------------------------------------------------------
   // The five header loads of a read are independent: issue them together, one read ahead of the one being processed,
   // so the compare work of read i hides the latency of read i + 256's header.
-  const uint4* hdrs = A.hdr + tile.read_lo;
   const uint32_t t0_lo = (uint32_t)t0;
-  uint4 next_hdr = make_uint4(0, 0, 0, 0);
-  int next_cnt = 0;  // STREAM: the read's event count travels with its header
+#if !GUAC_TK_EARLY
   if (tid < (int)n_reads_tile) {
     next_hdr = __ldg(hdrs + tid);
     if (STREAM) next_cnt = (int)__ldg(A.ev_count + tile.read_lo + tid);
   }
+#endif
   for (int rl = tid; rl < (int)n_reads_tile; rl += CFG::THREADS) {
     const int64_t r = tile.read_lo + rl;
     const uint4 hdr = next_hdr;
