@@ -77,6 +77,7 @@ struct guac_ctx {
   DevBuf b_nops, b_rflags, b_logtab, b_fallback;
   int64_t opt_ss_impl = 2;            // 2 = stream (read pass + locus pass; the default), 0 = single tile kernel, 1 = gather kernel only
   int64_t opt_force_fallback_mod = 0; // test hook: tiles with index % k == 0 are sent to the fallback path
+  int64_t opt_ss_rank_max = SS_RANK_MAX;  // test hook: more calls than this are put in order by the host instead of the device
   int64_t last_fallback_tiles = 0, last_heavy_loci = 0;
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;
   double bound_tab_vaf = -1;
@@ -965,7 +966,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     if (st == GUAC_OK) st = ensure(ctx, ctx->u_flag, (size_t)nc * sizeof(int));
     if (st == GUAC_OK) st = ensure(ctx, ctx->u_off, (size_t)nc * sizeof(guac_ss_call));
     if (st == GUAC_OK) {
-      if (nc <= SS_RANK_MAX) {
+      if (nc <= ctx->opt_ss_rank_max) {
         ss_call_rank_kernel<<<blocks_for(nc, 256), 256, 0, ctx->stream>>>(ctx->b_calls.as<SSCallDev>(), nc, ctx->u_flag.as<int>());
         ctx->launches += 1;
       } else {  // too many for the quadratic kernel: the host sorts the slots
@@ -1555,6 +1556,8 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
     ctx->opt_ss_impl = value;
   } else if (n == "ss_force_fallback_mod") {
     ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
+  } else if (n == "ss_rank_max") {
+    ctx->opt_ss_rank_max = value < 0 ? SS_RANK_MAX : std::min<int64_t>(value, SS_RANK_MAX);
   } else {
     return fail(ctx, GUAC_E_INVALID_INPUT, "unknown option " + n);
   }

@@ -463,7 +463,9 @@ void* guac_stream(guac_ctx* ctx);
 /* Implementation switches for tests and A/B measurements:
  *   "ss_impl"               somatic-standard: 2 = read pass + locus pass as two kernels (default), 0 = both in one tile
  *                           kernel, 1 = generic gather kernel only; all three fall back to the gather kernel per tile
- *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook) */
+ *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook)
+ *   "ss_rank_max"           somatic-standard puts more calls than this in output order on the host instead of on the
+ *                           device (test hook; default and maximum 32768, negative restores the default) */
 int guac_set_option(guac_ctx* ctx, const char* name, int64_t value);
 /* Tiles of the most recent guac_somatic_standard call that took the fallback path. */
 int64_t guac_last_fallback_tiles(guac_ctx* ctx);

@@ -9,15 +9,18 @@ from oracle import oracle
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["tile", "gather", "tile+fallback", "stream", "stream+fallback"])
+@pytest.fixture(params=["tile", "gather", "tile+fallback", "stream", "stream+fallback", "stream+hostorder"])
 def impl(request, gpu_ctx):
     """Every parity case runs through the tile kernel, the generic gather kernel, the tile kernel with every third
-    tile forced through its fallback path, and the stream implementation (read pass as a kernel of its own)."""
-    gpu_ctx.set_option("ss_impl", {"gather": 1, "stream": 2, "stream+fallback": 2}.get(request.param, 0))
+    tile forced through its fallback path, the stream implementation (read pass as a kernel of its own), and the stream
+    implementation with the calls put in output order by the host (the path taken beyond 32768 calls)."""
+    gpu_ctx.set_option("ss_impl", {"gather": 1, "stream": 2, "stream+fallback": 2, "stream+hostorder": 2}.get(request.param, 0))
     gpu_ctx.set_option("ss_force_fallback_mod", 3 if request.param.endswith("+fallback") else 0)
+    gpu_ctx.set_option("ss_rank_max", 0 if request.param.endswith("+hostorder") else -1)
     yield request.param
     gpu_ctx.set_option("ss_impl", 2)  # the default
     gpu_ctx.set_option("ss_force_fallback_mod", 0)
+    gpu_ctx.set_option("ss_rank_max", -1)
 
 EV_INT = ["read_depth", "allele_read_depth", "forward_depth", "allele_forward_depth"]
 EV_F = ["probability", "mean_mapping_quality", "median_mapping_quality", "mean_base_quality", "median_base_quality",
