@@ -292,12 +292,15 @@ def main():
     if not args.no_e2e:
         hb = ctx.export_reads_compact_struct()
         n = int(hb.n_reads)
-        n_bases = n * 100
-        n_cigar = n  # the generator's reads: one operator each unless they carry an indel; counted exactly below
-        n_cigar = int(np.frombuffer((C.c_uint16 * n).from_address(C.cast(hb.n_cigar_ops, C.c_void_p).value), dtype=np.uint16).sum())
-        # start, read_len, n_cigar_ops, mapq, flags, sample_id; cigar words; bases2; qualities (4-bit codes or bytes); exceptions
-        qual_bytes = (n_bases * int(hb.qual_bits) + 7) // 8
-        h2d = n * (8 + 2 + 2 + 1 + 1 + 1) + n_cigar * 4 + (n_bases + 3) // 4 + qual_bytes + int(hb.n_exc) * 9 + int(hb.n_contig_runs) * 12 + 8
+        def column(p, ctype, dtype):
+            return np.frombuffer((ctype * n).from_address(C.cast(p, C.c_void_p).value), dtype=dtype)
+
+        # bytes on the wire, counted from the columns the struct holds (narrow start / operator-count / read-length columns
+        # where the exporter could use them)
+        n_bases = n * int(hb.uniform_read_len) if hb.uniform_read_len > 0 else int(column(hb.read_len, C.c_uint16, np.uint16).sum(dtype=np.int64))
+        n_cigar = int(column(hb.n_cigar_ops8, C.c_uint8, np.uint8).sum(dtype=np.int64)) if hb.n_cigar_ops8 else \
+            int(column(hb.n_cigar_ops, C.c_uint16, np.uint16).sum(dtype=np.int64))
+        h2d = hb.wire_bytes(n_bases, n_cigar)
         d2h_box = [0]
 
         def step_e2e():

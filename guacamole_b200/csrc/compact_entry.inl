@@ -24,9 +24,26 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   DevBuf &d_len = ctx->u_len, &d_ops = ctx->u_ops, &d_runs_c = ctx->u_runs_c, &d_runs_f = ctx->u_runs_f, &d_tmp = ctx->u_tmp,
          &d_qpacked = ctx->u_qpacked, &d_bad = ctx->u_bad;
   GUAC_TRY(side_stream(ctx));
-  GUAC_TRY(upload(ctx, ctx->b_start, b->start, (size_t)n));
-  GUAC_TRY(upload(ctx, d_len, b->read_len, (size_t)n));
-  GUAC_TRY(upload(ctx, d_ops, b->n_cigar_ops, (size_t)n));
+  // which of the three narrow columns the caller sent (each replaces its wide column)
+  const bool narrow_start = b->start_rel != nullptr, narrow_ops = b->n_cigar_ops8 != nullptr;
+  const int64_t uniform_len = b->uniform_read_len > 0 ? b->uniform_read_len : 0;
+  if (narrow_start && b->n_contig_runs > 0 && !b->run_start_base) return fail(ctx, GUAC_E_INVALID_INPUT, "start_rel without run_start_base");
+  if (uniform_len > 65535) return fail(ctx, GUAC_E_INVALID_INPUT, "uniform_read_len beyond 65535");
+  if (narrow_start) {
+    GUAC_TRY(upload(ctx, ctx->u_start_rel, b->start_rel, (size_t)n));
+    GUAC_TRY(upload(ctx, ctx->u_runs_base, b->run_start_base, (size_t)b->n_contig_runs));
+    GUAC_TRY(ensure(ctx, ctx->b_start, (size_t)std::max<int64_t>(n, 1) * sizeof(int64_t)));
+  } else {
+    GUAC_TRY(upload(ctx, ctx->b_start, b->start, (size_t)n));
+  }
+  if (!uniform_len) GUAC_TRY(upload(ctx, d_len, b->read_len, (size_t)n));
+  if (narrow_ops) {
+    GUAC_TRY(upload(ctx, ctx->u_ops8, b->n_cigar_ops8, (size_t)n));
+    GUAC_TRY(ensure(ctx, ctx->u_ops_eff, (size_t)n + 16));
+    GUAC_TRY(ensure(ctx, ctx->u_wire_off, (size_t)(n + 1) * sizeof(int64_t)));
+  } else {
+    GUAC_TRY(upload(ctx, d_ops, b->n_cigar_ops, (size_t)n));
+  }
   GUAC_TRY(upload(ctx, d_runs_c, b->run_contig_id, (size_t)b->n_contig_runs));
   GUAC_TRY(upload(ctx, d_runs_f, b->run_first_read, (size_t)b->n_contig_runs + 1));
   GUAC_TRY(upload(ctx, ctx->b_mapq, b->mapq, (size_t)n));
@@ -42,27 +59,59 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   GUAC_TRY(ensure(ctx, d_bad, sizeof(int)));
   CUDA_TRY(ctx, cudaMemsetAsync(d_bad.p, 0, sizeof(int), ctx->stream));
   uint64_t n_bases = 0;
-  int64_t n_cigar = 0;
+  int64_t n_cigar = 0, n_wire = 0;  // operators of the batch, and how many of them travel (all, without the narrow column)
   if (n > 0) {
     int64_t* seq_off = ctx->b_seq_off.as<int64_t>();
-    GUAC_TRY((device_scan<true, uint16_t>(ctx, d_len.as<uint16_t>(), seq_off, n, OpSum(), seq_off + n)));
-    GUAC_TRY((device_scan<true, uint16_t>(ctx, d_ops.as<uint16_t>(), d_tmp.as<int64_t>(), n, OpSum(), d_tmp.as<int64_t>() + n)));
+    if (uniform_len) {
+      compact::uniform_offsets_kernel<<<blocks_for(n + 1, 256), 256, 0, ctx->stream>>>(n + 1, (uint64_t)uniform_len, ctx->b_seq_off.as<uint64_t>());
+      ctx->launches += 1;
+    } else {
+      GUAC_TRY((device_scan<true, uint16_t>(ctx, d_len.as<uint16_t>(), seq_off, n, OpSum(), seq_off + n)));
+    }
+    if (narrow_ops) {
+      compact::effective_ops_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->u_ops8.as<uint8_t>(), ctx->u_ops_eff.as<uint8_t>());
+      ctx->launches += 1;
+      GUAC_TRY((device_scan<true, uint8_t>(ctx, ctx->u_ops_eff.as<uint8_t>(), d_tmp.as<int64_t>(), n, OpSum(), d_tmp.as<int64_t>() + n)));
+      GUAC_TRY((device_scan<true, uint8_t>(ctx, ctx->u_ops8.as<uint8_t>(), ctx->u_wire_off.as<int64_t>(), n, OpSum(),
+                                           ctx->u_wire_off.as<int64_t>() + n)));
+    } else {
+      GUAC_TRY((device_scan<true, uint16_t>(ctx, d_ops.as<uint16_t>(), d_tmp.as<int64_t>(), n, OpSum(), d_tmp.as<int64_t>() + n)));
+    }
     compact::narrow_offsets_kernel<<<blocks_for(n + 1, 256), 256, 0, ctx->stream>>>(n + 1, d_tmp.as<int64_t>(), ctx->b_cigar_off.as<uint32_t>());
     compact::contig_from_runs_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, d_runs_c.as<int32_t>(), d_runs_f.as<int64_t>(),
                                                                                  b->n_contig_runs, ctx->b_contig.as<int32_t>());
+    if (narrow_start) {
+      compact::starts_from_rel_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->u_runs_base.as<int64_t>(), d_runs_f.as<int64_t>(),
+                                                                                  b->n_contig_runs, ctx->u_start_rel.as<uint32_t>(),
+                                                                                  ctx->b_start.as<int64_t>());
+      ctx->launches += 1;
+    }
     compact::validate_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->b_start.as<int64_t>(), ctx->b_contig.as<int32_t>(),
                                                                          ctx->b_sample.as<uint8_t>(), b->n_samples, d_bad.as<int>());
     ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
     CUDA_TRY(ctx, cudaMemcpyAsync(&n_bases, seq_off + n, sizeof n_bases, cudaMemcpyDeviceToHost, ctx->stream));
     CUDA_TRY(ctx, cudaMemcpyAsync(&n_cigar, d_tmp.as<int64_t>() + n, sizeof n_cigar, cudaMemcpyDeviceToHost, ctx->stream));
+    if (narrow_ops) CUDA_TRY(ctx, cudaMemcpyAsync(&n_wire, ctx->u_wire_off.as<int64_t>() + n, sizeof n_wire, cudaMemcpyDeviceToHost, ctx->stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (!narrow_ops) n_wire = n_cigar;
     if (n_cigar >= ((int64_t)1 << 32)) return fail(ctx, GUAC_E_UNSUPPORTED, "more than 2^32-1 CIGAR operators in one batch");
   } else {
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_seq_off.p, 0, sizeof(uint64_t), ctx->stream));
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_cigar_off.p, 0, sizeof(uint32_t), ctx->stream));
   }
-  GUAC_TRY(upload(ctx, ctx->b_cigar, b->cigar, (size_t)n_cigar));
+  if (narrow_ops) {
+    GUAC_TRY(upload(ctx, ctx->u_wire, b->cigar, (size_t)n_wire));
+    GUAC_TRY(ensure(ctx, ctx->b_cigar, (size_t)n_cigar * sizeof(uint32_t) + 16));
+    if (n > 0) {
+      compact::cigar_from_ops8_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(
+          n, ctx->u_ops8.as<uint8_t>(), ctx->b_cigar_off.as<uint32_t>(), ctx->u_wire_off.as<int64_t>(), ctx->u_wire.as<uint32_t>(),
+          ctx->b_seq_off.as<uint64_t>(), ctx->b_cigar.as<uint32_t>());
+      ctx->launches += 1;
+    }
+  } else {
+    GUAC_TRY(upload(ctx, ctx->b_cigar, b->cigar, (size_t)n_cigar));
+  }
   GUAC_TRY(ensure(ctx, ctx->b_bases2, (size_t)((n_bases + 3) / 4) + 64 + 16));
   GUAC_TRY(ensure(ctx, ctx->b_nmask, (size_t)((n_bases + 7) / 8) + 16));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_nmask.p, 0, (size_t)((n_bases + 7) / 8) + 16, ctx->stream));
@@ -178,10 +227,62 @@ int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out) {
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     if (too_long) return fail(ctx, GUAC_E_UNSUPPORTED, "a read has more than 65535 bases or CIGAR operators: use guac_reads_export");
   }
-  GUAC_TRY(host_out(ctx, const_cast<int64_t**>(&out->start), ctx->b_start.p, (size_t)n));
-  GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->read_len), d_len.p, (size_t)n));
-  GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->n_cigar_ops), d_ops.p, (size_t)n));
-  GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->cigar), ctx->b_cigar.p, (size_t)n_cigar));
+  // the narrow columns, where the batch allows them
+  bool narrow_start = false, narrow_ops = false;
+  int64_t uniform_len = 0, n_wire = 0;
+  DevBuf d_rel, d_ops8, d_woff, d_wire, d_nflags;
+  Free fr2{{&d_rel, &d_ops8, &d_woff, &d_wire, &d_nflags}};
+  if (n && ctx->opt_compact_narrow) {
+    GUAC_TRY(upload(ctx, ctx->u_runs_f, static_cast<const int64_t*>(hf), spans.size() + 1));
+    GUAC_TRY(ensure(ctx, d_rel, (size_t)n * sizeof(uint32_t)));
+    GUAC_TRY(ensure(ctx, d_ops8, (size_t)n + 16));
+    GUAC_TRY(ensure(ctx, d_nflags, sizeof(int)));
+    CUDA_TRY(ctx, cudaMemsetAsync(d_nflags.p, 0, sizeof(int), ctx->stream));
+    compact::narrow_columns_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(
+        n, ctx->R.start, ctx->u_runs_f.as<int64_t>(), (int)spans.size(), ctx->R.seq_off, ctx->R.cigar_off, ctx->R.cigar,
+        d_rel.as<uint32_t>(), d_ops8.as<uint8_t>(), d_nflags.as<int>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    int nflags = 0;
+    uint64_t first_offsets[2] = {0, 0};
+    CUDA_TRY(ctx, cudaMemcpyAsync(&nflags, d_nflags.p, sizeof nflags, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(first_offsets, ctx->R.seq_off, sizeof first_offsets, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    narrow_start = !(nflags & 1);
+    narrow_ops = !(nflags & 2);
+    if (!(nflags & 4) && first_offsets[1] - first_offsets[0] > 0) uniform_len = (int64_t)(first_offsets[1] - first_offsets[0]);
+    if (narrow_ops) {
+      GUAC_TRY(ensure(ctx, d_woff, (size_t)(n + 1) * sizeof(int64_t)));
+      GUAC_TRY((device_scan<true, uint8_t>(ctx, d_ops8.as<uint8_t>(), d_woff.as<int64_t>(), n, OpSum(), d_woff.as<int64_t>() + n)));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&n_wire, d_woff.as<int64_t>() + n, sizeof n_wire, cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+      GUAC_TRY(ensure(ctx, d_wire, (size_t)n_wire * sizeof(uint32_t) + 16));
+      compact::wire_cigar_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, d_ops8.as<uint8_t>(), ctx->R.cigar_off, ctx->R.cigar,
+                                                                            d_woff.as<int64_t>(), d_wire.as<uint32_t>());
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+    }
+  }
+  if (narrow_start) {
+    GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->start_rel), d_rel.p, (size_t)n));
+    void* hb = nullptr;
+    GUAC_TRY(pinned_alloc(ctx, &hb, std::max<size_t>(spans.size() * sizeof(int64_t), 16)));
+    for (size_t i = 0; i < spans.size(); ++i)  // the run's base = the start of its first read
+      CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<int64_t*>(hb) + i, ctx->R.start + spans[i].second.first, sizeof(int64_t),
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+    out->run_start_base = static_cast<int64_t*>(hb);
+  } else {
+    GUAC_TRY(host_out(ctx, const_cast<int64_t**>(&out->start), ctx->b_start.p, (size_t)n));
+  }
+  if (uniform_len) out->uniform_read_len = (int32_t)uniform_len;
+  else GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->read_len), d_len.p, (size_t)n));
+  if (narrow_ops) {
+    GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->n_cigar_ops8), d_ops8.p, (size_t)n));
+    GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->cigar), d_wire.p, (size_t)n_wire));
+  } else {
+    GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->n_cigar_ops), d_ops.p, (size_t)n));
+    GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->cigar), ctx->b_cigar.p, (size_t)n_cigar));
+  }
   GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->bases2), ctx->b_bases2.p, (size_t)((n_bases + 3) / 4)));
   out->n_exc = ctx->R.n_exc;
   GUAC_TRY(host_out(ctx, const_cast<uint64_t**>(&out->exc_pos), ctx->b_exc_pos.p, (size_t)ctx->R.n_exc));

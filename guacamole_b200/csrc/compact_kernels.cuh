@@ -20,6 +20,46 @@ __global__ void contig_from_runs_kernel(int64_t n, const int32_t* __restrict__ r
   contig_id[r] = run_contig[lo];
 }
 
+// narrow start column: start = base of the read's contig run + a 32-bit offset
+__global__ void starts_from_rel_kernel(int64_t n, const int64_t* __restrict__ run_base, const int64_t* __restrict__ run_first, int n_runs,
+                                       const uint32_t* __restrict__ rel, int64_t* __restrict__ start) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  int lo = 0, hi = n_runs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (run_first[mid] <= r) lo = mid; else hi = mid - 1;
+  }
+  start[r] = run_base[lo] + (int64_t)rel[r];
+}
+
+// every read has `len` bases: offsets without a scan
+__global__ void uniform_offsets_kernel(int64_t n_plus_1, uint64_t len, uint64_t* __restrict__ seq_off) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_plus_1) seq_off[i] = (uint64_t)i * len;
+}
+
+// narrow operator counts: a read with count 0 has one (implicit) operator
+__global__ void effective_ops_kernel(int64_t n, const uint8_t* __restrict__ ops8, uint8_t* __restrict__ eff) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n) eff[r] = ops8[r] ? ops8[r] : (uint8_t)1;
+}
+// ... and the full operator array: the implicit operator is `read length` M, the others are copied from the wire
+__global__ void cigar_from_ops8_kernel(int64_t n, const uint8_t* __restrict__ ops8, const uint32_t* __restrict__ cigar_off,
+                                       const int64_t* __restrict__ wire_off, const uint32_t* __restrict__ wire,
+                                       const uint64_t* __restrict__ seq_off, uint32_t* __restrict__ cigar) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const uint32_t o = cigar_off[r];
+  const int k = ops8[r];
+  if (k == 0) {
+    cigar[o] = (uint32_t)(seq_off[r + 1] - seq_off[r]) << 4;  // operator code 0 = M
+  } else {
+    const int64_t w = wire_off[r];
+    for (int j = 0; j < k; ++j) cigar[o + j] = wire[w + j];
+  }
+}
+
 __global__ void narrow_offsets_kernel(int64_t n, const int64_t* __restrict__ in, uint32_t* __restrict__ out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = (uint32_t)in[i];
@@ -75,6 +115,40 @@ __global__ void lengths_kernel(int64_t n, const uint64_t* __restrict__ seq_off, 
   if (len > 65535 || ops > 65535) *too_long = 1;
   read_len[r] = (uint16_t)len;
   n_ops[r] = (uint16_t)ops;
+}
+
+// narrow columns of the export: 32-bit start offsets within the contig run, 8-bit operator counts with the implicit
+// single-M form; flags bit 0: an offset beyond 32 bits, bit 1: a read with more than 255 operators, bit 2: reads of
+// different lengths
+__global__ void narrow_columns_kernel(int64_t n, const int64_t* __restrict__ start, const int64_t* __restrict__ run_first, int n_runs,
+                                      const uint64_t* __restrict__ seq_off, const uint32_t* __restrict__ cigar_off,
+                                      const uint32_t* __restrict__ cigar, uint32_t* __restrict__ rel, uint8_t* __restrict__ ops8,
+                                      int* __restrict__ flags) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  int lo = 0, hi = n_runs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (run_first[mid] <= r) lo = mid; else hi = mid - 1;
+  }
+  const int64_t d = start[r] - start[run_first[lo]];
+  if (d < 0 || d > 0xFFFFFFFFll) atomicOr(flags, 1);
+  rel[r] = (uint32_t)d;
+  const uint64_t len = seq_off[r + 1] - seq_off[r];
+  const uint32_t c0 = cigar_off[r], ops = cigar_off[r + 1] - c0;
+  if (ops > 255) atomicOr(flags, 2);
+  if (len != seq_off[1] - seq_off[0]) atomicOr(flags, 4);
+  const bool implicit = ops == 1 && cigar[c0] == ((uint32_t)len << 4) && len < (1u << 28);
+  ops8[r] = implicit ? (uint8_t)0 : (uint8_t)ops;
+}
+__global__ void wire_cigar_kernel(int64_t n, const uint8_t* __restrict__ ops8, const uint32_t* __restrict__ cigar_off,
+                                  const uint32_t* __restrict__ cigar, const int64_t* __restrict__ wire_off, uint32_t* __restrict__ wire) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const int k = ops8[r];
+  const uint32_t o = cigar_off[r];
+  const int64_t w = wire_off[r];
+  for (int j = 0; j < k; ++j) wire[w + j] = cigar[o + j];
 }
 
 __global__ void qual_histogram_kernel(uint64_t n_bases, const uint8_t* __restrict__ qual, unsigned int* __restrict__ present) {

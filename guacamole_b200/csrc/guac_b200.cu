@@ -86,6 +86,8 @@ struct guac_ctx {
   DevBuf b_bins, b_bin_count, b_medium;  // stream path: per-read event slots and counts; list of multi-operator reads
   int64_t n_medium = 0;
   DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
+  DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
+  int64_t opt_compact_narrow = 1;
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
 };
@@ -507,7 +509,8 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->fork) cudaEventDestroy(ctx->fork);
   if (ctx->join) cudaEventDestroy(ctx->join);
   for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
-                    &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off})
+                    &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
+                    &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire})
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
     if (kv.second.ref2) cudaFree(kv.second.ref2);
@@ -1556,6 +1559,8 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
     ctx->opt_ss_impl = value;
   } else if (n == "ss_force_fallback_mod") {
     ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
+  } else if (n == "compact_narrow") {
+    ctx->opt_compact_narrow = value != 0;
   } else if (n == "ss_rank_max") {
     ctx->opt_ss_rank_max = value < 0 ? SS_RANK_MAX : std::min<int64_t>(value, SS_RANK_MAX);
   } else {

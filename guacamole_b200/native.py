@@ -229,11 +229,22 @@ class ReadBatchCompactC(C.Structure):
                 ("run_first_read", i64p), ("start", i64p), ("read_len", u16p), ("n_cigar_ops", u16p), ("cigar", u32p),
                 ("bases2", u8p), ("n_exc", C.c_int64), ("exc_pos", u64p), ("exc_base", u8p), ("qual_bits", C.c_int32),
                 ("_pad", C.c_int32), ("qual_table", C.c_uint8 * 16), ("qual", u8p), ("mapq", u8p), ("flags", u8p),
-                ("sample_id", u8p)]
+                ("sample_id", u8p),
+                # narrow forms of start / n_cigar_ops / read_len (NULL / 0: the wide column is given)
+                ("run_start_base", i64p), ("start_rel", u32p), ("n_cigar_ops8", u8p), ("uniform_read_len", C.c_int32),
+                ("_pad2", C.c_int32)]
+
+    def wire_bytes(self, n_bases: int, n_cigar_words: int) -> int:
+        """Bytes this batch puts on the wire (what guac_reads_upload_compact copies to the device)."""
+        n = int(self.n_reads)
+        per_read = (4 if self.start_rel else 8) + (0 if self.uniform_read_len > 0 else 2) + (1 if self.n_cigar_ops8 else 2) + 3
+        q = n_bases if self.qual_bits == 8 else (n_bases * self.qual_bits + 7) // 8
+        return n * per_read + 4 * n_cigar_words + (n_bases + 3) // 4 + q + 9 * int(self.n_exc) + 20 * int(self.n_contig_runs) + 8
 
 
-def compact_struct(batch: ReadBatch) -> ReadBatchCompactC:
-    """Host-side packer of the compact wire form (numpy); keeps the arrays alive on the returned struct."""
+def compact_struct(batch: ReadBatch, narrow: bool = True) -> ReadBatchCompactC:
+    """Host-side packer of the compact wire form (numpy); keeps the arrays alive on the returned struct.
+    narrow: use the narrow start / operator-count / read-length columns where the batch allows them."""
     if batch.packed is None:
         batch.packed = pack_bases(batch.bases_ascii)
     p = batch.packed
@@ -271,6 +282,24 @@ def compact_struct(batch: ReadBatch) -> ReadBatchCompactC:
     b.run_contig_id, b.run_first_read = ptr(keep["run_contig"], i32p), ptr(keep["run_first"], i64p)
     b.start, b.read_len, b.n_cigar_ops = ptr(batch.start, i64p), ptr(keep["read_len"], u16p), ptr(keep["n_ops"], u16p)
     b.cigar, b.bases2 = ptr(batch.cigar, u32p), ptr(p["bases2"], u8p)
+    if narrow and n:
+        lens = np.diff(batch.seq_off.astype(np.int64))
+        ops = np.diff(batch.cigar_off.astype(np.int64))
+        base = batch.start[first[:-1]].astype(np.int64)  # the first read of a run has its lowest start
+        run_of = np.searchsorted(first, np.arange(n), side="right") - 1
+        rel = batch.start.astype(np.int64) - base[run_of]
+        if rel.min() >= 0 and rel.max() < 2**32:
+            keep["run_base"], keep["rel"] = np.ascontiguousarray(base), rel.astype(np.uint32)
+            b.run_start_base, b.start_rel, b.start = ptr(keep["run_base"], i64p), ptr(keep["rel"], u32p), None
+        if lens.min() == lens.max() and 0 < lens[0] <= 65535:
+            b.uniform_read_len, b.read_len = int(lens[0]), None
+        if ops.max() <= 255 and ops.min() >= 1:
+            first_word = batch.cigar[batch.cigar_off[:-1].astype(np.int64)]
+            implicit = (ops == 1) & (first_word == (lens.astype(np.uint32) << 4)) & (lens < 2**28)
+            ops8 = np.where(implicit, 0, ops).astype(np.uint8)
+            word_keep = np.repeat(~implicit, ops)  # per CIGAR word: does its read keep its words on the wire
+            keep["ops8"], keep["wire"] = ops8, np.ascontiguousarray(batch.cigar[word_keep])
+            b.n_cigar_ops8, b.n_cigar_ops, b.cigar = ptr(keep["ops8"], u8p), None, ptr(keep["wire"], u32p)
     b.n_exc, b.exc_pos, b.exc_base = p["n_exc"], ptr(p["exc_pos"], u64p), ptr(p["exc_base"], u8p)
     b.qual, b.mapq, b.flags, b.sample_id = ptr(keep["qual"], u8p), ptr(batch.mapq, u8p), ptr(batch.flags, u8p), ptr(batch.sample_id, u8p)
     b._keep = keep
@@ -362,7 +391,7 @@ class Context:
 
     def free_reads_compact_struct(self, b: ReadBatchCompactC):
         for name in ("run_contig_id", "run_first_read", "start", "read_len", "n_cigar_ops", "cigar", "bases2", "exc_pos", "exc_base",
-                     "qual", "mapq", "flags", "sample_id"):
+                     "qual", "mapq", "flags", "sample_id", "run_start_base", "start_rel", "n_cigar_ops8"):
             v = getattr(b, name)
             if v:
                 self.lib.guac_free(self.ctx, C.cast(v, C.c_void_p))

@@ -464,6 +464,7 @@ void* guac_stream(guac_ctx* ctx);
  *   "ss_impl"               somatic-standard: 2 = read pass + locus pass as two kernels (default), 0 = both in one tile
  *                           kernel, 1 = generic gather kernel only; all three fall back to the gather kernel per tile
  *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook)
+ *   "compact_narrow"        1 (default): guac_reads_export_compact emits the narrow columns where the batch allows; 0: never
  *   "ss_rank_max"           somatic-standard puts more calls than this in output order on the host instead of on the
  *                           device (test hook; default and maximum 32768, negative restores the default) */
 int guac_set_option(guac_ctx* ctx, const char* name, int64_t value);
@@ -491,8 +492,8 @@ int guac_reads_export(guac_ctx* ctx, guac_read_batch* out);
  * guac_read_batch with everything derivable left out — offsets become lengths (prefix sums run on the device),
  * the per-read contig id becomes runs, the not-ACGT mask is rebuilt from the exception list, and base qualities
  * travel as 2- or 4-bit codes into a table when the batch holds at most 4 / 16 distinct qualities (binned
- * Illumina qualities; otherwise one byte per base as before).  100-base single-operator reads: 69 / 94 B per read
- * instead of 168.5.  Lossless; replaces the same `Iterator[MappedRead]` as guac_reads_upload.
+ * Illumina qualities; otherwise one byte per base as before).  100-base single-operator reads: 58 / 83 B per read with
+ * the narrow columns at the end of the struct (69 / 94 B without) instead of 168.5.  Lossless; replaces the same `Iterator[MappedRead]` as guac_reads_upload.
  */
 typedef struct {
   int64_t n_reads;
@@ -515,6 +516,14 @@ typedef struct {
   const uint8_t* mapq;            /* [n_reads] */
   const uint8_t* flags;           /* [n_reads] */
   const uint8_t* sample_id;       /* [n_reads] */
+  /* Narrower forms of three columns (each optional: NULL / 0 = the wide column above is given instead).
+   * 100-base single-operator reads then travel in 58 B per read. */
+  const int64_t* run_start_base;  /* [n_contig_runs], with start_rel */
+  const uint32_t* start_rel;      /* [n_reads] start = run_start_base[run of the read] + start_rel; replaces `start` */
+  const uint8_t* n_cigar_ops8;    /* [n_reads] 0: the CIGAR is one M operator over all the read's bases and has no word in
+                                   * `cigar`; k > 0: the read's k words in `cigar`.  Replaces `n_cigar_ops` */
+  int32_t uniform_read_len;       /* > 0: every read has this many bases; replaces `read_len` */
+  int32_t _pad2;
 } guac_read_batch_compact;
 
 int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* batch);
