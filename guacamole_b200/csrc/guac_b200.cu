@@ -970,7 +970,8 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     if (st == GUAC_OK) st = ensure(ctx, ctx->u_off, (size_t)nc * sizeof(guac_ss_call));
     if (st == GUAC_OK) {
       if (nc <= ctx->opt_ss_rank_max) {
-        ss_call_rank_kernel<<<blocks_for(nc, 256), 256, 0, ctx->stream>>>(ctx->b_calls.as<SSCallDev>(), nc, ctx->u_flag.as<int>());
+        cudaMemsetAsync(ctx->u_flag.p, 0, (size_t)nc * sizeof(int), ctx->stream);
+        ss_call_rank_kernel<<<dim3(blocks_for(nc, 256), SS_RANK_SPLIT), 256, 0, ctx->stream>>>(ctx->b_calls.as<SSCallDev>(), nc, ctx->u_flag.as<int>());
         ctx->launches += 1;
       } else {  // too many for the quadratic kernel: the host sorts the slots
         std::vector<SSCallDev> tmp((size_t)nc);

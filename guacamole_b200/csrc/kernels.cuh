@@ -554,19 +554,22 @@ __device__ inline int count_of_mismatches(const ReadsView& R, int64_t r, const R
 // Position of every call in (range order, locus) order = the number of calls with a smaller slot (slots are distinct: one
 // call per locus).  Quadratic, for the few thousand calls of a partition; the host sorts instead beyond SS_RANK_MAX.
 constexpr int SS_RANK_MAX = 32768;
-__global__ void __launch_bounds__(256) ss_call_rank_kernel(const SSCallDev* __restrict__ calls, int n, int* __restrict__ rank) {
+constexpr int SS_RANK_SPLIT = 8;  // blockIdx.y: the slots are compared in this many slices, partial counts added up
+__global__ void __launch_bounds__(256) ss_call_rank_kernel(const SSCallDev* __restrict__ calls, int n, int* __restrict__ rank /* zeroed */) {
   __shared__ int64_t s_slot[256];
   const int i = blockIdx.x * 256 + threadIdx.x;
   const int64_t mine = i < n ? calls[i].slot : 0;
+  const int per = ((n + SS_RANK_SPLIT - 1) / SS_RANK_SPLIT + 255) & ~255;  // slice length, whole tiles of 256
+  const int j0 = blockIdx.y * per, j1 = min(n, j0 + per);
   int below = 0;
-  for (int base = 0; base < n; base += 256) {
+  for (int base = j0; base < j1; base += 256) {
     __syncthreads();
-    s_slot[threadIdx.x] = base + threadIdx.x < n ? calls[base + threadIdx.x].slot : INT64_MAX;
+    s_slot[threadIdx.x] = base + threadIdx.x < j1 ? calls[base + threadIdx.x].slot : INT64_MAX;
     __syncthreads();
 #pragma unroll 8
     for (int k = 0; k < 256; ++k) below += s_slot[k] < mine;
   }
-  if (i < n) rank[i] = below;
+  if (i < n && below) atomicAdd(rank + i, below);
 }
 
 constexpr int MM_BINS = 1024;
