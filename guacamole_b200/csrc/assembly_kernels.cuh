@@ -240,7 +240,9 @@ __global__ void __launch_bounds__(256) asm_count_kernel(ReadsView R, AsmWindow* 
   const int cap = w.table_cap, K = P.K;
   __shared__ int s_nodes;
   __shared__ float s_inv[ASM_MAX_K];
-  __shared__ uint8_t s_code[8][ASM_STAGE];
+  // the read's base codes as one bit stream, 3 bits per base, first base in the most significant bits of word 0: a k-mer
+  // word (21 bases) is then 63 consecutive bits of the stream, cut out with two loads and a funnel shift
+  __shared__ unsigned long long s_bits[8][ASM_STAGE * 3 / 64 + 2];
   __shared__ uint8_t s_qual[8][ASM_STAGE];
   if (threadIdx.x == 0) s_nodes = 0;
   for (int p = threadIdx.x; p < K; p += blockDim.x) s_inv[p] = __fdiv_rn(1.0f, (float)(p + 1));
@@ -271,28 +273,48 @@ __global__ void __launch_bounds__(256) asm_count_kernel(ReadsView R, AsmWindow* 
       if (n_at <= 0) continue;
       const uint64_t base0 = __ldg(R.seq_off + r);
       if (len <= ASM_STAGE) {
-        bool bad = false;
+        bool bad = false, zero_q = false;
+        const int n_words = (3 * len + 63) / 64 + 1;
+        for (int i = lane; i < n_words; i += 32) s_bits[warp][i] = 0ull;
+        __syncwarp();
         for (int i = lane; i < len; i += 32) {
           const int c = asm_base_code(read_base(R, base0 + i));
           bad |= c < 0;
-          s_code[warp][i] = (uint8_t)c;
-          s_qual[warp][i] = __ldg(R.qual + base0 + i);
+          const uint8_t q = __ldg(R.qual + base0 + i);
+          zero_q |= q == 0;
+          s_qual[warp][i] = q;
+          const int t = 3 * i, sh = t & 63;  // stream bits t .. t+2
+          const unsigned long long cc = (unsigned long long)(c & 7);
+          atomicOr(&s_bits[warp][t >> 6], sh <= 61 ? cc << (61 - sh) : cc >> (sh - 61));
+          if (sh > 61) atomicOr(&s_bits[warp][(t >> 6) + 1], cc << (125 - sh));
         }
         bad = __any_sync(0xffffffffu, bad);
+        zero_q = __any_sync(0xffffffffu, zero_q);
         __syncwarp();
         if (bad) {
           if (lane == 0) report_error(err, DERR_ASM_BASE, w.contig_id, w.locus, r);
         } else {
-          const int per = (n_at + 31) / 32, a0 = lane * per, a1 = min(n_at, a0 + per);
-          Kmer k;
-          for (int at = a0; at < a1; ++at) {
-            if (at == a0) {
-              k.clear();
-              for (int p = 0; p < K; ++p) k.set(p, s_code[warp][at + p]);
-            } else {
-              k = k.shifted_left(K, s_code[warp][at + K - 1]);
+          // breeze's mean of the k-mer's qualities is > 0 exactly when one of them is: the running mean starts at the
+          // first quality and never returns to 0 from a positive value (every step keeps at least (1 - 1/n) of it).  So a
+          // threshold below 0 passes every k-mer, and the default threshold 0 every k-mer of a read without a zero quality.
+          const bool all_pass = P.min_mean_kmer_quality < 0 || (P.min_mean_kmer_quality == 0 && !zero_q);
+          for (int at = lane; at < n_at; at += 32) {
+            if (!all_pass && !(asm_mean_quality(s_qual[warp] + at, K, s_inv) > (float)P.min_mean_kmer_quality)) continue;
+            Kmer k;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int nb = min(21, K - 21 * j);  // bases of the k-mer in word j
+              unsigned long long v = 0ull;
+              if (nb > 0) {
+                const int t0 = 3 * (at + 21 * j), sh = t0 & 63;
+                v = s_bits[warp][t0 >> 6] << sh;
+                if (sh) v |= s_bits[warp][(t0 >> 6) + 1] >> (64 - sh);
+                v >>= 1;
+                if (nb < 21) v &= ~0ull << (63 - 3 * nb);
+              }
+              k.w[j] = v;
             }
-            if (asm_mean_quality(s_qual[warp] + at, K, s_inv) > (float)P.min_mean_kmer_quality) visit(pass, k, r);
+            visit(pass, k, r);
           }
         }
         __syncwarp();
