@@ -104,9 +104,16 @@ germline_locus_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile*
   const int tsel = (int)blockIdx.x * WARPS_PER_CTA + warp;
   if (tsel >= n_heavy) return;
   const unsigned FULL = 0xffffffffu;
-  const Tile tile = heavy[tsel];
+  Tile tile = heavy[tsel];
   const RefView ref = refs[tile.ref_index];
   const int64_t x = tile.locus0;
+  {
+    // the single-locus tile arrives with the read span of the tile it came from: narrow it to the reads that can overlap
+    // the locus (start <= x, running-max end > x); every pass below, and the evidence kernel after it, walks this span
+    const int64_t key = ((int64_t)tile.contig_id << 40) | x;
+    tile.read_hi = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.start + i) > x; });
+    tile.read_lo = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.runmax_key + i) > key; });
+  }
 
   // pass 1: distinct alleles of the pileup (one table entry per lane), depth, active-region votes
   uint64_t tkey = 0;

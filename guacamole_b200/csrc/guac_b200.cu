@@ -88,6 +88,7 @@ struct guac_ctx {
   DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
   DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
   int64_t opt_compact_narrow = 1;
+  DevBuf g_active, g_jobs, g_evs, g_strings;  // scratch of guac_germline_standard, kept between calls
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
 };
@@ -510,7 +511,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->join) cudaEventDestroy(ctx->join);
   for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
                     &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
-                    &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire})
+                    &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings})
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
     if (kv.second.ref2) cudaFree(kv.second.ref2);
@@ -1314,6 +1315,7 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   if (!ctx || !params || !out_calls || !n_calls || !out_arena || !arena_len || !out_active_loci || !n_active) return GUAC_E_INVALID_INPUT;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   using TCfg = TileCfg<GUAC_TK_TL>;
+  Trace trace;
   if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
   if (params->sample_id < 0 || params->sample_id >= ctx->n_samples) return fail(ctx, GUAC_E_INVALID_INPUT, "bad sample id");
   Plan plan;
@@ -1400,7 +1402,7 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   int* d_nc = ctx->b_ncalls.as<int>();
   const int max_calls = std::max(n_heavy, 1);
   GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(GLCallDev)));
-  DevBuf d_active;
+  DevBuf& d_active = ctx->g_active;  // scratch of this entry point lives in the context: no cudaMalloc / cudaFree per call
   GUAC_TRY(ensure(ctx, d_active, (size_t)max_calls * 2 * sizeof(long long)));
   CUDA_TRY(ctx, cudaMemsetAsync(d_nc, 0, 2 * sizeof(int), ctx->stream));
   if (n_heavy > 0) {
@@ -1417,20 +1419,47 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   CUDA_TRY(ctx, cudaMemcpyAsync(both, d_nc, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   {
     int st = check_device_error(ctx);
-    if (st != GUAC_OK) {
-      cudaFree(d_active.p);
-      return st;
-    }
+    if (st != GUAC_OK) return st;
   }
   nc = both[0];
   na = both[1];
-  std::vector<GLCallDev> calls((size_t)nc);
+  trace.mark("per-locus kernels");
+  // the records come over through pinned memory and stay where they land; (range order, locus) order = slot order is
+  // an index sort
+  struct Pinned {
+    guac_ctx* ctx;
+    std::vector<void*> p;
+    ~Pinned() {
+      for (void* q : p) guac_free(ctx, q);
+    }
+    int get(void** out, size_t bytes) {
+      GUAC_TRY(pinned_alloc(ctx, out, std::max<size_t>(bytes, 16)));
+      p.push_back(*out);
+      return GUAC_OK;
+    }
+  } pinned{ctx, {}};
+  GLCallDev* calls_raw = nullptr;
+  GUAC_TRY(pinned.get(reinterpret_cast<void**>(&calls_raw), (size_t)nc * sizeof(GLCallDev)));
   std::vector<long long> active((size_t)na * 2);
-  if (nc) CUDA_TRY(ctx, cudaMemcpyAsync(calls.data(), ctx->b_calls.p, (size_t)nc * sizeof(GLCallDev), cudaMemcpyDeviceToHost, ctx->stream));
+  if (nc) CUDA_TRY(ctx, cudaMemcpyAsync(calls_raw, ctx->b_calls.p, (size_t)nc * sizeof(GLCallDev), cudaMemcpyDeviceToHost, ctx->stream));
   if (na) CUDA_TRY(ctx, cudaMemcpyAsync(active.data(), d_active.p, (size_t)na * 2 * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  cudaFree(d_active.p);
-  std::sort(calls.begin(), calls.end(), [](const GLCallDev& a, const GLCallDev& b) { return a.slot < b.slot; });
+  std::vector<std::pair<int64_t, int>> order((size_t)nc);
+  for (int i = 0; i < nc; ++i) order[(size_t)i] = {calls_raw[i].slot, i};
+  std::sort(order.begin(), order.end());
+  struct CallsInOrder {  // range-for over the records in slot order
+    const GLCallDev* raw;
+    const std::vector<std::pair<int64_t, int>>* order;
+    struct It {
+      const CallsInOrder* c;
+      size_t i;
+      const GLCallDev& operator*() const { return c->raw[(*c->order)[i].second]; }
+      It& operator++() { ++i; return *this; }
+      bool operator!=(const It& o) const { return i != o.i; }
+    };
+    It begin() const { return It{this, 0}; }
+    It end() const { return It{this, order->size()}; }
+  } calls{calls_raw, &order};
   // active loci sorted by (contig, locus) like the visiting order within a contig
   {
     std::vector<std::pair<long long, long long>> v;
@@ -1441,44 +1470,64 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
       active[2 * i + 1] = v[i].second;
     }
   }
+  trace.mark("records to the host, sorted");
   // AlleleEvidence of every called allele
-  std::vector<EvidenceJob> jobs;
-  for (auto& c : calls)
-    for (int t = 0; t < c.n_called; ++t) {
-      EvidenceJob j;
-      j.locus = c.locus;
-      j.read_lo = c.read_lo;
-      j.read_hi = c.read_hi;
-      j.key = c.called[t].key;
-      j.contig_id = c.contig_id;
-      j.ref_index = c.ref_index;
-      j.sample = params->sample_id;
-      j._pad = 0;
-      j.probability = std::exp(c.log_probability);  // :247
-      jobs.push_back(j);
-    }
-  std::vector<guac_allele_evidence> evs(jobs.size());
-  if (!jobs.empty()) {
-    DevBuf d_jobs, d_evs;
-    GUAC_TRY(upload(ctx, d_jobs, jobs.data(), jobs.size()));
-    GUAC_TRY(ensure(ctx, d_evs, jobs.size() * sizeof(guac_allele_evidence)));
-    allele_evidence_kernel<<<(unsigned)jobs.size(), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), d_jobs.as<EvidenceJob>(),
-                                                                             d_evs.as<guac_allele_evidence>(), ctx->b_err.as<DeviceError>());
+  size_t n_jobs = 0;
+  for (const GLCallDev& c : calls) n_jobs += (size_t)c.n_called;
+  EvidenceJob* jobs = nullptr;
+  guac_allele_evidence* evs = nullptr;
+  GUAC_TRY(pinned.get(reinterpret_cast<void**>(&jobs), n_jobs * sizeof(EvidenceJob)));
+  GUAC_TRY(pinned.get(reinterpret_cast<void**>(&evs), n_jobs * sizeof(guac_allele_evidence)));
+  {
+    size_t k = 0;
+    for (const GLCallDev& c : calls)
+      for (int t = 0; t < c.n_called; ++t) {
+        EvidenceJob& j = jobs[k++];
+        j.locus = c.locus;
+        j.read_lo = c.read_lo;
+        j.read_hi = c.read_hi;
+        j.key = c.called[t].key;
+        j.contig_id = c.contig_id;
+        j.ref_index = c.ref_index;
+        j.sample = params->sample_id;
+        j._pad = 0;
+        j.probability = std::exp(c.log_probability);  // :247
+      }
+  }
+  if (n_jobs) {
+    DevBuf &d_jobs = ctx->g_jobs, &d_evs = ctx->g_evs;
+    GUAC_TRY(upload(ctx, d_jobs, jobs, n_jobs));
+    GUAC_TRY(ensure(ctx, d_evs, n_jobs * sizeof(guac_allele_evidence)));
+    allele_evidence_kernel<<<(unsigned)n_jobs, 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), d_jobs.as<EvidenceJob>(),
+                                                                     d_evs.as<guac_allele_evidence>(), ctx->b_err.as<DeviceError>());
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaMemcpyAsync(evs.data(), d_evs.p, jobs.size() * sizeof(guac_allele_evidence), cudaMemcpyDeviceToHost, ctx->stream));
-    int st = check_device_error(ctx);
-    cudaFree(d_jobs.p);
-    cudaFree(d_evs.p);
-    if (st != GUAC_OK) return st;
+    CUDA_TRY(ctx, cudaMemcpyAsync(evs, d_evs.p, n_jobs * sizeof(guac_allele_evidence), cudaMemcpyDeviceToHost, ctx->stream));
+    GUAC_TRY(check_device_error(ctx));
   }
+  trace.mark("evidence");
   // keep calls with phredScaledLikelihood > min (:147); lay out the allele strings
   auto phred = [](double probability) {  // util/PhredUtils.scala:7-14 over ADAM's successProbabilityToPhred
     const double p = std::min(1 - 1e-16, probability);
     return (int)std::floor(-10.0 * std::log10(1.0 - p) + 0.5);
   };
-  std::vector<guac_called_allele> out;
-  std::vector<SJStringJob> strings;
+  guac_called_allele* out = nullptr;  // at most one record per job, straight into the pinned buffer the caller receives
+  {
+    void* hp = nullptr;
+    GUAC_TRY(pinned_alloc(ctx, &hp, std::max<size_t>(n_jobs * sizeof(guac_called_allele), 16)));
+    out = static_cast<guac_called_allele*>(hp);
+  }
+  size_t n_out = 0, n_strings = 0;
+  SJStringJob* strings = nullptr;
+  {
+    void* hp = nullptr;
+    int st = pinned.get(&hp, 2 * n_jobs * sizeof(SJStringJob));
+    if (st != GUAC_OK) {
+      guac_free(ctx, out);
+      return st;
+    }
+    strings = static_cast<SJStringJob*>(hp);
+  }
   uint32_t arena_off = 0;
   auto add_string = [&](int kind, int64_t a, int32_t b, int32_t len, uint32_t& off, uint32_t& out_len) {
     SJStringJob j;
@@ -1487,13 +1536,13 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
     j.len = len;
     j.arena_off = arena_off;
     j.kind = kind;
-    strings.push_back(j);
+    strings[n_strings++] = j;
     off = arena_off;
     out_len = (uint32_t)len;
     arena_off += (uint32_t)len;
   };
   size_t ji = 0;
-  for (auto& c : calls)
+  for (const GLCallDev& c : calls)
     for (int t = 0; t < c.n_called; ++t, ++ji) {
       if (!(phred(evs[ji].probability) > params->min_phred_scaled_likelihood)) continue;
       const GLAlleleDev& a = c.called[t];
@@ -1514,30 +1563,33 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
         add_string(1, c.locus, c.ref_index, a.indel_len + 1, g.ref_off, g.ref_len);
         add_string(1, c.locus, c.ref_index, 1, g.alt_off, g.alt_len);
       }
-      out.push_back(g);
+      out[n_out++] = g;
     }
   *arena_len = arena_off;
-  if (!strings.empty()) {
-    DevBuf d_strings;
-    GUAC_TRY(upload(ctx, d_strings, strings.data(), strings.size()));
-    GUAC_TRY(ensure(ctx, ctx->b_arena, arena_off + 16));
-    sj_strings_kernel<<<blocks_for((int64_t)strings.size(), 128), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(),
-                                                                                         d_strings.as<SJStringJob>(), (int)strings.size(),
-                                                                                         ctx->b_arena.as<char>());
-    ctx->launches += 1;
-    CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_strings.p);
+  int st_tail = GUAC_OK;
+  if (n_strings) {
+    DevBuf& d_strings = ctx->g_strings;
+    st_tail = upload(ctx, d_strings, strings, n_strings);
+    if (st_tail == GUAC_OK) st_tail = ensure(ctx, ctx->b_arena, arena_off + 16);
+    if (st_tail == GUAC_OK) {
+      sj_strings_kernel<<<blocks_for((int64_t)n_strings, 128), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(),
+                                                                                      d_strings.as<SJStringJob>(), (int)n_strings,
+                                                                                      ctx->b_arena.as<char>());
+      ctx->launches += 1;
+      if (cudaGetLastError() != cudaSuccess) st_tail = fail(ctx, GUAC_E_CUDA, "launch of the string kernel failed");
+    }
   }
-  GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)arena_off));
-  void* hc = nullptr;
+  trace.mark("strings");
   void* hact = nullptr;
-  GUAC_TRY(pinned_alloc(ctx, &hc, std::max<size_t>(out.size() * sizeof(guac_called_allele), 16)));
-  GUAC_TRY(pinned_alloc(ctx, &hact, std::max<size_t>(active.size() * sizeof(int64_t), 16)));
-  if (!out.empty()) std::memcpy(hc, out.data(), out.size() * sizeof(guac_called_allele));
+  if (st_tail == GUAC_OK) st_tail = host_out(ctx, out_arena, ctx->b_arena.p, (size_t)arena_off);
+  if (st_tail == GUAC_OK) st_tail = pinned_alloc(ctx, &hact, std::max<size_t>(active.size() * sizeof(int64_t), 16));
+  if (st_tail != GUAC_OK) {
+    guac_free(ctx, out);
+    return st_tail;
+  }
   if (!active.empty()) std::memcpy(hact, active.data(), active.size() * sizeof(int64_t));
-  *out_calls = (guac_called_allele*)hc;
-  *n_calls = (int64_t)out.size();
+  *out_calls = out;
+  *n_calls = (int64_t)n_out;
   *out_active_loci = (int64_t*)hact;
   *n_active = na;
   if (out_n_visited) {
@@ -1547,6 +1599,7 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
     *out_n_visited = (int64_t)v;
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  trace.mark("out");
   return GUAC_OK;
 }
 
