@@ -14,6 +14,7 @@
 #include <set>
 #include <string>
 #include <tuple>
+#include <thread>
 #include <vector>
 
 #include "../../include/guac_b200.h"
@@ -1248,14 +1249,37 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     out_len = (uint32_t)len;
     arena_off += (uint32_t)len;
   };
-  size_t job_i = 0;
+  // The per-site arithmetic (posteriors, annotations, emit policy) is independent from site to site: it runs on the
+  // host's cores in slices of the site list; the layout of the emitted records below stays serial and in site order.
+  std::vector<size_t> job_start((size_t)n_sites + 1, 0);
+  for (int oi = 0; oi < n_sites; ++oi) job_start[(size_t)oi + 1] = job_start[(size_t)oi] + (size_t)sites[order[(size_t)oi]].n_alleles;
+  std::vector<std::vector<joint::Record>> emitted_by_site((size_t)n_sites);
+  {
+    auto evaluate_sites = [&](int lo, int hi) {
+      std::vector<joint::Record> all;
+      for (int oi = lo; oi < hi; ++oi) {
+        const SJSiteDev& site = sites[order[(size_t)oi]];
+        all.clear();
+        for (int a = 0; a < site.n_alleles; ++a)
+          all.push_back(joint::evaluate(*params, site, a,
+                                        *reinterpret_cast<const SJEvidenceDev*>(raw + (job_start[(size_t)oi] + (size_t)a) * raw_stride)));
+        emitted_by_site[(size_t)oi] = joint::emit(*params, site.forced != 0, all);
+      }
+    };
+    const int n_threads = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)std::thread::hardware_concurrency(), 32, (int64_t)n_sites / 2048}));
+    if (n_threads <= 1) {
+      evaluate_sites(0, n_sites);
+    } else {
+      std::vector<std::thread> pool;
+      const int per = (n_sites + n_threads - 1) / n_threads;
+      for (int t = 0; t < n_threads; ++t) pool.emplace_back(evaluate_sites, std::min(n_sites, t * per), std::min(n_sites, (t + 1) * per));
+      for (auto& th : pool) th.join();
+    }
+  }
   int site_index = 0;
   for (int oi = 0; oi < n_sites; ++oi) {
     const SJSiteDev& site = sites[order[(size_t)oi]];
-    std::vector<joint::Record> all;
-    for (int a = 0; a < site.n_alleles; ++a, ++job_i)
-      all.push_back(joint::evaluate(*params, site, a, *reinterpret_cast<const SJEvidenceDev*>(raw + job_i * raw_stride)));
-    std::vector<joint::Record> emitted = joint::emit(*params, site.forced != 0, all);
+    std::vector<joint::Record>& emitted = emitted_by_site[(size_t)oi];
     if (emitted.empty()) continue;
     for (auto& rec : emitted) {
       const SJAlleleDev& al = site.alleles[rec.raw->allele];
