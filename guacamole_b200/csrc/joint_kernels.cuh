@@ -143,9 +143,16 @@ sj_discover_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tsel = tile_per_warp ? (int)blockIdx.x * WARPS_PER_CTA + warp : (int)blockIdx.x;
   if (tsel >= n_tiles) return;  // no block-wide barrier below
-  const Tile tile = tiles[tile_list ? tile_list[tsel] : tsel];
+  Tile tile = tiles[tile_list ? tile_list[tsel] : tsel];
   const RefView ref = refs[tile.ref_index];
   const unsigned FULL = 0xffffffffu;
+  if (tile_per_warp && tile.n_loci == 1) {
+    // a single-locus tile arrives with the read span of the tile it came from: narrow it to the reads that can overlap
+    // the locus (start <= x, running-max end > x); the passes below and the evidence kernel after them walk this span
+    const int64_t x = tile.locus0, key = ((int64_t)tile.contig_id << 40) | x;
+    tile.read_hi = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.start + i) > x; });
+    tile.read_lo = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.runmax_key + i) > key; });
+  }
   for (int li = tile_per_warp ? 0 : warp; li < tile.n_loci; li += tile_per_warp ? 1 : WARPS_PER_CTA) {
     const int64_t x = tile.locus0 + li, slot = tile.slot0 + li;
     // visited: any sample's window is non-empty (skipEmpty = true)
