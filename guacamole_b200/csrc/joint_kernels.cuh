@@ -533,13 +533,40 @@ sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P,
     }
   }
   __syncthreads();
-  if (threadIdx.x != 0) return;
-  // assemble: per-sample slots, then the pools (MultiplePileupStats.scala:12-18)
+  // The table is nearly empty (a handful of distinct sequences per site): its used entries are listed first, in table
+  // order, so that the assembly below walks that handful instead of all SJ_TABLE entries once per slot.
+  __shared__ uint16_t s_used[SJ_TABLE];
+  __shared__ int s_warp_total[4], s_n_used;
+  static_assert(SJ_TABLE == 4 * 128, "four table entries per thread of the 128-thread CTA");
+  {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int cnt = 0;
+    for (int k = 0; k < 4; ++k) cnt += tab[4 * threadIdx.x + k].tag != 0;
+    int incl = cnt;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp_total[warp] = incl;
+    __syncthreads();
+    int pos = incl - cnt;
+    for (int w = 0; w < warp; ++w) pos += s_warp_total[w];
+    for (int k = 0; k < 4; ++k)
+      if (tab[4 * threadIdx.x + k].tag != 0) s_used[pos++] = (uint16_t)(4 * threadIdx.x + k);
+    if (threadIdx.x == 127) s_n_used = pos;
+    __syncthreads();
+  }
+  if (threadIdx.x >= S + 2) return;
+  // assemble: per-sample slots, then the pools (MultiplePileupStats.scala:12-18), one thread per slot
   // records are packed with only the S + 2 slots in use (out_stride bytes each)
   SJEvidenceDev& E = *reinterpret_cast<SJEvidenceDev*>(out + (size_t)blockIdx.x * out_stride);
-  E.site = job.x;
-  E.allele = job.y;
-  for (int slot_i = 0; slot_i < S + 2; ++slot_i) {
+  if (threadIdx.x == 0) {
+    E.site = job.x;
+    E.allele = job.y;
+  }
+  const int n_used = s_n_used;
+  {
+    const int slot_i = threadIdx.x;
     SJSlotDev& o = E.slots[slot_i];
     const bool pool = slot_i >= S;
     const int want_kind = slot_i == NP ? GUAC_SJ_NORMAL_DNA : GUAC_SJ_TUMOR_DNA;
@@ -557,8 +584,8 @@ sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P,
     SJDepthDev merged[32];
     int nm = 0;
     bool too_many = false;
-    for (int i = 0; i < SJ_TABLE; ++i) {
-      if (tab[i].tag == 0) continue;
+    for (int u = 0; u < n_used; ++u) {
+      const int i = s_used[u];
       const int s = tab[i].sample;
       if (!(pool ? P.kind[s] == want_kind : s == slot_i)) continue;
       o.n_subsequences += tab[i].count;
