@@ -263,7 +263,7 @@ int assemble_chunk(guac_ctx* ctx, const guac_ga_params* params, std::vector<AsmW
   AsmStage st;
   const int n = (int)(w1 - w0);
   const int K = params->kmer_size, W = params->assembly_window_range;
-  st.P = AsmParams{params->sample_id, K, W, params->min_occurrence, params->min_mean_kmer_quality, ASM_MAX_PATHS, 2 * W, 0};
+  st.P = AsmParams{params->sample_id, K, W, std::max(params->min_occurrence, 0) /* counts are >= 1: a threshold below 0 is 0 */, params->min_mean_kmer_quality, ASM_MAX_PATHS, 2 * W, 0};
   AsmWindow* h = windows.data() + w0;
   GUAC_TRY(build_paths(ctx, st, h, n, nullptr));
   DevTmp& tmp = st.tmp;
@@ -579,7 +579,7 @@ int guac_discover_paths(guac_ctx* ctx, int32_t sample_id, const char* reference_
   if (reference_len < kmer_size) return fail(ctx, GUAC_E_INVALID_INPUT, "Source kmer has size != kmerSize");  // DeBruijnGraph.scala:190-191
   GUAC_TRY(reset_error(ctx));
   AsmStage st;
-  st.P = AsmParams{sample_id, kmer_size, 0, min_occurrence, min_mean_kmer_quality, max_paths, reference_len, 1};
+  st.P = AsmParams{sample_id, kmer_size, 0, std::max(min_occurrence, 0), min_mean_kmer_quality, max_paths, reference_len, 1};
   AsmWindow w;
   std::memset(&w, 0, sizeof w);
   w.read_clo = 0;

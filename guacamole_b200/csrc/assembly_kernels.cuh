@@ -260,7 +260,8 @@ __global__ void __launch_bounds__(256) asm_count_kernel(ReadsView R, AsmWindow* 
         if (old == tag) break;
         slot = (slot + 1) & (cap - 1);
       }
-      atomicAdd(T.count + off + slot, 1u);
+      // the instance that lifts a k-mer to minOccurrence counts it as a node (no scan of the table afterwards)
+      if (atomicAdd(T.count + off + slot, 1u) + 1u == (uint32_t)max(P.min_occurrence, 1)) atomicAdd(&s_nodes, 1);
     } else {
       const int slot = asm_find(T, off, cap, k);
       if (!(T.key[off + slot] == k)) report_error(err, DERR_ASM_COLLISION, w.contig_id, w.locus, r);
@@ -334,12 +335,7 @@ __global__ void __launch_bounds__(256) asm_count_kernel(ReadsView R, AsmWindow* 
     }
     __syncthreads();
   }
-  int mine = 0;
-  for (int s = threadIdx.x; s < cap; s += blockDim.x)
-    if (T.tag[off + s] != 0 && T.count[off + s] >= (uint32_t)P.min_occurrence) ++mine;
-  if (mine) atomicAdd(&s_nodes, mine);
-  __syncthreads();
-  if (threadIdx.x == 0) w.n_nodes = s_nodes;
+  if (threadIdx.x == 0) w.n_nodes = s_nodes;  // (the pass loop ends with a barrier)
 }
 
 // Per-node graph arrays (index = node_off + node id; node ids are lexicographic ranks).
