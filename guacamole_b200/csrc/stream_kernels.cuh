@@ -126,22 +126,44 @@ __global__ void __launch_bounds__(256, GUAC_K1_MINB) ss_read_events_kernel(Reads
         const int rsh = (int)(rbit & 31), fsh = (int)(fbit & 31);
         uint32_t rlo = __ldg(rw), flo = __ldg(fw);
         const int q_rel = rp0 - lb;  // read position of offset l = q_rel + l
-        auto step = [&](int l, uint32_t keep) {
+#ifndef GUAC_K1_PAIR
+#define GUAC_K1_PAIR 1
+#endif
+        // one 16-base word pair: the mismatch mask (bit 2k: base k differs)
+        auto diff = [&](uint32_t& rd) {
           const uint32_t rhi = __ldg(++rw), fhi = __ldg(++fw);
-          const uint32_t rd = __funnelshift_r(rlo, rhi, rsh);
+          rd = __funnelshift_r(rlo, rhi, rsh);
           const uint32_t x = rd ^ __funnelshift_r(flo, fhi, fsh);
           rlo = rhi;
           flo = fhi;
-          uint32_t m = (x | (x >> 1)) & keep;
+          return (x | (x >> 1)) & 0x55555555u;
+        };
+        int l = ca;
+#if GUAC_K1_PAIR
+        // Two steps at a time: the second step's mask rides in the odd bits, so the record path below (entered by a warp
+        // whenever any of its lanes has a mismatch) is entered once per 32 bases instead of once per 16.
+        for (; l + 32 <= cb; l += 32) {
+          uint32_t rd0, rd1;
+          uint32_t m = diff(rd0);
+          m |= diff(rd1) << 1;
+          while (m) {
+            const int bit = __ffs(m) - 1;
+            m &= m - 1;
+            const int off = l + ((bit & 1) << 4) + (bit >> 1);
+            push(off, GUAC_ALN_MISMATCH, (((bit & 1) ? rd1 : rd0) >> (bit & 30)) & 3, (uint32_t)(q_rel + off));
+          }
+        }
+#endif
+        for (; l < cb; l += 16) {
+          uint32_t rd;
+          uint32_t m = diff(rd);
+          if (cb - l < 16) m &= (1u << (2 * (cb - l))) - 1;
           while (m) {
             const int bit = __ffs(m) - 1;
             m &= m - 1;
             push(l + (bit >> 1), GUAC_ALN_MISMATCH, (rd >> bit) & 3, (uint32_t)(q_rel + l + (bit >> 1)));
           }
-        };
-        int l = ca;
-        for (; l + 16 <= cb; l += 16) step(l, 0x55555555u);
-        if (l < cb) step(l, ((1u << (2 * (cb - l))) - 1) & 0x55555555u);
+        }
       };
       if (rf & RF_FAST) {
         compare_segment(0, span, 0);
