@@ -39,7 +39,10 @@ namespace guac {
 template <int TL_>
 struct TileCfg {
   static constexpr int TL = TL_;  // loci per tile
-  static constexpr int THREADS = 256;
+#ifndef GUAC_TK_THREADS
+#define GUAC_TK_THREADS 256
+#endif
+  static constexpr int THREADS = GUAC_TK_THREADS;
   static constexpr int WARPS = THREADS / 32;
   static constexpr int R_MAX = 4095;     // reads per tile (12-bit read index in an event; depth < 2^16 follows)
   static constexpr int E_MAX = TL * GUAC_TK_EMUL;   // non-match events per tile
