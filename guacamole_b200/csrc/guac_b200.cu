@@ -89,6 +89,7 @@ struct guac_ctx {
   DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
   DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
   int64_t opt_compact_narrow = 1;
+  DevBuf r_bitmap, r_counts, r_prefix, r_rank;  // rank_by_slot
   DevBuf g_active, g_jobs, g_evs, g_strings;  // scratch of guac_germline_standard, kept between calls
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
@@ -198,6 +199,25 @@ int device_scan(guac_ctx* ctx, const TIn* in, int64_t* out, int64_t n, Op op, in
   CUDA_TRY(ctx, cudaGetLastError());
   if (grand_total_dev)
     CUDA_TRY(ctx, cudaMemcpyAsync(grand_total_dev, totals + n_tiles, sizeof(int64_t), cudaMemcpyDeviceToDevice, ctx->stream));
+  return GUAC_OK;
+}
+
+// rank[i] = position of record i among the n records in slot order (slots distinct, < n_slots); see slot_bitmap_*_kernel
+int rank_by_slot(guac_ctx* ctx, const void* d_records, size_t stride, size_t slot_offset, int n, int64_t n_slots, int* d_rank) {
+  if (n == 0) return GUAC_OK;
+  const int64_t n_words = (n_slots + 31) / 32;
+  GUAC_TRY(ensure(ctx, ctx->r_bitmap, (size_t)n_words * sizeof(unsigned int)));
+  GUAC_TRY(ensure(ctx, ctx->r_counts, (size_t)n_words + 16));
+  GUAC_TRY(ensure(ctx, ctx->r_prefix, (size_t)(n_words + 1) * sizeof(int64_t)));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->r_bitmap.p, 0, (size_t)n_words * sizeof(unsigned int), ctx->stream));
+  const unsigned char* rec = static_cast<const unsigned char*>(d_records);
+  slot_bitmap_set_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(rec, stride, slot_offset, n, ctx->r_bitmap.as<unsigned int>());
+  slot_bitmap_popc_kernel<<<blocks_for(n_words, 256), 256, 0, ctx->stream>>>(ctx->r_bitmap.as<unsigned int>(), n_words, ctx->r_counts.as<uint8_t>());
+  GUAC_TRY((device_scan<true, uint8_t>(ctx, ctx->r_counts.as<uint8_t>(), ctx->r_prefix.as<int64_t>(), n_words, OpSum())));
+  slot_bitmap_rank_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(rec, stride, slot_offset, n, ctx->r_bitmap.as<unsigned int>(),
+                                                                       ctx->r_prefix.as<int64_t>(), d_rank);
+  ctx->launches += 6;
+  CUDA_TRY(ctx, cudaGetLastError());
   return GUAC_OK;
 }
 
@@ -512,7 +532,8 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->join) cudaEventDestroy(ctx->join);
   for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
                     &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
-                    &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings})
+                    &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings,
+                    &ctx->r_bitmap, &ctx->r_counts, &ctx->r_prefix, &ctx->r_rank})
     if (b->p) cudaFree(b->p);
   for (auto& kv : ctx->contigs)
     if (kv.second.ref2) cudaFree(kv.second.ref2);
@@ -975,19 +996,8 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         cudaMemsetAsync(ctx->u_flag.p, 0, (size_t)nc * sizeof(int), ctx->stream);
         ss_call_rank_kernel<<<dim3(blocks_for(nc, 256), SS_RANK_SPLIT), 256, 0, ctx->stream>>>(ctx->b_calls.as<SSCallDev>(), nc, ctx->u_flag.as<int>());
         ctx->launches += 1;
-      } else {  // too many for the quadratic kernel: the host sorts the slots
-        std::vector<SSCallDev> tmp((size_t)nc);
-        std::vector<std::pair<int64_t, int>> order((size_t)nc);
-        std::vector<int> rank((size_t)nc);
-        if (cudaMemcpyAsync(tmp.data(), ctx->b_calls.p, (size_t)nc * sizeof(SSCallDev), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
-            cudaStreamSynchronize(ctx->stream) != cudaSuccess)
-          st = fail(ctx, GUAC_E_CUDA, "copy of the call records failed");
-        for (int i = 0; i < nc; ++i) order[(size_t)i] = {tmp[(size_t)i].slot, i};
-        std::sort(order.begin(), order.end());
-        for (int i = 0; i < nc; ++i) rank[(size_t)order[(size_t)i].second] = i;
-        if (st == GUAC_OK && (cudaMemcpyAsync(ctx->u_flag.p, rank.data(), (size_t)nc * sizeof(int), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
-                              cudaStreamSynchronize(ctx->stream) != cudaSuccess))
-          st = fail(ctx, GUAC_E_CUDA, "upload of the call order failed");
+      } else {  // too many for the quadratic kernel: bitmap over the slots, linear in the loci of the call
+        st = rank_by_slot(ctx, ctx->b_calls.p, sizeof(SSCallDev), offsetof(SSCallDev, slot), nc, plan.n_slots, ctx->u_flag.as<int>());
       }
     }
     for (int attempt = 0; st == GUAC_OK && attempt < 2; ++attempt) {
@@ -1465,12 +1475,16 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   GLCallDev* calls_raw = nullptr;
   GUAC_TRY(pinned.get(reinterpret_cast<void**>(&calls_raw), (size_t)nc * sizeof(GLCallDev)));
   std::vector<long long> active((size_t)na * 2);
+  int* rank = nullptr;  // position of each record in slot order, counted on the device (no sort on the host)
+  GUAC_TRY(pinned.get(reinterpret_cast<void**>(&rank), (size_t)nc * sizeof(int)));
+  GUAC_TRY(ensure(ctx, ctx->r_rank, (size_t)std::max(nc, 1) * sizeof(int)));
+  GUAC_TRY(rank_by_slot(ctx, ctx->b_calls.p, sizeof(GLCallDev), offsetof(GLCallDev, slot), nc, plan.n_slots, ctx->r_rank.as<int>()));
   if (nc) CUDA_TRY(ctx, cudaMemcpyAsync(calls_raw, ctx->b_calls.p, (size_t)nc * sizeof(GLCallDev), cudaMemcpyDeviceToHost, ctx->stream));
+  if (nc) CUDA_TRY(ctx, cudaMemcpyAsync(rank, ctx->r_rank.p, (size_t)nc * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   if (na) CUDA_TRY(ctx, cudaMemcpyAsync(active.data(), d_active.p, (size_t)na * 2 * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   std::vector<std::pair<int64_t, int>> order((size_t)nc);
-  for (int i = 0; i < nc; ++i) order[(size_t)i] = {calls_raw[i].slot, i};
-  std::sort(order.begin(), order.end());
+  for (int i = 0; i < nc; ++i) order[(size_t)rank[i]] = {calls_raw[i].slot, i};
   struct CallsInOrder {  // range-for over the records in slot order
     const GLCallDev* raw;
     const std::vector<std::pair<int64_t, int>>* order;

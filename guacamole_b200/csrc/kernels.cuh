@@ -572,6 +572,29 @@ __global__ void __launch_bounds__(256) ss_call_rank_kernel(const SSCallDev* __re
   if (i < n && below) atomicAdd(rank + i, below);
 }
 
+// The same order for any number of records, linear in the number of loci: a bitmap over the call's slots, the records'
+// slots set in it, an exclusive scan of the words' population counts; the position of a record is the count of set bits
+// below its own.  `records` + i * stride + slot_offset holds the (distinct) int64 slot of record i.
+__global__ void slot_bitmap_set_kernel(const unsigned char* __restrict__ records, size_t stride, size_t slot_offset, int n,
+                                       unsigned int* __restrict__ bitmap) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t slot = *reinterpret_cast<const int64_t*>(records + (size_t)i * stride + slot_offset);
+  atomicOr(bitmap + (slot >> 5), 1u << (slot & 31));
+}
+__global__ void slot_bitmap_popc_kernel(const unsigned int* __restrict__ bitmap, int64_t n_words, uint8_t* __restrict__ counts) {
+  const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < n_words) counts[w] = (uint8_t)__popc(bitmap[w]);
+}
+__global__ void slot_bitmap_rank_kernel(const unsigned char* __restrict__ records, size_t stride, size_t slot_offset, int n,
+                                        const unsigned int* __restrict__ bitmap, const int64_t* __restrict__ word_prefix,
+                                        int* __restrict__ rank) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t slot = *reinterpret_cast<const int64_t*>(records + (size_t)i * stride + slot_offset);
+  rank[i] = (int)word_prefix[slot >> 5] + __popc(bitmap[slot >> 5] & ((1u << (slot & 31)) - 1u));
+}
+
 constexpr int MM_BINS = 1024;
 
 // lower/upper middle of a histogram with n entries -> (a, b): values at ranks (n-1)/2 and n/2

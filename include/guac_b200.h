@@ -465,8 +465,8 @@ void* guac_stream(guac_ctx* ctx);
  *                           kernel, 1 = generic gather kernel only; all three fall back to the gather kernel per tile
  *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook)
  *   "compact_narrow"        1 (default): guac_reads_export_compact emits the narrow columns where the batch allows; 0: never
- *   "ss_rank_max"           somatic-standard puts more calls than this in output order on the host instead of on the
- *                           device (test hook; default and maximum 32768, negative restores the default) */
+ *   "ss_rank_max"           somatic-standard ranks more calls than this through a bitmap over the loci instead of by
+ *                           pairwise comparison (test hook; default and maximum 32768, negative restores the default) */
 int guac_set_option(guac_ctx* ctx, const char* name, int64_t value);
 /* Tiles of the most recent guac_somatic_standard call that took the fallback path. */
 int64_t guac_last_fallback_tiles(guac_ctx* ctx);

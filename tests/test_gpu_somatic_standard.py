@@ -9,14 +9,14 @@ from oracle import oracle
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["tile", "gather", "tile+fallback", "stream", "stream+fallback", "stream+hostorder"])
+@pytest.fixture(params=["tile", "gather", "tile+fallback", "stream", "stream+fallback", "stream+bitmaporder"])
 def impl(request, gpu_ctx):
     """Every parity case runs through the tile kernel, the generic gather kernel, the tile kernel with every third
     tile forced through its fallback path, the stream implementation (read pass as a kernel of its own), and the stream
-    implementation with the calls put in output order by the host (the path taken beyond 32768 calls)."""
-    gpu_ctx.set_option("ss_impl", {"gather": 1, "stream": 2, "stream+fallback": 2, "stream+hostorder": 2}.get(request.param, 0))
+    implementation with the calls ranked through the bitmap over the loci (the path taken beyond 32768 calls)."""
+    gpu_ctx.set_option("ss_impl", {"gather": 1, "stream": 2, "stream+fallback": 2, "stream+bitmaporder": 2}.get(request.param, 0))
     gpu_ctx.set_option("ss_force_fallback_mod", 3 if request.param.endswith("+fallback") else 0)
-    gpu_ctx.set_option("ss_rank_max", 0 if request.param.endswith("+hostorder") else -1)
+    gpu_ctx.set_option("ss_rank_max", 0 if request.param.endswith("+bitmaporder") else -1)
     yield request.param
     gpu_ctx.set_option("ss_impl", 2)  # the default
     gpu_ctx.set_option("ss_force_fallback_mod", 0)
