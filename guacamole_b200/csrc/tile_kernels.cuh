@@ -333,7 +333,9 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
           second = s0_rel + ev.y;  // quality index relative to the tile's first base
         } else if (kind == GUAC_ALN_DELETION && code == 4) {  // the deleted reference bases must exist (PE.scala:95)
           const int nlen = (int)((ev.y >> 8) & 0xFF);
-          for (int k = 1; k <= nlen; ++k)
+          // (every locus of this tile has an A C G T reference base, or the tile would not be here: only the part of the
+          // deletion that runs past the tile's end is looked up)
+          for (int k = max(1, n_loci - l); k <= nlen; ++k)
             if (ref.at(t0 + l + k) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + l + k, r);
         }
         push_event(l, rl, slot, kind, code, second);
@@ -404,7 +406,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
               }
               push_event(ll, rl, slot, GUAC_ALN_INSERTION, 4, direct(q, (int)((h ^ (h >> 8) ^ (h >> 16) ^ (h >> 24)) & 0xFF)));
             } else {  // Deletion: the deleted reference bases must exist (PE.scala:95)
-              for (int j = 1; j <= nlen; ++j)
+              for (int j = max(1, n_loci - ll); j <= nlen; ++j)  // inside the tile the reference is known to be there
                 if (ref.at(t0 + ll + j) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + ll + j, r);
               push_event(ll, rl, slot, GUAC_ALN_DELETION, nlen < 255 ? 4 : 5, direct(__ldg(R.qual + s0 + k), nlen));
             }
