@@ -481,11 +481,11 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       S.warp_tot[1][warp] = i_aux;
     }
     __syncthreads();
-    int c_cov = 0, c_aux = 0;
-    for (int w = 0; w < warp; ++w) {
-      c_cov += S.warp_tot[0][w];
-      c_aux += S.warp_tot[1][w];
-    }
+    // totals of the warps before this one: lane w holds warp w's, one warp-wide add each
+    static_assert(CFG::WARPS <= 32, "one lane per warp total");
+    const bool before = lane < warp;  // (warp < WARPS)
+    const int c_cov = __reduce_add_sync(FULL, before ? S.warp_tot[0][lane] : 0);
+    const int c_aux = __reduce_add_sync(FULL, before ? S.warp_tot[1][lane] : 0);
     int r_cov = c_cov + i_cov - s_cov, r_aux = c_aux + i_aux - s_aux;
     for (int i = b0; i < e0; ++i) {
       r_cov += S.cov[i];
