@@ -89,6 +89,7 @@ struct guac_ctx {
   DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
   DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
   int64_t opt_compact_narrow = 1;
+  std::vector<RangeDev> plan_ranges;            // host copy of the current call's range table (make_plan)
   DevBuf r_bitmap, r_counts, r_prefix, r_rank;  // rank_by_slot
   DevBuf g_active, g_jobs, g_evs, g_strings;  // scratch of guac_germline_standard, kept between calls
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
@@ -253,7 +254,8 @@ int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& pla
   if (!ctx->have_reads) return fail(ctx, GUAC_E_STATE, "no reads uploaded (guac_reads_upload)");
   if (n_ranges < 0 || (n_ranges > 0 && !loci)) return fail(ctx, GUAC_E_INVALID_INPUT, "bad loci ranges");
   GUAC_TRY(sync_refs(ctx));
-  std::vector<RangeDev> rs;
+  std::vector<RangeDev>& rs = ctx->plan_ranges;  // kept in the context, so nothing below has to wait for the copy
+  rs.clear();
   int64_t slot = 0, tile = 0;
   for (int i = 0; i < n_ranges; ++i) {
     const guac_range& g = loci[i];
@@ -294,8 +296,7 @@ int make_plan(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, Plan& pla
                                                                       ctx->R, ctx->b_tiles.as<Tile>(), ctx->d_refs.as<RefView>());
   ctx->launches += 1;
   CUDA_TRY(ctx, cudaGetLastError());
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `rs` is a temporary
-  return GUAC_OK;
+  return GUAC_OK;  // (no wait: the kernels that read the tiles follow on the same stream)
 }
 
 // Stream path: 2-bit copies of the reference windows, rebuilt for the windows that changed.
@@ -838,7 +839,10 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(int)));
   int max_calls = (int)std::max<size_t>(ctx->b_calls.cap / sizeof(SSCallDev), 1 << 16);
   int nc = 0;
+  unsigned long long visited_host = 0;  // loci visited, counted by the tile kernels
+  bool have_counts = false;             // nc / visited_host / the error record came with the list lengths
   for (int attempt = 0; attempt < 2; ++attempt) {
+    have_counts = false;
     GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(SSCallDev)));
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
     if (use_tiles) {
@@ -931,10 +935,15 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
       cudaEventRecord(ctx->ev1, ctx->stream);
+      // one host round trip for everything the host needs to know now: the two list lengths, the number of calls, the
+      // number of visited loci and the error record (every wait costs tens of microseconds, more on a busy host)
       int counts[2] = {0, 0};
       CUDA_TRY(ctx, cudaMemcpyAsync(&counts[0], fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
       CUDA_TRY(ctx, cudaMemcpyAsync(&counts[1], heavy_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-      CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&visited_host, visited_count, sizeof visited_host, cudaMemcpyDeviceToHost, ctx->stream));
+      GUAC_TRY(check_device_error(ctx));  // synchronises
+      have_counts = true;
       const int n_fb = counts[0], n_heavy = counts[1];
       ctx->last_fallback_tiles = n_fb;
       ctx->last_heavy_loci = n_heavy;
@@ -955,6 +964,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         ctx->launches += 1;
         CUDA_TRY(ctx, cudaGetLastError());
         cudaEventRecord(ctx->ev1, ctx->stream);  // the timed span then ends here
+        have_counts = false;                     // calls and visited loci of these tiles are still to come
       }
     } else {
       cudaEventRecord(ctx->ev0, ctx->stream);
@@ -969,8 +979,12 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     trace.mark("per-locus kernels launched");
     ctx->have_timing = true;
     ctx->timed_loci = plan.n_slots;
-    CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    GUAC_TRY(check_device_error(ctx));  // synchronises
+    if (!have_counts) {
+      CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      if (use_tiles)
+        CUDA_TRY(ctx, cudaMemcpyAsync(&visited_host, ctx->b_vcount.p, sizeof visited_host, cudaMemcpyDeviceToHost, ctx->stream));
+      GUAC_TRY(check_device_error(ctx));  // synchronises
+    }
     if (nc <= max_calls) break;
     max_calls = nc;  // rerun with room for every call
   }
@@ -1035,11 +1049,8 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   if (out_summary || (out_n_visited && !use_tiles)) {
     GUAC_TRY(compact_visited(ctx, plan, 1, nv));
     if (out_n_visited) *out_n_visited = nv;
-  } else if (out_n_visited) {  // counted by the tile kernel itself
-    unsigned long long v = 0;
-    CUDA_TRY(ctx, cudaMemcpyAsync(&v, ctx->b_vcount.p, sizeof v, cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    *out_n_visited = (int64_t)v;
+  } else if (out_n_visited) {  // counted by the tile kernels themselves, read back with the call count
+    *out_n_visited = (int64_t)visited_host;
   }
   if (out_summary) {
     DevBuf os;
