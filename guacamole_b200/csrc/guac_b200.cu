@@ -836,7 +836,16 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
   // the dense per-(locus, sample) summary is part of the kernel's output contract; it stays in HBM unless asked for
   GUAC_TRY(ensure(ctx, ctx->b_summary, (size_t)plan.n_slots * 2 * sizeof(guac_locus_summary)));
-  GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(int)));
+  // the call's counters share one small block: one memset to clear them, one copy to read them
+  struct SSCounters {
+    int n_calls, n_fallback, n_heavy;
+    unsigned int arena_used;
+    unsigned long long n_visited;
+  };
+  GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(SSCounters)));
+  SSCounters* d_cnt = ctx->b_ncalls.as<SSCounters>();
+  int* d_ncalls = &d_cnt->n_calls;
+  SSCounters h_cnt{};
   int max_calls = (int)std::max<size_t>(ctx->b_calls.cap / sizeof(SSCallDev), 1 << 16);
   int nc = 0;
   unsigned long long visited_host = 0;  // loci visited, counted by the tile kernels
@@ -844,12 +853,11 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   for (int attempt = 0; attempt < 2; ++attempt) {
     have_counts = false;
     GUAC_TRY(ensure(ctx, ctx->b_calls, (size_t)max_calls * sizeof(SSCallDev)));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(d_cnt, 0, sizeof(SSCounters), ctx->stream));
     if (use_tiles) {
       GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 2) * sizeof(int)));
-      int* fb_count = ctx->b_fallback.as<int>();
-      int* fb_list = fb_count + 1;
-      CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
+      int* fb_count = &d_cnt->n_fallback;
+      int* fb_list = ctx->b_fallback.as<int>();
       static bool attr_set = false;
       if (!attr_set) {
         CUDA_TRY(ctx, cudaFuncSetAttribute(ss_tile_kernel<TCfg, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -859,11 +867,8 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       // LOD-bound table for f = the VAF floor (see `prune` in tile_kernels.cuh)
       const int max_heavy = (int)std::min<int64_t>(plan.n_slots, plan.n_slots / 16 + 65536);
       GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
-      int* heavy_count = fb_count + 1 + plan.n_tiles;
-      CUDA_TRY(ctx, cudaMemsetAsync(heavy_count, 0, sizeof(int), ctx->stream));
-      GUAC_TRY(ensure(ctx, ctx->b_vcount, sizeof(unsigned long long)));
-      unsigned long long* visited_count = ctx->b_vcount.as<unsigned long long>();
-      CUDA_TRY(ctx, cudaMemsetAsync(visited_count, 0, sizeof(unsigned long long), ctx->stream));
+      int* heavy_count = &d_cnt->n_heavy;
+      unsigned long long* visited_count = &d_cnt->n_visited;
       TileArgs TA;
       std::memset(&TA, 0, sizeof TA);
       TA.rflags = ctx->b_rflags.as<uint8_t>();
@@ -887,7 +892,12 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         GUAC_TRY(ensure(ctx, ctx->b_bin_count, (size_t)ctx->n_reads + 16));
         TA.ev_by_read = ctx->b_bins.as<uint2>();
         TA.ev_count = ctx->b_bin_count.as<uint8_t>();
-        CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_bin_count.p, 0, (size_t)ctx->n_reads + 16, ctx->stream));  // contigs without a reference
+        {  // reads of a contig without a reference get no launch of the read pass: their counts must read 0
+          bool every_contig_has_a_reference = true;
+          for (auto& sp : ctx->contig_spans) every_contig_has_a_reference = every_contig_has_a_reference && ctx->contigs.count(sp.first) != 0;
+          if (!every_contig_has_a_reference)
+            CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_bin_count.p, 0, (size_t)ctx->n_reads + 16, ctx->stream));
+        }
         cudaEventRecord(ctx->ev0, ctx->stream);
         for (auto& sp : ctx->contig_spans) {  // one launch per contig of the batch: its reference rides in the arguments
           auto it = ctx->contigs.find(sp.first);
@@ -930,21 +940,19 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       // full machine and strides over the list, so no host round trip separates it from the locus pass.
       somatic_standard_kernel<<<(unsigned)std::min<int64_t>(blocks_for(max_heavy, WARPS_PER_CTA), 148 * 8), CTA_THREADS, 0, ctx->stream>>>(
           ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, max_heavy, 1, P, ctx->b_visited.as<uint8_t>(),
-          ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls, nullptr,
+          ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), d_ncalls, max_calls, nullptr,
           ctx->b_err.as<DeviceError>(), heavy_count);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
       cudaEventRecord(ctx->ev1, ctx->stream);
       // one host round trip for everything the host needs to know now: the two list lengths, the number of calls, the
       // number of visited loci and the error record (every wait costs tens of microseconds, more on a busy host)
-      int counts[2] = {0, 0};
-      CUDA_TRY(ctx, cudaMemcpyAsync(&counts[0], fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-      CUDA_TRY(ctx, cudaMemcpyAsync(&counts[1], heavy_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-      CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-      CUDA_TRY(ctx, cudaMemcpyAsync(&visited_host, visited_count, sizeof visited_host, cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&h_cnt, d_cnt, sizeof h_cnt, cudaMemcpyDeviceToHost, ctx->stream));
       GUAC_TRY(check_device_error(ctx));  // synchronises
       have_counts = true;
-      const int n_fb = counts[0], n_heavy = counts[1];
+      nc = h_cnt.n_calls;
+      visited_host = h_cnt.n_visited;
+      const int n_fb = h_cnt.n_fallback, n_heavy = h_cnt.n_heavy;
       ctx->last_fallback_tiles = n_fb;
       ctx->last_heavy_loci = n_heavy;
       if (n_heavy > max_heavy) {
@@ -959,7 +967,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       if (n_fb > 0) {  // tiles beyond a shared-memory capacity: generic kernel, still on the GPU
         somatic_standard_kernel<<<(unsigned)n_fb, CTA_THREADS, 0, ctx->stream>>>(
             ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, n_fb, 0, P, ctx->b_visited.as<uint8_t>(),
-            ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), ctx->b_ncalls.as<int>(), max_calls,
+            ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(), d_ncalls, max_calls,
             visited_count, ctx->b_err.as<DeviceError>());
         ctx->launches += 1;
         CUDA_TRY(ctx, cudaGetLastError());
@@ -971,7 +979,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       somatic_standard_kernel<<<(unsigned)plan.n_tiles, CTA_THREADS, 0, ctx->stream>>>(
           ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), nullptr, (int)plan.n_tiles, 0, P,
           ctx->b_visited.as<uint8_t>(), ctx->b_summary.as<guac_locus_summary>(), ctx->b_calls.as<SSCallDev>(),
-          ctx->b_ncalls.as<int>(), max_calls, nullptr, ctx->b_err.as<DeviceError>());
+          d_ncalls, max_calls, nullptr, ctx->b_err.as<DeviceError>());
       cudaEventRecord(ctx->ev1, ctx->stream);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
@@ -980,10 +988,10 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     ctx->have_timing = true;
     ctx->timed_loci = plan.n_slots;
     if (!have_counts) {
-      CUDA_TRY(ctx, cudaMemcpyAsync(&nc, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-      if (use_tiles)
-        CUDA_TRY(ctx, cudaMemcpyAsync(&visited_host, ctx->b_vcount.p, sizeof visited_host, cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(&h_cnt, d_cnt, sizeof h_cnt, cudaMemcpyDeviceToHost, ctx->stream));
       GUAC_TRY(check_device_error(ctx));  // synchronises
+      nc = h_cnt.n_calls;
+      visited_host = h_cnt.n_visited;
     }
     if (nc <= max_calls) break;
     max_calls = nc;  // rerun with room for every call
@@ -1001,8 +1009,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     oc = static_cast<guac_ss_call*>(hp);
   }
   if (nc > 0) {
-    int st = ensure(ctx, ctx->b_arena_used, sizeof(unsigned int));
-    if (st == GUAC_OK) st = ensure(ctx, ctx->b_arena, (size_t)nc * 32 + 4096);
+    int st = ensure(ctx, ctx->b_arena, (size_t)nc * 32 + 4096);
     if (st == GUAC_OK) st = ensure(ctx, ctx->u_flag, (size_t)nc * sizeof(int));
     if (st == GUAC_OK) st = ensure(ctx, ctx->u_off, (size_t)nc * sizeof(guac_ss_call));
     if (st == GUAC_OK) {
@@ -1016,16 +1023,16 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     }
     for (int attempt = 0; st == GUAC_OK && attempt < 2; ++attempt) {
       unsigned int used = 0;
-      cudaMemsetAsync(ctx->b_arena_used.p, 0, sizeof(unsigned int), ctx->stream);
+      if (attempt > 0) cudaMemsetAsync(&d_cnt->arena_used, 0, sizeof(unsigned int), ctx->stream);  // (cleared with the block the first time)
       ss_evidence_kernel<<<(unsigned)nc, 128, 0, ctx->stream>>>(
-          ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(), ctx->b_arena.as<char>(), ctx->b_arena_used.as<unsigned int>(),
+          ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(), ctx->b_arena.as<char>(), &d_cnt->arena_used,
           (unsigned int)std::min<size_t>(ctx->b_arena.cap, 0xFFFFFFFFu), ctx->b_err.as<DeviceError>(),
           have_events ? ctx->b_hdr.as<uint4>() : nullptr, have_events ? ctx->b_bins.as<uint2>() : nullptr,
           have_events ? ctx->b_bin_count.as<uint8_t>() : nullptr, STREAM_EV_CAP, ctx->u_flag.as<int>(), ctx->u_off.as<guac_ss_call>());
       ctx->launches += 1;
       if (cudaGetLastError() != cudaSuccess ||
           cudaMemcpyAsync(oc, ctx->u_off.p, (size_t)nc * sizeof(guac_ss_call), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
-          cudaMemcpyAsync(&used, ctx->b_arena_used.p, sizeof used, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) {
+          cudaMemcpyAsync(&used, &d_cnt->arena_used, sizeof used, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) {
         st = fail(ctx, GUAC_E_CUDA, "launch of the evidence kernel failed");
         break;
       }
