@@ -154,3 +154,37 @@ def test_world_size_2_gloo_shard_and_gather(tmp_path):
                           "127.0.0.1", "--master-port", "29517", str(script)], capture_output=True, text=True, env=env, timeout=280)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "GLOO_OK" in out.stdout
+
+
+def test_python_mirrors_match_the_header_layout(tmp_path):
+    """The ctypes structures and numpy record types of native.py are hand-written twins of include/guac_b200.h: their
+    sizes are checked against what a C compiler makes of the header (a field added on one side only shows up here, on
+    the CPU, instead of as garbage on the GPU box)."""
+    import ctypes as C
+    import subprocess
+    import numpy as np
+    from guacamole_b200 import native
+    pairs = {
+        "guac_read_batch": C.sizeof(native.ReadBatchC), "guac_range": C.sizeof(native.RangeC),
+        "guac_locus_counts": C.sizeof(native.LocusCountsC), "guac_element": C.sizeof(native.ElementC),
+        "guac_allele_evidence": C.sizeof(native.AlleleEvidenceC), "guac_ss_params": C.sizeof(native.SSParamsC),
+        "guac_ss_call": C.sizeof(native.SSCallC), "guac_locus_summary": C.sizeof(native.LocusSummaryC),
+        "guac_gs_params": C.sizeof(native.GSParamsC), "guac_ga_params": C.sizeof(native.GAParamsC),
+        "guac_read_batch_compact": C.sizeof(native.ReadBatchCompactC),
+        "guac_called_allele": native.CALLED_ALLELE_DTYPE.itemsize, "guac_assembled_window": native.ASSEMBLED_WINDOW_DTYPE.itemsize,
+    }
+    from guacamole_b200.commands import somatic_joint as sj
+    pairs.update({"guac_sj_params": C.sizeof(sj.SJParamsC), "guac_sj_sample_evidence": sj.SAMPLE_EVIDENCE_DTYPE.itemsize,
+                  "guac_sj_allele_evidence": sj.ALLELE_EVIDENCE_DTYPE.itemsize})
+    assert native.SS_CALL_DTYPE.itemsize == C.sizeof(native.SSCallC) and native.ELEMENT_DTYPE.itemsize == C.sizeof(native.ElementC)
+    assert native.LOCUS_SUMMARY_DTYPE.itemsize == C.sizeof(native.LocusSummaryC)
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "guac_b200.h"\nint main(void) {\n' +
+                   "".join(f'  printf("{name} %zu\\n", sizeof({name}));\n' for name in pairs) + "  return 0;\n}\n")
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = dict(line.split() for line in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for name, size in pairs.items():
+        assert int(out[name]) == size, (name, out[name], size)
+    # the narrow columns sit at the end of the compact batch, after the wide ones
+    assert native.ReadBatchCompactC.start_rel.offset > native.ReadBatchCompactC.sample_id.offset
