@@ -89,6 +89,7 @@ struct guac_ctx {
   DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
   DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
   int64_t opt_compact_narrow = 1;
+  int64_t opt_sj_host_threads = 0;  // 0: as many as the host has cores, at most 32
   std::vector<RangeDev> plan_ranges;            // host copy of the current call's range table (make_plan)
   DevBuf r_bitmap, r_counts, r_prefix, r_rank;  // rank_by_slot
   DevBuf g_active, g_jobs, g_evs, g_strings;  // scratch of guac_germline_standard, kept between calls
@@ -1294,7 +1295,8 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
         emitted_by_site[(size_t)oi] = joint::emit(*params, site.forced != 0, all);
       }
     };
-    const int n_threads = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)std::thread::hardware_concurrency(), 32, (int64_t)n_sites / 2048}));
+    const int64_t thread_cap = ctx->opt_sj_host_threads > 0 ? ctx->opt_sj_host_threads : std::min<int64_t>((int64_t)std::thread::hardware_concurrency(), 32);
+    const int n_threads = (int)std::max<int64_t>(1, std::min<int64_t>(thread_cap, (int64_t)n_sites / 2048));
     if (n_threads <= 1) {
       evaluate_sites(0, n_sites);
     } else {
@@ -1669,6 +1671,8 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
     ctx->opt_ss_impl = value;
   } else if (n == "ss_force_fallback_mod") {
     ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
+  } else if (n == "sj_host_threads") {
+    ctx->opt_sj_host_threads = value < 0 ? 0 : std::min<int64_t>(value, 256);
   } else if (n == "compact_narrow") {
     ctx->opt_compact_narrow = value != 0;
   } else if (n == "ss_rank_max") {

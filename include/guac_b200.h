@@ -464,6 +464,8 @@ void* guac_stream(guac_ctx* ctx);
  *   "ss_impl"               somatic-standard: 2 = read pass + locus pass as two kernels (default), 0 = both in one tile
  *                           kernel, 1 = generic gather kernel only; all three fall back to the gather kernel per tile
  *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook)
+ *   "sj_host_threads"       host threads guac_somatic_joint may use for its per-site arithmetic (0, the default: one per
+ *                           host core, at most 32; 1: the calling thread only)
  *   "compact_narrow"        1 (default): guac_reads_export_compact emits the narrow columns where the batch allows; 0: never
  *   "ss_rank_max"           somatic-standard ranks more calls than this through a bitmap over the loci instead of by
  *                           pairwise comparison (test hook; default and maximum 32768, negative restores the default) */

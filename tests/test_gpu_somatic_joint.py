@@ -111,3 +111,24 @@ def test_indel_alleles_and_non_standard_bases(gpu_ctx):
     want, _ = oracle.somatic_joint(batch, ref, [(0, 1, 14)], p, force_loci=force)
     assert {(e["ref"], e["alt"]) for e in want} >= {("A", "ACCC"), ("T", "G"), ("GA", "G")}
     assert_evidences_equal(got, want)
+
+
+def test_host_threads_do_not_change_the_records(gpu_ctx):
+    """Enough candidate sites for the per-site arithmetic to be split over several host threads: the records are the ones
+    the calling thread alone produces (option sj_host_threads)."""
+    contig_len, depths, tumor, kinds, seed = 600_000, (30, 60, 30), (False, True, True), [0, 1, 1], 4205
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, depths, tumor, seed)
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    loci = [(0, 1, contig_len)]
+    p = sj.sj_params(kinds, include_filtered=1)  # every candidate site comes back: thousands of records
+    try:
+        gpu_ctx.set_option("sj_host_threads", 1)
+        alone, nv1 = gpu_ctx.somatic_joint(loci, p)
+        gpu_ctx.set_option("sj_host_threads", 4)
+        shared, nv4 = gpu_ctx.somatic_joint(loci, p)
+    finally:
+        gpu_ctx.set_option("sj_host_threads", 0)
+    assert nv1 == nv4 and len(alone) > 100  # (emitted records; the candidate sites behind them are ~5 000: two threads)
+    assert_evidences_equal(shared, alone)
