@@ -188,3 +188,18 @@ def test_python_mirrors_match_the_header_layout(tmp_path):
         assert int(out[name]) == size, (name, out[name], size)
     # the narrow columns sit at the end of the compact batch, after the wide ones
     assert native.ReadBatchCompactC.start_rel.offset > native.ReadBatchCompactC.sample_id.offset
+
+
+def test_reference_arm_prints_the_contract_line(built):
+    """`bench.py --impl reference` (the CPU restatement timed on the host cores, no GPU involved) prints one JSON line with
+    the keys the driver reads; run here on a small bounded sample."""
+    import json
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                          "--contig-mbp", "5", "--reference-step-seconds", "0.3"], check=True, capture_output=True, text=True, timeout=300)
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["metric"] == "loci/sec (pileup+likelihood)" and line["unit"] == "loci/s"
+    assert line["higher_is_better"] is True and line["value"] > 0 and line["steps"] == 1 and line["n_gpus"] == 1
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1 and line["cpu_baseline"]["value"] == line["value"]
+    assert line["e2e"] == {"value": line["value"], "unit": "loci/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
