@@ -443,7 +443,7 @@ typedef struct {
  * pileup locus + 1 lies in `force_loci` (:181).  Per-element work — ReadSubsequence, AlleleAtLocus,
  * PileupStats and the mixture likelihoods (M/jointcaller/pileup_summarization/*, AlleleAtLocus.scala:85-149,
  * evidence/*SingleSampleSingleAlleleEvidence.scala) — runs on the device; posteriors, call logic, annotations
- * (M/jointcaller/evidence/MultiSampleSingleAlleleEvidence.scala:66-341, annotation/*.scala) and the emit
+ * (M/jointcaller/evidence/MultiSampleSingleAlleleEvidence.scala:66-341, the files of annotation/) and the emit
  * policy (MultiSampleMultiAlleleEvidence.scala:131-177) on the host side of the library.
  * Output: one guac_sj_allele_evidence per emitted allele, in (range order, locus, allele) order, each with
  * n_samples + 2 guac_sj_sample_evidence records; strings in the arena.
