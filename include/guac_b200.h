@@ -441,8 +441,8 @@ typedef struct {
  * pileupFlatMapMultipleSamples(skipEmpty = true, MultiSampleMultiAlleleEvidence.make) over the loci shifted
  * by -1 (lociSetMinusOne :143-152; the function does the shift itself).  A site is force-called when
  * pileup locus + 1 lies in `force_loci` (:181).  Per-element work — ReadSubsequence, AlleleAtLocus,
- * PileupStats and the mixture likelihoods (M/jointcaller/pileup_summarization/*, AlleleAtLocus.scala:85-149,
- * evidence/*SingleSampleSingleAlleleEvidence.scala) — runs on the device; posteriors, call logic, annotations
+ * PileupStats and the mixture likelihoods (M/jointcaller/pileup_summarization/ (all files), AlleleAtLocus.scala:85-149,
+ * evidence/ ...SingleSampleSingleAlleleEvidence.scala) — runs on the device; posteriors, call logic, annotations
  * (M/jointcaller/evidence/MultiSampleSingleAlleleEvidence.scala:66-341, the files of annotation/) and the emit
  * policy (MultiSampleMultiAlleleEvidence.scala:131-177) on the host side of the library.
  * Output: one guac_sj_allele_evidence per emitted allele, in (range order, locus, allele) order, each with
