@@ -249,11 +249,7 @@ AsmPenalties asm_penalties(double mismatch_probability, double open_gap_probabil
 }
 
 int asm_align_prepare(guac_ctx* ctx) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(ctx, cudaFuncSetAttribute(asm_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_align_smem(ASM_ALIGN_MAX_S)));
-    attr_set = true;
-  }
+  (void)ctx;  // the kernel's shared-memory attribute is set per device in guac_ctx_create
   return GUAC_OK;
 }
 

@@ -134,7 +134,16 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->fork, 0));
   if (n_bases > 0)
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->b_bases2.p, b->bases2, (size_t)((n_bases + 3) / 4), cudaMemcpyHostToDevice, ctx->stream2));
-  CUDA_TRY(ctx, cudaEventRecord(ctx->join, ctx->stream2));
+  // From here on the copy of the bases is in flight out of the caller's buffer: every exit goes through the wait on
+  // `join` at the end, so no early return below.
+  int st = GUAC_OK;
+  auto cuda_ok = [&](cudaError_t e, const char* what) {
+    if (e != cudaSuccess && st == GUAC_OK) {
+      ctx->err = std::string("CUDA error: ") + cudaGetErrorString(e) + " at " + what;
+      st = GUAC_E_CUDA;
+    }
+  };
+  cuda_ok(cudaEventRecord(ctx->join, ctx->stream2), "cudaEventRecord(join)");
   if (b->qual_bits != 8 && n_bases > 0) {
     compact::QualTable T;
     std::memcpy(T.q, b->qual_table, 16);
@@ -145,17 +154,10 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
       compact::expand_qual_kernel<2><<<blocks, 256, 0, ctx->stream>>>(n_bases, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
     ctx->launches += 1;
   }
-  CUDA_TRY(ctx, cudaGetLastError());
+  cuda_ok(cudaGetLastError(), "the quality expansion");
   int bad = 0;
-  CUDA_TRY(ctx, cudaMemcpyAsync(&bad, d_bad.p, sizeof bad, cudaMemcpyDeviceToHost, ctx->stream));
-  int st = GUAC_OK;
-  {
-    cudaError_t e = cudaStreamSynchronize(ctx->stream);
-    if (e != cudaSuccess) {
-      ctx->err = std::string("CUDA error: ") + cudaGetErrorString(e);
-      st = GUAC_E_CUDA;
-    }
-  }
+  cuda_ok(cudaMemcpyAsync(&bad, d_bad.p, sizeof bad, cudaMemcpyDeviceToHost, ctx->stream), "cudaMemcpyAsync(bad)");
+  cuda_ok(cudaStreamSynchronize(ctx->stream), "cudaStreamSynchronize");
   if (st == GUAC_OK && (bad & 1)) st = fail(ctx, GUAC_E_INVALID_INPUT, "Regions must be sorted by start locus");
   if (st == GUAC_OK && (bad & 2)) st = fail(ctx, GUAC_E_INVALID_INPUT, "sample_id >= n_samples");
   if (st == GUAC_OK && (bad & 4)) st = fail(ctx, GUAC_E_INVALID_INPUT, "read start out of range");

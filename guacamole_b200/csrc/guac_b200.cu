@@ -39,6 +39,16 @@ struct DevBuf {
   T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// A device buffer that lives for one call: released on every return path (cudaFree waits for the device).
+struct TmpDev : DevBuf {
+  TmpDev() = default;
+  TmpDev(const TmpDev&) = delete;
+  TmpDev& operator=(const TmpDev&) = delete;
+  ~TmpDev() {
+    if (p) cudaFree(p);
+  }
+};
+
 struct ContigDev {
   int64_t offset = 0, len = 0;
   uint8_t* bases = nullptr;
@@ -224,6 +234,7 @@ int rank_by_slot(guac_ctx* ctx, const void* d_records, size_t stride, size_t slo
 }
 
 int sync_ref2(guac_ctx* ctx);
+cudaError_t configure_device_functions();  // defined at the end of this file, after every kernel is in view
 
 int sync_refs(guac_ctx* ctx) {
   GUAC_TRY(sync_ref2(ctx));  // 2-bit copies and bad-group bitmaps of the windows that changed
@@ -499,6 +510,13 @@ int guac_ctx_create(int device, guac_ctx** out) {
   }
   cudaEventCreate(&ctx->ev0);
   cudaEventCreate(&ctx->ev1);
+  // Function attributes are per device: every context sets them for its own device (a process may hold contexts on
+  // several GPUs), for every instantiation that is ever launched with dynamic shared memory.
+  if (configure_device_functions() != cudaSuccess) {
+    (void)cudaGetLastError();
+    guac_ctx_destroy(ctx);
+    return GUAC_E_CUDA;
+  }
   *out = ctx;
   return GUAC_OK;
 }
@@ -677,7 +695,29 @@ int guac_reads_upload(guac_ctx* ctx, const guac_read_batch* b) {
   GUAC_TRY(upload(ctx, ctx->b_mapq, b->mapq, (size_t)n));
   GUAC_TRY(upload(ctx, ctx->b_flags, b->flags, (size_t)n));
   GUAC_TRY(upload(ctx, ctx->b_sample, b->sample_id, (size_t)n));
-  const int vst = validate();
+  int vst = validate();
+  if (vst == GUAC_OK && n > 0) {
+    // the offsets first (the length check walks the CIGAR words they point at), each with its own answer
+    vst = ensure(ctx, ctx->u_bad, sizeof(int));
+    int bad = 0;
+    for (int pass = 0; vst == GUAC_OK && pass < 2; ++pass) {
+      cudaMemsetAsync(ctx->u_bad.p, 0, sizeof(int), ctx->stream);
+      if (pass == 0)
+        validate_offsets_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->b_cigar_off.as<uint32_t>(), ctx->b_seq_off.as<uint64_t>(),
+                                                                           n_cigar, n_bases, ctx->u_bad.as<int>());
+      else
+        validate_lengths_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->b_cigar_off.as<uint32_t>(), ctx->b_cigar.as<uint32_t>(),
+                                                                           ctx->b_seq_off.as<uint64_t>(), ctx->u_bad.as<int>());
+      ctx->launches += 1;
+      if (cudaMemcpyAsync(&bad, ctx->u_bad.p, sizeof bad, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+          cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+        vst = fail(ctx, GUAC_E_CUDA, "validation of the read batch failed to run");
+      else if (bad & 1)
+        vst = fail(ctx, GUAC_E_INVALID_INPUT, "cigar_off / seq_off must be non-decreasing and end at the uploaded sizes");
+      else if (bad & 2)
+        vst = fail(ctx, GUAC_E_INVALID_INPUT, "a read's CIGAR does not consume as many bases as the read has");
+    }
+  }
   if (vst != GUAC_OK) {
     cudaStreamSynchronize(ctx->stream);
     return vst;
@@ -711,7 +751,7 @@ int guac_pileup_counts(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, 
   GUAC_TRY(check_device_error(ctx));
   int64_t nv = 0;
   GUAC_TRY(compact_visited(ctx, plan, skip_empty, nv));
-  DevBuf oc, ol, ocnt;
+  TmpDev oc, ol, ocnt;
   GUAC_TRY(ensure(ctx, oc, (size_t)nv * sizeof(int32_t)));
   GUAC_TRY(ensure(ctx, ol, (size_t)nv * sizeof(int64_t)));
   GUAC_TRY(ensure(ctx, ocnt, (size_t)nv * S * sizeof(guac_locus_counts)));
@@ -726,9 +766,6 @@ int guac_pileup_counts(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, 
   GUAC_TRY(host_out(ctx, out_locus, ol.p, (size_t)nv));
   GUAC_TRY(host_out(ctx, out_counts, ocnt.p, (size_t)nv * S));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  cudaFree(oc.p);
-  cudaFree(ol.p);
-  cudaFree(ocnt.p);
   *n_out = nv;
   return GUAC_OK;
 }
@@ -766,7 +803,7 @@ int guac_pileup_elements(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges
   CUDA_TRY(ctx, cudaMemcpyAsync(&n_elems, total_dev, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
   int64_t nv = 0;
   GUAC_TRY(compact_visited(ctx, plan, skip_empty, nv));
-  DevBuf oc, ol, oo, oe;
+  TmpDev oc, ol, oo, oe;
   GUAC_TRY(ensure(ctx, oc, (size_t)nv * sizeof(int32_t)));
   GUAC_TRY(ensure(ctx, ol, (size_t)nv * sizeof(int64_t)));
   GUAC_TRY(ensure(ctx, oo, (size_t)(nv + 1) * sizeof(int64_t)));
@@ -787,10 +824,6 @@ int guac_pileup_elements(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges
   if (st == GUAC_OK) st = host_out(ctx, out_offsets, oo.p, (size_t)nv + 1);
   if (st == GUAC_OK) st = host_out(ctx, out_elements, oe.p, (size_t)n_elems);
   cudaStreamSynchronize(ctx->stream);
-  cudaFree(oc.p);
-  cudaFree(ol.p);
-  cudaFree(oo.p);
-  cudaFree(oe.p);
   if (st != GUAC_OK) return st;
   *n_out = nv;
   return GUAC_OK;
@@ -859,12 +892,6 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 2) * sizeof(int)));
       int* fb_count = &d_cnt->n_fallback;
       int* fb_list = ctx->b_fallback.as<int>();
-      static bool attr_set = false;
-      if (!attr_set) {
-        CUDA_TRY(ctx, cudaFuncSetAttribute(ss_tile_kernel<TCfg, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)sizeof(TileSmem<TCfg>)));
-        attr_set = true;
-      }
       // LOD-bound table for f = the VAF floor (see `prune` in tile_kernels.cuh)
       const int max_heavy = (int)std::min<int64_t>(plan.n_slots, plan.n_slots / 16 + 65536);
       GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
@@ -1061,7 +1088,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     *out_n_visited = (int64_t)visited_host;
   }
   if (out_summary) {
-    DevBuf os;
+    TmpDev os;
     GUAC_TRY(ensure(ctx, os, (size_t)nv * 2 * sizeof(guac_locus_summary)));
     // one uint64 per (locus, sample) record; rows of 2
     gather_rows_kernel<unsigned long long><<<blocks_for(plan.n_slots * 2, 256), 256, 0, ctx->stream>>>(
@@ -1071,7 +1098,6 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
     CUDA_TRY(ctx, cudaGetLastError());
     int st = host_out(ctx, out_summary, os.p, (size_t)nv * 2);
     cudaStreamSynchronize(ctx->stream);
-    cudaFree(os.p);
     if (st != GUAC_OK) return st;
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1410,11 +1436,6 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
   CUDA_TRY(ctx, cudaMemsetAsync(heavy_count, 0, sizeof(int), ctx->stream));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_vcount.p, 0, sizeof(unsigned long long), ctx->stream));
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(ctx, cudaFuncSetAttribute(ss_tile_kernel<TCfg, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<TCfg>)));
-    attr_set = true;
-  }
   TileArgs TA;
   std::memset(&TA, 0, sizeof TA);
   TA.rflags = ctx->b_rflags.as<uint8_t>();
@@ -1820,11 +1841,11 @@ int guac_ref_export(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t le
 //
 // Some hosts of this library may not call cudaMalloc at the moment they need a pileup: a plugin
 // running inside an executor whose whole device memory is owned by the host framework's pool
-// allocator (an allocation behind its back fails or fragments the pool), or code that is already
-// between cudaStreamBeginCapture and cudaStreamEndCapture, where allocating is not allowed.  For
-// them this entry point does the work of guac_pileup_counts (dense, skip_empty = 0, one range of
-// one contig) with every byte of working memory taken from the fixed array below; inputs and the
-// output are device buffers the caller already owns.
+// allocator (an allocation behind its back fails or fragments the pool).  For them this entry
+// point does the work of guac_pileup_counts (dense, skip_empty = 0, one range of one contig) with
+// every byte of working memory taken from the fixed array below; inputs and the output are device
+// buffers the caller already owns.  The call waits on `stream` twice (its two small records travel
+// through the caller's stack) and returns with the caller's current device restored.
 //
 // The working memory holds the per-read end loci, the running maximum used to find a tile's first
 // read, the scan's partial totals, the tile descriptors, the visited flags, the one-entry reference
@@ -1891,13 +1912,25 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
   const int S = d_batch->n_samples;
   if (n < 0 || S <= 0 || S > 255 || range_start < 0 || n_loci < 0 || contig_id < 0 || contig_id >= (1 << 22))
     return noalloc_fail(GUAC_E_INVALID_INPUT, "bad read batch header or loci range");
+  if (ref_len < 0 || ref_offset < 0) return noalloc_fail(GUAC_E_INVALID_INPUT, "negative reference offset or length");
+  if (range_end >= ((int64_t)1 << 40))  // build_tiles_kernel packs contig_id << 40 | locus
+    return noalloc_fail(GUAC_E_INVALID_INPUT, "loci range beyond 2^40");
   if (n > NOALLOC_MAX_READS)
     return noalloc_fail(GUAC_E_UNSUPPORTED, "guac_pileup_counts_noalloc: " + std::to_string(n) + " reads exceed the fixed working memory (" +
                                                 std::to_string(NOALLOC_MAX_READS) + " reads per call); split the batch or use guac_pileup_counts");
   if (n_loci > NOALLOC_MAX_LOCI)
     return noalloc_fail(GUAC_E_UNSUPPORTED, "guac_pileup_counts_noalloc: " + std::to_string(n_loci) + " loci exceed the fixed working memory (" +
                                                 std::to_string(NOALLOC_MAX_LOCI) + " loci per call); split the range or use guac_pileup_counts");
-  NA_CUDA(cudaSetDevice(device));
+  // the caller's current device comes back on every return path (a plugin must not move its host's device)
+  struct DeviceRestore {
+    int prev = -1;
+    ~DeviceRestore() {
+      if (prev >= 0) cudaSetDevice(prev);
+    }
+  } restore;
+  NA_CUDA(cudaGetDevice(&restore.prev));
+  if (restore.prev == device) restore.prev = -1;
+  else NA_CUDA(cudaSetDevice(device));
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_handle);
   // Set-up, once per device and with that device current: resolve the symbol to its device address.
   // (The first call on a device therefore does a little extra work; make it before any stream capture.)
@@ -1981,3 +2014,17 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 
 #include "assembly_entry.inl"
 #include "compact_entry.inl"
+
+namespace {
+cudaError_t configure_device_functions() {
+  using TCfg = TileCfg<GUAC_TK_TL>;
+  const int tile_smem = (int)sizeof(TileSmem<TCfg>);
+  cudaError_t e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(asm_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_align_smem(ASM_ALIGN_MAX_S));
+  return e;
+}
+}  // namespace

@@ -84,6 +84,28 @@ __global__ void build_tiles_kernel(const RangeDev* __restrict__ ranges, int n_ra
   tiles[t] = tl;
 }
 
+// Offsets of a caller-built batch (guac_reads_upload): non-decreasing and inside the uploaded streams, and the
+// CIGAR's sequenced length equal to the read's base count — a batch that breaks either would make the kernels
+// index outside the read's own words / bases.  bad: bit 0 offsets, bit 1 lengths.
+__global__ void validate_offsets_kernel(int64_t n, const uint32_t* __restrict__ cigar_off, const uint64_t* __restrict__ seq_off,
+                                        uint32_t n_cigar, uint64_t n_bases, int* __restrict__ bad) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  if (cigar_off[r + 1] < cigar_off[r] || cigar_off[r + 1] > n_cigar || seq_off[r + 1] < seq_off[r] || seq_off[r + 1] > n_bases)
+    atomicOr(bad, 1);
+}
+__global__ void validate_lengths_kernel(int64_t n, const uint32_t* __restrict__ cigar_off, const uint32_t* __restrict__ cigar,
+                                        const uint64_t* __restrict__ seq_off, int* __restrict__ bad) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  uint64_t len = 0;
+  for (uint32_t c = cigar_off[r]; c < cigar_off[r + 1]; ++c) {
+    const uint32_t w = cigar[c];
+    if (consumes_read(w & 15)) len += w >> 4;
+  }
+  if (len != seq_off[r + 1] - seq_off[r]) atomicOr(bad, 2);
+}
+
 // read.end = start + getPaddedReferenceLength (MappedRead.scala:75): M D N = X and P count.
 __global__ void read_ends_kernel(int64_t n, const int64_t* __restrict__ start, const int32_t* __restrict__ contig_id,
                                  const uint32_t* __restrict__ cigar_off, const uint32_t* __restrict__ cigar,

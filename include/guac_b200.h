@@ -184,21 +184,24 @@ int guac_pileup_elements(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges
 /*
  * The counting closure for hosts that must not allocate.  (No counterpart in the reference: the JVM has no
  * such constraint.)  Some callers cannot call cudaMalloc when they need a pileup — a plugin inside an
- * executor whose device memory belongs entirely to the host framework's pool allocator, or code already
- * inside a stream capture — so this variant of guac_pileup_counts (dense: skip_empty = 0; ONE range of ONE
- * contig) takes no guac_ctx and allocates nothing, neither on the device nor pinned on the host: its
- * working memory is a fixed array inside the library, about 3.9 MiB per GPU that loads it, kept until the
- * process exits.
+ * executor whose device memory belongs entirely to the host framework's pool allocator — so this variant
+ * of guac_pileup_counts (dense: skip_empty = 0; ONE range of ONE contig) takes no guac_ctx and allocates
+ * nothing, neither on the device nor pinned on the host: its working memory is a fixed array inside the
+ * library, about 3.9 MiB per GPU that loads it, kept until the process exits.
  *
  *   d_batch      a guac_read_batch whose POINTERS ARE DEVICE POINTERS (the struct itself is on the host);
  *                every read lies on `contig_id`, sorted by start
  *   d_ref_bases  device pointer to upper-case ASCII reference bases of loci [ref_offset, ref_offset+ref_len)
  *   d_out_counts device buffer of (range_end - range_start) * n_samples records, written in locus order
- *   stream       the cudaStream_t to run on (NULL = default stream); the call returns after it has drained
+ *   stream       the cudaStream_t to run on (NULL = default stream); the call waits on it twice and returns
+ *                after it has drained
+ * Buffers need exactly the sizes guac_read_batch states (no padding).  The call makes `device` current while
+ * it runs and restores the caller's current device before it returns.
  *
  * Limits: at most guac_noalloc_max_reads() reads (131 072) and guac_noalloc_max_loci() loci (524 288) per
- * call; larger inputs are refused with GUAC_E_UNSUPPORTED and a message naming the limit.  The first call
- * on a device also resolves the array's device address; make that call before starting any stream capture.
+ * call; larger inputs are refused with GUAC_E_UNSUPPORTED and a message naming the limit; negative reference
+ * offsets / lengths and loci at or beyond 2^40 are GUAC_E_INVALID_INPUT.  The first call on a device also
+ * resolves the array's device address; make that call before starting any stream capture.
  * All calls on a device share the array and it keeps the last call's contents (the call clears what must
  * start at zero, including d_out_counts), so calls whose GPU work overlaps — two streams, two threads —
  * race; serialise them.  Errors: status code, text from guac_noalloc_last_error().

@@ -1,6 +1,6 @@
 """guac_pileup_counts_noalloc: the pileup-counting entry point for hosts that are not allowed to
-allocate GPU memory when they call (their framework owns the whole device pool, or they are
-already inside a stream capture).  It works out of a fixed array inside the library, so this test
+allocate GPU memory when they call (their framework owns the whole device pool).  It works out of
+a fixed array inside the library, so this test
 checks exactly what such a caller relies on: given device buffers it already owns, two calls in a
 row — the second on different, smaller input, so stale working memory would show — must each
 return what the allocating entry point guac_pileup_counts returns for the same reads, bit for bit.
@@ -29,9 +29,7 @@ def device_batch(torch, batch):
                 exc_base=batch.packed["exc_base"], qual=batch.qual, mapq=batch.mapq, flags=batch.flags, sample_id=batch.sample_id)
     for name, arr in cols.items():
         raw = np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
-        pad = np.zeros(raw.shape[0] + 64, np.uint8)  # the bit-stream readers look one word ahead
-        pad[:raw.shape[0]] = raw
-        t = torch.from_numpy(pad).cuda()
+        t = torch.from_numpy(raw.copy()).cuda()  # exactly the size guac_read_batch states: no padding is required
         keep.append(t)
         ftype = dict(ReadBatchC._fields_)[name]
         setattr(dev, name, C.cast(C.c_void_p(t.data_ptr()), ftype))
