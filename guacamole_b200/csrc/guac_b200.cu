@@ -23,7 +23,7 @@
 #include "synth_kernels.cuh"
 #include "tile_kernels.cuh"
 #include "stream_kernels.cuh"
-#include "joint_host.hpp"
+#include "joint_stream_kernels.cuh"
 #include "germline_kernels.cuh"
 #include "assembly_kernels.cuh"
 #include "compact_kernels.cuh"
@@ -103,6 +103,12 @@ struct guac_ctx {
   std::vector<RangeDev> plan_ranges;            // host copy of the current call's range table (make_plan)
   DevBuf r_bitmap, r_counts, r_prefix, r_rank;  // rank_by_slot
   DevBuf g_active, g_jobs, g_evs, g_strings;  // scratch of guac_germline_standard, kept between calls
+  // somatic-joint: force-call ranges, simple candidates, the fast kernel's sites / raw records / hand-backs, the generic
+  // kernels' raw records, emitted sites and their order, offsets, finished records, ln n! table
+  DevBuf j_force, j_simple, j_sites_fast, j_raw_fast, j_bail, j_raw_gen, j_emits, j_order, j_cnt, j_off, j_out_alleles, j_out_samples, j_logfact;
+  int64_t opt_sj_impl = 2;  // 2: read pass + classifying locus pass + fast site kernel (default); 1: single-kernel locus pass; 0: no fast site kernel
+  int64_t stat_sj_simple = 0, stat_sj_bail = 0, stat_sj_sites = 0, stat_sj_emitted_sites = 0;
+  void* h_counters = nullptr;  // pinned: the per-call counter block comes back without a staging copy
   std::vector<std::pair<void*, size_t>> asm_blocks;  // assembly scratch, bump-allocated per call (assembly_entry.inl)
   size_t asm_block = 0, asm_off = 0;
 };
@@ -475,6 +481,67 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   return GUAC_OK;
 }
 
+// ln n! for n < SJ_LOGFACT_N, summed in extended precision and rounded once (Fisher's exact test of the joint caller's
+// StrandBias annotation, filters/FishersExactTest.scala:12-19)
+constexpr int SJ_LOGFACT_N = 1 << 16;
+int sj_logfact_table(guac_ctx* ctx) {
+  if (ctx->j_logfact.p) return GUAC_OK;
+  std::vector<double> t((size_t)SJ_LOGFACT_N);
+  long double acc = 0.0L;
+  t[0] = 0.0;
+  for (int n = 1; n < SJ_LOGFACT_N; ++n) {
+    acc += std::log((long double)n);
+    t[(size_t)n] = (double)acc;
+  }
+  GUAC_TRY(upload(ctx, ctx->j_logfact, t.data(), t.size()));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `t` is a temporary
+  return GUAC_OK;
+}
+
+// Read pass of the stream form (stream_kernels.cuh): every read compared once with the 2-bit reference of its contig, its
+// non-Match elements left in its slot of b_bins / b_bin_count.  One launch per contig of the batch.
+int run_read_pass(guac_ctx* ctx) {
+  GUAC_TRY(sync_ref2(ctx));
+  GUAC_TRY(ensure(ctx, ctx->b_bins, (size_t)(ctx->n_reads + 1) * STREAM_EV_CAP * sizeof(uint2)));
+  GUAC_TRY(ensure(ctx, ctx->b_bin_count, (size_t)ctx->n_reads + 16));
+  {  // reads of a contig without a reference get no launch of the read pass: their counts must read 0
+    bool every_contig_has_a_reference = true;
+    for (auto& sp : ctx->contig_spans) every_contig_has_a_reference = every_contig_has_a_reference && ctx->contigs.count(sp.first) != 0;
+    if (!every_contig_has_a_reference) CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_bin_count.p, 0, (size_t)ctx->n_reads + 16, ctx->stream));
+  }
+  for (auto& sp : ctx->contig_spans) {  // one launch per contig of the batch: its reference rides in the arguments
+    auto it = ctx->contigs.find(sp.first);
+    if (it == ctx->contigs.end() || sp.second.second <= sp.second.first) continue;
+    StreamArgs SA;
+    SA.hdr = ctx->b_hdr.as<uint4>();
+    SA.read_lo = sp.second.first;
+    SA.read_hi = sp.second.second;
+    SA.ref.bases = it->second.bases;
+    SA.ref.offset = it->second.offset;
+    SA.ref.len = it->second.len;
+    SA.ref.bad = it->second.refbad;
+    SA.ref2 = it->second.ref2;
+    SA.events = ctx->b_bins.as<uint2>();
+    SA.n_events = ctx->b_bin_count.as<uint8_t>();
+    SA.list = nullptr;
+    SA.n_list = 0;
+    SA.list_blocks = SA.list_period = 0;
+    SA.inline_medium = ctx->contig_spans.size() == 1 ? 0 : 1;
+    unsigned blocks = blocks_for(SA.read_hi - SA.read_lo, 256);
+    if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {  // the multi-operator reads ride in the same launch
+      SA.list = ctx->b_medium.as<int64_t>();
+      SA.n_list = ctx->n_medium;
+      SA.list_blocks = blocks_for(ctx->n_medium, 256);
+      SA.list_period = std::max(1u, blocks / SA.list_blocks) + 1;
+      blocks += SA.list_blocks;
+    }
+    ss_read_events_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->R, SA);
+    ctx->launches += 1;
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  return GUAC_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -553,8 +620,11 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
                     &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
                     &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings,
-                    &ctx->r_bitmap, &ctx->r_counts, &ctx->r_prefix, &ctx->r_rank})
+                    &ctx->r_bitmap, &ctx->r_counts, &ctx->r_prefix, &ctx->r_rank, &ctx->j_force, &ctx->j_simple, &ctx->j_sites_fast,
+                    &ctx->j_raw_fast, &ctx->j_bail, &ctx->j_raw_gen, &ctx->j_emits, &ctx->j_order, &ctx->j_cnt, &ctx->j_off,
+                    &ctx->j_out_alleles, &ctx->j_out_samples, &ctx->j_logfact})
     if (b->p) cudaFree(b->p);
+  if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   for (auto& kv : ctx->contigs)
     if (kv.second.ref2) cudaFree(kv.second.ref2);
   for (auto& kv : ctx->contigs)
@@ -915,48 +985,10 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       TA.err = ctx->b_err.as<DeviceError>();
       if (ctx->opt_ss_impl == 2) {
         // stream implementation: the reads are compared with the reference by a kernel of their own, then the locus pass
-        GUAC_TRY(sync_ref2(ctx));
-        GUAC_TRY(ensure(ctx, ctx->b_bins, (size_t)(ctx->n_reads + 1) * STREAM_EV_CAP * sizeof(uint2)));
-        GUAC_TRY(ensure(ctx, ctx->b_bin_count, (size_t)ctx->n_reads + 16));
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        GUAC_TRY(run_read_pass(ctx));
         TA.ev_by_read = ctx->b_bins.as<uint2>();
         TA.ev_count = ctx->b_bin_count.as<uint8_t>();
-        {  // reads of a contig without a reference get no launch of the read pass: their counts must read 0
-          bool every_contig_has_a_reference = true;
-          for (auto& sp : ctx->contig_spans) every_contig_has_a_reference = every_contig_has_a_reference && ctx->contigs.count(sp.first) != 0;
-          if (!every_contig_has_a_reference)
-            CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_bin_count.p, 0, (size_t)ctx->n_reads + 16, ctx->stream));
-        }
-        cudaEventRecord(ctx->ev0, ctx->stream);
-        for (auto& sp : ctx->contig_spans) {  // one launch per contig of the batch: its reference rides in the arguments
-          auto it = ctx->contigs.find(sp.first);
-          if (it == ctx->contigs.end() || sp.second.second <= sp.second.first) continue;
-          StreamArgs SA;
-          SA.hdr = ctx->b_hdr.as<uint4>();
-          SA.read_lo = sp.second.first;
-          SA.read_hi = sp.second.second;
-          SA.ref.bases = it->second.bases;
-          SA.ref.offset = it->second.offset;
-          SA.ref.len = it->second.len;
-          SA.ref.bad = it->second.refbad;
-          SA.ref2 = it->second.ref2;
-          SA.events = ctx->b_bins.as<uint2>();
-          SA.n_events = ctx->b_bin_count.as<uint8_t>();
-          SA.list = nullptr;
-          SA.n_list = 0;
-          SA.list_blocks = SA.list_period = 0;
-          SA.inline_medium = ctx->contig_spans.size() == 1 ? 0 : 1;
-          unsigned blocks = blocks_for(SA.read_hi - SA.read_lo, 256);
-          if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {  // the multi-operator reads ride in the same launch
-            SA.list = ctx->b_medium.as<int64_t>();
-            SA.n_list = ctx->n_medium;
-            SA.list_blocks = blocks_for(ctx->n_medium, 256);
-            SA.list_period = std::max(1u, blocks / SA.list_blocks) + 1;
-            blocks += SA.list_blocks;
-          }
-          ss_read_events_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->R, SA);
-          ctx->launches += 1;
-        }
-        CUDA_TRY(ctx, cudaGetLastError());
         ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
       } else {
         cudaEventRecord(ctx->ev0, ctx->stream);
@@ -1160,31 +1192,48 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
   }
   GUAC_TRY(reset_error(ctx));
   GUAC_TRY(ensure(ctx, ctx->b_visited, (size_t)plan.n_slots));
-  GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(int)));
   GUAC_TRY(ensure(ctx, ctx->b_fallback, (size_t)(plan.n_tiles + 2) * sizeof(int)));
-  GUAC_TRY(ensure(ctx, ctx->b_vcount, sizeof(unsigned long long)));
-  DevBuf d_force;
-  GUAC_TRY(upload(ctx, d_force, force_loci, (size_t)n_force));
-  // Dense half: the streaming tile kernel marks the visited loci and lists the pileup loci where an alternate allele can
-  // start (>= any_allele_min_supporting_reads reads of the discovery samples with a non-Match element at the next
-  // locus, or a force-called locus); only those go to the per-locus discovery kernel.
+  GUAC_TRY(upload(ctx, ctx->j_force, force_loci, (size_t)n_force));
+  GUAC_TRY(sj_logfact_table(ctx));
+  // the call's counters: one block on the device, one pinned copy on the host
+  struct SJCounters {
+    int n_fallback, n_complex, n_simple, n_bail;
+    int n_sites_fast, n_jobs_fast, n_sites_gen, n_jobs_gen;
+    int n_emits, _pad;
+    unsigned long long n_visited;
+    long long total_alleles, total_string_bytes;
+  };
+  GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(SJCounters)));
+  SJCounters* d_cnt = ctx->b_ncalls.as<SJCounters>();
+  if (!ctx->h_counters) CUDA_TRY(ctx, cudaMallocHost(&ctx->h_counters, 256));
+  SJCounters& h_cnt = *static_cast<SJCounters*>(ctx->h_counters);
+  auto read_counters = [&]() -> int {
+    CUDA_TRY(ctx, cudaMemcpyAsync(&h_cnt, d_cnt, sizeof(SJCounters), cudaMemcpyDeviceToHost, ctx->stream));
+    return check_device_error(ctx);  // synchronises
+  };
+  // Dense half.  Stream form: the read pass leaves every read's non-Match elements in its slot, the locus pass (tile
+  // kernel, MODE 2) marks the visited loci and lists the pileup loci x where an alternate allele can start at x + 1:
+  // `simple` ones (single-base substitutions only; at most four samples) for the fast site kernel, the others — and
+  // every force-called locus — for the generic per-locus kernels.
+  bool every_contig_has_a_reference = true;
+  for (auto& sp : ctx->contig_spans) every_contig_has_a_reference = every_contig_has_a_reference && ctx->contigs.count(sp.first) != 0;
+  const bool stream = ctx->opt_sj_impl == 2 && every_contig_has_a_reference;
+  const bool classify = ctx->opt_sj_impl != 0 && S <= SJF_SMAX;
   SSParamsDev SP;
   std::memset(&SP, 0, sizeof SP);
   SP.normal_sample = SP.tumor_sample = -1;
   SP.n_samples = S;
   SP.min_alt_reads = std::max(1, params->any_allele_min_supporting_reads);
   for (int d = 0; d < P.n_discovery; ++d) SP.sample_mask |= 1u << P.discovery[d];
-  int* fb_count = ctx->b_fallback.as<int>();
-  int* fb_list = fb_count + 1;
-  int* heavy_count = fb_count + 1 + plan.n_tiles;
-  int max_heavy = (int)std::min<int64_t>(plan.n_slots, plan.n_slots / 4 + 65536);
-  int counts[2] = {0, 0};
+  int* fb_list = ctx->b_fallback.as<int>();
+  int max_heavy = (int)std::min<int64_t>(plan.n_slots, std::max<int64_t>(plan.n_slots / (classify ? 32 : 4) + 65536, (int64_t)(ctx->b_heavy.cap / sizeof(Tile)) - 1));
+  int max_simple = classify ? (int)std::min<int64_t>(plan.n_slots, std::max<int64_t>(plan.n_slots / 16 + 65536, (int64_t)(ctx->j_simple.cap / sizeof(Tile)) - 1)) : 0;
   cudaEventRecord(ctx->ev0, ctx->stream);
+  if (stream) GUAC_TRY(run_read_pass(ctx));
   for (int attempt = 0; attempt < 2; ++attempt) {
     GUAC_TRY(ensure(ctx, ctx->b_heavy, (size_t)max_heavy * sizeof(Tile) + 16));
-    CUDA_TRY(ctx, cudaMemsetAsync(fb_count, 0, sizeof(int), ctx->stream));
-    CUDA_TRY(ctx, cudaMemsetAsync(heavy_count, 0, sizeof(int), ctx->stream));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_vcount.p, 0, sizeof(unsigned long long), ctx->stream));
+    GUAC_TRY(ensure(ctx, ctx->j_simple, (size_t)max_simple * sizeof(Tile) + 16));
+    CUDA_TRY(ctx, cudaMemsetAsync(d_cnt, 0, sizeof(SJCounters), ctx->stream));
     TileArgs TA;
     std::memset(&TA, 0, sizeof TA);
     TA.rflags = ctx->b_rflags.as<uint8_t>();
@@ -1193,199 +1242,205 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     TA.tiles = ctx->b_tiles.as<Tile>();
     TA.visited = ctx->b_visited.as<uint8_t>();
     TA.heavy = ctx->b_heavy.as<Tile>();
-    TA.n_heavy = heavy_count;
+    TA.n_heavy = &d_cnt->n_complex;
     TA.max_heavy = max_heavy;
     TA.fallback_tiles = fb_list;
-    TA.n_fallback = fb_count;
+    TA.n_fallback = &d_cnt->n_fallback;
     TA.force_fallback_mod = (int)ctx->opt_force_fallback_mod;
-    TA.n_visited = ctx->b_vcount.as<unsigned long long>();
+    TA.n_visited = &d_cnt->n_visited;
     TA.err = ctx->b_err.as<DeviceError>();
-    TA.force = d_force.as<guac_range>();
+    TA.force = ctx->j_force.as<guac_range>();
     TA.n_force = n_force;
-    ss_tile_kernel<TCfg, 2><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, SP, TA);
+    TA.sample_bits = classify ? 1 : 0;
+    TA.simple = ctx->j_simple.as<Tile>();
+    TA.n_simple = &d_cnt->n_simple;
+    TA.max_simple = max_simple;
+    if (stream) {
+      TA.ev_by_read = ctx->b_bins.as<uint2>();
+      TA.ev_count = ctx->b_bin_count.as<uint8_t>();
+      ss_tile_kernel<TCfg, 2, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, SP, TA);
+    } else {
+      ss_tile_kernel<TCfg, 2, false><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, SP, TA);
+    }
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaMemcpyAsync(&counts[0], fb_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(&counts[1], heavy_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    if (counts[1] <= max_heavy) break;
-    max_heavy = counts[1];  // rerun with room for every candidate locus
+    GUAC_TRY(read_counters());
+    if (h_cnt.n_complex <= max_heavy && h_cnt.n_simple <= max_simple) break;
+    max_heavy = std::max(max_heavy, h_cnt.n_complex);  // rerun with room for every candidate locus
+    max_simple = std::max(max_simple, h_cnt.n_simple);
   }
-  ctx->last_fallback_tiles = counts[0];
-  ctx->last_heavy_loci = counts[1];
+  const int n_fb = h_cnt.n_fallback, n_complex = h_cnt.n_complex, n_simple = h_cnt.n_simple;
+  const unsigned long long n_visited_tiles = h_cnt.n_visited;
+  ctx->last_fallback_tiles = n_fb;
+  ctx->last_heavy_loci = n_complex;
+  ctx->stat_sj_simple = n_simple;
   trace.mark("dense prefilter");
-  int max_sites = (int)std::max<size_t>(ctx->b_sj_sites.cap / sizeof(SJSiteDev), 1 << 14);
-  int n_sites = 0;
-  for (int attempt = 0; attempt < 2; ++attempt) {
-    GUAC_TRY(ensure(ctx, ctx->b_sj_sites, (size_t)max_sites * sizeof(SJSiteDev)));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ncalls.p, 0, sizeof(int), ctx->stream));
-    if (counts[0] > 0) {  // whole tiles the streaming kernel declined
-      sj_discover_kernel<<<(unsigned)counts[0], CTA_THREADS, 0, ctx->stream>>>(
-          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, counts[0], 0, P, d_force.as<guac_range>(), n_force,
-          ctx->b_visited.as<uint8_t>(), ctx->b_sj_sites.as<SJSiteDev>(), ctx->b_ncalls.as<int>(), max_sites, ctx->b_err.as<DeviceError>());
-      ctx->launches += 1;
-    }
-    if (counts[1] > 0) {  // candidate loci, one warp each
-      sj_discover_kernel<<<blocks_for(counts[1], WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
-          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, counts[1], 1, P, d_force.as<guac_range>(), n_force, nullptr,
-          ctx->b_sj_sites.as<SJSiteDev>(), ctx->b_ncalls.as<int>(), max_sites, ctx->b_err.as<DeviceError>());
-      ctx->launches += 1;
-    }
-    cudaEventRecord(ctx->ev1, ctx->stream);
-    ctx->have_timing = true;
-    ctx->timed_loci = plan.n_slots;
-    CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaMemcpyAsync(&n_sites, ctx->b_ncalls.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    int st = check_device_error(ctx);
-    if (st != GUAC_OK) {
-      cudaFree(d_force.p);
-      return st;
-    }
-    if (n_sites <= max_sites) break;
-    max_sites = n_sites;
-  }
-  cudaFree(d_force.p);
-  trace.mark("discover");
-  // sites stay on the device in discovery order; the host walks them in (range order, locus) order through `order`
   const size_t raw_stride = offsetof(SJEvidenceDev, slots) + (size_t)(S + 2) * sizeof(SJSlotDev);
-  SJSiteDev* sites = nullptr;
-  unsigned char* raw = nullptr;
-  std::vector<int> order((size_t)n_sites);
-  std::vector<int2> jobs;
-  struct PinnedGuard {  // pinned staging goes back to the pool on every return path
-    guac_ctx* ctx;
-    void* p[2] = {nullptr, nullptr};
-    ~PinnedGuard() {
-      for (void* q : p)
-        if (q) guac_free(ctx, q);
+  // fast site kernel over the simple candidates: sites, alleles and raw evidence in one pass
+  int n_sites_fast = 0, n_bail = 0;
+  if (n_simple > 0) {
+    GUAC_TRY(ensure(ctx, ctx->j_sites_fast, (size_t)n_simple * sizeof(SJSiteDev)));
+    GUAC_TRY(ensure(ctx, ctx->j_bail, (size_t)n_simple * sizeof(Tile)));
+    int max_jobs = (int)std::max<int64_t>((int64_t)n_simple + n_simple / 4 + 1024, (int64_t)(ctx->j_raw_fast.cap / raw_stride));
+    for (int attempt = 0; attempt < 2; ++attempt) {
+      GUAC_TRY(ensure(ctx, ctx->j_raw_fast, (size_t)max_jobs * raw_stride));
+      if (attempt > 0) CUDA_TRY(ctx, cudaMemsetAsync(&d_cnt->n_bail, 0, 3 * sizeof(int), ctx->stream));  // n_bail, n_sites_fast, n_jobs_fast
+      SJFArgs FA;
+      std::memset(&FA, 0, sizeof FA);
+      FA.hdr = ctx->b_hdr.as<uint4>();
+      FA.refs = ctx->d_refs.as<RefView>();
+      FA.cands = ctx->j_simple.as<Tile>();
+      FA.n_cands = &d_cnt->n_simple;
+      FA.max_cands = n_simple;
+      FA.force = ctx->j_force.as<guac_range>();
+      FA.n_force = n_force;
+      FA.sites = ctx->j_sites_fast.as<SJSiteDev>();
+      FA.n_sites = &d_cnt->n_sites_fast;
+      FA.max_sites = n_simple;
+      FA.raw = ctx->j_raw_fast.as<unsigned char>();
+      FA.raw_stride = raw_stride;
+      FA.n_jobs = &d_cnt->n_jobs_fast;
+      FA.max_jobs = max_jobs;
+      FA.bail = ctx->j_bail.as<Tile>();
+      FA.n_bail = &d_cnt->n_bail;
+      FA.max_bail = n_simple;
+      FA.err = ctx->b_err.as<DeviceError>();
+      const unsigned grid = (unsigned)std::min<int64_t>(blocks_for(n_simple, 8), 148 * 16);
+      sj_snv_site_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->R, P, FA);
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+      GUAC_TRY(read_counters());
+      if (h_cnt.n_jobs_fast <= max_jobs) break;
+      max_jobs = h_cnt.n_jobs_fast;
     }
-  } staging{ctx};
-  if (n_sites > 0) {
-    GUAC_TRY(pinned_alloc(ctx, &staging.p[0], (size_t)n_sites * sizeof(SJSiteDev)));
-    sites = static_cast<SJSiteDev*>(staging.p[0]);
-    CUDA_TRY(ctx, cudaMemcpyAsync(sites, ctx->b_sj_sites.p, (size_t)n_sites * sizeof(SJSiteDev), cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    for (int i = 0; i < n_sites; ++i) order[(size_t)i] = i;
-    std::sort(order.begin(), order.end(), [&](int a, int b) { return sites[a].slot < sites[b].slot; });
-    for (int i = 0; i < n_sites; ++i)
-      for (int a = 0; a < sites[order[(size_t)i]].n_alleles; ++a) jobs.push_back(make_int2(order[(size_t)i], a));
-    DevBuf d_jobs, d_raw;
-    GUAC_TRY(upload(ctx, d_jobs, jobs.data(), jobs.size()));
-    GUAC_TRY(ensure(ctx, d_raw, jobs.size() * raw_stride));
-    GUAC_TRY(pinned_alloc(ctx, &staging.p[1], jobs.size() * raw_stride));
-    raw = static_cast<unsigned char*>(staging.p[1]);
-    sj_evidence_kernel<<<(unsigned)jobs.size(), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_sj_sites.as<SJSiteDev>(),
-                                                                         d_jobs.as<int2>(), d_raw.as<unsigned char>(), raw_stride,
-                                                                         ctx->b_err.as<DeviceError>());
+    n_sites_fast = h_cnt.n_sites_fast;
+    n_bail = h_cnt.n_bail;
+  }
+  ctx->stat_sj_bail = n_bail;
+  trace.mark("fast site kernel");
+  // generic per-locus kernels: whole tiles the locus pass declined, the complex candidates, the sites the fast kernel
+  // handed back
+  int n_sites_gen = 0, n_jobs_gen = 0;
+  const int64_t max_sites_gen = (int64_t)n_fb * TCfg::TL + n_complex + n_bail;
+  if (max_sites_gen > 0) {
+    GUAC_TRY(ensure(ctx, ctx->b_sj_sites, (size_t)max_sites_gen * sizeof(SJSiteDev)));
+    const int max_sites = (int)std::min<int64_t>(max_sites_gen, INT32_MAX);
+    if (n_fb > 0) {
+      sj_discover_kernel<<<(unsigned)n_fb, CTA_THREADS, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_tiles.as<Tile>(), fb_list, n_fb, 0, P, ctx->j_force.as<guac_range>(), n_force,
+          ctx->b_visited.as<uint8_t>(), ctx->b_sj_sites.as<SJSiteDev>(), &d_cnt->n_sites_gen, max_sites, &d_cnt->n_jobs_gen,
+          ctx->b_err.as<DeviceError>());
+      ctx->launches += 1;
+    }
+    if (n_complex > 0) {
+      sj_discover_kernel<<<blocks_for(n_complex, WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->b_heavy.as<Tile>(), nullptr, n_complex, 1, P, ctx->j_force.as<guac_range>(), n_force,
+          nullptr, ctx->b_sj_sites.as<SJSiteDev>(), &d_cnt->n_sites_gen, max_sites, &d_cnt->n_jobs_gen, ctx->b_err.as<DeviceError>());
+      ctx->launches += 1;
+    }
+    if (n_bail > 0) {
+      sj_discover_kernel<<<blocks_for(n_bail, WARPS_PER_CTA), CTA_THREADS, 0, ctx->stream>>>(
+          ctx->R, ctx->d_refs.as<RefView>(), ctx->j_bail.as<Tile>(), nullptr, n_bail, 1, P, ctx->j_force.as<guac_range>(), n_force,
+          nullptr, ctx->b_sj_sites.as<SJSiteDev>(), &d_cnt->n_sites_gen, max_sites, &d_cnt->n_jobs_gen, ctx->b_err.as<DeviceError>());
+      ctx->launches += 1;
+    }
+    CUDA_TRY(ctx, cudaGetLastError());
+    GUAC_TRY(read_counters());
+    n_sites_gen = h_cnt.n_sites_gen;
+    n_jobs_gen = h_cnt.n_jobs_gen;
+    if (n_sites_gen > 0) {
+      GUAC_TRY(ensure(ctx, ctx->j_raw_gen, (size_t)std::max(n_jobs_gen, 1) * raw_stride));
+      const int64_t ctas = (int64_t)n_sites_gen * P.max_alleles;
+      sj_evidence_kernel<<<(unsigned)ctas, 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_sj_sites.as<SJSiteDev>(), 0,
+                                                                  ctx->j_raw_gen.as<unsigned char>(), raw_stride, ctx->b_err.as<DeviceError>());
+      ctx->launches += 1;
+      CUDA_TRY(ctx, cudaGetLastError());
+    }
+  }
+  ctx->stat_sj_sites = (int64_t)n_sites_fast + n_sites_gen;
+  trace.mark("generic kernels");
+  // posteriors, calls, annotations, emit policy: one thread per site; only emitted sites are listed
+  const int n_sites_all = n_sites_fast + n_sites_gen;
+  int n_emits = 0;
+  if (n_sites_all > 0) {
+    GUAC_TRY(ensure(ctx, ctx->j_emits, (size_t)n_sites_all * sizeof(SJEmitDev)));
+    if (n_sites_fast > 0) {
+      sj_posterior_kernel<<<blocks_for(n_sites_fast, 128), 128, 0, ctx->stream>>>(
+          *params, ctx->j_logfact.as<double>(), SJ_LOGFACT_N, ctx->j_sites_fast.as<SJSiteDev>(), n_sites_fast, 0,
+          ctx->j_raw_fast.as<unsigned char>(), raw_stride, ctx->j_emits.as<SJEmitDev>(), &d_cnt->n_emits);
+      ctx->launches += 1;
+    }
+    if (n_sites_gen > 0) {
+      sj_posterior_kernel<<<blocks_for(n_sites_gen, 128), 128, 0, ctx->stream>>>(
+          *params, ctx->j_logfact.as<double>(), SJ_LOGFACT_N, ctx->b_sj_sites.as<SJSiteDev>(), n_sites_gen, SJ_SITE_GENERIC,
+          ctx->j_raw_gen.as<unsigned char>(), raw_stride, ctx->j_emits.as<SJEmitDev>(), &d_cnt->n_emits);
+      ctx->launches += 1;
+    }
+    CUDA_TRY(ctx, cudaGetLastError());
+    GUAC_TRY(read_counters());
+    n_emits = h_cnt.n_emits;
+  }
+  ctx->stat_sj_emitted_sites = n_emits;
+  trace.mark("posteriors");
+  // emitted sites in (range order, locus) = slot order; offsets of their records and strings by two scans; the finished
+  // records written on the device
+  int64_t total_alleles = 0, total_strings = 0;
+  if (n_emits > 0) {
+    GUAC_TRY(ensure(ctx, ctx->r_rank, (size_t)n_emits * sizeof(int)));
+    GUAC_TRY(ensure(ctx, ctx->j_order, (size_t)n_emits * sizeof(int)));
+    GUAC_TRY(ensure(ctx, ctx->j_cnt, (size_t)n_emits * 2 * sizeof(int32_t)));
+    GUAC_TRY(ensure(ctx, ctx->j_off, (size_t)(n_emits + 1) * 2 * sizeof(int64_t)));
+    GUAC_TRY(rank_by_slot(ctx, ctx->j_emits.p, sizeof(SJEmitDev), offsetof(SJEmitDev, slot), n_emits, plan.n_slots, ctx->r_rank.as<int>()));
+    int32_t* n_by_rank = ctx->j_cnt.as<int32_t>();
+    int32_t* len_by_rank = n_by_rank + n_emits;
+    int64_t* allele_off = ctx->j_off.as<int64_t>();
+    int64_t* string_off = allele_off + n_emits + 1;
+    sj_order_kernel<<<blocks_for(n_emits, 256), 256, 0, ctx->stream>>>(ctx->j_emits.as<SJEmitDev>(), ctx->r_rank.as<int>(), n_emits,
+                                                                       ctx->j_order.as<int>(), n_by_rank, len_by_rank);
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaMemcpyAsync(raw, d_raw.p, jobs.size() * raw_stride, cudaMemcpyDeviceToHost, ctx->stream));
-    int st = check_device_error(ctx);
-    cudaFree(d_jobs.p);
-    cudaFree(d_raw.p);
+    GUAC_TRY((device_scan<true, int32_t>(ctx, n_by_rank, allele_off, n_emits, OpSum(), (int64_t*)&d_cnt->total_alleles)));
+    GUAC_TRY((device_scan<true, int32_t>(ctx, len_by_rank, string_off, n_emits, OpSum(), (int64_t*)&d_cnt->total_string_bytes)));
+    GUAC_TRY(read_counters());
+    total_alleles = h_cnt.total_alleles;
+    total_strings = h_cnt.total_string_bytes;
+    if (total_strings >= ((int64_t)1 << 32)) return fail(ctx, GUAC_E_UNSUPPORTED, "more than 4 GiB of allele strings in one call: split the loci");
+    GUAC_TRY(ensure(ctx, ctx->j_out_alleles, (size_t)total_alleles * sizeof(guac_sj_allele_evidence)));
+    GUAC_TRY(ensure(ctx, ctx->j_out_samples, (size_t)total_alleles * (S + 2) * sizeof(guac_sj_sample_evidence)));
+    GUAC_TRY(ensure(ctx, ctx->b_arena, (size_t)total_strings + 16));
+    sj_final_kernel<<<blocks_for(n_emits, 128), 128, 0, ctx->stream>>>(
+        ctx->R, ctx->d_refs.as<RefView>(), *params, ctx->j_logfact.as<double>(), SJ_LOGFACT_N, ctx->j_sites_fast.as<SJSiteDev>(),
+        ctx->b_sj_sites.as<SJSiteDev>(), ctx->j_raw_fast.as<unsigned char>(), ctx->j_raw_gen.as<unsigned char>(), raw_stride,
+        ctx->j_emits.as<SJEmitDev>(), ctx->j_order.as<int>(), n_emits, allele_off, string_off,
+        ctx->j_out_alleles.as<guac_sj_allele_evidence>(), ctx->j_out_samples.as<guac_sj_sample_evidence>(), ctx->b_arena.as<char>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+  }
+  cudaEventRecord(ctx->ev1, ctx->stream);
+  ctx->have_timing = true;
+  ctx->timed_loci = plan.n_slots;
+  trace.mark("records on the device");
+  // only the emitted records cross PCIe
+  GUAC_TRY(host_out(ctx, out_alleles, ctx->j_out_alleles.p, (size_t)total_alleles));
+  {
+    int st = host_out(ctx, out_samples, ctx->j_out_samples.p, (size_t)total_alleles * (S + 2));
+    if (st == GUAC_OK) st = host_out(ctx, out_arena, ctx->b_arena.p, (size_t)total_strings);
+    if (st == GUAC_OK) st = check_device_error(ctx);  // synchronises
     if (st != GUAC_OK) return st;
   }
-  trace.mark("evidence kernel");
-  if (trace.on) std::fprintf(stderr, "[guac trace] sites %d jobs %zu\n", n_sites, jobs.size());
-  // host: posteriors, calls, annotations, emit policy; then lay out the strings
-  std::vector<guac_sj_allele_evidence> alleles;
-  std::vector<guac_sj_sample_evidence> samples;
-  std::vector<SJStringJob> strings;
-  uint32_t arena_off = 0;
-  auto add_string = [&](int kind, int64_t a, int32_t b, int32_t len, uint32_t& off, uint32_t& out_len) {
-    SJStringJob j;
-    j.a = a;
-    j.b = b;
-    j.len = len;
-    j.arena_off = arena_off;
-    j.kind = kind;
-    strings.push_back(j);
-    off = arena_off;
-    out_len = (uint32_t)len;
-    arena_off += (uint32_t)len;
-  };
-  // The per-site arithmetic (posteriors, annotations, emit policy) is independent from site to site: it runs on the
-  // host's cores in slices of the site list; the layout of the emitted records below stays serial and in site order.
-  std::vector<size_t> job_start((size_t)n_sites + 1, 0);
-  for (int oi = 0; oi < n_sites; ++oi) job_start[(size_t)oi + 1] = job_start[(size_t)oi] + (size_t)sites[order[(size_t)oi]].n_alleles;
-  std::vector<std::vector<joint::Record>> emitted_by_site((size_t)n_sites);
-  {
-    auto evaluate_sites = [&](int lo, int hi) {
-      std::vector<joint::Record> all;
-      for (int oi = lo; oi < hi; ++oi) {
-        const SJSiteDev& site = sites[order[(size_t)oi]];
-        all.clear();
-        for (int a = 0; a < site.n_alleles; ++a)
-          all.push_back(joint::evaluate(*params, site, a,
-                                        *reinterpret_cast<const SJEvidenceDev*>(raw + (job_start[(size_t)oi] + (size_t)a) * raw_stride)));
-        emitted_by_site[(size_t)oi] = joint::emit(*params, site.forced != 0, all);
-      }
-    };
-    const int64_t thread_cap = ctx->opt_sj_host_threads > 0 ? ctx->opt_sj_host_threads : std::min<int64_t>((int64_t)std::thread::hardware_concurrency(), 32);
-    const int n_threads = (int)std::max<int64_t>(1, std::min<int64_t>(thread_cap, (int64_t)n_sites / 2048));
-    if (n_threads <= 1) {
-      evaluate_sites(0, n_sites);
-    } else {
-      std::vector<std::thread> pool;
-      const int per = (n_sites + n_threads - 1) / n_threads;
-      for (int t = 0; t < n_threads; ++t) pool.emplace_back(evaluate_sites, std::min(n_sites, t * per), std::min(n_sites, (t + 1) * per));
-      for (auto& th : pool) th.join();
-    }
-  }
-  int site_index = 0;
-  for (int oi = 0; oi < n_sites; ++oi) {
-    const SJSiteDev& site = sites[order[(size_t)oi]];
-    std::vector<joint::Record>& emitted = emitted_by_site[(size_t)oi];
-    if (emitted.empty()) continue;
-    for (auto& rec : emitted) {
-      const SJAlleleDev& al = site.alleles[rec.raw->allele];
-      rec.allele.site_index = site_index;
-      add_string(1, site.locus + 1, site.ref_index, al.span, rec.allele.ref_off, rec.allele.ref_len);
-      if (al.key == 0) add_string(2, 0, 0, 1, rec.allele.alt_off, rec.allele.alt_len);
-      else add_string(0, al.rep_read, al.rep_start_rp, al.alt_len, rec.allele.alt_off, rec.allele.alt_len);
-      rec.allele.first_sample_evidence = (int64_t)samples.size();
-      for (int s = 0; s < S + 2; ++s) {
-        guac_sj_sample_evidence& e = rec.samples[s];
-        const SJSlotDev& r = rec.raw->slots[s];
-        for (int k = 0; k < r.n_depths; ++k)
-          add_string(0, r.depths[k].rep_read, r.depths[k].rep_start_rp, r.depths[k].len, e.depths[k].seq_off, e.depths[k].seq_len);
-        samples.push_back(e);
-      }
-      alleles.push_back(rec.allele);
-    }
-    ++site_index;
-  }
-  trace.mark("host evaluate");
-  *arena_len = arena_off;
-  if (!strings.empty()) {
-    DevBuf d_strings;
-    GUAC_TRY(upload(ctx, d_strings, strings.data(), strings.size()));
-    GUAC_TRY(ensure(ctx, ctx->b_arena, arena_off + 16));
-    sj_strings_kernel<<<blocks_for((int64_t)strings.size(), 128), 128, 0, ctx->stream>>>(ctx->R, ctx->d_refs.as<RefView>(),
-                                                                                         d_strings.as<SJStringJob>(), (int)strings.size(),
-                                                                                         ctx->b_arena.as<char>());
-    ctx->launches += 1;
-    CUDA_TRY(ctx, cudaGetLastError());
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_strings.p);
-  }
-  GUAC_TRY(host_out(ctx, out_arena, ctx->b_arena.p, (size_t)arena_off));
-  void* ha = nullptr;
-  void* hs = nullptr;
-  GUAC_TRY(pinned_alloc(ctx, &ha, std::max<size_t>(alleles.size() * sizeof(guac_sj_allele_evidence), 16)));
-  GUAC_TRY(pinned_alloc(ctx, &hs, std::max<size_t>(samples.size() * sizeof(guac_sj_sample_evidence), 16)));
-  if (!alleles.empty()) std::memcpy(ha, alleles.data(), alleles.size() * sizeof(guac_sj_allele_evidence));
-  if (!samples.empty()) std::memcpy(hs, samples.data(), samples.size() * sizeof(guac_sj_sample_evidence));
-  *out_alleles = (guac_sj_allele_evidence*)ha;
-  *out_samples = (guac_sj_sample_evidence*)hs;
-  *n_alleles = (int64_t)alleles.size();
-  *n_sample_evidences = (int64_t)samples.size();
+  *n_alleles = total_alleles;
+  *n_sample_evidences = total_alleles * (S + 2);
+  *arena_len = total_strings;
   if (out_n_visited) {
-    int64_t nv = 0;
-    GUAC_TRY(compact_visited(ctx, plan, 1, nv));
-    *out_n_visited = nv;
+    if (n_fb == 0) {
+      *out_n_visited = (int64_t)n_visited_tiles;  // counted by the locus pass itself
+    } else {
+      int64_t nv = 0;
+      GUAC_TRY(compact_visited(ctx, plan, 1, nv));
+      *out_n_visited = nv;
+    }
   }
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  trace.mark("records out");
   return GUAC_OK;
 }
 
@@ -1693,7 +1748,10 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
   } else if (n == "ss_force_fallback_mod") {
     ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
   } else if (n == "sj_host_threads") {
-    ctx->opt_sj_host_threads = value < 0 ? 0 : std::min<int64_t>(value, 256);
+    ctx->opt_sj_host_threads = value < 0 ? 0 : std::min<int64_t>(value, 256);  // accepted for old callers; nothing runs on host threads any more
+  } else if (n == "sj_impl") {
+    if (value < 0 || value > 2) return fail(ctx, GUAC_E_INVALID_INPUT, "sj_impl must be 0, 1 or 2");
+    ctx->opt_sj_impl = value;
   } else if (n == "compact_narrow") {
     ctx->opt_compact_narrow = value != 0;
   } else if (n == "ss_rank_max") {
@@ -1706,6 +1764,18 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
 
 int64_t guac_last_fallback_tiles(guac_ctx* ctx) { return ctx ? ctx->last_fallback_tiles : 0; }
 int64_t guac_last_heavy_loci(guac_ctx* ctx) { return ctx ? ctx->last_heavy_loci : 0; }
+
+int64_t guac_last_stat(guac_ctx* ctx, const char* name) {
+  if (!ctx || !name) return -1;
+  const std::string n(name);
+  if (n == "fallback_tiles") return ctx->last_fallback_tiles;
+  if (n == "heavy_loci") return ctx->last_heavy_loci;
+  if (n == "sj_simple") return ctx->stat_sj_simple;
+  if (n == "sj_bail") return ctx->stat_sj_bail;
+  if (n == "sj_sites") return ctx->stat_sj_sites;
+  if (n == "sj_emitted_sites") return ctx->stat_sj_emitted_sites;
+  return -1;
+}
 
 int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci) {
   if (!ctx || !ms) return GUAC_E_INVALID_INPUT;
@@ -2023,6 +2093,7 @@ cudaError_t configure_device_functions() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(asm_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_align_smem(ASM_ALIGN_MAX_S));
   return e;

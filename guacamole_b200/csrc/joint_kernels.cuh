@@ -10,8 +10,9 @@
 //                       the log10 mixture likelihoods the evidence classes ask for
 //                       (evidence/{NormalDNA,TumorDNA,TumorRNA}SingleSampleSingleAlleleEvidence.scala).
 //   sj_strings_kernel   writes the allele strings of the emitted records into the result arena.
-// Posteriors, call logic, annotations and the emit policy are scalar work on a handful of doubles per
-// site and run on the host side of the library (joint_host.hpp).
+// These are the generic kernels: any allele shape, any number of samples.  Sites whose alleles are single-base
+// substitutions take the fast site kernel of joint_stream_kernels.cuh instead, and posteriors, call logic, annotations
+// and the emit policy follow on the device for both (sj_posterior_kernel, sj_final_kernel there).
 // Reference file names below are relative to src/main/scala/org/hammerlab/guacamole/.
 #pragma once
 #include "kernels.cuh"
@@ -44,6 +45,7 @@ struct SJSiteDev {
   int64_t slot, locus;  // pileup locus x; alleles start at x + 1
   int64_t read_lo, read_hi;
   int32_t contig_id, ref_index, n_alleles, forced;
+  int32_t first_job, _pad;  // the site's alleles own the raw evidence records [first_job, first_job + n_alleles)
   SJAlleleDev alleles[SJ_MAX_ALLELES];
 };
 
@@ -139,7 +141,7 @@ sj_discover_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __
                    const int* __restrict__ tile_list /* nullptr: identity */, int n_tiles,
                    int tile_per_warp /* 0: the CTA's warps share one tile; 1: one (single-locus) tile per warp */, SJParamsDev P,
                    const guac_range* __restrict__ force, int n_force, uint8_t* __restrict__ visited /* nullptr: already written */,
-                   SJSiteDev* __restrict__ sites, int* __restrict__ n_sites, int max_sites, DeviceError* err) {
+                   SJSiteDev* __restrict__ sites, int* __restrict__ n_sites, int max_sites, int* __restrict__ n_jobs, DeviceError* err) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tsel = tile_per_warp ? (int)blockIdx.x * WARPS_PER_CTA + warp : (int)blockIdx.x;
   if (tsel >= n_tiles) return;  // no block-wide barrier below
@@ -326,8 +328,11 @@ sj_discover_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __
     }
     if (n_res > 0 && lane == 0) {
       const int idx = atomicAdd(n_sites, 1);
+      const int job0 = atomicAdd(n_jobs, n_res);
       if (idx < max_sites) {
         SJSiteDev s;
+        s.first_job = job0;
+        s._pad = 0;
         s.slot = slot;
         s.locus = x;
         s.read_lo = tile.read_lo;
@@ -402,16 +407,21 @@ __device__ inline int sj_table_find(SJTableEntry* tab, uint64_t key, int sample,
   return -1;
 }
 
+// Grid: one CTA per (site, allele index) of the sites [site0, site0 + n) — blockIdx.x = site * max_alleles + allele;
+// CTAs of allele indices the site does not have leave at once.  Record (site.first_job + allele) of `out` is written.
 __global__ void __launch_bounds__(128)
-sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P, const SJSiteDev* __restrict__ sites,
-                   const int2* __restrict__ jobs /* (site, allele) */, unsigned char* __restrict__ out, size_t out_stride, DeviceError* err) {
+sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P, const SJSiteDev* __restrict__ sites, int site0,
+                   unsigned char* __restrict__ out, size_t out_stride, DeviceError* err) {
   __shared__ SJTableEntry tab[SJ_TABLE];
   __shared__ int total_depth[SJ_MAX_SLOTS];
   __shared__ double vaf[SJ_MAX_SLOTS];
   __shared__ double ll[SJ_MAX_SLOTS][3];
   __shared__ int overflow;
-  const int2 job = jobs[blockIdx.x];
+  __shared__ double s_term[3][128];
+  __shared__ uint8_t s_smp[128];
+  const int2 job = make_int2(site0 + (int)(blockIdx.x / (unsigned)P.max_alleles), (int)(blockIdx.x % (unsigned)P.max_alleles));
   const SJSiteDev& site = sites[job.x];
+  if (job.y >= site.n_alleles) return;
   const SJAlleleDev al = site.alleles[job.y];
   const RefView ref = refs[site.ref_index];
   const int64_t x = site.locus;
@@ -479,59 +489,76 @@ sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P,
     vaf[TP] = fmax(P.vaf_floor, (double)pool_alt / (double)pool_total);
   }
   __syncthreads();
-  // pass B: log10 mixture likelihoods (PileupStats.logLikelihoodPileup :77-91)
-  for (int64_t r = site.read_lo + threadIdx.x; r < site.read_hi; r += blockDim.x) {
-    if (!(__ldg(R.start + r) <= x && x < __ldg(R.end + r))) continue;
-    const int smp = __ldg(R.sample_id + r);
-    if (smp >= S) continue;
-    Elem e0;
-    if (element_at(R, r, x, ref, e0) != DERR_NONE || e0.kind == GUAC_ALN_CLIPPED) continue;
-    SubSeq s;
-    if (fixed_length_subsequence(R, r, x, ref, e0, span, s) <= 0) continue;
-    const uint64_t s0 = __ldg(R.seq_off + r);
-    const int n = s.end_rp - s.start_rp;
-    const uint64_t key = seq_key(n, [&](int k) { return read_base(R, s0 + s.start_rp + k); });
-    const int slot = sj_table_find(tab, key, smp, false, nullptr);
-    if (slot >= 0 && tab[slot].first == (long long)r) {  // representative read of this (sample, sequence)
-      tab[slot].rep_start_rp = s.start_rp;
-      tab[slot].len = n;
-    }
-    const int mapq = __ldg(R.mapq + r);
-    if (mapq == 0) continue;  // contributes exactly 0.0
-    long qsum = 0;
-    int qn = 0;
-    if (n == 0) {
-      qsum = __ldg(R.qual + s0 + s.start_rp);
-      qn = 1;
-    } else {
-      for (int k = 0; k < n; ++k) qsum += __ldg(R.qual + s0 + s.start_rp + k);
-      qn = n;
-    }
-    const int q = (int)floor((double)qsum / qn + 0.5);  // meanBaseQuality.round.toInt
-    const double p = c_success_probability[q] * c_success_probability[mapq];
-    const bool is_ref = key == ref_key, is_alt = key == alt_key;
-    auto term = [&](double f) { return log10(f * p + (1 - f) * (1 - p)); };
-    const int kind = P.kind[smp];
-    if (kind == GUAC_SJ_NORMAL_DNA) {
-      const double t0 = term(is_ref ? 1.0 : 0.0), t1 = term((is_ref || is_alt) ? 0.5 : 0.0), t2 = term(is_alt ? 1.0 : 0.0);
-      atomicAdd(&ll[smp][0], t0);
-      atomicAdd(&ll[smp][1], t1);
-      atomicAdd(&ll[smp][2], t2);
-      atomicAdd(&ll[NP][0], t0);
-      atomicAdd(&ll[NP][1], t1);
-      atomicAdd(&ll[NP][2], t2);
-    } else {
-      const double t0 = term(is_ref ? 1.0 : 0.0);
-      const double v = vaf[smp];
-      atomicAdd(&ll[smp][0], t0);
-      atomicAdd(&ll[smp][1], term(is_alt ? v : (is_ref ? 1.0 - v : 0.0)));
-      if (kind == GUAC_SJ_TUMOR_DNA) {
-        const double vp = vaf[TP];
-        atomicAdd(&ll[TP][0], t0);
-        atomicAdd(&ll[TP][1], term(is_alt ? vp : (is_ref ? 1.0 - vp : 0.0)));
+  // pass B: log10 mixture likelihoods (PileupStats.logLikelihoodPileup :77-91).  Each chunk of 128 reads leaves its terms
+  // in shared memory; one thread per (evidence slot, mixture) then adds them in read order, so the sums do not depend on
+  // how the threads were scheduled.
+  double my_sum = 0.0;
+  const int my_slot = threadIdx.x / 3, my_k = threadIdx.x % 3;
+  for (int64_t base = site.read_lo; base < site.read_hi; base += blockDim.x) {
+    const int64_t r = base + threadIdx.x;
+    s_smp[threadIdx.x] = 255;
+    do {
+      if (r >= site.read_hi) break;
+      if (!(__ldg(R.start + r) <= x && x < __ldg(R.end + r))) break;
+      const int smp = __ldg(R.sample_id + r);
+      if (smp >= S) break;
+      Elem e0;
+      if (element_at(R, r, x, ref, e0) != DERR_NONE || e0.kind == GUAC_ALN_CLIPPED) break;
+      SubSeq s;
+      if (fixed_length_subsequence(R, r, x, ref, e0, span, s) <= 0) break;
+      const uint64_t s0 = __ldg(R.seq_off + r);
+      const int n = s.end_rp - s.start_rp;
+      const uint64_t key = seq_key(n, [&](int k) { return read_base(R, s0 + s.start_rp + k); });
+      const int slot = sj_table_find(tab, key, smp, false, nullptr);
+      if (slot >= 0 && tab[slot].first == (long long)r) {  // representative read of this (sample, sequence)
+        tab[slot].rep_start_rp = s.start_rp;
+        tab[slot].len = n;
+      }
+      const int mapq = __ldg(R.mapq + r);
+      if (mapq == 0) break;  // contributes exactly 0.0
+      long qsum = 0;
+      int qn = 0;
+      if (n == 0) {
+        qsum = __ldg(R.qual + s0 + s.start_rp);
+        qn = 1;
+      } else {
+        for (int k = 0; k < n; ++k) qsum += __ldg(R.qual + s0 + s.start_rp + k);
+        qn = n;
+      }
+      const int q = (int)floor((double)qsum / qn + 0.5);  // meanBaseQuality.round.toInt
+      const double p = c_success_probability[q] * c_success_probability[mapq];
+      const bool is_ref = key == ref_key, is_alt = key == alt_key;
+      auto term = [&](double f) { return log10(f * p + (1 - f) * (1 - p)); };
+      const int kind = P.kind[smp];
+      s_smp[threadIdx.x] = (uint8_t)smp;
+      s_term[0][threadIdx.x] = term(is_ref ? 1.0 : 0.0);
+      if (kind == GUAC_SJ_NORMAL_DNA) {
+        s_term[1][threadIdx.x] = term((is_ref || is_alt) ? 0.5 : 0.0);
+        s_term[2][threadIdx.x] = term(is_alt ? 1.0 : 0.0);
+      } else {
+        const double v = vaf[smp], vp = vaf[TP];
+        s_term[1][threadIdx.x] = term(is_alt ? v : (is_ref ? 1.0 - v : 0.0));
+        s_term[2][threadIdx.x] = kind == GUAC_SJ_TUMOR_DNA ? term(is_alt ? vp : (is_ref ? 1.0 - vp : 0.0)) : 0.0;  // pooled tumor mixture
+      }
+    } while (false);
+    __syncthreads();
+    if (my_slot < S + 2) {
+      for (int i = 0; i < (int)blockDim.x; ++i) {
+        const int smp = s_smp[i];
+        if (smp == 255) continue;
+        const int kind = P.kind[smp];
+        if (my_slot < S) {
+          if (smp == my_slot && (my_k < 2 || kind == GUAC_SJ_NORMAL_DNA)) my_sum += s_term[my_k][i];
+        } else if (my_slot == NP) {
+          if (kind == GUAC_SJ_NORMAL_DNA) my_sum += s_term[my_k][i];
+        } else if (kind == GUAC_SJ_TUMOR_DNA && my_k < 2) {
+          my_sum += s_term[my_k == 0 ? 0 : 2][i];
+        }
       }
     }
+    __syncthreads();
   }
+  if (my_slot < S + 2) ll[my_slot][my_k] = my_sum;
   __syncthreads();
   // The table is nearly empty (a handful of distinct sequences per site): its used entries are listed first, in table
   // order, so that the assembly below walks that handful instead of all SJ_TABLE entries once per slot.
@@ -559,7 +586,7 @@ sj_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SJParamsDev P,
   if (threadIdx.x >= S + 2) return;
   // assemble: per-sample slots, then the pools (MultiplePileupStats.scala:12-18), one thread per slot
   // records are packed with only the S + 2 slots in use (out_stride bytes each)
-  SJEvidenceDev& E = *reinterpret_cast<SJEvidenceDev*>(out + (size_t)blockIdx.x * out_stride);
+  SJEvidenceDev& E = *reinterpret_cast<SJEvidenceDev*>(out + (size_t)(site.first_job + job.y) * out_stride);
   if (threadIdx.x == 0) {
     E.site = job.x;
     E.allele = job.y;

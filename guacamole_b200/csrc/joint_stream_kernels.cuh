@@ -1,0 +1,790 @@
+// joint_stream_kernels.cuh — somatic-joint on the streaming architecture, back half on the device.
+//
+//   sj_snv_site_kernel   one warp per candidate site the locus pass (ss_tile_kernel MODE 2) classified as "simple"
+//                        (every alternate allele that can start at x + 1 is a single-base substitution).  One pass over
+//                        the reads of the site does ReadSubsequence.ofNextAltAllele, AlleleAtLocus.variantAlleles,
+//                        PileupStats of every sample and of both pools and the mixture likelihoods
+//                        (jointcaller/pileup_summarization/*.scala, jointcaller/AlleleAtLocus.scala:85-149,
+//                        evidence/{NormalDNA,TumorDNA,TumorRNA}SingleSampleSingleAlleleEvidence.scala): single-operator
+//                        reads are classified from three packed bases, the others through element_at().  Sums are
+//                        accumulated per lane and combined by fixed butterflies: the same input gives the same bits.
+//                        A site that turns out not to be simple (multi-base run, indel, N) is handed to the generic
+//                        kernels of joint_kernels.cuh.
+//   sj_posterior_kernel  one thread per site: posteriors, germline / somatic call logic, StrandBias (Fisher),
+//                        InsufficientNormal and the emit policy (evidence/MultiSampleSingleAlleleEvidence.scala:66-341,
+//                        annotation/StrandBias.scala:47-58, annotation/InsufficientNormal.scala:21-53,
+//                        filters/FishersExactTest.scala:12-19, evidence/MultiSampleMultiAlleleEvidence.scala:131-177);
+//                        only emitted sites are listed.
+//   sj_final_kernel      one thread per emitted site, in (range order, locus) order: the finished guac_sj_* records and
+//                        their strings, so that only emitted records cross PCIe.
+// Reference file names are relative to src/main/scala/org/hammerlab/guacamole/.
+#pragma once
+#include "joint_kernels.cuh"
+#include "tile_kernels.cuh"
+
+namespace guac {
+
+// ---- posteriors / annotations / emit policy ---------------------------------------------------------
+
+// ln C(n, k) as commons-math3 3.0 ArithmeticUtils.binomialCoefficientLog returns it to 1e-15 relative: its special cases
+// literally, everything else from a table of ln n! (correctly rounded sums made on the host in extended precision).
+__device__ __forceinline__ double sj_binomial_log(const double* __restrict__ lf, int lf_n, int n, int k) {
+  if (n == k || k == 0) return 0.0;
+  if (k == 1 || k == n - 1) return log((double)n);
+  if (n < lf_n) return __ldg(lf + n) - __ldg(lf + k) - __ldg(lf + (n - k));
+  return lgamma((double)n + 1.0) - lgamma((double)k + 1.0) - lgamma((double)(n - k) + 1.0);
+}
+
+struct SJAlleleCall {
+  int is_germline, is_somatic, germline_genotype, rna_expressed;
+  int has_in, in_ref, in_total, in_filtered;
+  unsigned failing;
+  __device__ bool is_call() const { return is_germline || is_somatic; }
+};
+
+// One MultiSampleSingleAlleleEvidence from the raw per-slot numbers.  WRITE: also fills the S + 2 sample records.
+template <bool WRITE>
+__device__ inline void sj_evaluate_allele(const guac_sj_params& P, const double* __restrict__ lf, int lf_n,
+                                          const SJSlotDev* __restrict__ slots, SJAlleleCall& call,
+                                          guac_sj_sample_evidence* __restrict__ out) {
+  const int S = P.n_samples, NP = S, TP = S + 1;
+  const double LN10 = 2.302585092994046;  // math.log(10)
+  unsigned sb_filtered = 0, triggered = 0;
+  auto kind_of = [&](int i) { return i == NP ? (int)GUAC_SJ_NORMAL_DNA : i == TP ? (int)GUAC_SJ_TUMOR_DNA : P.sample_kind[i]; };
+  for (int i = 0; i < S + 2; ++i) {
+    const SJSlotDev& r = slots[i];
+    // StrandBias (annotation/StrandBias.scala:47-58) over FishersExactTest.asLog10
+    const int vf = r.variant_forward, vr = r.variant_count - r.variant_forward;
+    const int tf = r.forward_subsequences, tr = r.n_subsequences - r.forward_subsequences;
+    const double sb = 10.0 * ((sj_binomial_log(lf, lf_n, tf, vf) + sj_binomial_log(lf, lf_n, tr, vr) -
+                               sj_binomial_log(lf, lf_n, tf + tr, vf + vr)) / LN10);
+    if (sb > P.filter_strand_bias_phred) sb_filtered |= 1u << i;
+    if (WRITE) {
+      guac_sj_sample_evidence& e = out[i];
+      const int kind = kind_of(i);
+      e.kind = kind;
+      e.total_depth = r.total_depth;
+      e.n_depths = r.n_depths;
+      e.n_likelihoods = kind == GUAC_SJ_NORMAL_DNA ? 3 : 2;
+      for (int k = 0; k < GUAC_SJ_MAX_DEPTH_ENTRIES; ++k) {
+        e.depths[k].seq_off = e.depths[k].seq_len = 0;
+        e.depths[k].count = k < r.n_depths ? r.depths[k].count : 0;
+        e.depths[k]._pad = 0;
+      }
+      for (int k = 0; k < 3; ++k) {
+        e.log_likelihoods[k] = k < e.n_likelihoods ? r.ll[k] : 0.0;
+        e.posteriors[k] = __longlong_as_double(0x7ff8000000000000ll);  // NaN until a posterior is defined
+      }
+      e.alt_vaf = kind == GUAC_SJ_NORMAL_DNA ? 0.0 : r.alt_vaf;
+      e.sb_variant_forward = vf;
+      e.sb_variant_reverse = vr;
+      e.sb_total_forward = tf;
+      e.sb_total_reverse = tr;
+      e.sb_phred = sb;
+      e.sb_filtered = (sb_filtered >> i) & 1u;
+      e.triggered = 0;
+    }
+  }
+  // germline posteriors: likelihood - prior (MultiSampleSingleAlleleEvidence.scala:66-123)
+  const double gprior[3] = {0.0, P.germline_neg_log10_het_prior, P.germline_neg_log10_hom_alt_prior};
+  if (WRITE)
+    for (int i = 0; i <= NP; ++i)
+      if (kind_of(i) == GUAC_SJ_NORMAL_DNA)
+        for (int g = 0; g < 3; ++g) out[i].posteriors[g] = slots[i].ll[g] - gprior[g];
+  int germline = 0;  // maxBy keeps the first of equal maxima
+  {
+    double best = slots[NP].ll[0] - gprior[0];
+    for (int g = 1; g < 3; ++g) {
+      const double v = slots[NP].ll[g] - gprior[g];
+      if (v > best) {
+        best = v;
+        germline = g;
+      }
+    }
+  }
+  call.germline_genotype = germline;
+  call.is_germline = germline != 0;
+  // A tumor mixture is {ref: 1} or {alt: vaf, ref: 1 - vaf}; its prior depends on which alleles have a positive fraction
+  // (:172-183), whether it triggers on its key set against the germline alleles (:220-224).
+  auto somatic_prior = [](int mixture, double vaf, double variant_prior) {
+    if (mixture == 0) return 0.0;
+    const bool has_alt = vaf > 0, has_ref = 1.0 - vaf > 0;
+    if (has_ref && !has_alt) return 0.0;
+    if (has_ref && has_alt) return variant_prior;
+    return 1.7976931348623157e308;  // Double.MaxValue
+  };
+  auto best_mixture = [&](int i, double variant_prior) {
+    const SJSlotDev& r = slots[i];
+    const double p0 = r.ll[0] - somatic_prior(0, r.alt_vaf, variant_prior), p1 = r.ll[1] - somatic_prior(1, r.alt_vaf, variant_prior);
+    if (WRITE) {
+      out[i].posteriors[0] = p0;
+      out[i].posteriors[1] = p1;
+    }
+    return p1 > p0 ? 1 : 0;
+  };
+  auto triggers = [&](int best) { return best == 0 ? germline != 0 : germline != 1; };
+  bool rna_expressed = false;
+  for (int i = 0; i < S; ++i) {
+    if (kind_of(i) != GUAC_SJ_TUMOR_RNA) continue;
+    if (triggers(best_mixture(i, P.somatic_neg_log10_variant_prior_rna))) {
+      triggered |= 1u << i;
+      rna_expressed = true;
+    }
+  }
+  call.rna_expressed = rna_expressed;
+  const double dna_prior = rna_expressed ? P.somatic_neg_log10_variant_prior_with_rna_evidence : P.somatic_neg_log10_variant_prior;
+  bool any_triggered = false;
+  for (int i = 0; i <= TP; ++i) {
+    if (i == NP || kind_of(i) != GUAC_SJ_TUMOR_DNA) continue;
+    if (triggers(best_mixture(i, dna_prior))) {
+      triggered |= 1u << i;
+      any_triggered = true;
+    }
+  }
+  call.is_somatic = !call.is_germline && any_triggered;
+  // InsufficientNormal (annotation/InsufficientNormal.scala:21-53): only for non-germline alleles
+  call.has_in = call.in_ref = call.in_total = call.in_filtered = 0;
+  if (!call.is_germline) {
+    call.has_in = 1;
+    call.in_ref = slots[NP].ref_count;
+    call.in_total = slots[NP].total_depth;
+    call.in_filtered = call.in_total < P.filter_somatic_normal_depth ||
+                       (call.in_total - call.in_ref) * 100.0 / call.in_total > P.filter_somatic_normal_nonreference_percent;
+  }
+  // failingFilterNames (:250-275)
+  bool have_trigger = false, all_fail = true;
+  if (call.is_germline) {
+    have_trigger = true;
+    all_fail = (sb_filtered >> NP) & 1u;
+  } else if (call.is_somatic) {
+    for (int i = 0; i <= TP; ++i)
+      if (i != NP && kind_of(i) == GUAC_SJ_TUMOR_DNA && ((triggered >> i) & 1u)) {
+        have_trigger = true;
+        all_fail = all_fail && ((sb_filtered >> i) & 1u);
+      }
+  }
+  call.failing = 0;
+  if (have_trigger && all_fail) call.failing |= 1u;
+  if (call.has_in && call.in_filtered) call.failing |= 2u;
+  if (WRITE)
+    for (int i = 0; i < S + 2; ++i) out[i].triggered = (triggered >> i) & 1u;
+}
+
+// MultiSampleMultiAlleleEvidence.make's emit policy (:131-177): bit a of the result = allele a is emitted
+__device__ inline unsigned sj_emit_mask(const guac_sj_params& P, bool forced, const SJAlleleCall* calls, int n_alleles) {
+  unsigned evidences = 0;
+  bool any_germline = false;
+  for (int a = 0; a < n_alleles; ++a)
+    if (calls[a].is_germline || calls[a].is_somatic) {
+      evidences |= 1u << a;
+      any_germline = any_germline || calls[a].is_germline;
+    }
+  const bool any_call = evidences != 0;
+  if (!any_call) evidences = 1u;  // allEvidences.take(1)
+  if (!forced) {
+    if (!any_call) return 0;
+    if (P.only_somatic && any_germline) return 0;
+  }
+  if (forced || P.include_filtered) return evidences;
+  unsigned passing = 0;
+  for (int a = 0; a < n_alleles; ++a)
+    if (((evidences >> a) & 1u) && calls[a].failing == 0) passing |= 1u << a;
+  return passing;
+}
+
+constexpr int SJ_SITE_GENERIC = 1 << 30;  // SJEmitDev::site: the site is in the generic kernels' list, not the fast kernel's
+
+struct SJEmitDev {  // one emitted site
+  int64_t slot;
+  int32_t site;       // index into its site list (| SJ_SITE_GENERIC)
+  int32_t n_emit;     // alleles emitted
+  uint32_t mask;      // which ones
+  uint32_t str_len;   // bytes of their strings
+};
+
+__device__ __forceinline__ const SJEvidenceDev* sj_raw_record(const unsigned char* raw, size_t stride, int job) {
+  return reinterpret_cast<const SJEvidenceDev*>(raw + (size_t)job * stride);
+}
+
+__global__ void __launch_bounds__(128)
+sj_posterior_kernel(const __grid_constant__ guac_sj_params P, const double* __restrict__ lf, int lf_n, const SJSiteDev* __restrict__ sites,
+                    int n_sites, int site_tag, const unsigned char* __restrict__ raw, size_t raw_stride, SJEmitDev* __restrict__ emits,
+                    int* __restrict__ n_emits) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_sites) return;
+  const SJSiteDev& site = sites[i];
+  const int S = P.n_samples;
+  SJAlleleCall calls[SJ_MAX_ALLELES];
+  for (int a = 0; a < site.n_alleles; ++a)
+    sj_evaluate_allele<false>(P, lf, lf_n, sj_raw_record(raw, raw_stride, site.first_job + a)->slots, calls[a], nullptr);
+  const unsigned mask = sj_emit_mask(P, site.forced != 0, calls, site.n_alleles);
+  if (mask == 0) return;
+  uint32_t len = 0;
+  for (int a = 0; a < site.n_alleles; ++a) {
+    if (!((mask >> a) & 1u)) continue;
+    len += (uint32_t)site.alleles[a].span + (uint32_t)(site.alleles[a].key == 0 ? 1 : site.alleles[a].alt_len);
+    const SJSlotDev* slots = sj_raw_record(raw, raw_stride, site.first_job + a)->slots;
+    for (int s = 0; s < S + 2; ++s)
+      for (int k = 0; k < slots[s].n_depths; ++k) len += (uint32_t)slots[s].depths[k].len;
+  }
+  SJEmitDev e;
+  e.slot = site.slot;
+  e.site = i | site_tag;
+  e.n_emit = __popc(mask);
+  e.mask = mask;
+  e.str_len = len;
+  emits[atomicAdd(n_emits, 1)] = e;
+}
+
+// rank -> per-rank arrays for the two offset scans
+__global__ void sj_order_kernel(const SJEmitDev* __restrict__ emits, const int* __restrict__ rank, int n, int* __restrict__ order,
+                                int32_t* __restrict__ n_by_rank, int32_t* __restrict__ len_by_rank) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int r = rank[i];
+  order[r] = i;
+  n_by_rank[r] = emits[i].n_emit;
+  len_by_rank[r] = (int32_t)emits[i].str_len;
+}
+
+// A string of a record: bases of a read, or (rep_read < 0) the single character in rep_start_rp
+__device__ inline void sj_write_read_string(const ReadsView& R, int64_t rep_read, int32_t rep_start_rp, int len, char* dst) {
+  if (rep_read < 0) {
+    dst[0] = (char)rep_start_rp;
+    return;
+  }
+  const uint64_t s0 = __ldg(R.seq_off + rep_read);
+  for (int k = 0; k < len; ++k) dst[k] = (char)read_base(R, s0 + rep_start_rp + k);
+}
+
+__global__ void __launch_bounds__(128)
+sj_final_kernel(ReadsView R, const RefView* __restrict__ refs, const __grid_constant__ guac_sj_params P, const double* __restrict__ lf,
+                int lf_n, const SJSiteDev* __restrict__ sites_fast, const SJSiteDev* __restrict__ sites_gen,
+                const unsigned char* __restrict__ raw_fast, const unsigned char* __restrict__ raw_gen, size_t raw_stride,
+                const SJEmitDev* __restrict__ emits, const int* __restrict__ order, int n_emits,
+                const int64_t* __restrict__ allele_off, const int64_t* __restrict__ string_off,
+                guac_sj_allele_evidence* __restrict__ out_alleles, guac_sj_sample_evidence* __restrict__ out_samples,
+                char* __restrict__ arena) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_emits) return;
+  const SJEmitDev em = emits[order[j]];
+  const bool generic = (em.site & SJ_SITE_GENERIC) != 0;
+  const SJSiteDev& site = (generic ? sites_gen : sites_fast)[em.site & ~SJ_SITE_GENERIC];
+  const unsigned char* raw = generic ? raw_gen : raw_fast;
+  const RefView ref = refs[site.ref_index];
+  const int S = P.n_samples;
+  int64_t ai = allele_off[j];
+  uint32_t so = (uint32_t)string_off[j];
+  for (int a = 0; a < site.n_alleles; ++a) {
+    if (!((em.mask >> a) & 1u)) continue;
+    const SJAlleleDev& al = site.alleles[a];
+    const SJSlotDev* slots = sj_raw_record(raw, raw_stride, site.first_job + a)->slots;
+    guac_sj_sample_evidence* samples = out_samples + ai * (S + 2);
+    SJAlleleCall call;
+    sj_evaluate_allele<true>(P, lf, lf_n, slots, call, samples);
+    guac_sj_allele_evidence o;
+    o.contig_id = site.contig_id;
+    o.site_index = j;
+    o.start = site.locus + 1;
+    o.ref_off = so;
+    o.ref_len = (uint32_t)al.span;
+    for (int k = 0; k < al.span; ++k) arena[so + k] = (char)ref.at(site.locus + 1 + k);
+    so += (uint32_t)al.span;
+    o.alt_off = so;
+    if (al.key == 0) {  // the "ref > N" placeholder of a forced site (AlleleAtLocus.scala:136-141)
+      o.alt_len = 1;
+      arena[so] = 'N';
+    } else {
+      o.alt_len = (uint32_t)al.alt_len;
+      sj_write_read_string(R, al.rep_read, al.rep_start_rp, al.alt_len, arena + so);
+    }
+    so += o.alt_len;
+    o.is_germline_call = call.is_germline;
+    o.is_somatic_call = call.is_somatic;
+    o.germline_genotype = call.germline_genotype;
+    o.tumor_rna_expressed = call.rna_expressed;
+    o.has_insufficient_normal = call.has_in;
+    o.in_reference_reads = call.in_ref;
+    o.in_total_reads = call.in_total;
+    o.in_filtered = call.in_filtered;
+    o.failing_filters = call.failing;
+    o.forced = site.forced;
+    o.first_sample_evidence = ai * (S + 2);
+    out_alleles[ai] = o;
+    for (int s = 0; s < S + 2; ++s)
+      for (int k = 0; k < slots[s].n_depths; ++k) {
+        const SJDepthDev& d = slots[s].depths[k];
+        samples[s].depths[k].seq_off = so;
+        samples[s].depths[k].seq_len = (uint32_t)d.len;
+        sj_write_read_string(R, d.rep_read, d.rep_start_rp, d.len, arena + so);
+        so += (uint32_t)d.len;
+      }
+    ++ai;
+  }
+}
+
+// ---- the fast site kernel ---------------------------------------------------------------------------
+
+constexpr int SJF_SMAX = 4;         // samples the fast site kernel handles (more: every candidate takes the generic kernels)
+constexpr int SJF_MAX_READS = 256;  // reads in the span of a site
+constexpr int SJF_LIST = 64;        // subsequences of a site that differ from the reference base
+
+struct SJFListEntry {
+  double p, A, B;  // P(correct), log10 p, log10 (1 - p)
+  int32_t rel;     // read index relative to the site's first read
+  uint8_t s, c, flags, _pad;  // sample, base code, 1: positive strand | 2: mapq > 0 | 4: starts an alternate allele
+};
+
+struct SJFWarpSmem {
+  double p[SJF_MAX_READS];      // P(correct) of the reads whose subsequence is the reference base
+  uint8_t meta[SJF_MAX_READS];  // sample | 4: such a read, with mapq > 0
+  SJFListEntry list[SJF_LIST];
+};
+
+struct SJFArgs {
+  const uint4* hdr;
+  const RefView* refs;
+  const Tile* cands;        // simple candidates as single-locus tiles (the read span of the tile they came from)
+  const int* n_cands;
+  int max_cands;
+  const guac_range* force;
+  int n_force;
+  SJSiteDev* sites;
+  int* n_sites;
+  int max_sites;
+  unsigned char* raw;
+  size_t raw_stride;
+  int* n_jobs;
+  int max_jobs;
+  Tile* bail;               // candidates handed to the generic kernels
+  int* n_bail;
+  int max_bail;
+  DeviceError* err;
+};
+
+__device__ __forceinline__ double warp_sum_fixed(double v) {  // the same tree for every call: deterministic
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+template <class T>
+__device__ __forceinline__ T pick4(T a0, T a1, T a2, T a3, int i) { return i == 0 ? a0 : i == 1 ? a1 : i == 2 ? a2 : a3; }
+
+__global__ void __launch_bounds__(256)
+sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __grid_constant__ SJFArgs A) {
+  __shared__ SJFWarpSmem smem_all[8];
+  const unsigned FULL = 0xffffffffu;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  SJFWarpSmem& W = smem_all[warp];
+  const int S = P.n_samples, NP = S, TP = S + 1;
+  const int n_cands = min(*A.n_cands, A.max_cands);
+  // sample kinds and the discovery order as packed words: no dynamically indexed parameter arrays in the loop
+  unsigned kinds = 0, disc_order = 0;
+  for (int s = 0; s < S; ++s) kinds |= (unsigned)P.kind[s] << (2 * s);
+  for (int d = 0; d < P.n_discovery; ++d) disc_order |= (unsigned)P.discovery[d] << (4 * d);
+  const double LOG10_HALF = -0.3010299956639812;  // math.log10(0.5)
+
+  for (int ci = blockIdx.x * 8 + warp; ci < n_cands; ci += gridDim.x * 8) {
+    Tile tile = A.cands[ci];
+    const RefView ref = A.refs[tile.ref_index];
+    const int64_t x = tile.locus0, key = ((int64_t)tile.contig_id << 40) | x;
+    // reads that can overlap x: start <= x, running-max end > x
+    tile.read_hi = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.start + i) > x; });
+    tile.read_lo = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.runmax_key + i) > key; });
+    const int n_span = (int)min((int64_t)(tile.read_hi - tile.read_lo), (int64_t)(SJF_MAX_READS + 1));
+    const uint8_t rb0 = ref.at(x), rb1 = ref.at(x + 1), rb2 = ref.at(x + 2);
+    bool bail = n_span > SJF_MAX_READS || rb0 == 0 || rb2 == 0;
+    if (rb1 == 0) {  // reference.getReferenceBase(contig, locus + 1) (MultiSampleMultiAlleleEvidence.scala:93)
+      if (lane == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x + 1, -1);
+      continue;
+    }
+    const int cr = base_code(rb1);
+    if (cr == 4) continue;  // not a standard base: no evidence at this site
+    const bool forced = locus_forced(A.force, A.n_force, tile.contig_id, x + 1);
+
+    int depth[SJF_SMAX], rcnt[SJF_SMAX], rfwd[SJF_SMAX], rfirst[SJF_SMAX], rll[SJF_SMAX];
+    double rA[SJF_SMAX], rB[SJF_SMAX];
+#pragma unroll
+    for (int s = 0; s < SJF_SMAX; ++s) {
+      depth[s] = rcnt[s] = rfwd[s] = rll[s] = 0;
+      rfirst[s] = INT_MAX;
+      rA[s] = rB[s] = 0.0;
+    }
+    int n_list = 0;
+    const uint32_t x_lo = (uint32_t)x;
+    for (int base = 0; base < n_span && !bail; base += 32) {
+      const int idx = base + lane;
+      const int64_t r = tile.read_lo + idx;
+      bool in_depth = false, has_sub = false, disc = false, my_bail = false;
+      int smp = 0, c = 0, q = 0;
+      uint8_t rf = 0;
+      if (idx < n_span) {
+        const uint4 h = __ldg(A.hdr + r);
+        smp = (int)((h.y >> 16) & 0xFF);
+        rf = (uint8_t)(h.y >> 24);
+        const int st = (int)(h.x - x_lo);  // start - x
+        int span = (int)(h.y & 0xFFFF);
+        if (span == 0xFFFF) span = (int)min((long long)(__ldg(R.end + r) - __ldg(R.start + r)), (1ll << 30));
+        const bool overlap = st <= 0 && st + span > 0 && smp < S;
+        if (overlap && (rf & RF_FAST)) {
+          // one aligned operator over standard bases: elements are Match / Mismatch, read position = locus - start
+          const uint64_t s0 = (uint64_t)h.z | ((uint64_t)h.w << 32);
+          const int p0 = -st;
+          in_depth = true;
+          auto base_at = [&](int rp) {
+            const uint64_t gi = s0 + (uint64_t)rp;
+            return (int)((__ldg(R.bases2 + (gi >> 2)) >> ((gi & 3) * 2)) & 3);
+          };
+          const bool e0_variant = "ACGT"[base_at(p0)] != (char)rb0;
+          if (!e0_variant && p0 + 1 < span - 1) {  // ReadSubsequence.scala:71,114: the read goes on past x + 1
+            c = base_at(p0 + 1);
+            q = (int)__ldg(R.qual + s0 + p0 + 1);
+            has_sub = true;
+            if (c != cr) {  // ofNextAltAllele: the run of variant elements from x + 1 must end at x + 2
+              disc = true;
+              if (p0 + 2 < span - 1 && "ACGT"[base_at(p0 + 2)] != (char)rb2) my_bail = true;
+            }
+          }
+        } else if (overlap) {  // the exact cursor
+          Elem e0;
+          const int ec = element_at(R, r, x, ref, e0);
+          if (ec != DERR_NONE) {
+            my_bail = true;  // the generic kernels report it
+          } else if (e0.kind != GUAC_ALN_CLIPPED) {  // Clipped elements are dropped first (:85-86)
+            in_depth = true;
+            SubSeq sa, sf;
+            const int fa = next_alt_allele(R, r, x, ref, e0, sa);
+            const int ff = fixed_length_subsequence(R, r, x, ref, e0, 1, sf);
+            if (fa < 0 || ff < 0) my_bail = true;
+            const uint64_t s0 = __ldg(R.seq_off + r);
+            if (ff > 0) {
+              const uint8_t b = sf.end_rp - sf.start_rp == 1 ? read_base(R, s0 + sf.start_rp) : (uint8_t)0;
+              c = base_code(b);
+              if (c == 4) {
+                my_bail = true;  // a subsequence that is not one standard base
+              } else {
+                has_sub = true;
+                q = (int)__ldg(R.qual + s0 + sf.start_rp);
+              }
+            }
+            if (fa > 0) {
+              disc = true;
+              // the alternate allele must be this very base over one locus
+              if (!(sa.end_locus - sa.start_locus == 1 && sa.end_rp - sa.start_rp == 1 && has_sub && sa.start_rp == sf.start_rp && c != cr))
+                my_bail = true;
+            }
+          }
+        }
+      }
+      if (__any_sync(FULL, my_bail)) {
+        bail = true;
+        break;
+      }
+      uint8_t meta = (uint8_t)(smp & 3);
+      double pq = 0.0, la = 0.0, lb = 0.0;
+      int mapq = 0;
+      bool fwd = false;
+      if (in_depth) {
+#pragma unroll
+        for (int s = 0; s < SJF_SMAX; ++s) depth[s] += smp == s;
+      }
+      if (has_sub) {
+        mapq = (int)__ldg(R.mapq + r);
+        fwd = (__ldg(R.flags + r) & GUAC_READ_POSITIVE_STRAND) != 0;
+        if (mapq != 0) {  // mapq 0 contributes exactly 0.0 (PileupStats.scala:79-80)
+          pq = c_success_probability[q] * c_success_probability[mapq];
+          la = log10(pq);
+          lb = log10(1.0 - pq);
+        }
+      }
+      const bool is_ref = has_sub && c == cr;
+      if (is_ref) {
+        if (mapq != 0) meta |= 4;
+        W.p[idx] = pq;
+#pragma unroll
+        for (int s = 0; s < SJF_SMAX; ++s)
+          if (smp == s) {
+            rcnt[s] += 1;
+            rfwd[s] += fwd;
+            rfirst[s] = min(rfirst[s], idx);
+            if (mapq != 0) {
+              rll[s] += 1;
+              rA[s] += la;
+              rB[s] += lb;
+            }
+          }
+      }
+      if (idx < n_span) W.meta[idx] = meta;
+      // the other subsequences go to the list in read order (ballot compaction: the same order every run)
+      const unsigned om = __ballot_sync(FULL, has_sub && !is_ref);
+      if (om) {
+        const int pos = n_list + __popc(om & ((1u << lane) - 1u));
+        if (has_sub && !is_ref && pos < SJF_LIST) {
+          SJFListEntry e;
+          e.p = pq;
+          e.A = la;
+          e.B = lb;
+          e.rel = idx;
+          e.s = (uint8_t)smp;
+          e.c = (uint8_t)c;
+          e.flags = (uint8_t)((fwd ? 1 : 0) | (mapq != 0 ? 2 : 0) | (disc ? 4 : 0));
+          e._pad = 0;
+          W.list[pos] = e;
+        }
+        n_list += __popc(om);
+        if (n_list > SJF_LIST) bail = true;
+      }
+    }
+    if (bail) {  // not a simple site after all: the generic kernels take it
+      if (lane == 0) {
+        const int b = atomicAdd(A.n_bail, 1);
+        if (b < A.max_bail) A.bail[b] = A.cands[ci];
+      }
+      continue;
+    }
+    __syncwarp();
+    // totals over the lanes (fixed trees)
+#pragma unroll
+    for (int s = 0; s < SJF_SMAX; ++s) {
+      depth[s] = __reduce_add_sync(FULL, depth[s]);
+      rcnt[s] = __reduce_add_sync(FULL, rcnt[s]);
+      rfwd[s] = __reduce_add_sync(FULL, rfwd[s]);
+      rll[s] = __reduce_add_sync(FULL, rll[s]);
+      rfirst[s] = __reduce_min_sync(FULL, rfirst[s]);
+      rA[s] = warp_sum_fixed(rA[s]);
+      rB[s] = warp_sum_fixed(rB[s]);
+    }
+    // cells: lane 4 s + c holds the numbers of sample s's subsequences equal to base c
+    int c_cnt = 0, c_fwd = 0, c_first = INT_MAX, c_ll = 0, c_disc = 0, c_dfirst = INT_MAX;
+    double c_A = 0.0, c_B = 0.0;
+    {
+      const int s = (lane >> 2) & 3, c = lane & 3;
+      if (lane < 16) {
+        if (c == cr) {
+          c_cnt = pick4(rcnt[0], rcnt[1], rcnt[2], rcnt[3], s);
+          c_fwd = pick4(rfwd[0], rfwd[1], rfwd[2], rfwd[3], s);
+          c_first = pick4(rfirst[0], rfirst[1], rfirst[2], rfirst[3], s);
+          c_ll = pick4(rll[0], rll[1], rll[2], rll[3], s);
+          c_A = pick4(rA[0], rA[1], rA[2], rA[3], s);
+          c_B = pick4(rB[0], rB[1], rB[2], rB[3], s);
+        } else {
+          for (int k = 0; k < n_list; ++k) {
+            const SJFListEntry& e = W.list[k];
+            if (e.s != s || e.c != c) continue;
+            c_cnt += 1;
+            c_fwd += e.flags & 1;
+            c_first = min(c_first, e.rel);
+            if (e.flags & 2) {
+              c_ll += 1;
+              c_A += e.A;
+              c_B += e.B;
+            }
+            if (e.flags & 4) {
+              c_disc += 1;
+              c_dfirst = min(c_dfirst, e.rel);
+            }
+          }
+        }
+      }
+    }
+    // AlleleAtLocus.variantAlleles (jointcaller/AlleleAtLocus.scala:85-149): per discovery sample, its alternate bases
+    // by (count desc, first read asc), kept when count >= max(minReads, depth * percent / 100); union, distinct, capped
+    int n_res = 0, res_c[4] = {-1, -1, -1, -1};
+    int tot_cnt[4] = {0, 0, 0, 0}, tot_first[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX};
+    for (int di = 0; di < P.n_discovery; ++di) {
+      const int smp = (int)((disc_order >> (4 * di)) & 15u);
+      const int dep = pick4(depth[0], depth[1], depth[2], depth[3], smp);
+      const double required = fmax((double)P.min_reads, dep * P.min_percent / 100.0);
+      int cnt[4], first[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        cnt[c] = __shfl_sync(FULL, c_disc, 4 * smp + c);
+        first[c] = __shfl_sync(FULL, c_dfirst, 4 * smp + c);
+        tot_cnt[c] += cnt[c];
+        tot_first[c] = min(tot_first[c], first[c]);
+      }
+      for (int round = 0; round < 3; ++round) {
+        int best = -1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (cnt[c] > 0 && (best < 0 || cnt[c] > cnt[best] || (cnt[c] == cnt[best] && first[c] < first[best]))) best = c;
+        if (best < 0) break;
+        if ((double)cnt[best] >= required) {
+          bool dup = false;
+          for (int k = 0; k < n_res; ++k) dup = dup || res_c[k] == best;
+          if (!dup && n_res < P.max_alleles) res_c[n_res++] = best;
+        }
+        cnt[best] = 0;
+      }
+    }
+    if (n_res == 0 && forced) {  // atLeastOneAllele (:126-141): the best supported allele overall, or ref > N
+      int best = -1;
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (tot_cnt[c] > 0 && (best < 0 || tot_cnt[c] > tot_cnt[best] || (tot_cnt[c] == tot_cnt[best] && tot_first[c] < tot_first[best])))
+          best = c;
+      res_c[0] = best;  // -1: the placeholder
+      n_res = 1;
+    }
+    if (n_res == 0) continue;
+    int site_idx = 0, job0 = 0;
+    if (lane == 0) {
+      site_idx = atomicAdd(A.n_sites, 1);
+      job0 = atomicAdd(A.n_jobs, n_res);
+    }
+    site_idx = __shfl_sync(FULL, site_idx, 0);
+    job0 = __shfl_sync(FULL, job0, 0);
+    if (site_idx >= A.max_sites || job0 + n_res > A.max_jobs) continue;  // the host sees the counters and reruns with room
+    if (lane == 0) {
+      SJSiteDev& st = A.sites[site_idx];
+      st.slot = tile.slot0;
+      st.locus = x;
+      st.read_lo = tile.read_lo;
+      st.read_hi = tile.read_hi;
+      st.contig_id = tile.contig_id;
+      st.ref_index = tile.ref_index;
+      st.n_alleles = n_res;
+      st.forced = forced ? 1 : 0;
+      st.first_job = job0;
+      st._pad = 0;
+      for (int k = 0; k < SJ_MAX_ALLELES; ++k) {
+        SJAlleleDev a;
+        const int c = k < n_res ? res_c[k & 3] : -1;
+        a.key = (k < n_res && c >= 0) ? ((1ull << 61) | (1ull << 54) | (uint64_t)c) : 0;  // seq_key of one standard base
+        a.rep_read = -1;  // its string is the single character in rep_start_rp
+        a.span = k < n_res ? 1 : 0;
+        a.alt_len = k < n_res ? 1 : 0;
+        a.rep_start_rp = c >= 0 ? (int)"ACGT"[c] : (int)'N';
+        a._pad = 0;
+        st.alleles[k] = a;
+      }
+    }
+    // per evidence slot (lane i < S + 2: sample i, pooled normal DNA, pooled tumor DNA): the member samples' cells
+    const int my_kind = lane < S ? (int)((kinds >> (2 * lane)) & 3u) : lane == NP ? (int)GUAC_SJ_NORMAL_DNA : (int)GUAC_SJ_TUMOR_DNA;
+    int g_depth = 0, g_cnt[4], g_fwd[4], g_first[4], g_ll[4];
+    double g_A[4], g_B[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      g_cnt[c] = g_fwd[c] = g_ll[c] = 0;
+      g_first[c] = INT_MAX;
+      g_A[c] = g_B[c] = 0.0;
+    }
+    for (int s = 0; s < S; ++s) {
+      const int sk = (int)((kinds >> (2 * s)) & 3u);
+      const bool member = lane < S ? lane == s : (lane == NP ? sk == GUAC_SJ_NORMAL_DNA : sk == GUAC_SJ_TUMOR_DNA);
+      if (member) g_depth += pick4(depth[0], depth[1], depth[2], depth[3], s);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int vc = __shfl_sync(FULL, c_cnt, 4 * s + c), vf = __shfl_sync(FULL, c_fwd, 4 * s + c);
+        const int v1 = __shfl_sync(FULL, c_first, 4 * s + c), vl = __shfl_sync(FULL, c_ll, 4 * s + c);
+        const double va = __shfl_sync(FULL, c_A, 4 * s + c), vb = __shfl_sync(FULL, c_B, 4 * s + c);
+        if (member) {
+          g_cnt[c] += vc;
+          g_fwd[c] += vf;
+          g_first[c] = min(g_first[c], v1);
+          g_ll[c] += vl;
+          g_A[c] += va;
+          g_B[c] += vb;
+        }
+      }
+    }
+    const int n_sub = g_cnt[0] + g_cnt[1] + g_cnt[2] + g_cnt[3], f_sub = g_fwd[0] + g_fwd[1] + g_fwd[2] + g_fwd[3];
+    for (int a = 0; a < n_res; ++a) {
+      const int ca = res_c[a];  // -1: placeholder, equal to no subsequence
+      const int alt_cnt = ca < 0 ? 0 : pick4(g_cnt[0], g_cnt[1], g_cnt[2], g_cnt[3], ca);
+      const int alt_fwd = ca < 0 ? 0 : pick4(g_fwd[0], g_fwd[1], g_fwd[2], g_fwd[3], ca);
+      const int alt_ll = ca < 0 ? 0 : pick4(g_ll[0], g_ll[1], g_ll[2], g_ll[3], ca);
+      // alt fraction of a tumor mixture (TumorDNASingleSampleSingleAlleleEvidence.scala:38)
+      const double my_vaf = fmax(P.vaf_floor, (double)alt_cnt / (double)g_depth);
+      // {alt: vaf, ref: 1 - vaf} over the reads whose subsequence is the reference base, from the stash
+      double v[SJF_SMAX];
+#pragma unroll
+      for (int s = 0; s < SJF_SMAX; ++s) v[s] = __shfl_sync(FULL, my_vaf, s);
+      const double vp = __shfl_sync(FULL, my_vaf, TP);
+      double acc[SJF_SMAX] = {0.0, 0.0, 0.0, 0.0}, acc_p = 0.0;
+      for (int i = lane; i < n_span; i += 32) {
+        const uint8_t m = W.meta[i];
+        if (!(m & 4)) continue;
+        const int s = m & 3, sk = (int)((kinds >> (2 * s)) & 3u);
+        if (sk == GUAC_SJ_NORMAL_DNA) continue;
+        const double pp = W.p[i];
+        const double vs = pick4(v[0], v[1], v[2], v[3], s);
+        const double t = log10((1.0 - vs) * pp + (1.0 - (1.0 - vs)) * (1.0 - pp));
+#pragma unroll
+        for (int k = 0; k < SJF_SMAX; ++k)
+          if (s == k) acc[k] += t;
+        if (sk == GUAC_SJ_TUMOR_DNA) acc_p += log10((1.0 - vp) * pp + (1.0 - (1.0 - vp)) * (1.0 - pp));
+      }
+#pragma unroll
+      for (int s = 0; s < SJF_SMAX; ++s) acc[s] = warp_sum_fixed(acc[s]);
+      acc_p = warp_sum_fixed(acc_p);
+      if (lane >= S + 2) continue;
+      // likelihoods of this slot (PileupStats.logLikelihoodPileup :77-91 per mixture)
+      double other_B = 0.0, nonref_B = 0.0, nonalt_B = 0.0;  // sums of log10(1 - p) over base classes
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (c != cr) nonref_B += g_B[c];
+        if (c != ca) nonalt_B += g_B[c];
+        if (c != cr && c != ca) other_B += g_B[c];
+      }
+      const double ref_A = pick4(g_A[0], g_A[1], g_A[2], g_A[3], cr);
+      const double alt_A = ca < 0 ? 0.0 : pick4(g_A[0], g_A[1], g_A[2], g_A[3], ca);
+      const int ref_ll = pick4(g_ll[0], g_ll[1], g_ll[2], g_ll[3], cr);
+      double ll0 = ref_A + nonref_B, ll1, ll2 = 0.0;
+      if (my_kind == GUAC_SJ_NORMAL_DNA) {
+        ll1 = (double)(ref_ll + alt_ll) * LOG10_HALF + other_B;  // {ref: 0.5, alt: 0.5}
+        ll2 = alt_A + nonalt_B;                                    // {alt: 1}
+      } else {
+        // reference-base reads from the stash; the alternate base's reads and the others from the list, in read order
+        ll1 = lane == TP ? acc_p : pick4(acc[0], acc[1], acc[2], acc[3], lane);
+        for (int k = 0; k < n_list; ++k) {
+          const SJFListEntry& e = W.list[k];
+          if (!(e.flags & 2)) continue;
+          const int sk = (int)((kinds >> (2 * e.s)) & 3u);
+          if (lane < S ? e.s != lane : sk != GUAC_SJ_TUMOR_DNA) continue;
+          ll1 += (int)e.c == ca ? log10(my_vaf * e.p + (1.0 - my_vaf) * (1.0 - e.p)) : e.B;
+        }
+      }
+      SJEvidenceDev* E = reinterpret_cast<SJEvidenceDev*>(A.raw + (size_t)(job0 + a) * A.raw_stride);
+      if (lane == 0) {
+        E->site = site_idx;
+        E->allele = a;
+      }
+      SJSlotDev& o = E->slots[lane];
+      o.total_depth = g_depth;
+      o.n_subsequences = n_sub;
+      o.forward_subsequences = f_sub;
+      o.variant_count = alt_cnt;
+      o.variant_forward = alt_fwd;
+      o.ref_count = pick4(g_cnt[0], g_cnt[1], g_cnt[2], g_cnt[3], cr);
+      o._pad = 0;
+      o.alt_vaf = my_vaf;
+      o.ll[0] = ll0;
+      o.ll[1] = ll1;
+      o.ll[2] = ll2;
+      // truncatedAllelicDepths(maxAllelesPerSite + 1): by count desc, first supporting read asc
+      int cnt[4] = {g_cnt[0], g_cnt[1], g_cnt[2], g_cnt[3]};
+      int nd = 0;
+      for (int round = 0; round < 4 && nd < P.max_alleles + 1; ++round) {
+        int best = -1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (cnt[c] > 0 && (best < 0 || cnt[c] > cnt[best] || (cnt[c] == cnt[best] && g_first[c] < g_first[best]))) best = c;
+        if (best < 0) break;
+        SJDepthDev d;
+        d.key = (1ull << 61) | (1ull << 54) | (uint64_t)best;
+        d.rep_read = -1;
+        d.rep_start_rp = (int)"ACGT"[best];
+        d.len = 1;
+        d.count = cnt[best];
+        d.forward = pick4(g_fwd[0], g_fwd[1], g_fwd[2], g_fwd[3], best);
+        o.depths[nd++] = d;
+        cnt[best] = 0;
+      }
+      o.n_depths = nd;
+    }
+  }
+}
+
+}  // namespace guac

@@ -142,8 +142,8 @@ struct TileSmem {
   uint32_t ref2[((CFG::TL + CFG::THREADS - 1) / CFG::THREADS) * (CFG::THREADS / 16) + 2];  // whole passes of the loader + read-ahead
   int cov[CFG::TL + 1];     // packed differences: normal | tumor << 16  -> depths after the scan
   int aux[CFG::TL + 1];     // low-quality tumor read differences | event count << 16 -> lowq | event end offset
-  int nonref[CFG::TL];      // non-Match elements: normal | tumor << 16
-  int cursor[CFG::TL];
+  int nonref[CFG::TL + 1];  // non-Match elements: normal | tumor << 16 (MODE 2 also keeps the locus behind the tile)
+  int cursor[CFG::TL + 1];
   uint2 ev[CFG::E_MAX];
   uint16_t ev_order[CFG::E_MAX];  // event indices bucketed by locus (2 B per event instead of a second copy)
   uint16_t slow[CFG::SLOW_MAX];
@@ -170,7 +170,13 @@ struct TileArgs {
   int n_force;
   // STREAM variant (stream_kernels.cuh): the reads were compared with the reference by a kernel of their own
   const uint2* ev_by_read;        // [n_reads][STREAM_EV_CAP] read-event records
-  const uint8_t* ev_count;        // [n_reads] (more than the cap: the tile goes to the generic kernel)
+  const uint8_t* ev_count;        // [n_reads] (more than the cap: the read is walked by the exact cursor)
+  // MODE 2 with at most four samples: events carry their sample id and candidate loci are classified — `simple` lists
+  // the sites whose alternate alleles can only be single-base substitutions (sj_snv_site_kernel), `heavy` the others
+  int sample_bits;
+  Tile* simple;
+  int* n_simple;
+  int max_simple;
 };
 
 // MODE 0: somatic-standard (two samples).  MODE 1: germline toy caller's dense half — one sample (the "tumor"
@@ -193,6 +199,9 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   const int n_loci = tile.n_loci;
   const int64_t t0 = tile.locus0;
   const int64_t n_reads_tile = tile.read_hi - tile.read_lo;
+  // loci whose events are kept: the stream form of MODE 2 also keeps the first locus behind the tile, where the alleles
+  // of the tile's last site start (every read that has an element there and at the last site is among the tile's reads)
+  const int n_ev_loci = (MODE == 2 && STREAM) ? n_loci + 1 : n_loci;
 
   bool too_big = n_reads_tile > CFG::R_MAX;
   if (A.force_fallback_mod > 0 && blockIdx.x % A.force_fallback_mod == 0) too_big = true;  // test hook
@@ -220,7 +229,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
 
   // ---- init ------------------------------------------------------------------------------
   for (int i = tid; i < TL + 1; i += CFG::THREADS) S.cov[i] = S.aux[i] = 0;
-  for (int i = tid; i < TL; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
+  for (int i = tid; i < TL + 1; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
   if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = 0;
   if (tid < 4) {  // padding words behind the tile
     S.ref2[TL / 16 + (tid & 1)] = 0;
@@ -263,10 +272,11 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       return;
     }
   }
+  uint32_t ev_sample = 0;  // MODE 2: the current read's sample id, bits 30..31 of its event words
   auto push_event = [&](int l, int rl, int slot, int kind, int code, uint32_t second) {
     atomicAdd(&S.nonref[l], slot ? 65536 : 1);
     const int e = atomicAdd(&S.n_events, 1);
-    if (e < CFG::E_MAX) S.ev[e] = make_uint2(pack_event(l, rl, slot, kind, code), second); else S.overflow = 1;
+    if (e < CFG::E_MAX) S.ev[e] = make_uint2(pack_event(l, rl, slot, kind, code) | ev_sample, second); else S.overflow = 1;
   };
   auto direct = [](int q, int detail) { return 0x80000000u | ((uint32_t)(detail & 0xFF) << 8) | (uint32_t)(q & 0xFF); };
 
@@ -292,6 +302,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const uint8_t rf = (uint8_t)(hdr.y >> 24);
     if (MODE == 2 ? smp >= P.n_samples : (smp != P.normal_sample && smp != P.tumor_sample)) continue;
     const int slot = MODE == 2 ? (int)((P.sample_mask >> smp) & 1u) : (smp == P.tumor_sample ? 1 : 0);
+    if (MODE == 2) ev_sample = A.sample_bits ? (uint32_t)(smp & 3) << 30 : 0u;
     // the reads of a tile start within 2^31 loci of it, so 32-bit wrap-around arithmetic gives the exact offset
     const int st = (int)(hdr.x - t0_lo);
     int en = st + (int)(hdr.y & 0xFFFF);
@@ -313,8 +324,9 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     if (STREAM) {  // the read was compared by ss_read_events_kernel: take the events that fall inside the tile
-      if (cnt > 8) {
-        S.overflow = 1;
+      if (cnt > 8) {  // more events than its slot holds: the exact cursor walks this read (rare)
+        const int i = atomicAdd(&S.n_slow, 1);
+        if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)rl; else S.overflow = 1;
         continue;
       }
       const uint2* evs = A.ev_by_read + r * 8;
@@ -324,10 +336,10 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         const int kind = (int)((ev.x >> 16) & 7), code = (int)((ev.x >> 19) & 7);
         if (kind == GUAC_ALN_MID_DELETION) {  // a run of deleted loci
           const int run = (int)((ev.y >> 16) & 0x7FFF);
-          for (int ll = max(l, 0); ll < min(l + run, n_loci); ++ll) push_event(ll, rl, slot, kind, code, ev.y & 0x8000FFFFu);
+          for (int ll = max(l, 0); ll < min(l + run, n_ev_loci); ++ll) push_event(ll, rl, slot, kind, code, ev.y & 0x8000FFFFu);
           continue;
         }
-        if (l < 0 || l >= n_loci) continue;
+        if (l < 0 || l >= n_ev_loci) continue;
         uint32_t second = ev.y;
         if (kind == GUAC_ALN_MISMATCH) {
           second = s0_rel + ev.y;  // quality index relative to the tile's first base
@@ -432,8 +444,9 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       const int64_t r = tile.read_lo + rl;
       const int smp = (int)__ldg(R.sample_id + r);
       const int slot = MODE == 2 ? (int)((P.sample_mask >> smp) & 1u) : (smp == P.tumor_sample ? 1 : 0);
+      if (MODE == 2) ev_sample = A.sample_bits ? (uint32_t)(smp & 3) << 30 : 0u;
       const int a = (int)max((long long)(__ldg(R.start + r) - t0), 0ll);
-      const int b = (int)min((long long)(__ldg(R.end + r) - t0), (long long)n_loci);
+      const int b = (int)min((long long)(__ldg(R.end + r) - t0), (long long)n_ev_loci);
       for (int l = a + lane; l < b; l += 32) {
         Elem e;
         const int ec = element_at(R, r, t0 + l, ref, e);
@@ -460,7 +473,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const int b0 = tid * PER, e0 = min(n_loci + 1, b0 + PER);
     int s_cov = 0, s_aux = 0;
     for (int i = b0; i < e0; ++i) {
-      if (i < n_loci) {  // add the locus's event count to the high half of aux
+      if (i < n_ev_loci) {  // add the locus's event count to the high half of aux
         const int nr = S.nonref[i];
         S.aux[i] += ((nr & 0xFFFF) + (nr >> 16)) << 16;
       }
@@ -516,7 +529,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     A.visited[slot] = dN + dT > 0 ? 1 : 0;
     my_visited += dN + dT > 0;
     // (a tile with a missing reference base never gets here: it went to the generic kernel, which reports the error)
-    bool candidate;
+    bool candidate, simple_site = false;
     if (MODE == 0) {  // early-outs (SomaticStandardCaller.scala:164-172)
       candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
     } else if (MODE == 1) {
@@ -526,15 +539,53 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       if (dN + dT > 0) {
         // reference.getReferenceBase(contig, locus + 1) (jointcaller/evidence/MultiSampleMultiAlleleEvidence.scala:93)
         if (ref.at(x + 1) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x + 1, -1);
-        candidate = l + 1 >= n_loci || (S.nonref[l + 1] >> 16) >= P.min_alt_reads;
-        for (int i = 0; i < A.n_force && !candidate; ++i)
-          candidate = A.force[i].contig_id == tile.contig_id && A.force[i].start <= x + 1 && x + 1 < A.force[i].end;
+        if (l + 1 >= n_ev_loci) {
+          candidate = true;  // (single-kernel form: the events of x + 1 are in the next tile)
+        } else if ((S.nonref[l + 1] >> 16) >= P.min_alt_reads) {
+          candidate = true;
+          if (A.sample_bits) {
+            // An allele needs min_alt_reads reads of ONE discovery sample whose elements at x + 1 are the same non-Match
+            // element (AlleleAtLocus.scala:99-124 can keep nothing less).  The site is simple when every such element
+            // is a substitution by a standard base: the fast site kernel then decides it exactly.
+            const int nr1 = S.nonref[l + 1];
+            const int e1 = S.aux[l + 1] >> 16, e0 = e1 - ((nr1 & 0xFFFF) + (nr1 >> 16));
+            if (e1 - e0 <= CFG::EV_SIMPLE) {
+              auto skey = [&](uint2 ev) {
+                const int kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7;
+                return (ev.x >> 30 << 16) | ((uint32_t)kind << 8) |
+                       (uint32_t)(kind == GUAC_ALN_MISMATCH ? code : (kind == GUAC_ALN_MID_DELETION ? 0 : (int)((ev.y >> 8) & 0xFF)));
+              };
+              simple_site = true;
+              int best = 0;
+              for (int i = e0; i < e1; ++i) {
+                const uint2 ev = S.ev[S.ev_order[i]];
+                if (((ev.x >> 23) & 1) != 1) continue;  // not a discovery sample
+                const int kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7;
+                if (!(kind == GUAC_ALN_MISMATCH && code < 4)) simple_site = false;
+                const uint32_t k = skey(ev);
+                int c = 0;
+                for (int j = e0; j < e1; ++j) {
+                  const uint2 ej = S.ev[S.ev_order[j]];
+                  c += ((ej.x >> 23) & 1) == 1 && skey(ej) == k;
+                }
+                best = max(best, c);
+              }
+              candidate = best >= P.min_alt_reads;
+            }
+          }
+        }
+        for (int i = 0; i < A.n_force; ++i)
+          if (A.force[i].contig_id == tile.contig_id && A.force[i].start <= x + 1 && x + 1 < A.force[i].end) {
+            candidate = true;  // force-called: always evaluated, by the generic kernels
+            simple_site = false;
+          }
       }
     }
     int flags = 0;
     if (MODE != 0 && candidate) {  // every candidate locus goes to the per-locus kernel
-      const int h = atomicAdd(A.n_heavy, 1);
-      if (h < A.max_heavy) {
+      const bool to_simple = MODE == 2 && simple_site;
+      const int h = atomicAdd(to_simple ? A.n_simple : A.n_heavy, 1);
+      if (h < (to_simple ? A.max_simple : A.max_heavy)) {
         Tile t;
         t.locus0 = x;
         t.n_loci = 1;
@@ -545,7 +596,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         t.ref_index = tile.ref_index;
         t._pad = 0;
         t.seq_base = t.seq_end = 0;
-        A.heavy[h] = t;
+        (to_simple ? A.simple : A.heavy)[h] = t;
       }
       flags = 1;
     }

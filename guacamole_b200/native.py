@@ -468,6 +468,12 @@ class Context:
     def set_option(self, name: str, value: int):
         self._check(self.lib.guac_set_option(self.ctx, name.encode(), C.c_int64(value)))
 
+    def last_stat(self, name: str) -> int:
+        """guac_last_stat: a counter of the most recent caller invocation ("fallback_tiles", "heavy_loci", "sj_simple", ...)."""
+        self.lib.guac_last_stat.restype = C.c_int64
+        self.lib.guac_last_stat.argtypes = [C.c_void_p, C.c_char_p]
+        return int(self.lib.guac_last_stat(self.ctx, name.encode()))
+
     @property
     def last_fallback_tiles(self) -> int:
         self.lib.guac_last_fallback_tiles.restype = C.c_int64

@@ -445,9 +445,10 @@ typedef struct {
  * by -1 (lociSetMinusOne :143-152; the function does the shift itself).  A site is force-called when
  * pileup locus + 1 lies in `force_loci` (:181).  Per-element work — ReadSubsequence, AlleleAtLocus,
  * PileupStats and the mixture likelihoods (M/jointcaller/pileup_summarization/ (all files), AlleleAtLocus.scala:85-149,
- * evidence/ ...SingleSampleSingleAlleleEvidence.scala) — runs on the device; posteriors, call logic, annotations
- * (M/jointcaller/evidence/MultiSampleSingleAlleleEvidence.scala:66-341, the files of annotation/) and the emit
- * policy (MultiSampleMultiAlleleEvidence.scala:131-177) on the host side of the library.
+ * evidence/ ...SingleSampleSingleAlleleEvidence.scala) — and posteriors, call logic, annotations
+ * (M/jointcaller/evidence/MultiSampleSingleAlleleEvidence.scala:66-341, annotation/StrandBias.scala:47-58 over
+ * filters/FishersExactTest.scala:12-19, annotation/InsufficientNormal.scala:21-53) and the emit policy
+ * (MultiSampleMultiAlleleEvidence.scala:131-177) all run on the device: only the emitted records come back.
  * Output: one guac_sj_allele_evidence per emitted allele, in (range order, locus, allele) order, each with
  * n_samples + 2 guac_sj_sample_evidence records; strings in the arena.
  */
@@ -467,8 +468,10 @@ void* guac_stream(guac_ctx* ctx);
  *   "ss_impl"               somatic-standard: 2 = read pass + locus pass as two kernels (default), 0 = both in one tile
  *                           kernel, 1 = generic gather kernel only; all three fall back to the gather kernel per tile
  *   "ss_force_fallback_mod" k > 0 sends every k-th tile through the fallback path (test hook)
- *   "sj_host_threads"       host threads guac_somatic_joint may use for its per-site arithmetic (0, the default: one per
- *                           host core, at most 32; 1: the calling thread only)
+ *   "sj_impl"               somatic-joint: 2 = read pass + classifying locus pass + fast site kernel (default), 1 = the same
+ *                           with the single-kernel locus pass, 0 = every candidate locus through the generic per-locus
+ *                           kernels; more than four samples always take the generic kernels
+ *   "sj_host_threads"       accepted and ignored (the per-site arithmetic runs on the device)
  *   "compact_narrow"        1 (default): guac_reads_export_compact emits the narrow columns where the batch allows; 0: never
  *   "ss_rank_max"           somatic-standard ranks more calls than this through a bitmap over the loci instead of by
  *                           pairwise comparison (test hook; default and maximum 32768, negative restores the default) */
@@ -477,6 +480,10 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value);
 int64_t guac_last_fallback_tiles(guac_ctx* ctx);
 /* Loci of that call whose likelihoods had to be evaluated in full (not excluded by the LOD bound). */
 int64_t guac_last_heavy_loci(guac_ctx* ctx);
+/* Counters of the most recent caller invocation by name: "fallback_tiles", "heavy_loci" (as above; for somatic-joint the
+ * candidate loci that went to the generic per-locus kernels), "sj_simple" (candidate loci the fast site kernel took),
+ * "sj_bail" (those it handed back), "sj_sites" (sites with at least one allele), "sj_emitted_sites".  -1: unknown name. */
+int64_t guac_last_stat(guac_ctx* ctx, const char* name);
 /* Device time in ms (CUDA events on the context's stream) of the dominant per-locus kernel
  * of the most recent caller invocation, and how many loci it processed. */
 int guac_last_kernel_ms(guac_ctx* ctx, float* ms, int64_t* n_loci);

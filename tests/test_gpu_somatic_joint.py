@@ -37,7 +37,7 @@ def assert_evidences_equal(got, want):
             assert math.isclose(gs["sb_phred"], ws["sb_phred"], rel_tol=1e-9, abs_tol=1e-12)
 
 
-def test_tiny_sjc_golden_vcf_on_gpu(gpu_ctx):
+def test_tiny_sjc_golden_vcf_on_gpu(gpu_ctx, sj_impl):
     batch, ref, extra = fixtures.load("tiny_sjc")
     kinds = [sj.NORMAL_DNA, sj.TUMOR_DNA, sj.TUMOR_DNA]
     loci = sj.loci_from_vcf_lines([str(x) for x in extra["force_call_vcf"]], batch.contig_names)
@@ -51,7 +51,7 @@ def test_tiny_sjc_golden_vcf_on_gpu(gpu_ctx):
     assert_evidences_equal(evs, want)
 
 
-def test_tiny_sjc_all_covered_loci(gpu_ctx):
+def test_tiny_sjc_all_covered_loci(gpu_ctx, sj_impl):
     """Beyond the single golden site: every covered locus of the fixture, no forcing, filtered calls included."""
     from guacamole_b200.commands.somatic_standard import covered_ranges
     batch, ref, _ = fixtures.load("tiny_sjc")
@@ -70,7 +70,7 @@ def test_tiny_sjc_all_covered_loci(gpu_ctx):
     ((30, 30, 60, 60), (False, False, True, True), [0, 0, 1, 1], 4005),   # BASELINE configs[3] shape: 2 normal + 2 tumor
     ((30, 60, 40), (False, True, True), [0, 1, 2], 4105),                   # with a tumor RNA sample
 ])
-def test_synthetic_multi_sample(gpu_ctx, depths, tumor, kinds, seed):
+def test_synthetic_multi_sample(gpu_ctx, sj_impl, depths, tumor, kinds, seed):
     contig_len = 20000
     ref = synth.make_reference(contig_len, seed)
     batch = synth.generate_reads(contig_len, depths, tumor, seed)
@@ -91,7 +91,7 @@ def test_synthetic_multi_sample(gpu_ctx, depths, tumor, kinds, seed):
     assert_evidences_equal(parts, whole)  # integer fields exact; likelihood sums are order-dependent in the last bits
 
 
-def test_indel_alleles_and_non_standard_bases(gpu_ctx):
+def test_indel_alleles_and_non_standard_bases(gpu_ctx, sj_impl):
     """ReadSubsequenceSuite / PileupStatsSuite reads: shared insertion alleles, an SNV, an N base."""
     ref = make_reference(("chr1", 0, "NTCGATCGACGTTACGGATCCA"))
     reads = []
@@ -113,22 +113,35 @@ def test_indel_alleles_and_non_standard_bases(gpu_ctx):
     assert_evidences_equal(got, want)
 
 
-def test_host_threads_do_not_change_the_records(gpu_ctx):
-    """Enough candidate sites for the per-site arithmetic to be split over several host threads: the records are the ones
-    the calling thread alone produces (option sj_host_threads)."""
+@pytest.fixture(params=[2, 1, 0], ids=["stream", "single-kernel-locus-pass", "generic-kernels"])
+def sj_impl(request, gpu_ctx):
+    """Every parity case runs through the default form (read pass + classifying locus pass + fast site kernel), the
+    single-kernel locus pass, and the generic per-locus kernels alone."""
+    gpu_ctx.set_option("sj_impl", request.param)
+    yield request.param
+    gpu_ctx.set_option("sj_impl", 2)
+
+
+def test_repeat_runs_are_bit_identical(gpu_ctx):
+    """The likelihood sums are taken in a fixed order (per-lane partial sums combined by fixed trees; the generic kernel adds
+    its terms in read order), so two runs over the same batch return the same bytes — rendered VCF rows cannot flip."""
     contig_len, depths, tumor, kinds, seed = 600_000, (30, 60, 30), (False, True, True), [0, 1, 1], 4205
     ref = synth.make_reference(contig_len, seed)
     batch = synth.generate_reads(contig_len, depths, tumor, seed)
     gpu_ctx.upload_reference(ref, batch.contig_names)
     gpu_ctx.upload_reads(batch)
     loci = [(0, 1, contig_len)]
-    p = sj.sj_params(kinds, include_filtered=1)  # every candidate site comes back: thousands of records
-    try:
-        gpu_ctx.set_option("sj_host_threads", 1)
-        alone, nv1 = gpu_ctx.somatic_joint(loci, p)
-        gpu_ctx.set_option("sj_host_threads", 4)
-        shared, nv4 = gpu_ctx.somatic_joint(loci, p)
-    finally:
-        gpu_ctx.set_option("sj_host_threads", 0)
-    assert nv1 == nv4 and len(alone) > 100  # (emitted records; the candidate sites behind them are ~5 000: two threads)
-    assert_evidences_equal(shared, alone)
+    p = sj.sj_params(kinds, include_filtered=1)
+    for impl in (2, 0):
+        gpu_ctx.set_option("sj_impl", impl)
+        try:
+            a1, s1, arena1, nv1 = gpu_ctx.somatic_joint_records(loci, p)
+            a2, s2, arena2, nv2 = gpu_ctx.somatic_joint_records(loci, p)
+        finally:
+            gpu_ctx.set_option("sj_impl", 2)
+        assert nv1 == nv2 and len(a1) > 100
+        assert a1.tobytes() == a2.tobytes() and s1.tobytes() == s2.tobytes() and arena1 == arena2
+    # and the fast site kernel took nearly every candidate of this SNV-only workload
+    gpu_ctx.somatic_joint_records(loci, p)
+    simple, bail, heavy = gpu_ctx.last_stat("sj_simple"), gpu_ctx.last_stat("sj_bail"), gpu_ctx.last_stat("heavy_loci")
+    assert simple > 0 and bail < 0.1 * simple and heavy < 0.1 * simple, (simple, bail, heavy)
