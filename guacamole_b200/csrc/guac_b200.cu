@@ -105,7 +105,8 @@ struct guac_ctx {
   DevBuf g_active, g_jobs, g_evs, g_strings;  // scratch of guac_germline_standard, kept between calls
   // somatic-joint: force-call ranges, simple candidates, the fast kernel's sites / raw records / hand-backs, the generic
   // kernels' raw records, emitted sites and their order, offsets, finished records, ln n! table
-  DevBuf j_force, j_simple, j_sites_fast, j_raw_fast, j_bail, j_raw_gen, j_emits, j_order, j_cnt, j_off, j_out_alleles, j_out_samples, j_logfact;
+  DevBuf j_force, j_simple, j_sites_fast, j_raw_fast, j_bail, j_raw_gen, j_emits, j_order, j_cnt, j_off, j_out_alleles, j_out_samples, j_logfact, j_logtab;
+  int64_t opt_sj_prune = 1;  // locus pass drops simple sites that certainly hold no call (test hook: 0 sends them all to the site kernel)
   int64_t opt_sj_impl = 2;  // 2: read pass + classifying locus pass + fast site kernel (default); 1: single-kernel locus pass; 0: no fast site kernel
   int64_t stat_sj_simple = 0, stat_sj_bail = 0, stat_sj_sites = 0, stat_sj_emitted_sites = 0;
   void* h_counters = nullptr;  // pinned: the per-call counter block comes back without a staging copy
@@ -495,6 +496,10 @@ int sj_logfact_table(guac_ctx* ctx) {
   }
   GUAC_TRY(upload(ctx, ctx->j_logfact, t.data(), t.size()));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `t` is a temporary
+  GUAC_TRY(ensure(ctx, ctx->j_logtab, 65536 * sizeof(double2)));
+  sj_log_table_kernel<<<256, 256, 0, ctx->stream>>>(ctx->j_logtab.as<double2>());
+  ctx->launches += 1;
+  CUDA_TRY(ctx, cudaGetLastError());
   return GUAC_OK;
 }
 
@@ -622,7 +627,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
                     &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings,
                     &ctx->r_bitmap, &ctx->r_counts, &ctx->r_prefix, &ctx->r_rank, &ctx->j_force, &ctx->j_simple, &ctx->j_sites_fast,
                     &ctx->j_raw_fast, &ctx->j_bail, &ctx->j_raw_gen, &ctx->j_emits, &ctx->j_order, &ctx->j_cnt, &ctx->j_off,
-                    &ctx->j_out_alleles, &ctx->j_out_samples, &ctx->j_logfact})
+                    &ctx->j_out_alleles, &ctx->j_out_samples, &ctx->j_logfact, &ctx->j_logtab})
     if (b->p) cudaFree(b->p);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   for (auto& kv : ctx->contigs)
@@ -1255,6 +1260,18 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     TA.simple = ctx->j_simple.as<Tile>();
     TA.n_simple = &d_cnt->n_simple;
     TA.max_simple = max_simple;
+    TA.log_table = ctx->j_logtab.as<double2>();
+    TA.het_prior = params->germline_neg_log10_het_prior;
+    TA.hom_prior = params->germline_neg_log10_hom_alt_prior;
+    TA.somatic_prior = params->somatic_neg_log10_variant_prior;
+    TA.vaf_floor = params->somatic_vaf_floor;
+    bool has_rna = false;
+    for (int s = 0; s < S && s < 4; ++s) {
+      TA.kinds |= (unsigned)P.kind[s] << (2 * s);
+      has_rna = has_rna || P.kind[s] == GUAC_SJ_TUMOR_RNA;
+    }
+    // (with RNA samples the DNA prior of a site depends on their posteriors: no in-tile shortcut)
+    TA.prune = classify && stream && !has_rna && ctx->opt_sj_prune ? 1 : 0;
     if (stream) {
       TA.ev_by_read = ctx->b_bins.as<uint2>();
       TA.ev_count = ctx->b_bin_count.as<uint8_t>();
@@ -1288,6 +1305,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
       SJFArgs FA;
       std::memset(&FA, 0, sizeof FA);
       FA.hdr = ctx->b_hdr.as<uint4>();
+      FA.log_table = ctx->j_logtab.as<double2>();
       FA.refs = ctx->d_refs.as<RefView>();
       FA.cands = ctx->j_simple.as<Tile>();
       FA.n_cands = &d_cnt->n_simple;
@@ -1306,7 +1324,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
       FA.max_bail = n_simple;
       FA.err = ctx->b_err.as<DeviceError>();
       const unsigned grid = (unsigned)std::min<int64_t>(blocks_for(n_simple, 8), 148 * 16);
-      sj_snv_site_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->R, P, FA);
+      sj_snv_site_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->R, P, *params, FA);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
       GUAC_TRY(read_counters());
@@ -1749,6 +1767,8 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
     ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
   } else if (n == "sj_host_threads") {
     ctx->opt_sj_host_threads = value < 0 ? 0 : std::min<int64_t>(value, 256);  // accepted for old callers; nothing runs on host threads any more
+  } else if (n == "sj_prune") {
+    ctx->opt_sj_prune = value != 0;
   } else if (n == "sj_impl") {
     if (value < 0 || value > 2) return fail(ctx, GUAC_E_INVALID_INPUT, "sj_impl must be 0, 1 or 2");
     ctx->opt_sj_impl = value;

@@ -327,22 +327,24 @@ sj_final_kernel(ReadsView R, const RefView* __restrict__ refs, const __grid_cons
 
 constexpr int SJF_SMAX = 4;         // samples the fast site kernel handles (more: every candidate takes the generic kernels)
 constexpr int SJF_MAX_READS = 256;  // reads in the span of a site
-constexpr int SJF_LIST = 64;        // subsequences of a site that differ from the reference base
+constexpr int SJF_LIST = 256;       // subsequences of a site that differ from the reference base (a heterozygous site has many)
 
-struct SJFListEntry {
-  double p, A, B;  // P(correct), log10 p, log10 (1 - p)
-  int32_t rel;     // read index relative to the site's first read
-  uint8_t s, c, flags, _pad;  // sample, base code, 1: positive strand | 2: mapq > 0 | 4: starts an alternate allele
+struct SJFListEntry {  // (P(correct) and its two logarithms are looked up again from the quality and mapq)
+  uint16_t rel;        // read index relative to the site's first read
+  uint8_t s, c, flags; // sample, base code, 1: positive strand | 2: mapq > 0 | 4: starts an alternate allele
+  uint8_t q, mapq, _pad;
 };
 
 struct SJFWarpSmem {
   double p[SJF_MAX_READS];      // P(correct) of the reads whose subsequence is the reference base
   uint8_t meta[SJF_MAX_READS];  // sample | 4: such a read, with mapq > 0
   SJFListEntry list[SJF_LIST];
+  uint16_t slow[SJF_LIST];      // reads the exact cursor walks (several operators, N skips, non-standard bases)
 };
 
 struct SJFArgs {
   const uint4* hdr;
+  const double2* log_table; // sj_log_table_kernel
   const RefView* refs;
   const Tile* cands;        // simple candidates as single-locus tiles (the read span of the tile they came from)
   const int* n_cands;
@@ -371,18 +373,65 @@ __device__ __forceinline__ double warp_sum_fixed(double v) {  // the same tree f
 template <class T>
 __device__ __forceinline__ T pick4(T a0, T a1, T a2, T a3, int i) { return i == 0 ? a0 : i == 1 ? a1 : i == 2 ? a2 : a3; }
 
-__global__ void __launch_bounds__(256)
-sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __grid_constant__ SJFArgs A) {
+// log10 p and log10 (1 - p) of p = P(quality) * P(mapq) (PileupStats.scala:83-86) for every (mapq, quality) pair: the
+// fast site kernel looks its per-read terms up instead of taking two logarithms per read (1 MB, L2-resident).
+__global__ void sj_log_table_kernel(double2* __restrict__ table) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 65536) return;
+  const double p = c_success_probability[i & 255] * c_success_probability[i >> 8];
+  table[i] = make_double2(log10(p), log10(1.0 - p));
+}
+
+// One read through the exact cursor, out of line (the fast kernel's code stays small): bit 0 in depth, bit 1 has a
+// one-base subsequence (code in bits 8..9, quality in bits 16..23), bit 2 that base starts a one-base alternate allele,
+// bit 3 starts an allele of another shape, bit 4 the site cannot be decided here.
+__device__ __noinline__ unsigned sjf_classify_slow(const ReadsView& R, int64_t r, int64_t x, const RefView& ref, int cr) {
+  Elem e0;
+  if (element_at(R, r, x, ref, e0) != DERR_NONE) return 16u;  // the generic kernels report it
+  if (e0.kind == GUAC_ALN_CLIPPED) return 0u;                 // Clipped elements are dropped first (:85-86)
+  unsigned out = 1u;
+  SubSeq sa, sf;
+  const int fa = next_alt_allele(R, r, x, ref, e0, sa);
+  const int ff = fixed_length_subsequence(R, r, x, ref, e0, 1, sf);
+  if (fa < 0 || ff < 0) return 16u;
+  const uint64_t s0 = __ldg(R.seq_off + r);
+  int c = 4;
+  if (ff > 0) {
+    const uint8_t b = sf.end_rp - sf.start_rp == 1 ? read_base(R, s0 + sf.start_rp) : (uint8_t)0;
+    c = base_code(b);
+    if (c == 4) return 16u;  // a subsequence that is not one standard base (an insertion, an N)
+    out |= 2u | ((unsigned)c << 8) | ((unsigned)__ldg(R.qual + s0 + sf.start_rp) << 16);
+  }
+  if (fa > 0) {  // a one-base allele is this very base over one locus; anything else is another shape
+    if (sa.end_locus - sa.start_locus == 1 && sa.end_rp - sa.start_rp == 1 && ff > 0 && sa.start_rp == sf.start_rp && c != cr) out |= 4u;
+    else out |= 8u;
+  }
+  return out;
+}
+
+#ifndef GUAC_SJF_MINB
+#define GUAC_SJF_MINB 2
+#endif
+__global__ void __launch_bounds__(256, GUAC_SJF_MINB)
+sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __grid_constant__ guac_sj_params EP,
+                   const __grid_constant__ SJFArgs A) {
   __shared__ SJFWarpSmem smem_all[8];
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   SJFWarpSmem& W = smem_all[warp];
   const int S = P.n_samples, NP = S, TP = S + 1;
   const int n_cands = min(*A.n_cands, A.max_cands);
-  // sample kinds and the discovery order as packed words: no dynamically indexed parameter arrays in the loop
-  unsigned kinds = 0, disc_order = 0;
-  for (int s = 0; s < S; ++s) kinds |= (unsigned)P.kind[s] << (2 * s);
-  for (int d = 0; d < P.n_discovery; ++d) disc_order |= (unsigned)P.discovery[d] << (4 * d);
+  // sample kinds and the discovery order as packed words: no dynamically indexed parameter arrays in the loops
+  unsigned kinds = 0, disc_order = 0, disc_mask = 0;
+  bool has_rna = false;
+  for (int s = 0; s < S; ++s) {
+    kinds |= (unsigned)P.kind[s] << (2 * s);
+    has_rna = has_rna || P.kind[s] == GUAC_SJ_TUMOR_RNA;
+  }
+  for (int d = 0; d < P.n_discovery; ++d) {
+    disc_order |= (unsigned)P.discovery[d] << (4 * d);
+    disc_mask |= 1u << P.discovery[d];
+  }
   const double LOG10_HALF = -0.3010299956639812;  // math.log10(0.5)
 
   for (int ci = blockIdx.x * 8 + warp; ci < n_cands; ci += gridDim.x * 8) {
@@ -394,35 +443,107 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
     tile.read_lo = warp_partition_point(tile.read_lo, tile.read_hi, lane, [&](int64_t i) { return __ldg(R.runmax_key + i) > key; });
     const int n_span = (int)min((int64_t)(tile.read_hi - tile.read_lo), (int64_t)(SJF_MAX_READS + 1));
     const uint8_t rb0 = ref.at(x), rb1 = ref.at(x + 1), rb2 = ref.at(x + 2);
-    bool bail = n_span > SJF_MAX_READS || rb0 == 0 || rb2 == 0;
     if (rb1 == 0) {  // reference.getReferenceBase(contig, locus + 1) (MultiSampleMultiAlleleEvidence.scala:93)
       if (lane == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x + 1, -1);
       continue;
     }
     const int cr = base_code(rb1);
     if (cr == 4) continue;  // not a standard base: no evidence at this site
-    const bool forced = locus_forced(A.force, A.n_force, tile.contig_id, x + 1);
+    // force-called sites (their fallback alleles can have any shape) and spans beyond the stash take the generic kernels
+    bool bail = n_span > SJF_MAX_READS || rb0 == 0 || rb2 == 0 || locus_forced(A.force, A.n_force, tile.contig_id, x + 1);
 
-    int depth[SJF_SMAX], rcnt[SJF_SMAX], rfwd[SJF_SMAX], rfirst[SJF_SMAX], rll[SJF_SMAX];
+    int depth[SJF_SMAX], rcnt[SJF_SMAX], rfwd[SJF_SMAX], rfirst[SJF_SMAX], rll[SJF_SMAX], ns_alt[SJF_SMAX];
     double rA[SJF_SMAX], rB[SJF_SMAX];
 #pragma unroll
     for (int s = 0; s < SJF_SMAX; ++s) {
-      depth[s] = rcnt[s] = rfwd[s] = rll[s] = 0;
+      depth[s] = rcnt[s] = rfwd[s] = rll[s] = ns_alt[s] = 0;
       rfirst[s] = INT_MAX;
       rA[s] = rB[s] = 0.0;
     }
-    int n_list = 0;
+    int n_list = 0, n_slow = 0;
     const uint32_t x_lo = (uint32_t)x;
+    // One read's contribution.  in_depth: it has a (non-Clipped) element at x; has_sub: its fixed-length-1 subsequence
+    // exists and is the standard base c with quality q; disc: that base starts a one-base alternate allele; other_alt:
+    // the read starts an alternate allele of another shape (counted: it only matters if a sample has enough of them).
+    bool low_p = false;  // a tumor read on the reference base with P(correct) <= 1/2: the call bound below does not hold
+    auto accumulate = [&](int idx, int smp, int mapq, bool fwd, bool in_depth, bool has_sub, int c, int q, bool disc, bool other_alt) {
+      uint8_t meta = (uint8_t)(smp & 3);
+      double pq = 0.0, la = 0.0, lb = 0.0;
+#pragma unroll
+      for (int s = 0; s < SJF_SMAX; ++s) {
+        depth[s] += in_depth && smp == s;
+        ns_alt[s] += other_alt && smp == s;
+      }
+      if (!has_sub) mapq = 0;
+      if (mapq != 0) {  // mapq 0 contributes exactly 0.0 (PileupStats.scala:79-80)
+        pq = c_success_probability[q] * c_success_probability[mapq];
+        const double2 t = __ldg(A.log_table + ((mapq << 8) | q));
+        la = t.x;
+        lb = t.y;
+      }
+      const bool is_ref = has_sub && c == cr;
+      if (is_ref && mapq != 0 && pq <= 0.5 && ((kinds >> (2 * smp)) & 3u) != GUAC_SJ_NORMAL_DNA) low_p = true;
+      if (is_ref) {
+        if (mapq != 0) meta |= 4;
+        W.p[idx] = pq;
+#pragma unroll
+        for (int s = 0; s < SJF_SMAX; ++s)
+          if (smp == s) {
+            rcnt[s] += 1;
+            rfwd[s] += fwd;
+            rfirst[s] = min(rfirst[s], idx);
+            if (mapq != 0) {
+              rll[s] += 1;
+              rA[s] += la;
+              rB[s] += lb;
+            }
+          }
+      }
+      if (idx >= 0 && idx < n_span) W.meta[idx] = meta;
+      // the other subsequences go to the list (ballot compaction: the same order every run)
+      const unsigned om = __ballot_sync(FULL, has_sub && !is_ref);
+      if (om) {
+        const int pos = n_list + __popc(om & ((1u << lane) - 1u));
+        if (has_sub && !is_ref && pos < SJF_LIST) {
+          SJFListEntry e;
+          e.rel = (uint16_t)idx;
+          e.s = (uint8_t)smp;
+          e.c = (uint8_t)c;
+          e.flags = (uint8_t)((fwd ? 1 : 0) | (mapq != 0 ? 2 : 0) | (disc ? 4 : 0));
+          e.q = (uint8_t)q;
+          e.mapq = (uint8_t)mapq;
+          e._pad = 0;
+          W.list[pos] = e;
+        }
+        n_list += __popc(om);
+      }
+    };
+    // single-operator reads inline; the others are listed and walked by the exact cursor afterwards, all at once
+    // the header, mapq and flags of a read depend on its index alone: those of the next chunk are requested while this
+    // one is worked on
+    uint4 next_h = make_uint4(0, 0, 0, 0);
+    int next_mapq = 0, next_flags = 0;
+    if (lane < n_span && !bail) {
+      next_h = __ldg(A.hdr + tile.read_lo + lane);
+      next_mapq = (int)__ldg(R.mapq + tile.read_lo + lane);
+      next_flags = (int)__ldg(R.flags + tile.read_lo + lane);
+    }
     for (int base = 0; base < n_span && !bail; base += 32) {
       const int idx = base + lane;
       const int64_t r = tile.read_lo + idx;
-      bool in_depth = false, has_sub = false, disc = false, my_bail = false;
+      bool in_depth = false, has_sub = false, disc = false, other_alt = false, slow = false;
       int smp = 0, c = 0, q = 0;
-      uint8_t rf = 0;
+      const uint4 h = next_h;
+      const int mapq = next_mapq;
+      const bool fwd = (next_flags & GUAC_READ_POSITIVE_STRAND) != 0;
+      if (idx + 32 < n_span) {
+        next_h = __ldg(A.hdr + r + 32);
+        next_mapq = (int)__ldg(R.mapq + r + 32);
+        next_flags = (int)__ldg(R.flags + r + 32);
+      }
       if (idx < n_span) {
-        const uint4 h = __ldg(A.hdr + r);
         smp = (int)((h.y >> 16) & 0xFF);
-        rf = (uint8_t)(h.y >> 24);
+        const uint8_t rf = (uint8_t)(h.y >> 24);
         const int st = (int)(h.x - x_lo);  // start - x
         int span = (int)(h.y & 0xFFFF);
         if (span == 0xFFFF) span = (int)min((long long)(__ldg(R.end + r) - __ldg(R.start + r)), (1ll << 30));
@@ -441,101 +562,52 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
             c = base_at(p0 + 1);
             q = (int)__ldg(R.qual + s0 + p0 + 1);
             has_sub = true;
-            if (c != cr) {  // ofNextAltAllele: the run of variant elements from x + 1 must end at x + 2
-              disc = true;
-              if (p0 + 2 < span - 1 && "ACGT"[base_at(p0 + 2)] != (char)rb2) my_bail = true;
+            if (c != cr) {  // ofNextAltAllele: a one-base allele when the run of variant elements ends at x + 2
+              if (p0 + 2 < span - 1 && "ACGT"[base_at(p0 + 2)] != (char)rb2) other_alt = true;
+              else disc = true;
             }
           }
-        } else if (overlap) {  // the exact cursor
-          Elem e0;
-          const int ec = element_at(R, r, x, ref, e0);
-          if (ec != DERR_NONE) {
-            my_bail = true;  // the generic kernels report it
-          } else if (e0.kind != GUAC_ALN_CLIPPED) {  // Clipped elements are dropped first (:85-86)
-            in_depth = true;
-            SubSeq sa, sf;
-            const int fa = next_alt_allele(R, r, x, ref, e0, sa);
-            const int ff = fixed_length_subsequence(R, r, x, ref, e0, 1, sf);
-            if (fa < 0 || ff < 0) my_bail = true;
-            const uint64_t s0 = __ldg(R.seq_off + r);
-            if (ff > 0) {
-              const uint8_t b = sf.end_rp - sf.start_rp == 1 ? read_base(R, s0 + sf.start_rp) : (uint8_t)0;
-              c = base_code(b);
-              if (c == 4) {
-                my_bail = true;  // a subsequence that is not one standard base
-              } else {
-                has_sub = true;
-                q = (int)__ldg(R.qual + s0 + sf.start_rp);
-              }
-            }
-            if (fa > 0) {
-              disc = true;
-              // the alternate allele must be this very base over one locus
-              if (!(sa.end_locus - sa.start_locus == 1 && sa.end_rp - sa.start_rp == 1 && has_sub && sa.start_rp == sf.start_rp && c != cr))
-                my_bail = true;
-            }
-          }
+        } else if (overlap) {
+          slow = true;
         }
       }
-      if (__any_sync(FULL, my_bail)) {
-        bail = true;
-        break;
+      const unsigned sm = __ballot_sync(FULL, slow);
+      if (sm) {
+        const int pos = n_slow + __popc(sm & ((1u << lane) - 1u));
+        if (slow && pos < SJF_LIST) W.slow[pos] = (uint16_t)idx;
+        n_slow += __popc(sm);
       }
-      uint8_t meta = (uint8_t)(smp & 3);
-      double pq = 0.0, la = 0.0, lb = 0.0;
-      int mapq = 0;
+      accumulate(idx, smp, mapq, fwd, in_depth, has_sub, c, q, disc, other_alt);
+    }
+    if (n_slow > SJF_LIST) bail = true;
+    __syncwarp();
+    for (int base = 0; base < n_slow && !bail; base += 32) {  // the exact cursor, one lane per listed read
+      unsigned cls = 0;
+      int smp = 0, idx = -1, mapq = 0;
       bool fwd = false;
-      if (in_depth) {
-#pragma unroll
-        for (int s = 0; s < SJF_SMAX; ++s) depth[s] += smp == s;
-      }
-      if (has_sub) {
+      if (base + lane < n_slow) {
+        idx = W.slow[base + lane];
+        const int64_t r = tile.read_lo + idx;
+        smp = (int)__ldg(R.sample_id + r);
         mapq = (int)__ldg(R.mapq + r);
         fwd = (__ldg(R.flags + r) & GUAC_READ_POSITIVE_STRAND) != 0;
-        if (mapq != 0) {  // mapq 0 contributes exactly 0.0 (PileupStats.scala:79-80)
-          pq = c_success_probability[q] * c_success_probability[mapq];
-          la = log10(pq);
-          lb = log10(1.0 - pq);
-        }
+        cls = sjf_classify_slow(R, r, x, ref, cr);
       }
-      const bool is_ref = has_sub && c == cr;
-      if (is_ref) {
-        if (mapq != 0) meta |= 4;
-        W.p[idx] = pq;
+      if (__any_sync(FULL, (cls & 16u) != 0)) bail = true;
+      accumulate(idx, smp, mapq, fwd, (cls & 1u) != 0, (cls & 2u) != 0, (int)((cls >> 8) & 3u), (int)((cls >> 16) & 255u), (cls & 4u) != 0,
+                 (cls & 8u) != 0);
+    }
+    if (n_list > SJF_LIST) bail = true;
+    // alternate alleles of other shapes: harmless while no discovery sample has enough of them to keep one
+    // (AlleleAtLocus.scala:99-124 needs at least minReads equal ones)
+    if (!bail) {
 #pragma unroll
-        for (int s = 0; s < SJF_SMAX; ++s)
-          if (smp == s) {
-            rcnt[s] += 1;
-            rfwd[s] += fwd;
-            rfirst[s] = min(rfirst[s], idx);
-            if (mapq != 0) {
-              rll[s] += 1;
-              rA[s] += la;
-              rB[s] += lb;
-            }
-          }
-      }
-      if (idx < n_span) W.meta[idx] = meta;
-      // the other subsequences go to the list in read order (ballot compaction: the same order every run)
-      const unsigned om = __ballot_sync(FULL, has_sub && !is_ref);
-      if (om) {
-        const int pos = n_list + __popc(om & ((1u << lane) - 1u));
-        if (has_sub && !is_ref && pos < SJF_LIST) {
-          SJFListEntry e;
-          e.p = pq;
-          e.A = la;
-          e.B = lb;
-          e.rel = idx;
-          e.s = (uint8_t)smp;
-          e.c = (uint8_t)c;
-          e.flags = (uint8_t)((fwd ? 1 : 0) | (mapq != 0 ? 2 : 0) | (disc ? 4 : 0));
-          e._pad = 0;
-          W.list[pos] = e;
-        }
-        n_list += __popc(om);
-        if (n_list > SJF_LIST) bail = true;
+      for (int s = 0; s < SJF_SMAX; ++s) {
+        ns_alt[s] = __reduce_add_sync(FULL, ns_alt[s]);
+        if (((disc_mask >> s) & 1u) && ns_alt[s] >= max(1, P.min_reads)) bail = true;
       }
     }
+    low_p = __any_sync(FULL, low_p);
     if (bail) {  // not a simple site after all: the generic kernels take it
       if (lane == 0) {
         const int b = atomicAdd(A.n_bail, 1);
@@ -574,15 +646,16 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
             if (e.s != s || e.c != c) continue;
             c_cnt += 1;
             c_fwd += e.flags & 1;
-            c_first = min(c_first, e.rel);
+            c_first = min(c_first, (int)e.rel);
             if (e.flags & 2) {
+              const double2 ab = __ldg(A.log_table + (((int)e.mapq << 8) | e.q));
               c_ll += 1;
-              c_A += e.A;
-              c_B += e.B;
+              c_A += ab.x;
+              c_B += ab.y;
             }
             if (e.flags & 4) {
               c_disc += 1;
-              c_dfirst = min(c_dfirst, e.rel);
+              c_dfirst = min(c_dfirst, (int)e.rel);
             }
           }
         }
@@ -591,7 +664,6 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
     // AlleleAtLocus.variantAlleles (jointcaller/AlleleAtLocus.scala:85-149): per discovery sample, its alternate bases
     // by (count desc, first read asc), kept when count >= max(minReads, depth * percent / 100); union, distinct, capped
     int n_res = 0, res_c[4] = {-1, -1, -1, -1};
-    int tot_cnt[4] = {0, 0, 0, 0}, tot_first[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX};
     for (int di = 0; di < P.n_discovery; ++di) {
       const int smp = (int)((disc_order >> (4 * di)) & 15u);
       const int dep = pick4(depth[0], depth[1], depth[2], depth[3], smp);
@@ -601,8 +673,6 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       for (int c = 0; c < 4; ++c) {
         cnt[c] = __shfl_sync(FULL, c_disc, 4 * smp + c);
         first[c] = __shfl_sync(FULL, c_dfirst, 4 * smp + c);
-        tot_cnt[c] += cnt[c];
-        tot_first[c] = min(tot_first[c], first[c]);
       }
       for (int round = 0; round < 3; ++round) {
         int best = -1;
@@ -618,48 +688,7 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
         cnt[best] = 0;
       }
     }
-    if (n_res == 0 && forced) {  // atLeastOneAllele (:126-141): the best supported allele overall, or ref > N
-      int best = -1;
-#pragma unroll
-      for (int c = 0; c < 4; ++c)
-        if (tot_cnt[c] > 0 && (best < 0 || tot_cnt[c] > tot_cnt[best] || (tot_cnt[c] == tot_cnt[best] && tot_first[c] < tot_first[best])))
-          best = c;
-      res_c[0] = best;  // -1: the placeholder
-      n_res = 1;
-    }
     if (n_res == 0) continue;
-    int site_idx = 0, job0 = 0;
-    if (lane == 0) {
-      site_idx = atomicAdd(A.n_sites, 1);
-      job0 = atomicAdd(A.n_jobs, n_res);
-    }
-    site_idx = __shfl_sync(FULL, site_idx, 0);
-    job0 = __shfl_sync(FULL, job0, 0);
-    if (site_idx >= A.max_sites || job0 + n_res > A.max_jobs) continue;  // the host sees the counters and reruns with room
-    if (lane == 0) {
-      SJSiteDev& st = A.sites[site_idx];
-      st.slot = tile.slot0;
-      st.locus = x;
-      st.read_lo = tile.read_lo;
-      st.read_hi = tile.read_hi;
-      st.contig_id = tile.contig_id;
-      st.ref_index = tile.ref_index;
-      st.n_alleles = n_res;
-      st.forced = forced ? 1 : 0;
-      st.first_job = job0;
-      st._pad = 0;
-      for (int k = 0; k < SJ_MAX_ALLELES; ++k) {
-        SJAlleleDev a;
-        const int c = k < n_res ? res_c[k & 3] : -1;
-        a.key = (k < n_res && c >= 0) ? ((1ull << 61) | (1ull << 54) | (uint64_t)c) : 0;  // seq_key of one standard base
-        a.rep_read = -1;  // its string is the single character in rep_start_rp
-        a.span = k < n_res ? 1 : 0;
-        a.alt_len = k < n_res ? 1 : 0;
-        a.rep_start_rp = c >= 0 ? (int)"ACGT"[c] : (int)'N';
-        a._pad = 0;
-        st.alleles[k] = a;
-      }
-    }
     // per evidence slot (lane i < S + 2: sample i, pooled normal DNA, pooled tumor DNA): the member samples' cells
     const int my_kind = lane < S ? (int)((kinds >> (2 * lane)) & 3u) : lane == NP ? (int)GUAC_SJ_NORMAL_DNA : (int)GUAC_SJ_TUMOR_DNA;
     int g_depth = 0, g_cnt[4], g_fwd[4], g_first[4], g_ll[4];
@@ -690,13 +719,69 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       }
     }
     const int n_sub = g_cnt[0] + g_cnt[1] + g_cnt[2] + g_cnt[3], f_sub = g_fwd[0] + g_fwd[1] + g_fwd[2] + g_fwd[3];
-    for (int a = 0; a < n_res; ++a) {
-      const int ca = res_c[a];  // -1: placeholder, equal to no subsequence
-      const int alt_cnt = ca < 0 ? 0 : pick4(g_cnt[0], g_cnt[1], g_cnt[2], g_cnt[3], ca);
-      const int alt_fwd = ca < 0 ? 0 : pick4(g_fwd[0], g_fwd[1], g_fwd[2], g_fwd[3], ca);
-      const int alt_ll = ca < 0 ? 0 : pick4(g_ll[0], g_ll[1], g_ll[2], g_ll[3], ca);
+    // One allele: every slot's likelihoods, then the call logic across the slots
+    // (MultiSampleSingleAlleleEvidence.scala:66-230).  write: the raw record for the posterior / final kernels.
+    auto eval_allele = [&](int a, bool write, int site_idx, int job0) -> bool {
+      const int ca = res_c[a];
+      const int alt_cnt = pick4(g_cnt[0], g_cnt[1], g_cnt[2], g_cnt[3], ca);
+      const int alt_fwd = pick4(g_fwd[0], g_fwd[1], g_fwd[2], g_fwd[3], ca);
+      const int alt_ll = pick4(g_ll[0], g_ll[1], g_ll[2], g_ll[3], ca);
       // alt fraction of a tumor mixture (TumorDNASingleSampleSingleAlleleEvidence.scala:38)
       const double my_vaf = fmax(P.vaf_floor, (double)alt_cnt / (double)g_depth);
+      // likelihoods of this lane's slot that need no per-read pass (PileupStats.logLikelihoodPileup :77-91 per mixture)
+      double other_B = 0.0, nonref_B = 0.0, nonalt_B = 0.0;  // sums of log10(1 - p) over base classes
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (c != cr) nonref_B += g_B[c];
+        if (c != ca) nonalt_B += g_B[c];
+        if (c != cr && c != ca) other_B += g_B[c];
+      }
+      const double ref_A = pick4(g_A[0], g_A[1], g_A[2], g_A[3], cr);
+      const double alt_A = pick4(g_A[0], g_A[1], g_A[2], g_A[3], ca);
+      const int ref_ll = pick4(g_ll[0], g_ll[1], g_ll[2], g_ll[3], cr);
+      const double ll0 = ref_A + nonref_B;                                   // {ref: 1}
+      double ll1 = (double)(ref_ll + alt_ll) * LOG10_HALF + other_B;         // normal DNA: {ref: 0.5, alt: 0.5}
+      const double ll2 = my_kind == GUAC_SJ_NORMAL_DNA ? alt_A + nonalt_B : 0.0;  // normal DNA: {alt: 1}
+      // germline genotype from the pooled normal posteriors (maxBy keeps the first maximum)
+      int germline = 0;
+      {
+        const double p0 = ll0, p1 = ll1 - EP.germline_neg_log10_het_prior, p2 = ll2 - EP.germline_neg_log10_hom_alt_prior;
+        int g = 0;
+        double best = p0;
+        if (p1 > best) {
+          best = p1;
+          g = 1;
+        }
+        if (p2 > best) g = 2;
+        germline = __shfl_sync(FULL, g, NP);
+      }
+      // the alternate base's reads of this slot's tumor mixture, from the list in list order
+      double alt_terms = 0.0, alt_B = 0.0, rest_B = 0.0;  // their mixture terms, their log10(1 - p), the other bases' log10(1 - p)
+      if (lane < S + 2 && my_kind != GUAC_SJ_NORMAL_DNA)
+        for (int k = 0; k < n_list; ++k) {
+          const SJFListEntry& e = W.list[k];
+          if (!(e.flags & 2)) continue;
+          const int sk = (int)((kinds >> (2 * e.s)) & 3u);
+          if (lane < S ? e.s != lane : sk != GUAC_SJ_TUMOR_DNA) continue;
+          const double eB = __ldg(A.log_table + (((int)e.mapq << 8) | e.q)).y;
+          if ((int)e.c == ca) {
+            const double ep = c_success_probability[e.q] * c_success_probability[e.mapq];
+            alt_terms += log10(my_vaf * ep + (1.0 - my_vaf) * (1.0 - ep));
+            alt_B += eB;
+          } else {
+            rest_B += eB;
+          }
+        }
+      // Before the pass over the reference-base reads: a reference-base read with P(correct) > 1/2 can only lower
+      // {alt: vaf, ref: 1 - vaf} against {ref: 1}, so the alternate reads' terms alone bound a tumor mixture's gain.
+      // No germline call and no tumor mixture that can win against its prior: the allele is not called
+      // (MultiSampleSingleAlleleEvidence.scala:120-123,220-230) and that pass is not needed.  (With RNA samples the
+      // DNA prior depends on their posteriors: no shortcut.)
+      if (!write && !low_p && !has_rna && germline == 0) {
+        const bool can_win = lane < S + 2 && lane != NP && my_kind == GUAC_SJ_TUMOR_DNA &&
+                             !((alt_terms - alt_B) - EP.somatic_neg_log10_variant_prior < -1e-6);
+        if (!__any_sync(FULL, can_win)) return false;
+      }
       // {alt: vaf, ref: 1 - vaf} over the reads whose subsequence is the reference base, from the stash
       double v[SJF_SMAX];
 #pragma unroll
@@ -719,33 +804,19 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
 #pragma unroll
       for (int s = 0; s < SJF_SMAX; ++s) acc[s] = warp_sum_fixed(acc[s]);
       acc_p = warp_sum_fixed(acc_p);
-      if (lane >= S + 2) continue;
-      // likelihoods of this slot (PileupStats.logLikelihoodPileup :77-91 per mixture)
-      double other_B = 0.0, nonref_B = 0.0, nonalt_B = 0.0;  // sums of log10(1 - p) over base classes
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        if (c != cr) nonref_B += g_B[c];
-        if (c != ca) nonalt_B += g_B[c];
-        if (c != cr && c != ca) other_B += g_B[c];
-      }
-      const double ref_A = pick4(g_A[0], g_A[1], g_A[2], g_A[3], cr);
-      const double alt_A = ca < 0 ? 0.0 : pick4(g_A[0], g_A[1], g_A[2], g_A[3], ca);
-      const int ref_ll = pick4(g_ll[0], g_ll[1], g_ll[2], g_ll[3], cr);
-      double ll0 = ref_A + nonref_B, ll1, ll2 = 0.0;
-      if (my_kind == GUAC_SJ_NORMAL_DNA) {
-        ll1 = (double)(ref_ll + alt_ll) * LOG10_HALF + other_B;  // {ref: 0.5, alt: 0.5}
-        ll2 = alt_A + nonalt_B;                                    // {alt: 1}
-      } else {
-        // reference-base reads from the stash; the alternate base's reads and the others from the list, in read order
-        ll1 = lane == TP ? acc_p : pick4(acc[0], acc[1], acc[2], acc[3], lane);
-        for (int k = 0; k < n_list; ++k) {
-          const SJFListEntry& e = W.list[k];
-          if (!(e.flags & 2)) continue;
-          const int sk = (int)((kinds >> (2 * e.s)) & 3u);
-          if (lane < S ? e.s != lane : sk != GUAC_SJ_TUMOR_DNA) continue;
-          ll1 += (int)e.c == ca ? log10(my_vaf * e.p + (1.0 - my_vaf) * (1.0 - e.p)) : e.B;
-        }
-      }
+      if (my_kind != GUAC_SJ_NORMAL_DNA)  // reference-base reads from the stash; the alternate base's reads and the others from the list
+        ll1 = (lane == TP ? acc_p : pick4(acc[0], acc[1], acc[2], acc[3], lane)) + (alt_terms + rest_B);
+      auto mixture_triggers = [&](double variant_prior) {
+        const bool has_alt = my_vaf > 0, has_ref = 1.0 - my_vaf > 0;
+        const double prior1 = has_ref && !has_alt ? 0.0 : has_ref && has_alt ? variant_prior : 1.7976931348623157e308;
+        const int best = (ll1 - prior1) > ll0 ? 1 : 0;
+        return best == 0 ? germline != 0 : germline != 1;
+      };
+      const bool rna = __any_sync(FULL, lane < S && my_kind == GUAC_SJ_TUMOR_RNA && mixture_triggers(EP.somatic_neg_log10_variant_prior_rna));
+      const double dna_prior = rna ? EP.somatic_neg_log10_variant_prior_with_rna_evidence : EP.somatic_neg_log10_variant_prior;
+      const bool trig = __any_sync(FULL, lane < S + 2 && lane != NP && my_kind == GUAC_SJ_TUMOR_DNA && mixture_triggers(dna_prior));
+      const bool is_call = germline != 0 || trig;
+      if (!write || lane >= S + 2) return is_call;
       SJEvidenceDev* E = reinterpret_cast<SJEvidenceDev*>(A.raw + (size_t)(job0 + a) * A.raw_stride);
       if (lane == 0) {
         E->site = site_idx;
@@ -783,7 +854,46 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
         cnt[best] = 0;
       }
       o.n_depths = nd;
+      return is_call;
+    };
+    // A site none of whose alleles is called is never emitted (MultiSampleMultiAlleleEvidence.scala:149-155; force-called
+    // sites are not here): it ends here, without a record.  Most candidate sites do.
+    bool any_call = false;
+    for (int a = 0; a < n_res; ++a) any_call = eval_allele(a, false, 0, 0) || any_call;
+    if (!any_call) continue;
+    int site_idx = 0, job0 = 0;
+    if (lane == 0) {
+      site_idx = atomicAdd(A.n_sites, 1);
+      job0 = atomicAdd(A.n_jobs, n_res);
     }
+    site_idx = __shfl_sync(FULL, site_idx, 0);
+    job0 = __shfl_sync(FULL, job0, 0);
+    if (site_idx >= A.max_sites || job0 + n_res > A.max_jobs) continue;  // the host sees the counters and reruns with room
+    if (lane == 0) {
+      SJSiteDev& st = A.sites[site_idx];
+      st.slot = tile.slot0;
+      st.locus = x;
+      st.read_lo = tile.read_lo;
+      st.read_hi = tile.read_hi;
+      st.contig_id = tile.contig_id;
+      st.ref_index = tile.ref_index;
+      st.n_alleles = n_res;
+      st.forced = 0;
+      st.first_job = job0;
+      st._pad = 0;
+      for (int k = 0; k < SJ_MAX_ALLELES; ++k) {
+        SJAlleleDev al;
+        const int c = k < n_res ? res_c[k & 3] : 0;
+        al.key = k < n_res ? ((1ull << 61) | (1ull << 54) | (uint64_t)c) : 0;  // seq_key of one standard base
+        al.rep_read = -1;  // its string is the single character in rep_start_rp
+        al.span = k < n_res ? 1 : 0;
+        al.alt_len = k < n_res ? 1 : 0;
+        al.rep_start_rp = (int)"ACGT"[c];
+        al._pad = 0;
+        st.alleles[k] = al;
+      }
+    }
+    for (int a = 0; a < n_res; ++a) eval_allele(a, true, site_idx, job0);
   }
 }
 

@@ -27,6 +27,9 @@
 #ifndef GUAC_TK_MINB
 #define GUAC_TK_MINB 7
 #endif
+#ifndef GUAC_TK_MINB_JOINT
+#define GUAC_TK_MINB_JOINT 5  // MODE 2 carries the call bound's FP64 arithmetic: more registers, fewer resident CTAs
+#endif
 #ifndef GUAC_TK_TL
 #define GUAC_TK_TL 512  // loci per tile
 #endif
@@ -54,7 +57,8 @@ struct TileCfg {
 enum : uint8_t {
   RF_FAST = 1,    // single M/=/X operator, ACGT only
   RF_HIQ = 2,     // every base quality >= 4, i.e. P(correct) >= 0.60 > 1/2 (licenses the LOD bound)
-  RF_MEDIUM = 4   // operators within {M,=,X,I,D,S,H}, ACGT only, CIGAR consistent with the sequence
+  RF_MEDIUM = 4,  // operators within {M,=,X,I,D,S,H}, ACGT only, CIGAR consistent with the sequence
+  RF_MAPQ_OK = 8  // mapq is 0 (the joint model ignores the read) or >= 8: with RF_HIQ, P(quality) P(mapq) > 1/2 at every base
 };
 static_assert(RF_MEDIUM == 4, "ss_evidence_kernel (kernels.cuh) tests this bit of the packed header");
 
@@ -97,7 +101,8 @@ __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags
       if ((t - 0x01010101u) & ~t & 0x80808080u) hiq = false;
     }
   }
-  rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0) | (medium ? RF_MEDIUM : 0);
+  const int mapq = R.mapq[r];
+  rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0) | (medium ? RF_MEDIUM : 0) | ((mapq == 0 || mapq >= 8) ? RF_MAPQ_OK : 0);
 }
 
 
@@ -140,14 +145,16 @@ __device__ __forceinline__ int base_code(uint8_t b) { return b == 'A' ? 0 : b ==
 template <class CFG>
 struct TileSmem {
   uint32_t ref2[((CFG::TL + CFG::THREADS - 1) / CFG::THREADS) * (CFG::THREADS / 16) + 2];  // whole passes of the loader + read-ahead
-  int cov[CFG::TL + 1];     // packed differences: normal | tumor << 16  -> depths after the scan
-  int aux[CFG::TL + 1];     // low-quality tumor read differences | event count << 16 -> lowq | event end offset
+  int cov[CFG::TL + 2];     // packed differences: normal | tumor << 16  -> depths after the scan (MODE 2: samples 0 | 1 << 16)
+  int aux[CFG::TL + 2];     // low-quality tumor read differences | event count << 16 -> lowq | event end offset
+  int cov2[CFG::TL + 2];    // MODE 2 with at most four samples: samples 2 | 3 << 16
   int nonref[CFG::TL + 1];  // non-Match elements: normal | tumor << 16 (MODE 2 also keeps the locus behind the tile)
   int cursor[CFG::TL + 1];
   uint2 ev[CFG::E_MAX];
   uint16_t ev_order[CFG::E_MAX];  // event indices bucketed by locus (2 B per event instead of a second copy)
   uint16_t slow[CFG::SLOW_MAX];
   int warp_tot[2][CFG::WARPS];
+  int warp_tot2[CFG::WARPS];
   int n_events, n_slow, overflow, ref_has_mask, n_cand;
 };
 
@@ -177,7 +184,50 @@ struct TileArgs {
   Tile* simple;
   int* n_simple;
   int max_simple;
+  // ... and simple sites that certainly hold no call are dropped in the tile (see `prune` in MODE 2 below)
+  int prune;
+  unsigned kinds;                 // GUAC_SJ_* of sample s in bits [2 s, 2 s + 2)
+  double het_prior, hom_prior, somatic_prior, vaf_floor;
+  const double2* log_table;       // (log10 p, log10 (1 - p)) by (mapq << 8 | quality), sj_log_table_kernel
 };
+
+// MODE 2, at most four samples: the discovery samples' events of one locus in one pass.  hist[s] holds, 16 bits per
+// standard base, how many reads of sample s have that substitution there.  Returns the largest number of equal
+// allele-starting elements in one sample (indel anchors of a sample counted together: an upper bound); `simple`: no
+// read of any sample has an insertion or a non-standard base there and no sample has min_reads indel anchors — every
+// allele that can start there is a one-base substitution.  An allele needs min_reads equal elements in ONE discovery
+// sample (jointcaller/AlleleAtLocus.scala:99-124); inside a deletion or an N skip the read's element one locus before
+// is a variant or Clipped, so those events start nothing.
+template <class SM>
+__device__ inline int sj_scan_events(const SM& S, int l1, int min_reads, unsigned long long (&hist)[4], bool& simple) {
+  const int nr1 = S.nonref[l1], e1 = S.aux[l1] >> 16, e0 = e1 - ((nr1 & 0xFFFF) + (nr1 >> 16));
+  hist[0] = hist[1] = hist[2] = hist[3] = 0ull;
+  unsigned indel = 0;  // 8 bits per sample (saturating)
+  simple = true;
+  for (int i = e0; i < e1; ++i) {
+    const uint2 ev = S.ev[S.ev_order[i]];
+    const int kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7, smp = (int)(ev.x >> 30);
+    if (kind == GUAC_ALN_INSERTION || (kind == GUAC_ALN_MISMATCH && code >= 4)) simple = false;
+    if (kind == GUAC_ALN_MID_DELETION || kind == GUAC_ALN_CLIPPED) continue;
+    if (((ev.x >> 23) & 1) != 1) continue;  // not a discovery sample
+    if (kind == GUAC_ALN_MISMATCH && code < 4) {
+      const unsigned long long f = (hist[smp] >> (16 * code)) & 0xFFFFull;
+      if (f < 0xFFFFull) hist[smp] += 1ull << (16 * code);
+    } else if (((indel >> (8 * smp)) & 0xFFu) < 0xFFu) {
+      indel += 1u << (8 * smp);
+    }
+  }
+  int best = 0;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) best = max(best, (int)((hist[s] >> (16 * c)) & 0xFFFFull));
+    const int n_indel = (int)((indel >> (8 * s)) & 0xFFu);
+    if (n_indel >= min_reads) simple = false;
+    best = max(best, n_indel);
+  }
+  return best;
+}
 
 // MODE 0: somatic-standard (two samples).  MODE 1: germline toy caller's dense half — one sample (the "tumor"
 // slot; normal_sample = -1), a locus is heavy when depth - referenceDepth >= P.min_alt_reads
@@ -187,7 +237,7 @@ struct TileArgs {
 // jointcaller/pileup_summarization/ReadSubsequence.scala:106-135), when x + 1 is force-called, or when x + 1 lies
 // in the next tile.
 template <class CFG, int MODE, bool STREAM = false>
-__global__ void __launch_bounds__(CFG::THREADS, GUAC_TK_MINB)
+__global__ void __launch_bounds__(CFG::THREADS, (MODE == 2 ? GUAC_TK_MINB_JOINT : GUAC_TK_MINB))
 ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TileSmem<CFG>& S = *reinterpret_cast<TileSmem<CFG>*>(smem_raw);
@@ -228,7 +278,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
 #endif
 
   // ---- init ------------------------------------------------------------------------------
-  for (int i = tid; i < TL + 1; i += CFG::THREADS) S.cov[i] = S.aux[i] = 0;
+  for (int i = tid; i < TL + 2; i += CFG::THREADS) S.cov[i] = S.aux[i] = S.cov2[i] = 0;
   for (int i = tid; i < TL + 1; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
   if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = 0;
   if (tid < 4) {  // padding words behind the tile
@@ -309,12 +359,25 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     if ((hdr.y & 0xFFFF) == 0xFFFF) en = (int)min((long long)(__ldg(R.end + r) - t0), (1ll << 30));  // a span beyond 16 bits
     const int a = max(st, 0), b = min(en, n_loci);  // overlap [a, b) in tile coordinates
     if (a >= b) continue;
-    const int one = slot ? 65536 : 1;
-    atomicAdd(&S.cov[a], one);
-    atomicAdd(&S.cov[b], -one);
-    if (slot == 1 && !(rf & RF_HIQ)) {
-      atomicAdd(&S.aux[a], 1);
-      atomicAdd(&S.aux[b], -1);
+    if (MODE == 2 && A.sample_bits) {
+      // per-sample depths, kept one locus behind the tile like the events; reads that can have P(correct) <= 1/2 somewhere
+      const int bc = min(en, n_ev_loci);
+      int* arr = (smp & 2) ? S.cov2 : S.cov;
+      const int one = (smp & 1) ? 65536 : 1;
+      atomicAdd(&arr[a], one);
+      atomicAdd(&arr[bc], -one);
+      if ((rf & (RF_HIQ | RF_MAPQ_OK)) != (RF_HIQ | RF_MAPQ_OK)) {
+        atomicAdd(&S.aux[a], 1);
+        atomicAdd(&S.aux[bc], -1);
+      }
+    } else {
+      const int one = slot ? 65536 : 1;
+      atomicAdd(&S.cov[a], one);
+      atomicAdd(&S.cov[b], -one);
+      if (slot == 1 && !(rf & RF_HIQ)) {
+        atomicAdd(&S.aux[a], 1);
+        atomicAdd(&S.aux[b], -1);
+      }
     }
     if (!(rf & RF_MEDIUM)) {
       const int i = atomicAdd(&S.n_slow, 1);
@@ -470,8 +533,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   // ---- B. one scan over both packed arrays ----------------------------------------------------
   {
     constexpr int PER = (TL + CFG::THREADS) / CFG::THREADS;  // covers TL + 1 entries
-    const int b0 = tid * PER, e0 = min(n_loci + 1, b0 + PER);
-    int s_cov = 0, s_aux = 0;
+    const int b0 = tid * PER, e0 = min(n_ev_loci + 1, b0 + PER);
+    int s_cov = 0, s_aux = 0, s_cov2 = 0;
     for (int i = b0; i < e0; ++i) {
       if (i < n_ev_loci) {  // add the locus's event count to the high half of aux
         const int nr = S.nonref[i];
@@ -479,19 +542,23 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       }
       s_cov += S.cov[i];
       s_aux += S.aux[i];
+      if (MODE == 2) s_cov2 += S.cov2[i];
     }
-    int i_cov = s_cov, i_aux = s_aux;
+    int i_cov = s_cov, i_aux = s_aux, i_cov2 = s_cov2;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const int oc = __shfl_up_sync(FULL, i_cov, d), oa = __shfl_up_sync(FULL, i_aux, d);
+      const int o2 = MODE == 2 ? __shfl_up_sync(FULL, i_cov2, d) : 0;
       if (lane >= d) {
         i_cov += oc;
         i_aux += oa;
+        i_cov2 += o2;
       }
     }
     if (lane == 31) {
       S.warp_tot[0][warp] = i_cov;
       S.warp_tot[1][warp] = i_aux;
+      if (MODE == 2) S.warp_tot2[warp] = i_cov2;
     }
     __syncthreads();
     // totals of the warps before this one: lane w holds warp w's, one warp-wide add each
@@ -499,12 +566,17 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const bool before = lane < warp;  // (warp < WARPS)
     const int c_cov = __reduce_add_sync(FULL, before ? S.warp_tot[0][lane] : 0);
     const int c_aux = __reduce_add_sync(FULL, before ? S.warp_tot[1][lane] : 0);
-    int r_cov = c_cov + i_cov - s_cov, r_aux = c_aux + i_aux - s_aux;
+    const int c_cov2 = MODE == 2 ? __reduce_add_sync(FULL, before ? S.warp_tot2[lane] : 0) : 0;
+    int r_cov = c_cov + i_cov - s_cov, r_aux = c_aux + i_aux - s_aux, r_cov2 = c_cov2 + i_cov2 - s_cov2;
     for (int i = b0; i < e0; ++i) {
       r_cov += S.cov[i];
       r_aux += S.aux[i];
       S.cov[i] = r_cov;
       S.aux[i] = r_aux;
+      if (MODE == 2) {
+        r_cov2 += S.cov2[i];
+        S.cov2[i] = r_cov2;
+      }
     }
     __syncthreads();
   }
@@ -526,8 +598,9 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const int dN = cv & 0xFFFF, dT = cv >> 16;
     const int nrN = nr & 0xFFFF, nrT = nr >> 16;
     const int64_t slot = tile.slot0 + l, x = t0 + l;
-    A.visited[slot] = dN + dT > 0 ? 1 : 0;
-    my_visited += dN + dT > 0;
+    const bool any_depth = (MODE == 2 && A.sample_bits) ? (cv | S.cov2[l]) != 0 : dN + dT > 0;
+    A.visited[slot] = any_depth ? 1 : 0;
+    my_visited += any_depth;
     // (a tile with a missing reference base never gets here: it went to the generic kernel, which reports the error)
     bool candidate, simple_site = false;
     if (MODE == 0) {  // early-outs (SomaticStandardCaller.scala:164-172)
@@ -536,7 +609,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       candidate = dT > 0 && nrT >= P.min_alt_reads;
     } else {
       candidate = false;
-      if (dN + dT > 0) {
+      if (any_depth) {
         // reference.getReferenceBase(contig, locus + 1) (jointcaller/evidence/MultiSampleMultiAlleleEvidence.scala:93)
         if (ref.at(x + 1) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x + 1, -1);
         if (l + 1 >= n_ev_loci) {
@@ -544,34 +617,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         } else if ((S.nonref[l + 1] >> 16) >= P.min_alt_reads) {
           candidate = true;
           if (A.sample_bits) {
-            // An allele needs min_alt_reads reads of ONE discovery sample whose elements at x + 1 are the same non-Match
-            // element (AlleleAtLocus.scala:99-124 can keep nothing less).  The site is simple when every such element
-            // is a substitution by a standard base: the fast site kernel then decides it exactly.
-            const int nr1 = S.nonref[l + 1];
-            const int e1 = S.aux[l + 1] >> 16, e0 = e1 - ((nr1 & 0xFFFF) + (nr1 >> 16));
-            if (e1 - e0 <= CFG::EV_SIMPLE) {
-              auto skey = [&](uint2 ev) {
-                const int kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7;
-                return (ev.x >> 30 << 16) | ((uint32_t)kind << 8) |
-                       (uint32_t)(kind == GUAC_ALN_MISMATCH ? code : (kind == GUAC_ALN_MID_DELETION ? 0 : (int)((ev.y >> 8) & 0xFF)));
-              };
-              simple_site = true;
-              int best = 0;
-              for (int i = e0; i < e1; ++i) {
-                const uint2 ev = S.ev[S.ev_order[i]];
-                if (((ev.x >> 23) & 1) != 1) continue;  // not a discovery sample
-                const int kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7;
-                if (!(kind == GUAC_ALN_MISMATCH && code < 4)) simple_site = false;
-                const uint32_t k = skey(ev);
-                int c = 0;
-                for (int j = e0; j < e1; ++j) {
-                  const uint2 ej = S.ev[S.ev_order[j]];
-                  c += ((ej.x >> 23) & 1) == 1 && skey(ej) == k;
-                }
-                best = max(best, c);
-              }
-              candidate = best >= P.min_alt_reads;
-            }
+            unsigned long long hist[4];
+            candidate = sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site) >= P.min_alt_reads;
           }
         }
         for (int i = 0; i < A.n_force; ++i)
@@ -579,6 +626,10 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
             candidate = true;  // force-called: always evaluated, by the generic kernels
             simple_site = false;
           }
+      }
+      if (candidate && simple_site && A.prune) {  // examined in the second pass below, with full warps
+        S.cursor[atomicAdd(&S.n_cand, 1)] = l;
+        continue;
       }
     }
     int flags = 0;
@@ -615,6 +666,129 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   }
   my_visited = __reduce_add_sync(FULL, my_visited);
   if (lane == 0 && my_visited) atomicAdd(A.n_visited, (unsigned long long)my_visited);
+  if (MODE == 2 && A.prune) {
+    // prune: a simple site is listed for the site kernel only if one of its possible alleles can be called.  With every
+    // read over x + 1 at P(correct) > 1/2 (no flagged read there), a read on the reference base can only lower a
+    // het / hom-alt genotype or a tumor mixture against the reference one (its term is log10(1/2) - log10 p,
+    // log10((1 - p) / p) or log10(((1 - v) p + v (1 - p)) / p): all <= 0), reads on other bases add exactly 0, and the
+    // alternate reads' terms — exact, from their qualities — bound every posterior gain
+    // (MultiSampleSingleAlleleEvidence.scala:66-230).  v is bounded above with the event count over the depth.
+    __syncthreads();
+    const int n_cand = S.n_cand;
+    const double LOG10_HALF = -0.3010299956639812;
+    // One warp per candidate, one lane per event of x + 1: the loads of the alternate reads' mapq and quality and their
+    // logarithms run side by side; the sums are combined by fixed butterflies.
+    for (int ci = warp; ci < n_cand; ci += CFG::WARPS) {
+      const int l = S.cursor[ci];
+      unsigned long long hist[4];
+      bool simple_site;
+      sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site);  // (every lane: the counts are needed by all)
+      bool keep = (S.aux[l + 1] & 0xFFFF) != 0;  // a read that may have P(correct) <= 1/2 covers x + 1
+      {
+        // Clipped elements at x leave the depths (MultiSampleMultiAlleleEvidence.scala:85-86): rare, no shortcut
+        const int nr0 = S.nonref[l], f1 = S.aux[l] >> 16, f0 = f1 - ((nr0 & 0xFFFF) + (nr0 >> 16));
+        for (int i = f0; i < f1; ++i) keep = keep || ((S.ev[S.ev_order[i]].x >> 24) & 7) == GUAC_ALN_CLIPPED;
+      }
+      const int cv = S.cov[l], cv2 = S.cov2[l];
+      const int d0 = cv & 0xFFFF, d1 = cv >> 16, d2 = cv2 & 0xFFFF, d3 = cv2 >> 16;
+      const int nr1 = S.nonref[l + 1], e1 = S.aux[l + 1] >> 16, e0 = e1 - ((nr1 & 0xFFFF) + (nr1 >> 16));
+      auto tumor = [&](int s) { return ((A.kinds >> (2 * s)) & 3u) == GUAC_SJ_TUMOR_DNA; };
+      const int dp = (tumor(0) ? d0 : 0) + (tumor(1) ? d1 : 0) + (tumor(2) ? d2 : 0) + (tumor(3) ? d3 : 0);
+      if (!keep) {
+        // per-lane terms of its events, by allele base; a quality / mapq pair is fetched once per event
+        double het[4] = {0, 0, 0, 0}, hom[4] = {0, 0, 0, 0}, tp[4] = {0, 0, 0, 0};  // index = base
+        double tm0[4] = {0, 0, 0, 0}, tm1[4] = {0, 0, 0, 0}, tm2[4] = {0, 0, 0, 0}, tm3[4] = {0, 0, 0, 0};  // tumor sample 0..3
+        bool low = false;
+        for (int i = e0 + lane; i < e1; i += 32) {
+          const uint2 ev = S.ev[S.ev_order[i]];
+          const int c = (int)((ev.x >> 27) & 7);
+          if (((ev.x >> 24) & 7) != GUAC_ALN_MISMATCH || c >= 4) continue;
+          const int smp = (int)(ev.x >> 30), rl = (int)((ev.x >> 11) & 0xFFF);
+          {
+            // The bound is about one-base alleles.  A read whose next element is not a Match either starts a longer
+            // allele (ReadSubsequence.scala:117-121), and with it come multi-base subsequences: the site kernel's case.
+            // So is a read the exact cursor walked (an N skip after x + 1 leaves no event), and the tile's last site,
+            // whose locus x + 2 lies outside the kept events.
+            bool longer = l + 2 >= n_ev_loci || !((__ldg(A.hdr + tile.read_lo + rl).y >> 24) & RF_MEDIUM);
+            if (!longer) {
+              const int nr2 = S.nonref[l + 2], g1 = S.aux[l + 2] >> 16, g0 = g1 - ((nr2 & 0xFFFF) + (nr2 >> 16));
+              for (int j = g0; j < g1; ++j) longer = longer || (int)((S.ev[S.ev_order[j]].x >> 11) & 0xFFF) == rl;
+            }
+            if (longer) {
+              low = true;
+              continue;
+            }
+          }
+          const int mapq = (int)__ldg(R.mapq + tile.read_lo + rl);
+          if (mapq == 0) continue;  // contributes exactly 0.0 (PileupStats.scala:79-80)
+          const int q = (ev.y >> 31) ? (int)(ev.y & 0xFF) : (int)__ldg(R.qual + seq_base + ev.y);
+          const double p = c_success_probability[q] * c_success_probability[mapq];
+          if (!(p > 0.5)) {
+            low = true;
+            continue;
+          }
+          const double2 ab = __ldg(A.log_table + ((mapq << 8) | q));
+          if (((A.kinds >> (2 * smp)) & 3u) == GUAC_SJ_NORMAL_DNA) {
+            const double h1 = fmax(0.0, LOG10_HALF - ab.y), h2 = fmax(0.0, ab.x - ab.y);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              het[k] += c == k ? h1 : 0.0;
+              hom[k] += c == k ? h2 : 0.0;
+            }
+          } else if (((A.kinds >> (2 * smp)) & 3u) == GUAC_SJ_TUMOR_DNA) {
+            // alt fraction bounded above by (events of this base in the sample) / depth, at most 1
+            const int ks = (int)((hist[smp] >> (16 * c)) & 0xFFFF);
+            const int ds = smp == 0 ? d0 : smp == 1 ? d1 : smp == 2 ? d2 : d3;
+            int kp = 0;
+#pragma unroll
+            for (int s2 = 0; s2 < 4; ++s2) kp += tumor(s2) ? (int)((hist[s2] >> (16 * c)) & 0xFFFF) : 0;
+            const double v = fmin(1.0, fmax(A.vaf_floor, (double)ks / ds)), vp = fmin(1.0, fmax(A.vaf_floor, (double)kp / dp));
+            const double t = fmax(0.0, log10(v * p + (1.0 - v) * (1.0 - p)) - ab.y);
+            const double u = fmax(0.0, log10(vp * p + (1.0 - vp) * (1.0 - p)) - ab.y);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              tm0[k] += (c == k && smp == 0) ? t : 0.0;
+              tm1[k] += (c == k && smp == 1) ? t : 0.0;
+              tm2[k] += (c == k && smp == 2) ? t : 0.0;
+              tm3[k] += (c == k && smp == 3) ? t : 0.0;
+              tp[k] += c == k ? u : 0.0;
+            }
+          }
+        }
+        keep = __any_sync(FULL, low);
+        auto wsum = [&](double v) {
+#pragma unroll
+          for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
+          return v;
+        };
+        const double margin = -1e-6;  // dwarfs the rounding of the sums; costs nothing in pruning power
+        for (int c = 0; c < 4 && !keep; ++c) {
+          int kmax = 0;
+#pragma unroll
+          for (int s2 = 0; s2 < 4; ++s2) kmax = max(kmax, (int)((hist[s2] >> (16 * c)) & 0xFFFF));
+          if (kmax < P.min_alt_reads) continue;  // not a possible allele (uniform across the warp)
+          const double g_het = wsum(het[c]), g_hom = wsum(hom[c]);
+          const double g_t = fmax(fmax(fmax(wsum(tm0[c]), wsum(tm1[c])), fmax(wsum(tm2[c]), wsum(tm3[c]))), wsum(tp[c]));
+          keep = !(g_het - A.het_prior <= margin) || !(g_hom - A.hom_prior <= margin) || !(g_t - A.somatic_prior <= margin);
+        }
+      }
+      if (!keep || lane != 0) continue;
+      const int h = atomicAdd(A.n_simple, 1);
+      if (h < A.max_simple) {
+        Tile t;
+        t.locus0 = t0 + l;
+        t.n_loci = 1;
+        t.contig_id = tile.contig_id;
+        t.slot0 = tile.slot0 + l;
+        t.read_lo = tile.read_lo;
+        t.read_hi = tile.read_hi;
+        t.ref_index = tile.ref_index;
+        t._pad = 0;
+        t.seq_base = t.seq_end = 0;
+        A.simple[h] = t;
+      }
+    }
+  }
   if (MODE != 0) return;
   __syncthreads();
   const int n_cand = S.n_cand;

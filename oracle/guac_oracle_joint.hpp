@@ -235,11 +235,12 @@ struct PileupStats {
 inline double binomialCoefficientLog(int n, int k) {
   if (n == k || k == 0) return 0;
   if (k == 1 || k == n - 1) return std::log((double)n);
-  if (n < 67) {  // exact long arithmetic
+  if (n < 67) {  // exact: commons-math divides by gcd(i, j) first for n > 61 so that no intermediate leaves 64 bits;
+                 // a 128-bit intermediate gives the same integers
     if (k > n / 2) k = n - k;
-    unsigned long long result = 1;
-    for (int j = 1, i = n - k + 1; j <= k; ++i, ++j) result = result * i / j;
-    return std::log((double)result);
+    unsigned __int128 result = 1;
+    for (int j = 1, i = n - k + 1; j <= k; ++i, ++j) result = result * (unsigned)i / (unsigned)j;
+    return std::log((double)(unsigned long long)result);
   }
   if (n < 1030) {  // binomialCoefficientDouble
     int kk = k > n / 2 ? n - k : k;

@@ -113,13 +113,16 @@ def test_indel_alleles_and_non_standard_bases(gpu_ctx, sj_impl):
     assert_evidences_equal(got, want)
 
 
-@pytest.fixture(params=[2, 1, 0], ids=["stream", "single-kernel-locus-pass", "generic-kernels"])
+@pytest.fixture(params=[(2, 1), (2, 0), (1, 1), (0, 1)], ids=["stream", "stream-no-prune", "single-kernel-locus-pass", "generic-kernels"])
 def sj_impl(request, gpu_ctx):
-    """Every parity case runs through the default form (read pass + classifying locus pass + fast site kernel), the
-    single-kernel locus pass, and the generic per-locus kernels alone."""
-    gpu_ctx.set_option("sj_impl", request.param)
+    """Every parity case runs through the default form (read pass + classifying, pruning locus pass + fast site kernel), the
+    same without the in-tile prune (every simple candidate reaches the site kernel), the single-kernel locus pass, and the
+    generic per-locus kernels alone."""
+    gpu_ctx.set_option("sj_impl", request.param[0])
+    gpu_ctx.set_option("sj_prune", request.param[1])
     yield request.param
     gpu_ctx.set_option("sj_impl", 2)
+    gpu_ctx.set_option("sj_prune", 1)
 
 
 def test_repeat_runs_are_bit_identical(gpu_ctx):
@@ -144,4 +147,4 @@ def test_repeat_runs_are_bit_identical(gpu_ctx):
     # and the fast site kernel took nearly every candidate of this SNV-only workload
     gpu_ctx.somatic_joint_records(loci, p)
     simple, bail, heavy = gpu_ctx.last_stat("sj_simple"), gpu_ctx.last_stat("sj_bail"), gpu_ctx.last_stat("heavy_loci")
-    assert simple > 0 and bail < 0.1 * simple and heavy < 0.1 * simple, (simple, bail, heavy)
+    assert simple > 0 and bail < 0.05 * simple and heavy < 0.15 * simple, (simple, bail, heavy)
