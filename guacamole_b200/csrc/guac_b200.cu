@@ -1324,7 +1324,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
       FA.max_bail = n_simple;
       FA.err = ctx->b_err.as<DeviceError>();
       const unsigned grid = (unsigned)std::min<int64_t>(blocks_for(n_simple, 8), 148 * 16);
-      sj_snv_site_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->R, P, *params, FA);
+      sj_snv_site_kernel<<<grid, 256, 8 * sizeof(SJFWarpSmem), ctx->stream>>>(ctx->R, P, *params, FA);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
       GUAC_TRY(read_counters());
@@ -2114,6 +2114,7 @@ cudaError_t configure_device_functions() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(sj_snv_site_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8 * sizeof(SJFWarpSmem)));
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(asm_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_align_smem(ASM_ALIGN_MAX_S));
   return e;

@@ -336,8 +336,10 @@ struct SJFListEntry {  // (P(correct) and its two logarithms are looked up again
 };
 
 struct SJFWarpSmem {
-  double p[SJF_MAX_READS];      // P(correct) of the reads whose subsequence is the reference base
-  uint8_t meta[SJF_MAX_READS];  // sample | 4: such a read, with mapq > 0
+  double p[SJF_MAX_READS];      // P(correct), log10 p, log10 (1 - p) of the reads that have a subsequence and mapq > 0
+  double A[SJF_MAX_READS];
+  double B[SJF_MAX_READS];
+  uint8_t meta[SJF_MAX_READS];  // sample | 4: such a read | base code << 3
   SJFListEntry list[SJF_LIST];
   uint16_t slow[SJF_LIST];      // reads the exact cursor walks (several operators, N skips, non-standard bases)
 };
@@ -415,10 +417,10 @@ __device__ __noinline__ unsigned sjf_classify_slow(const ReadsView& R, int64_t r
 __global__ void __launch_bounds__(256, GUAC_SJF_MINB)
 sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __grid_constant__ guac_sj_params EP,
                    const __grid_constant__ SJFArgs A) {
-  __shared__ SJFWarpSmem smem_all[8];
+  extern __shared__ __align__(16) unsigned char sjf_smem_raw[];  // 8 x SJFWarpSmem (dynamic: beyond the 48 KB static limit)
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  SJFWarpSmem& W = smem_all[warp];
+  SJFWarpSmem& W = reinterpret_cast<SJFWarpSmem*>(sjf_smem_raw)[warp];
   const int S = P.n_samples, NP = S, TP = S + 1;
   const int n_cands = min(*A.n_cands, A.max_cands);
   // sample kinds and the discovery order as packed words: no dynamically indexed parameter arrays in the loops
@@ -483,9 +485,13 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       }
       const bool is_ref = has_sub && c == cr;
       if (is_ref && mapq != 0 && pq <= 0.5 && ((kinds >> (2 * smp)) & 3u) != GUAC_SJ_NORMAL_DNA) low_p = true;
-      if (is_ref) {
-        if (mapq != 0) meta |= 4;
+      if (mapq != 0) {  // (has_sub)
+        meta |= (uint8_t)(4 | (c << 3));
         W.p[idx] = pq;
+        W.A[idx] = la;
+        W.B[idx] = lb;
+      }
+      if (is_ref) {
 #pragma unroll
         for (int s = 0; s < SJF_SMAX; ++s)
           if (smp == s) {
@@ -648,10 +654,9 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
             c_fwd += e.flags & 1;
             c_first = min(c_first, (int)e.rel);
             if (e.flags & 2) {
-              const double2 ab = __ldg(A.log_table + (((int)e.mapq << 8) | e.q));
               c_ll += 1;
-              c_A += ab.x;
-              c_B += ab.y;
+              c_A += W.A[e.rel];
+              c_B += W.B[e.rel];
             }
             if (e.flags & 4) {
               c_disc += 1;
@@ -720,8 +725,9 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
     }
     const int n_sub = g_cnt[0] + g_cnt[1] + g_cnt[2] + g_cnt[3], f_sub = g_fwd[0] + g_fwd[1] + g_fwd[2] + g_fwd[3];
     // One allele: every slot's likelihoods, then the call logic across the slots
-    // (MultiSampleSingleAlleleEvidence.scala:66-230).  write: the raw record for the posterior / final kernels.
-    auto eval_allele = [&](int a, bool write, int site_idx, int job0) -> bool {
+    // (MultiSampleSingleAlleleEvidence.scala:66-230), and the raw record for the posterior / final kernels.
+    // Returns 1: called, 0: not called, 2: certainly not called and NO record written (only with allow_shortcut).
+    auto eval_allele = [&](int a, bool allow_shortcut, int job0) -> int {
       const int ca = res_c[a];
       const int alt_cnt = pick4(g_cnt[0], g_cnt[1], g_cnt[2], g_cnt[3], ca);
       const int alt_fwd = pick4(g_fwd[0], g_fwd[1], g_fwd[2], g_fwd[3], ca);
@@ -755,57 +761,65 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
         if (p2 > best) g = 2;
         germline = __shfl_sync(FULL, g, NP);
       }
-      // the alternate base's reads of this slot's tumor mixture, from the list in list order
-      double alt_terms = 0.0, alt_B = 0.0, rest_B = 0.0;  // their mixture terms, their log10(1 - p), the other bases' log10(1 - p)
-      if (lane < S + 2 && my_kind != GUAC_SJ_NORMAL_DNA)
-        for (int k = 0; k < n_list; ++k) {
-          const SJFListEntry& e = W.list[k];
-          if (!(e.flags & 2)) continue;
-          const int sk = (int)((kinds >> (2 * e.s)) & 3u);
-          if (lane < S ? e.s != lane : sk != GUAC_SJ_TUMOR_DNA) continue;
-          const double eB = __ldg(A.log_table + (((int)e.mapq << 8) | e.q)).y;
-          if ((int)e.c == ca) {
-            const double ep = c_success_probability[e.q] * c_success_probability[e.mapq];
-            alt_terms += log10(my_vaf * ep + (1.0 - my_vaf) * (1.0 - ep));
-            alt_B += eB;
-          } else {
-            rest_B += eB;
-          }
-        }
-      // Before the pass over the reference-base reads: a reference-base read with P(correct) > 1/2 can only lower
-      // {alt: vaf, ref: 1 - vaf} against {ref: 1}, so the alternate reads' terms alone bound a tumor mixture's gain.
-      // No germline call and no tumor mixture that can win against its prior: the allele is not called
-      // (MultiSampleSingleAlleleEvidence.scala:120-123,220-230) and that pass is not needed.  (With RNA samples the
-      // DNA prior depends on their posteriors: no shortcut.)
-      if (!write && !low_p && !has_rna && germline == 0) {
-        const bool can_win = lane < S + 2 && lane != NP && my_kind == GUAC_SJ_TUMOR_DNA &&
-                             !((alt_terms - alt_B) - EP.somatic_neg_log10_variant_prior < -1e-6);
-        if (!__any_sync(FULL, can_win)) return false;
-      }
-      // {alt: vaf, ref: 1 - vaf} over the reads whose subsequence is the reference base, from the stash
+      // alt fractions of the tumor mixtures: every sample's own, and the pooled one
       double v[SJF_SMAX];
 #pragma unroll
       for (int s = 0; s < SJF_SMAX; ++s) v[s] = __shfl_sync(FULL, my_vaf, s);
       const double vp = __shfl_sync(FULL, my_vaf, TP);
+      // Before the pass over all reads: a reference-base read with P(correct) > 1/2 can only lower
+      // {alt: vaf, ref: 1 - vaf} against {ref: 1}, and reads on other bases add the same to both, so the alternate
+      // reads' terms alone bound a tumor mixture's gain.  No germline call and no tumor mixture that can win against its
+      // prior: the allele is not called (MultiSampleSingleAlleleEvidence.scala:120-123,220-230) and that pass is not
+      // needed.  (With RNA samples the DNA prior depends on their posteriors: no shortcut.)  One lane per listed read.
+      if (allow_shortcut && !low_p && !has_rna && germline == 0) {
+        double gain[SJF_SMAX] = {0.0, 0.0, 0.0, 0.0}, gain_p = 0.0;
+        for (int k = lane; k < n_list; k += 32) {
+          const SJFListEntry& e = W.list[k];
+          if (!(e.flags & 2) || (int)e.c != ca) continue;
+          const int s = e.s, sk = (int)((kinds >> (2 * s)) & 3u);
+          if (sk != GUAC_SJ_TUMOR_DNA) continue;
+          const double ep = W.p[e.rel], eB = W.B[e.rel];
+          const double vs = pick4(v[0], v[1], v[2], v[3], s);
+          const double t = log10(vs * ep + (1.0 - vs) * (1.0 - ep)) - eB;
+#pragma unroll
+          for (int j = 0; j < SJF_SMAX; ++j)
+            if (s == j) gain[j] += t;
+          gain_p += log10(vp * ep + (1.0 - vp) * (1.0 - ep)) - eB;
+        }
+        double best_gain = warp_sum_fixed(gain_p);
+#pragma unroll
+        for (int j = 0; j < SJF_SMAX; ++j) best_gain = fmax(best_gain, warp_sum_fixed(gain[j]));
+        if (best_gain - EP.somatic_neg_log10_variant_prior < -1e-6) return 2;
+      }
+      // {alt: vaf, ref: 1 - vaf} over every read of the tumor samples (PileupStats.logLikelihoodPileup :77-91), one lane per
+      // read, per-lane sums combined by fixed butterflies
       double acc[SJF_SMAX] = {0.0, 0.0, 0.0, 0.0}, acc_p = 0.0;
       for (int i = lane; i < n_span; i += 32) {
         const uint8_t m = W.meta[i];
         if (!(m & 4)) continue;
-        const int s = m & 3, sk = (int)((kinds >> (2 * s)) & 3u);
+        const int s = m & 3, c = (m >> 3) & 3, sk = (int)((kinds >> (2 * s)) & 3u);
         if (sk == GUAC_SJ_NORMAL_DNA) continue;
         const double pp = W.p[i];
         const double vs = pick4(v[0], v[1], v[2], v[3], s);
-        const double t = log10((1.0 - vs) * pp + (1.0 - (1.0 - vs)) * (1.0 - pp));
+        double t, u = 0.0;
+        if (c == cr) {  // mixtureFrequency = 1 - vaf
+          t = log10((1.0 - vs) * pp + (1.0 - (1.0 - vs)) * (1.0 - pp));
+          if (sk == GUAC_SJ_TUMOR_DNA) u = log10((1.0 - vp) * pp + (1.0 - (1.0 - vp)) * (1.0 - pp));
+        } else if (c == ca) {  // = vaf
+          t = log10(vs * pp + (1.0 - vs) * (1.0 - pp));
+          if (sk == GUAC_SJ_TUMOR_DNA) u = log10(vp * pp + (1.0 - vp) * (1.0 - pp));
+        } else {  // = 0
+          t = u = W.B[i];
+        }
 #pragma unroll
         for (int k = 0; k < SJF_SMAX; ++k)
           if (s == k) acc[k] += t;
-        if (sk == GUAC_SJ_TUMOR_DNA) acc_p += log10((1.0 - vp) * pp + (1.0 - (1.0 - vp)) * (1.0 - pp));
+        if (sk == GUAC_SJ_TUMOR_DNA) acc_p += u;
       }
 #pragma unroll
       for (int s = 0; s < SJF_SMAX; ++s) acc[s] = warp_sum_fixed(acc[s]);
       acc_p = warp_sum_fixed(acc_p);
-      if (my_kind != GUAC_SJ_NORMAL_DNA)  // reference-base reads from the stash; the alternate base's reads and the others from the list
-        ll1 = (lane == TP ? acc_p : pick4(acc[0], acc[1], acc[2], acc[3], lane)) + (alt_terms + rest_B);
+      if (my_kind != GUAC_SJ_NORMAL_DNA) ll1 = lane == TP ? acc_p : pick4(acc[0], acc[1], acc[2], acc[3], lane);
       auto mixture_triggers = [&](double variant_prior) {
         const bool has_alt = my_vaf > 0, has_ref = 1.0 - my_vaf > 0;
         const double prior1 = has_ref && !has_alt ? 0.0 : has_ref && has_alt ? variant_prior : 1.7976931348623157e308;
@@ -815,11 +829,11 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       const bool rna = __any_sync(FULL, lane < S && my_kind == GUAC_SJ_TUMOR_RNA && mixture_triggers(EP.somatic_neg_log10_variant_prior_rna));
       const double dna_prior = rna ? EP.somatic_neg_log10_variant_prior_with_rna_evidence : EP.somatic_neg_log10_variant_prior;
       const bool trig = __any_sync(FULL, lane < S + 2 && lane != NP && my_kind == GUAC_SJ_TUMOR_DNA && mixture_triggers(dna_prior));
-      const bool is_call = germline != 0 || trig;
-      if (!write || lane >= S + 2) return is_call;
+      const int is_call = (germline != 0 || trig) ? 1 : 0;
+      if (lane >= S + 2) return is_call;
       SJEvidenceDev* E = reinterpret_cast<SJEvidenceDev*>(A.raw + (size_t)(job0 + a) * A.raw_stride);
       if (lane == 0) {
-        E->site = site_idx;
+        E->site = -1;  // (the site record, if any, points here through first_job)
         E->allele = a;
       }
       SJSlotDev& o = E->slots[lane];
@@ -856,19 +870,26 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       o.n_depths = nd;
       return is_call;
     };
-    // A site none of whose alleles is called is never emitted (MultiSampleMultiAlleleEvidence.scala:149-155; force-called
-    // sites are not here): it ends here, without a record.  Most candidate sites do.
-    bool any_call = false;
-    for (int a = 0; a < n_res; ++a) any_call = eval_allele(a, false, 0, 0) || any_call;
-    if (!any_call) continue;
+    // The raw records of the site's alleles are written as they are evaluated; a site none of whose alleles is called
+    // is never emitted (MultiSampleMultiAlleleEvidence.scala:149-155; force-called sites are not here) and ends without
+    // a site record — its job slots stay unused.
     int site_idx = 0, job0 = 0;
-    if (lane == 0) {
-      site_idx = atomicAdd(A.n_sites, 1);
-      job0 = atomicAdd(A.n_jobs, n_res);
-    }
-    site_idx = __shfl_sync(FULL, site_idx, 0);
+    if (lane == 0) job0 = atomicAdd(A.n_jobs, n_res);
     job0 = __shfl_sync(FULL, job0, 0);
-    if (site_idx >= A.max_sites || job0 + n_res > A.max_jobs) continue;  // the host sees the counters and reruns with room
+    if (job0 + n_res > A.max_jobs) continue;  // the host sees the counter and reruns with room
+    bool any_call = false;
+    unsigned unwritten = 0;
+    for (int a = 0; a < n_res; ++a) {
+      const int r = eval_allele(a, true, job0);
+      any_call = any_call || r == 1;
+      if (r == 2) unwritten |= 1u << a;
+    }
+    if (!any_call) continue;
+    for (int a = 0; a < n_res; ++a)  // the emitted site's other alleles need their records too
+      if ((unwritten >> a) & 1u) eval_allele(a, false, job0);
+    if (lane == 0) site_idx = atomicAdd(A.n_sites, 1);
+    site_idx = __shfl_sync(FULL, site_idx, 0);
+    if (site_idx >= A.max_sites) continue;
     if (lane == 0) {
       SJSiteDev& st = A.sites[site_idx];
       st.slot = tile.slot0;
@@ -893,7 +914,6 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
         st.alleles[k] = al;
       }
     }
-    for (int a = 0; a < n_res; ++a) eval_allele(a, true, site_idx, job0);
   }
 }
 
