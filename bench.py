@@ -45,7 +45,11 @@ class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, period: float = 0.05):
+        # NVML queries serialise in the driver: with one sampler per rank a short period steals host time from the
+        # synchronous C calls of every rank (measured at N = 8).  50 ms by default; the timed region is stretched to
+        # hold a few samples by repeating the steps, never by sampling faster.
+        self.period = period
         self.gpu, self.rows, self.proc = gpu_index, [], None
         self.nvml, self.stop_flag, self.thread = None, threading.Event(), None
 
@@ -60,7 +64,7 @@ class ClockSampler:
                 self.rows.append([str(self.gpu), str(sm), str(self.max_sm), "0"] + ["Active" if mask & bit else "Not Active" for _, bit in names])
             except Exception:
                 pass
-            if self.stop_flag.wait(0.002):  # a timed region of a few steps lasts tens of ms: sample every 2 ms
+            if self.stop_flag.wait(self.period):
                 return
 
     def start(self):
@@ -132,14 +136,14 @@ def cpu_sample(contig_len: int, seed: int, n_threads: int, target_s: float = 12.
         ref = Reference({"synth1": ContigWindow("synth1", rlo, oracle.synth_reference(seed, rlo, rhi), contig_len)})
         t = time.perf_counter()
         out = oracle.somatic_standard(batch, ref, [(0, lo, hi)], n_threads=n_threads)
-        return out["n_visited"], time.perf_counter() - t, len(out["calls"])
+        return out["n_visited"], time.perf_counter() - t, out
 
     base = min(contig_len // 4, 10_000_000)
     n, dt, _ = run(base, min(contig_len - 200, base + 50_000 * max(1, n_threads // 4)))  # calibration
     rate = n / dt
     span = int(min(contig_len - 200 - base, max(100_000, rate * target_s)))
-    n, dt, calls = run(base, base + span)
-    return {"loci": n, "seconds": dt, "value": n / dt, "calls": calls, "window": [base, base + span]}
+    n, dt, out = run(base, base + span)
+    return {"loci": n, "seconds": dt, "value": n / dt, "calls": len(out["calls"]), "window": [base, base + span], "out": out}
 
 
 def run_reference(args, rank, world):
@@ -161,8 +165,9 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": v, "unit": "loci/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1000.0 * secs / max(1, len(vals)), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"somatic-standard tumor/normal synthetic 60x/30x, {args.contig_mbp} Mbp contig, planted SNVs "
-                               "(BASELINE configs[2])", "parallelism": f"cpu threads x{n_threads}"},
+        "config": {"workload": f"window of BASELINE configs[2] per step (loci {sample['window']} of the somatic-standard tumor/normal "
+                               f"synthetic 60x/30x {args.contig_mbp} Mbp contig, planted SNVs): a bounded sample, rates are per locus",
+                   "parallelism": f"cpu threads x{n_threads}"},
         "cpu_baseline": {"value": v, "unit": "loci/s", "cores": n_threads, "kind": "port",
                          "sample": f"oracle (C++ restatement; the Scala/Spark reference cannot run: no JVM) on loci "
                                    f"{sample['window']} of the seeded workload per step"},
@@ -170,6 +175,154 @@ def run_reference(args, rank, world):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+def oracle_threads_rate(prepare, n_threads, base, contig_len, target_s, calib=20_000):
+    """The oracle over n_threads disjoint windows at once (the ctypes calls release the GIL; this mirrors Spark local[N]):
+    prepare(lo, hi) builds one window's inputs (untimed) and returns a callable that runs the oracle and returns the loci
+    it visited."""
+    from concurrent.futures import ThreadPoolExecutor
+    t0 = time.perf_counter()
+    n = prepare(base, base + calib)()
+    rate = n / max(time.perf_counter() - t0, 1e-9)
+    w = int(max(calib, min((contig_len - 400 - base) // n_threads, rate * target_s)))
+    jobs = [prepare(base + k * w, base + (k + 1) * w) for k in range(n_threads)]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(n_threads) as ex:
+        loci = sum(ex.map(lambda j: j(), jobs))
+    wall = time.perf_counter() - t0
+    return {"value": loci / wall, "loci": int(loci), "seconds": wall, "window": [base, base + n_threads * w]}
+
+
+def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
+    """The other configurations of BASELINE.json through their own callers, each with the headline's blocks: configs[3]'s
+    per-GPU shape (somatic-joint, 2 normal + 2 tumor at 30/30/60/60), configs[1] (germline toy caller, one 30x sample) and
+    configs[4] (germline-assembly, k = 31).  Every rank runs them on its own seeded contig (weak scaling)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from guacamole_b200 import synth
+    from guacamole_b200.commands import somatic_joint as sj
+    from guacamole_b200.io import ContigWindow, Reference
+    from guacamole_b200.native import ga_params, gs_params
+    steps = max(1, min(args.steps, 3))
+
+    def total(x):
+        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def measure(name, reference, depths, tumor, contig_len, seed, call, visited_of, abytes, extra, oracle_job, roof=True):
+        ctx.synth_generate(contig_len, depths, tumor, seed)
+        kms = []
+
+        def step():
+            out = call()
+            try:
+                kms.append(ctx.last_kernel_ms()[0])
+            except Exception:
+                pass
+            return out
+        ms, _, outs = timed(step, steps, 1)
+        loci = visited_of(outs[0])
+        value = total(loci * steps) / (ms / 1000.0)
+        entry = {"reference": reference, "metric": METRIC, "value": value, "unit": "loci/s", "ms_per_step": ms / steps,
+                 "config": {"workload": name, "loci_per_step_per_gpu": int(loci), "reads_per_gpu": int(sum(depths) * contig_len // 100)}}
+        entry["config"].update(extra(outs[0]))
+        k_ms = sum(kms[-steps:]) / max(1, len(kms[-steps:])) if kms else None
+        if roof and k_ms:
+            achieved = abytes * loci / (k_ms / 1000.0) / 1e9
+            entry["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                                 "traffic": None, "kernel_ms": k_ms, "algorithmic_bytes_per_locus": abytes,
+                                 "algorithmic_bytes_per_launch": abytes * loci, "peak_source": peak_src,
+                                 "kernel": "every kernel of one call, first launch to last (CUDA events on the library's stream)"}
+        elif k_ms:
+            entry["kernel_ms"] = k_ms
+        if not args.no_e2e:
+            hb = ctx.export_reads_compact_struct()
+            n = int(hb.n_reads)
+
+            def column(p, ctype, dtype):
+                return np.frombuffer((ctype * n).from_address(C.cast(p, C.c_void_p).value), dtype=dtype)
+            n_bases = n * int(hb.uniform_read_len) if hb.uniform_read_len > 0 else int(column(hb.read_len, C.c_uint16, np.uint16).sum(dtype=np.int64))
+            n_cigar = int(column(hb.n_cigar_ops8, C.c_uint8, np.uint8).sum(dtype=np.int64)) if hb.n_cigar_ops8 else \
+                int(column(hb.n_cigar_ops, C.c_uint16, np.uint16).sum(dtype=np.int64))
+            h2d = hb.wire_bytes(n_bases, n_cigar)
+            d2h = [0]
+
+            def step_e2e():
+                ctx.upload_reads_compact(hb)
+                out = call()
+                d2h[0] = sum(int(getattr(x, "nbytes", len(x) if isinstance(x, (bytes, bytearray)) else 0)) for x in
+                             (out.values() if isinstance(out, dict) else out))
+                return out
+            e_ms, _, e_outs = timed(step_e2e, steps, 1)
+            entry["e2e"] = {"value": total(visited_of(e_outs[0]) * steps) / (e_ms / 1000.0), "unit": "loci/s",
+                            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h[0]),
+                            "note": f"reads in the compact wire form ({hb.qual_bits}-bit qualities) from pinned host memory each step"}
+            ctx.free_reads_compact_struct(hb)
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            from oracle import oracle
+            nthreads = os.cpu_count() or 1
+
+            def prepare(lo, hi):
+                j_lo, j_hi = synth.read_window_for_loci(contig_len, depths, lo, hi)
+                j_lo -= j_lo % 8
+                batch = oracle.synth_generate(contig_len, depths, tumor, seed, j_lo, j_hi)
+                rlo, rhi = max(0, lo - 512), min(contig_len, hi + 512)
+                ref = Reference({"synth1": ContigWindow("synth1", rlo, oracle.synth_reference(seed, rlo, rhi), contig_len)})
+                return lambda: oracle_job(oracle, batch, ref, lo, hi)
+            c = oracle_threads_rate(prepare, nthreads, min(contig_len // 4, 1_000_000), contig_len, target_s=6.0)
+            entry["cpu_baseline"] = {"value": c["value"], "unit": "loci/s", "cores": nthreads, "kind": "port",
+                                     "sample": f"oracle, {nthreads} threads each over its own window, loci {c['window']} of the same seeded "
+                                               f"workload: {c['loci']} loci in {c['seconds']:.1f} s"}
+        return entry
+
+    paths = {}
+    # configs[3]: somatic-joint, 2 normal + 2 tumor (one rank's shard of the sharded genome)
+    depths, tumor = (30, 30, 60, 60), (False, False, True, True)
+    kinds = [sj.NORMAL_DNA, sj.NORMAL_DNA, sj.TUMOR_DNA, sj.TUMOR_DNA]
+    n = args.joint_mbp * 1_000_000
+    pj = sj.sj_params(kinds)
+    paths["somatic_joint_2n2t"] = measure(
+        f"somatic-joint 2 normal + 2 tumor synthetic 30x/30x/60x/60x, {args.joint_mbp} Mbp contig per GPU, planted SNVs (one GPU's shard of "
+        "BASELINE configs[3])", "commands/SomaticJointCaller.scala:154-203", depths, tumor, n, 4000 + rank,
+        lambda: ctx.somatic_joint_records([(0, 0, n)], pj), lambda o: o[3], algorithmic_bytes_per_locus(sum(depths), len(depths)),
+        lambda o: {"alleles_emitted": int(len(o[0])), **{k: ctx.last_stat(k) for k in ("fallback_tiles", "heavy_loci", "sj_simple", "sj_bail",
+                                                                                       "sj_sites", "sj_emitted_sites")}},
+        lambda oracle, b, r, lo, hi: oracle.somatic_joint(b, r, [(0, lo, hi)], pj)[1])
+    # configs[1]: the germline toy caller on one 30x sample
+    n1 = args.germline_mbp * 1_000_000
+    pg = gs_params()
+    paths["germline_standard_30x"] = measure(
+        f"germline toy caller (callPileupVariant) on one synthetic 30x sample, {args.germline_mbp} Mbp contig (BASELINE configs[1])",
+        "commands/GermlineAssemblyCaller.scala:135-153,233-261", (30,), (False,), n1, 1000 + rank,
+        lambda: ctx.germline_standard([(0, 0, n1)], pg), lambda o: o["n_visited"], algorithmic_bytes_per_locus(30, 1),
+        lambda o: {"calls": int(len(o["calls"])), "fallback_tiles": ctx.last_stat("fallback_tiles"), "heavy_loci": ctx.last_stat("heavy_loci")},
+        lambda oracle, b, r, lo, hi: oracle.germline_standard(b, r, [(0, lo, hi)], pg)["n_visited"])
+    # configs[4]: germline-assembly, k = 31 windows (hash-table / latency bound: windows and k-mers per second, no HBM roofline)
+    n4 = args.assembly_mbp * 1_000_000
+    pa = ga_params(kmer_size=31, assembly_window_range=41, min_occurrence=3, min_mean_kmer_quality=0)
+
+    def asm_extra(o):
+        wins = int(len(o["windows"]))
+        kmers = wins * int(30 * (82 + 100) / 100) * (100 - 31 + 1)  # SURVEY 8: reads per window x k-mers per read
+        d = {"windows_assembled": wins, "windows_consumed": int(o["windows"]["consumed"].sum()), "calls": int(len(o["calls"])),
+             "kmer_insertions_per_step_estimate": kmers,
+             "note": "the generator's indels are per read (1 % insertions, 1 % deletions of 1..10 bases); it plants SNVs only"}
+        try:
+            ms, nw = ctx.last_kernel_ms()
+            d.update({"assembly_stage_ms": ms, "windows_per_s": nw / (ms * 1e-3), "kmers_per_s_estimate": kmers / (ms * 1e-3),
+                      "gb_per_s_estimate": wins * (54.6 * READ_BYTES + 82 + 3822 * 16) / (ms * 1e-3) / 1e9})
+        except Exception:
+            pass
+        return d
+    paths["germline_assembly_k31"] = measure(
+        f"germline-assembly (discoverGermlineVariants) k = 31, window range 41, one synthetic 30x sample, {args.assembly_mbp} Mbp (BASELINE "
+        "configs[4])", "commands/GermlineAssemblyCaller.scala:84-219", (30,), (False,), n4, 5000 + rank,
+        lambda: ctx.germline_assembly([(0, 200, n4 - 200)], pa), lambda o: n4 - 400, 0.0, asm_extra,
+        lambda oracle, b, r, lo, hi: (oracle.germline_assembly(b, r, [(0, lo, hi)], pa), hi - lo)[1], roof=False)
+    return paths
 
 
 def main():
@@ -182,11 +335,33 @@ def main():
     ap.add_argument("--reference-step-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-pin", action="store_true", help="do not pin the ranks to disjoint core sets")
+    ap.add_argument("--clock-period-ms", type=float, default=None,
+                    help="clock sampler period (default 5 ms on one GPU, 50 ms with several ranks: NVML queries of all ranks serialise "
+                         "in the driver); 0 disables the sampler (A/B)")
+    ap.add_argument("--no-paths", action="store_true", help="skip the `paths` block (the other callers / configurations)")
+    ap.add_argument("--joint-mbp", type=int, default=50)
+    ap.add_argument("--germline-mbp", type=int, default=10)
+    ap.add_argument("--assembly-mbp", type=int, default=2)
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.clock_period_ms is None:
+        args.clock_period_ms = 5.0 if world == 1 else 50.0
+
+    # ranks on disjoint core sets: eight synchronous host loops plus their driver threads otherwise migrate over each other
+    pinned_cores = None
+    if world > 1 and not args.no_pin and hasattr(os, "sched_setaffinity"):
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = max(1, len(cores) // world)
+            mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+            os.sched_setaffinity(0, mine)
+            pinned_cores = len(mine)
+        except OSError:
+            pinned_cores = None
 
     import __graft_entry__ as graft
     if rank == 0:
@@ -241,12 +416,15 @@ def main():
 
     kernel_ms = []
 
+    counters = [0, 0]
+
     def step_resident():
         out = ctx.somatic_standard(ranges)
         kernel_ms.append(ctx.last_kernel_ms()[0])
+        counters[0], counters[1] = ctx.last_stat("fallback_tiles"), ctx.last_stat("heavy_loci")
         return out["n_visited"], len(out["calls"])
 
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, period=max(args.clock_period_ms, 1.0) / 1000.0)
     launches0 = None
 
     def step_counted():
@@ -257,9 +435,20 @@ def main():
         step_resident()
     kernel_ms.clear()
     launches0 = ctx.kernel_launches
-    sampler.start()
+    if args.clock_period_ms > 0:
+        sampler.start()
     ms_total, wall, outs = timed(step_counted, args.steps, 0)
-    clocks = sampler.stop()
+    clocks = sampler.stop() if args.clock_period_ms > 0 else {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["sampler off"], "samples": 0}
+    if args.clock_period_ms > 0 and clocks.get("samples", 0) < 3:
+        # the timed region was shorter than a few sampler periods: sample the clocks over a second, untimed run of the
+        # same steps under load (the timed numbers above are not touched)
+        sampler = ClockSampler(local_rank, period=0.01)
+        sampler.start()
+        t_end = time.perf_counter() + 0.25
+        while time.perf_counter() < t_end:
+            step_resident()
+        clocks = sampler.stop()
+        clocks["note"] = "sampled over 0.25 s of the same steps right after the timed region (the region itself is shorter than the sampler period)"
     launches = ctx.kernel_launches - launches0
     loci_step = outs[0][0]
     total_loci = torch.tensor([float(sum(o[0] for o in outs))], dtype=torch.float64, device="cuda")
@@ -319,13 +508,30 @@ def main():
                        "memory each step; reference genome resident"}
         ctx.free_reads_compact_struct(hb)
 
-    cpu = None
+    cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         nthreads = os.cpu_count() or 1
         s = cpu_sample(contig_len, 3000, nthreads)
         cpu = {"value": s["value"], "unit": "loci/s", "cores": nthreads, "kind": "port",
                "sample": f"oracle (C++ restatement of the Scala reference, {nthreads} threads over loci ranges) on loci "
                          f"{s['window']} of the same seeded workload: {s['loci']} loci in {s['seconds']:.1f} s"}
+        # parity where the number is made: the GPU's calls inside the oracle's window of this very batch
+        lo, hi = s["window"]
+        got = ctx.somatic_standard(ranges)
+        g, w = got["calls"], s["out"]["calls"]
+        g = g[(g["start"] >= lo) & (g["start"] < hi)]
+
+        def alleles(calls, arena):
+            return [(int(c["start"]), arena[c["ref_off"]:c["ref_off"] + c["ref_len"]], arena[c["alt_off"]:c["alt_off"] + c["alt_len"]])
+                    for c in calls]
+        ok = len(g) == len(w) and alleles(g, got["arena"]) == alleles(w, s["out"]["arena"]) and bool(
+            np.allclose(g["somatic_log_odds"], w["somatic_log_odds"], rtol=1e-9, atol=0))
+        parity = {"loci": int(s["loci"]), "calls": int(len(w)), "gpu_calls": int(len(g)), "ok": bool(ok),
+                  "compared": "start, ref / alt alleles exactly, somatic log odds at 1e-9 relative, oracle vs GPU inside the cpu_baseline window"}
+
+    paths = None
+    if not args.no_paths:
+        paths = run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src)
 
     if rank == 0:
         line = {
@@ -335,12 +541,15 @@ def main():
             "config": {"workload": f"somatic-standard tumor/normal synthetic 60x/30x, {args.contig_mbp} Mbp contig per GPU, planted "
                                    "SNVs (BASELINE configs[2]); configs[3] is this path sharded by loci ranges",
                        "loci_per_step_per_gpu": loci_step, "reads_per_gpu": int(sum(DEPTHS) * contig_len // 100),
-                       "calls_per_step": outs[0][1], "parallelism": f"loci-range shards x{world}, no collective",
+                       "calls_per_step": outs[0][1], "fallback_tiles": counters[0], "heavy_loci": counters[1],
+                       "parallelism": f"loci-range shards x{world}, no collective", "cores_per_rank": pinned_cores,
                        "l2": "inputs (7.3 GB per GPU) are far larger than L2 (126 MB); no flush needed"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "wall_s_timed": wall,
+            "wall_s_timed": wall, "parity": parity, "paths": paths,
         }
         print(json.dumps(line), flush=True)
+        if parity is not None and not parity["ok"]:
+            sys.exit("parity check failed: GPU calls differ from the oracle's inside the cpu_baseline window")
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -353,9 +353,18 @@ int reset_error(guac_ctx* ctx) {
   return GUAC_OK;
 }
 
+// Small results (counter blocks, the error record) come back through one pinned block per context: a copy into
+// pageable memory is staged by the driver and costs a second synchronisation.  Layout: [0, 256) counters of the
+// call, [256, 512) the DeviceError.
+int pinned_block(guac_ctx* ctx) {
+  if (!ctx->h_counters) CUDA_TRY(ctx, cudaMallocHost(&ctx->h_counters, 512));
+  return GUAC_OK;
+}
+
 // Translates a device-side error into the reference's wording.
 int check_device_error(guac_ctx* ctx) {
-  DeviceError e;
+  GUAC_TRY(pinned_block(ctx));
+  DeviceError& e = *reinterpret_cast<DeviceError*>(static_cast<unsigned char*>(ctx->h_counters) + 256);
   CUDA_TRY(ctx, cudaMemcpyAsync(&e, ctx->b_err.p, sizeof e, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   if (e.code == DERR_NONE) return GUAC_OK;
@@ -954,7 +963,9 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
   GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(SSCounters)));
   SSCounters* d_cnt = ctx->b_ncalls.as<SSCounters>();
   int* d_ncalls = &d_cnt->n_calls;
-  SSCounters h_cnt{};
+  GUAC_TRY(pinned_block(ctx));
+  SSCounters& h_cnt = *static_cast<SSCounters*>(ctx->h_counters);  // pinned: no staging copy, no extra wait
+  h_cnt = SSCounters{};
   int max_calls = (int)std::max<size_t>(ctx->b_calls.cap / sizeof(SSCallDev), 1 << 16);
   int nc = 0;
   unsigned long long visited_host = 0;  // loci visited, counted by the tile kernels
@@ -1087,7 +1098,8 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
       }
     }
     for (int attempt = 0; st == GUAC_OK && attempt < 2; ++attempt) {
-      unsigned int used = 0;
+      unsigned int& used = *reinterpret_cast<unsigned int*>(static_cast<unsigned char*>(ctx->h_counters) + 128);
+      used = 0;
       if (attempt > 0) cudaMemsetAsync(&d_cnt->arena_used, 0, sizeof(unsigned int), ctx->stream);  // (cleared with the block the first time)
       ss_evidence_kernel<<<(unsigned)nc, 128, 0, ctx->stream>>>(
           ctx->R, ctx->d_refs.as<RefView>(), P, ctx->b_calls.as<SSCallDev>(), ctx->b_arena.as<char>(), &d_cnt->arena_used,
@@ -1210,7 +1222,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
   };
   GUAC_TRY(ensure(ctx, ctx->b_ncalls, sizeof(SJCounters)));
   SJCounters* d_cnt = ctx->b_ncalls.as<SJCounters>();
-  if (!ctx->h_counters) CUDA_TRY(ctx, cudaMallocHost(&ctx->h_counters, 256));
+  GUAC_TRY(pinned_block(ctx));
   SJCounters& h_cnt = *static_cast<SJCounters*>(ctx->h_counters);
   auto read_counters = [&]() -> int {
     CUDA_TRY(ctx, cudaMemcpyAsync(&h_cnt, d_cnt, sizeof(SJCounters), cudaMemcpyDeviceToHost, ctx->stream));

@@ -193,17 +193,18 @@ struct TileArgs {
 
 // MODE 2, at most four samples: the discovery samples' events of one locus in one pass.  hist[s] holds, 16 bits per
 // standard base, how many reads of sample s have that substitution there.  Returns the largest number of equal
-// allele-starting elements in one sample (indel anchors of a sample counted together: an upper bound); `simple`: no
-// read of any sample has an insertion or a non-standard base there and no sample has min_reads indel anchors — every
-// allele that can start there is a one-base substitution.  An allele needs min_reads equal elements in ONE discovery
+// allele-starting elements in one sample (indel anchors of a sample counted together: an upper bound);
+// `one_base_alleles`: no sample has min_reads indel anchors there — every allele that can start there is a substitution
+// (the call bound applies); `simple`: moreover no read of any sample has an insertion or a non-standard base there —
+// every subsequence is one standard base (the fast site kernel applies).  An allele needs min_reads equal elements in ONE discovery
 // sample (jointcaller/AlleleAtLocus.scala:99-124); inside a deletion or an N skip the read's element one locus before
 // is a variant or Clipped, so those events start nothing.
 template <class SM>
-__device__ inline int sj_scan_events(const SM& S, int l1, int min_reads, unsigned long long (&hist)[4], bool& simple) {
+__device__ inline int sj_scan_events(const SM& S, int l1, int min_reads, unsigned long long (&hist)[4], bool& simple, bool& one_base_alleles) {
   const int nr1 = S.nonref[l1], e1 = S.aux[l1] >> 16, e0 = e1 - ((nr1 & 0xFFFF) + (nr1 >> 16));
   hist[0] = hist[1] = hist[2] = hist[3] = 0ull;
   unsigned indel = 0;  // 8 bits per sample (saturating)
-  simple = true;
+  simple = one_base_alleles = true;
   for (int i = e0; i < e1; ++i) {
     const uint2 ev = S.ev[S.ev_order[i]];
     const int kind = (ev.x >> 24) & 7, code = (ev.x >> 27) & 7, smp = (int)(ev.x >> 30);
@@ -223,7 +224,7 @@ __device__ inline int sj_scan_events(const SM& S, int l1, int min_reads, unsigne
 #pragma unroll
     for (int c = 0; c < 4; ++c) best = max(best, (int)((hist[s] >> (16 * c)) & 0xFFFFull));
     const int n_indel = (int)((indel >> (8 * s)) & 0xFFu);
-    if (n_indel >= min_reads) simple = false;
+    if (n_indel >= min_reads) simple = one_base_alleles = false;
     best = max(best, n_indel);
   }
   return best;
@@ -602,7 +603,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     A.visited[slot] = any_depth ? 1 : 0;
     my_visited += any_depth;
     // (a tile with a missing reference base never gets here: it went to the generic kernel, which reports the error)
-    bool candidate, simple_site = false;
+    bool candidate, simple_site = false, one_base = false;
     if (MODE == 0) {  // early-outs (SomaticStandardCaller.scala:164-172)
       candidate = dT > 0 && dN > 0 && dT <= P.max_read_depth && dN <= P.max_read_depth && nrT != 0 && nrN <= P.max_normal_alt;
     } else if (MODE == 1) {
@@ -618,16 +619,16 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
           candidate = true;
           if (A.sample_bits) {
             unsigned long long hist[4];
-            candidate = sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site) >= P.min_alt_reads;
+            candidate = sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site, one_base) >= P.min_alt_reads;
           }
         }
         for (int i = 0; i < A.n_force; ++i)
           if (A.force[i].contig_id == tile.contig_id && A.force[i].start <= x + 1 && x + 1 < A.force[i].end) {
             candidate = true;  // force-called: always evaluated, by the generic kernels
-            simple_site = false;
+            simple_site = one_base = false;
           }
       }
-      if (candidate && simple_site && A.prune) {  // examined in the second pass below, with full warps
+      if (candidate && one_base && A.prune) {  // examined in the second pass below, with full warps
         S.cursor[atomicAdd(&S.n_cand, 1)] = l;
         continue;
       }
@@ -681,8 +682,8 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     for (int ci = warp; ci < n_cand; ci += CFG::WARPS) {
       const int l = S.cursor[ci];
       unsigned long long hist[4];
-      bool simple_site;
-      sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site);  // (every lane: the counts are needed by all)
+      bool simple_site, one_base;
+      sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site, one_base);  // (every lane: the counts are needed by all)
       bool keep = (S.aux[l + 1] & 0xFFFF) != 0;  // a read that may have P(correct) <= 1/2 covers x + 1
       {
         // Clipped elements at x leave the depths (MultiSampleMultiAlleleEvidence.scala:85-86): rare, no shortcut
@@ -704,12 +705,16 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
           const int c = (int)((ev.x >> 27) & 7);
           if (((ev.x >> 24) & 7) != GUAC_ALN_MISMATCH || c >= 4) continue;
           const int smp = (int)(ev.x >> 30), rl = (int)((ev.x >> 11) & 0xFFF);
+          // (the three loads below depend on the event alone: requested together)
+          const uint32_t hy = __ldg(A.hdr + tile.read_lo + rl).y;
+          const int mapq = (int)__ldg(R.mapq + tile.read_lo + rl);
+          const int q = (ev.y >> 31) ? (int)(ev.y & 0xFF) : (int)__ldg(R.qual + seq_base + ev.y);
           {
             // The bound is about one-base alleles.  A read whose next element is not a Match either starts a longer
             // allele (ReadSubsequence.scala:117-121), and with it come multi-base subsequences: the site kernel's case.
             // So is a read the exact cursor walked (an N skip after x + 1 leaves no event), and the tile's last site,
             // whose locus x + 2 lies outside the kept events.
-            bool longer = l + 2 >= n_ev_loci || !((__ldg(A.hdr + tile.read_lo + rl).y >> 24) & RF_MEDIUM);
+            bool longer = l + 2 >= n_ev_loci || !((hy >> 24) & RF_MEDIUM);
             if (!longer) {
               const int nr2 = S.nonref[l + 2], g1 = S.aux[l + 2] >> 16, g0 = g1 - ((nr2 & 0xFFFF) + (nr2 >> 16));
               for (int j = g0; j < g1; ++j) longer = longer || (int)((S.ev[S.ev_order[j]].x >> 11) & 0xFFF) == rl;
@@ -719,9 +724,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
               continue;
             }
           }
-          const int mapq = (int)__ldg(R.mapq + tile.read_lo + rl);
           if (mapq == 0) continue;  // contributes exactly 0.0 (PileupStats.scala:79-80)
-          const int q = (ev.y >> 31) ? (int)(ev.y & 0xFF) : (int)__ldg(R.qual + seq_base + ev.y);
           const double p = c_success_probability[q] * c_success_probability[mapq];
           if (!(p > 0.5)) {
             low = true;
@@ -773,8 +776,9 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         }
       }
       if (!keep || lane != 0) continue;
-      const int h = atomicAdd(A.n_simple, 1);
-      if (h < A.max_simple) {
+      // kept: the fast site kernel where every subsequence is one standard base, the generic kernels otherwise
+      const int h = atomicAdd(simple_site ? A.n_simple : A.n_heavy, 1);
+      if (h < (simple_site ? A.max_simple : A.max_heavy)) {
         Tile t;
         t.locus0 = t0 + l;
         t.n_loci = 1;
@@ -785,7 +789,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         t.ref_index = tile.ref_index;
         t._pad = 0;
         t.seq_base = t.seq_end = 0;
-        A.simple[h] = t;
+        (simple_site ? A.simple : A.heavy)[h] = t;
       }
     }
   }
