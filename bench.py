@@ -335,6 +335,9 @@ def main():
     ap.add_argument("--reference-step-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default, the headline): every rank has its own contig; strong: ONE seeded contig cut by "
+                         "UniformPartitioner ranges, every rank calls its range, the calls are gathered and checked against the uncut run")
     ap.add_argument("--no-pin", action="store_true", help="do not pin the ranks to disjoint core sets")
     ap.add_argument("--clock-period-ms", type=float, default=None,
                     help="clock sampler period (default 5 ms on one GPU, 50 ms with several ranks: NVML queries of all ranks serialise "
@@ -384,9 +387,17 @@ def main():
 
     contig_len = args.contig_mbp * 1_000_000
     ctx = Context(local_rank)
-    seed = 3000 + rank
+    strong = args.scaling == "strong"
+    seed = 3000 if strong else 3000 + rank
     ctx.synth_generate(contig_len, DEPTHS, TUMOR, seed)
     ranges = [(0, 0, contig_len)]
+    if strong:
+        # LociPartitioning ranges of UniformPartitioner (loci/partitioning/UniformPartitioner.scala:48-86), one per rank.  Every
+        # rank holds the whole contig's reads in HBM — a superset of its partition's reads plus halo
+        # (readsets/rdd/PartitionedRegions.scala:186-208) — and the planner only ever touches the reads over its own range.
+        from guacamole_b200 import partitioning
+        ranges = partitioning.ranges_of_partition(partitioning.uniform_partition([(0, 0, contig_len)], world), rank)
+        args.no_paths = args.no_e2e = True  # (the end-to-end and per-path legs belong to the weak-scaling headline)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local_rank))
 
     def barrier():
@@ -508,8 +519,26 @@ def main():
                        "memory each step; reference genome resident"}
         ctx.free_reads_compact_struct(hb)
 
+    strong_check = None
+    if strong:
+        mine = ctx.somatic_standard(ranges)
+        gathered = [None] * world
+        if world > 1:
+            dist.all_gather_object(gathered, {"start": mine["calls"]["start"].copy(), "odds": mine["calls"]["somatic_log_odds"].copy(),
+                                              "n_visited": mine["n_visited"]})
+        else:
+            gathered = [{"start": mine["calls"]["start"], "odds": mine["calls"]["somatic_log_odds"], "n_visited": mine["n_visited"]}]
+        if rank == 0:  # host-side gather of the sparse records, against the uncut run of the same contig
+            whole = ctx.somatic_standard([(0, 0, contig_len)])
+            starts = np.concatenate([g["start"] for g in gathered])
+            odds = np.concatenate([g["odds"] for g in gathered])
+            order = np.argsort(starts, kind="stable")
+            ok = (len(starts) == len(whole["calls"]) and np.array_equal(starts[order], whole["calls"]["start"]) and
+                  bool(np.allclose(odds[order], whole["calls"]["somatic_log_odds"], rtol=1e-9, atol=0)) and
+                  sum(g["n_visited"] for g in gathered) == whole["n_visited"])
+            strong_check = {"calls": int(len(starts)), "uncut_calls": int(len(whole["calls"])), "ok": bool(ok)}
     cpu, parity = None, None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not strong:
         nthreads = os.cpu_count() or 1
         s = cpu_sample(contig_len, 3000, nthreads)
         cpu = {"value": s["value"], "unit": "loci/s", "cores": nthreads, "kind": "port",
@@ -536,10 +565,13 @@ def main():
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "loci/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"somatic-standard tumor/normal synthetic 60x/30x, {args.contig_mbp} Mbp contig per GPU, planted "
-                                   "SNVs (BASELINE configs[2]); configs[3] is this path sharded by loci ranges",
+            "config": {"workload": (f"somatic-standard tumor/normal synthetic 60x/30x, ONE {args.contig_mbp} Mbp contig cut into {world} "
+                                    "UniformPartitioner ranges, one per GPU, calls gathered on the host (BASELINE configs[2], strong scaling)"
+                                    if strong else
+                                    f"somatic-standard tumor/normal synthetic 60x/30x, {args.contig_mbp} Mbp contig per GPU, planted "
+                                    "SNVs (BASELINE configs[2]); configs[3] is this path sharded by loci ranges"),
                        "loci_per_step_per_gpu": loci_step, "reads_per_gpu": int(sum(DEPTHS) * contig_len // 100),
                        "calls_per_step": outs[0][1], "fallback_tiles": counters[0], "heavy_loci": counters[1],
                        "parallelism": f"loci-range shards x{world}, no collective", "cores_per_rank": pinned_cores,
@@ -547,7 +579,11 @@ def main():
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "wall_s_timed": wall, "parity": parity, "paths": paths,
         }
+        if strong:
+            line["strong_scaling_check"] = strong_check
         print(json.dumps(line), flush=True)
+        if strong_check is not None and not strong_check["ok"]:
+            sys.exit("strong-scaling check failed: the gathered calls differ from the uncut run")
         if parity is not None and not parity["ok"]:
             sys.exit("parity check failed: GPU calls differ from the oracle's inside the cpu_baseline window")
     if world > 1:

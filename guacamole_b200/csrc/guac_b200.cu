@@ -27,6 +27,7 @@
 #include "germline_kernels.cuh"
 #include "assembly_kernels.cuh"
 #include "compact_kernels.cuh"
+#include "support_kernels.cuh"
 
 using namespace guac;
 
@@ -1005,10 +1006,10 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         GUAC_TRY(run_read_pass(ctx));
         TA.ev_by_read = ctx->b_bins.as<uint2>();
         TA.ev_count = ctx->b_bin_count.as<uint8_t>();
-        ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+        ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, offsetof(TileSmem<TCfg>, cov2), ctx->stream>>>(ctx->R, P, TA);
       } else {
         cudaEventRecord(ctx->ev0, ctx->stream);
-        ss_tile_kernel<TCfg, 0><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+        ss_tile_kernel<TCfg, 0><<<(unsigned)plan.n_tiles, TCfg::THREADS, offsetof(TileSmem<TCfg>, cov2), ctx->stream>>>(ctx->R, P, TA);
       }
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
@@ -1538,7 +1539,7 @@ int guac_germline_standard(guac_ctx* ctx, const guac_gs_params* params, const gu
   TA.n_visited = ctx->b_vcount.as<unsigned long long>();
   TA.err = ctx->b_err.as<DeviceError>();
   cudaEventRecord(ctx->ev0, ctx->stream);
-  ss_tile_kernel<TCfg, 1><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, P, TA);
+  ss_tile_kernel<TCfg, 1><<<(unsigned)plan.n_tiles, TCfg::THREADS, offsetof(TileSmem<TCfg>, cov2), ctx->stream>>>(ctx->R, P, TA);
   ctx->launches += 1;
   CUDA_TRY(ctx, cudaGetLastError());
   int counts[2] = {0, 0};
@@ -2116,6 +2117,7 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 
 #include "assembly_entry.inl"
 #include "compact_entry.inl"
+#include "support_entry.inl"
 
 namespace {
 cudaError_t configure_device_functions() {

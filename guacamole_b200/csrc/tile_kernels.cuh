@@ -147,15 +147,16 @@ struct TileSmem {
   uint32_t ref2[((CFG::TL + CFG::THREADS - 1) / CFG::THREADS) * (CFG::THREADS / 16) + 2];  // whole passes of the loader + read-ahead
   int cov[CFG::TL + 2];     // packed differences: normal | tumor << 16  -> depths after the scan (MODE 2: samples 0 | 1 << 16)
   int aux[CFG::TL + 2];     // low-quality tumor read differences | event count << 16 -> lowq | event end offset
-  int cov2[CFG::TL + 2];    // MODE 2 with at most four samples: samples 2 | 3 << 16
   int nonref[CFG::TL + 1];  // non-Match elements: normal | tumor << 16 (MODE 2 also keeps the locus behind the tile)
   int cursor[CFG::TL + 1];
   uint2 ev[CFG::E_MAX];
   uint16_t ev_order[CFG::E_MAX];  // event indices bucketed by locus (2 B per event instead of a second copy)
   uint16_t slow[CFG::SLOW_MAX];
   int warp_tot[2][CFG::WARPS];
-  int warp_tot2[CFG::WARPS];
   int n_events, n_slow, overflow, ref_has_mask, n_cand;
+  int warp_tot2[CFG::WARPS];
+  // MODE 2 only, and last on purpose: the other modes are launched with offsetof(TileSmem, cov2) bytes of shared memory
+  int cov2[CFG::TL + 2];    // with at most four samples: depths of samples 2 | 3 << 16
 };
 
 struct TileArgs {
@@ -279,7 +280,10 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
 #endif
 
   // ---- init ------------------------------------------------------------------------------
-  for (int i = tid; i < TL + 2; i += CFG::THREADS) S.cov[i] = S.aux[i] = S.cov2[i] = 0;
+  for (int i = tid; i < TL + 2; i += CFG::THREADS) {
+    S.cov[i] = S.aux[i] = 0;
+    if (MODE == 2) S.cov2[i] = 0;
+  }
   for (int i = tid; i < TL + 1; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
   if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = 0;
   if (tid < 4) {  // padding words behind the tile

@@ -95,6 +95,10 @@ def gs_params(sample_id=0, min_alt_reads=2, min_phred_scaled_likelihood=0, respe
     return p
 
 
+ALLELE_COUNT_DTYPE = np.dtype([("contig_id", np.int32), ("sample_id", np.int32), ("locus", np.int64), ("ref_off", np.uint32),
+                               ("ref_len", np.uint32), ("alt_off", np.uint32), ("alt_len", np.uint32), ("count", np.int32), ("_pad", np.int32)])
+VARIANT_LOCUS_DTYPE = np.dtype([("sample_id", np.int32), ("contig_id", np.int32), ("locus", np.int64),
+                                ("variant_allele_frequency", np.float32), ("_pad", np.int32)])
 LOCUS_COUNTS_DTYPE = np.dtype([(n, np.uint32) for n, _ in LocusCountsC._fields_])
 ELEMENT_DTYPE = np.dtype([("read_index", np.int64), ("read_position", np.int32), ("cigar_element_index", np.int32),
                           ("cigar_element_locus", np.int64), ("index_within_cigar_element", np.int32), ("kind", np.uint8),
@@ -577,6 +581,32 @@ class Context:
         from .commands import somatic_joint as sj
         alleles, samples, arena_b, nv = self.somatic_joint_records(loci, params, force_loci)
         return sj.decode(alleles, samples, arena_b, params.n_samples), nv
+
+    # -- other consumers of the pileup operator ---------------------------------------
+    def variant_support(self, loci: Sequence[Tuple[int, int, int]]):
+        """guac_variant_support -> [(sample_id, contig_id, locus, ref, alt, count)] (commands/VariantSupport.scala:100-112)."""
+        r = make_ranges(loci)
+        out, n, arena, alen = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64()
+        self._check(self.lib.guac_variant_support(self.ctx, r, C.c_int32(len(loci)), C.byref(out), C.byref(n), C.byref(arena), C.byref(alen)))
+        a = C.string_at(arena, alen.value) if arena else b""
+        if arena:
+            self.lib.guac_free(self.ctx, arena)
+        rec = _take(self.lib, self.ctx, out, ALLELE_COUNT_DTYPE, n.value)
+        return [(int(x["sample_id"]), int(x["contig_id"]), int(x["locus"]), a[x["ref_off"]:x["ref_off"] + x["ref_len"]].decode(),
+                 a[x["alt_off"]:x["alt_off"] + x["alt_len"]].decode(), int(x["count"])) for x in rec]
+
+    def vaf_histogram(self, loci: Sequence[Tuple[int, int, int]], bins: int = 20, min_read_depth: int = 0, min_vaf_percent: int = 0,
+                      want_loci: bool = True):
+        """guac_vaf_histogram -> (hist [n_samples, 101], variant loci per sample, VariantLocus records or None)
+        (commands/VAFHistogram.scala:194-245)."""
+        S = self._batch.n_samples
+        r = make_ranges(loci)
+        hist, tot = np.zeros((S, 101), np.int64), np.zeros(S, np.int64)
+        out, n = C.c_void_p(), C.c_int64()
+        self._check(self.lib.guac_vaf_histogram(self.ctx, r, C.c_int32(len(loci)), C.c_int32(bins), C.c_int32(min_read_depth),
+                                                C.c_int32(min_vaf_percent), hist.ctypes.data_as(C.c_void_p), tot.ctypes.data_as(C.c_void_p),
+                                                C.byref(out) if want_loci else None, C.byref(n)))
+        return hist, tot, (_take(self.lib, self.ctx, out, VARIANT_LOCUS_DTYPE, n.value) if want_loci else None)
 
     # -- callers -----------------------------------------------------------------
     def somatic_standard(self, ranges: Sequence[Tuple[int, int, int]], params: Optional[SSParamsC] = None,

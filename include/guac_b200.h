@@ -457,6 +457,43 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
                        guac_sj_sample_evidence** out_samples, int64_t* n_sample_evidences, char** out_arena, int64_t* arena_len,
                        int64_t* out_n_visited);
 
+/* ---- other consumers of the pileup operator ------------------------------------
+ * M/commands/VariantSupport.scala:100-112 (pileupsToAlleleCounts through pileupFlatMapMultipleSamples, skipEmpty = true):
+ * one record per (visited locus, sample, distinct allele of the pileup's elements) with the number of elements that
+ * carry it.  Alleles as M/pileup/Alignment.scala:14-75 defines them — Match (b, b), Mismatch (ref, b), Insertion
+ * (sequenced head, head + inserted), Deletion (ref incl. deleted, ref head), MidDeletion (ref, ""), Clipped ("", "").
+ * Records come in (range order, locus), sample, (ref, alt) string order (the reference's order inside a pileup is a
+ * hash map's; its suite sorts before comparing). */
+typedef struct {
+  int32_t contig_id;
+  int32_t sample_id;
+  int64_t locus;
+  uint32_t ref_off, ref_len, alt_off, alt_len; /* into the returned string arena */
+  int32_t count;
+  int32_t _pad;
+} guac_allele_count;
+int guac_variant_support(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, guac_allele_count** out_counts, int64_t* n_out,
+                         char** out_arena, int64_t* arena_len);
+
+/* M/commands/VAFHistogram.scala:30-58 (VariantLocus) */
+typedef struct {
+  int32_t sample_id;
+  int32_t contig_id;
+  int64_t locus;
+  float variant_allele_frequency; /* (depth - referenceDepth).toFloat / depth */
+  int32_t _pad;
+} guac_variant_locus;
+/*
+ * VAFHistogram.variantLociFromReads + generateVAFHistograms (M/commands/VAFHistogram.scala:194-245): every (locus, sample)
+ * with depth >= min_read_depth, referenceDepth != depth and variant allele frequency >= min_vaf_percent / 100.0 is a
+ * VariantLocus; out_hist[s * 101 + b] counts sample s's loci whose rounded percentage falls in bin b = p - p % (100 / bins)
+ * (p = (vaf * 100).toInt), out_n_variant_loci[s] their number.  Both are caller-provided ([n_samples * 101], [n_samples]).
+ * out_loci (optional, may be NULL) receives the records in (range order, locus, sample) order.
+ */
+int guac_vaf_histogram(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, int32_t bins, int32_t min_read_depth,
+                       int32_t min_vaf_percent, int64_t* out_hist, int64_t* out_n_variant_loci, guac_variant_locus** out_loci,
+                       int64_t* n_loci);
+
 /* ---- measurement support ----------------------------------------------------
  * These have no counterpart in the reference: they exist so that bench.py and the
  * tests can generate SURVEY.md 8(d)'s seeded synthetic reads directly in HBM, read them

@@ -364,3 +364,43 @@ def germline_assembly(batch: ReadBatch, reference: Reference, ranges, params):
         f = l.split("\t")
         out.append(tuple([f[0], int(f[1]), int(f[2])] + f[3:]))
     return out
+
+
+# ---- the small consumers of the operator, restated over the oracle's own pileups -------------------------
+def variant_support(batch: ReadBatch, reference: Reference, loci):
+    """VariantSupport.Caller.pileupsToAlleleCounts (M/commands/VariantSupport.scala:100-112) through
+    pileupFlatMapMultipleSamples(skipEmpty = true) (:83-89): per visited locus, per sample, pileup.elements.groupBy(_.allele)
+    with the group sizes.  -> [(sample_id, contig_id, locus, ref, alt, count)] in (range order, locus), sample, (ref, alt)
+    order (the Scala's order inside a pileup is a hash map's; VariantSupportSuite sorts before it compares)."""
+    import collections
+    contigs, positions, _ = pileup_counts(batch, reference, loci, skip_empty=True)
+    out = []
+    for c, x in zip(contigs, positions):
+        for s in range(batch.n_samples):
+            groups = collections.Counter((ref, alt) for ref, alt, _, _ in pileup_alleles(batch, reference, batch.contig_names[int(c)], int(x), s))
+            out += [(s, int(c), int(x), ref, alt, n) for (ref, alt), n in sorted(groups.items())]
+    return out
+
+
+def vaf_histogram(batch: ReadBatch, reference: Reference, loci, bins=20, min_read_depth=0, min_vaf_percent=0):
+    """VariantLocus.apply (M/commands/VAFHistogram.scala:37-58), the filter of variantLociFromReads (:214-229) and
+    generateVAFHistograms (:194-212), Float arithmetic as written there.  -> (hist [n_samples, 101], loci per sample,
+    [(sample_id, contig_id, locus, vaf float32)])."""
+    assert 1 <= bins <= 100, "Bins should be between 1 and 100"
+    contigs, positions, counts = pileup_counts(batch, reference, loci, skip_empty=True)
+    S = batch.n_samples
+    hist, tot, recs = np.zeros((S, 101), np.int64), np.zeros(S, np.int64), []
+    for i, (c, x) in enumerate(zip(contigs, positions)):
+        for s in range(S):
+            depth, ref_depth = int(counts[i, s]["depth"]), int(counts[i, s]["reference_depth"])
+            if depth < min_read_depth or ref_depth == depth:
+                continue
+            vaf = np.float32(depth - ref_depth) / np.float32(depth)   # (depth - referenceDepth).toFloat / depth
+            if float(vaf) < min_vaf_percent / 100.0:
+                continue
+            percent = int(np.float32(vaf) * np.float32(100))          # (variantAlleleFrequency * 100).toInt
+            b = percent - (percent % (100 // bins))
+            hist[s, b] += 1
+            tot[s] += 1
+            recs.append((s, int(c), int(x), np.float32(vaf)))
+    return hist, tot, recs

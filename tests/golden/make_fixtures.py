@@ -91,6 +91,12 @@ def main():
         reads = [r for r in filter_reads(normal + tumor) if any(r.start <= p < r.end for p in positions)]
         batch = ReadBatch.from_reads(reads, [c for c, _ in contigs], 2)
         np.savez_compressed(os.path.join(OUT, f"real_{name}.npz"), **pack(batch, ref, positions=np.array(positions, np.int64)))
+    # 5. VariantSupportSuite.scala:58-122: gatk_mini_bundle_extract.bam, every read over the loci the suite probes
+    #    (no duplicate filter here: the suite applies it in one of its tests, and so do ours, from the flags)
+    rs, cs = read_bam(RES + "gatk_mini_bundle_extract.bam", 0)
+    sel = [r for r in rs if r.contig == "20" and r.start < 10009000 and r.end > 9999900]
+    batch = ReadBatch.from_reads(sel, [c for c, _ in cs], 1)
+    np.savez_compressed(os.path.join(OUT, "gatk_mini.npz"), **pack(batch, ref))
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(OUT, f)))
