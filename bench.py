@@ -212,8 +212,8 @@ def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    def measure(name, reference, depths, tumor, contig_len, seed, call, visited_of, abytes, extra, oracle_job, roof=True):
-        ctx.synth_generate(contig_len, depths, tumor, seed)
+    def measure(name, reference, depths, tumor, contig_len, seed, call, visited_of, abytes, extra, oracle_job, roof=True, profile=0):
+        ctx.synth_generate(contig_len, depths, tumor, seed, profile=profile)
         kms = []
 
         def step():
@@ -268,7 +268,7 @@ def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
             def prepare(lo, hi):
                 j_lo, j_hi = synth.read_window_for_loci(contig_len, depths, lo, hi)
                 j_lo -= j_lo % 8
-                batch = oracle.synth_generate(contig_len, depths, tumor, seed, j_lo, j_hi)
+                batch = oracle.synth_generate(contig_len, depths, tumor, seed, j_lo, j_hi, profile=profile)
                 rlo, rhi = max(0, lo - 512), min(contig_len, hi + 512)
                 ref = Reference({"synth1": ContigWindow("synth1", rlo, oracle.synth_reference(seed, rlo, rhi), contig_len)})
                 return lambda: oracle_job(oracle, batch, ref, lo, hi)
@@ -279,6 +279,16 @@ def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
         return entry
 
     paths = {}
+    # configs[2] again, on the "realistic" variant of the read model (guacamole_b200/synth.py profile 1): does the fast path
+    # survive reads with quality-2 tails, depth that varies, 10 % multi-operator reads and 1 % reads with 10..20 mismatches?
+    n2 = args.contig_mbp * 1_000_000
+    paths["somatic_standard_realistic_reads"] = measure(
+        f"somatic-standard tumor/normal synthetic 60x/30x, {args.contig_mbp} Mbp contig per GPU, realistic read model: read density varying "
+        "like a Poisson pileup's, 15 % of reads with a quality-2 tail of 5..30 bases, 10 % multi-operator reads, 1 % of reads with 10..20 "
+        "mismatches (BASELINE configs[2] shape)", "commands/SomaticStandardCaller.scala:100-117,155-253", DEPTHS, TUMOR, n2, 3000 + rank,
+        lambda: ctx.somatic_standard([(0, 0, n2)]), lambda o: o["n_visited"], algorithmic_bytes_per_locus(sum(DEPTHS), len(DEPTHS)),
+        lambda o: {"calls": int(len(o["calls"])), "fallback_tiles": ctx.last_stat("fallback_tiles"), "heavy_loci": ctx.last_stat("heavy_loci")},
+        lambda oracle, b, r, lo, hi: oracle.somatic_standard(b, r, [(0, lo, hi)])["n_visited"], profile=1)
     # configs[3]: somatic-joint, 2 normal + 2 tumor (one rank's shard of the sharded genome)
     depths, tumor = (30, 30, 60, 60), (False, False, True, True)
     kinds = [sj.NORMAL_DNA, sj.NORMAL_DNA, sj.TUMOR_DNA, sj.TUMOR_DNA]

@@ -107,6 +107,7 @@ struct guac_ctx {
   // somatic-joint: force-call ranges, simple candidates, the fast kernel's sites / raw records / hand-backs, the generic
   // kernels' raw records, emitted sites and their order, offsets, finished records, ln n! table
   DevBuf j_force, j_simple, j_sites_fast, j_raw_fast, j_bail, j_raw_gen, j_emits, j_order, j_cnt, j_off, j_out_alleles, j_out_samples, j_logfact, j_logtab;
+  int64_t opt_synth_profile = 0;  // guac_synth_generate: 0 the SURVEY 8(d) workload, 1 its "realistic" variant (synth_model.h)
   int64_t opt_sj_prune = 1;  // locus pass drops simple sites that certainly hold no call (test hook: 0 sends them all to the site kernel)
   int64_t opt_sj_impl = 2;  // 2: read pass + classifying locus pass + fast site kernel (default); 1: single-kernel locus pass; 0: no fast site kernel
   int64_t stat_sj_simple = 0, stat_sj_bail = 0, stat_sj_sites = 0, stat_sj_emitted_sites = 0;
@@ -1780,6 +1781,9 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
     ctx->opt_force_fallback_mod = value < 0 ? 0 : value;
   } else if (n == "sj_host_threads") {
     ctx->opt_sj_host_threads = value < 0 ? 0 : std::min<int64_t>(value, 256);  // accepted for old callers; nothing runs on host threads any more
+  } else if (n == "synth_profile") {
+    if (value < 0 || value > 1) return fail(ctx, GUAC_E_INVALID_INPUT, "synth_profile must be 0 or 1");
+    ctx->opt_synth_profile = value;
   } else if (n == "sj_prune") {
     ctx->opt_sj_prune = value != 0;
   } else if (n == "sj_impl") {
@@ -1830,6 +1834,7 @@ int guac_synth_generate(guac_ctx* ctx, int32_t contig_id, int64_t contig_len, in
   P.seed = seed;
   P.contig_len = contig_len;
   P.n_samples = n_samples;
+  P.profile = (int32_t)ctx->opt_synth_profile;
   // interleaving pattern proportional to depths: round-robin, largest first (synth.py sample_pattern)
   int64_t total_depth = 0;
   int g = 0;

@@ -43,7 +43,7 @@ __global__ void medium_reads_scatter_kernel(const uint8_t* __restrict__ flag, co
   if (r < n && flag[r]) list[offset[r]] = r;
 }
 
-constexpr int STREAM_EV_CAP = 8;  // event records kept per read; a read with more sends its tiles to the generic kernel
+constexpr int STREAM_EV_CAP = STREAM_EV_CAP_C;  // event records kept per read; a read with more is walked by the exact cursor in the locus pass
 
 struct StreamArgs {
   const uint4* hdr;     // packed read headers

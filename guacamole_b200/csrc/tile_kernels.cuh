@@ -30,6 +30,11 @@
 #ifndef GUAC_TK_MINB_JOINT
 #define GUAC_TK_MINB_JOINT 5  // MODE 2 carries the call bound's FP64 arithmetic: more registers, fewer resident CTAs
 #endif
+// event records kept per read by the read pass (stream_kernels.cuh); a read with more is walked by the exact cursor
+#ifndef GUAC_STREAM_EV_CAP
+#define GUAC_STREAM_EV_CAP 16
+#endif
+constexpr int STREAM_EV_CAP_C = GUAC_STREAM_EV_CAP;
 #ifndef GUAC_TK_TL
 #define GUAC_TK_TL 512  // loci per tile
 #endif
@@ -58,8 +63,15 @@ enum : uint8_t {
   RF_FAST = 1,    // single M/=/X operator, ACGT only
   RF_HIQ = 2,     // every base quality >= 4, i.e. P(correct) >= 0.60 > 1/2 (licenses the LOD bound)
   RF_MEDIUM = 4,  // operators within {M,=,X,I,D,S,H}, ACGT only, CIGAR consistent with the sequence
-  RF_MAPQ_OK = 8  // mapq is 0 (the joint model ignores the read) or >= 8: with RF_HIQ, P(quality) P(mapq) > 1/2 at every base
+  RF_MAPQ_OK = 8, // mapq is 0 (the joint model ignores the read) or >= 8: with RF_HIQ, P(quality) P(mapq) > 1/2 at every base
+  RF_NOZEROQ = 16 // every base quality >= 1: P(correct) >= 0.2057, so (1 - p) / p <= 3.8621 (the LOD bound's term for a read
+                  // that is not RF_HIQ)
 };
+// log(1 - f + f (1 - p) / p) <= log(1 + f * LOWQ_ODDS_M1) for every base of quality >= 1
+constexpr float LOWQ_ODDS_M1 = 2.8622f;
+// weight of a tumor read with a quality-0 base in the low-quality count of a locus: any such read over a locus sends it to
+// the exact evaluation; a tile may hold 15 of them before its 16-bit counts would overflow (then the whole tile falls back)
+constexpr int ZEROQ_WEIGHT = 4096;
 static_assert(RF_MEDIUM == 4, "ss_evidence_kernel (kernels.cuh) tests this bit of the packed header");
 
 __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags) {
@@ -89,8 +101,8 @@ __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags
   const bool medium = acgt && ops_ok && !leading_ins_at_zero && read_len == s1 - s0 && seen_ref_op;
   const bool fast = medium && (c1 - c0 == 1);
   // every quality >= 4  <=>  no byte with (q & 0xFC) == 0; four qualities per aligned word, the bytes outside
-  // [s0, s1) forced high
-  bool hiq = true;
+  // [s0, s1) forced high.  Every quality >= 1  <=>  no zero byte.
+  bool hiq = true, nozero = true;
   if (s1 > s0) {
     const uint32_t* qw = reinterpret_cast<const uint32_t*>(R.qual);
     for (uint64_t w = s0 >> 2; w <= ((s1 - 1) >> 2); ++w) {
@@ -99,10 +111,12 @@ __global__ void read_fast_flags_kernel(ReadsView R, uint8_t* __restrict__ rflags
       if (w == ((s1 - 1) >> 2) && ((s1 & 3) != 0)) v |= ~((1u << (8 * (s1 & 3))) - 1);
       const uint32_t t = v & 0xFCFCFCFCu;
       if ((t - 0x01010101u) & ~t & 0x80808080u) hiq = false;
+      if ((v - 0x01010101u) & ~v & 0x80808080u) nozero = false;
     }
   }
   const int mapq = R.mapq[r];
-  rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0) | (medium ? RF_MEDIUM : 0) | ((mapq == 0 || mapq >= 8) ? RF_MAPQ_OK : 0);
+  rflags[r] = (fast ? RF_FAST : 0) | (hiq ? RF_HIQ : 0) | (medium ? RF_MEDIUM : 0) | ((mapq == 0 || mapq >= 8) ? RF_MAPQ_OK : 0) |
+              (nozero ? RF_NOZEROQ : 0);
 }
 
 
@@ -153,7 +167,7 @@ struct TileSmem {
   uint16_t ev_order[CFG::E_MAX];  // event indices bucketed by locus (2 B per event instead of a second copy)
   uint16_t slow[CFG::SLOW_MAX];
   int warp_tot[2][CFG::WARPS];
-  int n_events, n_slow, overflow, ref_has_mask, n_cand;
+  int n_events, n_slow, overflow, ref_has_mask, n_cand, n_zeroq;
   int warp_tot2[CFG::WARPS];
   // MODE 2 only, and last on purpose: the other modes are launched with offsetof(TileSmem, cov2) bytes of shared memory
   int cov2[CFG::TL + 2];    // with at most four samples: depths of samples 2 | 3 << 16
@@ -285,7 +299,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     if (MODE == 2) S.cov2[i] = 0;
   }
   for (int i = tid; i < TL + 1; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
-  if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = 0;
+  if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = S.n_zeroq = 0;
   if (tid < 4) {  // padding words behind the tile
     S.ref2[TL / 16 + (tid & 1)] = 0;
   }
@@ -379,9 +393,11 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       const int one = slot ? 65536 : 1;
       atomicAdd(&S.cov[a], one);
       atomicAdd(&S.cov[b], -one);
-      if (slot == 1 && !(rf & RF_HIQ)) {
-        atomicAdd(&S.aux[a], 1);
-        atomicAdd(&S.aux[b], -1);
+      if (slot == 1 && !(rf & RF_HIQ)) {  // tumor reads that may have a base below quality 4 over each locus
+        const int w = (rf & RF_NOZEROQ) ? 1 : ZEROQ_WEIGHT;
+        atomicAdd(&S.aux[a], w);
+        atomicAdd(&S.aux[b], -w);
+        if (w != 1 && atomicAdd(&S.n_zeroq, 1) >= 15) S.overflow = 1;
       }
     }
     if (!(rf & RF_MEDIUM)) {
@@ -392,12 +408,12 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     if (STREAM) {  // the read was compared by ss_read_events_kernel: take the events that fall inside the tile
-      if (cnt > 8) {  // more events than its slot holds: the exact cursor walks this read (rare)
+      if (cnt > STREAM_EV_CAP_C) {  // more events than its slot holds: the exact cursor walks this read (rare)
         const int i = atomicAdd(&S.n_slow, 1);
         if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)rl; else S.overflow = 1;
         continue;
       }
-      const uint2* evs = A.ev_by_read + r * 8;
+      const uint2* evs = A.ev_by_read + r * STREAM_EV_CAP_C;
       for (int j = 0; j < cnt; ++j) {
         const uint2 ev = __ldg(evs + j);
         const int l = st + (int)(ev.x & 0xFFFF);
@@ -879,9 +895,13 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
             bound += __logf(fmaf(ff, c_odds_minus_one[q], 1.0f));
           }
         }
+        // tumor reads over the locus that are not RF_HIQ: each adds at most log(1 + f * LOWQ_ODDS_M1) if its element is
+        // of the reference allele (nothing otherwise); one with a quality-0 base anywhere sends the locus to the exact path
+        const int lowq = S.aux[l] & 0xFFFF;
+        bound += (float)lowq * __logf(fmaf(ff, LOWQ_ODDS_M1, 1.0f));
         // a mid-deletion allele has empty alt bases and is never called (:233)
         const bool never_called = (best >> 8) == GUAC_ALN_MID_DELETION;
-        if (never_called || ((S.aux[l] & 0xFFFF) == 0 && bound < (float)P.tumor_odds - 0.5f)) {
+        if (never_called || (lowq < ZEROQ_WEIGHT && bound < (float)P.tumor_odds - 0.5f)) {
           top_t = bcnt;
           top_n = n_alt_normal;
           flags = 1;

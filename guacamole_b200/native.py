@@ -402,7 +402,8 @@ class Context:
 
     # -- measurement support -----------------------------------------------------
     def synth_generate(self, contig_len: int, depths: Sequence[int], tumor: Sequence[bool], seed: int, contig_id: int = 0,
-                       contig_name: str = "synth1"):
+                       contig_name: str = "synth1", profile: int = 0):
+        self.set_option("synth_profile", profile)
         d = np.asarray(depths, np.int32)
         t = np.asarray(tumor, np.uint8)
         self._check(self.lib.guac_synth_generate(self.ctx, C.c_int32(contig_id), C.c_int64(contig_len), C.c_int32(len(d)),

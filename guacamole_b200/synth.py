@@ -28,7 +28,7 @@ _M1, _M2 = U64(0xBF58476D1CE4E5B9), U64(0x94D049BB133111EB)
 _G1, _G2 = U64(0x9E3779B97F4A7C15), U64(0xC2B2AE3D27D4EB4F)
 
 # streams
-S_REF, S_START, S_READ, S_BASE, S_QUAL, S_ERR, S_SITE, S_INS = (U64(i) for i in range(1, 9))
+S_REF, S_START, S_READ, S_BASE, S_QUAL, S_ERR, S_SITE, S_INS, S_DENS, S_TAIL = (U64(i) for i in range(1, 11))
 # error thresholds on 24 bits: round(10^(-q/10) * 2^24)
 ERR_THR = {40: 1678, 30: 16777, 20: 167772, 10: 1677722}
 
@@ -88,8 +88,12 @@ def site_info(seed: int, pos: np.ndarray):
 
 
 def generate_reads(contig_len: int, depths: Sequence[int], tumor: Sequence[bool], seed: int, read_lo: int = 0,
-                   read_hi: int = None, contig_name: str = "synth1") -> ReadBatch:
-    """Reads [read_lo, read_hi) of the synthetic batch (all samples interleaved, sorted by start)."""
+                   read_hi: int = None, contig_name: str = "synth1", profile: int = 0) -> ReadBatch:
+    """Reads [read_lo, read_hi) of the synthetic batch (all samples interleaved, sorted by start).
+
+    profile 0: the workload of SURVEY.md 8(d).  profile 1: the "realistic" variant — read density modulated in 256-locus
+    blocks (depth varies like a Poisson pileup's), 15 % of reads end in 5..30 quality-2 bases with 10 % errors, 10 %
+    multi-operator reads (4 % insertions, 4 % deletions, 2 % soft clips), 1 % of reads with 15 % errors throughout."""
     N = n_reads_total(contig_len, depths)
     read_hi = N if read_hi is None else min(read_hi, N)
     read_lo = max(0, read_lo)
@@ -103,6 +107,12 @@ def generate_reads(contig_len: int, depths: Sequence[int], tumor: Sequence[bool]
     u16 = (rnd(seed, S_START, ju) & U64(0xFFFF)).astype(np.int64)
     js = j * span  # floor((j * 65536 + u16) * span / (N * 65536)) without int64 overflow
     start = js // N + ((js % N) * 65536 + u16 * span) // (N * 65536)
+    if profile == 1:  # density modulation inside 256-locus blocks, monotone in the start
+        blk = start >> 8
+        t = start & 255
+        cut = 128 + (rnd(seed, S_DENS, blk.astype(U64)) % U64(61)).astype(np.int64) - 30
+        remapped = (blk << 8) + np.where(t < cut, t * 128 // cut, 128 + (t - cut) * 128 // (256 - cut))
+        start = np.where(((blk + 1) << 8) <= span, remapped, start)
     hr = rnd(seed, S_READ, ju)
     positive = (hr & U64(1)).astype(bool)
     hap = ((hr >> U64(1)) & U64(1)).astype(np.uint8)
@@ -115,6 +125,13 @@ def generate_reads(contig_len: int, depths: Sequence[int], tumor: Sequence[bool]
     a_del = 5 + ((hr >> U64(32)) % U64(91)).astype(np.int64)
     s_clip = ((hr >> U64(40)) % U64(20)).astype(np.int64) + 1
     is_ins, is_del, is_clip = ck == 97, ck == 98, ck == 99
+    tail = np.zeros(n, np.int64)
+    noisy = np.zeros(n, bool)
+    if profile == 1:
+        is_ins, is_del, is_clip = (ck >= 90) & (ck < 94), (ck >= 94) & (ck < 98), ck >= 98
+        noisy = ((hr >> U64(48)) % U64(100)) == U64(0)
+        ht = rnd(seed, S_TAIL, ju)
+        tail = np.where(((ht >> U64(32)) % U64(100)) < U64(15), 5 + (ht % U64(26)).astype(np.int64), 0)
 
     # CIGAR words
     n_ops = np.where(is_ins | is_del, 3, np.where(is_clip, 2, 1))
@@ -160,6 +177,10 @@ def generate_reads(contig_len: int, depths: Sequence[int], tumor: Sequence[bool]
     qual = np.where(hq < 70, 40, np.where(hq < 90, 30, np.where(hq < 98, 20, 10))).astype(np.uint8)
     he = rnd(seed, S_ERR, gi)
     thr = np.where(qual == 40, ERR_THR[40], np.where(qual == 30, ERR_THR[30], np.where(qual == 20, ERR_THR[20], ERR_THR[10])))
+    in_tail = k >= (READ_LEN - tail)[:, None]
+    qual = np.where(in_tail, 2, qual).astype(np.uint8)
+    thr = np.where(in_tail, ERR_THR[10], thr)          # the quality-2 tail: 10 % errors
+    thr = np.where(noisy[:, None], np.maximum(thr, 2516582), thr)  # 15 % errors
     is_err = (he & U64(0xFFFFFF)).astype(np.int64) < thr
     err_off = (((he >> U64(24)) % U64(3)) + U64(1)).astype(np.uint8)
     code = np.where(is_err, (code + err_off) & 3, code).astype(np.uint8)
@@ -176,8 +197,9 @@ def read_window_for_loci(contig_len: int, depths: Sequence[int], lo: int, hi: in
     """Index range of reads that can overlap loci [lo, hi) (halo included)."""
     N = n_reads_total(contig_len, depths)
     span = contig_len - MARGIN
-    j_lo = max(0, (max(0, lo - READ_LEN - 16) * N) // span - 2)
-    j_hi = min(N, (hi * N) // span + 2)
+    # (profile 1 moves a start by less than a 256-locus block: the window is widened by one block on either side)
+    j_lo = max(0, (max(0, lo - READ_LEN - 16 - 256) * N) // span - 2)
+    j_hi = min(N, ((hi + 256) * N) // span + 2)
     return int(j_lo), int(j_hi)
 
 

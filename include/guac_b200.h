@@ -509,6 +509,11 @@ void* guac_stream(guac_ctx* ctx);
  *                           with the single-kernel locus pass, 0 = every candidate locus through the generic per-locus
  *                           kernels; more than four samples always take the generic kernels
  *   "sj_host_threads"       accepted and ignored (the per-site arithmetic runs on the device)
+ *   "sj_prune"              1 (default): the joint caller's locus pass drops candidate sites that certainly hold no call;
+ *                           0: every candidate reaches the site kernels (test hook)
+ *   "synth_profile"         guac_synth_generate: 0 (default) the workload of SURVEY.md 8(d); 1 its "realistic" variant (read
+ *                           density varying like a Poisson pileup's, 15 % of reads with a quality-2 tail, 10 % multi-operator
+ *                           reads, 1 % of reads with 10..20 mismatches)
  *   "compact_narrow"        1 (default): guac_reads_export_compact emits the narrow columns where the batch allows; 0: never
  *   "ss_rank_max"           somatic-standard ranks more calls than this through a bitmap over the loci instead of by
  *                           pairwise comparison (test hook; default and maximum 32768, negative restores the default) */

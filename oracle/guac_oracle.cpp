@@ -456,10 +456,11 @@ double oracle_phred_to_success_probability(int q) { return phredToSuccessProbabi
 extern "C" int oracle_synth_generate(int64_t contig_len, int32_t n_samples, const int32_t* depths, const uint8_t* tumor,
                                      const uint8_t* pattern, int32_t pattern_len, uint64_t seed, int64_t read_lo,
                                      int64_t read_hi, int64_t* start, uint32_t* cigar_off, uint32_t* cigar, uint8_t* bases_ascii,
-                                     uint8_t* qual, uint8_t* mapq, uint8_t* flags, uint8_t* sample, int n_threads) {
+                                     uint8_t* qual, uint8_t* mapq, uint8_t* flags, uint8_t* sample, int n_threads, int profile) {
   using namespace guac::synth;
   Params P;
   std::memset(&P, 0, sizeof P);
+  P.profile = profile;
   P.seed = seed;
   P.contig_len = contig_len;
   P.n_samples = n_samples;

@@ -196,7 +196,7 @@ def success_probability_to_phred(p: float) -> int:
 
 
 def synth_generate(contig_len: int, depths, tumor, seed: int, read_lo: int = 0, read_hi=None, contig_name="synth1",
-                   n_threads: int = 0) -> ReadBatch:
+                   n_threads: int = 0, profile: int = 0) -> ReadBatch:
     """C twin of guacamole_b200.synth.generate_reads (fast; used for large CPU-side samples)."""
     from guacamole_b200 import synth
     N = synth.n_reads_total(contig_len, depths)
@@ -215,7 +215,7 @@ def synth_generate(contig_len: int, depths, tumor, seed: int, read_lo: int = 0, 
     lib().oracle_synth_generate(C.c_int64(contig_len), C.c_int32(len(d)), ptr(d, i32p), ptr(t, u8p), ptr(pat, u8p),
                                 C.c_int32(len(pat)), C.c_uint64(seed), C.c_int64(read_lo), C.c_int64(read_hi), ptr(start, i64p),
                                 ptr(cigar_off, u32p), ptr(cigar, u32p), ptr(bases, u8p), ptr(qual, u8p), ptr(mapq, u8p),
-                                ptr(flags, u8p), ptr(sample, u8p), C.c_int(n_threads or (os.cpu_count() or 1)))
+                                ptr(flags, u8p), ptr(sample, u8p), C.c_int(n_threads or (os.cpu_count() or 1)), C.c_int(profile))
     return ReadBatch(n_samples=len(d), contig_names=[contig_name], contig_id=np.zeros(n, np.int32), start=start,
                      cigar_off=cigar_off, cigar=cigar[:int(cigar_off[-1])].copy(),
                      seq_off=np.arange(n + 1, dtype=np.uint64) * np.uint64(100), bases_ascii=bases, qual=qual, mapq=mapq,

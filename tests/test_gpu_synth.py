@@ -11,12 +11,13 @@ pytestmark = pytest.mark.gpu
 FIELDS = ["start", "cigar_off", "cigar", "seq_off", "bases_ascii", "qual", "mapq", "flags", "sample_id", "contig_id"]
 
 
+@pytest.mark.parametrize("profile", [0, 1])
 @pytest.mark.parametrize("contig_len,depths,tumor,seed", [(30000, (30, 60), (False, True), 3000),
                                                           (20000, (30, 30, 60, 60), (False, False, True, True), 4001)])
-def test_device_generator_matches_numpy(gpu_ctx, contig_len, depths, tumor, seed):
-    gpu_ctx.synth_generate(contig_len, depths, tumor, seed)
+def test_device_generator_matches_numpy(gpu_ctx, contig_len, depths, tumor, seed, profile):
+    gpu_ctx.synth_generate(contig_len, depths, tumor, seed, profile=profile)
     got = gpu_ctx.export_reads(["synth1"])
-    want = synth.generate_reads(contig_len, depths, tumor, seed)
+    want = synth.generate_reads(contig_len, depths, tumor, seed, profile=profile)
     for f in FIELDS:
         assert np.array_equal(getattr(got, f), getattr(want, f)), f
     assert np.array_equal(gpu_ctx.export_reference(0, 0, contig_len), synth.reference_bases(seed, 0, contig_len))

@@ -71,11 +71,17 @@ def test_generator_twins_agree():
     for (L, depths, tumor, seed, lo, hi) in [(20000, (30, 60), (False, True), 12, 0, 3000),
                                              (50_000_000, (30, 60), (False, True), 3000, 1_000_000, 1_002_000),
                                              (125_000_000, (30, 30, 60, 60), (False, False, True, True), 4001, 200_000_000, 200_001_000)]:
-        a = synth.generate_reads(L, depths, tumor, seed, lo, hi)
-        b = oracle.synth_generate(L, depths, tumor, seed, lo, hi)
-        for f in ["start", "cigar_off", "cigar", "seq_off", "bases_ascii", "qual", "mapq", "flags", "sample_id"]:
-            assert np.array_equal(getattr(a, f), getattr(b, f)), f
-        assert np.all(np.diff(a.start) >= 0)
+        for profile in (0, 1):
+            a = synth.generate_reads(L, depths, tumor, seed, lo, hi, profile=profile)
+            b = oracle.synth_generate(L, depths, tumor, seed, lo, hi, profile=profile)
+            for f in ["start", "cigar_off", "cigar", "seq_off", "bases_ascii", "qual", "mapq", "flags", "sample_id"]:
+                assert np.array_equal(getattr(a, f), getattr(b, f)), (f, profile)
+            assert np.all(np.diff(a.start) >= 0)
+            if profile == 1 and hi - lo >= 2000:  # the realistic variant's shares: multi-operator reads, quality-2 tails
+                n_ops = np.diff(a.cigar_off.astype(np.int64))
+                assert 0.06 < np.mean(n_ops > 1) < 0.14
+                tails = (a.qual.reshape(-1, 100)[:, -1] == 2)
+                assert 0.10 < tails.mean() < 0.20
     assert np.array_equal(synth.reference_bases(5, 100, 1000), oracle.synth_reference(5, 100, 1000))
 
 
