@@ -39,6 +39,7 @@ struct RefView {
   int64_t offset;
   int64_t len;
   const uint32_t* bad;  // bit g: loci [offset + 16 g, +16) hold a base that is not A C G T (nullptr where unused)
+  const uint32_t* ref2; // 2-bit copy of the window, 16 loci per word (stream form; nullptr where unused)
   __device__ __forceinline__ uint8_t at(int64_t locus) const {
     int64_t i = locus - offset;
     return (i >= 0 && i < len) ? __ldg(bases + i) : (uint8_t)0;

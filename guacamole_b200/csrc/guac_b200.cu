@@ -257,6 +257,7 @@ int sync_refs(guac_ctx* ctx) {
     r.offset = kv.second.offset;
     r.len = kv.second.len;
     r.bad = kv.second.refbad;
+    r.ref2 = kv.second.ref2;
     v.push_back(r);
   }
   GUAC_TRY(upload(ctx, ctx->d_refs, v.data(), v.size()));
@@ -536,6 +537,7 @@ int run_read_pass(guac_ctx* ctx) {
     SA.ref.offset = it->second.offset;
     SA.ref.len = it->second.len;
     SA.ref.bad = it->second.refbad;
+    SA.ref.ref2 = it->second.ref2;
     SA.ref2 = it->second.ref2;
     SA.events = ctx->b_bins.as<uint2>();
     SA.n_events = ctx->b_bin_count.as<uint8_t>();
@@ -2088,6 +2090,7 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
   ref.offset = ref_offset;
   ref.len = ref_len;
   ref.bad = nullptr;
+  ref.ref2 = nullptr;
   RangeDev rg;
   rg.start = range_start;
   rg.end = range_end;

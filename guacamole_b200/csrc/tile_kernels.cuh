@@ -32,7 +32,7 @@
 #endif
 // event records kept per read by the read pass (stream_kernels.cuh); a read with more is walked by the exact cursor
 #ifndef GUAC_STREAM_EV_CAP
-#define GUAC_STREAM_EV_CAP 16
+#define GUAC_STREAM_EV_CAP 8
 #endif
 constexpr int STREAM_EV_CAP_C = GUAC_STREAM_EV_CAP;
 #ifndef GUAC_TK_TL
@@ -408,7 +408,38 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     if (STREAM) {  // the read was compared by ss_read_events_kernel: take the events that fall inside the tile
-      if (cnt > STREAM_EV_CAP_C) {  // more events than its slot holds: the exact cursor walks this read (rare)
+      if (cnt > STREAM_EV_CAP_C && (rf & RF_FAST) && ref.ref2 != nullptr) {
+        // More mismatches than the read's slot holds (a mis-mapped or very noisy read), one aligned operator: the compare of
+        // the read pass again, here, for the part of the read inside the tile — against the 2-bit reference in HBM / L2
+        const long long ref_rel = (long long)t0 + st - (long long)ref.offset;  // reference-window index of the read's first locus
+        const int ca = (int)max(max((long long)a, (long long)st - ref_rel), (long long)st);
+        const int cb = (int)min((long long)min(en, n_ev_loci), (long long)st + ((long long)ref.len - ref_rel));
+        if (ca < cb) {
+          const uint64_t rbit = 2 * (s0 + (uint64_t)(ca - st));
+          const uint32_t* rw = reinterpret_cast<const uint32_t*>(R.bases2) + (rbit >> 5);
+          const uint64_t fbit = 2 * (uint64_t)(ref_rel + (ca - st));
+          const uint32_t* fw = ref.ref2 + (fbit >> 5);
+          const int rsh = (int)(rbit & 31), fsh = (int)(fbit & 31);
+          uint32_t rlo = __ldg(rw), flo = __ldg(fw);
+          for (int l = ca; l < cb; l += 16) {
+            const uint32_t rhi = __ldg(++rw), fhi = __ldg(++fw);
+            const uint32_t rd = __funnelshift_r(rlo, rhi, rsh);
+            const uint32_t x = rd ^ __funnelshift_r(flo, fhi, fsh);
+            rlo = rhi;
+            flo = fhi;
+            uint32_t m = (x | (x >> 1)) & 0x55555555u;
+            if (cb - l < 16) m &= (1u << (2 * (cb - l))) - 1;
+            while (m) {
+              const int bit = __ffs(m) - 1;
+              m &= m - 1;
+              const int ll = l + (bit >> 1);
+              push_event(ll, rl, slot, GUAC_ALN_MISMATCH, (rd >> bit) & 3, s0_rel + (uint32_t)(ll - st));
+            }
+          }
+        }
+        continue;
+      }
+      if (cnt > STREAM_EV_CAP_C) {  // ... of a read with several operators: the exact cursor walks it (rare)
         const int i = atomicAdd(&S.n_slow, 1);
         if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)rl; else S.overflow = 1;
         continue;
