@@ -28,6 +28,7 @@
 #include "assembly_kernels.cuh"
 #include "compact_kernels.cuh"
 #include "support_kernels.cuh"
+#include "partition_kernels.cuh"
 
 using namespace guac;
 
@@ -2126,6 +2127,7 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 #include "assembly_entry.inl"
 #include "compact_entry.inl"
 #include "support_entry.inl"
+#include "partition_entry.inl"
 
 namespace {
 cudaError_t configure_device_functions() {

@@ -609,6 +609,35 @@ class Context:
                                                 C.byref(out) if want_loci else None, C.byref(n)))
         return hist, tot, (_take(self.lib, self.ctx, out, VARIANT_LOCUS_DTYPE, n.value) if want_loci else None)
 
+    # -- coverage-aware partitioning -----------------------------------------------------
+    def _intervals(self, out, part, n):
+        r = _take(self.lib, self.ctx, out, np.dtype([("contig_id", np.int32), ("_pad", np.int32), ("start", np.int64), ("end", np.int64)]), n)
+        p = _take(self.lib, self.ctx, part, np.int32, n)
+        return [(int(a["contig_id"]), int(a["start"]), int(a["end"]), int(b)) for a, b in zip(r, p)]
+
+    def take_loci(self, coverages, max_regions_per_partition: int, trim_ranges: bool = False):
+        """guac_take_loci: [(contig_id, locus, depth, starts)] -> [(contig_id, start, end, partition)] (loci/set/TakeLociIterator.scala)."""
+        c = np.asarray([x[0] for x in coverages], np.int32)
+        l = np.asarray([x[1] for x in coverages], np.int64)
+        d = np.asarray([x[2] for x in coverages], np.int32)
+        s = np.asarray([x[3] for x in coverages], np.int32)
+        out, part, n, npart = C.c_void_p(), C.c_void_p(), C.c_int64(), C.c_int32()
+        self._check(self.lib.guac_take_loci(self.ctx, c.ctypes.data_as(C.c_void_p), l.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p),
+                                            s.ctypes.data_as(C.c_void_p), C.c_int64(len(c)), C.c_int32(max_regions_per_partition),
+                                            C.c_int32(int(trim_ranges)), C.byref(out), C.byref(part), C.byref(n), C.byref(npart)))
+        return self._intervals(out, part, n.value), npart.value
+
+    def capped_partitioning(self, loci: Sequence[Tuple[int, int, int]], half_window: int = 0, max_reads_per_partition: int = 100000,
+                            trim_ranges: bool = False):
+        """guac_capped_partitioning -> ([(contig_id, start, end, partition)], number of partitions)
+        (loci/partitioning/CappedRegionsPartitioner.scala:66-88)."""
+        r = make_ranges(loci)
+        out, part, n, npart = C.c_void_p(), C.c_void_p(), C.c_int64(), C.c_int32()
+        self._check(self.lib.guac_capped_partitioning(self.ctx, r, C.c_int32(len(loci)), C.c_int32(half_window),
+                                                      C.c_int32(max_reads_per_partition), C.c_int32(int(trim_ranges)), C.byref(out),
+                                                      C.byref(part), C.byref(n), C.byref(npart)))
+        return self._intervals(out, part, n.value), npart.value
+
     # -- callers -----------------------------------------------------------------
     def somatic_standard(self, ranges: Sequence[Tuple[int, int, int]], params: Optional[SSParamsC] = None,
                          want_summary: bool = False):

@@ -98,6 +98,20 @@ def shard(batch: ReadBatch, loci: Sequence[Range], world_size: int, half_window:
     return out
 
 
+def assign_partitions(intervals: Sequence[Tuple[int, int, int, int]], n_partitions: int, world_size: int) -> Dict[int, List[Range]]:
+    """rank -> loci ranges: the loci sets of the capped partitioner (`Context.capped_partitioning`,
+    loci/partitioning/CappedRegionsPartitioner.scala:66-88 — each holds at most maxReadsPerPartition reads) dealt to the
+    ranks in contiguous blocks, so every rank gets about the same number of reads whatever the coverage looks like."""
+    out: Dict[int, List[Range]] = {r: [] for r in range(world_size)}
+    for c, s, e, p in intervals:
+        rank = min(world_size - 1, p * world_size // max(1, n_partitions))
+        if out[rank] and out[rank][-1][0] == c and out[rank][-1][2] == s:
+            out[rank][-1] = (c, out[rank][-1][1], e)
+        else:
+            out[rank].append((c, s, e))
+    return out
+
+
 def gather_calls(per_rank_results: Sequence[dict]) -> dict:
     """Host-side gather of the per-rank sparse results: concatenate, re-base the allele arena offsets,
     sort by (contig, start)."""

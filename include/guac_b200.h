@@ -494,6 +494,24 @@ int guac_vaf_histogram(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, 
                        int32_t min_vaf_percent, int64_t* out_hist, int64_t* out_n_variant_loci, guac_variant_locus** out_loci,
                        int64_t* n_loci);
 
+/* ---- coverage-aware loci partitioning -------------------------------------------
+ * The "capped" LociPartitioner (M/loci/partitioning/CappedRegionsPartitioner.scala:66-88, the reference's default):
+ * CoverageRDD.traversalCoverage (M/readsets/rdd/CoverageRDD.scala:120-143, M/readsets/iterator/ContigCoverageIterator.scala:28-117)
+ * gives every eligible locus a Coverage(depth, starts) over the uploaded reads of all samples, a read counting at every
+ * locus of [start - half_window, end + half_window); TakeLociIterator (M/loci/set/TakeLociIterator.scala:25-196) then cuts
+ * greedy loci sets of at most max_reads_per_partition reads, dropping loci deeper than that.  `loci` must be in contig
+ * order (the reference visits contigs in name order; here the caller's contig ids are the order).  Output: intervals
+ * out_ranges[i] of loci set out_partition[i], in order; with trim_ranges = 0 one interval per (loci set, stretch of a
+ * contig) spanning uncovered loci, as the reference's default.  The result feeds the shards of a multi-GPU run in place of
+ * UniformPartitioner's ranges when coverage is uneven. */
+int guac_capped_partitioning(guac_ctx* ctx, const guac_range* loci, int32_t n_ranges, int32_t half_window, int32_t max_reads_per_partition,
+                             int32_t trim_ranges, guac_range** out_ranges, int32_t** out_partition, int64_t* n_out, int32_t* n_partitions);
+/* TakeLociIterator alone, over (position, coverage) pairs the caller already has (M/loci/set/TakeLociIterator.scala:25-196;
+ * the form TakeLociIteratorSuite feeds): entries sorted by (contig, locus), uncovered loci absent. */
+int guac_take_loci(guac_ctx* ctx, const int32_t* contig_id, const int64_t* locus, const int32_t* depth, const int32_t* starts, int64_t n,
+                   int32_t max_regions_per_partition, int32_t trim_ranges, guac_range** out_ranges, int32_t** out_partition, int64_t* n_out,
+                   int32_t* n_partitions);
+
 /* ---- measurement support ----------------------------------------------------
  * These have no counterpart in the reference: they exist so that bench.py and the
  * tests can generate SURVEY.md 8(d)'s seeded synthetic reads directly in HBM, read them

@@ -404,3 +404,102 @@ def vaf_histogram(batch: ReadBatch, reference: Reference, loci, bins=20, min_rea
             tot[s] += 1
             recs.append((s, int(c), int(x), np.float32(vaf)))
     return hist, tot, recs
+
+
+# ---- coverage-aware ("capped") partitioning, restated literally; pure Python: small cases only ------------
+def contig_coverage(intervals, half_window=0, eligible=None):
+    """ContigCoverageIterator (M/readsets/iterator/ContigCoverageIterator.scala:28-117) restricted to `eligible` loci (its
+    `intersect`, M/readsets/rdd/CoverageRDD.scala:134-137): [(locus, depth, starts)] for every evaluated locus with coverage.
+    An interval counts towards depth at every locus of [start - halfWindow, end + halfWindow) and towards starts at the first
+    EVALUATED one of them.  `intervals` sorted by start; `eligible` a sorted iterable of loci (None: every locus)."""
+    last = 0
+    for s, _ in intervals:
+        if s < last:
+            raise ValueError(f"Consecutive regions rewinding from {last} to {s}")  # RegionsNotSortedException (:71-76)
+        last = s
+    if not intervals:
+        return []
+    if eligible is None:
+        eligible = range(max(0, min(s for s, _ in intervals) - half_window), max(e for _, e in intervals) + half_window)
+    counted, out = set(), []
+    for x in eligible:
+        covering = [i for i, (s, e) in enumerate(intervals) if s <= x + half_window and e > max(0, x - half_window)]
+        if covering:
+            out.append((x, len(covering), sum(1 for i in covering if i not in counted)))
+            counted.update(covering)
+    return out
+
+
+def take_loci(coverages, max_regions_per_partition, trim_ranges=False):
+    """TakeLociIterator (M/loci/set/TakeLociIterator.scala:25-196), literally: `coverages` = [(contig, locus, depth, starts)]
+    sorted by (contig, locus) -> list of loci sets, each a list of (contig, start, end) intervals in the order they were
+    built."""
+    by_contig, order = {}, []
+    for c, x, d, st in coverages:
+        if c not in by_contig:
+            by_contig[c] = []
+            order.append(c)
+        by_contig[c].append((x, d, st))
+    heads = {c: 0 for c in order}
+
+    def take(contig, num_regions, drop_above):  # takeLoci (:108-196)
+        its, intervals, cur, cur_iv = by_contig[contig], [], 0, None
+        while heads[contig] < len(its):
+            locus, depth, starts = its[heads[contig]]
+            new = depth if cur == 0 else starts
+            if cur + new > num_regions:
+                if cur_iv:
+                    intervals.append(cur_iv)
+                    cur_iv = None
+                if new > drop_above:
+                    heads[contig] += 1
+                else:
+                    return (cur, intervals) if intervals else None
+            else:
+                cur += new
+                if cur_iv and (not trim_ranges or locus == cur_iv[1]):
+                    cur_iv = (cur_iv[0], locus + 1)
+                else:
+                    if cur_iv:
+                        intervals.append(cur_iv)
+                    cur_iv = (locus, locus + 1)
+                heads[contig] += 1
+        if cur_iv:
+            intervals.append(cur_iv)
+        return (cur, intervals) if intervals else None
+
+    sets, ci = [], 0
+    while ci < len(order):  # _advance (:36-100), once per loci set
+        cur_regions, contigs, done = 0, [], False
+        while ci < len(order) and not done:
+            c = order[ci]
+            got = take(c, max_regions_per_partition - cur_regions, max_regions_per_partition)
+            if got is None:
+                if heads[c] < len(by_contig[c]):
+                    done = True
+                else:
+                    ci += 1
+            else:
+                cur_regions += got[0]
+                contigs += [(c, a, b) for a, b in got[1]]
+        if contigs:
+            sets.append(contigs)
+        elif not done:
+            break
+    return sets
+
+
+def capped_partitioning(batch: ReadBatch, loci, half_window=0, max_reads_per_partition=100000, trim_ranges=False):
+    """CappedRegionsPartitioner.partition (M/loci/partitioning/CappedRegionsPartitioner.scala:66-88): coverage of all the
+    batch's reads over the eligible loci, then TakeLociIterator.  -> [(contig_id, start, end, partition)]."""
+    ends = batch.ends()
+    cov = []
+    for c in sorted({r[0] for r in loci}):
+        sel = np.flatnonzero(batch.contig_id == c)
+        intervals = [(int(batch.start[i]), int(ends[i])) for i in sel]
+        eligible = [x for (cc, s, e) in loci if cc == c for x in range(s, e)]
+        cov += [(c, x, d, st) for x, d, st in contig_coverage(intervals, half_window, eligible)]
+    out = []
+    for p, contigs in enumerate(take_loci(cov, max_reads_per_partition, trim_ranges)):
+        out += [(c, a, b, p) for c, a, b in contigs]
+    return out
