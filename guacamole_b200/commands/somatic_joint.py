@@ -113,7 +113,7 @@ def java_g8(x: float) -> str:
         return "Infinity" if x > 0 else "-Infinity"
     if x == 0:
         return "0.0000000"
-    d = Decimal(repr(x))
+    d = Decimal(x)  # the exact value of the double, as the JVM's Formatter takes it
     exp = d.adjusted()
     rounded = d.quantize(Decimal(1).scaleb(exp - 7), rounding=ROUND_HALF_UP)
     exp = rounded.adjusted()
@@ -123,16 +123,31 @@ def java_g8(x: float) -> str:
     return f"{mant:.7f}e{'+' if exp >= 0 else '-'}{abs(exp):02d}"
 
 
+def java_fixed(x: float, frac: int) -> str:
+    """Java's String.format("%.<frac>f", x): HALF_UP on the exact value of the double (Python's own formatting rounds
+    half-even: 0.625 -> "0.62", the JVM prints "0.63")."""
+    if math.isnan(x):
+        return "NaN"
+    if math.isinf(x):
+        return "Infinity" if x > 0 else "-Infinity"
+    q = Decimal(x).quantize(Decimal(1).scaleb(-frac), rounding=ROUND_HALF_UP)
+    s = f"{q:.{frac}f}"
+    return s[1:] if s.startswith("-") and float(q) == 0 else s
+
+
 def format_vcf_double(d: float) -> str:
     """htsjdk VCFEncoder.formatVCFDouble."""
     if d < 1:
         if d < 0.01:
             if abs(d) >= 1e-20:
-                m, e = f"{d:.3e}".split("e")
-                return f"{m}e{e[0]}{int(e[1:]):02d}"
+                dd = Decimal(d)
+                exp = dd.adjusted()
+                r = dd.quantize(Decimal(1).scaleb(exp - 3), rounding=ROUND_HALF_UP)
+                exp = r.adjusted()
+                return f"{r.scaleb(-exp):.3f}e{'+' if exp >= 0 else '-'}{abs(exp):02d}"
             return "0.00"
-        return f"{d:.3f}"
-    return f"{d:.2f}"
+        return java_fixed(d, 3)
+    return java_fixed(d, 2)
 
 
 def _allele_str(x: str) -> str:
@@ -203,7 +218,7 @@ def vcf_row(ev: dict, contig_names: Sequence[str], sample_names: Sequence[str], 
                     a1 = a2 = ref
             else:
                 a1, a2 = (ref, alt) if se["triggered"] else (ref, ref)
-            vals["RL"] = ",".join("[" + "|".join(f"{_allele_str(a)}->{f:.2f}" for a, f in m) + f"]={java_g8(p)}"
+            vals["RL"] = ",".join("[" + "|".join(f"{_allele_str(a)}->{java_fixed(f, 2)}" for a, f in m) + f"]={java_g8(p)}"
                                   for m, p in zip(mixtures, se["posteriors"]))
             vals["TRIGGERED"] = ("EXPRESSED" if kind == TUMOR_RNA else "YES") if se["triggered"] else "NO"
         vals["GT"] = "/".join(sorted([gt_index(a1), gt_index(a2)]))

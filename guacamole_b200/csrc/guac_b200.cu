@@ -2128,6 +2128,7 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 #include "compact_entry.inl"
 #include "support_entry.inl"
 #include "partition_entry.inl"
+#include "host_stage.inl"
 
 namespace {
 cudaError_t configure_device_functions() {

@@ -606,6 +606,79 @@ int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out);
 /* Copies [offset, offset+len) of a contig's reference window to `dst` (host). */
 int guac_ref_export(guac_ctx* ctx, int32_t contig_id, int64_t offset, int64_t len, uint8_t* dst);
 
+/* ---- host stages either side of the device path (no GPU work; usable without a context) -------------------
+ * One partition's decoded SAM records, column-wise, as a JNI shim copies them out of htsjdk SAMRecords — the inputs of
+ * Read.apply (M/reads/Read.scala:63-116). */
+typedef struct {
+  int64_t n_records;
+  int32_t n_samples;
+  int32_t _pad;
+  const uint16_t* sam_flags;       /* [n] SAM FLAG: 0x1 paired, 0x4 unmapped, 0x10 reverse strand, 0x200 failed QC, 0x400 duplicate */
+  const int32_t* reference_index;  /* [n] getReferenceIndex; < 0: none (the contig ids of this library) */
+  const int64_t* alignment_start;  /* [n] getAlignmentStart, 1-based */
+  const uint8_t* mapping_quality;  /* [n] */
+  const uint32_t* cigar_off;       /* [n + 1] */
+  const uint32_t* cigar;           /* BAM-encoded operators */
+  const uint64_t* seq_off;         /* [n + 1] */
+  const uint8_t* bases_ascii;      /* getReadString bytes */
+  const uint8_t* base_qualities;   /* getBaseQualities (Phred, not +33) */
+  const uint8_t* sample_id;        /* [n] */
+} guac_sam_records;
+
+/* InputConfig (M/readsets/io/InputConfig.scala:20-45) as ReadSets.filterRDD applies it (M/readsets/ReadSets.scala:272-304) */
+typedef struct {
+  int32_t non_duplicate;                /* drop reads with the duplicate bit */
+  int32_t passed_vendor_quality_checks; /* drop reads with the failed-QC bit */
+  int32_t is_paired;                    /* keep paired-end reads only */
+  int32_t min_alignment_quality;        /* > 0: keep mapped reads with at least this mapping quality */
+  const guac_range* overlaps_loci;      /* n_overlaps_loci > 0: keep reads that overlap one of these ranges */
+  int32_t n_overlaps_loci;
+  int32_t _pad;
+} guac_read_filters;
+
+/*
+ * Read.apply + ReadSets.filterRDD + the partition's (contig, start) order (M/readsets/rdd/PartitionedRegions.scala:186-208)
+ * + the packer: mapped records that pass the filters become one guac_read_batch_compact (narrow columns and 2- / 4-bit
+ * quality codes where the reads allow them), built on n_threads host threads (<= 0: one per core).  With a context the
+ * columns live in its pinned pool (release each with guac_free); with ctx == NULL on the C heap (guac_host_free).
+ * Feed the result to guac_reads_upload_compact.
+ */
+int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* records, const guac_read_filters* filters, int32_t n_threads,
+                    guac_read_batch_compact* out, int64_t* n_kept);
+void guac_host_free(void* p);
+
+/* SomaticGenotypeFilter.SomaticGenotypeFilterArguments (M/filters/somatic/SomaticGenotypeFilter.scala:34-80); < 0 = not set */
+typedef struct {
+  int32_t min_likelihood;                 /* --min-likelihood, not set */
+  int32_t min_vaf;                        /* --min-vaf, 0 */
+  int32_t min_average_mapping_quality;    /* 20 */
+  int32_t min_average_base_quality;       /* 20 */
+  int32_t min_tumor_read_depth;           /* 5 */
+  int32_t min_normal_read_depth;          /* 5 */
+  int32_t max_tumor_read_depth;           /* Int.MaxValue */
+  int32_t min_tumor_alternate_read_depth; /* not set */
+  int32_t maximum_median_mismatches;      /* not set */
+  int32_t _pad;
+} guac_ss_filter_params;
+/* SomaticGenotypeFilter.apply (M/filters/somatic/SomaticGenotypeFilter.scala:82-130, with the reference's quirk that the
+ * "average base quality" filter tests meanMappingQuality): keep[i] = 1 for the calls that pass. */
+int guac_ss_genotype_filter(const guac_ss_filter_params* params, const guac_ss_call* calls, int64_t n, uint8_t* keep);
+/* The header line and data rows the reference's VCF writer renders for the (kept) calls
+ * (M/variants/CalledSomaticAllele.scala:45-64, M/variants/GenotypeOutputArgs.scala:86-113), '\n' separated.  Text functions
+ * write into the caller's buffer: *needed always receives the length; GUAC_E_OOM when cap is too small (call again). */
+int guac_ss_vcf_rows(const guac_ss_call* calls, int64_t n, const uint8_t* keep /* may be NULL: all */, const char* arena,
+                     const char* const* contig_names, const char* sample_name, char* out_text, int64_t cap, int64_t* needed);
+/* VCFOutput.writeVcf's rows for guac_somatic_joint's records (M/jointcaller/VCFOutput.scala:97-100,127-413 through htsjdk
+ * 2.6.1): include_pooled_* < 0 = the caller's default (more than one sample of the kind, SomaticJointCaller.scala:223);
+ * somatic_genotype_policy 0 = presence (default), 1 = trigger. */
+int guac_sj_vcf_rows(const guac_sj_params* params, const guac_sj_allele_evidence* alleles, int64_t n_alleles,
+                     const guac_sj_sample_evidence* samples, const char* arena, const char* const* contig_names,
+                     const char* const* sample_names, int32_t include_pooled_normal, int32_t include_pooled_tumor,
+                     int32_t somatic_genotype_policy, char* out_text, int64_t cap, int64_t* needed);
+/* Number formatting as the JVM does it (HALF_UP on the exact decimal expansion): kind 0 String.format("%.8g"), 1 htsjdk
+ * VCFEncoder.formatVCFDouble, 2 String.format("%.2f").  Test support for the two row writers. */
+int guac_format_double(int32_t kind, double x, char* out, int32_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -228,7 +228,7 @@ def synth_reference(seed: int, lo: int, hi: int) -> np.ndarray:
     return out
 
 
-def somatic_joint(batch: ReadBatch, reference: Reference, loci, params, force_loci=()):
+def somatic_joint(batch: ReadBatch, reference: Reference, loci, params, force_loci=(), raw_records=False):
     """SomaticJoint.makeCalls over one partition -> list of per-allele evidence dicts
     (guacamole_b200.commands.somatic_joint.decode form) plus the number of loci visited."""
     from guacamole_b200.commands import somatic_joint as sj
@@ -242,6 +242,8 @@ def somatic_joint(batch: ReadBatch, reference: Reference, loci, params, force_lo
     lib().oracle_free(arena)
     alleles = _take(al, sj.ALLELE_EVIDENCE_DTYPE, na.value)
     samples = _take(sm, sj.SAMPLE_EVIDENCE_DTYPE, ns.value)
+    if raw_records:
+        return alleles, samples, arena_b, nv.value
     return sj.decode(alleles, samples, arena_b, batch.n_samples), nv.value
 
 
