@@ -193,6 +193,35 @@ def oracle_threads_rate(prepare, n_threads, base, contig_len, target_s, calib=20
     return {"value": loci / wall, "loci": int(loci), "seconds": wall, "window": [base, base + n_threads * w]}
 
 
+def e2e_with_packer(ctx, timed, args, mbp: int = 5):
+    """The end-to-end leg from where a shim really starts: decoded SAM records (ASCII bases, one quality byte per base, SAM
+    flags) -> guac_pack_reads (Read.apply, the ingest filters, the compact wire form; all host cores) -> guac_reads_upload_compact
+    -> guac_somatic_standard, on a shard of the workload small enough to build its records on the host in seconds."""
+    import numpy as np
+    from guacamole_b200 import host_stage as hs
+    from oracle import oracle
+    n = mbp * 1_000_000
+    batch = oracle.synth_generate(n, DEPTHS, TUMOR, 3000)
+    records, keepalive = hs.sam_records_of(batch)
+    from guacamole_b200.io import ContigWindow, Reference
+    ctx.upload_reference(Reference({"synth1": ContigWindow("synth1", 0, oracle.synth_reference(3000, 0, n), n)}), ["synth1"])
+    pack_s = []
+
+    def step():
+        t = time.perf_counter()
+        packed, kept = hs.pack_reads(records, ctx=ctx, non_duplicate=True, passed_vendor_quality_checks=True, is_paired=True)
+        pack_s.append(time.perf_counter() - t)
+        ctx.upload_reads_compact(packed)
+        out = ctx.somatic_standard([(0, 0, n)])
+        hs.free_packed(packed, ctx=ctx)
+        return out["n_visited"], len(out["calls"])
+    ms, _, outs = timed(step, 2, 1)
+    raw_bytes = sum(int(a.nbytes) for a in keepalive)
+    return {"form": f"from SAM-record columns through the host packer (guac_pack_reads, {os.cpu_count()} threads), {mbp} Mbp shard of the workload",
+            "value": sum(o[0] for o in outs) / (ms / 1000.0), "unit": "loci/s", "host_pack_ms": 1000.0 * sum(pack_s[-2:]) / 2,
+            "sam_record_bytes": raw_bytes, "reads": int(batch.n_reads)}
+
+
 def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
     """The other configurations of BASELINE.json through their own callers, each with the headline's blocks: configs[3]'s
     per-GPU shape (somatic-joint, 2 normal + 2 tumor at 30/30/60/60), configs[1] (germline toy caller, one 30x sample) and
@@ -528,6 +557,29 @@ def main():
                "note": f"reads in the compact wire form (guac_read_batch_compact, {hb.qual_bits}-bit qualities) from pinned host "
                        "memory each step; reference genome resident"}
         ctx.free_reads_compact_struct(hb)
+        # the same leg with the wider quality forms of the wire format (real, unbinned qualities travel as 4-bit codes when
+        # a batch holds at most 16 distinct values, one byte per base otherwise), and with the host packer inside
+        variants = []
+        for bits in (4, 8):
+            ctx.set_option("compact_min_qual_bits", bits)
+            hv = ctx.export_reads_compact_struct()
+            ctx.set_option("compact_min_qual_bits", 2)
+
+            def step_v():
+                ctx.upload_reads_compact(hv)
+                out = ctx.somatic_standard(ranges)
+                return out["n_visited"], len(out["calls"])
+            v_ms, _, v_outs = timed(step_v, 2, 1)
+            v_loci = torch.tensor([float(sum(o[0] for o in v_outs))], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(v_loci, op=dist.ReduceOp.SUM)
+            variants.append({"form": f"{hv.qual_bits}-bit qualities", "value": float(v_loci.item()) / (v_ms / 1000.0), "unit": "loci/s",
+                             "h2d_bytes_per_step": int(hv.wire_bytes(n_bases, n_cigar))})
+            ctx.free_reads_compact_struct(hv)
+        if rank == 0 and world == 1:
+            variants.append(e2e_with_packer(ctx, timed, args))
+            ctx.synth_generate(contig_len, DEPTHS, TUMOR, seed)  # (the packer leg uploaded its own shard: restore the workload)
+        e2e["variants"] = variants
 
     strong_check = None
     if strong:

@@ -300,8 +300,9 @@ int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out) {
       }
       ++distinct;
     }
-  if (distinct <= 16 && n_bases > 0) {
-    out->qual_bits = distinct <= 4 ? 2 : 4;
+  // (opt_compact_min_qual_bits: measurement hook — the 4-bit and 8-bit forms of a batch whose qualities would fit 2 bits)
+  if (distinct <= 16 && n_bases > 0 && ctx->opt_compact_min_qual_bits < 8) {
+    out->qual_bits = (distinct <= 4 && ctx->opt_compact_min_qual_bits <= 2) ? 2 : 4;
     const int per_byte = 8 / out->qual_bits;
     const size_t packed = (size_t)((n_bases + per_byte - 1) / per_byte);
     GUAC_TRY(ensure(ctx, d_qpacked, packed + 16));
@@ -314,6 +315,7 @@ int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out) {
     GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->qual), d_qpacked.p, packed));
   } else {
     out->qual_bits = 8;
+    std::memset(out->qual_table, 0, sizeof out->qual_table);
     GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->qual), ctx->b_qual.p, (size_t)n_bases));
   }
   GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->mapq), ctx->b_mapq.p, (size_t)n));

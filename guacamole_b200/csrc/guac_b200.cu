@@ -101,6 +101,7 @@ struct guac_ctx {
   DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
   DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
   int64_t opt_compact_narrow = 1;
+  int64_t opt_compact_min_qual_bits = 2;  // guac_reads_export_compact: 2 (default) the narrowest form the qualities allow; 4 / 8 force wider ones
   int64_t opt_sj_host_threads = 0;  // 0: as many as the host has cores, at most 32
   std::vector<RangeDev> plan_ranges;            // host copy of the current call's range table (make_plan)
   DevBuf r_bitmap, r_counts, r_prefix, r_rank;  // rank_by_slot
@@ -1792,6 +1793,9 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
   } else if (n == "sj_impl") {
     if (value < 0 || value > 2) return fail(ctx, GUAC_E_INVALID_INPUT, "sj_impl must be 0, 1 or 2");
     ctx->opt_sj_impl = value;
+  } else if (n == "compact_min_qual_bits") {
+    if (value != 2 && value != 4 && value != 8) return fail(ctx, GUAC_E_INVALID_INPUT, "compact_min_qual_bits must be 2, 4 or 8");
+    ctx->opt_compact_min_qual_bits = value;
   } else if (n == "compact_narrow") {
     ctx->opt_compact_narrow = value != 0;
   } else if (n == "ss_rank_max") {

@@ -266,26 +266,62 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   std::vector<uint64_t> base_off((size_t)n + 1, 0);
   std::vector<int64_t> wire_off((size_t)n + 1, 0);
   std::vector<uint8_t> implicit((size_t)n, 0);
+  const int64_t len0 = n ? (int64_t)(in->seq_off[idx[0] + 1] - in->seq_off[idx[0]]) : 0;
+  // per chunk: lengths, flags and the chunk's totals; then the offsets from the totals' prefix (two passes, all threads)
+  struct ChunkTotals {
+    uint64_t bases = 0;
+    int64_t words = 0, wire_words = 0;
+    bool uniform = true, ops_fit8 = true, too_long = false;
+  };
+  std::vector<ChunkTotals> chunk((size_t)n_threads);
+  std::vector<std::pair<int64_t, int64_t>> bounds((size_t)n_threads, {0, 0});
+  host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
+    ChunkTotals c;
+    for (int64_t k = lo; k < hi; ++k) {
+      const int64_t i = idx[(size_t)k];
+      const int64_t len = (int64_t)(in->seq_off[i + 1] - in->seq_off[i]);
+      const int64_t ops = (int64_t)in->cigar_off[i + 1] - (int64_t)in->cigar_off[i];
+      c.too_long = c.too_long || len > 65535 || ops > 65535;
+      c.uniform = c.uniform && len == len0;
+      c.ops_fit8 = c.ops_fit8 && ops >= 1 && ops <= 255;
+      implicit[(size_t)k] = ops == 1 && in->cigar[in->cigar_off[i]] == ((uint32_t)len << 4) && len < (1 << 28);
+      c.bases += (uint64_t)len;
+      c.words += ops;
+      c.wire_words += implicit[(size_t)k] ? 0 : ops;
+    }
+    chunk[(size_t)t] = c;
+    bounds[(size_t)t] = {lo, hi};
+  });
   bool uniform = n > 0, ops_fit8 = true;
-  int64_t len0 = n ? (int64_t)(in->seq_off[idx[0] + 1] - in->seq_off[idx[0]]) : 0;
-  for (int64_t k = 0; k < n; ++k) {
-    const int64_t i = idx[(size_t)k];
-    const int64_t len = (int64_t)(in->seq_off[i + 1] - in->seq_off[i]);
-    const int64_t ops = (int64_t)in->cigar_off[i + 1] - (int64_t)in->cigar_off[i];
-    if (len > 65535 || ops > 65535) return failp(GUAC_E_UNSUPPORTED, "a read longer than 65535 bases or CIGAR operators (wire-form limit)");
-    uniform = uniform && len == len0;
-    ops_fit8 = ops_fit8 && ops >= 1 && ops <= 255;
-    implicit[(size_t)k] = ops == 1 && in->cigar[in->cigar_off[i]] == ((uint32_t)len << 4) && len < (1 << 28);
-    base_off[(size_t)k + 1] = base_off[(size_t)k] + (uint64_t)len;
-    wire_off[(size_t)k + 1] = wire_off[(size_t)k] + ops;
+  for (auto& c : chunk) {
+    if (c.too_long) return failp(GUAC_E_UNSUPPORTED, "a read longer than 65535 bases or CIGAR operators (wire-form limit)");
+    uniform = uniform && c.uniform;
+    ops_fit8 = ops_fit8 && c.ops_fit8;
   }
   const bool narrow_ops = ops_fit8 && n > 0;
-  if (narrow_ops) {
-    wire_off[0] = 0;
-    for (int64_t k = 0; k < n; ++k) {
-      const int64_t i = idx[(size_t)k];
-      wire_off[(size_t)k + 1] = wire_off[(size_t)k] + (implicit[(size_t)k] ? 0 : (int64_t)in->cigar_off[i + 1] - (int64_t)in->cigar_off[i]);
+  {
+    std::vector<uint64_t> b0((size_t)n_threads + 1, 0);
+    std::vector<int64_t> w0((size_t)n_threads + 1, 0);
+    for (int t = 0; t < n_threads; ++t) {
+      b0[(size_t)t + 1] = b0[(size_t)t] + chunk[(size_t)t].bases;
+      w0[(size_t)t + 1] = w0[(size_t)t] + (narrow_ops ? chunk[(size_t)t].wire_words : chunk[(size_t)t].words);
     }
+    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
+      // (same chunking as above: host_parallel_for cuts [0, n) the same way for the same n and thread count)
+      uint64_t b = b0[(size_t)t];
+      int64_t w = w0[(size_t)t];
+      for (int64_t k = lo; k < hi; ++k) {
+        const int64_t i = idx[(size_t)k];
+        base_off[(size_t)k] = b;
+        wire_off[(size_t)k] = w;
+        b += in->seq_off[i + 1] - in->seq_off[i];
+        w += (narrow_ops && implicit[(size_t)k]) ? 0 : (int64_t)in->cigar_off[i + 1] - (int64_t)in->cigar_off[i];
+      }
+      if (hi == n) {
+        base_off[(size_t)n] = b;
+        wire_off[(size_t)n] = w;
+      }
+    });
   }
   const uint64_t n_bases = base_off[(size_t)n];
   // contig runs and the narrow start column
@@ -305,7 +341,14 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
     for (int64_t k = lo; k < hi; ++k) {
       const int64_t i = idx[(size_t)k];
-      for (uint64_t b = in->seq_off[i]; b < in->seq_off[i + 1]; ++b) seen[(size_t)t][in->base_qualities[b]] = 1;
+      uint8_t* st = seen[(size_t)t].data();
+      const uint8_t* q = in->base_qualities + in->seq_off[i];
+      const uint8_t* qe = in->base_qualities + in->seq_off[i + 1];
+      for (; q + 8 <= qe; q += 8) {
+        st[q[0]] = 1, st[q[1]] = 1, st[q[2]] = 1, st[q[3]] = 1;
+        st[q[4]] = 1, st[q[5]] = 1, st[q[6]] = 1, st[q[7]] = 1;
+      }
+      for (; q < qe; ++q) st[*q] = 1;
     }
   });
   int n_values = 0;
@@ -376,6 +419,12 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   // bases and qualities: every thread owns a range of OUTPUT bytes (global base indices [g0, g1), multiples of 8), so
   // no two threads ever touch the same byte
   std::vector<std::vector<std::pair<uint64_t, uint8_t>>> exc((size_t)n_threads);
+  uint8_t base_lut[256];
+  std::memset(base_lut, 4, sizeof base_lut);
+  base_lut['A'] = 0;
+  base_lut['C'] = 1;
+  base_lut['G'] = 2;
+  base_lut['T'] = 3;
   const int64_t n_groups = (int64_t)((n_bases + 7) / 8);
   host_parallel_for(n_threads, n_groups, [&](int64_t glo, int64_t ghi, int t) {
     const uint64_t g0 = (uint64_t)glo * 8, g1 = std::min<uint64_t>(n_bases, (uint64_t)ghi * 8);
@@ -383,26 +432,44 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
     std::memset(o_bases2 + g0 / 4, 0, (size_t)((g1 + 3) / 4 - g0 / 4));
     std::memset(o_qual + g0 / per_byte, 0, (size_t)((g1 + per_byte - 1) / per_byte - g0 / per_byte));
     int64_t k = (int64_t)(std::upper_bound(base_off.begin(), base_off.end(), g0) - base_off.begin()) - 1;
+    const int qshift = qual_bits == 2 ? 2 : qual_bits == 4 ? 1 : 0;  // log2(bases per quality byte)
+    const unsigned qmask = (1u << qshift) - 1;
     for (uint64_t g = g0; g < g1;) {
       while (base_off[(size_t)k + 1] <= g) ++k;
       const int64_t i = idx[(size_t)k];
       const uint64_t end = std::min<uint64_t>(g1, base_off[(size_t)k + 1]);
       const uint8_t* sb = in->bases_ascii + in->seq_off[i] + (g - base_off[(size_t)k]);
       const uint8_t* sq = in->base_qualities + in->seq_off[i] + (g - base_off[(size_t)k]);
-      for (; g < end; ++g, ++sb, ++sq) {
-        int code;
-        switch (*sb) {
-          case 'A': code = 0; break;
-          case 'C': code = 1; break;
-          case 'G': code = 2; break;
-          case 'T': code = 3; break;
-          default: code = -1;
-        }
-        if (code >= 0) o_bases2[g >> 2] |= (uint8_t)(code << ((g & 3) * 2));
+      auto one = [&]() {  // one base, read-modify-write of its output bytes
+        const int code = base_lut[*sb];
+        if (code < 4) o_bases2[g >> 2] |= (uint8_t)(code << ((g & 3) * 2));
         else exc[(size_t)t].push_back({g, *sb});
         if (qual_bits == 8) o_qual[g] = *sq;
-        else o_qual[g / per_byte] |= (uint8_t)(code_of[*sq] << (qual_bits * (g % per_byte)));
+        else o_qual[g >> qshift] |= (uint8_t)(code_of[*sq] << (qual_bits * (int)(g & qmask)));
+        ++g, ++sb, ++sq;
+      };
+      while (g < end && (g & 3)) one();
+      for (; g + 4 <= end; g += 4, sb += 4, sq += 4) {  // four bases per output byte, plain stores
+        const int c0 = base_lut[sb[0]], c1 = base_lut[sb[1]], c2 = base_lut[sb[2]], c3 = base_lut[sb[3]];
+        if ((c0 | c1 | c2 | c3) < 4) {
+          o_bases2[g >> 2] = (uint8_t)(c0 | (c1 << 2) | (c2 << 4) | (c3 << 6));
+        } else {
+          for (int j = 0; j < 4; ++j) {
+            const int c = base_lut[sb[j]];
+            if (c < 4) o_bases2[g >> 2] |= (uint8_t)(c << (2 * j));
+            else exc[(size_t)t].push_back({g + (uint64_t)j, sb[j]});
+          }
+        }
+        if (qual_bits == 2) {
+          o_qual[g >> 2] = (uint8_t)(code_of[sq[0]] | (code_of[sq[1]] << 2) | (code_of[sq[2]] << 4) | (code_of[sq[3]] << 6));
+        } else if (qual_bits == 4) {
+          o_qual[g >> 1] = (uint8_t)(code_of[sq[0]] | (code_of[sq[1]] << 4));
+          o_qual[(g >> 1) + 1] = (uint8_t)(code_of[sq[2]] | (code_of[sq[3]] << 4));
+        } else {
+          std::memcpy(o_qual + g, sq, 4);
+        }
       }
+      while (g < end) one();
     }
   });
   size_t n_exc = 0;

@@ -532,6 +532,8 @@ void* guac_stream(guac_ctx* ctx);
  *   "synth_profile"         guac_synth_generate: 0 (default) the workload of SURVEY.md 8(d); 1 its "realistic" variant (read
  *                           density varying like a Poisson pileup's, 15 % of reads with a quality-2 tail, 10 % multi-operator
  *                           reads, 1 % of reads with 10..20 mismatches)
+ *   "compact_min_qual_bits" guac_reads_export_compact: 2 (default) the narrowest quality form the batch allows; 4 or 8 force
+ *                           the wider ones (measurement hook: what real, unbinned qualities cost on the wire)
  *   "compact_narrow"        1 (default): guac_reads_export_compact emits the narrow columns where the batch allows; 0: never
  *   "ss_rank_max"           somatic-standard ranks more calls than this through a bitmap over the loci instead of by
  *                           pairwise comparison (test hook; default and maximum 32768, negative restores the default) */

@@ -128,3 +128,32 @@ def test_ordering_contract(gpu_ctx):
     c.start_rel = c._keep["rel_swapped"].ctypes.data_as(C.POINTER(C.c_uint32))
     with pytest.raises(GuacError, match="Regions must be sorted by start locus"):
         gpu_ctx.upload_reads_compact(c)
+
+
+def test_host_packer_feeds_the_device(gpu_ctx):
+    """SAM-record columns -> guac_pack_reads (pinned outputs of the context) -> guac_reads_upload_compact -> the device batch is
+    byte-identical to the plain upload of the same (filtered) reads, and the caller gives the same records."""
+    from guacamole_b200 import host_stage as hs
+    from guacamole_b200 import partitioning
+    from guacamole_b200.reads import FLAG_DUPLICATE
+    batch, ref, _ = fixtures.load("tough")
+    fl = batch.flags.copy()
+    fl[::7] |= FLAG_DUPLICATE
+    batch.flags = fl
+    records, keepalive = hs.sam_records_of(batch)
+    packed, kept = hs.pack_reads(records, ctx=gpu_ctx, non_duplicate=True)
+    want_batch = partitioning.take_reads(batch, np.flatnonzero((fl & FLAG_DUPLICATE) == 0))
+    assert kept == want_batch.n_reads
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads_compact(packed)
+    gpu_ctx._batch = want_batch
+    got = gpu_ctx.export_reads(batch.contig_names)
+    for f in ["contig_id", "start", "cigar_off", "cigar", "seq_off", "bases_ascii", "qual", "mapq", "flags", "sample_id"]:
+        assert np.array_equal(getattr(got, f), getattr(want_batch, f)), f
+    from guacamole_b200.commands.somatic_standard import covered_ranges
+    loci = covered_ranges(want_batch)
+    a = gpu_ctx.somatic_standard(loci)
+    gpu_ctx.upload_reads(want_batch)
+    b = gpu_ctx.somatic_standard(loci)
+    assert a["calls"].tobytes() == b["calls"].tobytes() and a["arena"] == b["arena"]
+    hs.free_packed(packed, ctx=gpu_ctx)
