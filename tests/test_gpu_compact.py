@@ -155,5 +155,8 @@ def test_host_packer_feeds_the_device(gpu_ctx):
     a = gpu_ctx.somatic_standard(loci)
     gpu_ctx.upload_reads(want_batch)
     b = gpu_ctx.somatic_standard(loci)
-    assert a["calls"].tobytes() == b["calls"].tobytes() and a["arena"] == b["arena"]
+    from guacamole_b200.commands.somatic_standard import alleles_of
+    assert len(a["calls"]) == len(b["calls"]) > 0 and alleles_of(a) == alleles_of(b)  # (arena offsets are handed out in any order)
+    for f in ("start", "somatic_log_odds", "tumor_variant_evidence", "normal_reference_evidence"):
+        assert np.array_equal(a["calls"][f], b["calls"][f]), f
     hs.free_packed(packed, ctx=gpu_ctx)
