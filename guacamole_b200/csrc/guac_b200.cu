@@ -98,7 +98,10 @@ struct guac_ctx {
   cudaEvent_t fork = nullptr, join = nullptr;
   DevBuf b_bins, b_bin_count, b_medium;  // stream path: per-read event slots and counts; list of multi-operator reads
   int64_t n_medium = 0;
-  DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off;  // upload scratch, kept between calls
+  // every READ_INDEX_STRIDE-th entry of the start column, of the running-max end keys and of the multi-operator list, on the
+  // host: a call over part of the batch's loci runs the read pass over the reads that can overlap them only
+  std::vector<int64_t> h_idx_start, h_idx_runmax, h_idx_medium;
+  DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off, u_idx;  // upload scratch, kept between calls
   DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
   int64_t opt_compact_narrow = 1;
   int64_t opt_compact_min_qual_bits = 2;  // guac_reads_export_compact: 2 (default) the narrowest form the qualities allow; 4 / 8 force wider ones
@@ -438,6 +441,38 @@ int side_stream(guac_ctx* ctx) {
   return GUAC_OK;
 }
 
+constexpr int64_t READ_INDEX_STRIDE = 1024;
+__global__ void sample_columns_kernel(const int64_t* a, int64_t na, const int64_t* b, int64_t nb, const int64_t* c, int64_t nc,
+                                      int64_t* out) {
+  const int64_t ka = (na + READ_INDEX_STRIDE - 1) / READ_INDEX_STRIDE, kb = (nb + READ_INDEX_STRIDE - 1) / READ_INDEX_STRIDE,
+                kc = (nc + READ_INDEX_STRIDE - 1) / READ_INDEX_STRIDE;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < ka) out[i] = a[i * READ_INDEX_STRIDE];
+  else if (i < ka + kb) out[i] = b[(i - ka) * READ_INDEX_STRIDE];
+  else if (i < ka + kb + kc) out[i] = c[(i - ka - kb) * READ_INDEX_STRIDE];
+}
+// The host's sampled index of the batch (see guac_ctx::h_idx_start): one small kernel, one copy.
+int sample_read_index(guac_ctx* ctx, int64_t n) {
+  const int64_t kr = (n + READ_INDEX_STRIDE - 1) / READ_INDEX_STRIDE, km = (ctx->n_medium + READ_INDEX_STRIDE - 1) / READ_INDEX_STRIDE;
+  ctx->h_idx_start.assign((size_t)kr, 0);
+  ctx->h_idx_runmax.assign((size_t)kr, 0);
+  ctx->h_idx_medium.assign((size_t)km, 0);
+  const int64_t total = 2 * kr + km;
+  if (total == 0) return GUAC_OK;
+  GUAC_TRY(ensure(ctx, ctx->u_idx, (size_t)total * sizeof(int64_t)));
+  sample_columns_kernel<<<blocks_for(total, 256), 256, 0, ctx->stream>>>(ctx->b_start.as<int64_t>(), n, ctx->b_runmax.as<int64_t>(), n,
+                                                                        ctx->b_medium.as<int64_t>(), ctx->n_medium, ctx->u_idx.as<int64_t>());
+  ctx->launches += 1;
+  CUDA_TRY(ctx, cudaGetLastError());
+  std::vector<int64_t> h((size_t)total);
+  CUDA_TRY(ctx, cudaMemcpyAsync(h.data(), ctx->u_idx.p, (size_t)total * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  std::copy(h.begin(), h.begin() + kr, ctx->h_idx_start.begin());
+  std::copy(h.begin() + kr, h.begin() + 2 * kr, ctx->h_idx_runmax.begin());
+  std::copy(h.begin() + 2 * kr, h.end(), ctx->h_idx_medium.begin());
+  return GUAC_OK;
+}
+
 int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   GUAC_TRY(ensure(ctx, ctx->b_end, (size_t)(n + 1) * sizeof(int64_t)));
   GUAC_TRY(ensure(ctx, ctx->b_key, (size_t)(n + 1) * sizeof(int64_t)));
@@ -489,7 +524,10 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
     ctx->launches += 7;
     CUDA_TRY(ctx, cudaGetLastError());
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  } else {
+    ctx->n_medium = 0;
   }
+  GUAC_TRY(sample_read_index(ctx, n));
   ctx->n_reads = n;
   ctx->n_samples = n_samples;
   ctx->have_reads = true;
@@ -531,10 +569,32 @@ int run_read_pass(guac_ctx* ctx) {
   for (auto& sp : ctx->contig_spans) {  // one launch per contig of the batch: its reference rides in the arguments
     auto it = ctx->contigs.find(sp.first);
     if (it == ctx->contigs.end() || sp.second.second <= sp.second.first) continue;
+    // the reads that can overlap the loci of this call (make_plan's ranges), to the grain of the host's sampled index: from
+    // the last sampled read whose running-max end is still at or before the first locus, to the first sampled read that
+    // starts at or after the last one
+    int64_t first_locus = INT64_MAX, end_locus = INT64_MIN;
+    for (const RangeDev& r : ctx->plan_ranges)
+      if (r.contig_id == sp.first) {
+        first_locus = std::min<int64_t>(first_locus, r.start);
+        end_locus = std::max<int64_t>(end_locus, r.end);
+      }
+    if (end_locus <= first_locus) continue;
+    int64_t read_lo = sp.second.first, read_hi = sp.second.second;
+    {
+      const int64_t k0 = (read_lo + READ_INDEX_STRIDE - 1) / READ_INDEX_STRIDE, k1 = (read_hi + READ_INDEX_STRIDE - 1) / READ_INDEX_STRIDE;
+      const int64_t key = ((int64_t)sp.first << 40) | first_locus;  // (read_ends_kernel's key)
+      const int64_t* rm = ctx->h_idx_runmax.data();
+      const int64_t* st = ctx->h_idx_start.data();
+      const int64_t ka = std::upper_bound(rm + k0, rm + k1, key) - rm;           // first sample with running max > key
+      if (ka > k0) read_lo = (ka - 1) * READ_INDEX_STRIDE;
+      const int64_t kb = std::lower_bound(st + k0, st + k1, end_locus) - st;      // first sample starting at or after the end
+      if (kb < k1) read_hi = kb * READ_INDEX_STRIDE;
+    }
+    if (read_hi <= read_lo) continue;
     StreamArgs SA;
     SA.hdr = ctx->b_hdr.as<uint4>();
-    SA.read_lo = sp.second.first;
-    SA.read_hi = sp.second.second;
+    SA.read_lo = read_lo;
+    SA.read_hi = read_hi;
     SA.ref.bases = it->second.bases;
     SA.ref.offset = it->second.offset;
     SA.ref.len = it->second.len;
@@ -549,11 +609,21 @@ int run_read_pass(guac_ctx* ctx) {
     SA.inline_medium = ctx->contig_spans.size() == 1 ? 0 : 1;
     unsigned blocks = blocks_for(SA.read_hi - SA.read_lo, 256);
     if (ctx->contig_spans.size() == 1 && ctx->n_medium > 0) {  // the multi-operator reads ride in the same launch
-      SA.list = ctx->b_medium.as<int64_t>();
-      SA.n_list = ctx->n_medium;
-      SA.list_blocks = blocks_for(ctx->n_medium, 256);
-      SA.list_period = std::max(1u, blocks / SA.list_blocks) + 1;
-      blocks += SA.list_blocks;
+      // (the part of the list inside [read_lo, read_hi), again to the grain of the sampled index)
+      const int64_t* md = ctx->h_idx_medium.data();
+      const int64_t km = (int64_t)ctx->h_idx_medium.size();
+      const int64_t ma = std::lower_bound(md, md + km, read_lo) - md, mb = std::lower_bound(md, md + km, read_hi) - md;
+      const int64_t list_lo = std::max<int64_t>(0, ma - 1) * READ_INDEX_STRIDE;
+      const int64_t list_hi = std::min<int64_t>(ctx->n_medium, mb * READ_INDEX_STRIDE);
+      if (list_hi > list_lo) {
+        SA.list = ctx->b_medium.as<int64_t>() + list_lo;
+        SA.n_list = list_hi - list_lo;
+        SA.list_blocks = blocks_for(SA.n_list, 256);
+        SA.list_period = std::max(1u, blocks / SA.list_blocks) + 1;
+        blocks += SA.list_blocks;
+      } else {
+        SA.inline_medium = 1;  // (no multi-operator read in range)
+      }
     }
     ss_read_events_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->R, SA);
     ctx->launches += 1;
@@ -638,7 +708,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->fork) cudaEventDestroy(ctx->fork);
   if (ctx->join) cudaEventDestroy(ctx->join);
   for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
-                    &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
+                    &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_idx, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
                     &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings,
                     &ctx->r_bitmap, &ctx->r_counts, &ctx->r_prefix, &ctx->r_rank, &ctx->j_force, &ctx->j_simple, &ctx->j_sites_fast,
                     &ctx->j_raw_fast, &ctx->j_bail, &ctx->j_raw_gen, &ctx->j_emits, &ctx->j_order, &ctx->j_cnt, &ctx->j_off,

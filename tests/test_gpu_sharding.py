@@ -35,6 +35,39 @@ def test_somatic_standard_shards(gpu_ctx):
         np.testing.assert_allclose(merged["calls"]["somatic_log_odds"], other["calls"]["somatic_log_odds"], rtol=1e-9)
 
 
+@pytest.mark.parametrize("profile", [0, 1])
+def test_loci_subsets_of_a_resident_batch(gpu_ctx, profile):
+    """The whole batch stays on the device and the callers are asked for some of its loci only (what `bench.py --scaling
+    strong` does): the read pass then runs over the reads near those loci, and the records are the whole call's records at
+    those loci."""
+    contig_len, seed = 300000, 5151
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, (30, 60), (False, True), seed, profile=profile)
+    assert batch.n_reads > 100 * 1024  # (many entries in the host's sampled index of the batch)
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    whole = gpu_ctx.somatic_standard([(0, 0, contig_len)])
+    w_start, w_alleles = whole["calls"]["start"], ss.alleles_of(whole)
+    assert len(w_start) > 20
+    p = sj.sj_params([0, 1])
+    whole_j, _ = gpu_ctx.somatic_joint([(0, 1, contig_len)], p)
+    for ranges in ([(0, 0, 1)], [(0, 123457, 123458)], [(0, 1000, 1999), (0, 2050, 2051), (0, 250000, 299999)], [(0, 299000, contig_len)],
+                   [(0, 150000, 150700)]):
+        part = gpu_ctx.somatic_standard(ranges)
+        inside = np.zeros(len(w_start), bool)
+        for _, s, e in ranges:
+            inside |= (w_start >= s) & (w_start < e)
+        assert part["n_visited"] <= sum(e - s for _, s, e in ranges)
+        assert np.array_equal(part["calls"]["start"], w_start[inside])
+        assert ss.alleles_of(part) == [a for a, k in zip(w_alleles, inside) if k]
+        assert np.array_equal(part["calls"]["somatic_log_odds"], whole["calls"]["somatic_log_odds"][inside])
+        part_j, _ = gpu_ctx.somatic_joint([(c, max(1, s), e) for c, s, e in ranges], p)
+        want_j = [e_ for e_ in whole_j if any(s <= e_["start"] - 1 < e for _, s, e in ranges)]  # (pileup locus = allele start - 1)
+        key = lambda e_: (e_["start"], e_["ref"], e_["alt"], e_["is_germline_call"], e_["is_somatic_call"],
+                          tuple(tuple(s_["log_likelihoods"]) for s_ in e_["samples"]))
+        assert [key(e_) for e_ in part_j] == [key(e_) for e_ in want_j]
+
+
 def test_somatic_joint_shards(gpu_ctx):
     contig_len, depths, tumor, kinds, seed = 40000, (30, 30, 60, 60), (False, False, True, True), [0, 0, 1, 1], 4401
     ref = synth.make_reference(contig_len, seed)
