@@ -326,8 +326,9 @@ def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
     paths["somatic_joint_2n2t"] = measure(
         f"somatic-joint 2 normal + 2 tumor synthetic 30x/30x/60x/60x, {args.joint_mbp} Mbp contig per GPU, planted SNVs (one GPU's shard of "
         "BASELINE configs[3])", "commands/SomaticJointCaller.scala:154-203", depths, tumor, n, 4000 + rank,
-        lambda: ctx.somatic_joint_records([(0, 0, n)], pj), lambda o: o[3], algorithmic_bytes_per_locus(sum(depths), len(depths)),
-        lambda o: {"alleles_emitted": int(len(o[0])), **{k: ctx.last_stat(k) for k in ("fallback_tiles", "heavy_loci", "sj_simple", "sj_bail",
+        lambda: ctx.somatic_joint_records([(0, 0, n)], pj, copy=False), lambda o: o[3], algorithmic_bytes_per_locus(sum(depths), len(depths)),
+        lambda o: {"alleles_emitted": int(len(o[0])), "records": "read in place in the library's pinned output buffers (no host copy)",
+                   **{k: ctx.last_stat(k) for k in ("fallback_tiles", "heavy_loci", "sj_simple", "sj_bail",
                                                                                        "sj_sites", "sj_emitted_sites")}},
         lambda oracle, b, r, lo, hi: oracle.somatic_joint(b, r, [(0, lo, hi)], pj)[1])
     # configs[1]: the germline toy caller on one 30x sample

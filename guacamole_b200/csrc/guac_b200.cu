@@ -2198,6 +2198,15 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 
 }  // extern "C"
 
+#ifdef GUAC_TK_PHASE_CLOCKS
+// development builds only: reads and clears the phase clocks of ss_tile_kernel (tile_kernels.cuh)
+extern "C" int guac_debug_phase_clocks(unsigned long long* out16) {
+  cudaDeviceSynchronize();
+  if (cudaMemcpyFromSymbol(out16, guac::g_tk_phase_clocks, 16 * sizeof(unsigned long long)) != cudaSuccess) return 1;
+  unsigned long long zero[16] = {0};
+  return cudaMemcpyToSymbol(guac::g_tk_phase_clocks, zero, sizeof zero) != cudaSuccess;
+}
+#endif
 #include "assembly_entry.inl"
 #include "compact_entry.inl"
 #include "support_entry.inl"

@@ -169,6 +169,7 @@ struct TileSmem {
   int warp_tot[2][CFG::WARPS];
   int n_events, n_slow, overflow, ref_has_mask, n_cand, n_zeroq;
   int warp_tot2[CFG::WARPS];
+  int n_scan;  // MODE 2: loci whose events are scanned in a dense second loop
   // MODE 2 only, and last on purpose: the other modes are launched with offsetof(TileSmem, cov2) bytes of shared memory
   int cov2[CFG::TL + 2];    // with at most four samples: depths of samples 2 | 3 << 16
 };
@@ -245,6 +246,94 @@ __device__ inline int sj_scan_events(const SM& S, int l1, int min_reads, unsigne
   return best;
 }
 
+// The same answer for min_reads = 2 (the reference's default, AlleleAtLocus.scala:99) without the counters: an allele
+// can start at the locus iff two discovery events there agree in (sample, class), the classes being the four standard
+// substitutions and "indel anchor or non-standard base".  One bit per (sample, class) seen so far.
+constexpr int SJ_SCAN_SERIAL_MAX = 6;       // events a single lane scans by itself; loci with more go to the warp pass
+constexpr int SJ_PRUNE_MAX_ALT_READS = 8;  // with this many equal alternate reads in a sample no bound is attempted
+#ifndef GUAC_SJ_PAIRSCAN
+#define GUAC_SJ_PAIRSCAN 1
+#endif
+template <class SM>
+__device__ inline bool sj_scan_pairs(const SM& S, int l1, bool& simple, bool& one_base_alleles) {
+  const int nr1 = S.nonref[l1], e1 = S.aux[l1] >> 16, e0 = e1 - ((nr1 & 0xFFFF) + (nr1 >> 16));
+  unsigned seen = 0, twice = 0;
+  bool plain = true;
+  for (int i = e0; i < e1; ++i) {
+    const uint32_t x = S.ev[S.ev_order[i]].x;
+    const unsigned kind = (x >> 24) & 7, code = (x >> 27) & 7;
+    const bool sub = kind == GUAC_ALN_MISMATCH && code < 4;
+    plain = plain && !(kind == GUAC_ALN_INSERTION || (kind == GUAC_ALN_MISMATCH && code >= 4));
+    if (kind == GUAC_ALN_MID_DELETION || kind == GUAC_ALN_CLIPPED || !((x >> 23) & 1)) continue;
+    const unsigned bit = 1u << (((x >> 30) << 3) + (sub ? code : 4u));
+    twice |= seen & bit;
+    seen |= bit;
+  }
+  const bool indel_twice = (twice & 0x10101010u) != 0;
+  simple = plain && !indel_twice;
+  one_base_alleles = !indel_twice;
+  return twice != 0;
+}
+
+// sj_scan_events by a whole warp: lane k takes the events k, k + 32, ... of the locus and the counters are added across
+// the lanes (a tile holds fewer than 2^16 events, so no 16-bit field overflows).  Every lane returns the same values.
+template <class SM>
+__device__ inline int sj_scan_events_warp(const SM& S, int l1, int min_reads, unsigned long long (&hist)[4], bool& simple, bool& one_base_alleles) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int nr1 = S.nonref[l1], e1 = S.aux[l1] >> 16, e0 = e1 - ((nr1 & 0xFFFF) + (nr1 >> 16));
+  unsigned long long h0 = 0, h1 = 0, h2 = 0, h3 = 0, indel = 0;  // indel: 16 bits per sample
+  bool plain = true;
+  for (int i = e0 + lane; i < e1; i += 32) {
+    const uint32_t x = S.ev[S.ev_order[i]].x;
+    const unsigned kind = (x >> 24) & 7, code = (x >> 27) & 7, smp = x >> 30;
+    plain = plain && !(kind == GUAC_ALN_INSERTION || (kind == GUAC_ALN_MISMATCH && code >= 4));
+    if (kind == GUAC_ALN_MID_DELETION || kind == GUAC_ALN_CLIPPED || !((x >> 23) & 1)) continue;
+    if (kind == GUAC_ALN_MISMATCH && code < 4) {
+      const unsigned long long one = 1ull << (16 * code);
+      h0 += smp == 0 ? one : 0ull;
+      h1 += smp == 1 ? one : 0ull;
+      h2 += smp == 2 ? one : 0ull;
+      h3 += smp == 3 ? one : 0ull;
+    } else {
+      indel += 1ull << (16 * smp);
+    }
+  }
+  if (e1 - e0 > 1) {  // (uniform across the warp)
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      h0 += __shfl_xor_sync(FULL, h0, d);
+      h1 += __shfl_xor_sync(FULL, h1, d);
+      h2 += __shfl_xor_sync(FULL, h2, d);
+      h3 += __shfl_xor_sync(FULL, h3, d);
+      indel += __shfl_xor_sync(FULL, indel, d);
+    }
+  } else {  // at most one event, in lane 0
+    h0 = __shfl_sync(FULL, h0, 0);
+    h1 = __shfl_sync(FULL, h1, 0);
+    h2 = __shfl_sync(FULL, h2, 0);
+    h3 = __shfl_sync(FULL, h3, 0);
+    indel = __shfl_sync(FULL, indel, 0);
+  }
+  plain = __all_sync(FULL, plain);
+  hist[0] = h0;
+  hist[1] = h1;
+  hist[2] = h2;
+  hist[3] = h3;
+  simple = plain;
+  one_base_alleles = true;
+  int best = 0;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) best = max(best, (int)((hist[s] >> (16 * c)) & 0xFFFFull));
+    const int n_indel = (int)((indel >> (16 * s)) & 0xFFFFull);
+    if (n_indel >= min_reads) simple = one_base_alleles = false;
+    best = max(best, n_indel);
+  }
+  return best;
+}
+
 // MODE 0: somatic-standard (two samples).  MODE 1: germline toy caller's dense half — one sample (the "tumor"
 // slot; normal_sample = -1), a locus is heavy when depth - referenceDepth >= P.min_alt_reads
 // (commands/GermlineAssemblyCaller.scala:135-138).  MODE 2: somatic-joint prefilter — every sample below P.n_samples
@@ -252,9 +341,28 @@ __device__ inline int sj_scan_events(const SM& S, int l1, int min_reads, unsigne
 // P.min_alt_reads of their reads have a non-Match element at x + 1 (an alternate allele can only start there,
 // jointcaller/pileup_summarization/ReadSubsequence.scala:106-135), when x + 1 is force-called, or when x + 1 lies
 // in the next tile.
+// Development aid (-DGUAC_TK_PHASE_CLOCKS): SM clocks spent between the phase boundaries of ss_tile_kernel, summed over
+// the CTAs by their thread 0; read back with guac_debug_phase_clocks.  Off in the product build.
+#ifdef GUAC_TK_PHASE_CLOCKS
+__device__ unsigned long long g_tk_phase_clocks[16];
+#define TK_PHASE(k)                                                                  \
+  do {                                                                               \
+    if (threadIdx.x == 0) {                                                          \
+      const long long now_ = clock64();                                              \
+      atomicAdd(&g_tk_phase_clocks[k], (unsigned long long)(now_ - phase_t_));       \
+      phase_t_ = now_;                                                               \
+    }                                                                                \
+  } while (0)
+#else
+#define TK_PHASE(k) do { } while (0)
+#endif
+
 template <class CFG, int MODE, bool STREAM = false>
 __global__ void __launch_bounds__(CFG::THREADS, (MODE == 2 ? GUAC_TK_MINB_JOINT : GUAC_TK_MINB))
 ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
+#ifdef GUAC_TK_PHASE_CLOCKS
+  long long phase_t_ = clock64();
+#endif
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TileSmem<CFG>& S = *reinterpret_cast<TileSmem<CFG>*>(smem_raw);
   constexpr int TL = CFG::TL;
@@ -299,7 +407,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     if (MODE == 2) S.cov2[i] = 0;
   }
   for (int i = tid; i < TL + 1; i += CFG::THREADS) S.nonref[i] = S.cursor[i] = 0;
-  if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = S.n_zeroq = 0;
+  if (tid == 0) S.n_events = S.n_slow = S.overflow = S.ref_has_mask = S.n_cand = S.n_zeroq = S.n_scan = 0;
   if (tid < 4) {  // padding words behind the tile
     S.ref2[TL / 16 + (tid & 1)] = 0;
   }
@@ -350,6 +458,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   auto direct = [](int q, int detail) { return 0x80000000u | ((uint32_t)(detail & 0xFF) << 8) | (uint32_t)(q & 0xFF); };
 
   // ---- A. read-parallel pass ---------------------------------------------------------------
+  TK_PHASE(0);
   // The five header loads of a read are independent: issue them together, one read ahead of the one being processed,
   // so the compare work of read i hides the latency of read i + 256's header.
   const uint32_t t0_lo = (uint32_t)t0;
@@ -552,6 +661,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   }
   __syncthreads();
   // reads that need the exact cursor: one warp per read, one lane per locus
+  TK_PHASE(1);
   {
     const int n_slow = min(S.n_slow, CFG::SLOW_MAX);
     for (int si = warp; si < n_slow; si += CFG::WARPS) {
@@ -583,6 +693,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   }
 
   // ---- B. one scan over both packed arrays ----------------------------------------------------
+  TK_PHASE(2);
   {
     constexpr int PER = (TL + CFG::THREADS) / CFG::THREADS;  // covers TL + 1 entries
     const int b0 = tid * PER, e0 = min(n_ev_loci + 1, b0 + PER);
@@ -633,6 +744,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     __syncthreads();
   }
   // bucket the events by locus: events of locus l occupy [end(l) - count(l), end(l))
+  TK_PHASE(3);
   const int n_events = S.n_events;
   for (int i = tid; i < n_events; i += CFG::THREADS) {
     const uint2 ev = S.ev[i];
@@ -644,6 +756,26 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   __syncthreads();
 
   // ---- C. one thread per locus ------------------------------------------------------------------
+  TK_PHASE(4);
+  // MODE 2: two lists of tile loci share S.cursor's words as 16-bit halves (the bucketing above was its last use)
+  uint16_t* const scan_list = reinterpret_cast<uint16_t*>(S.cursor);
+  uint16_t* const prune_list = scan_list + (TL + 1);
+  auto route = [&](int l, bool to_simple) {  // pileup locus t0 + l goes to a per-locus kernel's list
+    const int h = atomicAdd(to_simple ? A.n_simple : A.n_heavy, 1);
+    if (h < (to_simple ? A.max_simple : A.max_heavy)) {
+      Tile t;
+      t.locus0 = t0 + l;
+      t.n_loci = 1;
+      t.contig_id = tile.contig_id;
+      t.slot0 = tile.slot0 + l;
+      t.read_lo = tile.read_lo;
+      t.read_hi = tile.read_hi;
+      t.ref_index = tile.ref_index;
+      t._pad = 0;
+      t.seq_base = t.seq_end = 0;
+      (to_simple ? A.simple : A.heavy)[h] = t;
+    }
+  };
   int my_visited = 0;
   for (int l = tid; l < n_loci; l += CFG::THREADS) {
     const int cv = S.cov[l], nr = S.nonref[l];
@@ -664,43 +796,27 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       if (any_depth) {
         // reference.getReferenceBase(contig, locus + 1) (jointcaller/evidence/MultiSampleMultiAlleleEvidence.scala:93)
         if (ref.at(x + 1) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, x + 1, -1);
-        if (l + 1 >= n_ev_loci) {
+        bool forced = false;
+        for (int i = 0; i < A.n_force; ++i)
+          forced = forced || (A.force[i].contig_id == tile.contig_id && A.force[i].start <= x + 1 && x + 1 < A.force[i].end);
+        if (forced) {
+          candidate = true;  // force-called: always evaluated, by the generic kernels
+        } else if (l + 1 >= n_ev_loci) {
           candidate = true;  // (single-kernel form: the events of x + 1 are in the next tile)
         } else if ((S.nonref[l + 1] >> 16) >= P.min_alt_reads) {
-          candidate = true;
           if (A.sample_bits) {
-            unsigned long long hist[4];
-            candidate = sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site, one_base) >= P.min_alt_reads;
+            // its events are looked at in the loop after this one, where every lane has such a locus (here one lane in
+            // six does, and the warp would wait for it)
+            scan_list[atomicAdd(&S.n_scan, 1)] = (uint16_t)l;
+            continue;
           }
+          candidate = true;
         }
-        for (int i = 0; i < A.n_force; ++i)
-          if (A.force[i].contig_id == tile.contig_id && A.force[i].start <= x + 1 && x + 1 < A.force[i].end) {
-            candidate = true;  // force-called: always evaluated, by the generic kernels
-            simple_site = one_base = false;
-          }
-      }
-      if (candidate && one_base && A.prune) {  // examined in the second pass below, with full warps
-        S.cursor[atomicAdd(&S.n_cand, 1)] = l;
-        continue;
       }
     }
     int flags = 0;
     if (MODE != 0 && candidate) {  // every candidate locus goes to the per-locus kernel
-      const bool to_simple = MODE == 2 && simple_site;
-      const int h = atomicAdd(to_simple ? A.n_simple : A.n_heavy, 1);
-      if (h < (to_simple ? A.max_simple : A.max_heavy)) {
-        Tile t;
-        t.locus0 = x;
-        t.n_loci = 1;
-        t.contig_id = tile.contig_id;
-        t.slot0 = slot;
-        t.read_lo = tile.read_lo;
-        t.read_hi = tile.read_hi;
-        t.ref_index = tile.ref_index;
-        t._pad = 0;
-        t.seq_base = t.seq_end = 0;
-        (to_simple ? A.simple : A.heavy)[h] = t;
-      }
+      route(l, false);
       flags = 1;
     }
     if (MODE == 0 && candidate) {  // the few candidate loci are examined densely in a second pass
@@ -718,7 +834,34 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   }
   my_visited = __reduce_add_sync(FULL, my_visited);
   if (lane == 0 && my_visited) atomicAdd(A.n_visited, (unsigned long long)my_visited);
-  if (MODE == 2 && A.prune) {
+  if (MODE == 2 && A.sample_bits) {
+    __syncthreads();
+    TK_PHASE(5);
+    const int n_scan = S.n_scan;
+    for (int i = tid; i < n_scan; i += CFG::THREADS) {
+      const int l = scan_list[i];
+      bool candidate, simple_site, one_base;
+      {
+        // a locus with many events (a germline site: every other read) would keep this lane busy long after the other
+        // lanes are done: the warp pass below scans it, a lane per event
+        const int nr1 = S.nonref[l + 1];
+        if ((nr1 & 0xFFFF) + (nr1 >> 16) > SJ_SCAN_SERIAL_MAX) {
+          prune_list[atomicAdd(&S.n_cand, 1)] = (uint16_t)(l | 0x8000);
+          continue;
+        }
+      }
+      if (GUAC_SJ_PAIRSCAN && P.min_alt_reads == 2) {
+        candidate = sj_scan_pairs(S, l + 1, simple_site, one_base);
+      } else {
+        unsigned long long hist[4];
+        candidate = sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site, one_base) >= P.min_alt_reads;
+      }
+      if (!candidate) continue;
+      if (one_base && A.prune) prune_list[atomicAdd(&S.n_cand, 1)] = (uint16_t)l;  // examined below, a warp each
+      else route(l, simple_site);
+    }
+  }
+  if (MODE == 2 && A.sample_bits) {
     // prune: a simple site is listed for the site kernel only if one of its possible alleles can be called.  With every
     // read over x + 1 at P(correct) > 1/2 (no flagged read there), a read on the reference base can only lower a
     // het / hom-alt genotype or a tumor mixture against the reference one (its term is log10(1/2) - log10 p,
@@ -726,16 +869,41 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     // alternate reads' terms — exact, from their qualities — bound every posterior gain
     // (MultiSampleSingleAlleleEvidence.scala:66-230).  v is bounded above with the event count over the depth.
     __syncthreads();
+    TK_PHASE(6);
+#ifdef GUAC_TK_PHASE_CLOCKS
+    if (threadIdx.x == 0) {
+      atomicAdd(&g_tk_phase_clocks[9], 1ull);
+      atomicAdd(&g_tk_phase_clocks[10], (unsigned long long)S.n_scan);
+      atomicAdd(&g_tk_phase_clocks[11], (unsigned long long)S.n_cand);
+      atomicAdd(&g_tk_phase_clocks[12], (unsigned long long)S.n_events);
+      atomicAdd(&g_tk_phase_clocks[13], (unsigned long long)n_reads_tile);
+    }
+#endif
     const int n_cand = S.n_cand;
     const double LOG10_HALF = -0.3010299956639812;
     // One warp per candidate, one lane per event of x + 1: the loads of the alternate reads' mapq and quality and their
     // logarithms run side by side; the sums are combined by fixed butterflies.
     for (int ci = warp; ci < n_cand; ci += CFG::WARPS) {
-      const int l = S.cursor[ci];
+      const int entry = prune_list[ci], l = entry & 0x7FFF;
       unsigned long long hist[4];
       bool simple_site, one_base;
-      sj_scan_events(S, l + 1, P.min_alt_reads, hist, simple_site, one_base);  // (every lane: the counts are needed by all)
-      bool keep = (S.aux[l + 1] & 0xFFFF) != 0;  // a read that may have P(correct) <= 1/2 covers x + 1
+#ifdef GUAC_TK_PHASE_CLOCKS
+      long long sub_t_ = clock64();
+#endif
+      const int most = sj_scan_events_warp(S, l + 1, P.min_alt_reads, hist, simple_site, one_base);
+#ifdef GUAC_TK_PHASE_CLOCKS
+      if (threadIdx.x == 0) { const long long n_ = clock64(); atomicAdd(&g_tk_phase_clocks[14], (unsigned long long)(n_ - sub_t_)); sub_t_ = n_; }
+#endif
+      if (entry & 0x8000) {  // not looked at yet: is it a candidate at all, and one for the bound?
+        if (most < P.min_alt_reads) continue;
+        if (!(one_base && A.prune)) {
+          if (lane == 0) route(l, simple_site);
+          continue;
+        }
+      }
+      // a read that may have P(correct) <= 1/2 covers x + 1; or some allele has so many reads that no bound can hold
+      // (keeping a site is always right: the site kernel decides)
+      bool keep = (S.aux[l + 1] & 0xFFFF) != 0 || most >= SJ_PRUNE_MAX_ALT_READS;
       {
         // Clipped elements at x leave the depths (MultiSampleMultiAlleleEvidence.scala:85-86): rare, no shortcut
         const int nr0 = S.nonref[l], f1 = S.aux[l] >> 16, f0 = f1 - ((nr0 & 0xFFFF) + (nr0 >> 16));
@@ -747,69 +915,13 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       auto tumor = [&](int s) { return ((A.kinds >> (2 * s)) & 3u) == GUAC_SJ_TUMOR_DNA; };
       const int dp = (tumor(0) ? d0 : 0) + (tumor(1) ? d1 : 0) + (tumor(2) ? d2 : 0) + (tumor(3) ? d3 : 0);
       if (!keep) {
-        // per-lane terms of its events, by allele base; a quality / mapq pair is fetched once per event
-        double het[4] = {0, 0, 0, 0}, hom[4] = {0, 0, 0, 0}, tp[4] = {0, 0, 0, 0};  // index = base
-        double tm0[4] = {0, 0, 0, 0}, tm1[4] = {0, 0, 0, 0}, tm2[4] = {0, 0, 0, 0}, tm3[4] = {0, 0, 0, 0};  // tumor sample 0..3
-        bool low = false;
-        for (int i = e0 + lane; i < e1; i += 32) {
-          const uint2 ev = S.ev[S.ev_order[i]];
-          const int c = (int)((ev.x >> 27) & 7);
-          if (((ev.x >> 24) & 7) != GUAC_ALN_MISMATCH || c >= 4) continue;
-          const int smp = (int)(ev.x >> 30), rl = (int)((ev.x >> 11) & 0xFFF);
-          // (the three loads below depend on the event alone: requested together)
-          const uint32_t hy = __ldg(A.hdr + tile.read_lo + rl).y;
-          const int mapq = (int)__ldg(R.mapq + tile.read_lo + rl);
-          const int q = (ev.y >> 31) ? (int)(ev.y & 0xFF) : (int)__ldg(R.qual + seq_base + ev.y);
-          {
-            // The bound is about one-base alleles.  A read whose next element is not a Match either starts a longer
-            // allele (ReadSubsequence.scala:117-121), and with it come multi-base subsequences: the site kernel's case.
-            // So is a read the exact cursor walked (an N skip after x + 1 leaves no event), and the tile's last site,
-            // whose locus x + 2 lies outside the kept events.
-            bool longer = l + 2 >= n_ev_loci || !((hy >> 24) & RF_MEDIUM);
-            if (!longer) {
-              const int nr2 = S.nonref[l + 2], g1 = S.aux[l + 2] >> 16, g0 = g1 - ((nr2 & 0xFFFF) + (nr2 >> 16));
-              for (int j = g0; j < g1; ++j) longer = longer || (int)((S.ev[S.ev_order[j]].x >> 11) & 0xFFF) == rl;
-            }
-            if (longer) {
-              low = true;
-              continue;
-            }
-          }
-          if (mapq == 0) continue;  // contributes exactly 0.0 (PileupStats.scala:79-80)
-          const double p = c_success_probability[q] * c_success_probability[mapq];
-          if (!(p > 0.5)) {
-            low = true;
-            continue;
-          }
-          const double2 ab = __ldg(A.log_table + ((mapq << 8) | q));
-          if (((A.kinds >> (2 * smp)) & 3u) == GUAC_SJ_NORMAL_DNA) {
-            const double h1 = fmax(0.0, LOG10_HALF - ab.y), h2 = fmax(0.0, ab.x - ab.y);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              het[k] += c == k ? h1 : 0.0;
-              hom[k] += c == k ? h2 : 0.0;
-            }
-          } else if (((A.kinds >> (2 * smp)) & 3u) == GUAC_SJ_TUMOR_DNA) {
-            // alt fraction bounded above by (events of this base in the sample) / depth, at most 1
-            const int ks = (int)((hist[smp] >> (16 * c)) & 0xFFFF);
-            const int ds = smp == 0 ? d0 : smp == 1 ? d1 : smp == 2 ? d2 : d3;
-            int kp = 0;
-#pragma unroll
-            for (int s2 = 0; s2 < 4; ++s2) kp += tumor(s2) ? (int)((hist[s2] >> (16 * c)) & 0xFFFF) : 0;
-            const double v = fmin(1.0, fmax(A.vaf_floor, (double)ks / ds)), vp = fmin(1.0, fmax(A.vaf_floor, (double)kp / dp));
-            const double t = fmax(0.0, log10(v * p + (1.0 - v) * (1.0 - p)) - ab.y);
-            const double u = fmax(0.0, log10(vp * p + (1.0 - vp) * (1.0 - p)) - ab.y);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              tm0[k] += (c == k && smp == 0) ? t : 0.0;
-              tm1[k] += (c == k && smp == 1) ? t : 0.0;
-              tm2[k] += (c == k && smp == 2) ? t : 0.0;
-              tm3[k] += (c == k && smp == 3) ? t : 0.0;
-              tp[k] += c == k ? u : 0.0;
-            }
-          }
-        }
-        keep = __any_sync(FULL, low);
+        // One possible allele (a base with min_reads equal events in a discovery sample) at a time — there is seldom a
+        // second — so a lane carries seven sums, not twenty-eight.  Events of other bases add exactly 0 to this allele's
+        // sums whatever their quality (they miss every allele of either hypothesis).
+        auto count_of = [&](int s, int c) {
+          const unsigned long long h = s == 0 ? hist[0] : s == 1 ? hist[1] : s == 2 ? hist[2] : hist[3];
+          return (int)((h >> (16 * c)) & 0xFFFFull);
+        };
         auto wsum = [&](double v) {
 #pragma unroll
           for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
@@ -817,14 +929,70 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         };
         const double margin = -1e-6;  // dwarfs the rounding of the sums; costs nothing in pruning power
         for (int c = 0; c < 4 && !keep; ++c) {
-          int kmax = 0;
-#pragma unroll
-          for (int s2 = 0; s2 < 4; ++s2) kmax = max(kmax, (int)((hist[s2] >> (16 * c)) & 0xFFFF));
-          if (kmax < P.min_alt_reads) continue;  // not a possible allele (uniform across the warp)
-          const double g_het = wsum(het[c]), g_hom = wsum(hom[c]);
-          const double g_t = fmax(fmax(fmax(wsum(tm0[c]), wsum(tm1[c])), fmax(wsum(tm2[c]), wsum(tm3[c]))), wsum(tp[c]));
+          const int k0 = count_of(0, c), k1 = count_of(1, c), k2 = count_of(2, c), k3 = count_of(3, c);
+          if (max(max(k0, k1), max(k2, k3)) < P.min_alt_reads) continue;  // not a possible allele (uniform across the warp)
+          const int kp = (tumor(0) ? k0 : 0) + (tumor(1) ? k1 : 0) + (tumor(2) ? k2 : 0) + (tumor(3) ? k3 : 0);
+          const double vp = fmin(1.0, fmax(A.vaf_floor, (double)kp / dp));  // (only used with a tumor read: dp > 0 then)
+          double het = 0, hom = 0, tp = 0, tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;
+          bool low = false;
+          for (int i = e0 + lane; i < e1; i += 32) {
+            const uint2 ev = S.ev[S.ev_order[i]];
+            if (((ev.x >> 24) & 7) != GUAC_ALN_MISMATCH || (int)((ev.x >> 27) & 7) != c) continue;
+            const int smp = (int)(ev.x >> 30), rl = (int)((ev.x >> 11) & 0xFFF);
+            // (the three loads below depend on the event alone: requested together)
+            const uint32_t hy = __ldg(A.hdr + tile.read_lo + rl).y;
+            const int mapq = (int)__ldg(R.mapq + tile.read_lo + rl);
+            const int q = (ev.y >> 31) ? (int)(ev.y & 0xFF) : (int)__ldg(R.qual + seq_base + ev.y);
+            {
+              // The bound is about one-base alleles.  A read whose next element is not a Match either starts a longer
+              // allele (ReadSubsequence.scala:117-121), and with it come multi-base subsequences: the site kernel's case.
+              // So is a read the exact cursor walked (an N skip after x + 1 leaves no event), and the tile's last site,
+              // whose locus x + 2 lies outside the kept events.
+              bool longer = l + 2 >= n_ev_loci || !((hy >> 24) & RF_MEDIUM);
+              if (!longer) {
+                const int nr2 = S.nonref[l + 2], g1 = S.aux[l + 2] >> 16, g0 = g1 - ((nr2 & 0xFFFF) + (nr2 >> 16));
+                for (int j = g0; j < g1; ++j) longer = longer || (int)((S.ev[S.ev_order[j]].x >> 11) & 0xFFF) == rl;
+              }
+              if (longer) {
+                low = true;
+                continue;
+              }
+            }
+            if (mapq == 0) continue;  // contributes exactly 0.0 (PileupStats.scala:79-80)
+            const double p = c_success_probability[q] * c_success_probability[mapq];
+            if (!(p > 0.5)) {
+              low = true;
+              continue;
+            }
+            const double2 ab = __ldg(A.log_table + ((mapq << 8) | q));
+            const unsigned sample_kind = (A.kinds >> (2 * smp)) & 3u;
+            if (sample_kind == GUAC_SJ_NORMAL_DNA) {
+              het += fmax(0.0, LOG10_HALF - ab.y);
+              hom += fmax(0.0, ab.x - ab.y);
+            } else if (sample_kind == GUAC_SJ_TUMOR_DNA) {
+              // alt fraction bounded above by (events of this base in the sample) / depth, at most 1
+              const int ks = smp == 0 ? k0 : smp == 1 ? k1 : smp == 2 ? k2 : k3;
+              const int ds = smp == 0 ? d0 : smp == 1 ? d1 : smp == 2 ? d2 : d3;
+              const double v = fmin(1.0, fmax(A.vaf_floor, (double)ks / ds));
+              const double t = fmax(0.0, log10(v * p + (1.0 - v) * (1.0 - p)) - ab.y);
+              tp += fmax(0.0, log10(vp * p + (1.0 - vp) * (1.0 - p)) - ab.y);
+              tm0 += smp == 0 ? t : 0.0;
+              tm1 += smp == 1 ? t : 0.0;
+              tm2 += smp == 2 ? t : 0.0;
+              tm3 += smp == 3 ? t : 0.0;
+            }
+          }
+          if (__any_sync(FULL, low)) {
+            keep = true;
+            break;
+          }
+          const double g_het = wsum(het), g_hom = wsum(hom);
+          const double g_t = fmax(fmax(fmax(wsum(tm0), wsum(tm1)), fmax(wsum(tm2), wsum(tm3))), wsum(tp));
           keep = !(g_het - A.het_prior <= margin) || !(g_hom - A.hom_prior <= margin) || !(g_t - A.somatic_prior <= margin);
         }
+#ifdef GUAC_TK_PHASE_CLOCKS
+        if (threadIdx.x == 0) { const long long n_ = clock64(); atomicAdd(&g_tk_phase_clocks[15], (unsigned long long)(n_ - sub_t_)); sub_t_ = n_; }
+#endif
       }
       if (!keep || lane != 0) continue;
       // kept: the fast site kernel where every subsequence is one standard base, the generic kernels otherwise
@@ -844,6 +1012,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
       }
     }
   }
+  TK_PHASE(7);
   if (MODE != 0) return;
   __syncthreads();
   const int n_cand = S.n_cand;
@@ -967,6 +1136,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     v.w = (uint32_t)min(top_t, 65535) | ((uint32_t)flags << 16);
     reinterpret_cast<uint4*>(A.summary)[slot] = v;
   }
+  TK_PHASE(8);
 }
 
 }  // namespace guac

@@ -562,9 +562,14 @@ class Context:
                                                  C.byref(rs), C.byref(re_), C.byref(sc), C.byref(raw)))
         return buf.value.decode(), rs.value, re_.value, sc.value, raw.value
 
-    def somatic_joint_records(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
-        """guac_somatic_joint -> (allele records, sample-evidence records, arena bytes, loci visited) as numpy arrays."""
+    def somatic_joint_records(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = (),
+                              copy: bool = True):
+        """guac_somatic_joint -> (allele records, sample-evidence records, arena bytes, loci visited) as numpy arrays.
+
+        copy=False: the two record arrays are views of the library's pinned output buffers (what a JNI / C++ consumer reads in
+        place), valid until the next call with copy=False or `release_outputs()`; nothing is copied on the host."""
         from .commands import somatic_joint as sj
+        self.release_outputs()
         r, f = make_ranges(loci), make_ranges(force_loci)
         al, na, sm, ns, arena, alen, nv = C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_void_p(), C.c_int64(), C.c_int64()
         self._check(self.lib.guac_somatic_joint(self.ctx, C.byref(params), r, C.c_int32(len(loci)), f, C.c_int32(len(force_loci)),
@@ -573,9 +578,23 @@ class Context:
         arena_b = C.string_at(arena, alen.value) if arena else b""
         if arena:
             self.lib.guac_free(self.ctx, arena)
-        alleles = _take(self.lib, self.ctx, al, sj.ALLELE_EVIDENCE_DTYPE, na.value)
-        samples = _take(self.lib, self.ctx, sm, sj.SAMPLE_EVIDENCE_DTYPE, ns.value)
+        if copy:
+            alleles = _take(self.lib, self.ctx, al, sj.ALLELE_EVIDENCE_DTYPE, na.value)
+            samples = _take(self.lib, self.ctx, sm, sj.SAMPLE_EVIDENCE_DTYPE, ns.value)
+        else:
+            def view(p, dtype, n):
+                if not p or n == 0:
+                    return np.zeros(0, dtype)
+                return np.frombuffer((C.c_char * (int(n) * dtype.itemsize)).from_address(p.value), dtype=dtype)
+            alleles, samples = view(al, sj.ALLELE_EVIDENCE_DTYPE, na.value), view(sm, sj.SAMPLE_EVIDENCE_DTYPE, ns.value)
+            self._held_outputs = [x for x in (al, sm) if x]
         return alleles, samples, arena_b, nv.value
+
+    def release_outputs(self):
+        """Hands the pinned output buffers of a copy=False call back to the library (guac_free)."""
+        for p in getattr(self, "_held_outputs", []):
+            self.lib.guac_free(self.ctx, p)
+        self._held_outputs = []
 
     def somatic_joint(self, loci: Sequence[Tuple[int, int, int]], params, force_loci: Sequence[Tuple[int, int, int]] = ()):
         """guac_somatic_joint -> (list of per-allele evidence dicts, loci visited); see commands/somatic_joint.py."""

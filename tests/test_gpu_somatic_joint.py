@@ -144,6 +144,12 @@ def test_repeat_runs_are_bit_identical(gpu_ctx):
             gpu_ctx.set_option("sj_impl", 2)
         assert nv1 == nv2 and len(a1) > 100
         assert a1.tobytes() == a2.tobytes() and s1.tobytes() == s2.tobytes() and arena1 == arena2
+    # the records read in place in the library's pinned buffers (what a JNI consumer does) are the same bytes
+    a1, s1, arena1, nv1 = gpu_ctx.somatic_joint_records(loci, p)
+    a3, s3, arena3, nv3 = gpu_ctx.somatic_joint_records(loci, p, copy=False)
+    assert nv3 == nv1 and a3.tobytes() == a1.tobytes() and s3.tobytes() == s1.tobytes() and arena3 == arena1
+    del a3, s3
+    gpu_ctx.release_outputs()
     # and the fast site kernel took nearly every candidate of this SNV-only workload
     gpu_ctx.somatic_joint_records(loci, p)
     simple, bail, heavy = gpu_ctx.last_stat("sj_simple"), gpu_ctx.last_stat("sj_bail"), gpu_ctx.last_stat("heavy_loci")

@@ -28,12 +28,12 @@ def main():
     ctx.synth_generate(n, depths, tumor, 4000)
     ctx.set_option("sj_impl", a.impl)
     p = sj.sj_params(kinds)
-    out = ctx.somatic_joint_records([(0, 0, n)], p)
+    out = ctx.somatic_joint_records([(0, 0, n)], p, copy=False)
     torch.cuda.synchronize()
     ks = []
     t0 = time.perf_counter()
     for _ in range(a.steps):
-        out = ctx.somatic_joint_records([(0, 0, n)], p)
+        out = ctx.somatic_joint_records([(0, 0, n)], p, copy=False)
         ks.append(ctx.last_kernel_ms()[0])
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / a.steps
