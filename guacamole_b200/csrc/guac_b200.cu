@@ -1411,8 +1411,8 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
       FA.n_bail = &d_cnt->n_bail;
       FA.max_bail = n_simple;
       FA.err = ctx->b_err.as<DeviceError>();
-      const unsigned grid = (unsigned)std::min<int64_t>(blocks_for(n_simple, 8), 148 * 16);
-      sj_snv_site_kernel<<<grid, 256, 8 * sizeof(SJFWarpSmem), ctx->stream>>>(ctx->R, P, *params, FA);
+      const unsigned grid = (unsigned)std::min<int64_t>(blocks_for(n_simple, SJF_WARPS), 148 * 16 * 8 / SJF_WARPS);
+      sj_snv_site_kernel<<<grid, 32 * SJF_WARPS, SJF_WARPS * sizeof(SJFWarpSmem), ctx->stream>>>(ctx->R, P, *params, FA);
       ctx->launches += 1;
       CUDA_TRY(ctx, cudaGetLastError());
       GUAC_TRY(read_counters());
@@ -2200,10 +2200,10 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
 
 #ifdef GUAC_TK_PHASE_CLOCKS
 // development builds only: reads and clears the phase clocks of ss_tile_kernel (tile_kernels.cuh)
-extern "C" int guac_debug_phase_clocks(unsigned long long* out16) {
+extern "C" int guac_debug_phase_clocks(unsigned long long* out32) {
   cudaDeviceSynchronize();
-  if (cudaMemcpyFromSymbol(out16, guac::g_tk_phase_clocks, 16 * sizeof(unsigned long long)) != cudaSuccess) return 1;
-  unsigned long long zero[16] = {0};
+  if (cudaMemcpyFromSymbol(out32, guac::g_tk_phase_clocks, 32 * sizeof(unsigned long long)) != cudaSuccess) return 1;
+  unsigned long long zero[32] = {0};
   return cudaMemcpyToSymbol(guac::g_tk_phase_clocks, zero, sizeof zero) != cudaSuccess;
 }
 #endif
@@ -2222,7 +2222,7 @@ cudaError_t configure_device_functions() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(ss_tile_kernel<TCfg, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tile_smem);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(sj_snv_site_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8 * sizeof(SJFWarpSmem)));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(sj_snv_site_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SJF_WARPS * sizeof(SJFWarpSmem)));
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(asm_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_align_smem(ASM_ALIGN_MAX_S));
   return e;

@@ -411,13 +411,69 @@ __device__ __noinline__ unsigned sjf_classify_slow(const ReadsView& R, int64_t r
   return out;
 }
 
+// The same answer for most reads with several operators (RF_MEDIUM: M = X I D S H over standard bases, CIGAR consistent
+// with the sequence) without the cursor: when x .. x + 3 lie inside one M operator, the elements at x, x + 1, x + 2 are
+// plain Match / Mismatch elements and the read goes on past them — exactly the single-operator case, with the read
+// position taken from the operator.  Returns false when the loci are not inside one M operator (the cursor decides).
+__device__ __forceinline__ bool sjf_classify_medium(const ReadsView& R, int64_t r, const uint4& h, int64_t x, uint8_t rb0, uint8_t rb2, int cr,
+                                                    unsigned& cls) {
+  const int off = (int)((uint32_t)x - h.x);  // x - start (the caller checked the overlap: 0 <= off < span)
+  const uint32_t c0 = __ldg(R.cigar_off + r), c1 = __ldg(R.cigar_off + r + 1);
+  int cl = 0, rp = 0, p0 = -1;
+  for (uint32_t ci = c0; ci < c1 && cl <= off; ++ci) {
+    const uint32_t w = __ldg(R.cigar + ci);
+    const int op = (int)(w & 15), len = (int)(w >> 4);
+    if (op == OPC_M) {
+      if (off >= cl && off + 3 < cl + len) p0 = rp + (off - cl);
+      cl += len;
+      rp += len;
+    } else if (op == OPC_EQ || op == OPC_X) {
+      cl += len;
+      rp += len;
+    } else if (op == OPC_D) {
+      cl += len;
+    } else if (op == OPC_I || op == OPC_S) {
+      rp += len;
+    }
+  }
+  if (p0 < 0) return false;
+  const uint64_t s0 = (uint64_t)h.z | ((uint64_t)h.w << 32);
+  auto base_at = [&](int q) {
+    const uint64_t gi = s0 + (uint64_t)q;
+    return (int)((__ldg(R.bases2 + (gi >> 2)) >> ((gi & 3) * 2)) & 3);
+  };
+  cls = 1u;
+  if ("ACGT"[base_at(p0)] == (char)rb0) {
+    const int c = base_at(p0 + 1);
+    cls |= 2u | ((unsigned)c << 8) | ((unsigned)__ldg(R.qual + s0 + p0 + 1) << 16);
+    if (c != cr) cls |= "ACGT"[base_at(p0 + 2)] != (char)rb2 ? 8u : 4u;
+  }
+  return true;
+}
+
 #ifndef GUAC_SJF_MINB
 #define GUAC_SJF_MINB 2
 #endif
-__global__ void __launch_bounds__(256, GUAC_SJF_MINB)
+#ifndef GUAC_SJF_WARPS
+#define GUAC_SJF_WARPS 8
+#endif
+constexpr int SJF_WARPS = GUAC_SJF_WARPS;  // sites in flight per CTA, a warp each
+#ifdef GUAC_TK_PHASE_CLOCKS
+#define SJF_PHASE(k)                                                                      \
+  do {                                                                                    \
+    if (threadIdx.x == 0) {                                                               \
+      const long long now_ = clock64();                                                   \
+      atomicAdd(&g_tk_phase_clocks[16 + (k)], (unsigned long long)(now_ - sjf_t_));       \
+      sjf_t_ = now_;                                                                      \
+    }                                                                                     \
+  } while (0)
+#else
+#define SJF_PHASE(k) do { } while (0)
+#endif
+__global__ void __launch_bounds__(32 * SJF_WARPS, GUAC_SJF_MINB)
 sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __grid_constant__ guac_sj_params EP,
                    const __grid_constant__ SJFArgs A) {
-  extern __shared__ __align__(16) unsigned char sjf_smem_raw[];  // 8 x SJFWarpSmem (dynamic: beyond the 48 KB static limit)
+  extern __shared__ __align__(16) unsigned char sjf_smem_raw[];  // SJF_WARPS x SJFWarpSmem (dynamic: beyond the 48 KB static limit)
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   SJFWarpSmem& W = reinterpret_cast<SJFWarpSmem*>(sjf_smem_raw)[warp];
@@ -436,8 +492,11 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
   }
   const double LOG10_HALF = -0.3010299956639812;  // math.log10(0.5)
 
-  for (int ci = blockIdx.x * 8 + warp; ci < n_cands; ci += gridDim.x * 8) {
+  for (int ci = blockIdx.x * SJF_WARPS + warp; ci < n_cands; ci += gridDim.x * SJF_WARPS) {
     Tile tile = A.cands[ci];
+#ifdef GUAC_TK_PHASE_CLOCKS
+    long long sjf_t_ = clock64();
+#endif
     const RefView ref = A.refs[tile.ref_index];
     const int64_t x = tile.locus0, key = ((int64_t)tile.contig_id << 40) | x;
     // reads that can overlap x: start <= x, running-max end > x
@@ -454,6 +513,7 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
     // force-called sites (their fallback alleles can have any shape) and spans beyond the stash take the generic kernels
     bool bail = n_span > SJF_MAX_READS || rb0 == 0 || rb2 == 0 || locus_forced(A.force, A.n_force, tile.contig_id, x + 1);
 
+    SJF_PHASE(0);
     int depth[SJF_SMAX], rcnt[SJF_SMAX], rfwd[SJF_SMAX], rfirst[SJF_SMAX], rll[SJF_SMAX], ns_alt[SJF_SMAX];
     double rA[SJF_SMAX], rB[SJF_SMAX];
 #pragma unroll
@@ -585,6 +645,7 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       }
       accumulate(idx, smp, mapq, fwd, in_depth, has_sub, c, q, disc, other_alt);
     }
+    SJF_PHASE(1);
     if (n_slow > SJF_LIST) bail = true;
     __syncwarp();
     for (int base = 0; base < n_slow && !bail; base += 32) {  // the exact cursor, one lane per listed read
@@ -597,7 +658,9 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
         smp = (int)__ldg(R.sample_id + r);
         mapq = (int)__ldg(R.mapq + r);
         fwd = (__ldg(R.flags + r) & GUAC_READ_POSITIVE_STRAND) != 0;
-        cls = sjf_classify_slow(R, r, x, ref, cr);
+        const uint4 h = __ldg(A.hdr + r);
+        const uint8_t rf = (uint8_t)(h.y >> 24);
+        if (!((rf & RF_MEDIUM) && sjf_classify_medium(R, r, h, x, rb0, rb2, cr, cls))) cls = sjf_classify_slow(R, r, x, ref, cr);
       }
       if (__any_sync(FULL, (cls & 16u) != 0)) bail = true;
       accumulate(idx, smp, mapq, fwd, (cls & 1u) != 0, (cls & 2u) != 0, (int)((cls >> 8) & 3u), (int)((cls >> 16) & 255u), (cls & 4u) != 0,
@@ -622,6 +685,7 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       continue;
     }
     __syncwarp();
+    SJF_PHASE(2);
     // totals over the lanes (fixed trees)
 #pragma unroll
     for (int s = 0; s < SJF_SMAX; ++s) {
@@ -633,39 +697,65 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
       rA[s] = warp_sum_fixed(rA[s]);
       rB[s] = warp_sum_fixed(rB[s]);
     }
-    // cells: lane 4 s + c holds the numbers of sample s's subsequences equal to base c
+    // cells: lane 4 s + c holds the numbers of sample s's subsequences equal to base c.  The reference base's come from
+    // the totals above; the others from the list, one cell at a time: every lane takes the listed reads k, k + 32, ... and
+    // the per-lane numbers are combined by fixed trees (a heterozygous site lists half its reads, in four cells or so)
     int c_cnt = 0, c_fwd = 0, c_first = INT_MAX, c_ll = 0, c_disc = 0, c_dfirst = INT_MAX;
     double c_A = 0.0, c_B = 0.0;
     {
       const int s = (lane >> 2) & 3, c = lane & 3;
-      if (lane < 16) {
-        if (c == cr) {
-          c_cnt = pick4(rcnt[0], rcnt[1], rcnt[2], rcnt[3], s);
-          c_fwd = pick4(rfwd[0], rfwd[1], rfwd[2], rfwd[3], s);
-          c_first = pick4(rfirst[0], rfirst[1], rfirst[2], rfirst[3], s);
-          c_ll = pick4(rll[0], rll[1], rll[2], rll[3], s);
-          c_A = pick4(rA[0], rA[1], rA[2], rA[3], s);
-          c_B = pick4(rB[0], rB[1], rB[2], rB[3], s);
-        } else {
-          for (int k = 0; k < n_list; ++k) {
-            const SJFListEntry& e = W.list[k];
-            if (e.s != s || e.c != c) continue;
-            c_cnt += 1;
-            c_fwd += e.flags & 1;
-            c_first = min(c_first, (int)e.rel);
-            if (e.flags & 2) {
-              c_ll += 1;
-              c_A += W.A[e.rel];
-              c_B += W.B[e.rel];
-            }
-            if (e.flags & 4) {
-              c_disc += 1;
-              c_dfirst = min(c_dfirst, (int)e.rel);
-            }
+      if (lane < 16 && c == cr) {
+        c_cnt = pick4(rcnt[0], rcnt[1], rcnt[2], rcnt[3], s);
+        c_fwd = pick4(rfwd[0], rfwd[1], rfwd[2], rfwd[3], s);
+        c_first = pick4(rfirst[0], rfirst[1], rfirst[2], rfirst[3], s);
+        c_ll = pick4(rll[0], rll[1], rll[2], rll[3], s);
+        c_A = pick4(rA[0], rA[1], rA[2], rA[3], s);
+        c_B = pick4(rB[0], rB[1], rB[2], rB[3], s);
+      }
+      unsigned present = 0;
+      for (int k = lane; k < n_list; k += 32) present |= 1u << (4 * (W.list[k].s & 3) + (W.list[k].c & 3));
+      present = __reduce_or_sync(FULL, present);
+      for (; present; present &= present - 1) {
+        const int cell = __ffs(present) - 1, cs = cell >> 2, cc = cell & 3;
+        int t_cnt = 0, t_fwd = 0, t_first = INT_MAX, t_ll = 0, t_disc = 0, t_dfirst = INT_MAX;
+        double t_A = 0.0, t_B = 0.0;
+        for (int k = lane; k < n_list; k += 32) {
+          const SJFListEntry e = W.list[k];
+          if (e.s != cs || e.c != cc) continue;
+          t_cnt += 1;
+          t_fwd += e.flags & 1;
+          t_first = min(t_first, (int)e.rel);
+          if (e.flags & 2) {
+            t_ll += 1;
+            t_A += W.A[e.rel];
+            t_B += W.B[e.rel];
           }
+          if (e.flags & 4) {
+            t_disc += 1;
+            t_dfirst = min(t_dfirst, (int)e.rel);
+          }
+        }
+        t_cnt = __reduce_add_sync(FULL, t_cnt);
+        t_fwd = __reduce_add_sync(FULL, t_fwd);
+        t_first = __reduce_min_sync(FULL, t_first);
+        t_ll = __reduce_add_sync(FULL, t_ll);
+        t_disc = __reduce_add_sync(FULL, t_disc);
+        t_dfirst = __reduce_min_sync(FULL, t_dfirst);
+        t_A = warp_sum_fixed(t_A);
+        t_B = warp_sum_fixed(t_B);
+        if (lane == cell) {
+          c_cnt = t_cnt;
+          c_fwd = t_fwd;
+          c_first = t_first;
+          c_ll = t_ll;
+          c_disc = t_disc;
+          c_dfirst = t_dfirst;
+          c_A = t_A;
+          c_B = t_B;
         }
       }
     }
+    SJF_PHASE(3);
     // AlleleAtLocus.variantAlleles (jointcaller/AlleleAtLocus.scala:85-149): per discovery sample, its alternate bases
     // by (count desc, first read asc), kept when count >= max(minReads, depth * percent / 100); union, distinct, capped
     int n_res = 0, res_c[4] = {-1, -1, -1, -1};
@@ -873,6 +963,7 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
     // The raw records of the site's alleles are written as they are evaluated; a site none of whose alleles is called
     // is never emitted (MultiSampleMultiAlleleEvidence.scala:149-155; force-called sites are not here) and ends without
     // a site record — its job slots stay unused.
+    SJF_PHASE(4);
     int site_idx = 0, job0 = 0;
     if (lane == 0) job0 = atomicAdd(A.n_jobs, n_res);
     job0 = __shfl_sync(FULL, job0, 0);
@@ -887,6 +978,7 @@ sj_snv_site_kernel(ReadsView R, const __grid_constant__ SJParamsDev P, const __g
     if (!any_call) continue;
     for (int a = 0; a < n_res; ++a)  // the emitted site's other alleles need their records too
       if ((unwritten >> a) & 1u) eval_allele(a, false, job0);
+    SJF_PHASE(5);
     if (lane == 0) site_idx = atomicAdd(A.n_sites, 1);
     site_idx = __shfl_sync(FULL, site_idx, 0);
     if (site_idx >= A.max_sites) continue;

@@ -344,7 +344,7 @@ __device__ inline int sj_scan_events_warp(const SM& S, int l1, int min_reads, un
 // Development aid (-DGUAC_TK_PHASE_CLOCKS): SM clocks spent between the phase boundaries of ss_tile_kernel, summed over
 // the CTAs by their thread 0; read back with guac_debug_phase_clocks.  Off in the product build.
 #ifdef GUAC_TK_PHASE_CLOCKS
-__device__ unsigned long long g_tk_phase_clocks[16];
+__device__ unsigned long long g_tk_phase_clocks[32];
 #define TK_PHASE(k)                                                                  \
   do {                                                                               \
     if (threadIdx.x == 0) {                                                          \

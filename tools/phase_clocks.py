@@ -17,7 +17,7 @@ def main():
     what = sys.argv[1] if len(sys.argv) > 1 else "joint"
     n = int(float(sys.argv[2]) * 1e6) if len(sys.argv) > 2 else 20_000_000
     ctx = Context(0)
-    out = (C.c_ulonglong * 16)()
+    out = (C.c_ulonglong * 32)()
     if what == "joint":
         ctx.synth_generate(n, (30, 30, 60, 60), (False, False, True, True), 4000)
         p = sj.sj_params([sj.NORMAL_DNA, sj.NORMAL_DNA, sj.TUMOR_DNA, sj.TUMOR_DNA])
@@ -38,6 +38,19 @@ def main():
         if k == 7 and what != "joint":
             name = "(end of C)"
         print(f"  {out[k] / tot * 100:5.1f} %  {name}")
+    site_report(out)
+
+
+SITE = ["read-range searches + reference", "span loop (one lane per read)", "slow reads + bail tests", "lane totals + cells",
+        "discovery + slot sums", "allele evaluation + records"]
+
+
+def site_report(out):
+    tot = sum(out[16:22])
+    if tot:
+        print("  site kernel (warp 0 of every CTA; sites that end early count only the phases they reach):")
+        for k, name in enumerate(SITE):
+            print(f"    {out[16 + k] / tot * 100:5.1f} %  {name}")
 
 
 if __name__ == "__main__":
