@@ -31,6 +31,9 @@ struct ReadsView {
   const uint8_t* mapq;
   const uint8_t* flags;
   const uint8_t* sample_id;
+  // derived at upload, or null: per read (start low word, span | sample << 16 | RF_* flags << 24, seq_off low, high)
+  // (read_headers_pack_kernel)
+  const uint4* hdr;
 };
 
 // One contig window in device memory: ASCII upper-case, 0 = missing.

@@ -96,6 +96,7 @@ struct guac_ctx {
   double bound_tab_vaf = -1;
   cudaStream_t stream2 = nullptr;  // second stream: the copy of the bases in guac_reads_upload_compact
   cudaEvent_t fork = nullptr, join = nullptr;
+  DevBuf b_ev_overflow;  // stream path: overflow arena of the read pass (first 64 bytes: its counter)
   DevBuf b_bins, b_bin_count, b_medium;  // stream path: per-read event slots and counts; list of multi-operator reads
   int64_t n_medium = 0;
   // every READ_INDEX_STRIDE-th entry of the start column, of the running-max end keys and of the multi-operator list, on the
@@ -505,6 +506,7 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
   R.sample_id = ctx->b_sample.as<uint8_t>();
   GUAC_TRY(ensure(ctx, ctx->b_rflags, (size_t)n + 16));
   GUAC_TRY(ensure(ctx, ctx->b_hdr, ((size_t)n + 1) * sizeof(uint4)));
+  R.hdr = nullptr;  // (the kernels below build it)
   if (n > 0) {
     read_fast_flags_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>());
     read_headers_pack_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(R, ctx->b_rflags.as<uint8_t>(), ctx->b_hdr.as<uint4>());
@@ -528,6 +530,7 @@ int finish_reads(guac_ctx* ctx, int64_t n, int32_t n_samples, int64_t n_exc) {
     ctx->n_medium = 0;
   }
   GUAC_TRY(sample_read_index(ctx, n));
+  R.hdr = n > 0 ? ctx->b_hdr.as<uint4>() : nullptr;
   ctx->n_reads = n;
   ctx->n_samples = n_samples;
   ctx->have_reads = true;
@@ -561,6 +564,11 @@ int run_read_pass(guac_ctx* ctx) {
   GUAC_TRY(sync_ref2(ctx));
   GUAC_TRY(ensure(ctx, ctx->b_bins, (size_t)(ctx->n_reads + 1) * STREAM_EV_CAP * sizeof(uint2)));
   GUAC_TRY(ensure(ctx, ctx->b_bin_count, (size_t)ctx->n_reads + 16));
+  // overflow arena: room for one read in 32 (a read beyond it, or with more than STREAM_OVF_CAP events, is walked in the
+  // locus pass as before)
+  const int max_overflow = (int)std::min<int64_t>(ctx->n_reads / 32 + 1024, 1 << 24);
+  GUAC_TRY(ensure(ctx, ctx->b_ev_overflow, 64 + (size_t)max_overflow * STREAM_OVF_CAP * sizeof(uint2)));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ev_overflow.p, 0, 64, ctx->stream));
   {  // reads of a contig without a reference get no launch of the read pass: their counts must read 0
     bool every_contig_has_a_reference = true;
     for (auto& sp : ctx->contig_spans) every_contig_has_a_reference = every_contig_has_a_reference && ctx->contigs.count(sp.first) != 0;
@@ -603,6 +611,9 @@ int run_read_pass(guac_ctx* ctx) {
     SA.ref2 = it->second.ref2;
     SA.events = ctx->b_bins.as<uint2>();
     SA.n_events = ctx->b_bin_count.as<uint8_t>();
+    SA.overflow = reinterpret_cast<uint2*>(static_cast<unsigned char*>(ctx->b_ev_overflow.p) + 64);
+    SA.n_overflow = ctx->b_ev_overflow.as<int>();
+    SA.max_overflow = max_overflow;
     SA.list = nullptr;
     SA.n_list = 0;
     SA.list_blocks = SA.list_period = 0;
@@ -707,7 +718,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
   if (ctx->fork) cudaEventDestroy(ctx->fork);
   if (ctx->join) cudaEventDestroy(ctx->join);
-  for (DevBuf* b : {&ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
+  for (DevBuf* b : {&ctx->b_ev_overflow, &ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
                     &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_idx, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
                     &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings,
                     &ctx->r_bitmap, &ctx->r_counts, &ctx->r_prefix, &ctx->r_rank, &ctx->j_force, &ctx->j_simple, &ctx->j_sites_fast,
@@ -1081,6 +1092,7 @@ int guac_somatic_standard(guac_ctx* ctx, const guac_ss_params* params, const gua
         GUAC_TRY(run_read_pass(ctx));
         TA.ev_by_read = ctx->b_bins.as<uint2>();
         TA.ev_count = ctx->b_bin_count.as<uint8_t>();
+        TA.ev_overflow = reinterpret_cast<const uint2*>(static_cast<const unsigned char*>(ctx->b_ev_overflow.p) + 64);
         ss_tile_kernel<TCfg, 0, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, offsetof(TileSmem<TCfg>, cov2), ctx->stream>>>(ctx->R, P, TA);
       } else {
         cudaEventRecord(ctx->ev0, ctx->stream);
@@ -1363,6 +1375,7 @@ int guac_somatic_joint(guac_ctx* ctx, const guac_sj_params* params, const guac_r
     if (stream) {
       TA.ev_by_read = ctx->b_bins.as<uint2>();
       TA.ev_count = ctx->b_bin_count.as<uint8_t>();
+      TA.ev_overflow = reinterpret_cast<const uint2*>(static_cast<const unsigned char*>(ctx->b_ev_overflow.p) + 64);
       ss_tile_kernel<TCfg, 2, true><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, SP, TA);
     } else {
       ss_tile_kernel<TCfg, 2, false><<<(unsigned)plan.n_tiles, TCfg::THREADS, sizeof(TileSmem<TCfg>), ctx->stream>>>(ctx->R, SP, TA);
@@ -2148,6 +2161,7 @@ int guac_pileup_counts_noalloc(int device, const guac_read_batch* d_batch, const
   R.exc_pos = d_batch->exc_pos;
   R.exc_base = d_batch->exc_base;
   R.qual = d_batch->qual;
+  R.hdr = nullptr;
   R.mapq = d_batch->mapq;
   R.flags = d_batch->flags;
   R.sample_id = d_batch->sample_id;

@@ -320,7 +320,47 @@ __device__ __forceinline__ int64_t warp_partition_point(int64_t lo, int64_t hi, 
   return lo;
 }
 
-__global__ void __launch_bounds__(CTA_THREADS)
+// Read r at locus x for the per-locus kernels: overlap, sample, and (when `want`) the pileup element.  With the packed
+// headers of the batch (ReadsView::hdr) one 16-byte load answers the first two, and a read of one aligned operator over
+// standard bases (bit 0 of the flags byte, RF_FAST) has its element at read position x - start: no cursor.
+struct ReadAtLocus {
+  bool overlaps;
+  int sample;
+  int error;  // DERR_* of the element (DERR_NONE when not wanted)
+};
+template <class Want>
+__device__ __forceinline__ ReadAtLocus read_at_locus(const ReadsView& R, int64_t r, int64_t x, const RefView& ref, Elem& e, Want want) {
+  ReadAtLocus out;
+  out.error = DERR_NONE;
+  if (R.hdr == nullptr) {
+    out.overlaps = __ldg(R.start + r) <= x && x < __ldg(R.end + r);
+    out.sample = out.overlaps ? (int)__ldg(R.sample_id + r) : -1;
+    if (out.overlaps && want(out.sample)) out.error = element_at(R, r, x, ref, e);
+    return out;
+  }
+  const uint4 h = __ldg(R.hdr + r);
+  const int span = (int)(h.y & 0xFFFF);
+  const int off = (int)((uint32_t)x - h.x);  // exact: reads and loci of a call lie within 2^31 of each other on a contig
+  out.overlaps = span != 0xFFFF ? (off >= 0 && off < span) : (__ldg(R.start + r) <= x && x < __ldg(R.end + r));
+  out.sample = out.overlaps ? (int)((h.y >> 16) & 0xFF) : -1;
+  if (!(out.overlaps && want(out.sample))) return out;
+  const uint8_t rb = ref.at(x);
+  if (((h.y >> 24) & 1u) && rb != 0) {
+    const uint64_t gi = ((uint64_t)h.z | ((uint64_t)h.w << 32)) + (uint64_t)off;
+    e.read_position = off;
+    e.indel_length = 0;
+    e.ref_base = rb;
+    e.base = (uint8_t)"ACGT"[(__ldg(R.bases2 + (gi >> 2)) >> ((gi & 3) * 2)) & 3];
+    e.kind = e.base == rb ? GUAC_ALN_MATCH : GUAC_ALN_MISMATCH;
+    e.quality = __ldg(R.qual + gi);
+    e.followed_by_ref_skip = false;
+  } else {
+    out.error = element_at(R, r, x, ref, e);
+  }
+  return out;
+}
+
+__global__ void __launch_bounds__(CTA_THREADS, 3)
 somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Tile* __restrict__ tiles,
                         const int* __restrict__ tile_list /* nullptr: identity */, int n_tiles,
                         int tile_per_warp /* 0: the CTA's warps share tile blockIdx.x; 1: one (single-locus) tile per warp */,
@@ -355,17 +395,18 @@ somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Til
     for (int64_t base = tile.read_lo; base < tile.read_hi; base += 32) {
       const int64_t r = base + lane;
       bool ov = false;
-      if (r < tile.read_hi) ov = __ldg(R.start + r) <= x && x < __ldg(R.end + r);
-      int smp = ov ? (int)__ldg(R.sample_id + r) : -1;
-      if (ov && smp >= P.n_samples) ov = false;
-      any = any || __any_sync(FULL, ov);
+      int smp = -1;
       Elem e;
       e.kind = GUAC_ALN_CLIPPED;
-      const bool mine = ov && (smp == P.normal_sample || smp == P.tumor_sample);
-      if (mine) {
-        int ec = element_at(R, r, x, ref, e);
-        if (ec != DERR_NONE) report_error(err, ec, tile.contig_id, x, r);
+      if (r < tile.read_hi) {
+        const ReadAtLocus at = read_at_locus(R, r, x, ref, e, [&](int s) { return s == P.normal_sample || s == P.tumor_sample; });
+        ov = at.overlaps;
+        smp = at.sample;
+        if (at.error != DERR_NONE) report_error(err, at.error, tile.contig_id, x, r);
       }
+      if (ov && smp >= P.n_samples) ov = false;
+      any = any || __any_sync(FULL, ov);
+      const bool mine = ov && (smp == P.normal_sample || smp == P.tumor_sample);
       const bool isN = mine && smp == P.normal_sample, isT = mine && smp == P.tumor_sample;
       depthN += __popc(__ballot_sync(FULL, isN));
       depthT += __popc(__ballot_sync(FULL, isT));
@@ -429,13 +470,19 @@ somatic_standard_kernel(ReadsView R, const RefView* __restrict__ refs, const Til
       for (int64_t base = tile.read_lo; base < tile.read_hi; base += 32) {
         const int64_t r = base + lane;
         bool ov = false;
-        if (r < tile.read_hi) ov = __ldg(R.start + r) <= x && x < __ldg(R.end + r);
-        int smp = ov ? (int)__ldg(R.sample_id + r) : -1;
+        int smp = -1;
+        Elem e;
+        int ec = DERR_NONE;
+        if (r < tile.read_hi) {
+          const ReadAtLocus at = read_at_locus(R, r, x, ref, e, [&](int s) { return s == P.normal_sample || s == P.tumor_sample; });
+          ov = at.overlaps;
+          smp = at.sample;
+          ec = at.error;
+        }
         const bool mine = ov && (smp == P.normal_sample || smp == P.tumor_sample);
         bool isAlt = false;
         if (mine) {
-          Elem e;
-          if (element_at(R, r, x, ref, e) == DERR_NONE) {
+          if (ec == DERR_NONE) {
             const double p = c_success_probability[e.quality];  // probabilityCorrectIgnoringAlignment
             const bool isRef = e.kind == GUAC_ALN_MATCH;
             isAlt = e.kind != GUAC_ALN_MATCH && e.kind != GUAC_ALN_CLIPPED && allele_key(R, r, e) == bkey;
@@ -727,7 +774,7 @@ ss_evidence_kernel(ReadsView R, const RefView* __restrict__ refs, SSParamsDev P,
       const int64_t r = c.read_lo + (s_mm_read[j] >> 1);
       const int cnt = __ldg(ev_count + r);
       const int64_t s = __ldg(R.start + r), en = __ldg(R.end + r);
-      bool ok = ((__ldg(hdr + r).y >> 24) & 4 /* RF_MEDIUM */) && cnt != 255 && s >= ref.offset && en <= ref.offset + ref.len && en > s;
+      bool ok = ((__ldg(hdr + r).y >> 24) & 4 /* RF_MEDIUM */) && cnt <= ev_cap /* a complete slot */ && s >= ref.offset && en <= ref.offset + ref.len && en > s;
       if (ok && ref.bad != nullptr)
         for (int64_t g = (s - ref.offset) >> 4; ok && g <= (en - 1 - ref.offset) >> 4; ++g) ok = !((__ldg(ref.bad + (g >> 5)) >> (g & 31)) & 1u);
       int n = -1;

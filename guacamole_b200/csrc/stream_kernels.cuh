@@ -59,6 +59,11 @@ struct StreamArgs {
   const int64_t* list;
   int64_t n_list;
   unsigned list_blocks, list_period;  // list_blocks = 0: no list
+  // Overflow arena (see STREAM_EV_OVERFLOW in tile_kernels.cuh): records of STREAM_OVF_CAP events, handed out by an atomic
+  // counter (which record a read gets differs from run to run; what it holds does not).  Null: none.
+  uint2* overflow;
+  int* n_overflow;
+  int max_overflow;
 };
 
 // Read-event record (per read, independent of the loci of the call):
@@ -68,42 +73,14 @@ __device__ __forceinline__ uint32_t pack_read_event(int off, int kind, int code)
   return (uint32_t)off | ((uint32_t)kind << 16) | ((uint32_t)code << 19);
 }
 
-// One thread per read: the read's non-Match elements against the 2-bit reference.  No shared memory, no barrier, no atomic.
-// 8 CTAs per SM (32 registers, a dozen bytes of spills): the kernel lives on loads in flight, and the two extra CTAs are
-// worth more than the spills cost (measured 2.44 -> 2.36 ms for the step; 7 CTAs 2.37 ms).
-#ifndef GUAC_K1_MINB
-#define GUAC_K1_MINB 8
-#endif
-__global__ void __launch_bounds__(256, GUAC_K1_MINB) ss_read_events_kernel(ReadsView R, const __grid_constant__ StreamArgs A) {
-  // block -> a block of the list or a block of the read range (see StreamArgs)
-  unsigned b = blockIdx.x;
-  bool from_list = false;
-  if (A.list_blocks) {
-    const unsigned g = b / A.list_period, k = b % A.list_period;
-    if (g < A.list_blocks) {
-      from_list = k == A.list_period - 1;
-      b = from_list ? g : g * (A.list_period - 1) + k;
-    } else {
-      b -= A.list_blocks;
-    }
-  }
-  int64_t r;
-  if (from_list) {
-    const int64_t i = (int64_t)b * blockDim.x + threadIdx.x;
-    if (i >= A.n_list) return;
-    r = __ldg(A.list + i);
-  } else {
-    r = A.read_lo + (int64_t)b * blockDim.x + threadIdx.x;
-    if (r >= A.read_hi) return;
-  }
-  const uint4 hdr = __ldg(A.hdr + r);
+// The walk of one read: its non-Match elements against the 2-bit reference, the first `cap` of them written to `out`.
+// Returns their number (4096: an element the record cannot express).
+__device__ __forceinline__ int read_events_walk(const ReadsView& R, const StreamArgs& A, int64_t r, const uint4 hdr, uint2* out, int cap) {
   const uint8_t rf = (uint8_t)(hdr.y >> 24);
-  if (!from_list && !A.inline_medium && (rf & RF_MEDIUM) && !(rf & RF_FAST)) return;  // visited through the list
   int n_ev = 0;
-  uint2* mine = A.events + r * STREAM_EV_CAP;
   auto push = [&](int off, int kind, int code, uint32_t second) {
-    if (n_ev < STREAM_EV_CAP && off < 65536) mine[n_ev] = make_uint2(pack_read_event(off, kind, code), second);
-    else if (off >= 65536) n_ev = 256;  // not representable: treated like an overflow
+    if (n_ev < cap && off < 65536) out[n_ev] = make_uint2(pack_read_event(off, kind, code), second);
+    else if (off >= 65536) n_ev = 4096;  // not representable: treated like an overflow
     ++n_ev;
   };
   auto direct = [](int q, int detail) { return 0x80000000u | ((uint32_t)(detail & 0xFF) << 8) | (uint32_t)(q & 0xFF); };
@@ -215,6 +192,53 @@ __global__ void __launch_bounds__(256, GUAC_K1_MINB) ss_read_events_kernel(Reads
       }
     }
   }
+  return n_ev;
+}
+
+// A read with more events than its slot holds: walked again, into a record of the overflow arena (out of line: the read
+// pass proper keeps its registers).  Returns the count byte of the read.
+__device__ __noinline__ int read_events_to_arena(const ReadsView& R, const StreamArgs& A, int64_t r, const uint4 hdr, uint2* mine) {
+  const int ovf = atomicAdd(A.n_overflow, 1);
+  if (ovf >= A.max_overflow) return 255;
+  const int n = read_events_walk(R, A, r, hdr, A.overflow + (size_t)ovf * STREAM_OVF_CAP, STREAM_OVF_CAP);
+  if (n > STREAM_OVF_CAP) return 255;  // (cannot happen: the first walk counted the same events)
+  mine[0] = make_uint2((uint32_t)ovf, (uint32_t)n);
+  return STREAM_EV_OVERFLOW;
+}
+
+// One thread per read: the read's non-Match elements against the 2-bit reference.  No shared memory, no barrier, no atomic.
+// 8 CTAs per SM (32 registers, a dozen bytes of spills): the kernel lives on loads in flight, and the two extra CTAs are
+// worth more than the spills cost (measured 2.44 -> 2.36 ms for the step; 7 CTAs 2.37 ms).
+#ifndef GUAC_K1_MINB
+#define GUAC_K1_MINB 8
+#endif
+__global__ void __launch_bounds__(256, GUAC_K1_MINB) ss_read_events_kernel(const __grid_constant__ ReadsView R, const __grid_constant__ StreamArgs A) {
+  // block -> a block of the list or a block of the read range (see StreamArgs)
+  unsigned b = blockIdx.x;
+  bool from_list = false;
+  if (A.list_blocks) {
+    const unsigned g = b / A.list_period, k = b % A.list_period;
+    if (g < A.list_blocks) {
+      from_list = k == A.list_period - 1;
+      b = from_list ? g : g * (A.list_period - 1) + k;
+    } else {
+      b -= A.list_blocks;
+    }
+  }
+  int64_t r;
+  if (from_list) {
+    const int64_t i = (int64_t)b * blockDim.x + threadIdx.x;
+    if (i >= A.n_list) return;
+    r = __ldg(A.list + i);
+  } else {
+    r = A.read_lo + (int64_t)b * blockDim.x + threadIdx.x;
+    if (r >= A.read_hi) return;
+  }
+  const uint4 hdr = __ldg(A.hdr + r);
+  const uint8_t rf = (uint8_t)(hdr.y >> 24);
+  if (!from_list && !A.inline_medium && (rf & RF_MEDIUM) && !(rf & RF_FAST)) return;  // visited through the list
+  uint2* mine = A.events + r * STREAM_EV_CAP;
+  int n_ev = read_events_walk(R, A, r, hdr, mine, STREAM_EV_CAP);
 #ifndef GUAC_K1_PAD
 #define GUAC_K1_PAD 1
 #endif
@@ -224,7 +248,8 @@ __global__ void __launch_bounds__(256, GUAC_K1_MINB) ss_read_events_kernel(Reads
   if (n_ev < STREAM_EV_CAP)
     for (int k = n_ev; k & 3; ++k) mine[k] = make_uint2(0u, 0u);
 #endif
-  A.n_events[r] = (uint8_t)min(n_ev, 255);
+  if (n_ev > STREAM_EV_CAP) n_ev = (n_ev <= STREAM_OVF_CAP && A.overflow != nullptr) ? read_events_to_arena(R, A, r, hdr, mine) : 255;
+  A.n_events[r] = (uint8_t)n_ev;
 }
 
 }  // namespace guac

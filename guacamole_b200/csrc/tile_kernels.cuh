@@ -35,6 +35,11 @@
 #define GUAC_STREAM_EV_CAP 8
 #endif
 constexpr int STREAM_EV_CAP_C = GUAC_STREAM_EV_CAP;
+// A read with more events than its slot holds gets a record of the overflow arena (ss_read_events_kernel): its count byte
+// reads STREAM_EV_OVERFLOW, the first record of its slot is (arena record, number of events), and the arena record holds
+// all its events, up to STREAM_OVF_CAP.  Count 255: no arena record (more events still, or the arena was full).
+constexpr int STREAM_EV_OVERFLOW = 254;
+constexpr int STREAM_OVF_CAP = 64;
 #ifndef GUAC_TK_TL
 #define GUAC_TK_TL 512  // loci per tile
 #endif
@@ -194,6 +199,7 @@ struct TileArgs {
   // STREAM variant (stream_kernels.cuh): the reads were compared with the reference by a kernel of their own
   const uint2* ev_by_read;        // [n_reads][STREAM_EV_CAP] read-event records
   const uint8_t* ev_count;        // [n_reads] (more than the cap: the read is walked by the exact cursor)
+  const uint2* ev_overflow;       // [records][STREAM_OVF_CAP] (see STREAM_EV_OVERFLOW)
   // MODE 2 with at most four samples: events carry their sample id and candidate loci are classified — `simple` lists
   // the sites whose alternate alleles can only be single-base substitutions (sj_snv_site_kernel), `heavy` the others
   int sample_bits;
@@ -468,6 +474,28 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     if (STREAM) next_cnt = (int)__ldg(A.ev_count + tile.read_lo + tid);
   }
 #endif
+  // one record of the read pass -> the tile's events (the part of it inside the tile)
+  auto take_event = [&](const uint2 ev, int st, int rl, int slot, uint32_t s0_rel, int64_t r) {
+    const int l = st + (int)(ev.x & 0xFFFF);
+    const int kind = (int)((ev.x >> 16) & 7), code = (int)((ev.x >> 19) & 7);
+    if (kind == GUAC_ALN_MID_DELETION) {  // a run of deleted loci
+      const int run = (int)((ev.y >> 16) & 0x7FFF);
+      for (int ll = max(l, 0); ll < min(l + run, n_ev_loci); ++ll) push_event(ll, rl, slot, kind, code, ev.y & 0x8000FFFFu);
+      return;
+    }
+    if (l < 0 || l >= n_ev_loci) return;
+    uint32_t second = ev.y;
+    if (kind == GUAC_ALN_MISMATCH) {
+      second = s0_rel + ev.y;  // quality index relative to the tile's first base
+    } else if (kind == GUAC_ALN_DELETION && code == 4) {  // the deleted reference bases must exist (PE.scala:95)
+      const int nlen = (int)((ev.y >> 8) & 0xFF);
+      // (every locus of this tile has an A C G T reference base, or the tile would not be here: only the part of the
+      // deletion that runs past the tile's end is looked up)
+      for (int k = max(1, n_loci - l); k <= nlen; ++k)
+        if (ref.at(t0 + l + k) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + l + k, r);
+    }
+    push_event(l, rl, slot, kind, code, second);
+  };
   for (int rl = tid; rl < (int)n_reads_tile; rl += CFG::THREADS) {
     const int64_t r = tile.read_lo + rl;
     const uint4 hdr = next_hdr;
@@ -517,6 +545,11 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
     const uint64_t s0 = (uint64_t)hdr.z | ((uint64_t)hdr.w << 32);
     const uint32_t s0_rel = (uint32_t)(s0 - seq_base);
     if (STREAM) {  // the read was compared by ss_read_events_kernel: take the events that fall inside the tile
+      if (cnt == STREAM_EV_OVERFLOW) {  // its events are in the overflow arena: copied after this loop, a warp per such read
+        const int i = atomicAdd(&S.n_slow, 1);
+        if (i < CFG::SLOW_MAX) S.slow[i] = (uint16_t)(rl | 0x8000); else S.overflow = 1;
+        continue;
+      }
       if (cnt > STREAM_EV_CAP_C && (rf & RF_FAST) && ref.ref2 != nullptr) {
         // More mismatches than the read's slot holds (a mis-mapped or very noisy read), one aligned operator: the compare of
         // the read pass again, here, for the part of the read inside the tile — against the 2-bit reference in HBM / L2
@@ -554,28 +587,7 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
         continue;
       }
       const uint2* evs = A.ev_by_read + r * STREAM_EV_CAP_C;
-      for (int j = 0; j < cnt; ++j) {
-        const uint2 ev = __ldg(evs + j);
-        const int l = st + (int)(ev.x & 0xFFFF);
-        const int kind = (int)((ev.x >> 16) & 7), code = (int)((ev.x >> 19) & 7);
-        if (kind == GUAC_ALN_MID_DELETION) {  // a run of deleted loci
-          const int run = (int)((ev.y >> 16) & 0x7FFF);
-          for (int ll = max(l, 0); ll < min(l + run, n_ev_loci); ++ll) push_event(ll, rl, slot, kind, code, ev.y & 0x8000FFFFu);
-          continue;
-        }
-        if (l < 0 || l >= n_ev_loci) continue;
-        uint32_t second = ev.y;
-        if (kind == GUAC_ALN_MISMATCH) {
-          second = s0_rel + ev.y;  // quality index relative to the tile's first base
-        } else if (kind == GUAC_ALN_DELETION && code == 4) {  // the deleted reference bases must exist (PE.scala:95)
-          const int nlen = (int)((ev.y >> 8) & 0xFF);
-          // (every locus of this tile has an A C G T reference base, or the tile would not be here: only the part of the
-          // deletion that runs past the tile's end is looked up)
-          for (int k = max(1, n_loci - l); k <= nlen; ++k)
-            if (ref.at(t0 + l + k) == 0) report_error(A.err, DERR_REF_MISSING, tile.contig_id, t0 + l + k, r);
-        }
-        push_event(l, rl, slot, kind, code, second);
-      }
+      for (int j = 0; j < cnt; ++j) take_event(__ldg(evs + j), st, rl, slot, s0_rel, r);
       continue;
     }
     // aligned segment: loci [lb, le) (tile coordinates, unclipped) hold read positions rp0..; 16 bases per step
@@ -665,8 +677,19 @@ ss_tile_kernel(ReadsView R, SSParamsDev P, TileArgs A) {
   {
     const int n_slow = min(S.n_slow, CFG::SLOW_MAX);
     for (int si = warp; si < n_slow; si += CFG::WARPS) {
-      const int rl = S.slow[si];
+      const int entry = S.slow[si], rl = entry & 0x7FFF;
       const int64_t r = tile.read_lo + rl;
+      if (STREAM && (entry & 0x8000)) {  // the read's events from the overflow arena, a lane each
+        const uint4 hdr = __ldg(hdrs + rl);
+        const int smp = (int)((hdr.y >> 16) & 0xFF);
+        const int slot = MODE == 2 ? (int)((P.sample_mask >> smp) & 1u) : (smp == P.tumor_sample ? 1 : 0);
+        if (MODE == 2) ev_sample = A.sample_bits ? (uint32_t)(smp & 3) << 30 : 0u;
+        const uint2 head = __ldg(A.ev_by_read + r * STREAM_EV_CAP_C);  // (arena record, number of events)
+        const uint2* evs = A.ev_overflow + (size_t)head.x * STREAM_OVF_CAP;
+        const uint32_t s0_rel = (uint32_t)(((uint64_t)hdr.z | ((uint64_t)hdr.w << 32)) - seq_base);
+        for (int k = lane; k < (int)head.y; k += 32) take_event(__ldg(evs + k), (int)(hdr.x - t0_lo), rl, slot, s0_rel, r);
+        continue;
+      }
       const int smp = (int)__ldg(R.sample_id + r);
       const int slot = MODE == 2 ? (int)((P.sample_mask >> smp) & 1u) : (smp == P.tumor_sample ? 1 : 0);
       if (MODE == 2) ev_sample = A.sample_bits ? (uint32_t)(smp & 3) << 30 : 0u;
