@@ -567,7 +567,7 @@ int run_read_pass(guac_ctx* ctx) {
   // overflow arena: room for one read in 32 (a read beyond it, or with more than STREAM_OVF_CAP events, is walked in the
   // locus pass as before)
   const int max_overflow = (int)std::min<int64_t>(ctx->n_reads / 32 + 1024, 1 << 24);
-  GUAC_TRY(ensure(ctx, ctx->b_ev_overflow, 64 + (size_t)max_overflow * STREAM_OVF_CAP * sizeof(uint2)));
+  GUAC_TRY(ensure(ctx, ctx->b_ev_overflow, 64 + (size_t)max_overflow * (STREAM_OVF_CAP * sizeof(uint2) + sizeof(int64_t))));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_ev_overflow.p, 0, 64, ctx->stream));
   {  // reads of a contig without a reference get no launch of the read pass: their counts must read 0
     bool every_contig_has_a_reference = true;
@@ -614,6 +614,8 @@ int run_read_pass(guac_ctx* ctx) {
     SA.overflow = reinterpret_cast<uint2*>(static_cast<unsigned char*>(ctx->b_ev_overflow.p) + 64);
     SA.n_overflow = ctx->b_ev_overflow.as<int>();
     SA.max_overflow = max_overflow;
+    SA.overflow_reads = reinterpret_cast<int64_t*>(static_cast<unsigned char*>(ctx->b_ev_overflow.p) + 64 +
+                                                   (size_t)max_overflow * STREAM_OVF_CAP * sizeof(uint2));
     SA.list = nullptr;
     SA.n_list = 0;
     SA.list_blocks = SA.list_period = 0;
@@ -637,7 +639,8 @@ int run_read_pass(guac_ctx* ctx) {
       }
     }
     ss_read_events_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->R, SA);
-    ctx->launches += 1;
+    ss_read_overflow_kernel<<<(unsigned)std::min<int64_t>(blocks_for(max_overflow, 128), 148 * 8), 128, 0, ctx->stream>>>(ctx->R, SA);
+    ctx->launches += 2;
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return GUAC_OK;

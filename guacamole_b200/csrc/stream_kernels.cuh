@@ -64,6 +64,7 @@ struct StreamArgs {
   uint2* overflow;
   int* n_overflow;
   int max_overflow;
+  int64_t* overflow_reads;  // [max_overflow] the read of each arena record (ss_read_overflow_kernel fills the records)
 };
 
 // Read-event record (per read, independent of the loci of the call):
@@ -195,17 +196,6 @@ __device__ __forceinline__ int read_events_walk(const ReadsView& R, const Stream
   return n_ev;
 }
 
-// A read with more events than its slot holds: walked again, into a record of the overflow arena (out of line: the read
-// pass proper keeps its registers).  Returns the count byte of the read.
-__device__ __noinline__ int read_events_to_arena(const ReadsView& R, const StreamArgs& A, int64_t r, const uint4 hdr, uint2* mine) {
-  const int ovf = atomicAdd(A.n_overflow, 1);
-  if (ovf >= A.max_overflow) return 255;
-  const int n = read_events_walk(R, A, r, hdr, A.overflow + (size_t)ovf * STREAM_OVF_CAP, STREAM_OVF_CAP);
-  if (n > STREAM_OVF_CAP) return 255;  // (cannot happen: the first walk counted the same events)
-  mine[0] = make_uint2((uint32_t)ovf, (uint32_t)n);
-  return STREAM_EV_OVERFLOW;
-}
-
 // One thread per read: the read's non-Match elements against the 2-bit reference.  No shared memory, no barrier, no atomic.
 // 8 CTAs per SM (32 registers, a dozen bytes of spills): the kernel lives on loads in flight, and the two extra CTAs are
 // worth more than the spills cost (measured 2.44 -> 2.36 ms for the step; 7 CTAs 2.37 ms).
@@ -248,8 +238,33 @@ __global__ void __launch_bounds__(256, GUAC_K1_MINB) ss_read_events_kernel(const
   if (n_ev < STREAM_EV_CAP)
     for (int k = n_ev; k & 3; ++k) mine[k] = make_uint2(0u, 0u);
 #endif
-  if (n_ev > STREAM_EV_CAP) n_ev = (n_ev <= STREAM_OVF_CAP && A.overflow != nullptr) ? read_events_to_arena(R, A, r, hdr, mine) : 255;
+  if (n_ev > STREAM_EV_CAP) {
+    // more events than the slot holds: the read gets a record of the overflow arena, filled by ss_read_overflow_kernel —
+    // a second walk, with every lane of its warps on such a read instead of one lane here and 31 waiting
+    int ovf = INT_MAX;
+    if (n_ev <= STREAM_OVF_CAP && A.overflow != nullptr) ovf = atomicAdd(A.n_overflow, 1);
+    if (ovf < A.max_overflow) {
+      A.overflow_reads[ovf] = r;
+      mine[0] = make_uint2((uint32_t)ovf, (uint32_t)n_ev);
+      n_ev = STREAM_EV_OVERFLOW;
+    } else {
+      n_ev = 255;
+    }
+  }
   A.n_events[r] = (uint8_t)n_ev;
+}
+
+// The arena records of the reads ss_read_events_kernel listed: one thread per record, the read walked again with room for
+// all its events.  The launch is sized before the number of records is known and strides over them.
+__global__ void __launch_bounds__(128) ss_read_overflow_kernel(const __grid_constant__ ReadsView R, const __grid_constant__ StreamArgs A) {
+  const int n = min(*A.n_overflow, A.max_overflow);
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const int64_t r = A.overflow_reads[t];
+    // (a batch of several contigs has one launch pair per contig, each with that contig's reference, and one arena: the
+    // records of the other contigs' reads belong to their launches)
+    if (A.list_blocks == 0 && (r < A.read_lo || r >= A.read_hi)) continue;
+    read_events_walk(R, A, r, __ldg(A.hdr + r), A.overflow + (size_t)t * STREAM_OVF_CAP, STREAM_OVF_CAP);
+  }
 }
 
 }  // namespace guac

@@ -33,6 +33,43 @@ def test_somatic_standard_on_realistic_reads(gpu_ctx):
     assert fallback <= 0.01 * ((contig_len + 511) // 512) and heavy <= 0.01 * got["n_visited"], (fallback, heavy)
 
 
+def test_two_contigs_of_realistic_reads(gpu_ctx):
+    """A batch of two contigs: the read pass runs once per contig (each with its own reference) and both share the overflow
+    arena of the reads with more events than their slot holds (the 1 % of reads with 10..20 mismatches)."""
+    from guacamole_b200.io import Reference
+    from guacamole_b200.reads import ReadBatch
+    lens, seeds, names = (60_000, 90_000), (3201, 3202), ("ctgA", "ctgB")
+    refs = [synth.make_reference(n, s) for n, s in zip(lens, seeds)]
+    parts = [synth.generate_reads(n, (30, 60), (False, True), s, profile=1, contig_name=c) for n, s, c in zip(lens, seeds, names)]
+    windows = {}
+    for c, r in zip(names, refs):
+        (w,) = r.contigs.values()
+        w.name = c
+        windows[c] = w
+    ref = Reference(windows)
+    a, b = parts
+    batch = ReadBatch(
+        n_samples=2, contig_names=list(names), contig_id=np.concatenate([a.contig_id, b.contig_id + 1]), start=np.concatenate([a.start, b.start]),
+        cigar_off=np.concatenate([a.cigar_off, b.cigar_off[1:] + a.cigar_off[-1]]).astype(np.uint32), cigar=np.concatenate([a.cigar, b.cigar]),
+        seq_off=np.concatenate([a.seq_off, b.seq_off[1:] + a.seq_off[-1]]).astype(np.uint64), bases_ascii=np.concatenate([a.bases_ascii, b.bases_ascii]),
+        qual=np.concatenate([a.qual, b.qual]), mapq=np.concatenate([a.mapq, b.mapq]), flags=np.concatenate([a.flags, b.flags]),
+        sample_id=np.concatenate([a.sample_id, b.sample_id]))
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    gpu_ctx.upload_reads(batch)
+    loci = [(0, 0, lens[0]), (1, 0, lens[1])]
+    got = gpu_ctx.somatic_standard(loci, want_summary=True)
+    want = oracle.somatic_standard(batch, ref, loci, want_summary=True, n_threads=8)
+    assert got["n_visited"] == want["n_visited"] and len(want["calls"]) > 5
+    assert gpu_ctx.last_stat("fallback_tiles") == 0
+    assert np.array_equal(got["summary"], want["summary"])
+    assert np.array_equal(got["calls"]["contig_id"], want["calls"]["contig_id"]) and np.array_equal(got["calls"]["start"], want["calls"]["start"])
+    np.testing.assert_allclose(got["calls"]["somatic_log_odds"], want["calls"]["somatic_log_odds"], rtol=1e-9)
+    # and the second contig alone, its reads in the middle of the batch's arena
+    part = gpu_ctx.somatic_standard([(1, 20_000, 50_000)])
+    inside = (want["calls"]["contig_id"] == 1) & (want["calls"]["start"] >= 20_000) & (want["calls"]["start"] < 50_000)
+    assert np.array_equal(part["calls"]["start"], want["calls"]["start"][inside])
+
+
 def test_somatic_joint_on_realistic_reads(gpu_ctx):
     contig_len, depths, tumor, kinds, seed = 150_000, (30, 30, 60, 60), (False, False, True, True), [0, 0, 1, 1], 4500
     ref = synth.make_reference(contig_len, seed)
