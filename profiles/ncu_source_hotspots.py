@@ -6,10 +6,11 @@ rows = list(csv.reader(open(sys.argv[1])))
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 agg = collections.OrderedDict()
 fname, cur, hdr = None, None, None
+seen = set()  # (source line, SASS address): the page can list a function twice
 for r in rows:
     if not r:
         continue
-    if r[0] == "File Name":
+    if r[0] in ("File Name", "File Path"):
         fname = r[1].split("/")[-1]; continue
     if r[0] == "Line No":
         hdr = r; ie = r.index("Instructions Executed"); ws = r.index("Warp Stall Sampling (All Samples)"); continue
@@ -17,8 +18,9 @@ for r in rows:
         continue
     if r[0] != "":
         cur = (fname, int(r[0]), r[1].strip()[:100]); agg.setdefault(cur, [0, 0, collections.Counter()]); continue
-    if cur is None or r[2] == "...":
+    if cur is None or r[2] == "..." or (cur, r[2]) in seen:
         continue
+    seen.add((cur, r[2]))
     try:
         n, s = int(r[ie] or 0), int(r[ws] or 0)
     except ValueError:
