@@ -517,7 +517,7 @@ def main():
     abytes = algorithmic_bytes_per_locus(sum(DEPTHS), len(DEPTHS))
     achieved = abytes * loci_step / (k_ms / 1000.0) / 1e9
     traffic, traffic_src = None, None
-    tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r2_traffic.json")
     if os.path.exists(tpath) and args.contig_mbp == 50:
         tj = json.load(open(tpath))
         traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
