@@ -1,5 +1,45 @@
 // compact_entry.inl — guac_reads_upload_compact / guac_reads_export_compact (included at the end of guac_b200.cu).
 
+namespace {
+// guac_read_batch_compact::mm_count given: the full 2-bit base column from the explicit reads' stream, the contigs' 2-bit
+// reference windows and the difference words.  Runs on the context's stream behind the copy of the explicit bases.
+int expand_ref_relative(guac_ctx* ctx, const guac_read_batch_compact* b, int64_t n, uint64_t n_bases) {
+  GUAC_TRY(upload(ctx, ctx->u_mm_count, b->mm_count, (size_t)n));
+  GUAC_TRY(upload(ctx, ctx->u_mm_words, b->mm_words, (size_t)b->n_mm_words, 16));
+  GUAC_TRY(ensure(ctx, ctx->u_expl_len, (size_t)n * sizeof(uint16_t) + 16));
+  GUAC_TRY(ensure(ctx, ctx->u_mm_n, (size_t)n + 16));
+  GUAC_TRY(ensure(ctx, ctx->u_expl_off, (size_t)(n + 1) * sizeof(int64_t)));
+  GUAC_TRY(ensure(ctx, ctx->u_mm_off, (size_t)(n + 1) * sizeof(int64_t)));
+  compact::refrel_lengths_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, ctx->u_mm_count.as<uint8_t>(), ctx->b_seq_off.as<uint64_t>(),
+                                                                             ctx->u_expl_len.as<uint16_t>(), ctx->u_mm_n.as<uint8_t>(),
+                                                                             ctx->u_bad.as<int>());
+  ctx->launches += 1;
+  GUAC_TRY((device_scan<true, uint16_t>(ctx, ctx->u_expl_len.as<uint16_t>(), ctx->u_expl_off.as<int64_t>(), n, OpSum(),
+                                        ctx->u_expl_off.as<int64_t>() + n)));
+  GUAC_TRY((device_scan<true, uint8_t>(ctx, ctx->u_mm_n.as<uint8_t>(), ctx->u_mm_off.as<int64_t>(), n, OpSum(), ctx->u_mm_off.as<int64_t>() + n)));
+  int64_t totals[2] = {0, 0};
+  CUDA_TRY(ctx, cudaMemcpyAsync(&totals[0], ctx->u_expl_off.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(&totals[1], ctx->u_mm_off.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (totals[0] != b->n_explicit_bases || totals[1] != b->n_mm_words)
+    return fail(ctx, GUAC_E_INVALID_INPUT, "reference-relative bases: n_explicit_bases / n_mm_words do not match mm_count");
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->b_bases2.p, 0, (size_t)((n_bases + 3) / 4) + 64, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->join, 0));  // the explicit bases have arrived
+  for (auto& sp : ctx->contig_spans) {  // one launch per contig of the batch: its reference rides in the arguments
+    const ContigDev& c = ctx->contigs.at(sp.first);
+    const int64_t lo = sp.second.first, hi = sp.second.second;
+    if (hi <= lo) continue;
+    compact::refrel_expand_kernel<<<blocks_for(hi - lo, 256), 256, 0, ctx->stream>>>(
+        lo, hi, ctx->u_mm_count.as<uint8_t>(), ctx->u_mm_words.as<uint16_t>(), ctx->u_mm_off.as<int64_t>(), ctx->u_expl.as<uint32_t>(),
+        ctx->u_expl_off.as<int64_t>(), ctx->b_start.as<int64_t>(), ctx->b_seq_off.as<uint64_t>(), c.ref2, c.offset, c.len,
+        ctx->b_bases2.as<uint32_t>(), ctx->u_bad.as<int>());
+    ctx->launches += 1;
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  return GUAC_OK;
+}
+}  // namespace
+
 int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   if (!ctx || !b) return GUAC_E_INVALID_INPUT;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -20,6 +60,17 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   }
   if (n > 0 && (b->n_contig_runs == 0 || b->run_first_read[b->n_contig_runs] != n))
     return fail(ctx, GUAC_E_INVALID_INPUT, "contig runs do not cover the batch");
+  // reference-relative bases: the 2-bit copies of the contigs' reference windows are the source of most reads' bases
+  const bool ref_rel = b->mm_count != nullptr;
+  if (ref_rel) {
+    if (b->n_mm_words < 0 || b->n_explicit_bases < 0 || (b->n_mm_words > 0 && !b->mm_words))
+      return fail(ctx, GUAC_E_INVALID_INPUT, "bad reference-relative columns");
+    for (auto& sp : ctx->contig_spans)
+      if (!ctx->contigs.count(sp.first))
+        return fail(ctx, GUAC_E_STATE, "reference-relative bases: upload the reference window of contig " + std::to_string(sp.first) +
+                                           " before the reads");
+    GUAC_TRY(sync_ref2(ctx));
+  }
   // scratch kept in the context: a cudaMalloc / cudaFree pair per column and call costs more than the kernels here
   DevBuf &d_len = ctx->u_len, &d_ops = ctx->u_ops, &d_runs_c = ctx->u_runs_c, &d_runs_f = ctx->u_runs_f, &d_tmp = ctx->u_tmp,
          &d_qpacked = ctx->u_qpacked, &d_bad = ctx->u_bad;
@@ -132,8 +183,13 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   }
   CUDA_TRY(ctx, cudaEventRecord(ctx->fork, ctx->stream));
   CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->fork, 0));
-  if (n_bases > 0)
+  if (ref_rel) {  // the explicit reads' bases only; the rest is built below
+    GUAC_TRY(ensure(ctx, ctx->u_expl, (size_t)((b->n_explicit_bases + 3) / 4) + 64));
+    if (b->n_explicit_bases > 0)
+      CUDA_TRY(ctx, cudaMemcpyAsync(ctx->u_expl.p, b->bases2, (size_t)((b->n_explicit_bases + 3) / 4), cudaMemcpyHostToDevice, ctx->stream2));
+  } else if (n_bases > 0) {
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->b_bases2.p, b->bases2, (size_t)((n_bases + 3) / 4), cudaMemcpyHostToDevice, ctx->stream2));
+  }
   // From here on the copy of the bases is in flight out of the caller's buffer: every exit goes through the wait on
   // `join` at the end, so no early return below.
   int st = GUAC_OK;
@@ -155,12 +211,16 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
     ctx->launches += 1;
   }
   cuda_ok(cudaGetLastError(), "the quality expansion");
+  if (ref_rel && n > 0 && st == GUAC_OK) st = expand_ref_relative(ctx, b, n, n_bases);
   int bad = 0;
   cuda_ok(cudaMemcpyAsync(&bad, d_bad.p, sizeof bad, cudaMemcpyDeviceToHost, ctx->stream), "cudaMemcpyAsync(bad)");
   cuda_ok(cudaStreamSynchronize(ctx->stream), "cudaStreamSynchronize");
   if (st == GUAC_OK && (bad & 1)) st = fail(ctx, GUAC_E_INVALID_INPUT, "Regions must be sorted by start locus");
   if (st == GUAC_OK && (bad & 2)) st = fail(ctx, GUAC_E_INVALID_INPUT, "sample_id >= n_samples");
   if (st == GUAC_OK && (bad & 4)) st = fail(ctx, GUAC_E_INVALID_INPUT, "read start out of range");
+  if (st == GUAC_OK && (bad & (8 | 16 | 32)))
+    st = fail(ctx, GUAC_E_INVALID_INPUT, "reference-relative bases: a read of 16384 bases or more, a read outside its contig's reference window, "
+                                         "or a difference word out of range");
   if (st == GUAC_OK) st = finish_reads(ctx, n, b->n_samples, b->n_exc);
   // the caller's buffers may go away after return, whatever the outcome: the copy of the bases must have ended
   const cudaError_t e2 = cudaEventSynchronize(ctx->join);
@@ -285,7 +345,67 @@ int guac_reads_export_compact(guac_ctx* ctx, guac_read_batch_compact* out) {
     GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->n_cigar_ops), d_ops.p, (size_t)n));
     GUAC_TRY(host_out(ctx, const_cast<uint32_t**>(&out->cigar), ctx->b_cigar.p, (size_t)n_cigar));
   }
-  GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->bases2), ctx->b_bases2.p, (size_t)((n_bases + 3) / 4)));
+  bool ref_rel = ctx->opt_compact_ref_relative && n > 0;
+  for (auto& sp : ctx->contig_spans) ref_rel = ref_rel && ctx->contigs.count(sp.first) != 0;
+  DevBuf d_mm_count, d_mm_words, d_expl, d_expl_len, d_mm_n, d_expl_off, d_mm_off;
+  Free fr3{{&d_mm_count, &d_mm_words, &d_expl, &d_expl_len, &d_mm_n, &d_expl_off, &d_mm_off}};
+  if (ref_rel) {
+    // the read pass over the whole batch: a single-operator read's records are its differences from the reference
+    ctx->plan_ranges.clear();
+    for (auto& sp : ctx->contig_spans) {
+      RangeDev rg;
+      std::memset(&rg, 0, sizeof rg);
+      rg.contig_id = sp.first;
+      rg.start = 0;
+      rg.end = (int64_t)1 << 40;
+      ctx->plan_ranges.push_back(rg);
+    }
+    GUAC_TRY(run_read_pass(ctx));
+    GUAC_TRY(ensure(ctx, d_mm_count, (size_t)n + 16));
+    GUAC_TRY(ensure(ctx, d_expl_len, (size_t)n * sizeof(uint16_t) + 16));
+    GUAC_TRY(ensure(ctx, d_mm_n, (size_t)n + 16));
+    GUAC_TRY(ensure(ctx, d_expl_off, (size_t)(n + 1) * sizeof(int64_t)));
+    GUAC_TRY(ensure(ctx, d_mm_off, (size_t)(n + 1) * sizeof(int64_t)));
+    for (auto& sp : ctx->contig_spans) {
+      const ContigDev& c = ctx->contigs.at(sp.first);
+      const int64_t lo = sp.second.first, hi = sp.second.second;
+      if (hi <= lo) continue;
+      compact::refrel_classify_kernel<<<blocks_for(hi - lo, 256), 256, 0, ctx->stream>>>(
+          lo, hi, ctx->b_hdr.as<uint4>(), ctx->b_bin_count.as<uint8_t>(), STREAM_EV_CAP, ctx->R.start, ctx->R.end, ctx->R.seq_off, c.offset, c.len,
+          c.refbad, d_mm_count.as<uint8_t>(), d_expl_len.as<uint16_t>(), d_mm_n.as<uint8_t>());
+      ctx->launches += 1;
+    }
+    CUDA_TRY(ctx, cudaGetLastError());
+    GUAC_TRY((device_scan<true, uint16_t>(ctx, d_expl_len.as<uint16_t>(), d_expl_off.as<int64_t>(), n, OpSum(), d_expl_off.as<int64_t>() + n)));
+    GUAC_TRY((device_scan<true, uint8_t>(ctx, d_mm_n.as<uint8_t>(), d_mm_off.as<int64_t>(), n, OpSum(), d_mm_off.as<int64_t>() + n)));
+    int64_t totals[2] = {0, 0};
+    CUDA_TRY(ctx, cudaMemcpyAsync(&totals[0], d_expl_off.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&totals[1], d_mm_off.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    out->n_explicit_bases = totals[0];
+    out->n_mm_words = totals[1];
+    GUAC_TRY(ensure(ctx, d_mm_words, (size_t)totals[1] * sizeof(uint16_t) + 16));
+    GUAC_TRY(ensure(ctx, d_expl, (size_t)((totals[0] + 3) / 4) + 64));
+    CUDA_TRY(ctx, cudaMemsetAsync(d_expl.p, 0, (size_t)((totals[0] + 3) / 4) + 64, ctx->stream));
+    for (auto& sp : ctx->contig_spans) {
+      const ContigDev& c = ctx->contigs.at(sp.first);
+      const int64_t lo = sp.second.first, hi = sp.second.second;
+      if (hi <= lo) continue;
+      compact::refrel_words_kernel<<<blocks_for(hi - lo, 256), 256, 0, ctx->stream>>>(
+          lo, hi, d_mm_count.as<uint8_t>(), d_mm_off.as<int64_t>(), ctx->b_bins.as<uint2>(), STREAM_EV_CAP, ctx->R.start, c.ref2, c.offset,
+          d_mm_words.as<uint16_t>());
+      ctx->launches += 1;
+    }
+    compact::refrel_explicit_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(n, d_mm_count.as<uint8_t>(), d_expl_off.as<int64_t>(), ctx->R.seq_off,
+                                                                               reinterpret_cast<const uint32_t*>(ctx->R.bases2), d_expl.as<uint32_t>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->mm_count), d_mm_count.p, (size_t)n));
+    GUAC_TRY(host_out(ctx, const_cast<uint16_t**>(&out->mm_words), d_mm_words.p, (size_t)totals[1]));
+    GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->bases2), d_expl.p, (size_t)((totals[0] + 3) / 4)));
+  } else {
+    GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->bases2), ctx->b_bases2.p, (size_t)((n_bases + 3) / 4)));
+  }
   out->n_exc = ctx->R.n_exc;
   GUAC_TRY(host_out(ctx, const_cast<uint64_t**>(&out->exc_pos), ctx->b_exc_pos.p, (size_t)ctx->R.n_exc));
   GUAC_TRY(host_out(ctx, const_cast<uint8_t**>(&out->exc_base), ctx->b_exc_base.p, (size_t)ctx->R.n_exc));

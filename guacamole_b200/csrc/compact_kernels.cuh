@@ -191,5 +191,126 @@ __global__ void validate_kernel(int64_t n, const int64_t* __restrict__ start, co
   if (r > 0 && contig_id[r] == contig_id[r - 1] && s < start[r - 1]) atomicOr(bad, 1);
 }
 
+
+// ---- reference-relative bases (guac_read_batch_compact::mm_count / mm_words) ------------------------------------------
+
+// 32 bits of a 2-bit stream starting at bit `bit` (the word after the last one of a buffer is padding, never garbage-sensitive:
+// callers mask what they use)
+__device__ __forceinline__ uint32_t bits32_at(const uint32_t* __restrict__ words, uint64_t bit) {
+  const uint32_t* w = words + (bit >> 5);
+  return __funnelshift_r(__ldg(w), __ldg(w + 1), (int)(bit & 31));
+}
+
+// Copies n 2-bit symbols from (src, symbol src_sym) to (dst, symbol dst_sym).  dst is zeroed beforehand; the words this run
+// shares with its neighbours are merged with atomicOr, the words it owns are stored.
+__device__ __forceinline__ void copy_symbols(uint32_t* __restrict__ dst, uint64_t dst_sym, const uint32_t* __restrict__ src, uint64_t src_sym, int n) {
+  uint64_t dbit = 2 * dst_sym, sbit = 2 * src_sym;
+  int left = 2 * n;  // bits
+  if (left <= 0) return;
+  const int head = (int)(dbit & 31);
+  if (head) {  // up to the next word boundary of dst
+    const int take = min(left, 32 - head);
+    const uint32_t v = bits32_at(src, sbit) & (take == 32 ? 0xFFFFFFFFu : ((1u << take) - 1u));
+    atomicOr(dst + (dbit >> 5), v << head);
+    dbit += take;
+    sbit += take;
+    left -= take;
+  }
+  for (; left >= 32; left -= 32, dbit += 32, sbit += 32) dst[dbit >> 5] = bits32_at(src, sbit);
+  if (left > 0) atomicOr(dst + (dbit >> 5), bits32_at(src, sbit) & ((1u << left) - 1u));
+}
+
+// per read: how many of its bases travel explicitly, and how many difference words it has
+__global__ void refrel_lengths_kernel(int64_t n, const uint8_t* __restrict__ mm_count, const uint64_t* __restrict__ seq_off,
+                                      uint16_t* __restrict__ expl_len, uint8_t* __restrict__ mm_n, int* __restrict__ bad) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const uint64_t len = seq_off[r + 1] - seq_off[r];
+  const bool expl = mm_count[r] == 255;
+  expl_len[r] = expl ? (uint16_t)len : (uint16_t)0;
+  mm_n[r] = expl ? (uint8_t)0 : mm_count[r];
+  if (!expl && len >= 16384) atomicOr(bad, 8);  // positions are 14 bits
+}
+
+// The full 2-bit base column from the wire form, one thread per read of one contig: explicit reads from the explicit
+// stream, the others from the contig's 2-bit reference window with their differences patched in.
+__global__ void refrel_expand_kernel(int64_t read_lo, int64_t read_hi, const uint8_t* __restrict__ mm_count,
+                                     const uint16_t* __restrict__ mm_words, const int64_t* __restrict__ mm_off,
+                                     const uint32_t* __restrict__ expl, const int64_t* __restrict__ expl_off,
+                                     const int64_t* __restrict__ start, const uint64_t* __restrict__ seq_off,
+                                     const uint32_t* __restrict__ ref2, int64_t ref_offset, int64_t ref_len, uint32_t* __restrict__ bases2,
+                                     int* __restrict__ bad) {
+  const int64_t r = read_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= read_hi) return;
+  const uint64_t s0 = seq_off[r];
+  const int len = (int)(seq_off[r + 1] - s0);
+  if (mm_count[r] == 255) {
+    copy_symbols(bases2, s0, expl, (uint64_t)expl_off[r], len);
+    return;
+  }
+  const int64_t rel = start[r] - ref_offset;
+  if (ref2 == nullptr || rel < 0 || rel + len > ref_len) {  // the sender promised a read inside the window
+    atomicOr(bad, 16);
+    return;
+  }
+  copy_symbols(bases2, s0, ref2, (uint64_t)rel, len);
+  const int64_t m0 = mm_off[r];
+  for (int k = 0; k < (int)mm_count[r]; ++k) {
+    const uint32_t w = mm_words[m0 + k];
+    const uint32_t pos = w >> 2, x = w & 3u;
+    if ((int)pos >= len || x == 0) {
+      atomicOr(bad, 32);
+      continue;
+    }
+    const uint64_t bit = 2 * (s0 + pos);
+    atomicXor(bases2 + (bit >> 5), x << (bit & 31));
+  }
+}
+
+// Export side.  Which reads can travel as differences: one aligned operator over A C G T bases (RF_FAST, bit 0 of the flags
+// byte of the packed header), a complete slot of the read pass (every record of such a read is a Mismatch), wholly on
+// A C G T reference inside the window, shorter than 16384 bases.
+__global__ void refrel_classify_kernel(int64_t read_lo, int64_t read_hi, const uint4* __restrict__ hdr, const uint8_t* __restrict__ ev_count,
+                                       int ev_cap, const int64_t* __restrict__ start, const int64_t* __restrict__ end,
+                                       const uint64_t* __restrict__ seq_off, int64_t ref_offset, int64_t ref_len,
+                                       const uint32_t* __restrict__ ref_bad, uint8_t* __restrict__ mm_count, uint16_t* __restrict__ expl_len,
+                                       uint8_t* __restrict__ mm_n) {
+  const int64_t r = read_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= read_hi) return;
+  const uint64_t len = seq_off[r + 1] - seq_off[r];
+  const int64_t s = start[r], e = end[r];
+  const int cnt = ev_count ? (int)ev_count[r] : 255;
+  bool ok = ((hdr[r].y >> 24) & 1u) && cnt <= ev_cap && len < 16384 && e > s && s >= ref_offset && e <= ref_offset + ref_len;
+  if (ok && ref_bad != nullptr)
+    for (int64_t g = (s - ref_offset) >> 4; ok && g <= (e - 1 - ref_offset) >> 4; ++g) ok = !((__ldg(ref_bad + (g >> 5)) >> (g & 31)) & 1u);
+  mm_count[r] = ok ? (uint8_t)cnt : (uint8_t)255;
+  expl_len[r] = ok ? (uint16_t)0 : (uint16_t)len;
+  mm_n[r] = ok ? (uint8_t)cnt : (uint8_t)0;
+}
+
+// ... their difference words, from the read pass's records (x = offset | kind << 16 | read base code << 19)
+__global__ void refrel_words_kernel(int64_t read_lo, int64_t read_hi, const uint8_t* __restrict__ mm_count, const int64_t* __restrict__ mm_off,
+                                    const uint2* __restrict__ events, int ev_cap, const int64_t* __restrict__ start,
+                                    const uint32_t* __restrict__ ref2, int64_t ref_offset, uint16_t* __restrict__ mm_words) {
+  const int64_t r = read_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= read_hi || mm_count[r] == 255) return;
+  const int64_t rel = start[r] - ref_offset, m0 = mm_off[r];
+  for (int k = 0; k < (int)mm_count[r]; ++k) {
+    const uint32_t x = events[r * ev_cap + k].x;
+    const uint32_t pos = x & 0xFFFFu, code = (x >> 19) & 3u;
+    const uint64_t bit = 2 * (uint64_t)(rel + pos);
+    const uint32_t ref_code = (__ldg(ref2 + (bit >> 5)) >> (bit & 31)) & 3u;
+    mm_words[m0 + k] = (uint16_t)((pos << 2) | (ref_code ^ code));
+  }
+}
+
+// ... and the explicit reads' bases, concatenated
+__global__ void refrel_explicit_kernel(int64_t n, const uint8_t* __restrict__ mm_count, const int64_t* __restrict__ expl_off,
+                                       const uint64_t* __restrict__ seq_off, const uint32_t* __restrict__ bases2, uint32_t* __restrict__ expl) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n || mm_count[r] != 255) return;
+  copy_symbols(expl, (uint64_t)expl_off[r], bases2, seq_off[r], (int)(seq_off[r + 1] - seq_off[r]));
+}
+
 }  // namespace compact
 }  // namespace guac

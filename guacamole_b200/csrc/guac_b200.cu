@@ -102,9 +102,10 @@ struct guac_ctx {
   // every READ_INDEX_STRIDE-th entry of the start column, of the running-max end keys and of the multi-operator list, on the
   // host: a call over part of the batch's loci runs the read pass over the reads that can overlap them only
   std::vector<int64_t> h_idx_start, h_idx_runmax, h_idx_medium;
-  DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off, u_idx;  // upload scratch, kept between calls
+  DevBuf u_len, u_ops, u_runs_c, u_runs_f, u_tmp, u_qpacked, u_bad, u_flag, u_off, u_idx, u_expl, u_mm_count, u_mm_words, u_expl_len, u_mm_n, u_expl_off, u_mm_off;  // upload scratch, kept between calls
   DevBuf u_start_rel, u_runs_base, u_ops8, u_ops_eff, u_wire_off, u_wire;          // ... of the narrow columns of the wire form
   int64_t opt_compact_narrow = 1;
+  int64_t opt_compact_ref_relative = 0;  // guac_reads_export_compact: reads as differences from the reference where they can
   int64_t opt_compact_min_qual_bits = 2;  // guac_reads_export_compact: 2 (default) the narrowest form the qualities allow; 4 / 8 force wider ones
   int64_t opt_sj_host_threads = 0;  // 0: as many as the host has cores, at most 32
   std::vector<RangeDev> plan_ranges;            // host copy of the current call's range table (make_plan)
@@ -722,7 +723,8 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->fork) cudaEventDestroy(ctx->fork);
   if (ctx->join) cudaEventDestroy(ctx->join);
   for (DevBuf* b : {&ctx->b_ev_overflow, &ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
-                    &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_idx, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
+                    &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_idx, &ctx->u_expl, &ctx->u_mm_count, &ctx->u_mm_words, &ctx->u_expl_len, &ctx->u_mm_n,
+                    &ctx->u_expl_off, &ctx->u_mm_off, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
                     &ctx->u_ops_eff, &ctx->u_wire_off, &ctx->u_wire, &ctx->g_active, &ctx->g_jobs, &ctx->g_evs, &ctx->g_strings,
                     &ctx->r_bitmap, &ctx->r_counts, &ctx->r_prefix, &ctx->r_rank, &ctx->j_force, &ctx->j_simple, &ctx->j_sites_fast,
                     &ctx->j_raw_fast, &ctx->j_bail, &ctx->j_raw_gen, &ctx->j_emits, &ctx->j_order, &ctx->j_cnt, &ctx->j_off,
@@ -1882,6 +1884,8 @@ int guac_set_option(guac_ctx* ctx, const char* name, int64_t value) {
   } else if (n == "compact_min_qual_bits") {
     if (value != 2 && value != 4 && value != 8) return fail(ctx, GUAC_E_INVALID_INPUT, "compact_min_qual_bits must be 2, 4 or 8");
     ctx->opt_compact_min_qual_bits = value;
+  } else if (n == "compact_ref_relative") {
+    ctx->opt_compact_ref_relative = value != 0;
   } else if (n == "compact_narrow") {
     ctx->opt_compact_narrow = value != 0;
   } else if (n == "ss_rank_max") {

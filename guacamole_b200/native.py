@@ -236,19 +236,25 @@ class ReadBatchCompactC(C.Structure):
                 ("sample_id", u8p),
                 # narrow forms of start / n_cigar_ops / read_len (NULL / 0: the wide column is given)
                 ("run_start_base", i64p), ("start_rel", u32p), ("n_cigar_ops8", u8p), ("uniform_read_len", C.c_int32),
-                ("_pad2", C.c_int32)]
+                ("_pad2", C.c_int32),
+                # reference-relative bases (NULL: bases2 holds every read)
+                ("mm_count", u8p), ("mm_words", u16p), ("n_mm_words", C.c_int64), ("n_explicit_bases", C.c_int64)]
 
     def wire_bytes(self, n_bases: int, n_cigar_words: int) -> int:
         """Bytes this batch puts on the wire (what guac_reads_upload_compact copies to the device)."""
         n = int(self.n_reads)
         per_read = (4 if self.start_rel else 8) + (0 if self.uniform_read_len > 0 else 2) + (1 if self.n_cigar_ops8 else 2) + 3
         q = n_bases if self.qual_bits == 8 else (n_bases * self.qual_bits + 7) // 8
-        return n * per_read + 4 * n_cigar_words + (n_bases + 3) // 4 + q + 9 * int(self.n_exc) + 20 * int(self.n_contig_runs) + 8
+        bases = (n_bases + 3) // 4
+        if self.mm_count:  # reference-relative: a count per read, the difference words, the explicit reads' bases
+            bases = n + 2 * int(self.n_mm_words) + (int(self.n_explicit_bases) + 3) // 4
+        return n * per_read + 4 * n_cigar_words + bases + q + 9 * int(self.n_exc) + 20 * int(self.n_contig_runs) + 8
 
 
-def compact_struct(batch: ReadBatch, narrow: bool = True) -> ReadBatchCompactC:
+def compact_struct(batch: ReadBatch, narrow: bool = True, ref=None) -> ReadBatchCompactC:
     """Host-side packer of the compact wire form (numpy); keeps the arrays alive on the returned struct.
-    narrow: use the narrow start / operator-count / read-length columns where the batch allows them."""
+    narrow: use the narrow start / operator-count / read-length columns where the batch allows them.
+    ref (a `Reference`): reads that can travel as their differences from it do (mm_count / mm_words)."""
     if batch.packed is None:
         batch.packed = pack_bases(batch.bases_ascii)
     p = batch.packed
@@ -306,8 +312,60 @@ def compact_struct(batch: ReadBatch, narrow: bool = True) -> ReadBatchCompactC:
             b.n_cigar_ops8, b.n_cigar_ops, b.cigar = ptr(keep["ops8"], u8p), None, ptr(keep["wire"], u32p)
     b.n_exc, b.exc_pos, b.exc_base = p["n_exc"], ptr(p["exc_pos"], u64p), ptr(p["exc_base"], u8p)
     b.qual, b.mapq, b.flags, b.sample_id = ptr(keep["qual"], u8p), ptr(batch.mapq, u8p), ptr(batch.flags, u8p), ptr(batch.sample_id, u8p)
+    if ref is not None and n:
+        mm_count, mm_words, explicit = reference_relative_columns(batch, ref)
+        code = np.full(256, 0, np.uint8)
+        for i, ch in enumerate(b"ACGT"):
+            code[ch] = i
+        sym = code[explicit] if len(explicit) else np.zeros(0, np.uint8)
+        if len(sym) % 4:
+            sym = np.concatenate([sym, np.zeros(4 - len(sym) % 4, np.uint8)])
+        packed = (sym[0::4] | (sym[1::4] << 2) | (sym[2::4] << 4) | (sym[3::4] << 6)).astype(np.uint8) if len(sym) else np.zeros(0, np.uint8)
+        keep["mm_count"], keep["mm_words"] = mm_count, np.concatenate([mm_words, np.zeros(1, np.uint16)])
+        keep["explicit2"] = np.concatenate([packed, np.zeros(8, np.uint8)])
+        b.mm_count, b.mm_words, b.bases2 = ptr(keep["mm_count"], u8p), ptr(keep["mm_words"], u16p), ptr(keep["explicit2"], u8p)
+        b.n_mm_words, b.n_explicit_bases = len(mm_words), len(explicit)
     b._keep = keep
     return b
+
+
+def reference_relative_columns(batch: ReadBatch, ref):
+    """(mm_count [n_reads] u8, mm_words u16, ASCII bases of the explicit reads) — see guac_read_batch_compact::mm_count: a read
+    with one aligned operator over all its bases, A C G T only, wholly on A C G T reference inside its contig's window and
+    shorter than 16384 bases travels as its differences (position << 2 | reference code XOR read code), at most 254 of them."""
+    n = batch.n_reads
+    code = np.full(256, 255, np.uint8)
+    for i, ch in enumerate(b"ACGT"):
+        code[ch] = i
+    mm_count = np.full(n, 255, np.uint8)
+    words, explicit = [], []
+    seq_off, cig_off = batch.seq_off.astype(np.int64), batch.cigar_off.astype(np.int64)
+    for r in range(n):
+        s0, s1 = int(seq_off[r]), int(seq_off[r + 1])
+        bases = batch.bases_ascii[s0:s1]
+        ok = cig_off[r + 1] - cig_off[r] == 1 and s1 - s0 < 16384
+        if ok:
+            w = int(batch.cigar[cig_off[r]])
+            ok = (w & 15) in (0, 7, 8) and (w >> 4) == s1 - s0  # M, =, X over every base
+        window = ref.contigs.get(batch.contig_names[int(batch.contig_id[r])]) if ok else None
+        if window is not None:
+            rel = int(batch.start[r]) - window.offset
+            ok = rel >= 0 and rel + (s1 - s0) <= len(window.bases)
+            if ok:
+                rc, bc = code[window.bases[rel:rel + s1 - s0]], code[bases]
+                ok = bool((rc < 4).all() and (bc < 4).all())
+                if ok:
+                    pos = np.flatnonzero(rc != bc)
+                    ok = len(pos) < 255
+                    if ok:
+                        mm_count[r] = len(pos)
+                        words.append(((pos.astype(np.uint16) << 2) | (rc[pos] ^ bc[pos])).astype(np.uint16))
+        else:
+            ok = False
+        if not ok:
+            explicit.append(bases)
+    return (mm_count, np.concatenate(words).astype(np.uint16) if words else np.zeros(0, np.uint16),
+            np.concatenate(explicit) if explicit else np.zeros(0, np.uint8))
 
 
 def _take(lib, ctx, p, dtype, n) -> np.ndarray:
@@ -395,7 +453,7 @@ class Context:
 
     def free_reads_compact_struct(self, b: ReadBatchCompactC):
         for name in ("run_contig_id", "run_first_read", "start", "read_len", "n_cigar_ops", "cigar", "bases2", "exc_pos", "exc_base",
-                     "qual", "mapq", "flags", "sample_id", "run_start_base", "start_rel", "n_cigar_ops8"):
+                     "qual", "mapq", "flags", "sample_id", "run_start_base", "start_rel", "n_cigar_ops8", "mm_count", "mm_words"):
             v = getattr(b, name)
             if v:
                 self.lib.guac_free(self.ctx, C.cast(v, C.c_void_p))

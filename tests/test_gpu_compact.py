@@ -101,6 +101,89 @@ def test_binned_qualities_travel_as_codes(gpu_ctx, narrow):
         gpu_ctx.free_reads_compact_struct(e)
 
 
+def _u8(p, n):
+    return np.frombuffer(C.string_at(C.cast(p, C.c_void_p), n), np.uint8)
+
+
+@pytest.mark.parametrize("name", ["tough", "tiny_sjc", "synth0", "synth1", "odd"])
+def test_reference_relative_bases(gpu_ctx, name):
+    """Reads as differences from the reference (mm_count / mm_words): the numpy packer's form and the device's own export of it
+    both expand, on the device, to the very batch the plain upload gives."""
+    if name.startswith("synth"):
+        contig_len, seed = 30000, 4100
+        ref = synth.make_reference(contig_len, seed)
+        batch = synth.generate_reads(contig_len, (30, 60), (False, True), seed, profile=int(name[-1]))
+    elif name == "odd":  # read lengths that are no multiple of 4: every read shares its first and last byte with a neighbour
+        contig_len, seed = 4000, 4101
+        ref = synth.make_reference(contig_len, seed)
+        (w,) = ref.contigs.values()
+        rng = np.random.default_rng(5)
+        reads = []
+        for i in range(300):
+            ln, st = int(rng.integers(1, 40)), int(rng.integers(0, contig_len - 50))
+            seq = bytearray(w.bases[st:st + ln].tobytes())
+            for k in rng.integers(0, ln, size=int(rng.integers(0, 3))):
+                seq[k] = b"ACGT"[(b"ACGT".index(seq[k]) + 1 + int(rng.integers(0, 3))) % 4]
+            cigar = f"{ln}M" if i % 5 or ln < 3 else f"1M1I{ln - 2}M"  # every fifth read travels explicitly
+            reads.append(make_read(seq.decode(), cigar, start=st, sample_id=i % 2, chr=w.name))
+        batch = ReadBatch.from_reads(reads, contig_names=list(ref.contigs))
+    else:
+        batch, ref, _ = fixtures.load(name)
+    gpu_ctx.upload_reference(ref, batch.contig_names)
+    c = compact_struct(batch, ref=ref)
+    n, n_bases = batch.n_reads, int(batch.seq_off[-1])
+    mm = np.ctypeslib.as_array(c.mm_count, (n,)).copy()
+    assert (mm != 255).sum() > 0.5 * n or name in ("tough", "tiny_sjc")  # most synthetic reads travel as differences
+    assert c.wire_bytes(n_bases, 0) < compact_struct(batch).wire_bytes(n_bases, 0)
+    gpu_ctx.upload_reads_compact(c)
+    assert_same_batch(device_copy(gpu_ctx, batch.contig_names), batch)
+    # the device's own packing of the same batch: a read with more differences than a slot of the read pass holds stays
+    # explicit there, every other read agrees with the numpy packer
+    gpu_ctx.set_option("compact_ref_relative", 1)
+    try:
+        e = gpu_ctx.export_reads_compact_struct()
+    finally:
+        gpu_ctx.set_option("compact_ref_relative", 0)
+    try:
+        assert bool(e.mm_count)
+        emm = _u8(e.mm_count, n)
+        few = mm <= 8
+        # (the device may keep a few more reads explicit: it tests the reference for A C G T in groups of 16 loci)
+        same = emm[few] == mm[few]
+        assert (same | (emm[few] == 255)).all() and (emm[~few] == 255).all()
+        assert same.mean() > 0.5 if name in ("tough", "tiny_sjc") else same.all()  # (partial-FASTA fixtures: windows with holes)
+        if few.all() and same.all():
+            assert e.n_mm_words == c.n_mm_words and e.n_explicit_bases == c.n_explicit_bases
+            assert C.string_at(C.cast(e.mm_words, C.c_void_p), 2 * int(e.n_mm_words)) == C.string_at(C.cast(c.mm_words, C.c_void_p), 2 * int(c.n_mm_words))
+            nb = (int(e.n_explicit_bases) + 3) // 4
+            assert C.string_at(C.cast(e.bases2, C.c_void_p), nb) == C.string_at(C.cast(c.bases2, C.c_void_p), nb)
+        gpu_ctx.upload_reads_compact(e)
+        assert_same_batch(device_copy(gpu_ctx, batch.contig_names), batch)
+    finally:
+        gpu_ctx.free_reads_compact_struct(e)
+
+
+def test_reference_relative_bases_need_the_reference_first(gpu_ctx):
+    contig_len, seed = 5000, 4102
+    ref = synth.make_reference(contig_len, seed)
+    batch = synth.generate_reads(contig_len, (10, 10), (False, True), seed)
+    c = compact_struct(batch, ref=ref)
+    fresh = type(gpu_ctx)(0)
+    try:
+        with pytest.raises(GuacError, match="upload the reference window"):
+            fresh.upload_reads_compact(c)
+        fresh.upload_reference(ref, batch.contig_names)
+        c._keep["mm_words"][0] = (200 << 2) | 1  # a position beyond the read
+        with pytest.raises(GuacError, match="difference word out of range"):
+            fresh.upload_reads_compact(c)
+        c2 = compact_struct(batch, ref=ref)
+        c2.n_mm_words -= 1
+        with pytest.raises(GuacError, match="do not match mm_count"):
+            fresh.upload_reads_compact(c2)
+    finally:
+        fresh.close()
+
+
 def test_odd_base_count_and_empty_batch(gpu_ctx):
     # 4 distinct qualities (2-bit codes), then 7 (4-bit codes), neither filling the last byte
     for quals in ([7, 9, 7, 9, 11], [7, 9, 12, 13, 14]):
