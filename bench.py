@@ -204,12 +204,14 @@ def e2e_with_packer(ctx, timed, args, mbp: int = 5):
     batch = oracle.synth_generate(n, DEPTHS, TUMOR, 3000)
     records, keepalive = hs.sam_records_of(batch)
     from guacamole_b200.io import ContigWindow, Reference
-    ctx.upload_reference(Reference({"synth1": ContigWindow("synth1", 0, oracle.synth_reference(3000, 0, n), n)}), ["synth1"])
+    host_ref = Reference({"synth1": ContigWindow("synth1", 0, oracle.synth_reference(3000, 0, n), n)})
+    ctx.upload_reference(host_ref, ["synth1"])
     pack_s = []
 
     def step():
         t = time.perf_counter()
-        packed, kept = hs.pack_reads(records, ctx=ctx, non_duplicate=True, passed_vendor_quality_checks=True, is_paired=True)
+        packed, kept = hs.pack_reads(records, ctx=ctx, non_duplicate=True, passed_vendor_quality_checks=True, is_paired=True,
+                                     ref=None if args.e2e_explicit_bases else host_ref, contig_names=["synth1"])
         pack_s.append(time.perf_counter() - t)
         ctx.upload_reads_compact(packed)
         out = ctx.somatic_standard([(0, 0, n)])
@@ -217,7 +219,8 @@ def e2e_with_packer(ctx, timed, args, mbp: int = 5):
         return out["n_visited"], len(out["calls"])
     ms, _, outs = timed(step, 2, 1)
     raw_bytes = sum(int(a.nbytes) for a in keepalive)
-    return {"form": f"from SAM-record columns through the host packer (guac_pack_reads, {os.cpu_count()} threads), {mbp} Mbp shard of the workload",
+    return {"form": f"from SAM-record columns through the host packer (guac_pack_reads{'' if args.e2e_explicit_bases else '_ref'}, {os.cpu_count()} threads), "
+                    f"{mbp} Mbp shard of the workload",
             "value": sum(o[0] for o in outs) / (ms / 1000.0), "unit": "loci/s", "host_pack_ms": 1000.0 * sum(pack_s[-2:]) / 2,
             "sam_record_bytes": raw_bytes, "reads": int(batch.n_reads)}
 
@@ -375,6 +378,7 @@ def main():
     ap.add_argument("--reference-step-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-explicit-bases", action="store_true", help="e2e: every read's bases on the wire (no reference-relative column)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak (default, the headline): every rank has its own contig; strong: ONE seeded contig cut by "
                          "UniformPartitioner ranges, every rank calls its range, the calls are gathered and checked against the uncut run")
@@ -530,7 +534,11 @@ def main():
     # expansion) -> guac_somatic_standard -> call records on host
     e2e = None
     if not args.no_e2e:
+        # the wire form with reference-relative bases (the reference genome is resident, as it is for a Spark executor that
+        # calls partition after partition): a read of one aligned operator travels as its differences from the reference
+        ctx.set_option("compact_ref_relative", 0 if args.e2e_explicit_bases else 1)
         hb = ctx.export_reads_compact_struct()
+        ctx.set_option("compact_ref_relative", 0)
         n = int(hb.n_reads)
         def column(p, ctype, dtype):
             return np.frombuffer((ctype * n).from_address(C.cast(p, C.c_void_p).value), dtype=dtype)
@@ -550,18 +558,22 @@ def main():
             return out["n_visited"], len(out["calls"])
 
         e_ms, _, e_outs = timed(step_e2e, max(1, min(args.steps, 3)), 1)
+        if any(tuple(o) != tuple(outs[0][:2]) for o in e_outs):
+            sys.exit(f"e2e: the batch that went through the wire form gives {e_outs[0]}, the resident one {outs[0][:2]} (loci visited, calls)")
         e_loci = torch.tensor([float(sum(o[0] for o in e_outs))], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(e_loci, op=dist.ReduceOp.SUM)
         e2e = {"value": float(e_loci.item()) / (e_ms / 1000.0), "unit": "loci/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h_box[0]),
-               "note": f"reads in the compact wire form (guac_read_batch_compact, {hb.qual_bits}-bit qualities) from pinned host "
-                       "memory each step; reference genome resident"}
+               "note": f"reads in the compact wire form (guac_read_batch_compact, {hb.qual_bits}-bit qualities, "
+                       + ("bases as differences from the resident reference where a read allows it" if hb.mm_count else "every read's bases explicit")
+                       + f": {h2d / max(n, 1):.1f} B per read) from pinned host memory each step; reference genome resident"}
+        had_ref_relative = bool(hb.mm_count)
         ctx.free_reads_compact_struct(hb)
         # the same leg with the wider quality forms of the wire format (real, unbinned qualities travel as 4-bit codes when
         # a batch holds at most 16 distinct values, one byte per base otherwise), and with the host packer inside
         variants = []
-        for bits in (4, 8):
+        for bits in ((2, 4, 8) if had_ref_relative else (4, 8)):  # (all with every read's bases explicit)
             ctx.set_option("compact_min_qual_bits", bits)
             hv = ctx.export_reads_compact_struct()
             ctx.set_option("compact_min_qual_bits", 2)
@@ -574,7 +586,7 @@ def main():
             v_loci = torch.tensor([float(sum(o[0] for o in v_outs))], dtype=torch.float64, device="cuda")
             if world > 1:
                 dist.all_reduce(v_loci, op=dist.ReduceOp.SUM)
-            variants.append({"form": f"{hv.qual_bits}-bit qualities", "value": float(v_loci.item()) / (v_ms / 1000.0), "unit": "loci/s",
+            variants.append({"form": f"{hv.qual_bits}-bit qualities, every read's bases explicit", "value": float(v_loci.item()) / (v_ms / 1000.0), "unit": "loci/s",
                              "h2d_bytes_per_step": int(hv.wire_bytes(n_bases, n_cigar))})
             ctx.free_reads_compact_struct(hv)
         if rank == 0 and world == 1:

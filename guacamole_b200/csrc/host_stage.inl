@@ -199,9 +199,11 @@ int guac_format_double(int32_t kind, double x, char* out, int32_t cap) {
   return GUAC_OK;
 }
 
-int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_filters* filters, int32_t n_threads,
-                    guac_read_batch_compact* out, int64_t* n_kept) {
-  if (!in || !out || in->n_records < 0 || in->n_samples <= 0 || in->n_samples > 255) return GUAC_E_INVALID_INPUT;
+namespace {
+int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_filters* filters, const guac_host_reference* refs, int32_t n_refs,
+                    int32_t n_threads, guac_read_batch_compact* out, int64_t* n_kept) {
+  if (!in || !out || in->n_records < 0 || in->n_samples <= 0 || in->n_samples > 255 || n_refs < 0 || (n_refs > 0 && !refs))
+    return GUAC_E_INVALID_INPUT;
   auto failp = [&](int st, const char* msg) {
     if (ctx) ctx->err = msg;
     return st;
@@ -369,6 +371,82 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   const int qual_bits = (n_values >= 1 && n_values <= 4) ? 2 : (n_values <= 16 && n_values >= 1) ? 4 : 8;
   const int per_byte = 8 / qual_bits;
   if (qual_bits == 8) std::memset(out->qual_table, 0, sizeof out->qual_table);  // (no table: one byte per base)
+  // 4b. reference-relative bases (guac_read_batch_compact::mm_count): which reads travel as differences, how many words each
+  const bool ref_rel = n_refs > 0 && n > 0;
+  std::vector<uint8_t> mm_count;
+  std::vector<uint64_t> expl_off;  // explicit reads' bases, concatenated: offsets over the kept reads (0 bases for the others)
+  std::vector<int64_t> mm_off;
+  uint8_t base_code[256];
+  std::memset(base_code, 4, sizeof base_code);
+  base_code['A'] = 0, base_code['C'] = 1, base_code['G'] = 2, base_code['T'] = 3;
+  auto window_of = [&](int32_t contig) -> const guac_host_reference* {
+    for (int r = 0; r < n_refs; ++r)
+      if (refs[r].contig_id == contig) return &refs[r];
+    return nullptr;
+  };
+  // differences of kept read k from its contig's window, or -1 when it has to travel explicitly; `emit` sees each word
+  auto differences = [&](int64_t k, auto&& emit) -> int {
+    const int64_t i = idx[(size_t)k];
+    const int64_t len = (int64_t)(in->seq_off[i + 1] - in->seq_off[i]);
+    if ((int64_t)in->cigar_off[i + 1] - (int64_t)in->cigar_off[i] != 1 || len >= 16384 || len == 0) return -1;
+    const uint32_t w = in->cigar[in->cigar_off[i]];
+    const int op = (int)(w & 15);
+    if (!(op == GUAC_CIGAR_M || op == GUAC_CIGAR_EQ || op == GUAC_CIGAR_X) || (int64_t)(w >> 4) != len) return -1;
+    const guac_host_reference* win = window_of(in->reference_index[i]);
+    if (!win) return -1;
+    const int64_t rel = in->alignment_start[i] - 1 - win->offset;
+    if (rel < 0 || rel + len > win->len) return -1;
+    const uint8_t* rb = win->bases + rel;
+    const uint8_t* sb = in->bases_ascii + in->seq_off[i];
+    int cnt = 0;
+    for (int64_t p = 0; p < len; ++p) {
+      const int rc = base_code[rb[p]], bc = base_code[sb[p]];
+      if ((rc | bc) >= 4) return -1;
+      if (rc != bc) {
+        if (++cnt >= 255) return -1;
+        emit((uint16_t)((p << 2) | (rc ^ bc)));
+      }
+    }
+    return cnt;
+  };
+  if (ref_rel) {
+    mm_count.assign((size_t)n, 255);
+    expl_off.assign((size_t)n + 1, 0);
+    mm_off.assign((size_t)n + 1, 0);
+    std::vector<uint64_t> cb((size_t)n_threads + 1, 0);
+    std::vector<int64_t> cw((size_t)n_threads + 1, 0);
+    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
+      uint64_t eb = 0;
+      int64_t ew = 0;
+      for (int64_t k = lo; k < hi; ++k) {
+        const int c = differences(k, [](uint16_t) {});
+        mm_count[(size_t)k] = c < 0 ? (uint8_t)255 : (uint8_t)c;
+        if (c < 0) eb += base_off[(size_t)k + 1] - base_off[(size_t)k];
+        else ew += c;
+      }
+      cb[(size_t)t + 1] = eb;
+      cw[(size_t)t + 1] = ew;
+    });
+    for (int t = 0; t < n_threads; ++t) {
+      cb[(size_t)t + 1] += cb[(size_t)t];
+      cw[(size_t)t + 1] += cw[(size_t)t];
+    }
+    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
+      uint64_t eb = cb[(size_t)t];
+      int64_t ew = cw[(size_t)t];
+      for (int64_t k = lo; k < hi; ++k) {
+        expl_off[(size_t)k] = eb;
+        mm_off[(size_t)k] = ew;
+        if (mm_count[(size_t)k] == 255) eb += base_off[(size_t)k + 1] - base_off[(size_t)k];
+        else ew += mm_count[(size_t)k];
+      }
+      if (hi == n) {
+        expl_off[(size_t)n] = eb;
+        mm_off[(size_t)n] = ew;
+      }
+    });
+  }
+  const uint64_t n_explicit = ref_rel ? expl_off[(size_t)n] : n_bases;
   // 5. outputs
   PackAlloc A{ctx};
   auto* o_run_contig = static_cast<int32_t*>(A.get(run_contig.size() * sizeof(int32_t)));
@@ -380,7 +458,9 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   auto* o_ops16 = narrow_ops ? nullptr : static_cast<uint16_t*>(A.get((size_t)n * sizeof(uint16_t)));
   auto* o_ops8 = narrow_ops ? static_cast<uint8_t*>(A.get((size_t)n)) : nullptr;
   auto* o_cigar = static_cast<uint32_t*>(A.get((size_t)wire_off[(size_t)n] * sizeof(uint32_t)));
-  auto* o_bases2 = static_cast<uint8_t*>(A.get((size_t)((n_bases + 3) / 4) + 8));
+  auto* o_bases2 = static_cast<uint8_t*>(A.get((size_t)((n_explicit + 3) / 4) + 8));
+  auto* o_mm_count = ref_rel ? static_cast<uint8_t*>(A.get((size_t)n)) : nullptr;
+  auto* o_mm_words = ref_rel ? static_cast<uint16_t*>(A.get((size_t)mm_off[(size_t)n] * sizeof(uint16_t) + 8)) : nullptr;
   auto* o_qual = static_cast<uint8_t*>(A.get((size_t)((n_bases + per_byte - 1) / per_byte) + 8));
   auto* o_mapq = static_cast<uint8_t*>(A.get((size_t)n));
   auto* o_flags = static_cast<uint8_t*>(A.get((size_t)n));
@@ -429,7 +509,7 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   host_parallel_for(n_threads, n_groups, [&](int64_t glo, int64_t ghi, int t) {
     const uint64_t g0 = (uint64_t)glo * 8, g1 = std::min<uint64_t>(n_bases, (uint64_t)ghi * 8);
     if (g0 >= g1) return;
-    std::memset(o_bases2 + g0 / 4, 0, (size_t)((g1 + 3) / 4 - g0 / 4));
+    if (!ref_rel) std::memset(o_bases2 + g0 / 4, 0, (size_t)((g1 + 3) / 4 - g0 / 4));
     std::memset(o_qual + g0 / per_byte, 0, (size_t)((g1 + per_byte - 1) / per_byte - g0 / per_byte));
     int64_t k = (int64_t)(std::upper_bound(base_off.begin(), base_off.end(), g0) - base_off.begin()) - 1;
     const int qshift = qual_bits == 2 ? 2 : qual_bits == 4 ? 1 : 0;  // log2(bases per quality byte)
@@ -442,8 +522,8 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       const uint8_t* sq = in->base_qualities + in->seq_off[i] + (g - base_off[(size_t)k]);
       auto one = [&]() {  // one base, read-modify-write of its output bytes
         const int code = base_lut[*sb];
-        if (code < 4) o_bases2[g >> 2] |= (uint8_t)(code << ((g & 3) * 2));
-        else exc[(size_t)t].push_back({g, *sb});
+        if (code >= 4) exc[(size_t)t].push_back({g, *sb});
+        else if (!ref_rel) o_bases2[g >> 2] |= (uint8_t)(code << ((g & 3) * 2));
         if (qual_bits == 8) o_qual[g] = *sq;
         else o_qual[g >> qshift] |= (uint8_t)(code_of[*sq] << (qual_bits * (int)(g & qmask)));
         ++g, ++sb, ++sq;
@@ -452,12 +532,12 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       for (; g + 4 <= end; g += 4, sb += 4, sq += 4) {  // four bases per output byte, plain stores
         const int c0 = base_lut[sb[0]], c1 = base_lut[sb[1]], c2 = base_lut[sb[2]], c3 = base_lut[sb[3]];
         if ((c0 | c1 | c2 | c3) < 4) {
-          o_bases2[g >> 2] = (uint8_t)(c0 | (c1 << 2) | (c2 << 4) | (c3 << 6));
+          if (!ref_rel) o_bases2[g >> 2] = (uint8_t)(c0 | (c1 << 2) | (c2 << 4) | (c3 << 6));
         } else {
           for (int j = 0; j < 4; ++j) {
             const int c = base_lut[sb[j]];
-            if (c < 4) o_bases2[g >> 2] |= (uint8_t)(c << (2 * j));
-            else exc[(size_t)t].push_back({g + (uint64_t)j, sb[j]});
+            if (c >= 4) exc[(size_t)t].push_back({g + (uint64_t)j, sb[j]});
+            else if (!ref_rel) o_bases2[g >> 2] |= (uint8_t)(c << (2 * j));
           }
         }
         if (qual_bits == 2) {
@@ -472,6 +552,34 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       while (g < end) one();
     }
   });
+  if (ref_rel) {
+    // the difference words, and the explicit reads' bases: every thread owns a range of output bytes of the explicit stream
+    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int) {
+      for (int64_t k = lo; k < hi; ++k) {
+        o_mm_count[k] = mm_count[(size_t)k];
+        if (mm_count[(size_t)k] == 255) continue;
+        uint16_t* w = o_mm_words + mm_off[(size_t)k];
+        differences(k, [&](uint16_t word) { *w++ = word; });
+      }
+    });
+    const int64_t e_groups = (int64_t)((n_explicit + 7) / 8);
+    host_parallel_for(n_threads, e_groups, [&](int64_t glo, int64_t ghi, int) {
+      const uint64_t g0 = (uint64_t)glo * 8, g1 = std::min<uint64_t>(n_explicit, (uint64_t)ghi * 8);
+      if (g0 >= g1) return;
+      std::memset(o_bases2 + g0 / 4, 0, (size_t)((g1 + 3) / 4 - g0 / 4));
+      int64_t k = (int64_t)(std::upper_bound(expl_off.begin(), expl_off.end(), g0) - expl_off.begin()) - 1;
+      for (uint64_t g = g0; g < g1;) {
+        while (expl_off[(size_t)k + 1] <= g) ++k;
+        const int64_t i = idx[(size_t)k];
+        const uint64_t end = std::min<uint64_t>(g1, expl_off[(size_t)k + 1]);
+        const uint8_t* sb = in->bases_ascii + in->seq_off[i] + (g - expl_off[(size_t)k]);
+        for (; g < end; ++g, ++sb) {
+          const int code = base_lut[*sb];
+          if (code < 4) o_bases2[g >> 2] |= (uint8_t)(code << ((g & 3) * 2));
+        }
+      }
+    });
+  }
   size_t n_exc = 0;
   for (auto& v : exc) n_exc += v.size();
   auto* o_exc_pos = static_cast<uint64_t*>(A.get(n_exc * sizeof(uint64_t)));
@@ -510,8 +618,25 @@ int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   out->start_rel = o_start_rel;
   out->n_cigar_ops8 = o_ops8;
   out->uniform_read_len = uniform ? (int32_t)len0 : 0;
+  if (ref_rel) {
+    out->mm_count = o_mm_count;
+    out->mm_words = o_mm_words;
+    out->n_mm_words = mm_off[(size_t)n];
+    out->n_explicit_bases = (int64_t)n_explicit;
+  }
   if (n_kept) *n_kept = n;
   return GUAC_OK;
+}
+}  // namespace
+
+int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* in, const guac_read_filters* filters, int32_t n_threads,
+                    guac_read_batch_compact* out, int64_t* n_kept) {
+  return pack_reads_impl(ctx, in, filters, nullptr, 0, n_threads, out, n_kept);
+}
+
+int guac_pack_reads_ref(guac_ctx* ctx, const guac_sam_records* in, const guac_read_filters* filters, const guac_host_reference* refs,
+                        int32_t n_refs, int32_t n_threads, guac_read_batch_compact* out, int64_t* n_kept) {
+  return pack_reads_impl(ctx, in, filters, refs, n_refs, n_threads, out, n_kept);
 }
 
 int guac_ss_genotype_filter(const guac_ss_filter_params* P, const guac_ss_call* calls, int64_t n, uint8_t* keep) {

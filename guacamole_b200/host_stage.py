@@ -60,17 +60,44 @@ def sam_records_of(batch: ReadBatch, extra_flags: Optional[np.ndarray] = None):
     return s, list(cols.values())
 
 
+class HostReferenceC(C.Structure):
+    """guac_host_reference: one contig window of the reference in host memory."""
+    _fields_ = [("contig_id", C.c_int32), ("_pad", C.c_int32), ("offset", C.c_int64), ("len", C.c_int64), ("bases", C.c_void_p)]
+
+
+def host_references(ref, contig_names: Sequence[str]):
+    """(array of guac_host_reference, keep-alive list) for the windows of a `Reference` whose contigs are in contig_names."""
+    windows = [(i, ref.contigs[c]) for i, c in enumerate(contig_names) if c in ref.contigs]
+    arr = (HostReferenceC * max(1, len(windows)))()
+    keep = []
+    for k, (i, w) in enumerate(windows):
+        bases = np.ascontiguousarray(w.bases, np.uint8)
+        keep.append(bases)
+        arr[k] = HostReferenceC(i, 0, int(w.offset), int(bases.shape[0]), bases.ctypes.data)
+    return arr, len(windows), keep
+
+
 def pack_reads(records: SamRecordsC, ctx=None, non_duplicate=False, passed_vendor_quality_checks=False, is_paired=False,
-               min_alignment_quality=0, overlaps_loci: Sequence[Tuple[int, int, int]] = (), n_threads: int = 0):
-    """guac_pack_reads -> (ReadBatchCompactC, reads kept).  ctx: a native.Context (pinned outputs) or None (C heap)."""
+               min_alignment_quality=0, overlaps_loci: Sequence[Tuple[int, int, int]] = (), n_threads: int = 0, ref=None,
+               contig_names: Sequence[str] = ()):
+    """guac_pack_reads -> (ReadBatchCompactC, reads kept).  ctx: a native.Context (pinned outputs) or None (C heap).
+    ref (a `Reference`, with contig_names giving the contig ids): guac_pack_reads_ref — reference-relative bases."""
     lib = load_library()
     f = ReadFiltersC(int(non_duplicate), int(passed_vendor_quality_checks), int(is_paired), int(min_alignment_quality), None, 0, 0)
     ranges = make_ranges(overlaps_loci) if overlaps_loci else None
     if ranges is not None:
         f.overlaps_loci, f.n_overlaps_loci = C.cast(ranges, C.c_void_p), len(overlaps_loci)
     out, n = ReadBatchCompactC(), C.c_int64()
-    lib.guac_pack_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
-    st = lib.guac_pack_reads(ctx.ctx if ctx is not None else None, C.byref(records), C.byref(f), C.c_int32(n_threads), C.byref(out), C.byref(n))
+    if ref is not None:
+        refs, n_refs, keep = host_references(ref, contig_names)
+        lib.guac_pack_reads_ref.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+        st = lib.guac_pack_reads_ref(ctx.ctx if ctx is not None else None, C.byref(records), C.byref(f), refs, C.c_int32(n_refs),
+                                     C.c_int32(n_threads), C.byref(out), C.byref(n))
+        del keep
+    else:
+        lib.guac_pack_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+        st = lib.guac_pack_reads(ctx.ctx if ctx is not None else None, C.byref(records), C.byref(f), C.c_int32(n_threads), C.byref(out),
+                                 C.byref(n))
     if st != 0:
         raise RuntimeError(f"guac_pack_reads failed ({st})" + (": " + lib.guac_last_error(ctx.ctx).decode() if ctx is not None else ""))
     return out, n.value

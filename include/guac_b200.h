@@ -661,6 +661,20 @@ typedef struct {
  */
 int guac_pack_reads(guac_ctx* ctx, const guac_sam_records* records, const guac_read_filters* filters, int32_t n_threads,
                     guac_read_batch_compact* out, int64_t* n_kept);
+/* One contig window of the reference in host memory (ASCII upper-case, 0 = missing), as ReferenceBroadcast holds it
+ * (M/reference/ReferenceBroadcast.scala:70-83). */
+typedef struct {
+  int32_t contig_id;
+  int32_t _pad;
+  int64_t offset;        /* locus of bases[0] */
+  int64_t len;
+  const uint8_t* bases;
+} guac_host_reference;
+/* guac_pack_reads with the reference-relative base column (guac_read_batch_compact::mm_count): a read of one aligned operator
+ * over A C G T bases that lies wholly on A C G T bases of its contig's window travels as its differences from it.  The same
+ * windows must be on the device (guac_ref_upload) before the result is uploaded. */
+int guac_pack_reads_ref(guac_ctx* ctx, const guac_sam_records* records, const guac_read_filters* filters, const guac_host_reference* refs,
+                        int32_t n_refs, int32_t n_threads, guac_read_batch_compact* out, int64_t* n_kept);
 void guac_host_free(void* p);
 
 /* SomaticGenotypeFilter.SomaticGenotypeFilterArguments (M/filters/somatic/SomaticGenotypeFilter.scala:34-80); < 0 = not set */

@@ -213,7 +213,8 @@ def test_ordering_contract(gpu_ctx):
         gpu_ctx.upload_reads_compact(c)
 
 
-def test_host_packer_feeds_the_device(gpu_ctx):
+@pytest.mark.parametrize("with_ref", [False, True])
+def test_host_packer_feeds_the_device(gpu_ctx, with_ref):
     """SAM-record columns -> guac_pack_reads (pinned outputs of the context) -> guac_reads_upload_compact -> the device batch is
     byte-identical to the plain upload of the same (filtered) reads, and the caller gives the same records."""
     from guacamole_b200 import host_stage as hs
@@ -224,9 +225,9 @@ def test_host_packer_feeds_the_device(gpu_ctx):
     fl[::7] |= FLAG_DUPLICATE
     batch.flags = fl
     records, keepalive = hs.sam_records_of(batch)
-    packed, kept = hs.pack_reads(records, ctx=gpu_ctx, non_duplicate=True)
+    packed, kept = hs.pack_reads(records, ctx=gpu_ctx, non_duplicate=True, ref=ref if with_ref else None, contig_names=batch.contig_names)
     want_batch = partitioning.take_reads(batch, np.flatnonzero((fl & FLAG_DUPLICATE) == 0))
-    assert kept == want_batch.n_reads
+    assert kept == want_batch.n_reads and bool(packed.mm_count) == with_ref
     gpu_ctx.upload_reference(ref, batch.contig_names)
     gpu_ctx.upload_reads_compact(packed)
     gpu_ctx._batch = want_batch

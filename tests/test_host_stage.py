@@ -84,7 +84,10 @@ def _columns(c):
                 run_first=arr(c.run_first_read, np.int64, int(c.n_contig_runs) + 1), start=arr(c.start, np.int64, n),
                 run_base=arr(c.run_start_base, np.int64, int(c.n_contig_runs)), start_rel=arr(c.start_rel, np.uint32, n),
                 read_len=arr(c.read_len, np.uint16, n), uniform=int(c.uniform_read_len), ops16=arr(c.n_cigar_ops, np.uint16, n), ops8=ops8,
-                cigar=arr(c.cigar, np.uint32, n_cigar), bases2=arr(c.bases2, np.uint8, (n_bases + 3) // 4), n_exc=int(c.n_exc),
+                cigar=arr(c.cigar, np.uint32, n_cigar),
+                bases2=arr(c.bases2, np.uint8, ((int(c.n_explicit_bases) if c.mm_count else n_bases) + 3) // 4),
+                mm_count=arr(c.mm_count, np.uint8, n) if c.mm_count else 0, n_mm_words=int(c.n_mm_words), n_explicit=int(c.n_explicit_bases),
+                mm_words=arr(c.mm_words, np.uint16, int(c.n_mm_words)) if c.mm_count and c.n_mm_words else 0, n_exc=int(c.n_exc),
                 exc_pos=arr(c.exc_pos, np.uint64, int(c.n_exc)), exc_base=arr(c.exc_base, np.uint8, int(c.n_exc)), qual_bits=int(c.qual_bits),
                 qual_table=bytes(c.qual_table), qual=arr(c.qual, np.uint8, (n_bases + per - 1) // per), mapq=arr(c.mapq, np.uint8, n),
                 flags=arr(c.flags, np.uint8, n), sample=arr(c.sample_id, np.uint8, n))
@@ -139,6 +142,32 @@ def test_pack_reads_equals_the_numpy_packer(name):
     ends = batch.ends()
     assert n_kept == int(np.count_nonzero(~unmapped & (batch.contig_id == c0) & (batch.start < lo + 50) & (ends > lo)))
     hs.free_packed(got)
+
+
+@pytest.mark.parametrize("name", ["tiny_sjc", "tough", "synthetic", "synthetic_plain"])
+def test_pack_reads_with_the_reference_equals_the_numpy_packer(name):
+    """guac_pack_reads_ref: reads that can travel as their differences from the reference do, the others' bases are packed
+    on their own — every wire column equals the numpy twin's (native.compact_struct(batch, ref=...))."""
+    if name.startswith("synthetic"):
+        from guacamole_b200 import synth
+        ref = synth.make_reference(30000, 12)
+        batch = synth.generate_reads(30000, (30, 60), (False, True), 12, profile=0 if name.endswith("plain") else 1)
+    else:
+        batch, ref, _ = fixtures.load(name)
+    fl = batch.flags.copy()
+    fl[::9] |= FLAG_DUPLICATE
+    batch.flags = fl
+    records, keepalive = hs.sam_records_of(batch)
+    from guacamole_b200 import partitioning
+    for threads in (1, 5):
+        got, n_kept = hs.pack_reads(records, non_duplicate=True, ref=ref, contig_names=batch.contig_names, n_threads=threads)
+        want_batch = partitioning.take_reads(batch, np.flatnonzero((fl & FLAG_DUPLICATE) == 0))
+        assert n_kept == want_batch.n_reads > 0
+        want = compact_struct(want_batch, ref=ref)
+        cols = _columns(got)
+        assert isinstance(cols["mm_count"], np.ndarray) and (cols["mm_count"] != 255).sum() > 0.5 * n_kept
+        _assert_same_columns(cols, _columns(want))
+        hs.free_packed(got)
 
 
 def test_pack_reads_sorts_a_shuffled_partition():
