@@ -384,6 +384,22 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       if (refs[r].contig_id == contig) return &refs[r];
     return nullptr;
   };
+  // one bit per base of every window: not A C G T (or missing).  A read on clean reference is compared eight bases at a time.
+  std::vector<std::vector<uint64_t>> ref_bad((size_t)n_refs);
+  for (int r = 0; r < n_refs && n > 0; ++r) {
+    const int64_t len = refs[r].len;
+    ref_bad[(size_t)r].assign((size_t)(len / 64) + 2, 0);
+    uint64_t* bits = ref_bad[(size_t)r].data();
+    const uint8_t* rb = refs[r].bases;
+    host_parallel_for(n_threads, (len + 63) / 64, [&](int64_t lo, int64_t hi, int) {
+      for (int64_t w = lo; w < hi; ++w) {
+        uint64_t v = 0;
+        const int64_t end = std::min<int64_t>(len, 64 * w + 64);
+        for (int64_t p = 64 * w; p < end; ++p) v |= (uint64_t)(base_code[rb[p]] >= 4) << (p & 63);
+        bits[w] = v;
+      }
+    });
+  }
   // differences of kept read k from its contig's window, or -1 when it has to travel explicitly; `emit` sees each word
   auto differences = [&](int64_t k, auto&& emit) -> int {
     const int64_t i = idx[(size_t)k];
@@ -396,36 +412,63 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
     if (!win) return -1;
     const int64_t rel = in->alignment_start[i] - 1 - win->offset;
     if (rel < 0 || rel + len > win->len) return -1;
+    {  // every reference base under the read is A C G T
+      const uint64_t* bits = ref_bad[(size_t)(win - refs)].data();
+      const int64_t w0 = rel >> 6, w1 = (rel + len - 1) >> 6;
+      for (int64_t q = w0; q <= w1; ++q) {
+        uint64_t v = bits[q];
+        if (q == w0) v &= ~0ull << (rel & 63);
+        if (q == w1 && ((rel + len) & 63)) v &= ~0ull >> (64 - ((rel + len) & 63));
+        if (v) return -1;
+      }
+    }
     const uint8_t* rb = win->bases + rel;
     const uint8_t* sb = in->bases_ascii + in->seq_off[i];
     int cnt = 0;
-    for (int64_t p = 0; p < len; ++p) {
-      const int rc = base_code[rb[p]], bc = base_code[sb[p]];
-      if ((rc | bc) >= 4) return -1;
+    auto one = [&](int64_t p) {  // false: the read has to travel explicitly
+      const int bc = base_code[sb[p]];
+      if (bc >= 4) return false;
+      const int rc = base_code[rb[p]];
       if (rc != bc) {
-        if (++cnt >= 255) return -1;
+        if (++cnt >= 255) return false;
         emit((uint16_t)((p << 2) | (rc ^ bc)));
       }
+      return true;
+    };
+    int64_t p = 0;
+    for (; p + 8 <= len; p += 8) {  // equal to clean reference: nothing to look at
+      uint64_t a, b;
+      std::memcpy(&a, rb + p, 8);
+      std::memcpy(&b, sb + p, 8);
+      if (a == b) continue;
+      for (int64_t q = p; q < p + 8; ++q)
+        if (!one(q)) return -1;
     }
+    for (; p < len; ++p)
+      if (!one(p)) return -1;
     return cnt;
   };
+  std::vector<std::vector<uint16_t>> thread_words((size_t)n_threads);
+  std::vector<int64_t> cw((size_t)n_threads + 1, 0);
   if (ref_rel) {
     mm_count.assign((size_t)n, 255);
     expl_off.assign((size_t)n + 1, 0);
     mm_off.assign((size_t)n + 1, 0);
     std::vector<uint64_t> cb((size_t)n_threads + 1, 0);
-    std::vector<int64_t> cw((size_t)n_threads + 1, 0);
     host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
       uint64_t eb = 0;
-      int64_t ew = 0;
+      std::vector<uint16_t>& words = thread_words[(size_t)t];  // (the reads of a thread are consecutive: so are their words)
       for (int64_t k = lo; k < hi; ++k) {
-        const int c = differences(k, [](uint16_t) {});
+        const size_t before = words.size();
+        const int c = differences(k, [&](uint16_t word) { words.push_back(word); });
         mm_count[(size_t)k] = c < 0 ? (uint8_t)255 : (uint8_t)c;
-        if (c < 0) eb += base_off[(size_t)k + 1] - base_off[(size_t)k];
-        else ew += c;
+        if (c < 0) {
+          words.resize(before);
+          eb += base_off[(size_t)k + 1] - base_off[(size_t)k];
+        }
       }
       cb[(size_t)t + 1] = eb;
-      cw[(size_t)t + 1] = ew;
+      cw[(size_t)t + 1] = (int64_t)words.size();
     });
     for (int t = 0; t < n_threads; ++t) {
       cb[(size_t)t + 1] += cb[(size_t)t];
@@ -554,13 +597,10 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   });
   if (ref_rel) {
     // the difference words, and the explicit reads' bases: every thread owns a range of output bytes of the explicit stream
-    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int) {
-      for (int64_t k = lo; k < hi; ++k) {
-        o_mm_count[k] = mm_count[(size_t)k];
-        if (mm_count[(size_t)k] == 255) continue;
-        uint16_t* w = o_mm_words + mm_off[(size_t)k];
-        differences(k, [&](uint16_t word) { *w++ = word; });
-      }
+    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
+      for (int64_t k = lo; k < hi; ++k) o_mm_count[k] = mm_count[(size_t)k];
+      const std::vector<uint16_t>& words = thread_words[(size_t)t];
+      if (!words.empty()) std::memcpy(o_mm_words + cw[(size_t)t], words.data(), words.size() * sizeof(uint16_t));
     });
     const int64_t e_groups = (int64_t)((n_explicit + 7) / 8);
     host_parallel_for(n_threads, e_groups, [&](int64_t glo, int64_t ghi, int) {
