@@ -80,6 +80,37 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   const int64_t uniform_len = b->uniform_read_len > 0 ? b->uniform_read_len : 0;
   if (narrow_start && b->n_contig_runs > 0 && !b->run_start_base) return fail(ctx, GUAC_E_INVALID_INPUT, "start_rel without run_start_base");
   if (uniform_len > 65535) return fail(ctx, GUAC_E_INVALID_INPUT, "uniform_read_len beyond 65535");
+  // The qualities are the largest column.  When the number of bases is known up front (one read length for the whole batch)
+  // their copy goes first, on the second stream, with their expansion behind it there: the expansion then runs under the
+  // copies of the other columns instead of after the last of them.
+  const bool early_qual = uniform_len > 0 && n > 0 && b->qual_bits != 8;
+  if (early_qual) {
+    const uint64_t nb = (uint64_t)n * (uint64_t)uniform_len;
+    const int per_byte = 8 / b->qual_bits;
+    const size_t packed = (size_t)((nb + per_byte - 1) / per_byte);
+    GUAC_TRY(ensure(ctx, d_qpacked, packed + 32 + 16));
+    GUAC_TRY(ensure(ctx, ctx->b_qual, (size_t)nb + 32));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->fork, ctx->stream));  // (behind whatever still reads the old batch's buffers)
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->fork, 0));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_qpacked.p, b->qual, packed, cudaMemcpyHostToDevice, ctx->stream2));
+    compact::QualTable T;
+    std::memcpy(T.q, b->qual_table, 16);
+    const unsigned blocks = blocks_for((int64_t)((nb + 15) / 16), 256);
+    if (b->qual_bits == 4)
+      compact::expand_qual_kernel<4><<<blocks, 256, 0, ctx->stream2>>>(nb, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
+    else
+      compact::expand_qual_kernel<2><<<blocks, 256, 0, ctx->stream2>>>(nb, d_qpacked.as<uint8_t>(), T, ctx->b_qual.as<uint8_t>());
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaEventRecord(ctx->qual_ready, ctx->stream2));
+  }
+  // (the copy is in flight out of the caller's buffer from here on: whichever way the function returns, it waits for it)
+  struct WaitOnExit {
+    cudaEvent_t ev;
+    bool armed;
+    ~WaitOnExit() {
+      if (armed) cudaEventSynchronize(ev);
+    }
+  } qual_copy_guard{ctx->qual_ready, early_qual};
   if (narrow_start) {
     GUAC_TRY(upload(ctx, ctx->u_start_rel, b->start_rel, (size_t)n));
     GUAC_TRY(upload(ctx, ctx->u_runs_base, b->run_start_base, (size_t)b->n_contig_runs));
@@ -174,7 +205,11 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
   // The qualities travel before the bases: nothing of the on-device preparation below (quality expansion, read ends,
   // flags, headers, the multi-operator list) reads a base, so the copy of the bases, queued on the second stream
   // behind the copy of the qualities, runs under those kernels.
-  if (b->qual_bits == 8) {
+  if (early_qual) {
+    if (n_bases != (uint64_t)n * (uint64_t)uniform_len) {  // (cannot happen: the offsets are n x uniform_len)
+      return fail(ctx, GUAC_E_INVALID_INPUT, "uniform_read_len does not match the batch");
+    }
+  } else if (b->qual_bits == 8) {
     GUAC_TRY(upload(ctx, ctx->b_qual, b->qual, (size_t)n_bases));
   } else {
     const int per_byte = 8 / b->qual_bits;
@@ -200,7 +235,9 @@ int guac_reads_upload_compact(guac_ctx* ctx, const guac_read_batch_compact* b) {
     }
   };
   cuda_ok(cudaEventRecord(ctx->join, ctx->stream2), "cudaEventRecord(join)");
-  if (b->qual_bits != 8 && n_bases > 0) {
+  if (early_qual) {
+    cuda_ok(cudaStreamWaitEvent(ctx->stream, ctx->qual_ready, 0), "cudaStreamWaitEvent(qual_ready)");  // what follows reads the qualities
+  } else if (b->qual_bits != 8 && n_bases > 0) {
     compact::QualTable T;
     std::memcpy(T.q, b->qual_table, 16);
     const unsigned blocks = blocks_for((int64_t)((n_bases + 15) / 16), 256);

@@ -95,7 +95,7 @@ struct guac_ctx {
   DevBuf b_heavy, b_boundtab, b_vcount, b_sj_sites, b_arena_used, b_hdr;
   double bound_tab_vaf = -1;
   cudaStream_t stream2 = nullptr;  // second stream: the copy of the bases in guac_reads_upload_compact
-  cudaEvent_t fork = nullptr, join = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr, qual_ready = nullptr;
   DevBuf b_ev_overflow;  // stream path: overflow arena of the read pass (first 64 bytes: its counter)
   DevBuf b_bins, b_bin_count, b_medium;  // stream path: per-read event slots and counts; list of multi-operator reads
   int64_t n_medium = 0;
@@ -440,6 +440,7 @@ int side_stream(guac_ctx* ctx) {
   CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
   CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming));
   CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->join, cudaEventDisableTiming));
+  CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->qual_ready, cudaEventDisableTiming));
   return GUAC_OK;
 }
 
@@ -722,6 +723,7 @@ void guac_ctx_destroy(guac_ctx* ctx) {
   if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
   if (ctx->fork) cudaEventDestroy(ctx->fork);
   if (ctx->join) cudaEventDestroy(ctx->join);
+  if (ctx->qual_ready) cudaEventDestroy(ctx->qual_ready);
   for (DevBuf* b : {&ctx->b_ev_overflow, &ctx->b_bins, &ctx->b_bin_count, &ctx->b_medium, &ctx->u_len, &ctx->u_ops, &ctx->u_runs_c, &ctx->u_runs_f, &ctx->u_tmp,
                     &ctx->u_qpacked, &ctx->u_bad, &ctx->u_flag, &ctx->u_off, &ctx->u_idx, &ctx->u_expl, &ctx->u_mm_count, &ctx->u_mm_words, &ctx->u_expl_len, &ctx->u_mm_n,
                     &ctx->u_expl_off, &ctx->u_mm_off, &ctx->u_start_rel, &ctx->u_runs_base, &ctx->u_ops8,
