@@ -271,7 +271,9 @@ def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
         elif k_ms:
             entry["kernel_ms"] = k_ms
         if not args.no_e2e:
+            ctx.set_option("compact_ref_relative", 0 if args.e2e_explicit_bases else 1)
             hb = ctx.export_reads_compact_struct()
+            ctx.set_option("compact_ref_relative", 0)
             n = int(hb.n_reads)
 
             def column(p, ctype, dtype):
@@ -291,7 +293,9 @@ def run_paths(ctx, args, rank, local_rank, world, timed, peak, peak_src):
             e_ms, _, e_outs = timed(step_e2e, steps, 1)
             entry["e2e"] = {"value": total(visited_of(e_outs[0]) * steps) / (e_ms / 1000.0), "unit": "loci/s",
                             "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h[0]),
-                            "note": f"reads in the compact wire form ({hb.qual_bits}-bit qualities) from pinned host memory each step"}
+                            "note": f"reads in the compact wire form ({hb.qual_bits}-bit qualities, "
+                                    + ("bases as differences from the resident reference where a read allows it" if hb.mm_count else "every read's bases explicit")
+                                    + f": {h2d / max(n, 1):.1f} B per read) from pinned host memory each step"}
             ctx.free_reads_compact_struct(hb)
         if rank == 0 and world == 1 and not args.no_cpu_baseline:
             from oracle import oracle
