@@ -454,6 +454,8 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    local_ms = [0.0]
+
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):
             step_fn()
@@ -468,6 +470,7 @@ def main():
         ms = max(e0.elapsed_time(e1), 0.0)
         # the C call is synchronous, so host time between the events is part of the step; use the larger
         ms = max(ms, 0.0)
+        local_ms[0] = ms  # this rank's own time (the returned one is the maximum over the ranks)
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -498,6 +501,13 @@ def main():
         sampler.start()
     ms_total, wall, outs = timed(step_counted, args.steps, 0)
     clocks = sampler.stop() if args.clock_period_ms > 0 else {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["sampler off"], "samples": 0}
+    # every rank's own step: its time over the timed region, the kernels' share (CUDA events inside the library), the rest
+    # (launches, the one wait of the call, the records' copy, Python) — what an N-process box adds shows in the last
+    mine = torch.tensor([local_ms[0] / args.steps, sum(kernel_ms) / max(1, len(kernel_ms))], dtype=torch.float64, device="cuda")
+    per_rank = [mine.clone() for _ in range(world)]
+    if world > 1:
+        dist.all_gather(per_rank, mine)
+    per_rank = [{"rank": r, "ms_per_step": float(t[0]), "kernel_ms": float(t[1]), "host_ms": float(t[0] - t[1])} for r, t in enumerate(per_rank)]
     if args.clock_period_ms > 0 and clocks.get("samples", 0) < 3:
         # the timed region was shorter than a few sampler periods: sample the clocks over a second, untimed run of the
         # same steps under load (the timed numbers above are not touched)
@@ -656,7 +666,7 @@ def main():
                        "parallelism": f"loci-range shards x{world}, no collective", "cores_per_rank": pinned_cores,
                        "l2": "inputs (7.3 GB per GPU) are far larger than L2 (126 MB); no flush needed"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "wall_s_timed": wall, "parity": parity, "paths": paths,
+            "wall_s_timed": wall, "parity": parity, "per_rank": per_rank, "paths": paths,
         }
         if strong:
             line["strong_scaling_check"] = strong_check

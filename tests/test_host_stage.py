@@ -170,6 +170,44 @@ def test_pack_reads_with_the_reference_equals_the_numpy_packer(name):
         hs.free_packed(got)
 
 
+def test_reference_relative_columns_expand_to_the_reads():
+    """The wire semantics without a GPU: the bases rebuilt from guac_pack_reads_ref's columns — the reference window patched
+    with the difference words, or the explicit stream — are the reads' bases (what refrel_expand_kernel does on the device)."""
+    from guacamole_b200 import synth
+    ref = synth.make_reference(20000, 31)
+    batch = synth.generate_reads(20000, (20, 40), (False, True), 31, profile=1)
+    (window,) = ref.contigs.values()
+    records, keepalive = hs.sam_records_of(batch)
+    got, n_kept = hs.pack_reads(records, ref=ref, contig_names=batch.contig_names, n_threads=3)
+    assert n_kept == batch.n_reads
+    c = _columns(got)
+    mm, words = c["mm_count"], c["mm_words"]
+    explicit = np.repeat(c["bases2"], 4)
+    explicit = (explicit >> np.tile(np.array([0, 2, 4, 6], np.uint8), len(c["bases2"]))) & 3  # one 2-bit code per entry
+    code = np.full(256, 255, np.uint8)
+    for i, ch in enumerate(b"ACGT"):
+        code[ch] = i
+    w = e = 0
+    for r in range(batch.n_reads):
+        s0, s1 = int(batch.seq_off[r]), int(batch.seq_off[r + 1])
+        want = code[batch.bases_ascii[s0:s1]]
+        if mm[r] == 255:
+            have = explicit[e:e + s1 - s0]
+            e += s1 - s0
+            n_mask = want > 3  # (not A C G T: travels in the exception list, any code here)
+            assert np.array_equal(have[~n_mask], want[~n_mask]), r
+        else:
+            rel = int(batch.start[r]) - window.offset
+            have = code[window.bases[rel:rel + s1 - s0]].copy()
+            for word in words[w:w + int(mm[r])]:
+                assert word & 3, r
+                have[int(word) >> 2] ^= int(word) & 3
+            w += int(mm[r])
+            assert np.array_equal(have, want), r
+    assert w == c["n_mm_words"] and e == c["n_explicit"]
+    hs.free_packed(got)
+
+
 def test_pack_reads_sorts_a_shuffled_partition():
     batch, _, _ = fixtures.load("tough")
     from guacamole_b200 import partitioning
