@@ -208,6 +208,43 @@ def test_reference_relative_columns_expand_to_the_reads():
     hs.free_packed(got)
 
 
+def test_pack_reads_ref_edge_cases():
+    """Which reads may travel as differences: hand-made reads at the window's edges, on a reference base that is not A C G T,
+    with an N, with = / X operators, with two operators, on a contig without a window — C++ packer and numpy twin agree, and the
+    expected reads are the explicit ones."""
+    from guacamole_b200.io import ContigWindow, Reference
+    from guacamole_b200.reads import ReadBatch, make_read
+    window = np.frombuffer(b"ACGTACGTNNACGTACGTACGTTTGGCCAAACGT", np.uint8).copy()  # offset 100: loci 100..133, N at 108, 109
+    ref = Reference({"c1": ContigWindow("c1", 100, window, 1000)})
+    def seq(lo, hi):
+        return window[lo - 100:hi - 100].tobytes().decode()
+    reads = [
+        make_read(seq(100, 108), "8M", start=100, chr="c1"),                      # 0: first base of the window: relative
+        make_read("T" + seq(101, 108), "8M", start=100, chr="c1"),                # 1: one difference at position 0
+        make_read(seq(104, 112).replace("N", "A"), "8M", start=104, chr="c1"),    # 2: over the N bases of the reference: explicit
+        make_read(seq(110, 118), "8=", start=110, chr="c1"),                      # 3: '=' operator: relative
+        make_read(seq(110, 114) + "A" + seq(115, 118), "4=1X3=", start=110, chr="c1"),  # 4: three operators: explicit
+        make_read(seq(112, 116) + "N" + seq(117, 120), "8M", start=112, chr="c1"),      # 5: an N in the read: explicit
+        make_read(seq(126, 134), "8M", start=126, chr="c1"),                      # 6: ends at the window's last base: relative
+        make_read(seq(127, 134) + "A", "8M", start=127, chr="c1"),                # 7: one base past the window: explicit
+        make_read("ACGTACGT", "8M", start=5, chr="c2"),                           # 8: a contig without a window: explicit
+        make_read("ACGTAC", "2S4M", start=120, chr="c1"),                         # 9: soft clip: explicit
+        make_read("ACGTACGT"[::-1], "8X", start=114, chr="c1"),                   # 10: 'X' operator over all bases: relative
+    ]
+    batch = ReadBatch.from_reads(reads, contig_names=["c1", "c2"])
+    order = sorted(range(len(reads)), key=lambda i: (0 if reads[i].contig == "c1" else 1, reads[i].start, i))
+    records, keepalive = hs.sam_records_of(batch)
+    got, n_kept = hs.pack_reads(records, ref=ref, contig_names=batch.contig_names, n_threads=2)
+    want = compact_struct(batch, ref=ref)
+    cols = _columns(got)
+    _assert_same_columns(cols, _columns(want))
+    explicit_reads = {2, 4, 5, 7, 8, 9}
+    assert [int(m) == 255 for m in cols["mm_count"]] == [i in explicit_reads for i in order]
+    by_read = dict(zip(order, cols["mm_count"]))
+    assert by_read[0] == 0 and by_read[1] == 1 and by_read[3] == 0 and by_read[6] == 0 and by_read[10] > 0
+    hs.free_packed(got)
+
+
 def test_pack_reads_sorts_a_shuffled_partition():
     batch, _, _ = fixtures.load("tough")
     from guacamole_b200 import partitioning
