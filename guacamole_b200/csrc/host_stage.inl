@@ -563,8 +563,10 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       const uint64_t end = std::min<uint64_t>(g1, base_off[(size_t)k + 1]);
       const uint8_t* sb = in->bases_ascii + in->seq_off[i] + (g - base_off[(size_t)k]);
       const uint8_t* sq = in->base_qualities + in->seq_off[i] + (g - base_off[(size_t)k]);
+      // a read that travels as differences has A C G T bases only (no exception to find) and no bases to pack
+      const bool skip_bases = ref_rel && mm_count[(size_t)k] != 255;
       auto one = [&]() {  // one base, read-modify-write of its output bytes
-        const int code = base_lut[*sb];
+        const int code = skip_bases ? 0 : base_lut[*sb];
         if (code >= 4) exc[(size_t)t].push_back({g, *sb});
         else if (!ref_rel) o_bases2[g >> 2] |= (uint8_t)(code << ((g & 3) * 2));
         if (qual_bits == 8) o_qual[g] = *sq;
@@ -573,7 +575,8 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       };
       while (g < end && (g & 3)) one();
       for (; g + 4 <= end; g += 4, sb += 4, sq += 4) {  // four bases per output byte, plain stores
-        const int c0 = base_lut[sb[0]], c1 = base_lut[sb[1]], c2 = base_lut[sb[2]], c3 = base_lut[sb[3]];
+        const int c0 = skip_bases ? 0 : base_lut[sb[0]], c1 = skip_bases ? 0 : base_lut[sb[1]], c2 = skip_bases ? 0 : base_lut[sb[2]],
+                  c3 = skip_bases ? 0 : base_lut[sb[3]];
         if ((c0 | c1 | c2 | c3) < 4) {
           if (!ref_rel) o_bases2[g >> 2] = (uint8_t)(c0 | (c1 << 2) | (c2 << 4) | (c3 << 6));
         } else {
