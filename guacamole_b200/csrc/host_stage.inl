@@ -24,6 +24,22 @@ void host_parallel_for(int n_threads, int64_t n, F fn) {  // fn(lo, hi, thread)
   for (auto& th : pool) th.join();
 }
 
+// An array whose every element the passes below write before anything reads it: no serial zero-fill of tens of megabytes,
+// and the pages are first touched by the threads that use them.
+template <class T>
+struct Uninit {
+  std::unique_ptr<T[]> p;
+  size_t n = 0;
+  void alloc(size_t k) {
+    p.reset(new T[k]);
+    n = k;
+  }
+  T& operator[](size_t i) { return p[i]; }
+  const T& operator[](size_t i) const { return p[i]; }
+  T* begin() { return p.get(); }
+  T* end() { return p.get() + n; }
+};
+
 // memory of guac_pack_reads' outputs: the context's pinned pool (fast H2D) or, without a context, the C heap
 struct PackAlloc {
   guac_ctx* ctx;
@@ -215,8 +231,10 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   if (filters) F = *filters;
   std::memset(out, 0, sizeof *out);
   // 1. Read.apply + ReadSets.filterRDD per record: kept <=> a mapped read that passes every filter
-  std::vector<uint8_t> keep((size_t)N);
-  std::vector<int64_t> ref_len((size_t)N);  // padded reference length (MappedRead.scala:75), for overlapsLoci
+  Uninit<uint8_t> keep;
+  keep.alloc((size_t)N + 1);
+  Uninit<int64_t> ref_len;
+  ref_len.alloc((size_t)N + 1);  // padded reference length (MappedRead.scala:75), for overlapsLoci
   host_parallel_for(n_threads, N, [&](int64_t lo, int64_t hi, int) {
     for (int64_t i = lo; i < hi; ++i) {
       const uint16_t fl = in->sam_flags[i];
@@ -247,17 +265,38 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       keep[(size_t)i] = k;
     }
   });
+  // the kept records' indices, in input order: counts per chunk, their prefix, then every chunk writes its own part
   std::vector<int64_t> idx;
-  idx.reserve((size_t)N);
-  for (int64_t i = 0; i < N; ++i)
-    if (keep[(size_t)i]) idx.push_back(i);
+  {
+    std::vector<int64_t> kept((size_t)n_threads + 1, 0);
+    host_parallel_for(n_threads, N, [&](int64_t lo, int64_t hi, int t) {
+      int64_t c = 0;
+      for (int64_t i = lo; i < hi; ++i) c += keep[(size_t)i];
+      kept[(size_t)t + 1] = c;
+    });
+    for (int t = 0; t < n_threads; ++t) kept[(size_t)t + 1] += kept[(size_t)t];
+    idx.resize((size_t)kept[(size_t)n_threads]);
+    host_parallel_for(n_threads, N, [&](int64_t lo, int64_t hi, int t) {
+      int64_t w = kept[(size_t)t];
+      for (int64_t i = lo; i < hi; ++i)
+        if (keep[(size_t)i]) idx[(size_t)w++] = i;
+    });
+  }
   const int64_t n = (int64_t)idx.size();
   // 2. (contig, start) order, stable (repartitionAndSortWithinPartitions of PartitionedRegions.scala:186-208)
   bool sorted = true;
-  for (int64_t k = 1; k < n && sorted; ++k) {
-    const int64_t a = idx[(size_t)k - 1], b = idx[(size_t)k];
-    sorted = in->reference_index[a] < in->reference_index[b] ||
+  {
+    std::vector<uint8_t> unsorted((size_t)n_threads, 0);
+    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
+      bool ok = true;
+      for (int64_t k = std::max<int64_t>(lo, 1); k < hi && ok; ++k) {  // (k = lo compares across the chunk boundary)
+        const int64_t a = idx[(size_t)k - 1], b = idx[(size_t)k];
+        ok = in->reference_index[a] < in->reference_index[b] ||
              (in->reference_index[a] == in->reference_index[b] && in->alignment_start[a] <= in->alignment_start[b]);
+      }
+      unsorted[(size_t)t] = !ok;
+    });
+    for (uint8_t u : unsorted) sorted = sorted && !u;
   }
   if (!sorted)
     std::stable_sort(idx.begin(), idx.end(), [&](int64_t a, int64_t b) {
@@ -265,9 +304,14 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
       return in->alignment_start[a] < in->alignment_start[b];
     });
   // 3. offsets of the kept reads' bases and CIGAR words; which reads are "one M over all their bases"
-  std::vector<uint64_t> base_off((size_t)n + 1, 0);
-  std::vector<int64_t> wire_off((size_t)n + 1, 0);
-  std::vector<uint8_t> implicit((size_t)n, 0);
+  Uninit<uint64_t> base_off;
+  base_off.alloc((size_t)n + 1);
+  Uninit<int64_t> wire_off;
+  wire_off.alloc((size_t)n + 1);
+  Uninit<uint8_t> implicit;
+  implicit.alloc((size_t)n + 1);
+  base_off[(size_t)n] = 0;  // (n = 0: nothing below writes it)
+  wire_off[(size_t)n] = 0;
   const int64_t len0 = n ? (int64_t)(in->seq_off[idx[0] + 1] - in->seq_off[idx[0]]) : 0;
   // per chunk: lengths, flags and the chunk's totals; then the offsets from the totals' prefix (two passes, all threads)
   struct ChunkTotals {
@@ -329,11 +373,18 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   // contig runs and the narrow start column
   std::vector<int32_t> run_contig;
   std::vector<int64_t> run_first;
-  for (int64_t k = 0; k < n; ++k)
-    if (k == 0 || in->reference_index[idx[(size_t)k]] != in->reference_index[idx[(size_t)k - 1]]) {
-      run_contig.push_back(in->reference_index[idx[(size_t)k]]);
-      run_first.push_back(k);
-    }
+  {
+    std::vector<std::vector<int64_t>> starts((size_t)n_threads);  // run starts found by each chunk, in order
+    host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
+      for (int64_t k = lo; k < hi; ++k)
+        if (k == 0 || in->reference_index[idx[(size_t)k]] != in->reference_index[idx[(size_t)k - 1]]) starts[(size_t)t].push_back(k);
+    });
+    for (auto& v : starts)
+      for (int64_t k : v) {
+        run_contig.push_back(in->reference_index[idx[(size_t)k]]);
+        run_first.push_back(k);
+      }
+  }
   run_first.push_back(n);
   bool narrow_start = n > 0;
   for (size_t r = 0; r + 1 < run_first.size() && narrow_start; ++r)
@@ -373,9 +424,9 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   if (qual_bits == 8) std::memset(out->qual_table, 0, sizeof out->qual_table);  // (no table: one byte per base)
   // 4b. reference-relative bases (guac_read_batch_compact::mm_count): which reads travel as differences, how many words each
   const bool ref_rel = n_refs > 0 && n > 0;
-  std::vector<uint8_t> mm_count;
-  std::vector<uint64_t> expl_off;  // explicit reads' bases, concatenated: offsets over the kept reads (0 bases for the others)
-  std::vector<int64_t> mm_off;
+  Uninit<uint8_t> mm_count;
+  Uninit<uint64_t> expl_off;  // explicit reads' bases, concatenated: offsets over the kept reads (0 bases for the others)
+  Uninit<int64_t> mm_off;
   uint8_t base_code[256];
   std::memset(base_code, 4, sizeof base_code);
   base_code['A'] = 0, base_code['C'] = 1, base_code['G'] = 2, base_code['T'] = 3;
@@ -451,9 +502,9 @@ int pack_reads_impl(guac_ctx* ctx, const guac_sam_records* in, const guac_read_f
   std::vector<std::vector<uint16_t>> thread_words((size_t)n_threads);
   std::vector<int64_t> cw((size_t)n_threads + 1, 0);
   if (ref_rel) {
-    mm_count.assign((size_t)n, 255);
-    expl_off.assign((size_t)n + 1, 0);
-    mm_off.assign((size_t)n + 1, 0);
+    mm_count.alloc((size_t)n + 1);
+    expl_off.alloc((size_t)n + 1);
+    mm_off.alloc((size_t)n + 1);
     std::vector<uint64_t> cb((size_t)n_threads + 1, 0);
     host_parallel_for(n_threads, n, [&](int64_t lo, int64_t hi, int t) {
       uint64_t eb = 0;
